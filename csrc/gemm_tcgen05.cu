@@ -1,0 +1,268 @@
+// Persistent, warp-specialised bf16 GEMM on 5th-gen tensor cores (tcgen05 + TMEM + TMA), sm_100a.
+//
+//   D[M, N] (+)= A_op[M, K] * B_op[N, K]^T       (fp32 accumulate in TMEM; D bf16 or fp32)
+//
+// This is the compute core behind ColumnParallelLinear / RowParallelLinear forward, dgrad and
+// wgrad (reference src/neuronx_distributed/parallel_layers/layers.py:325,348,409 -- plain
+// torch.matmul lowered by XLA).  The three operand layouts are handled with the operand-major
+// bits of the UMMA descriptors, never with transposed copies:
+//     "nt"  A = X[M,K]   (K-major)    B = W[N,K]   (K-major)      forward
+//     "nn"  A = dY[M,K]  (K-major)    B = W[K,N]   (MN-major)     dgrad
+//     "tn"  A = dY[K,M]  (MN-major)   B = X[K,N]   (MN-major)     wgrad
+//
+// Structure (one CTA pair = one cluster of 2 CTAs = one 256 x BLOCK_N output tile):
+//   warp 0   TMA producer: each CTA loads its 128 rows of A and its BLOCK_N/2 rows of B per
+//            64-wide K block into a kStages-deep smem ring (SWIZZLE_128B); transaction bytes of
+//            both CTAs are credited to the LEADER CTA's "full" mbarrier.
+//   warp 1   MMA issuer (leader CTA only, one elected lane): tcgen05.mma.cta_group::2 with
+//            M=256, N=BLOCK_N, K=16; tcgen05.commit (multicast to both CTAs) releases smem slots
+//            and publishes finished accumulators.
+//   warp 2   TMEM allocator (2 accumulator stages x BLOCK_N fp32 columns).
+//   warps 4-7 epilogue: tcgen05.ld the 128 x BLOCK_N accumulator (lane = row), convert, store.
+//            The accumulator is double buffered so the epilogue of tile i overlaps the main
+//            loop of tile i+1.
+// Tiles are visited persistently (grid = #SM/2 clusters) in an L2-friendly grouped order.
+#include "common.cuh"
+#include "gemm_tcgen05.cuh"
+#include "ptx.cuh"
+
+namespace nxd_gemm {
+
+template <int BN, bool A_MN, bool B_MN, int OUT_MODE>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
+gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+                 const EpilogueArgs ep, int M, int N, int K) {
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    using L = SmemLayout<BN>;
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + L::kBarrierOffset);
+    constexpr int kStages = L::kStages;
+    uint64_t* empty_bar = full_bar + kStages;
+    uint64_t* tmem_full_bar = empty_bar + kStages;
+    uint64_t* tmem_empty_bar = tmem_full_bar + kAccStages;
+    uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(tmem_empty_bar + kAccStages);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const uint32_t cta_rank = ptx::cluster_ctarank();
+    const bool is_leader = cta_rank == 0;
+
+    const int num_m_tiles = (M + kTileM - 1) / kTileM;
+    const int num_n_tiles = (N + BN - 1) / BN;
+    const int num_tiles = num_m_tiles * num_n_tiles;
+    const int num_k_blocks = (K + kBlockK - 1) / kBlockK;
+    const int cluster_id = blockIdx.x >> 1;
+    const int num_clusters = gridDim.x >> 1;
+
+    if (warp == 0 && lane == 0) {
+        ptx::prefetch_tensormap(&tmap_a);
+        ptx::prefetch_tensormap(&tmap_b);
+    }
+    if (warp == 1 && lane == 0) {
+        for (int i = 0; i < kStages; ++i) {
+            ptx::mbar_init(&full_bar[i], 1);
+            ptx::mbar_init(&empty_bar[i], 1);
+        }
+        for (int i = 0; i < kAccStages; ++i) {
+            ptx::mbar_init(&tmem_full_bar[i], 1);
+            ptx::mbar_init(&tmem_empty_bar[i], 2 * kEpilogueWarps);  // both CTAs' epilogue warps
+        }
+        ptx::fence_barrier_init();
+    }
+    if (warp == 2) ptx::tmem_alloc<2>(tmem_ptr_smem, L::kTmemCols);
+    ptx::tcgen05_fence_before();
+    ptx::cluster_sync();
+    ptx::tcgen05_fence_after();
+    const uint32_t tmem_base = *tmem_ptr_smem;
+
+    if (warp == 0) {
+        // ======================= TMA producer =======================
+        if (lane == 0) {
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
+                int tm, tn;
+                tile_coords(tile, num_m_tiles, num_n_tiles, tm, tn);
+                const int m0 = tm * kTileM + (int)cta_rank * kBlockM;
+                const int n0 = tn * BN + (int)cta_rank * (BN / 2);
+                for (int kb = 0; kb < num_k_blocks; ++kb) {
+                    ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
+                    uint8_t* sa = smem + stage * L::kStageBytes;
+                    uint8_t* sb = sa + L::kABytes;
+                    const int k0 = kb * kBlockK;
+                    if (is_leader) ptx::mbar_arrive_expect_tx(&full_bar[stage], 2 * L::kStageBytes);
+                    if constexpr (!A_MN) {
+                        ptx::tma_load_2d_pair(&tmap_a, &full_bar[stage], sa, k0, m0);
+                    } else {
+#pragma unroll
+                        for (int g = 0; g < kBlockM / 64; ++g)
+                            ptx::tma_load_2d_pair(&tmap_a, &full_bar[stage], sa + g * (kBlockK * 128), m0 + g * 64,
+                                                  k0);
+                    }
+                    if constexpr (!B_MN) {
+                        ptx::tma_load_2d_pair(&tmap_b, &full_bar[stage], sb, k0, n0);
+                    } else {
+#pragma unroll
+                        for (int g = 0; g < (BN / 2) / 64; ++g)
+                            ptx::tma_load_2d_pair(&tmap_b, &full_bar[stage], sb + g * (kBlockK * 128), n0 + g * 64,
+                                                  k0);
+                    }
+                    if (++stage == kStages) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ======================= MMA issuer (leader CTA) =======================
+        if (is_leader && lane == 0) {
+            constexpr uint32_t idesc = ptx::make_idesc_bf16(kTileM, BN, A_MN ? 1 : 0, B_MN ? 1 : 0);
+            // K-major: 8-row groups 1024 B apart; step 32 B per UMMA_K inside the 128 B swizzle row.
+            // MN-major: 64-element MN groups kBlockK*128 B apart (LBO), 8-k-row groups 1024 B apart
+            // (SBO); step 16 k-rows = 2048 B per UMMA_K.
+            constexpr uint32_t a_lbo = A_MN ? kBlockK * 128 : 16, b_lbo = B_MN ? kBlockK * 128 : 16;
+            constexpr uint32_t a_kstep = A_MN ? 2048 : 32, b_kstep = B_MN ? 2048 : 32;
+            int stage = 0;
+            uint32_t phase = 0;
+            int acc = 0;
+            uint32_t acc_phase = 0;
+            for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
+                ptx::mbar_wait_cluster(&tmem_empty_bar[acc], acc_phase ^ 1);
+                ptx::tcgen05_fence_after();
+                const uint32_t tmem_d = tmem_base + acc * BN;
+                for (int kb = 0; kb < num_k_blocks; ++kb) {
+                    ptx::mbar_wait_cluster(&full_bar[stage], phase);
+                    ptx::tcgen05_fence_after();
+                    const uint32_t sa = ptx::smem_u32(smem + stage * L::kStageBytes);
+                    const uint32_t sb = sa + L::kABytes;
+#pragma unroll
+                    for (int k = 0; k < kBlockK / 16; ++k) {
+                        const uint64_t da = ptx::make_smem_desc(sa + k * a_kstep, a_lbo, 1024);
+                        const uint64_t db = ptx::make_smem_desc(sb + k * b_kstep, b_lbo, 1024);
+                        ptx::umma_bf16<2>(tmem_d, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
+                    }
+                    ptx::umma_commit_pair(&empty_bar[stage], 0b11);  // frees the slot in both CTAs
+                    if (++stage == kStages) { stage = 0; phase ^= 1; }
+                }
+                ptx::umma_commit_pair(&tmem_full_bar[acc], 0b11);  // accumulator ready (both CTAs)
+                if (++acc == kAccStages) { acc = 0; acc_phase ^= 1; }
+            }
+        }
+    } else if (warp >= kFirstEpilogueWarp) {
+        // ======================= epilogue =======================
+        const int q = warp & 3;  // TMEM lane quadrant this warp may access
+        int acc = 0;
+        uint32_t acc_phase = 0;
+        for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
+            int tm, tn;
+            tile_coords(tile, num_m_tiles, num_n_tiles, tm, tn);
+            const int row = tm * kTileM + (int)cta_rank * kBlockM + q * 32 + lane;
+            const int n0 = tn * BN;
+            ptx::mbar_wait(&tmem_full_bar[acc], acc_phase);
+            ptx::tcgen05_fence_after();
+            const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + acc * BN;
+#pragma unroll 1
+            for (int c = 0; c < BN / 32; ++c) {
+                uint32_t r[32];
+                ptx::tmem_ld_32x32b_x32(taddr + c * 32, r);
+                ptx::tmem_ld_wait();
+                store_chunk<OUT_MODE>(ep, r, row, n0 + c * 32, M, N);
+            }
+            ptx::tcgen05_fence_before();
+            __syncwarp();
+            if (lane == 0) ptx::mbar_arrive_cluster(&tmem_empty_bar[acc], 0);
+            if (++acc == kAccStages) { acc = 0; acc_phase ^= 1; }
+        }
+    }
+
+    // ---- teardown: both CTAs must be done with TMEM (and with remote barrier traffic) ----
+    ptx::tcgen05_fence_before();
+    ptx::cluster_sync();
+    if (warp == 2) ptx::tmem_dealloc<2>(tmem_base, L::kTmemCols);
+}
+
+// ---------------------------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------------------------
+
+template <int BN, bool A_MN, bool B_MN, int OUT_MODE>
+static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const EpilogueArgs& ep, int M, int N, int K,
+                  cudaStream_t stream) {
+    using L = SmemLayout<BN>;
+    auto kern = gemm_pair_kernel<BN, A_MN, B_MN, OUT_MODE>;
+    static bool configured = false;
+    if (!configured) {
+        NXD_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kSmemBytes));
+        configured = true;
+    }
+    const int num_tiles = ((M + kTileM - 1) / kTileM) * ((N + BN - 1) / BN);
+    int clusters = nxd_num_sms() / 2;
+    if (clusters > num_tiles) clusters = num_tiles;
+    kern<<<dim3(clusters * 2), dim3(kThreads), L::kSmemBytes, stream>>>(ta, tb, ep, M, N, K);
+    NXD_LAUNCH_CHECK();
+    return 0;
+}
+
+template <int BN, int OUT_MODE>
+static int dispatch_layout(int layout, const CUtensorMap& ta, const CUtensorMap& tb, const EpilogueArgs& ep, int M,
+                           int N, int K, cudaStream_t s) {
+    switch (layout) {
+        case kLayoutNT: return launch<BN, false, false, OUT_MODE>(ta, tb, ep, M, N, K, s);
+        case kLayoutNN: return launch<BN, false, true, OUT_MODE>(ta, tb, ep, M, N, K, s);
+        default: return launch<BN, true, true, OUT_MODE>(ta, tb, ep, M, N, K, s);
+    }
+}
+
+int pick_block_n(int M, int N) {
+    // Fewer, fatter tiles amortise operand traffic (256 x 256 per CTA pair is the sweet spot), but a
+    // partial last wave wastes SMs: estimate cost = waves * tile_n for both candidates.
+    const int clusters = nxd_num_sms() / 2;
+    const int mt = (M + kTileM - 1) / kTileM;
+    const long t256 = (long)mt * ((N + 255) / 256), t128 = (long)mt * ((N + 127) / 128);
+    const long w256 = (t256 + clusters - 1) / clusters, w128 = (t128 + clusters - 1) / clusters;
+    // a 128-wide tile runs at ~0.55x the time of a 256-wide one (less operand reuse)
+    return (w256 * 100 <= w128 * 55) ? 256 : 128;
+}
+
+int run(int layout, const void* a, const void* b, long long lda, long long ldb, const EpilogueArgs& ep, int M, int N,
+        int K, int block_n, cudaStream_t stream) {
+    NXD_REQUIRE(layout >= 0 && layout <= 2, "gemm: bad layout %d", layout);
+    NXD_REQUIRE(M > 0 && N > 0 && K > 0, "gemm: empty problem %dx%dx%d", M, N, K);
+    NXD_REQUIRE(lda % 8 == 0 && ldb % 8 == 0 && ep.ldd % 8 == 0, "gemm: leading dims must be multiples of 8 elements");
+    NXD_REQUIRE(((uintptr_t)a & 15) == 0 && ((uintptr_t)b & 15) == 0 && ((uintptr_t)ep.d & 15) == 0,
+                "gemm: operands must be 16-byte aligned");
+    const bool a_mn = layout == kLayoutTN;
+    const bool b_mn = layout != kLayoutNT;
+    const int bn = block_n > 0 ? block_n : pick_block_n(M, N);
+    NXD_REQUIRE(bn == 128 || bn == 256, "gemm: block_n must be 128 or 256");
+    CUtensorMap ta, tb;
+    int rc;
+    // A: K-major -> global [M rows, K cols], box {64 k, 128 rows}; MN-major -> global [K rows, M cols], box {64 m, 64 k}
+    if (!a_mn) rc = make_tmap_2d(&ta, a, (uint64_t)K, (uint64_t)M, (uint64_t)lda, 64, kBlockM);
+    else rc = make_tmap_2d(&ta, a, (uint64_t)M, (uint64_t)K, (uint64_t)lda, 64, kBlockK);
+    if (rc) return rc;
+    if (!b_mn) rc = make_tmap_2d(&tb, b, (uint64_t)K, (uint64_t)N, (uint64_t)ldb, 64, bn / 2);
+    else rc = make_tmap_2d(&tb, b, (uint64_t)N, (uint64_t)K, (uint64_t)ldb, 64, kBlockK);
+    if (rc) return rc;
+#define NXD_GEMM_DISPATCH(BN_)                                                                           \
+    switch (ep.mode) {                                                                                   \
+        case kOutBF16: return dispatch_layout<BN_, kOutBF16>(layout, ta, tb, ep, M, N, K, stream);       \
+        case kOutF32: return dispatch_layout<BN_, kOutF32>(layout, ta, tb, ep, M, N, K, stream);         \
+        case kOutF32Acc: return dispatch_layout<BN_, kOutF32Acc>(layout, ta, tb, ep, M, N, K, stream);   \
+        default: nxd_set_error("gemm: bad output mode %d", ep.mode); return -1;                          \
+    }
+    if (bn == 256) { NXD_GEMM_DISPATCH(256) }
+    NXD_GEMM_DISPATCH(128)
+#undef NXD_GEMM_DISPATCH
+}
+
+}  // namespace nxd_gemm
+
+// C-ABI: layout 0 = nt, 1 = nn, 2 = tn (see header).  out_mode 0 = bf16, 1 = fp32, 2 = fp32 accumulate.
+// lda / ldb / ldd are row pitches in elements of the row-major operands as they sit in memory.
+NXD_API int nxd_gemm_bf16(int layout, const void* a, const void* b, void* d, int M, int N, int K, long long lda,
+                          long long ldb, long long ldd, int out_mode, int block_n, void* stream) {
+    nxd_gemm::EpilogueArgs ep{};
+    ep.d = d;
+    ep.ldd = ldd;
+    ep.mode = out_mode;
+    return nxd_gemm::run(layout, a, b, lda, ldb, ep, M, N, K, block_n, (cudaStream_t)stream);
+}

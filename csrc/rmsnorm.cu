@@ -1,0 +1,248 @@
+// RMSNorm forward / backward for sm_100a.
+//
+// Replaces the reference's fp64-upcast torch ops
+// (examples/training/llama/modeling_llama_nxd.py:142-149) and the inference
+// `RmsNorm` custom call (examples/inference/modules/custom_calls.py:5-16).
+//
+// Layout: x [rows, H] bf16 row-major, H % 8 == 0.  One CTA per row keeps the row
+// in registers as fp32 between the sum-of-squares pass and the scale pass, so HBM
+// traffic is exactly one read + one write of the activation (HBM-bound op).
+// Optional fused residual add:  s = x + r;  y = rmsnorm(s);  s is also written.
+//
+// Backward: dx = rstd * (g - xhat * mean(g * xhat)),  g = dy * w,  xhat = x * rstd
+//           dw = sum_rows(dy * xhat)   -> persistent CTAs accumulate per-thread
+//           partials in registers, write [P, H] fp32 partials to scratch, and a
+//           second kernel reduces the P partial rows.
+#include "common.cuh"
+
+namespace {
+
+template <int VPT>  // 16-byte vectors per thread
+__global__ void rmsnorm_fwd_kernel(const bf16* __restrict__ x, const bf16* __restrict__ res,
+                                   const bf16* __restrict__ w, bf16* __restrict__ y,
+                                   bf16* __restrict__ res_out, float* __restrict__ rstd_out, int H,
+                                   float eps) {
+    __shared__ float red[32];
+    const int row = blockIdx.x;
+    const int nvec = H >> 3;
+    const bf16x8* xr = reinterpret_cast<const bf16x8*>(x + (size_t)row * H);
+    const bf16x8* rr = res ? reinterpret_cast<const bf16x8*>(res + (size_t)row * H) : nullptr;
+    float v[VPT][8];
+    float ss = 0.f;
+#pragma unroll
+    for (int i = 0; i < VPT; ++i) {
+        const int c = threadIdx.x + i * blockDim.x;
+        if (c < nvec) {
+            bf16x8 p = xr[c];
+            unpack8(p, v[i]);
+            if (rr) {
+                float r[8];
+                bf16x8 q = rr[c];
+                unpack8(q, r);
+#pragma unroll
+                for (int k = 0; k < 8; ++k) v[i][k] += r[k];
+                if (res_out) {
+                    // round the residual stream to bf16 once, and normalise the rounded value
+                    bf16x8 s = pack8(v[i]);
+                    reinterpret_cast<bf16x8*>(res_out + (size_t)row * H)[c] = s;
+                    unpack8(s, v[i]);
+                }
+            }
+#pragma unroll
+            for (int k = 0; k < 8; ++k) ss += v[i][k] * v[i][k];
+        }
+    }
+    ss = block_sum(ss, red);
+    const float rstd = rsqrtf(ss / (float)H + eps);
+    if (threadIdx.x == 0 && rstd_out) rstd_out[row] = rstd;
+    const bf16x8* wr = reinterpret_cast<const bf16x8*>(w);
+    bf16x8* yr = reinterpret_cast<bf16x8*>(y + (size_t)row * H);
+#pragma unroll
+    for (int i = 0; i < VPT; ++i) {
+        const int c = threadIdx.x + i * blockDim.x;
+        if (c < nvec) {
+            float wv[8], o[8];
+            bf16x8 p = wr[c];
+            unpack8(p, wv);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) o[k] = v[i][k] * rstd * wv[k];
+            yr[c] = pack8(o);
+        }
+    }
+}
+
+template <int VPT>
+__global__ void rmsnorm_bwd_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ x,
+                                   const bf16* __restrict__ w, const float* __restrict__ rstd,
+                                   const bf16* __restrict__ dres, bf16* __restrict__ dx,
+                                   float* __restrict__ dw_partial, int rows, int H) {
+    __shared__ float red[32];
+    const int nvec = H >> 3;
+    float wv[VPT][8], dwacc[VPT][8];
+    const bf16x8* wr = reinterpret_cast<const bf16x8*>(w);
+#pragma unroll
+    for (int i = 0; i < VPT; ++i) {
+        const int c = threadIdx.x + i * blockDim.x;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) dwacc[i][k] = 0.f;
+        if (c < nvec) {
+            bf16x8 p = wr[c];
+            unpack8(p, wv[i]);
+        }
+    }
+    for (int row = blockIdx.x; row < rows; row += gridDim.x) {
+        const bf16x8* dyr = reinterpret_cast<const bf16x8*>(dy + (size_t)row * H);
+        const bf16x8* xr = reinterpret_cast<const bf16x8*>(x + (size_t)row * H);
+        const float rs = rstd[row];
+        float g[VPT][8], xh[VPT][8];
+        float dot = 0.f;
+#pragma unroll
+        for (int i = 0; i < VPT; ++i) {
+            const int c = threadIdx.x + i * blockDim.x;
+            if (c < nvec) {
+                float d[8], xv[8];
+                bf16x8 p = dyr[c];
+                unpack8(p, d);
+                bf16x8 q = xr[c];
+                unpack8(q, xv);
+#pragma unroll
+                for (int k = 0; k < 8; ++k) {
+                    xh[i][k] = xv[k] * rs;
+                    g[i][k] = d[k] * wv[i][k];
+                    dot += g[i][k] * xh[i][k];
+                    dwacc[i][k] += d[k] * xh[i][k];
+                }
+            }
+        }
+        dot = block_sum(dot, red) / (float)H;
+        bf16x8* dxr = reinterpret_cast<bf16x8*>(dx + (size_t)row * H);
+        const bf16x8* drr = dres ? reinterpret_cast<const bf16x8*>(dres + (size_t)row * H) : nullptr;
+#pragma unroll
+        for (int i = 0; i < VPT; ++i) {
+            const int c = threadIdx.x + i * blockDim.x;
+            if (c < nvec) {
+                float o[8];
+#pragma unroll
+                for (int k = 0; k < 8; ++k) o[k] = rs * (g[i][k] - xh[i][k] * dot);
+                if (drr) {  // fused add of the gradient flowing through the residual branch
+                    float r[8];
+                    bf16x8 q = drr[c];
+                    unpack8(q, r);
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) o[k] += r[k];
+                }
+                dxr[c] = pack8(o);
+            }
+        }
+    }
+    float* out = dw_partial + (size_t)blockIdx.x * H;
+#pragma unroll
+    for (int i = 0; i < VPT; ++i) {
+        const int c = threadIdx.x + i * blockDim.x;
+        if (c < nvec) {
+            float4* o4 = reinterpret_cast<float4*>(out + (size_t)c * 8);
+            o4[0] = make_float4(dwacc[i][0], dwacc[i][1], dwacc[i][2], dwacc[i][3]);
+            o4[1] = make_float4(dwacc[i][4], dwacc[i][5], dwacc[i][6], dwacc[i][7]);
+        }
+    }
+}
+
+// dw[h] = sum_p partial[p, h]; optionally accumulates into an fp32 buffer.
+__global__ void colsum_partials_kernel(const float* __restrict__ partial, int P, int H,
+                                       bf16* __restrict__ dw_bf16, float* __restrict__ dw_f32,
+                                       int accumulate) {
+    const int h = blockIdx.x * blockDim.x + threadIdx.x;
+    if (h >= H) return;
+    float s = 0.f;
+    for (int p = 0; p < P; ++p) s += partial[(size_t)p * H + h];
+    if (dw_f32) dw_f32[h] = accumulate ? dw_f32[h] + s : s;
+    if (dw_bf16) dw_bf16[h] = __float2bfloat16(s);
+}
+
+struct NormCfg {
+    int threads;
+    int vpt;
+};
+
+NormCfg pick_cfg(int H) {
+    const int nvec = H / 8;
+    NormCfg c;
+    if (nvec <= 128) {
+        c.vpt = 1;
+    } else if (nvec <= 512) {
+        c.vpt = 2;
+    } else if (nvec <= 2048) {
+        c.vpt = 4;
+    } else {
+        c.vpt = 8;
+    }
+    int t = (nvec + c.vpt - 1) / c.vpt;
+    t = ((t + 31) / 32) * 32;
+    if (t > 1024) t = 1024;
+    if (t < 32) t = 32;
+    c.threads = t;
+    return c;
+}
+
+}  // namespace
+
+// Number of partial rows (persistent CTAs) the backward kernel uses; the scratch
+// buffer passed to nxd_rmsnorm_bwd must hold nxd_rmsnorm_bwd_num_partials * H floats.
+NXD_API int nxd_rmsnorm_bwd_num_partials(int rows) {
+    int p = nxd_num_sms() * 4;
+    if (p > rows) p = rows;
+    if (p < 1) p = 1;
+    return p;
+}
+
+NXD_API int nxd_rmsnorm_fwd(const void* x, const void* residual, const void* w, void* y, void* residual_out,
+                            float* rstd, int rows, int H, float eps, void* stream) {
+    NXD_REQUIRE(H % 8 == 0 && H <= 65536, "rmsnorm: H=%d must be a multiple of 8 and <= 65536", H);
+    if (rows == 0) return 0;
+    NormCfg c = pick_cfg(H);
+    cudaStream_t s = (cudaStream_t)stream;
+#define LAUNCH(V)                                                                                          \
+    rmsnorm_fwd_kernel<V><<<rows, c.threads, 0, s>>>((const bf16*)x, (const bf16*)residual, (const bf16*)w, \
+                                                     (bf16*)y, (bf16*)residual_out, rstd, H, eps)
+    switch (c.vpt) {
+        case 1: LAUNCH(1); break;
+        case 2: LAUNCH(2); break;
+        case 4: LAUNCH(4); break;
+        default: LAUNCH(8); break;
+    }
+#undef LAUNCH
+    NXD_LAUNCH_CHECK();
+    return 0;
+}
+
+static int rmsnorm_bwd_impl(const void* dy, const void* x, const void* w, const float* rstd, const void* dresidual,
+                            void* dx, void* dw_bf16, float* dw_f32, int accumulate, float* scratch, int rows,
+                            int H, cudaStream_t s) {
+    NormCfg c = pick_cfg(H);
+    const int P = nxd_rmsnorm_bwd_num_partials(rows);
+#define LAUNCH(V)                                                                                        \
+    rmsnorm_bwd_kernel<V><<<P, c.threads, 0, s>>>((const bf16*)dy, (const bf16*)x, (const bf16*)w, rstd, \
+                                                  (const bf16*)dresidual, (bf16*)dx, scratch, rows, H)
+    switch (c.vpt) {
+        case 1: LAUNCH(1); break;
+        case 2: LAUNCH(2); break;
+        case 4: LAUNCH(4); break;
+        default: LAUNCH(8); break;
+    }
+#undef LAUNCH
+    NXD_LAUNCH_CHECK();
+    colsum_partials_kernel<<<(H + 255) / 256, 256, 0, s>>>(scratch, P, H, (bf16*)dw_bf16, dw_f32, accumulate);
+    NXD_LAUNCH_CHECK();
+    return 0;
+}
+
+// scratch: caller-provided device buffer of nxd_rmsnorm_bwd_num_partials(rows) * H floats.
+NXD_API int nxd_rmsnorm_bwd(const void* dy, const void* x, const void* w, const float* rstd,
+                            const void* dresidual, void* dx, void* dw_bf16, float* dw_f32, int accumulate,
+                            float* scratch, int rows, int H, void* stream) {
+    NXD_REQUIRE(H % 8 == 0 && H <= 65536, "rmsnorm_bwd: H=%d must be a multiple of 8 and <= 65536", H);
+    NXD_REQUIRE(scratch != nullptr, "rmsnorm_bwd: scratch buffer is required");
+    if (rows == 0) return 0;
+    return rmsnorm_bwd_impl(dy, x, w, rstd, dresidual, dx, dw_bf16, dw_f32, accumulate, scratch, rows, H,
+                            (cudaStream_t)stream);
+}

@@ -1,0 +1,96 @@
+/* nxd_b200 -- C ABI of the sm_100a kernel library (libnxd_b200.so).
+ *
+ * Conventions: every function returns 0 on success, a cudaError_t value or -1 otherwise
+ * (nxd_last_error() gives the message of the last failure on the calling thread).  Pointers
+ * are device pointers unless stated otherwise; `stream` is a cudaStream_t; bf16 tensors are
+ * row-major with the stated shape.  No entry point allocates device memory: scratch buffers
+ * are passed by the caller (their sizes come from the *_num_* helpers).
+ * The "reference" citations name the file:line of the upstream NeuronxDistributed code whose
+ * behaviour the kernel provides on B200.
+ */
+#ifndef NXD_B200_H
+#define NXD_B200_H
+
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- runtime ---------------------------------------------------------------------------- */
+const char* nxd_last_error(void);
+int nxd_version(void);
+int nxd_device_sm_count(void);
+/* Overwrite `bytes` of `buf` (> L2 size) so the next timed iteration starts with a cold L2. */
+int nxd_l2_flush(void* buf, size_t bytes, void* stream);
+
+/* ---- GEMM: D[M,N] (+)= A_op[M,K] * B_op[N,K]^T on tcgen05/TMEM/TMA -------------------------
+ * reference: parallel_layers/layers.py:325 (fwd), :348 (dgrad), :409 (wgrad) -- torch.matmul.
+ * layout 0 "nt": a = [M,K], b = [N,K];  1 "nn": a = [M,K], b = [K,N];  2 "tn": a = [K,M], b = [K,N].
+ * lda/ldb/ldd: row pitch in elements of the tensors as stored.  out_mode 0 bf16, 1 fp32,
+ * 2 fp32 accumulate (d += result).  block_n 0 = auto, else 128 or 256. */
+int nxd_gemm_bf16(int layout, const void* a, const void* b, void* d, int M, int N, int K, long long lda,
+                  long long ldb, long long ldd, int out_mode, int block_n, void* stream);
+
+/* ---- RMSNorm (reference: examples/training/llama/modeling_llama_nxd.py:142-149;
+ *      examples/inference/modules/custom_calls.py:5-16) ---------------------------------------- */
+int nxd_rmsnorm_fwd(const void* x, const void* residual, const void* w, void* y, void* residual_out,
+                    float* rstd, int rows, int H, float eps, void* stream);
+int nxd_rmsnorm_bwd_num_partials(int rows);
+/* scratch: nxd_rmsnorm_bwd_num_partials(rows) * H floats */
+int nxd_rmsnorm_bwd(const void* dy, const void* x, const void* w, const float* rstd, const void* dresidual,
+                    void* dx, void* dw_bf16, float* dw_f32, int accumulate, float* scratch, int rows, int H,
+                    void* stream);
+
+/* ---- SwiGLU / RoPE (reference: modeling_llama_nxd.py:197-208, :398-399;
+ *      examples/inference/modules/attention/utils.py:27-41) ------------------------------------- */
+int nxd_swiglu_fwd(const void* gate_up, void* out, long long rows, int I, void* stream);
+int nxd_swiglu_bwd(const void* gate_up, const void* dy, void* dgate_up, long long rows, int I, void* stream);
+int nxd_rope_inplace(void* x, const float* cos_t, const float* sin_t, const int* positions, long long T,
+                     int heads_total, int n_rot_heads, int D, int pos_div, int pos_mod, int inverse,
+                     void* stream);
+
+/* ---- vocab-parallel cross entropy (reference: parallel_layers/loss_functions.py:11-130) ------- */
+int nxd_ce_stats(const void* logits, const long long* target, float* stats, long long T, int V, int vocab_start,
+                 void* stream);
+int nxd_ce_bwd(const void* logits, const long long* target, const float* lse, const float* grad_out,
+               void* grad_logits, long long T, int V, int vocab_start, float smoothing, int vocab_global,
+               void* stream);
+
+/* ---- optimizer / grad-norm (reference: optimizer/zero_redundancy_optimizer.py:29-156,
+ *      utils/adamw_fp32_optim_params.py:88-153, parallel_layers/grads.py:33-240) ----------------- */
+int nxd_sumsq_num_partials(void);
+int nxd_sumsq(const void* x, long long n, int dtype, float* scratch, float* out, int accumulate, void* stream);
+int nxd_clip_coef(const float* total_sumsq, float max_norm, float* coef, float* norm_out, void* stream);
+int nxd_adamw_step(float* master, float* exp_avg, float* exp_avg_sq, const void* grad, int grad_dtype,
+                   void* param_out, long long n, float lr, float beta1, float beta2, float eps,
+                   float weight_decay, int step, float grad_scale, const float* clip_coef, void* stream);
+int nxd_scale_inplace(void* x, long long n, int dtype, float scale, const float* dev_scale, void* stream);
+
+/* ---- sampling (reference: utils/sampling.py:27-77) -------------------------------------------- */
+int nxd_argmax(const void* logits, int dtype, int B, int V, long long row_stride, long long* out, void* stream);
+int nxd_topk_sample(const void* logits, int dtype, int B, int V, long long row_stride, int top_k, float top_p,
+                    float temperature, const float* uniform, long long* out, void* stream);
+
+/* ---- decode attention + KV cache (reference: examples/inference/modules/attention/
+ *      attention_base.py:141-170; modules/model_base.py:388-422) -------------------------------- */
+int nxd_decode_attn_num_splits(int B, int n_kv, int max_len);
+/* scratch: B * n_q * n_splits * (D + 2) floats */
+int nxd_decode_attn(const void* q, const void* cache_k, const void* cache_v, const int* lengths,
+                    const int* block_table, long long stride_b, long long stride_h, int page_size,
+                    int max_pages, void* out, float* scratch, int B, int n_q, int n_kv, int D, int n_splits,
+                    float scale, void* stream);
+int nxd_kv_cache_update(const void* new_k, const void* new_v, void* cache_k, void* cache_v, const int* positions,
+                        const int* seq_ids, const int* block_table, long long stride_b, long long stride_h,
+                        int page_size, int max_pages, int B, int n_kv, int T_new, int D, void* stream);
+
+/* ---- embedding (reference: parallel_layers/layers.py:215-238) ---------------------------------- */
+int nxd_embedding_fwd(const long long* ids, const void* weight, void* out, long long T, int H, int vocab_start,
+                      int vocab_local, int B, int S, int seq_first_out, void* stream);
+int nxd_embedding_bwd(const long long* ids, const void* dy, float* dw, long long T, int H, int vocab_start,
+                      int vocab_local, int B, int S, int seq_first_in, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NXD_B200_H */

@@ -1,0 +1,161 @@
+"""Attention ops.
+
+* ``flash_attn_func`` -- training / prefill causal attention with native GQA.  API parity with the
+  reference's ``nki_flash_attn_func(q, k, v, dropout_p, softmax_scale, causal, ...)``
+  (``src/neuronx_distributed/kernels/flash_attn.py:151-191``; tensors ``[B, H, S, D]``), without its
+  ``S % 2048`` restriction and without ``repeat_kv`` (the reference expands KV heads first,
+  ``examples/training/llama/modeling_llama_nxd.py:409-410``).
+* ``decode_attention`` / ``kv_cache_update`` -- token generation over a contiguous or paged cache.
+
+Backends for ``flash_attn_func`` (``NXD_ATTN_BACKEND``):
+  ``nxd``   hand-written sm_100a tcgen05 kernel (``csrc/flash_attn_tcgen05.cu``)  [default on GPU]
+  ``sdpa``  ``torch.nn.functional.scaled_dot_product_attention`` -- library call, used only as the
+            baseline arm and as the numerics oracle
+  ``ref``   plain fp32 PyTorch math (CPU tests)
+"""
+from __future__ import annotations
+
+import ctypes as _c
+import math
+import os
+from typing import Optional
+
+import torch
+import torch.nn.functional as F
+
+from . import _lib
+
+
+def attention_ref(q, k, v, causal=True, softmax_scale=None):
+    """fp32 reference.  q [B,Hq,S,D], k/v [B,Hkv,Sk,D]."""
+    B, Hq, S, D = q.shape
+    Hkv = k.shape[1]
+    scale = softmax_scale if softmax_scale is not None else 1.0 / math.sqrt(D)
+    g = Hq // Hkv
+    kf = k.float().repeat_interleave(g, dim=1)
+    vf = v.float().repeat_interleave(g, dim=1)
+    s = torch.matmul(q.float(), kf.transpose(-1, -2)) * scale
+    if causal:
+        Sk = k.shape[2]
+        mask = torch.ones(S, Sk, dtype=torch.bool, device=q.device).tril(diagonal=Sk - S)
+        s = s.masked_fill(~mask, float("-inf"))
+    p = torch.softmax(s, dim=-1)
+    return torch.matmul(p, vf).to(q.dtype)
+
+
+def _backend(q: torch.Tensor) -> str:
+    if not q.is_cuda:
+        return "ref"
+    be = os.environ.get("NXD_ATTN_BACKEND", "nxd")
+    if be == "nxd" and not (_lib.available() and hasattr(_lib.lib(), "nxd_flash_attn_fwd")
+                            and q.dtype == torch.bfloat16 and q.shape[-1] in (64, 128)):
+        return "sdpa"
+    return be
+
+
+def flash_attn_func(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, dropout_p: float = 0.0,
+                    softmax_scale: Optional[float] = None, causal: bool = True, mixed_precision: bool = True,
+                    seed: Optional[int] = None) -> torch.Tensor:
+    """q ``[B, Hq, S, D]``, k/v ``[B, Hkv, S, D]`` (any strides with unit stride on D) -> ``[B, Hq, S, D]``."""
+    assert dropout_p == 0.0, "attention dropout is not implemented (Llama-3.x trains with 0.0)"
+    be = _backend(q)
+    if be == "nxd":
+        from .flash_attn import flash_attn_nxd
+
+        return flash_attn_nxd(q, k, v, softmax_scale, causal)
+    if be == "sdpa":
+        return F.scaled_dot_product_attention(q, k, v, is_causal=causal, scale=softmax_scale,
+                                              enable_gqa=(q.shape[1] != k.shape[1]))
+    return attention_ref(q, k, v, causal, softmax_scale)
+
+
+nki_flash_attn_func = flash_attn_func  # reference-compatible alias
+
+
+# ---------------------------------------------------------------------------------------------
+# decode path
+# ---------------------------------------------------------------------------------------------
+
+_decode_scratch = {}
+
+
+def kv_cache_update(cache_k: torch.Tensor, cache_v: torch.Tensor, new_k: torch.Tensor, new_v: torch.Tensor,
+                    positions: torch.Tensor, seq_ids: Optional[torch.Tensor] = None,
+                    block_table: Optional[torch.Tensor] = None, page_size: int = 0) -> None:
+    """Write ``new_k/new_v [B, Hkv, T, D]`` at rows ``positions[b] + t`` of cache line ``seq_ids[b]``
+    (default ``b``).  Cache: contiguous ``[Bmax, Hkv, Smax, D]`` or paged ``[pages, Hkv, page, D]``."""
+    B, Hkv, T, D = new_k.shape
+    if cache_k.is_cuda and cache_k.dtype == torch.bfloat16 and _lib.available():
+        pos = positions.to(torch.int32).contiguous()
+        sid = seq_ids.to(torch.int32).contiguous() if seq_ids is not None else None
+        bt = block_table.to(torch.int32).contiguous() if block_table is not None else None
+        rc = _lib.lib().nxd_kv_cache_update(
+            _lib.ptr(new_k.contiguous()), _lib.ptr(new_v.contiguous()), _lib.ptr(cache_k), _lib.ptr(cache_v),
+            _lib.ptr(pos), _lib.ptr(sid), _lib.ptr(bt), _c.c_longlong(cache_k.stride(0)),
+            _c.c_longlong(cache_k.stride(1)), _c.c_int(page_size), _c.c_int(bt.shape[1] if bt is not None else 0),
+            _c.c_int(B), _c.c_int(Hkv), _c.c_int(T), _c.c_int(D), _lib.stream_ptr())
+        _lib.check(rc, "nxd_kv_cache_update")
+        return
+    for b in range(B):
+        line = int(seq_ids[b]) if seq_ids is not None else b
+        p0 = int(positions[b])
+        for t in range(T):
+            pos = p0 + t
+            if block_table is not None:
+                page = int(block_table[line, pos // page_size])
+                cache_k[page, :, pos % page_size] = new_k[b, :, t]
+                cache_v[page, :, pos % page_size] = new_v[b, :, t]
+            else:
+                cache_k[line, :, pos] = new_k[b, :, t]
+                cache_v[line, :, pos] = new_v[b, :, t]
+
+
+def decode_attention(q: torch.Tensor, cache_k: torch.Tensor, cache_v: torch.Tensor, lengths: torch.Tensor,
+                     softmax_scale: Optional[float] = None, block_table: Optional[torch.Tensor] = None,
+                     page_size: int = 0) -> torch.Tensor:
+    """One new token per sequence: q ``[B, Hq, D]`` attends to cache rows ``[0, lengths[b])``."""
+    B, Hq, D = q.shape
+    Hkv = cache_k.shape[1]
+    scale = softmax_scale if softmax_scale is not None else 1.0 / math.sqrt(D)
+    if q.is_cuda and q.dtype == torch.bfloat16 and D in (64, 128) and _lib.available():
+        lens = lengths.to(torch.int32).contiguous()
+        max_len = cache_k.shape[2] if block_table is None else block_table.shape[1] * page_size
+        n_splits = _lib.lib().nxd_decode_attn_num_splits(_c.c_int(B), _c.c_int(Hkv), _c.c_int(max_len))
+        need = B * Hq * n_splits * (D + 2)
+        key = (q.device.index, need)
+        scratch = _decode_scratch.get(key)
+        if scratch is None:
+            scratch = torch.empty(need, dtype=torch.float32, device=q.device)
+            _decode_scratch.clear()
+            _decode_scratch[key] = scratch
+        out = torch.empty_like(q)
+        bt = block_table.to(torch.int32).contiguous() if block_table is not None else None
+        rc = _lib.lib().nxd_decode_attn(
+            _lib.ptr(q.contiguous()), _lib.ptr(cache_k), _lib.ptr(cache_v), _lib.ptr(lens), _lib.ptr(bt),
+            _c.c_longlong(cache_k.stride(0)), _c.c_longlong(cache_k.stride(1)), _c.c_int(page_size),
+            _c.c_int(bt.shape[1] if bt is not None else 0), _lib.ptr(out), _lib.ptr(scratch), _c.c_int(B),
+            _c.c_int(Hq), _c.c_int(Hkv), _c.c_int(D), _c.c_int(n_splits), _c.c_float(scale), _lib.stream_ptr())
+        _lib.check(rc, "nxd_decode_attn")
+        return out
+    return decode_attention_ref(q, cache_k, cache_v, lengths, scale, block_table, page_size)
+
+
+def decode_attention_ref(q, cache_k, cache_v, lengths, scale, block_table=None, page_size=0):
+    B, Hq, D = q.shape
+    Hkv = cache_k.shape[1]
+    g = Hq // Hkv
+    outs = []
+    for b in range(B):
+        L = int(lengths[b])
+        if block_table is not None:
+            pages = block_table[b, : (L + page_size - 1) // page_size].long()
+            kk = cache_k[pages].permute(1, 0, 2, 3).reshape(Hkv, -1, D)[:, :L]
+            vv = cache_v[pages].permute(1, 0, 2, 3).reshape(Hkv, -1, D)[:, :L]
+        else:
+            kk, vv = cache_k[b, :, :L], cache_v[b, :, :L]
+        kk = kk.float().repeat_interleave(g, dim=0)
+        vv = vv.float().repeat_interleave(g, dim=0)
+        s = torch.einsum("hd,hld->hl", q[b].float(), kk) * scale
+        p = torch.softmax(s, dim=-1)
+        outs.append(torch.einsum("hl,hld->hd", p, vv))
+    return torch.stack(outs).to(q.dtype)

@@ -1,0 +1,92 @@
+"""GEMM dispatch: the three operand layouts a Linear needs in fwd + bwd.
+
+All matrices are row-major 2-D views:
+
+* ``gemm_nt(a[M,K], b[N,K]) -> [M,N]``    forward     ``Y = X W^T``
+* ``gemm_nn(a[M,K], b[K,N]) -> [M,N]``    dgrad       ``dX = dY W``
+* ``gemm_tn(a[K,M], b[K,N]) -> [M,N]``    wgrad       ``dW = dY^T X``
+
+On a B200 with the kernel library loaded, bf16 inputs go to the hand-written
+tcgen05/TMA kernel in ``csrc/gemm_tcgen05.cu`` (all three layouts are handled by
+operand-major bits in the UMMA descriptors, no transposed copies).  Everything
+else (CPU tests, fp32, odd shapes) takes the plain ``torch.matmul`` path.
+
+``NXD_GEMM_BACKEND`` = ``tcgen05`` (default on GPU) | ``cublas`` selects the
+library GEMM instead; the latter is the NCCL+cuBLAS *baseline* arm.
+"""
+from __future__ import annotations
+
+import os
+from typing import Optional
+
+import torch
+
+from . import _lib
+
+
+def _backend() -> str:
+    return os.environ.get("NXD_GEMM_BACKEND", "tcgen05")
+
+
+def _use_kernel(a: torch.Tensor, b: torch.Tensor, m: int, n: int, k: int) -> bool:
+    if not (a.is_cuda and b.is_cuda):
+        return False
+    if a.dtype != torch.bfloat16 or b.dtype != torch.bfloat16:
+        return False
+    if _backend() != "tcgen05":
+        return False
+    # TMA needs 16-byte aligned row pitches; tiles are masked by TMA OOB handling.
+    if (k % 8) or (n % 8) or (m % 8):
+        return False
+    return _lib.available()
+
+
+def gemm_nt(a: torch.Tensor, b: torch.Tensor, out: Optional[torch.Tensor] = None,
+            out_dtype: Optional[torch.dtype] = None, accumulate: bool = False) -> torch.Tensor:
+    """``a[M,K] @ b[N,K]^T``.  ``accumulate`` adds into ``out`` (fp32 grad accumulation)."""
+    m, k = a.shape
+    n = b.shape[0]
+    if _use_kernel(a, b, m, n, k):
+        from .gemm import gemm
+
+        return gemm(a, b, "nt", out=out, out_dtype=out_dtype, accumulate=accumulate)
+    res = torch.matmul(a, b.t())
+    return _finish(res, out, out_dtype, accumulate)
+
+
+def gemm_nn(a: torch.Tensor, b: torch.Tensor, out: Optional[torch.Tensor] = None,
+            out_dtype: Optional[torch.dtype] = None, accumulate: bool = False) -> torch.Tensor:
+    """``a[M,K] @ b[K,N]``."""
+    m, k = a.shape
+    n = b.shape[1]
+    if _use_kernel(a, b, m, n, k):
+        from .gemm import gemm
+
+        return gemm(a, b, "nn", out=out, out_dtype=out_dtype, accumulate=accumulate)
+    res = torch.matmul(a, b)
+    return _finish(res, out, out_dtype, accumulate)
+
+
+def gemm_tn(a: torch.Tensor, b: torch.Tensor, out: Optional[torch.Tensor] = None,
+            out_dtype: Optional[torch.dtype] = None, accumulate: bool = False) -> torch.Tensor:
+    """``a[K,M]^T @ b[K,N]``."""
+    k, m = a.shape
+    n = b.shape[1]
+    if _use_kernel(a, b, m, n, k):
+        from .gemm import gemm
+
+        return gemm(a, b, "tn", out=out, out_dtype=out_dtype, accumulate=accumulate)
+    res = torch.matmul(a.t(), b)
+    return _finish(res, out, out_dtype, accumulate)
+
+
+def _finish(res, out, out_dtype, accumulate):
+    if out is not None:
+        if accumulate:
+            out.add_(res.to(out.dtype))
+        else:
+            out.copy_(res)
+        return out
+    if out_dtype is not None and res.dtype != out_dtype:
+        res = res.to(out_dtype)
+    return res

@@ -1,0 +1,75 @@
+"""Vocab-parallel cross entropy.
+
+Reference: ``src/neuronx_distributed/parallel_layers/loss_functions.py:11-135``:
+three TP all-reduces (row max, target logit, sum-exp), softmax saved for backward.
+
+B200 version: logits ``[T, V/tp]`` stay in bf16; one kernel pass produces the
+per-row local (max, sum-exp, target-logit) triple in fp32, ranks exchange the
+triple with ONE packed all-gather (3 floats per row) and combine with the usual
+log-sum-exp merge, and backward recomputes ``softmax - onehot`` in place from the
+saved logits + row statistics, so no fp32 ``[T, V/tp]`` tensor is ever
+materialised (the reference upcasts logits to fp64,
+``examples/training/llama/modeling_llama_nxd.py:731``).
+
+Label smoothing follows the mathematically consistent form (the reference's
+backward uses ``1 - target_mask`` which looks inverted; we
+test against ``torch.nn.functional.cross_entropy(label_smoothing=...)``).
+"""
+from __future__ import annotations
+
+import torch
+import torch.distributed as dist
+
+from ..ops import cross_entropy as ce_ops
+from . import parallel_state as ps
+
+
+class _ParallelCrossEntropy(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, vocab_parallel_logits: torch.Tensor, target: torch.Tensor, label_smoothing: float = 0.0):
+        tp = ps.get_tensor_model_parallel_size()
+        rank = ps.get_tensor_model_parallel_rank()
+        shape = target.shape
+        logits2d = vocab_parallel_logits.reshape(-1, vocab_parallel_logits.shape[-1])
+        tgt = target.reshape(-1)
+        v_local = logits2d.shape[-1]
+        vocab_start = rank * v_local
+        # local statistics: [T, 4] fp32 = (max, sumexp(rel. to max), target_logit or 0, sum_logits)
+        stats = ce_ops.ce_local_stats(logits2d, tgt, vocab_start)
+        if tp > 1:
+            group = ps.get_tensor_model_parallel_group()
+            gathered = torch.empty((tp,) + tuple(stats.shape), dtype=stats.dtype, device=stats.device)
+            dist.all_gather_into_tensor(gathered, stats.contiguous(), group=group)
+            gmax = gathered[..., 0].max(dim=0).values
+            sumexp = (gathered[..., 1] * torch.exp(gathered[..., 0] - gmax)).sum(dim=0)
+            tlogit = gathered[..., 2].sum(dim=0)
+            sum_logits = gathered[..., 3].sum(dim=0)
+        else:
+            gmax, sumexp, tlogit, sum_logits = stats[:, 0], stats[:, 1], stats[:, 2], stats[:, 3]
+        lse = gmax + torch.log(sumexp)
+        loss = lse - tlogit
+        vocab = v_local * tp
+        if label_smoothing > 0:
+            # (1-a) * nll + a * mean_v(-log p_v) ; -log p_v = lse - z_v
+            smooth = lse - sum_logits / vocab
+            loss = (1.0 - label_smoothing) * loss + label_smoothing * smooth
+        ctx.save_for_backward(logits2d, tgt, lse)
+        ctx.vocab_start = vocab_start
+        ctx.label_smoothing = label_smoothing
+        ctx.vocab = vocab
+        ctx.in_shape = vocab_parallel_logits.shape
+        return loss.reshape(shape)
+
+    @staticmethod
+    def backward(ctx, grad_output: torch.Tensor):
+        logits2d, tgt, lse = ctx.saved_tensors
+        g = grad_output.reshape(-1).to(torch.float32).contiguous()
+        grad = ce_ops.ce_backward(logits2d, tgt, lse, g, ctx.vocab_start, ctx.label_smoothing, ctx.vocab)
+        return grad.reshape(ctx.in_shape), None, None
+
+
+def parallel_cross_entropy(vocab_parallel_logits: torch.Tensor, target: torch.Tensor,
+                           label_smoothing: float = 0.0) -> torch.Tensor:
+    """Per-token loss, same shape as ``target``.  ``vocab_parallel_logits`` is
+    ``[..., V/tp]`` (this rank's vocab slice)."""
+    return _ParallelCrossEntropy.apply(vocab_parallel_logits, target, label_smoothing)
