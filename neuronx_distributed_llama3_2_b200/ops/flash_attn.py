@@ -1,0 +1,73 @@
+"""ctypes binding + autograd wrapper of the hand-written flash attention (``csrc/flash_attn.cu``)."""
+from __future__ import annotations
+
+import ctypes as _c
+import math
+from typing import Optional
+
+import torch
+
+from . import _lib
+
+
+def _dense_like(t: torch.Tensor) -> torch.Tensor:
+    """Uninitialised dense tensor with ``t``'s shape and dim ordering (so a ``[S,B,H,D]``-stored
+    ``[B,H,S,D]`` view yields an output that reshapes to ``[S,B,H*D]`` without a copy)."""
+    order = sorted(range(t.dim()), key=lambda d: (t.stride(d), -d), reverse=True)
+    shape = [t.shape[d] for d in order]
+    buf = torch.empty(shape, dtype=t.dtype, device=t.device)
+    inv = [order.index(d) for d in range(t.dim())]
+    return buf.permute(inv)
+
+
+def _fix(t: torch.Tensor) -> torch.Tensor:
+    if t.stride(-1) != 1 or any(s % 8 for s in t.stride()[:-1]):
+        return t.contiguous()
+    return t
+
+
+def _strides(*ts) -> "_c.Array":
+    vals = []
+    for t in ts:
+        vals += [t.stride(0), t.stride(1), t.stride(2)]
+    return (_c.c_longlong * len(vals))(*vals)
+
+
+class _FlashAttnFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, q, k, v, scale, causal):
+        q, k, v = _fix(q), _fix(k), _fix(v)
+        B, Hq, Sq, D = q.shape
+        Hkv, Sk = k.shape[1], k.shape[2]
+        o = _dense_like(q)
+        lse = torch.empty((B, Hq, Sq), dtype=torch.float32, device=q.device)
+        rc = _lib.lib().nxd_flash_attn_fwd(
+            _lib.ptr(q), _lib.ptr(k), _lib.ptr(v), _lib.ptr(o), _lib.ptr(lse), _strides(q, k, v, o), _c.c_int(B),
+            _c.c_int(Hq), _c.c_int(Hkv), _c.c_int(Sq), _c.c_int(Sk), _c.c_int(D), _c.c_float(scale),
+            _c.c_int(1 if causal else 0), _lib.stream_ptr())
+        _lib.check(rc, "nxd_flash_attn_fwd")
+        ctx.save_for_backward(q, k, v, o, lse)
+        ctx.scale, ctx.causal = scale, causal
+        return o
+
+    @staticmethod
+    def backward(ctx, do):
+        q, k, v, o, lse = ctx.saved_tensors
+        do = _fix(do)
+        B, Hq, Sq, D = q.shape
+        Hkv, Sk = k.shape[1], k.shape[2]
+        dq, dk, dv = _dense_like(q), _dense_like(k), _dense_like(v)
+        delta = torch.empty_like(lse)
+        rc = _lib.lib().nxd_flash_attn_bwd(
+            _lib.ptr(q), _lib.ptr(k), _lib.ptr(v), _lib.ptr(o), _lib.ptr(do), _lib.ptr(lse), _lib.ptr(delta),
+            _lib.ptr(dq), _lib.ptr(dk), _lib.ptr(dv), _strides(q, k, v, o, do, dq, dk, dv), _c.c_int(B), _c.c_int(Hq),
+            _c.c_int(Hkv), _c.c_int(Sq), _c.c_int(Sk), _c.c_int(D), _c.c_float(ctx.scale),
+            _c.c_int(1 if ctx.causal else 0), _lib.stream_ptr())
+        _lib.check(rc, "nxd_flash_attn_bwd")
+        return dq, dk, dv, None, None
+
+
+def flash_attn_nxd(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, softmax_scale: Optional[float] = None,
+                   causal: bool = True) -> torch.Tensor:
+    scale = softmax_scale if softmax_scale is not None else 1.0 / math.sqrt(q.shape[-1])
+    return _FlashAttnFn.apply(q, k, v, float(scale), bool(causal))

@@ -1,0 +1,388 @@
+"""Numerics of every hand-written sm_100a kernel against a plain fp32 PyTorch restatement of the same op.
+
+Run on the B200 box:  python -m pytest tests -m gpu -x -q
+"""
+from __future__ import annotations
+
+import math
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _lib():
+    from neuronx_distributed_llama3_2_b200.ops import _lib
+
+    assert _lib.available(), "libnxd_b200.so must load on a GPU box"
+    return _lib
+
+
+def _rel_err(a: torch.Tensor, b: torch.Tensor) -> float:
+    a, b = a.float(), b.float()
+    return ((a - b).norm() / (b.norm() + 1e-12)).item()
+
+
+# ---------------------------------------------------------------------------------------------
+# tcgen05 GEMM
+# ---------------------------------------------------------------------------------------------
+
+_SHAPES = [
+    (256, 256, 64),
+    (256, 128, 128),
+    (512, 384, 512),
+    (1024, 1024, 1024),
+    (8192, 2048, 3072),
+    (4096, 3072, 8192),
+    (1000, 264, 328),     # ragged M/N/K (multiples of 8 only)
+    (128, 5120, 3072),
+]
+
+
+@pytest.mark.parametrize("layout", ["nt", "nn", "tn"])
+@pytest.mark.parametrize("shape", _SHAPES)
+def test_gemm_layouts(layout, shape):
+    from neuronx_distributed_llama3_2_b200.ops.gemm import gemm
+
+    _lib()
+    M, N, K = shape
+    g = torch.Generator(device="cuda").manual_seed(M * 7 + N * 3 + K)
+    if layout == "nt":
+        a = torch.randn(M, K, device="cuda", generator=g).bfloat16()
+        b = torch.randn(N, K, device="cuda", generator=g).bfloat16()
+        ref = a.float() @ b.float().t()
+    elif layout == "nn":
+        a = torch.randn(M, K, device="cuda", generator=g).bfloat16()
+        b = torch.randn(K, N, device="cuda", generator=g).bfloat16()
+        ref = a.float() @ b.float()
+    else:
+        a = torch.randn(K, M, device="cuda", generator=g).bfloat16()
+        b = torch.randn(K, N, device="cuda", generator=g).bfloat16()
+        ref = a.float().t() @ b.float()
+    for bn in (128, 256):
+        out = gemm(a, b, layout, block_n=bn)
+        torch.cuda.synchronize()
+        assert _rel_err(out, ref) < 6e-3, (layout, shape, bn, _rel_err(out, ref))
+    out32 = gemm(a, b, layout, out_dtype=torch.float32)
+    assert _rel_err(out32, ref) < 1e-4
+    acc = torch.ones(M, N, device="cuda", dtype=torch.float32)
+    gemm(a, b, layout, out=acc, accumulate=True)
+    assert _rel_err(acc, ref + 1.0) < 1e-4
+
+
+def test_gemm_strided_operands():
+    from neuronx_distributed_llama3_2_b200.ops.gemm import gemm
+
+    _lib()
+    big = torch.randn(512, 1024, device="cuda").bfloat16()
+    a = big[:, 256:768]                        # row pitch 1024, K = 512
+    w = torch.randn(384, 512, device="cuda").bfloat16()
+    out_big = torch.zeros(512, 1024, device="cuda", dtype=torch.bfloat16)
+    out = out_big[:, 128:512]
+    gemm(a, w, "nt", out=out)
+    ref = a.float() @ w.float().t()
+    assert _rel_err(out, ref) < 6e-3
+    assert out_big[:, :128].abs().max().item() == 0 and out_big[:, 512:].abs().max().item() == 0
+
+
+# ---------------------------------------------------------------------------------------------
+# RMSNorm / SwiGLU / RoPE
+# ---------------------------------------------------------------------------------------------
+
+@pytest.mark.parametrize("H", [256, 2048, 3072, 4096, 8192])
+@pytest.mark.parametrize("rows", [1, 37, 4096])
+def test_rmsnorm_fwd_bwd(rows, H):
+    from neuronx_distributed_llama3_2_b200.ops.norm import fused_add_rms_norm, rms_norm, rms_norm_ref
+
+    _lib()
+    x = torch.randn(rows, H, device="cuda").bfloat16().requires_grad_()
+    w = (1 + 0.1 * torch.randn(H, device="cuda")).bfloat16().requires_grad_()
+    dy = torch.randn(rows, H, device="cuda").bfloat16()
+    y = rms_norm(x, w, 1e-5)
+    y.backward(dy)
+    xr = x.detach().float().requires_grad_()
+    wr = w.detach().float().requires_grad_()
+    yr = rms_norm_ref(xr, wr, 1e-5)
+    yr.backward(dy.float())
+    assert _rel_err(y, yr) < 6e-3
+    assert _rel_err(x.grad, xr.grad) < 8e-3
+    assert _rel_err(w.grad, wr.grad) < 8e-3
+
+    res = torch.randn(rows, H, device="cuda").bfloat16()
+    y2, s2 = fused_add_rms_norm(x.detach(), res, w.detach(), 1e-5)
+    s_ref = (x.detach().float() + res.float()).bfloat16()
+    assert torch.equal(s2, s_ref)
+    assert _rel_err(y2, rms_norm_ref(s_ref.float(), w.detach().float(), 1e-5)) < 6e-3
+
+
+def test_fused_add_rmsnorm_backward():
+    from neuronx_distributed_llama3_2_b200.ops.norm import fused_add_rms_norm, rms_norm_ref
+
+    _lib()
+    rows, H = 300, 2048
+    x = torch.randn(rows, H, device="cuda").bfloat16().requires_grad_()
+    r = torch.randn(rows, H, device="cuda").bfloat16().requires_grad_()
+    w = torch.randn(H, device="cuda").bfloat16().requires_grad_()
+    y, s = fused_add_rms_norm(x, r, w, 1e-5)
+    gy, gs = torch.randn_like(y), torch.randn_like(s)
+    (y.float() * gy.float()).sum().add((s.float() * gs.float()).sum()).backward()
+    xf, rf, wf = (t.detach().float().requires_grad_() for t in (x, r, w))
+    sf = xf + rf
+    yf = rms_norm_ref(sf, wf, 1e-5)
+    ((yf * gy.float()).sum() + (sf * gs.float()).sum()).backward()
+    assert _rel_err(x.grad, xf.grad) < 1e-2
+    assert _rel_err(r.grad, rf.grad) < 1e-2
+    assert _rel_err(w.grad, wf.grad) < 1e-2
+
+
+@pytest.mark.parametrize("I", [1024, 8192])
+def test_swiglu(I):
+    from neuronx_distributed_llama3_2_b200.ops.activation import swiglu, swiglu_ref
+
+    _lib()
+    gu = torch.randn(777, 2 * I, device="cuda").bfloat16().requires_grad_()
+    dy = torch.randn(777, I, device="cuda").bfloat16()
+    out = swiglu(gu)
+    out.backward(dy)
+    gr = gu.detach().float().requires_grad_()
+    outr = swiglu_ref(gr)
+    outr.backward(dy.float())
+    assert _rel_err(out, outr) < 6e-3
+    assert _rel_err(gu.grad, gr.grad) < 8e-3
+
+
+@pytest.mark.parametrize("D", [64, 128])
+def test_rope(D):
+    from neuronx_distributed_llama3_2_b200.ops.rope import apply_rope, build_rope_cache, rope_ref
+
+    _lib()
+    S, B, heads, nrot = 128, 2, 6, 4
+    cos, sin = build_rope_cache(S, D, 500000.0, {"rope_type": "llama3", "factor": 32.0}, device="cuda")
+    x = torch.randn(S * B, heads, D, device="cuda").bfloat16().requires_grad_()
+    y = apply_rope(x, cos, sin, nrot, pos_div=B, pos_mod=S)
+    ref = rope_ref(x.detach().float(), cos, sin, nrot, B, S)
+    assert _rel_err(y, ref) < 6e-3
+    dy = torch.randn_like(y)
+    y.backward(dy)
+    ref_g = rope_ref(dy.float(), cos, sin, nrot, B, S, inverse=True)
+    assert _rel_err(x.grad, ref_g) < 6e-3
+    pos = torch.randint(0, S, (S * B,), device="cuda")
+    y2 = apply_rope(x.detach(), cos, sin, nrot, positions=pos)
+    assert _rel_err(y2, rope_ref(x.detach().float(), cos, sin, nrot, 1, 1, positions=pos)) < 6e-3
+
+
+# ---------------------------------------------------------------------------------------------
+# cross entropy, embedding
+# ---------------------------------------------------------------------------------------------
+
+def test_cross_entropy_kernels():
+    from neuronx_distributed_llama3_2_b200.ops import cross_entropy as ce
+
+    _lib()
+    T, V, start = 513, 16032, 16032
+    logits = (3 * torch.randn(T, V, device="cuda")).bfloat16()
+    target = torch.randint(0, 3 * V, (T,), device="cuda")
+    target[5] = -100
+    stats = ce.ce_local_stats(logits, target, start)
+    z = logits.float()
+    m = z.max(-1).values
+    assert torch.allclose(stats[:, 0], m)
+    assert _rel_err(stats[:, 1], torch.exp(z - m[:, None]).sum(-1)) < 1e-4
+    local = target - start
+    ok = (local >= 0) & (local < V)
+    tl = torch.where(ok, z.gather(1, local.clamp(0, V - 1)[:, None]).squeeze(1), torch.zeros_like(m))
+    assert torch.allclose(stats[:, 2], tl)
+    assert _rel_err(stats[:, 3], z.sum(-1)) < 1e-3
+    lse = m + torch.log(stats[:, 1])
+    go = torch.rand(T, device="cuda")
+    for smoothing in (0.0, 0.1):
+        grad = ce.ce_backward(logits, target, lse, go, start, smoothing, 3 * V)
+        p = torch.exp(z - lse[:, None]) - smoothing / (3 * V)
+        onehot = torch.zeros_like(p)
+        onehot.scatter_(1, local.clamp(0, V - 1)[:, None], ok[:, None].float())
+        ref = (p - (1 - smoothing) * onehot) * torch.where(target < 0, torch.zeros_like(go), go)[:, None]
+        assert _rel_err(grad, ref) < 8e-3
+
+
+def test_embedding_kernels():
+    from neuronx_distributed_llama3_2_b200.ops.embedding import vocab_parallel_embedding
+
+    _lib()
+    V, H, B, S, start = 1000, 512, 3, 64, 500
+    w = torch.randn(V, H, device="cuda").bfloat16().requires_grad_()
+    ids = torch.randint(0, 2000, (B, S), device="cuda")
+    for seq_first in (False, True):
+        w.grad = None
+        out = vocab_parallel_embedding(ids, w, start, seq_first_out=seq_first)
+        local = ids - start
+        mask = (local < 0) | (local >= V)
+        ref = torch.nn.functional.embedding(local.masked_fill(mask, 0), w.detach()).masked_fill(mask[..., None], 0)
+        if seq_first:
+            ref = ref.transpose(0, 1)
+        assert torch.equal(out, ref.contiguous())
+        dy = torch.randn_like(out)
+        out.backward(dy)
+        wr = w.detach().float().requires_grad_()
+        refo = torch.nn.functional.embedding(local.masked_fill(mask, 0), wr).masked_fill(mask[..., None], 0)
+        if seq_first:
+            refo = refo.transpose(0, 1)
+        refo.backward(dy.float())
+        assert _rel_err(w.grad, wr.grad) < 8e-3
+
+
+# ---------------------------------------------------------------------------------------------
+# optimizer kernels
+# ---------------------------------------------------------------------------------------------
+
+def test_optimizer_kernels():
+    from neuronx_distributed_llama3_2_b200.ops import optim
+
+    _lib()
+    n = 3_000_017
+    for dt in (torch.float32, torch.bfloat16):
+        x = torch.randn(n, device="cuda").to(dt)
+        out = torch.zeros(1, device="cuda")
+        optim.sumsq_(x, out)
+        assert abs(out.item() - x.float().pow(2).sum().item()) / n < 1e-3
+        optim.sumsq_(x, out, accumulate=True)
+        assert abs(out.item() - 2 * x.float().pow(2).sum().item()) / n < 2e-3
+    coef = torch.empty(1, device="cuda")
+    norm = torch.empty(1, device="cuda")
+    tot = torch.tensor([25.0], device="cuda")
+    optim.clip_coef_(tot, 1.0, coef, norm)
+    assert abs(norm.item() - 5.0) < 1e-5 and abs(coef.item() - 1.0 / (5.0 + 1e-6)) < 1e-6
+    optim.clip_coef_(torch.tensor([0.01], device="cuda"), 1.0, coef, norm)
+    assert coef.item() == 1.0
+
+    master = torch.randn(n, device="cuda")
+    m = torch.zeros(n, device="cuda")
+    v = torch.zeros(n, device="cuda")
+    ref_p = master.clone().requires_grad_()
+    opt = torch.optim.AdamW([ref_p], lr=1e-2, betas=(0.9, 0.95), eps=1e-8, weight_decay=0.1)
+    pout = torch.empty(n, device="cuda", dtype=torch.bfloat16)
+    for step in range(1, 4):
+        g = torch.randn(n, device="cuda").bfloat16()
+        cc = torch.tensor([0.5], device="cuda")
+        optim.adamw_step_(master, m, v, g, pout, 1e-2, 0.9, 0.95, 1e-8, 0.1, step, grad_scale=2.0, clip_coef=cc)
+        ref_p.grad = g.float()  # 2.0 * 0.5 = 1
+        opt.step()
+        assert _rel_err(master, ref_p.detach()) < 1e-5
+        assert torch.equal(pout, master.bfloat16())
+    x = torch.randn(1001, device="cuda").bfloat16()
+    x0 = x.clone()
+    optim.scale_(x, 0.5, torch.tensor([4.0], device="cuda"))
+    assert _rel_err(x, x0.float() * 2) < 1e-2
+
+
+# ---------------------------------------------------------------------------------------------
+# sampling
+# ---------------------------------------------------------------------------------------------
+
+@pytest.mark.parametrize("dt", [torch.float32, torch.bfloat16])
+def test_sampling(dt):
+    from neuronx_distributed_llama3_2_b200.ops import sampling
+
+    _lib()
+    B, V = 9, 128256
+    logits = torch.randn(B, V, device="cuda").to(dt)
+    assert torch.equal(sampling.argmax(logits), torch.argmax(logits.float(), -1))
+    u = torch.rand(B, device="cuda")
+    for k, p in ((1, 1.0), (50, 1.0), (256, 0.9)):
+        got = sampling.topk_sample(logits, k, p, 0.8, u)
+        ref = sampling.topk_sample_ref(logits, k, p, 0.8, u)
+        # bf16 ties / fp rounding at the CDF boundary may move a pick by one slot: require membership in top-k
+        topk = torch.topk(logits.float(), k, dim=-1).indices
+        assert all(int(got[b]) in topk[b].tolist() for b in range(B))
+        assert (got == ref).float().mean().item() >= 0.75, (k, p, got, ref)
+
+
+# ---------------------------------------------------------------------------------------------
+# decode attention + KV cache
+# ---------------------------------------------------------------------------------------------
+
+@pytest.mark.parametrize("D", [64, 128])
+def test_decode_attention_contiguous_and_paged(D):
+    from neuronx_distributed_llama3_2_b200.ops import attention as A
+
+    _lib()
+    B, Hq, Hkv, Smax = 5, 8, 2, 4096
+    ck = torch.randn(B, Hkv, Smax, D, device="cuda").bfloat16()
+    cv = torch.randn(B, Hkv, Smax, D, device="cuda").bfloat16()
+    q = torch.randn(B, Hq, D, device="cuda").bfloat16()
+    lens = torch.tensor([1, 17, 1000, 4096, 2049], device="cuda")
+    out = A.decode_attention(q, ck, cv, lens)
+    ref = A.decode_attention_ref(q, ck, cv, lens, 1.0 / math.sqrt(D))
+    assert _rel_err(out, ref) < 1e-2
+
+    page = 128
+    n_pages = B * Smax // page
+    perm = torch.randperm(n_pages, device="cuda")
+    table = perm.reshape(B, Smax // page).int()
+    pk = torch.empty(n_pages, Hkv, page, D, device="cuda", dtype=torch.bfloat16)
+    pv = torch.empty_like(pk)
+    for b in range(B):
+        for j in range(Smax // page):
+            pk[table[b, j]] = ck[b, :, j * page:(j + 1) * page]
+            pv[table[b, j]] = cv[b, :, j * page:(j + 1) * page]
+    out_p = A.decode_attention(q, pk, pv, lens, block_table=table, page_size=page)
+    assert _rel_err(out_p, ref) < 1e-2
+
+    # KV write: T new tokens at position p of line seq_ids[b]
+    nk = torch.randn(B, Hkv, 3, D, device="cuda").bfloat16()
+    nv = torch.randn(B, Hkv, 3, D, device="cuda").bfloat16()
+    pos = torch.tensor([0, 5, 100, 4093, 7], device="cuda")
+    ck2, cv2 = ck.clone(), cv.clone()
+    A.kv_cache_update(ck2, cv2, nk, nv, pos)
+    for b in range(B):
+        assert torch.equal(ck2[b, :, int(pos[b]):int(pos[b]) + 3], nk[b])
+        assert torch.equal(cv2[b, :, int(pos[b]):int(pos[b]) + 3], nv[b])
+    pk2, pv2 = pk.clone(), pv.clone()
+    A.kv_cache_update(pk2, pv2, nk, nv, pos, block_table=table, page_size=page)
+    for b in range(B):
+        for t in range(3):
+            p = int(pos[b]) + t
+            assert torch.equal(pk2[table[b, p // page], :, p % page], nk[b, :, t])
+
+
+# ---------------------------------------------------------------------------------------------
+# flash attention fwd / bwd
+# ---------------------------------------------------------------------------------------------
+
+@pytest.mark.parametrize("D", [64, 128])
+@pytest.mark.parametrize("S", [128, 1024, 1000])
+def test_flash_attention(S, D):
+    from neuronx_distributed_llama3_2_b200.ops import attention as A
+
+    _lib()
+    B, Hq, Hkv = 2, 6, 2
+    q = torch.randn(B, Hq, S, D, device="cuda").bfloat16().requires_grad_()
+    k = torch.randn(B, Hkv, S, D, device="cuda").bfloat16().requires_grad_()
+    v = torch.randn(B, Hkv, S, D, device="cuda").bfloat16().requires_grad_()
+    do = torch.randn(B, Hq, S, D, device="cuda").bfloat16()
+    assert A._backend(q) == "nxd", "the hand-written flash attention must be the GPU path"
+    out = A.flash_attn_func(q, k, v, causal=True)
+    out.backward(do)
+    qf, kf, vf = (t.detach().float().requires_grad_() for t in (q, k, v))
+    ref = A.attention_ref(qf, kf, vf, True, None)
+    ref.backward(do.float())
+    assert _rel_err(out, ref) < 1e-2
+    assert _rel_err(q.grad, qf.grad) < 2e-2
+    assert _rel_err(k.grad, kf.grad) < 2e-2
+    assert _rel_err(v.grad, vf.grad) < 2e-2
+
+
+def test_flash_attention_strided_layout_noncausal():
+    """[S, B, heads, D] storage viewed as [B, H, S, D] (how the SP transformer block holds q/k/v)."""
+    from neuronx_distributed_llama3_2_b200.ops import attention as A
+
+    _lib()
+    S, B, Hq, Hkv, D = 512, 2, 4, 1, 128
+    qkv = torch.randn(S, B, Hq + 2 * Hkv, D, device="cuda").bfloat16()
+    q = qkv[:, :, :Hq].permute(1, 2, 0, 3)
+    k = qkv[:, :, Hq:Hq + Hkv].permute(1, 2, 0, 3)
+    v = qkv[:, :, Hq + Hkv:].permute(1, 2, 0, 3)
+    for causal in (True, False):
+        out = A.flash_attn_func(q, k, v, causal=causal)
+        ref = A.attention_ref(q.float(), k.float(), v.float(), causal, None)
+        assert _rel_err(out, ref) < 1e-2
