@@ -169,12 +169,23 @@ class ParallelEmbedding(torch.nn.Module):
             if self.pad and self.pad_size > 0:
                 out = out[..., : self.embedding_dim - self.pad_size]
             return out
+        w = self.weight
+        if (w.is_cuda and w.dtype == torch.bfloat16 and self.max_norm is None and self.padding_idx is None
+                and input_.dim() == 2):
+            # sm_100a gather kernel: masks out-of-shard ids and writes [S, B, H] directly when SP is on
+            from ..ops.embedding import vocab_parallel_embedding
+
+            out = vocab_parallel_embedding(input_, w, self.start_index if tp > 1 else 0,
+                                           seq_first_out=self.sequence_parallel_enabled)
+            if self.sequence_parallel_enabled:
+                return mappings.reduce_scatter_to_sequence_parallel_region(out)
+            return mappings.reduce_from_tensor_model_parallel_region(out)
         if tp > 1:
             mask = (input_ < self.start_index) | (input_ >= self.end_index)
             local = (input_ - self.start_index).masked_fill(mask, 0)
         else:
             mask, local = None, input_
-        out = F.embedding(local, self.weight, self.padding_idx if tp == 1 else None, self.max_norm, self.norm_type,
+        out = F.embedding(local, w, self.padding_idx if tp == 1 else None, self.max_norm, self.norm_type,
                           self.scale_grad_by_freq, self.sparse)
         if mask is not None:
             out = out.masked_fill(mask.unsqueeze(-1), 0.0)

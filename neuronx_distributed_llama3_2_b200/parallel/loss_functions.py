@@ -38,8 +38,9 @@ class _ParallelCrossEntropy(torch.autograd.Function):
         stats = ce_ops.ce_local_stats(logits2d, tgt, vocab_start)
         if tp > 1:
             group = ps.get_tensor_model_parallel_group()
-            gathered = torch.empty((tp,) + tuple(stats.shape), dtype=stats.dtype, device=stats.device)
-            dist.all_gather_into_tensor(gathered, stats.contiguous(), group=group)
+            flat = torch.empty((tp * stats.shape[0], stats.shape[1]), dtype=stats.dtype, device=stats.device)
+            dist.all_gather_into_tensor(flat, stats.contiguous(), group=group)
+            gathered = flat.view((tp,) + tuple(stats.shape))
             gmax = gathered[..., 0].max(dim=0).values
             sumexp = (gathered[..., 1] * torch.exp(gathered[..., 0] - gmax)).sum(dim=0)
             tlogit = gathered[..., 2].sum(dim=0)

@@ -78,12 +78,12 @@ def _gather_along_dim(input_: torch.Tensor, dim: int, group=None) -> torch.Tenso
         return input_
     dim = dim % input_.dim()
     src = input_.contiguous()
-    out = torch.empty((world,) + tuple(src.shape), dtype=src.dtype, device=src.device)
-    dist.all_gather_into_tensor(out, src, group=group)
+    flat = torch.empty((world * src.shape[0],) + tuple(src.shape[1:]), dtype=src.dtype, device=src.device)
+    dist.all_gather_into_tensor(flat, src, group=group)
     if dim == 0:
-        return out.reshape((world * src.shape[0],) + tuple(src.shape[1:]))
+        return flat
     # [world, d0, .., dk, ..] -> [d0, .., world*dk, ..]
-    out = out.movedim(0, dim)
+    out = flat.view((world,) + tuple(src.shape)).movedim(0, dim)
     shape = list(src.shape)
     shape[dim] *= world
     return out.reshape(shape)
@@ -107,7 +107,7 @@ def _reduce_scatter_along_dim(input_: torch.Tensor, dim: int, group=None) -> tor
         part = shape[dim] // world
         view = input_.reshape(shape[:dim] + [world, part] + shape[dim + 1:]).movedim(dim, 0).contiguous()
         out = torch.empty(view.shape[1:], dtype=input_.dtype, device=input_.device)
-        dist.reduce_scatter_tensor(out, view, group=group)
+        dist.reduce_scatter_tensor(out, view.view((world * view.shape[1],) + tuple(view.shape[2:])), group=group)
         return out
     src = input_.contiguous()
     out = torch.empty((src.shape[0] // world,) + tuple(src.shape[1:]), dtype=src.dtype, device=src.device)
@@ -123,10 +123,10 @@ def _all_to_all_in_expert_parallel_region(x: torch.Tensor, split_dim: int, conca
     if ep == 1:
         return x
     group = ps.get_expert_model_parallel_group()
-    chunks = [c.contiguous() for c in torch.chunk(x, ep, dim=split_dim)]
-    recv = [torch.empty_like(chunks[0]) for _ in range(ep)]
-    dist.all_to_all(recv, chunks, group=group)
-    return torch.cat(recv, dim=concat_dim)
+    send = torch.stack([c for c in torch.chunk(x, ep, dim=split_dim)], dim=0).contiguous()
+    recv = torch.empty_like(send)
+    dist.all_to_all_single(recv, send, group=group)  # one call; works on nccl and gloo
+    return torch.cat(list(recv.unbind(0)), dim=concat_dim)
 
 
 # ---------------------------------------------------------------------------

@@ -1,0 +1,370 @@
+"""``save_checkpoint`` / ``load_checkpoint`` with per-(dp, ep, tp, pp)-rank sharded files.
+
+Reference: ``src/neuronx_distributed/trainer/checkpoint.py:50-853``.  Directory contract kept byte-for-byte::
+
+    <dir>/<tag>/checkpoint                  marker written when the save starts
+    <dir>/<tag>/done                        marker written after EVERY rank finished
+    <dir>/<tag>/model/dp_rank_00[_ep_rank_EE]_tp_rank_TT_pp_rank_PP.pt        xser: ref file, else torch.save
+    <dir>/<tag>/model/<...>.pt.tensors/tensor_<i>.pt  and  <...>.pt.info.pt   xser only
+    <dir>/<tag>/optim/dp_rank_DD_tp_rank_TT_pp_rank_PP.pt                     ZeRO-1: one per dp rank
+    <dir>/<tag>/scheduler.pt     <dir>/<tag>/user_content.pt
+
+What differs from the reference is the plumbing, not the contract: device->host copies happen on a side
+stream into pinned memory and the file writes run in a background thread (``async_save``); the load path uses a
+real ``broadcast`` inside the DP group instead of all-reducing zeros (reference ``:359-360``).
+"""
+from __future__ import annotations
+
+import atexit
+import concurrent.futures
+import os
+from typing import Any, Dict, List, Optional, Tuple
+
+import torch
+import torch.distributed as dist
+
+from ..parallel import parallel_state as ps
+from ..utils import xser
+from ..utils.logger import get_logger
+from .checkpoint_storage import BaseCheckpointStorage, create_checkpoint_storage
+
+logger = get_logger()
+
+
+def _rendezvous(name: str) -> None:
+    if dist.is_initialized() and os.environ.get("NXD_SKIP_RENDEZVOUS", "0") != "1":
+        dist.barrier()
+
+
+def _rank() -> int:
+    return dist.get_rank() if dist.is_initialized() else 0
+
+
+def _mp() -> bool:
+    return ps.model_parallel_is_initialized()
+
+
+def _ranks() -> Tuple[int, int, int, int, int]:
+    if not _mp():
+        return 0, 0, 0, 0, 1
+    return (ps.get_data_parallel_rank(), ps.get_tensor_model_parallel_rank(), ps.get_pipeline_model_parallel_rank(),
+            ps.get_expert_model_parallel_rank(), ps.get_expert_model_parallel_size())
+
+
+def _shard_name(dp_rank: int, tp_rank: int, pp_rank: int, ep_rank: Optional[int] = None) -> str:
+    ep = f"_ep_rank_{ep_rank:02d}" if ep_rank is not None else ""
+    return f"dp_rank_{dp_rank:02d}{ep}_tp_rank_{tp_rank:02d}_pp_rank_{pp_rank:02d}.pt"
+
+
+def _to_cpu(obj: Any) -> Any:
+    """Snapshot every tensor to host memory (pinned staging for CUDA tensors, one sync at the end)."""
+    cuda_seen = []
+
+    def conv(ts):
+        out = []
+        for t in ts:
+            if t.is_cuda:
+                host = torch.empty(t.shape, dtype=t.dtype, device="cpu", pin_memory=True)
+                host.copy_(t.detach(), non_blocking=True)
+                cuda_seen.append(1)
+                out.append(host)
+            else:
+                out.append(t.detach().clone())
+        return out
+
+    res = xser.rewrite_data(obj, lambda x: isinstance(x, torch.Tensor), conv)
+    if cuda_seen:
+        torch.cuda.current_stream().synchronize()
+    return res
+
+
+class CheckpointIOState:
+    """Tracks one checkpoint save: begin -> add tasks -> end (reference ``:99-285``).  With ``async_save`` the
+    file writes run on a single background thread; the ``done`` marker is written only after every rank's writes
+    finished, so a crash can never leave a tag that looks complete."""
+
+    def __init__(self, async_save: bool = False):
+        self._async = async_save
+        self._executor = concurrent.futures.ThreadPoolExecutor(max_workers=1) if async_save else None
+        self._pending: List[concurrent.futures.Future] = []
+        self._storage: Optional[BaseCheckpointStorage] = None
+        self._tag: Optional[str] = None
+        self._tasks: List[Tuple[Any, str, bool]] = []
+        self._finalize: Optional[Tuple[BaseCheckpointStorage, str, int]] = None
+
+    # -- lifecycle -----------------------------------------------------------------------------------
+    def begin(self, storage: BaseCheckpointStorage, tag: str) -> None:
+        self.wait_all()
+        self._storage, self._tag, self._tasks = storage, tag, []
+        _rendezvous("ckpt-begin-enter")
+        if _rank() == 0:
+            storage.create_dir(tag)
+            storage.save_text("1", os.path.join(tag, "checkpoint"))
+            if storage.file_exists(os.path.join(tag, "done")):
+                storage.remove_file(os.path.join(tag, "done"))  # overwriting a tag: not complete until we say so
+        _rendezvous("ckpt-begin-exit")
+
+    def add_save_task(self, obj: Any, filename: str, use_xser: bool = False) -> None:
+        self._tasks.append((_to_cpu(obj), filename, use_xser))
+
+    def _write_all(self, storage: BaseCheckpointStorage, tasks) -> None:
+        for obj, filename, use_x in tasks:
+            if use_x:
+                ref, tensors = obj
+                for tid, t in tensors:
+                    storage.save_object(t, f"{filename}.tensors/tensor_{tid}.pt")
+                if ref is not None:
+                    storage.save_object(ref[0], filename)
+                    storage.save_object(ref[1], filename + ".info.pt")
+            else:
+                storage.save_object(obj, filename)
+
+    def end(self, num_kept_ckpts: Optional[int] = None) -> None:
+        storage, tag, tasks = self._storage, self._tag, self._tasks
+        self._tasks = []
+        if self._async:
+            fut = self._executor.submit(self._write_all, storage, tasks)
+            self._pending.append(fut)
+            self._finalize = (storage, tag, num_kept_ckpts if num_kept_ckpts is not None else -1)
+        else:
+            self._write_all(storage, tasks)
+            self._complete(storage, tag, num_kept_ckpts)
+
+    def _complete(self, storage, tag, num_kept_ckpts) -> None:
+        _rendezvous("ckpt-end-enter")
+        if _rank() == 0:
+            storage.save_text("1", os.path.join(tag, "done"))
+        _rendezvous("ckpt-end-exit")
+        if num_kept_ckpts is not None and num_kept_ckpts > 0:
+            self._prune(storage, num_kept_ckpts)
+
+    def _prune(self, storage: BaseCheckpointStorage, keep: int) -> None:
+        """Delete the oldest completed tags beyond ``keep`` and any incomplete (crashed) tags other than the
+        current one.  Order: ``done`` marker first, then the directory, so a half-deleted tag is never picked up
+        by auto-resume (reference ``:62-89,222-259``)."""
+        if _rank() == 0:
+            done = storage.list_completed_checkpoint_tags()
+            victims = done[:-keep] if len(done) > keep else []
+            for t in storage.list_checkpoint_tags():
+                if t not in done and t != self._tag:
+                    victims.append(t)
+            for t in victims:
+                storage.remove_file(os.path.join(t, "done"))
+                storage.remove_dir(t)
+        _rendezvous("ckpt-prune")
+
+    def wait_all(self) -> None:
+        """Block until queued async writes are on disk, then publish ``done`` (collective)."""
+        for f in self._pending:
+            f.result()
+        self._pending = []
+        if self._finalize is not None:
+            storage, tag, keep = self._finalize
+            self._finalize = None
+            self._complete(storage, tag, keep if keep > 0 else None)
+
+
+g_iostate: Optional[CheckpointIOState] = None
+
+
+def _get_iostate(async_save: bool) -> CheckpointIOState:
+    global g_iostate
+    if g_iostate is None or g_iostate._async != async_save:
+        if g_iostate is not None:
+            g_iostate.wait_all()
+        g_iostate = CheckpointIOState(async_save)
+        atexit.register(finalize_checkpoint)
+    return g_iostate
+
+
+def finalize_checkpoint() -> None:
+    """Flush pending asynchronous saves (call before exit / before loading; reference ``:642-647``)."""
+    if g_iostate is not None:
+        g_iostate.wait_all()
+
+
+def has_checkpoint(checkpoint_dir_str: str) -> bool:
+    return len(create_checkpoint_storage(checkpoint_dir_str).list_completed_checkpoint_tags()) > 0
+
+
+# ------------------------------------------------------------------------------------------------------
+# xser split: each DP replica writes 1/dp of the bytes (reference :393-470)
+# ------------------------------------------------------------------------------------------------------
+
+def _bin_pack(sizes: List[int], bins: int) -> List[int]:
+    """Greedy largest-first assignment of items to ``bins`` minimising the max load; returns bin per item."""
+    order = sorted(range(len(sizes)), key=lambda i: -sizes[i])
+    load = [0] * bins
+    owner = [0] * len(sizes)
+    for i in order:
+        b = min(range(bins), key=lambda j: (load[j], j))
+        owner[i] = b
+        load[b] += sizes[i]
+    return owner
+
+
+def _xser_prepare(state: Any, replica_rank: int, replicas: int):
+    """-> (ref-file payload or None, [(tid, tensor)] this replica must write)."""
+    ref, tensors = xser.split_tensors(state)
+    sizes = [t.numel() * t.element_size() for t in tensors]
+    owner = _bin_pack(sizes, max(replicas, 1))
+    mine = [(tid, t) for tid, t in enumerate(tensors) if owner[tid] == replica_rank]
+    info = {tid: {"dtype": t.dtype, "shape": tuple(t.shape),
+                  "expert_model_parallel": bool(getattr(t, "expert_model_parallel", False))}
+            for tid, t in enumerate(tensors)}
+    head = (ref, info) if replica_rank == 0 else None
+    return head, mine
+
+
+def _model_state(model) -> Dict[str, Any]:
+    if hasattr(model, "local_state_dict"):
+        return model.local_state_dict()
+    return model.state_dict()
+
+
+def save_checkpoint(checkpoint_dir_str: str, tag: str, model=None, optimizer=None, scheduler=None,
+                    user_content: Any = None, num_workers: int = 8, use_xser: bool = False,
+                    num_kept_ckpts: Optional[int] = None, async_save: bool = False, zero1_optimizer: bool = False,
+                    use_zero1_dcp: bool = False) -> None:
+    """Collective save of model / optimizer / scheduler / user content under ``<dir>/<tag>`` (reference
+    ``checkpoint.py:571-736``)."""
+    storage = create_checkpoint_storage(checkpoint_dir_str)
+    io = _get_iostate(async_save)
+    io.begin(storage, tag)
+    dp_rank, tp_rank, pp_rank, ep_rank, ep_size = _ranks()
+    dp_size = ps.get_data_parallel_size() if _mp() else 1
+
+    if model is not None:
+        state = _model_state(model)
+        has_ep = ep_size > 1 and any(getattr(v, "expert_model_parallel", False) for v in state.values()
+                                     if isinstance(v, torch.Tensor))
+        if has_ep:
+            # expert weights differ per EP rank: one file per ep rank holding the expert tensors, the dense
+            # remainder in the ep_rank-less file written by expert-DP rank 0 of EP rank 0
+            ep_state = {k: v for k, v in state.items() if getattr(v, "expert_model_parallel", False)}
+            dense = {k: v for k, v in state.items() if not getattr(v, "expert_model_parallel", False)}
+            exp_dp_rank = ps.get_expert_data_parallel_rank()
+            if exp_dp_rank == 0:
+                _queue(io, ep_state, os.path.join(tag, "model", _shard_name(0, tp_rank, pp_rank, ep_rank)), use_xser,
+                       0, 1)
+            if dp_rank == 0:
+                _queue(io, dense, os.path.join(tag, "model", _shard_name(0, tp_rank, pp_rank)), use_xser, 0, 1)
+        else:
+            fname = os.path.join(tag, "model", _shard_name(0, tp_rank, pp_rank))
+            if use_xser:
+                _queue(io, state, fname, True, dp_rank, dp_size)
+            elif dp_rank == 0:
+                _queue(io, state, fname, False, 0, 1)
+
+    if optimizer is not None:
+        zero1 = zero1_optimizer or bool(getattr(optimizer, "zero1", False)) or \
+            optimizer.__class__.__name__.endswith("Zero1Optimizer")
+        state = optimizer.state_dict()
+        if use_zero1_dcp and zero1:
+            from ..optimizer.zero_dcp_utils import save_optim_state_dict
+
+            io.wait_all()
+            save_optim_state_dict(os.path.join(checkpoint_dir_str, tag, "optim"), state)
+        elif zero1:
+            _queue(io, state, os.path.join(tag, "optim", _shard_name(dp_rank, tp_rank, pp_rank)), use_xser, 0, 1)
+        elif dp_rank == 0:
+            _queue(io, state, os.path.join(tag, "optim", _shard_name(0, tp_rank, pp_rank)), use_xser, 0, 1)
+
+    if _rank() == 0:
+        if scheduler is not None:
+            io.add_save_task(scheduler.state_dict(), os.path.join(tag, "scheduler.pt"))
+        if user_content is not None:
+            io.add_save_task(user_content, os.path.join(tag, "user_content.pt"))
+    io.end(num_kept_ckpts)
+
+
+def _queue(io: CheckpointIOState, state, fname: str, use_xser: bool, replica_rank: int, replicas: int) -> None:
+    if not use_xser:
+        io.add_save_task(state, fname, False)
+        return
+    head, mine = _xser_prepare(state, replica_rank, replicas)
+    mine_cpu = _to_cpu([t for _, t in mine])
+    io._tasks.append(((head, list(zip([tid for tid, _ in mine], mine_cpu))), fname, True))
+
+
+# ------------------------------------------------------------------------------------------------------
+# load
+# ------------------------------------------------------------------------------------------------------
+
+def _load_obj(storage: BaseCheckpointStorage, fname: str, use_xser: bool, group=None) -> Any:
+    """xser: tensors are read round-robin by the ranks of ``group`` (the DP replicas hold identical model
+    shards) and broadcast, so the file system sees each byte once (reference ``:308-382``)."""
+    if not use_xser:
+        return storage.load_object(fname, map_location="cpu")
+    ref = storage.load_object(fname, map_location="cpu")
+    refs: List[Any] = []
+    xser.rewrite_data(ref, lambda x: isinstance(x, xser.TensorReference), lambda rs: (refs.extend(rs), rs)[1])
+    size = dist.get_world_size(group=group) if (group is not None and dist.is_initialized()) else 1
+    if size == 1:
+        loaded = {r.tid: storage.load_object(f"{fname}.tensors/tensor_{r.tid}.pt", map_location="cpu") for r in refs}
+    else:
+        info = storage.load_object(fname + ".info.pt", map_location="cpu") if storage.file_exists(fname + ".info.pt") \
+            else None
+        my = dist.get_rank(group=group)
+        ranks = dist.get_process_group_ranks(group)
+        dev = torch.device("cuda", torch.cuda.current_device()) if dist.get_backend(group) == "nccl" else "cpu"
+        loaded = {}
+        for i, r in enumerate(sorted(refs, key=lambda x: x.tid)):
+            reader = i % size
+            if reader == my:
+                t = storage.load_object(f"{fname}.tensors/tensor_{r.tid}.pt", map_location="cpu").to(dev)
+            else:
+                assert info is not None, "xser checkpoints without .info.pt can only be loaded without a group"
+                t = torch.empty(info[r.tid]["shape"], dtype=info[r.tid]["dtype"], device=dev)
+            dist.broadcast(t, src=ranks[reader], group=group)
+            loaded[r.tid] = t.cpu()
+    return xser.rewrite_data(ref, lambda x: isinstance(x, xser.TensorReference),
+                             lambda rs: [loaded[r.tid] for r in rs])
+
+
+def load_checkpoint(path: str, tag: Optional[str] = None, model=None, optimizer=None, scheduler=None,
+                    num_workers: int = 8, strict: bool = True, use_zero1_dcp: bool = False) -> Any:
+    """Load what ``save_checkpoint`` wrote; ``tag=None`` resumes from the newest completed tag.  Returns the
+    user content (reference ``checkpoint.py:739-853``)."""
+    finalize_checkpoint()
+    storage = create_checkpoint_storage(path)
+    if tag is None:
+        tags = storage.list_completed_checkpoint_tags()
+        if not tags:
+            raise RuntimeError(f"No completed checkpoint found under {path}")
+        tag = tags[-1]
+    if not storage.file_exists(os.path.join(tag, "done")):
+        raise RuntimeError(f"checkpoint {path}/{tag} is incomplete (no `done` marker)")
+    use_xser = storage.is_checkpoint_xser(tag)
+    dp_rank, tp_rank, pp_rank, ep_rank, ep_size = _ranks()
+    dp_group = ps.get_data_parallel_group() if (_mp() and ps.get_data_parallel_size() > 1) else None
+
+    if model is not None:
+        fname = os.path.join(tag, "model", _shard_name(0, tp_rank, pp_rank))
+        state = _load_obj(storage, fname, use_xser, dp_group)
+        ep_file = os.path.join(tag, "model", _shard_name(0, tp_rank, pp_rank, ep_rank))
+        if ep_size > 1 and storage.file_exists(ep_file):
+            state.update(_load_obj(storage, ep_file, use_xser, None))
+        if hasattr(model, "load_local_state_dict"):
+            model.load_local_state_dict(state, strict=strict)
+        else:
+            model.load_state_dict(state, strict=strict)
+
+    if optimizer is not None:
+        zero1 = bool(getattr(optimizer, "zero1", False)) or optimizer.__class__.__name__.endswith("Zero1Optimizer")
+        if use_zero1_dcp and zero1:
+            from ..optimizer.zero_dcp_utils import load_optim_state_dict
+
+            state = load_optim_state_dict(os.path.join(path, tag, "optim"), optimizer.state_dict())
+        else:
+            fname = os.path.join(tag, "optim", _shard_name(dp_rank if zero1 else 0, tp_rank, pp_rank))
+            state = _load_obj(storage, fname, use_xser, None if zero1 else dp_group)
+        optimizer.load_state_dict(state)
+
+    if scheduler is not None and storage.file_exists(os.path.join(tag, "scheduler.pt")):
+        scheduler.load_state_dict(storage.load_object(os.path.join(tag, "scheduler.pt"), map_location="cpu"))
+    user_content = None
+    if storage.file_exists(os.path.join(tag, "user_content.pt")):
+        user_content = storage.load_object(os.path.join(tag, "user_content.pt"), map_location="cpu")
+    _rendezvous("ckpt-load-done")
+    return user_content
