@@ -18,9 +18,12 @@
 //            M=256, N=BLOCK_N, K=16; tcgen05.commit (multicast to both CTAs) releases smem slots
 //            and publishes finished accumulators.
 //   warp 2   TMEM allocator (2 accumulator stages x BLOCK_N fp32 columns).
-//   warps 4-7 epilogue: tcgen05.ld the 128 x BLOCK_N accumulator (lane = row), convert, store.
-//            The accumulator is double buffered so the epilogue of tile i overlaps the main
-//            loop of tile i+1.
+//   warps 4-7 epilogue: tcgen05.ld the 128 x BLOCK_N accumulator (lane = row), convert, stage 32 x 128 B
+//            boxes in swizzled smem and hand them to the TMA unit (bulk tensor store; fp32
+//            accumulate = TMA reduce-add).  The accumulator is double buffered so the epilogue of
+//            tile i overlaps the main loop of tile i+1.  (The first version stored 16 B per thread
+//            straight from registers; at K = 3072 that epilogue (~50k cycles / tile) was longer than
+//            the main loop (~25k) and capped the kernel at 0.66 of the measured peak.)
 // Tiles are visited persistently (grid = #SM/2 clusters) in an L2-friendly grouped order.
 #include "common.cuh"
 #include "gemm_tcgen05.cuh"
@@ -31,7 +34,7 @@ namespace nxd_gemm {
 template <int BN, bool A_MN, bool B_MN, int OUT_MODE>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
 gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
-                 const EpilogueArgs ep, int M, int N, int K) {
+                 const __grid_constant__ CUtensorMap tmap_d, int M, int N, int K) {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     using L = SmemLayout<BN>;
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -57,6 +60,7 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     if (warp == 0 && lane == 0) {
         ptx::prefetch_tensormap(&tmap_a);
         ptx::prefetch_tensormap(&tmap_b);
+        ptx::prefetch_tensormap(&tmap_d);
     }
     if (warp == 1 && lane == 0) {
         for (int i = 0; i < kStages; ++i) {
@@ -148,29 +152,68 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         }
     } else if (warp >= kFirstEpilogueWarp) {
         // ======================= epilogue =======================
+        // TMEM -> registers -> swizzled smem staging -> TMA store (or TMA fp32 reduce-add): every global write is
+        // a full 128-byte row segment issued by the TMA unit, nothing goes through the LSU store path.
         const int q = warp & 3;  // TMEM lane quadrant this warp may access
+        constexpr int kCols = (OUT_MODE == kOutBF16) ? 64 : 32;  // accumulator columns per 128-byte staging row
+        uint8_t* stg = smem + L::kStagingOffset + q * L::kStagingBytesPerWarp;
+        int buf = 0;
         int acc = 0;
         uint32_t acc_phase = 0;
         for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
             int tm, tn;
             tile_coords(tile, num_m_tiles, num_n_tiles, tm, tn);
-            const int row = tm * kTileM + (int)cta_rank * kBlockM + q * 32 + lane;
+            const int row0 = tm * kTileM + (int)cta_rank * kBlockM + q * 32;
             const int n0 = tn * BN;
             ptx::mbar_wait(&tmem_full_bar[acc], acc_phase);
             ptx::tcgen05_fence_after();
             const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + acc * BN;
 #pragma unroll 1
-            for (int c = 0; c < BN / 32; ++c) {
-                uint32_t r[32];
-                ptx::tmem_ld_32x32b_x32(taddr + c * 32, r);
+            for (int c = 0; c < BN / kCols; ++c) {
+                if (lane == 0) ptx::bulk_wait_read<1>();  // the store that used this buffer two chunks ago has read it
+                __syncwarp();
+                uint32_t r[kCols];
+                ptx::tmem_ld_32x32b_x32(taddr + c * kCols, r);
+                if constexpr (kCols == 64) ptx::tmem_ld_32x32b_x32(taddr + c * kCols + 32, r + 32);
                 ptx::tmem_ld_wait();
-                store_chunk<OUT_MODE>(ep, r, row, n0 + c * 32, M, N);
+                if (c == BN / kCols - 1) {  // accumulator fully read: hand it back to the MMA warp early
+                    ptx::tcgen05_fence_before();
+                    __syncwarp();
+                    if (lane == 0) ptx::mbar_arrive_cluster(&tmem_empty_bar[acc], 0);
+                }
+                uint8_t* dst = stg + buf * (32 * 128) + lane * 128;
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    uint4 v;
+                    if constexpr (OUT_MODE == kOutBF16) {
+                        bf162 p0 = __floats2bfloat162_rn(__uint_as_float(r[8 * j]), __uint_as_float(r[8 * j + 1]));
+                        bf162 p1 = __floats2bfloat162_rn(__uint_as_float(r[8 * j + 2]), __uint_as_float(r[8 * j + 3]));
+                        bf162 p2 = __floats2bfloat162_rn(__uint_as_float(r[8 * j + 4]), __uint_as_float(r[8 * j + 5]));
+                        bf162 p3 = __floats2bfloat162_rn(__uint_as_float(r[8 * j + 6]), __uint_as_float(r[8 * j + 7]));
+                        v = make_uint4(*reinterpret_cast<uint32_t*>(&p0), *reinterpret_cast<uint32_t*>(&p1),
+                                       *reinterpret_cast<uint32_t*>(&p2), *reinterpret_cast<uint32_t*>(&p3));
+                    } else {
+                        v = make_uint4(r[4 * j], r[4 * j + 1], r[4 * j + 2], r[4 * j + 3]);
+                    }
+                    *reinterpret_cast<uint4*>(dst + ((j ^ (lane & 7)) << 4)) = v;
+                }
+                ptx::fence_proxy_async();
+                __syncwarp();
+                if (lane == 0) {
+                    const int col0 = n0 + c * kCols;
+                    if (col0 < N && row0 < M) {
+                        if constexpr (OUT_MODE == kOutF32Acc)
+                            ptx::tma_reduce_add_2d(&tmap_d, stg + buf * (32 * 128), col0, row0);
+                        else
+                            ptx::tma_store_2d(&tmap_d, stg + buf * (32 * 128), col0, row0);
+                    }
+                    ptx::bulk_commit();
+                }
+                buf ^= 1;
             }
-            ptx::tcgen05_fence_before();
-            __syncwarp();
-            if (lane == 0) ptx::mbar_arrive_cluster(&tmem_empty_bar[acc], 0);
             if (++acc == kAccStages) { acc = 0; acc_phase ^= 1; }
         }
+        if (lane == 0) ptx::bulk_wait<0>();
     }
 
     // ---- teardown: both CTAs must be done with TMEM (and with remote barrier traffic) ----
@@ -184,7 +227,7 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
 // ---------------------------------------------------------------------------------------------
 
 template <int BN, bool A_MN, bool B_MN, int OUT_MODE>
-static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const EpilogueArgs& ep, int M, int N, int K,
+static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& td, int M, int N, int K,
                   cudaStream_t stream) {
     using L = SmemLayout<BN>;
     auto kern = gemm_pair_kernel<BN, A_MN, B_MN, OUT_MODE>;
@@ -196,18 +239,18 @@ static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const EpilogueAr
     const int num_tiles = ((M + kTileM - 1) / kTileM) * ((N + BN - 1) / BN);
     int clusters = nxd_num_sms() / 2;
     if (clusters > num_tiles) clusters = num_tiles;
-    kern<<<dim3(clusters * 2), dim3(kThreads), L::kSmemBytes, stream>>>(ta, tb, ep, M, N, K);
+    kern<<<dim3(clusters * 2), dim3(kThreads), L::kSmemBytes, stream>>>(ta, tb, td, M, N, K);
     NXD_LAUNCH_CHECK();
     return 0;
 }
 
 template <int BN, int OUT_MODE>
-static int dispatch_layout(int layout, const CUtensorMap& ta, const CUtensorMap& tb, const EpilogueArgs& ep, int M,
+static int dispatch_layout(int layout, const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& td, int M,
                            int N, int K, cudaStream_t s) {
     switch (layout) {
-        case kLayoutNT: return launch<BN, false, false, OUT_MODE>(ta, tb, ep, M, N, K, s);
-        case kLayoutNN: return launch<BN, false, true, OUT_MODE>(ta, tb, ep, M, N, K, s);
-        default: return launch<BN, true, true, OUT_MODE>(ta, tb, ep, M, N, K, s);
+        case kLayoutNT: return launch<BN, false, false, OUT_MODE>(ta, tb, td, M, N, K, s);
+        case kLayoutNN: return launch<BN, false, true, OUT_MODE>(ta, tb, td, M, N, K, s);
+        default: return launch<BN, true, true, OUT_MODE>(ta, tb, td, M, N, K, s);
     }
 }
 
@@ -227,6 +270,7 @@ int run(int layout, const void* a, const void* b, long long lda, long long ldb, 
     NXD_REQUIRE(layout >= 0 && layout <= 2, "gemm: bad layout %d", layout);
     NXD_REQUIRE(M > 0 && N > 0 && K > 0, "gemm: empty problem %dx%dx%d", M, N, K);
     NXD_REQUIRE(lda % 8 == 0 && ldb % 8 == 0 && ep.ldd % 8 == 0, "gemm: leading dims must be multiples of 8 elements");
+    NXD_REQUIRE(N % 8 == 0 && (ep.mode == kOutBF16 || N % 4 == 0), "gemm: N must be a multiple of 8");
     NXD_REQUIRE(((uintptr_t)a & 15) == 0 && ((uintptr_t)b & 15) == 0 && ((uintptr_t)ep.d & 15) == 0,
                 "gemm: operands must be 16-byte aligned");
     const bool a_mn = layout == kLayoutTN;
@@ -242,11 +286,16 @@ int run(int layout, const void* a, const void* b, long long lda, long long ldb, 
     if (!b_mn) rc = make_tmap_2d(&tb, b, (uint64_t)K, (uint64_t)N, (uint64_t)ldb, 64, bn / 2);
     else rc = make_tmap_2d(&tb, b, (uint64_t)N, (uint64_t)K, (uint64_t)ldb, 64, kBlockK);
     if (rc) return rc;
+    // D: staged per warp as 32 rows x 128 bytes (64 bf16 or 32 fp32 columns)
+    CUtensorMap td;
+    if (ep.mode == kOutBF16) rc = make_tmap_2d(&td, ep.d, (uint64_t)N, (uint64_t)M, (uint64_t)ep.ldd, 64, 32, 2);
+    else rc = make_tmap_2d(&td, ep.d, (uint64_t)N, (uint64_t)M, (uint64_t)ep.ldd, 32, 32, 4);
+    if (rc) return rc;
 #define NXD_GEMM_DISPATCH(BN_)                                                                           \
     switch (ep.mode) {                                                                                   \
-        case kOutBF16: return dispatch_layout<BN_, kOutBF16>(layout, ta, tb, ep, M, N, K, stream);       \
-        case kOutF32: return dispatch_layout<BN_, kOutF32>(layout, ta, tb, ep, M, N, K, stream);         \
-        case kOutF32Acc: return dispatch_layout<BN_, kOutF32Acc>(layout, ta, tb, ep, M, N, K, stream);   \
+        case kOutBF16: return dispatch_layout<BN_, kOutBF16>(layout, ta, tb, td, M, N, K, stream);       \
+        case kOutF32: return dispatch_layout<BN_, kOutF32>(layout, ta, tb, td, M, N, K, stream);         \
+        case kOutF32Acc: return dispatch_layout<BN_, kOutF32Acc>(layout, ta, tb, td, M, N, K, stream);   \
         default: nxd_set_error("gemm: bad output mode %d", ep.mode); return -1;                          \
     }
     if (bn == 256) { NXD_GEMM_DISPATCH(256) }

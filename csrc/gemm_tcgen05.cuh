@@ -22,7 +22,10 @@ struct SmemLayout {
     static constexpr int kBBytes = (BN / 2) * kBlockK * 2;       // this CTA's half of B
     static constexpr int kStageBytes = kABytes + kBBytes;
     static constexpr int kStages = (BN == 256) ? 6 : 8;
-    static constexpr int kBarrierOffset = kStages * kStageBytes;
+    // epilogue staging: per epilogue warp two 32-row x 128-byte buffers (SWIZZLE_128B boxes for the TMA store)
+    static constexpr int kStagingOffset = kStages * kStageBytes;
+    static constexpr int kStagingBytesPerWarp = 2 * 32 * 128;
+    static constexpr int kBarrierOffset = kStagingOffset + kEpilogueWarps * kStagingBytesPerWarp;
     static constexpr int kBarrierBytes = (2 * kStages + 2 * kAccStages) * 8 + 16;
     static constexpr int kSmemBytes = kBarrierOffset + kBarrierBytes + 1024;  // +1024: manual alignment slack
     static constexpr int kTmemCols = kAccStages * BN;            // 512 or 256 (power of two)
@@ -47,43 +50,10 @@ __device__ __forceinline__ void tile_coords(int tile, int num_m_tiles, int num_n
     tn = in_group / rows_in_group;
 }
 
-// One thread owns one output row and 32 consecutive fp32 accumulator columns.
-template <int OUT_MODE>
-__device__ __forceinline__ void store_chunk(const EpilogueArgs& ep, const uint32_t* r, int row, int col0, int M,
-                                            int N) {
-    if (row >= M || col0 >= N) return;
-    if constexpr (OUT_MODE == kOutBF16) {
-        bf16* dst = reinterpret_cast<bf16*>(ep.d) + (size_t)row * ep.ldd + col0;
-#pragma unroll
-        for (int v = 0; v < 4; ++v) {
-            if (col0 + v * 8 < N) {  // N % 8 == 0 is required by the host wrapper
-                float f[8];
-#pragma unroll
-                for (int k = 0; k < 8; ++k) f[k] = __uint_as_float(r[v * 8 + k]);
-                reinterpret_cast<bf16x8*>(dst)[v] = pack8(f);
-            }
-        }
-    } else {
-        float* dst = reinterpret_cast<float*>(ep.d) + (size_t)row * ep.ldd + col0;
-#pragma unroll
-        for (int v = 0; v < 8; ++v) {
-            if (col0 + v * 4 < N) {
-                float4 o = make_float4(__uint_as_float(r[v * 4]), __uint_as_float(r[v * 4 + 1]),
-                                       __uint_as_float(r[v * 4 + 2]), __uint_as_float(r[v * 4 + 3]));
-                if constexpr (OUT_MODE == kOutF32Acc) {
-                    const float4 old = reinterpret_cast<const float4*>(dst)[v];
-                    o.x += old.x; o.y += old.y; o.z += old.z; o.w += old.w;
-                }
-                reinterpret_cast<float4*>(dst)[v] = o;
-            }
-        }
-    }
-}
-
-// 2-D bf16 tensor map: `inner` contiguous elements, `outer` rows with pitch `pitch_elems`;
-// box = {box_inner, box_outer}; SWIZZLE_128B (box_inner must be 64 bf16 = 128 B).
+// 2-D tensor map: `inner` contiguous elements, `outer` rows with pitch `pitch_elems`;
+// box = {box_inner, box_outer}; SWIZZLE_128B (box_inner * elem_bytes must be 128 B).  elem_bytes 2 = bf16, 4 = fp32.
 int make_tmap_2d(CUtensorMap* out, const void* base, uint64_t inner, uint64_t outer, uint64_t pitch_elems,
-                 uint32_t box_inner, uint32_t box_outer);
+                 uint32_t box_inner, uint32_t box_outer, int elem_bytes = 2);
 
 int pick_block_n(int M, int N);
 

@@ -19,14 +19,14 @@ static PFN_cuTensorMapEncodeTiled_v12000 get_encode() {
 }
 
 int make_tmap_2d(CUtensorMap* out, const void* base, uint64_t inner, uint64_t outer, uint64_t pitch_elems,
-                 uint32_t box_inner, uint32_t box_outer) {
+                 uint32_t box_inner, uint32_t box_outer, int elem_bytes) {
     auto encode = get_encode();
     NXD_REQUIRE(encode != nullptr, "cuTensorMapEncodeTiled could not be resolved from the driver");
     cuuint64_t dims[2] = {inner, outer};
-    cuuint64_t strides[1] = {pitch_elems * 2};  // bytes, for dim 1
+    cuuint64_t strides[1] = {pitch_elems * (cuuint64_t)elem_bytes};  // bytes, for dim 1
     cuuint32_t box[2] = {box_inner, box_outer};
     cuuint32_t estr[2] = {1, 1};
-    CUresult r = encode(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+    CUresult r = encode(out, elem_bytes == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     NXD_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed (%d): inner=%llu outer=%llu pitch=%llu box=%ux%u",
