@@ -1,0 +1,444 @@
+// Flash attention FORWARD on 5th-gen tensor cores (tcgen05 + TMEM + TMA), sm_100a  (SURVEY G4/G6, C23).
+//
+// Same contract as nxd_flash_attn_fwd in flash_attn.cu (reference: the external NKI `flash_fwd` kernel behind
+// src/neuronx_distributed/kernels/flash_attn.py:151-191 and the inference prefill kernel,
+// examples/inference/modules/attention/attention_base.py:98-139); this is the fast path, the mma.sync kernel
+// stays as the portable fallback and as a second oracle in the tests.
+//
+// One CTA = 128 query rows of one (batch, head); 192 threads, TWO CTAs per SM so that one CTA's softmax overlaps
+// the other CTA's MMAs on the shared tensor core:
+//   warp 0    TMA producer: Q once (4-D tensor map over the strided [B,H,S,D] view), then K/V tiles of 64 rows into a
+//             3-slot ring in CONSUMPTION order  K0, K1, V0, K2, V1, ...  (so a slot's next load never waits on a
+//             late MMA).  K and V tiles have the same smem image (64-wide column groups of 128-byte swizzled rows);
+//             only the UMMA descriptor differs: K is the K-major B operand of S = Q K^T, V the MN-major B of O += P V.
+//   warp 1    TMEM allocation (O: D columns, S: 64 columns) and MMA issue.  S(j+1) is issued BEFORE waiting for
+//             P(j), so it runs while the softmax warps work on tile j.
+//   warps 2-5 softmax: one thread per query row (TMEM lane).  tcgen05.ld S -> scale, mask, running max, exp2 ->
+//             bf16 P written to swizzled smem (the K-major A operand of the PV MMA).  O stays in TMEM across the
+//             whole loop; it is rescaled (tcgen05.ld / st) only when the running max moved by more than 2^8
+//             ("lazy rescale"), which is rare after the first tiles.  Epilogue: O / l -> bf16 -> smem -> TMA store.
+#include "common.cuh"
+#include "gemm_tcgen05.cuh"
+#include "ptx.cuh"
+
+#include <cudaTypedefs.h>
+
+namespace {
+
+constexpr int kBM = 128;
+constexpr int kBN = 64;
+constexpr int kSlots = 3;
+constexpr int kThreadsTc = 192;
+constexpr float kRescaleThreshold = 8.0f;  // log2 units
+
+struct TcParams {
+    float* lse;
+    int B, Hq, Hkv, Sq, Sk;
+    int pos_q[3], pos_k[3], pos_v[3], pos_o[3];  // coordinate slot (1..3) of (row, head, batch) in each tensor map
+    float scale_log2;
+};
+
+template <int D>
+struct TcSmem {
+    static constexpr int kQBytes = kBM * D * 2;
+    static constexpr int kSlotBytes = kBN * D * 2;
+    static constexpr int kPBytes = kBM * kBN * 2;
+    static constexpr int kQOff = 0;
+    static constexpr int kRingOff = kQBytes;
+    static constexpr int kPOff = kRingOff + kSlots * kSlotBytes;
+    static constexpr int kBarOff = kPOff + kPBytes;
+    static constexpr int kNumBars = 1 + 2 * kSlots + 4;
+    static constexpr int kBytes = kBarOff + kNumBars * 8 + 16 + 1024;  // + manual 1024-byte alignment slack
+    static constexpr int kTmemCols = (D + kBN <= 128) ? 128 : 256;
+};
+
+__device__ __forceinline__ void tma_load_4d(const CUtensorMap* map, uint64_t* bar, void* dst, int c0, int c1, int c2,
+                                            int c3) {
+    asm volatile(
+        "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
+        ::"r"(ptx::smem_u32(dst)), "l"(reinterpret_cast<uint64_t>(map)), "r"(ptx::smem_u32(bar)), "r"(c0), "r"(c1),
+        "r"(c2), "r"(c3)
+        : "memory");
+}
+__device__ __forceinline__ void tma_store_4d(const CUtensorMap* map, const void* src, int c0, int c1, int c2, int c3) {
+    asm volatile("cp.async.bulk.tensor.4d.global.shared::cta.bulk_group [%0, {%2, %3, %4, %5}], [%1];" ::"l"(
+                     reinterpret_cast<uint64_t>(map)),
+                 "r"(ptx::smem_u32(src)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+                 : "memory");
+}
+__device__ __forceinline__ void coords(const int* pos, int row, int h, int b, int* c) {
+    c[pos[0]] = row;
+    c[pos[1]] = h;
+    c[pos[2]] = b;
+}
+
+__device__ __forceinline__ void tmem_st_32x32b_x32(uint32_t taddr, const uint32_t* r) {
+    asm volatile(
+        "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
+        "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "
+        "%17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, %32};" ::"r"(taddr),
+        "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]), "r"(r[9]),
+        "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15]), "r"(r[16]), "r"(r[17]), "r"(r[18]),
+        "r"(r[19]), "r"(r[20]), "r"(r[21]), "r"(r[22]), "r"(r[23]), "r"(r[24]), "r"(r[25]), "r"(r[26]), "r"(r[27]),
+        "r"(r[28]), "r"(r[29]), "r"(r[30]), "r"(r[31])
+        : "memory");
+}
+__device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+
+template <int D, bool CAUSAL>
+__global__ void __launch_bounds__(kThreadsTc, 2)
+fa_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_k,
+                 const __grid_constant__ CUtensorMap tmap_v, const __grid_constant__ CUtensorMap tmap_o,
+                 const TcParams p) {
+    using L = TcSmem<D>;
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* sQ = smem + L::kQOff;
+    uint8_t* sRing = smem + L::kRingOff;
+    uint8_t* sP = smem + L::kPOff;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L::kBarOff);
+    uint64_t* q_full = bars;
+    uint64_t* slot_full = bars + 1;
+    uint64_t* slot_empty = slot_full + kSlots;
+    uint64_t* s_full = slot_empty + kSlots;
+    uint64_t* s_empty = s_full + 1;
+    uint64_t* p_full = s_empty + 1;
+    uint64_t* pv_done = p_full + 1;
+    uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(pv_done + 1);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int mb = gridDim.x - 1 - blockIdx.x;  // late (long) causal blocks first
+    const int hq = blockIdx.y, b = blockIdx.z;
+    const int hkv = hq / (p.Hq / p.Hkv);
+    const int m0 = mb * kBM;
+    const int offset = p.Sk - p.Sq;
+    int n_tiles = (p.Sk + kBN - 1) / kBN;
+    if (CAUSAL) n_tiles = min(n_tiles, max((m0 + kBM + offset + kBN - 1) / kBN, 0));
+
+    if (warp == 0 && lane == 0) {
+        ptx::prefetch_tensormap(&tmap_q);
+        ptx::prefetch_tensormap(&tmap_k);
+        ptx::prefetch_tensormap(&tmap_v);
+        ptx::prefetch_tensormap(&tmap_o);
+        ptx::mbar_init(q_full, 1);
+        for (int i = 0; i < kSlots; ++i) {
+            ptx::mbar_init(&slot_full[i], 1);
+            ptx::mbar_init(&slot_empty[i], 1);
+        }
+        ptx::mbar_init(s_full, 1);
+        ptx::mbar_init(s_empty, 128);
+        ptx::mbar_init(p_full, 128);
+        ptx::mbar_init(pv_done, 1);
+        ptx::fence_barrier_init();
+    }
+    if (warp == 1) ptx::tmem_alloc<1>(tmem_ptr_smem, L::kTmemCols);
+    ptx::tcgen05_fence_before();
+    __syncthreads();
+    ptx::tcgen05_fence_after();
+    const uint32_t tmem_base = *tmem_ptr_smem;
+    const uint32_t tmem_o = tmem_base;
+    const uint32_t tmem_s = tmem_base + D;
+
+    if (warp == 0) {
+        // ============================ TMA producer ============================
+        if (lane == 0 && n_tiles > 0) {
+            int c[4];
+            ptx::mbar_arrive_expect_tx(q_full, L::kQBytes);
+#pragma unroll
+            for (int g = 0; g < D / 64; ++g) {
+                c[0] = g * 64;
+                coords(p.pos_q, m0, hq, b, c);
+                tma_load_4d(&tmap_q, q_full, sQ + g * (kBM * 128), c[0], c[1], c[2], c[3]);
+            }
+            int it = 0;
+            auto load = [&](const CUtensorMap* map, const int* pos, int row0) {
+                const int slot = it % kSlots;
+                const uint32_t ph = (uint32_t)(it / kSlots) & 1u;
+                ptx::mbar_wait(&slot_empty[slot], ph ^ 1u);
+                ptx::mbar_arrive_expect_tx(&slot_full[slot], L::kSlotBytes);
+#pragma unroll
+                for (int g = 0; g < D / 64; ++g) {
+                    c[0] = g * 64;
+                    coords(pos, row0, hkv, b, c);
+                    tma_load_4d(map, &slot_full[slot], sRing + slot * L::kSlotBytes + g * (kBN * 128), c[0], c[1], c[2],
+                                c[3]);
+                }
+                ++it;
+            };
+            load(&tmap_k, p.pos_k, 0);
+            for (int j = 0; j < n_tiles; ++j) {
+                if (j + 1 < n_tiles) load(&tmap_k, p.pos_k, (j + 1) * kBN);
+                load(&tmap_v, p.pos_v, j * kBN);
+            }
+        }
+    } else if (warp == 1) {
+        // ============================ MMA issuer ============================
+        if (lane == 0 && n_tiles > 0) {
+            constexpr uint32_t idesc_s = ptx::make_idesc_bf16(kBM, kBN, 0, 0);
+            constexpr uint32_t idesc_o = ptx::make_idesc_bf16(kBM, D, 0, 1);
+            const uint32_t q_addr = ptx::smem_u32(sQ), ring_addr = ptx::smem_u32(sRing), p_addr = ptx::smem_u32(sP);
+            int it = 0;
+            auto issue_s = [&](int j) {
+                const int slot = it % kSlots;
+                const uint32_t ph = (uint32_t)(it / kSlots) & 1u;
+                ++it;
+                ptx::mbar_wait(&slot_full[slot], ph);
+                ptx::mbar_wait(s_empty, ((uint32_t)j & 1u) ^ 1u);  // softmax(j-1) has read S out of TMEM
+                ptx::tcgen05_fence_after();
+                const uint32_t kb = ring_addr + slot * L::kSlotBytes;
+#pragma unroll
+                for (int kk = 0; kk < D / 16; ++kk) {
+                    const uint64_t da = ptx::make_smem_desc(q_addr + (kk >> 2) * (kBM * 128) + (kk & 3) * 32, 16, 1024);
+                    const uint64_t db = ptx::make_smem_desc(kb + (kk >> 2) * (kBN * 128) + (kk & 3) * 32, 16, 1024);
+                    ptx::umma_bf16<1>(tmem_s, da, db, idesc_s, kk != 0 ? 1u : 0u);
+                }
+                ptx::umma_commit(&slot_empty[slot]);
+                ptx::umma_commit(s_full);
+            };
+            ptx::mbar_wait(q_full, 0);
+            issue_s(0);
+            for (int j = 0; j < n_tiles; ++j) {
+                if (j + 1 < n_tiles) issue_s(j + 1);
+                const int slot = it % kSlots;
+                const uint32_t ph = (uint32_t)(it / kSlots) & 1u;
+                ++it;
+                ptx::mbar_wait(&slot_full[slot], ph);
+                ptx::mbar_wait(p_full, (uint32_t)j & 1u);
+                ptx::tcgen05_fence_after();
+                const uint32_t vb = ring_addr + slot * L::kSlotBytes;
+#pragma unroll
+                for (int kk = 0; kk < kBN / 16; ++kk) {
+                    const uint64_t da = ptx::make_smem_desc(p_addr + kk * 32, 16, 1024);
+                    const uint64_t db = ptx::make_smem_desc(vb + kk * 2048, kBN * 128, 1024);
+                    ptx::umma_bf16<1>(tmem_o, da, db, idesc_o, (j | kk) != 0 ? 1u : 0u);
+                }
+                ptx::umma_commit(&slot_empty[slot]);
+                ptx::umma_commit(pv_done);
+            }
+        }
+    } else {
+        // ============================ softmax / epilogue ============================
+        const int q = warp & 3;                 // TMEM lane quadrant of this warp
+        const int row = q * 32 + lane;          // row inside the q tile == TMEM lane
+        const int grow = m0 + row;
+        const uint32_t lane_off = (uint32_t)(q * 32) << 16;
+        float m_run = -INFINITY, l_run = 0.f;
+        for (int j = 0; j < n_tiles; ++j) {
+            ptx::mbar_wait(s_full, (uint32_t)j & 1u);
+            ptx::tcgen05_fence_after();
+            uint32_t sr[kBN];
+            ptx::tmem_ld_32x32b_x32(tmem_s + lane_off, sr);
+            ptx::tmem_ld_32x32b_x32(tmem_s + lane_off + 32, sr + 32);
+            ptx::tmem_ld_wait();
+            ptx::tcgen05_fence_before();
+            ptx::mbar_arrive(s_empty);
+            const int n0 = j * kBN;
+            const bool need_mask = (n0 + kBN > p.Sk) || (CAUSAL && (n0 + kBN - 1 > m0 + q * 32 + offset));
+            float mx = -INFINITY;
+#pragma unroll
+            for (int c = 0; c < kBN; ++c) {
+                float v = __uint_as_float(sr[c]) * p.scale_log2;
+                if (need_mask) {
+                    const int col = n0 + c;
+                    if (col >= p.Sk || (CAUSAL && col > grow + offset)) v = -INFINITY;
+                }
+                sr[c] = __float_as_uint(v);
+                mx = fmaxf(mx, v);
+            }
+            // lazy rescale: keep the stale max unless it moved by more than 2^8
+            float alpha = 1.f;
+            bool rescale = false;
+            if (mx > m_run + kRescaleThreshold || m_run == -INFINITY) {
+                const float m_new = fmaxf(m_run, mx);
+                if (m_new != -INFINITY) {
+                    alpha = exp2f(m_run - m_new);   // 0 when m_run was -inf
+                    rescale = (j > 0) && (m_run != -INFINITY);
+                    m_run = m_new;
+                }
+            }
+            const float m_use = (m_run == -INFINITY) ? 0.f : m_run;
+            float rs = 0.f;
+            uint32_t pk[kBN / 2];
+#pragma unroll
+            for (int c = 0; c < kBN; c += 2) {
+                const float p0 = exp2f(__uint_as_float(sr[c]) - m_use);
+                const float p1 = exp2f(__uint_as_float(sr[c + 1]) - m_use);
+                rs += p0 + p1;
+                bf162 t = __floats2bfloat162_rn(p0, p1);
+                pk[c >> 1] = *reinterpret_cast<uint32_t*>(&t);
+            }
+            l_run = l_run * alpha + rs;
+            if (j > 0) {
+                ptx::mbar_wait(pv_done, ((uint32_t)(j - 1)) & 1u);  // P buffer free, O up to date
+                ptx::tcgen05_fence_after();
+                if (__any_sync(0xffffffffu, rescale)) {
+#pragma unroll 1
+                    for (int c = 0; c < D / 32; ++c) {
+                        uint32_t o[32];
+                        ptx::tmem_ld_32x32b_x32(tmem_o + lane_off + c * 32, o);
+                        ptx::tmem_ld_wait();
+                        const float a_o = rescale ? alpha : 1.f;
+#pragma unroll
+                        for (int e = 0; e < 32; ++e) o[e] = __float_as_uint(__uint_as_float(o[e]) * a_o);
+                        tmem_st_32x32b_x32(tmem_o + lane_off + c * 32, o);
+                    }
+                    tmem_st_wait();
+                }
+            }
+            uint8_t* prow = sP + row * 128;
+#pragma unroll
+            for (int c = 0; c < 8; ++c)
+                *reinterpret_cast<uint4*>(prow + ((c ^ (row & 7)) << 4)) =
+                    make_uint4(pk[4 * c], pk[4 * c + 1], pk[4 * c + 2], pk[4 * c + 3]);
+            ptx::fence_proxy_async();
+            ptx::tcgen05_fence_before();
+            ptx::mbar_arrive(p_full);
+        }
+        // ---- epilogue ----
+        if (n_tiles > 0) {
+            ptx::mbar_wait(pv_done, ((uint32_t)(n_tiles - 1)) & 1u);
+            ptx::tcgen05_fence_after();
+        }
+        const float inv = l_run > 0.f ? 1.f / l_run : 0.f;
+        if (p.lse && grow < p.Sq)
+            p.lse[((long long)b * p.Hq + hq) * p.Sq + grow] = l_run > 0.f ? m_run + log2f(l_run) : INFINITY;
+        // every MMA that read Q has completed: reuse the Q tile as staging (warp q owns rows [32q, 32q+32) of
+        // each 64-column group: 32 rows x 128 bytes = one TMA store box)
+#pragma unroll 1
+        for (int g = 0; g < D / 64; ++g) {
+            uint32_t o[64];
+            if (n_tiles > 0) {
+                ptx::tmem_ld_32x32b_x32(tmem_o + lane_off + g * 64, o);
+                ptx::tmem_ld_32x32b_x32(tmem_o + lane_off + g * 64 + 32, o + 32);
+                ptx::tmem_ld_wait();
+            } else {
+#pragma unroll
+                for (int e = 0; e < 64; ++e) o[e] = 0u;
+            }
+            uint8_t* dst = sQ + g * (kBM * 128) + row * 128;
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+                uint32_t w[4];
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    bf162 t = __floats2bfloat162_rn(__uint_as_float(o[8 * c + 2 * e]) * inv,
+                                                    __uint_as_float(o[8 * c + 2 * e + 1]) * inv);
+                    w[e] = *reinterpret_cast<uint32_t*>(&t);
+                }
+                *reinterpret_cast<uint4*>(dst + ((c ^ (row & 7)) << 4)) = make_uint4(w[0], w[1], w[2], w[3]);
+            }
+            ptx::fence_proxy_async();
+            __syncwarp();
+            if (lane == 0 && m0 + q * 32 < p.Sq) {
+                int c[4];
+                c[0] = g * 64;
+                coords(p.pos_o, m0 + q * 32, hq, b, c);
+                tma_store_4d(&tmap_o, sQ + g * (kBM * 128) + q * 32 * 128, c[0], c[1], c[2], c[3]);
+                ptx::bulk_commit();
+            }
+        }
+        if (lane == 0) ptx::bulk_wait<0>();
+    }
+    ptx::tcgen05_fence_before();
+    __syncthreads();
+    if (warp == 1) ptx::tmem_dealloc<1>(tmem_base, L::kTmemCols);
+}
+
+PFN_cuTensorMapEncodeTiled_v12000 get_encode_fn() {
+    static PFN_cuTensorMapEncodeTiled_v12000 fn = nullptr;
+    if (fn) return fn;
+    void* ptr = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &q) != cudaSuccess ||
+        q != cudaDriverEntryPointSuccess)
+        return nullptr;
+    fn = reinterpret_cast<PFN_cuTensorMapEncodeTiled_v12000>(ptr);
+    return fn;
+}
+
+// 4-D bf16 map over a strided [B, H, S, D] view.  The three outer dims are ordered by ascending stride (TMA wants
+// a conventional layout); pos[] returns the coordinate slot (1..3) of (row, head, batch).
+int make_tmap_bhsd(CUtensorMap* out, const void* base, int D, long long S, long long H, long long B, long long s_s,
+                   long long s_h, long long s_b, int box_rows, int* pos) {
+    auto encode = get_encode_fn();
+    NXD_REQUIRE(encode != nullptr, "cuTensorMapEncodeTiled could not be resolved from the driver");
+    struct Dim { long long size, stride; int box, id; };
+    Dim d[3] = {{S, s_s, box_rows, 0}, {H, s_h, 1, 1}, {B, s_b, 1, 2}};
+    for (int i = 0; i < 3; ++i)
+        for (int j = i + 1; j < 3; ++j) {
+            // size-1 dims carry meaningless strides: sort them last
+            const bool swap = (d[j].size > 1 && d[i].size == 1) ||
+                              (d[j].size > 1 && d[i].size > 1 && d[j].stride < d[i].stride);
+            if (swap) { Dim t = d[i]; d[i] = d[j]; d[j] = t; }
+        }
+    cuuint64_t dims[4] = {(cuuint64_t)D, 0, 0, 0};
+    cuuint64_t strides[3];
+    cuuint32_t box[4] = {64, 1, 1, 1};
+    cuuint32_t estr[4] = {1, 1, 1, 1};
+    long long prev_extent = (long long)D * 2;
+    for (int i = 0; i < 3; ++i) {
+        dims[i + 1] = (cuuint64_t)d[i].size;
+        long long st = d[i].stride * 2;
+        if (d[i].size == 1 && (st < prev_extent || st % 16)) st = prev_extent;  // any legal value
+        strides[i] = (cuuint64_t)st;
+        prev_extent = st * d[i].size;
+        box[i + 1] = (cuuint32_t)d[i].box;
+        pos[d[i].id] = i + 1;
+    }
+    CUresult r = encode(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), dims, strides, box, estr,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    NXD_REQUIRE(r == CUDA_SUCCESS,
+                "cuTensorMapEncodeTiled(4d) failed (%d): dims=[%d,%llu,%llu,%llu] strides=[%llu,%llu,%llu] box_rows=%d",
+                (int)r, D, (unsigned long long)dims[1], (unsigned long long)dims[2], (unsigned long long)dims[3],
+                (unsigned long long)strides[0], (unsigned long long)strides[1], (unsigned long long)strides[2],
+                box_rows);
+    return 0;
+}
+
+template <int D>
+int launch_fwd_tc(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const CUtensorMap& to,
+                  const TcParams& p, int causal, cudaStream_t st) {
+    using L = TcSmem<D>;
+    dim3 grid((p.Sq + kBM - 1) / kBM, p.Hq, p.B);
+    if (causal) {
+        static cudaError_t once = cudaFuncSetAttribute(fa_fwd_tc_kernel<D, true>,
+                                                       cudaFuncAttributeMaxDynamicSharedMemorySize, L::kBytes);
+        NXD_CHECK_CUDA(once);
+        fa_fwd_tc_kernel<D, true><<<grid, kThreadsTc, L::kBytes, st>>>(tq, tk, tv, to, p);
+    } else {
+        static cudaError_t once = cudaFuncSetAttribute(fa_fwd_tc_kernel<D, false>,
+                                                       cudaFuncAttributeMaxDynamicSharedMemorySize, L::kBytes);
+        NXD_CHECK_CUDA(once);
+        fa_fwd_tc_kernel<D, false><<<grid, kThreadsTc, L::kBytes, st>>>(tq, tk, tv, to, p);
+    }
+    NXD_LAUNCH_CHECK();
+    return 0;
+}
+
+}  // namespace
+
+// Same arguments as nxd_flash_attn_fwd.  Extra requirement: 16-byte aligned base pointers.
+NXD_API int nxd_flash_attn_fwd_tc(const void* q, const void* k, const void* v, void* o, float* lse,
+                                  const long long* strides, int B, int Hq, int Hkv, int Sq, int Sk, int D, float scale,
+                                  int causal, void* stream) {
+    NXD_REQUIRE(D == 64 || D == 128, "flash_attn_tc: head dim %d not supported (64 or 128)", D);
+    NXD_REQUIRE(B > 0 && Hq > 0 && Hkv > 0 && Sq > 0 && Sk > 0 && Hq % Hkv == 0, "flash_attn_tc: bad problem");
+    for (int i = 0; i < 12; ++i)
+        NXD_REQUIRE(strides[i] % 8 == 0, "flash_attn_tc: stride %d (=%lld) must be a multiple of 8 elements", i,
+                    strides[i]);
+    NXD_REQUIRE((((uintptr_t)q | (uintptr_t)k | (uintptr_t)v | (uintptr_t)o) & 15) == 0,
+                "flash_attn_tc: tensors must be 16-byte aligned");
+    TcParams p{};
+    p.lse = lse;
+    p.B = B; p.Hq = Hq; p.Hkv = Hkv; p.Sq = Sq; p.Sk = Sk;
+    p.scale_log2 = scale * 1.4426950408889634f;
+    CUtensorMap tq, tk, tv, to;
+    int rc;
+    if ((rc = make_tmap_bhsd(&tq, q, D, Sq, Hq, B, strides[2], strides[1], strides[0], kBM, p.pos_q))) return rc;
+    if ((rc = make_tmap_bhsd(&tk, k, D, Sk, Hkv, B, strides[5], strides[4], strides[3], kBN, p.pos_k))) return rc;
+    if ((rc = make_tmap_bhsd(&tv, v, D, Sk, Hkv, B, strides[8], strides[7], strides[6], kBN, p.pos_v))) return rc;
+    if ((rc = make_tmap_bhsd(&to, o, D, Sq, Hq, B, strides[11], strides[10], strides[9], 32, p.pos_o))) return rc;
+    return D == 64 ? launch_fwd_tc<64>(tq, tk, tv, to, p, causal, (cudaStream_t)stream)
+                   : launch_fwd_tc<128>(tq, tk, tv, to, p, causal, (cudaStream_t)stream);
+}

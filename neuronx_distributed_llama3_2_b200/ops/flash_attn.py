@@ -3,6 +3,7 @@ from __future__ import annotations
 
 import ctypes as _c
 import math
+import os
 from typing import Optional
 
 import torch
@@ -41,11 +42,13 @@ class _FlashAttnFn(torch.autograd.Function):
         Hkv, Sk = k.shape[1], k.shape[2]
         o = _dense_like(q)
         lse = torch.empty((B, Hq, Sq), dtype=torch.float32, device=q.device)
-        rc = _lib.lib().nxd_flash_attn_fwd(
-            _lib.ptr(q), _lib.ptr(k), _lib.ptr(v), _lib.ptr(o), _lib.ptr(lse), _strides(q, k, v, o), _c.c_int(B),
-            _c.c_int(Hq), _c.c_int(Hkv), _c.c_int(Sq), _c.c_int(Sk), _c.c_int(D), _c.c_float(scale),
-            _c.c_int(1 if causal else 0), _lib.stream_ptr())
-        _lib.check(rc, "nxd_flash_attn_fwd")
+        # "tc": tcgen05/TMEM/TMA kernel (csrc/flash_attn_tc.cu); "mma": mma.sync kernel (csrc/flash_attn.cu)
+        impl = os.environ.get("NXD_ATTN_FWD", "tc")
+        fn = _lib.lib().nxd_flash_attn_fwd_tc if impl == "tc" else _lib.lib().nxd_flash_attn_fwd
+        rc = fn(_lib.ptr(q), _lib.ptr(k), _lib.ptr(v), _lib.ptr(o), _lib.ptr(lse), _strides(q, k, v, o), _c.c_int(B),
+                _c.c_int(Hq), _c.c_int(Hkv), _c.c_int(Sq), _c.c_int(Sk), _c.c_int(D), _c.c_float(scale),
+                _c.c_int(1 if causal else 0), _lib.stream_ptr())
+        _lib.check(rc, f"nxd_flash_attn_fwd[{impl}]")
         ctx.save_for_backward(q, k, v, o, lse)
         ctx.scale, ctx.causal = scale, causal
         return o
