@@ -1,0 +1,484 @@
+// Flash attention BACKWARD on 5th-gen tensor cores (tcgen05 + TMEM + TMA), sm_100a, head dim 128.
+//
+// Same contract as nxd_flash_attn_bwd in flash_attn.cu (reference: the external NKI `flash_attn_bwd` kernel behind
+// src/neuronx_distributed/kernels/flash_attn.py:19-28,103-148).
+//
+// One CTA owns 128 K/V rows of one (batch, kv head) and walks over the q heads of its GQA group and their query
+// tiles of 64 rows.  Everything that is accumulated over the walk lives in TMEM (512 columns, one CTA per SM):
+//     dK [128 x 128]   dV [128 x 128]   S^T [128 x 64]   dP^T [128 x 64]   dQ^T [128(d) x 64(q)]
+// Per query tile i, five MMAs (A/B are smem descriptors over tiles that are each loaded / written ONCE):
+//     S^T  = K   Q_i^T          A = K    (K-major)     B = Q_i  (K-major)
+//     dP^T = V   dO_i^T         A = V    (K-major)     B = dO_i (K-major)
+//     dV  += P^T  dO_i          A = P^T  (K-major)     B = dO_i (MN-major: the same smem tile read "transposed")
+//     dK  += dS^T Q_i           A = dS^T (K-major)     B = Q_i  (MN-major)
+//     dQ^T = K^T dS^T           A = K    (MN-major)    B = dS^T (MN-major)
+// S^T / dP^T are produced transposed so that one thread owns one K/V row (TMEM lane): it reads its 64 scores,
+// forms P^T = exp2(S^T c - L_q) and dS^T = P^T (dP^T - Delta_q) and writes one 128-byte swizzled smem row of each --
+// exactly the K-major A operand of dV / dK and, read MN-major, the B operand of dQ^T.  dQ^T tiles are drained
+// TMEM -> smem (transposed back) and added into an fp32 dQ accumulator with TMA reduce-add; dK (x scale) and dV
+// leave through smem + TMA store.  The GQA reduction of dK/dV over the q-head group happens in TMEM for free.
+//
+// warp 0: TMA producer (K, V once; Q_i, dO_i, L_i, Delta_i through a 2-stage ring)   warp 1: TMEM alloc + MMA issue
+// warps 2-5: softmax-backward math, dQ drain, epilogue.
+#include "attn_tc_common.cuh"
+#include "gemm_tcgen05.cuh"
+#include "ptx.cuh"
+
+namespace {
+using namespace nxd_attn;
+
+constexpr int kBN = 128;  // K/V rows per CTA
+constexpr int kBM = 64;   // query rows per tile
+constexpr int kD = 128;
+constexpr int kThreadsBwd = 192;
+
+struct BwdParams {
+    const float* lse_pad;    // [B*Hq, Sq_pad] log2-domain LSE, +inf in the padding
+    const float* delta_pad;  // [B*Hq, Sq_pad]
+    int B, Hq, Hkv, Sq, Sk, Sq_pad;
+    int pos_q[3], pos_do[3], pos_k[3], pos_v[3], pos_dk[3], pos_dv[3], pos_dq[3];
+    float scale, scale_log2;
+};
+
+struct BwdSmem {
+    static constexpr int kKOff = 0;                       // [2 groups][128 rows][64]   32 KB
+    static constexpr int kVOff = kKOff + kBN * kD * 2;    // 32 KB
+    static constexpr int kQOff = kVOff + kBN * kD * 2;    // 2 stages x [2 groups][64 rows][64]   32 KB
+    static constexpr int kDOOff = kQOff + 2 * kBM * kD * 2;   // 32 KB
+    static constexpr int kPtOff = kDOOff + 2 * kBM * kD * 2;  // [128 rows][64] bf16   16 KB
+    static constexpr int kDStOff = kPtOff + kBN * kBM * 2;    // 16 KB
+    static constexpr int kDQOff = kDStOff + kBN * kBM * 2;    // [4 groups][64 q rows][32 fp32]   32 KB
+    static constexpr int kLOff = kDQOff + kBM * kD * 4;       // 2 stages x (64 L + 64 Delta) floats   1 KB
+    static constexpr int kBarOff = kLOff + 2 * 2 * kBM * 4;
+    static constexpr int kNumBars = 1 + 2 + 2 + 6;
+    static constexpr int kBytes = kBarOff + kNumBars * 8 + 16 + 1024;
+    static constexpr int kStageBytes = kBM * kD * 2;          // one Q (or dO) tile
+    static constexpr int kTxPerStage = 2 * kStageBytes + 2 * kBM * 4;
+};
+static_assert(BwdSmem::kBytes <= 232448, "shared memory budget exceeded");
+
+constexpr uint32_t kColDK = 0, kColDV = 128, kColST = 256, kColDPT = 320, kColDQT = 384;
+
+template <bool CAUSAL>
+__global__ void __launch_bounds__(kThreadsBwd, 1)
+fa_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_do,
+                 const __grid_constant__ CUtensorMap tmap_k, const __grid_constant__ CUtensorMap tmap_v,
+                 const __grid_constant__ CUtensorMap tmap_dk, const __grid_constant__ CUtensorMap tmap_dv,
+                 const __grid_constant__ CUtensorMap tmap_dq, const BwdParams p) {
+    using L = BwdSmem;
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* sK = smem + L::kKOff;
+    uint8_t* sV = smem + L::kVOff;
+    uint8_t* sQ = smem + L::kQOff;
+    uint8_t* sDO = smem + L::kDOOff;
+    uint8_t* sPt = smem + L::kPtOff;
+    uint8_t* sDSt = smem + L::kDStOff;
+    uint8_t* sDQ = smem + L::kDQOff;
+    float* sLD = reinterpret_cast<float*>(smem + L::kLOff);  // [stage][0: L, 1: Delta][64]
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L::kBarOff);
+    uint64_t* kv_full = bars;
+    uint64_t* qdo_full = bars + 1;    // [2]
+    uint64_t* qdo_empty = bars + 3;   // [2]
+    uint64_t* st_full = bars + 5;
+    uint64_t* st_empty = bars + 6;
+    uint64_t* pds_full = bars + 7;
+    uint64_t* pds_empty = bars + 8;
+    uint64_t* dq_full = bars + 9;
+    uint64_t* dq_empty = bars + 10;
+    uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bars + L::kNumBars);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int nbk = blockIdx.x, hkv = blockIdx.y, b = blockIdx.z;
+    const int group = p.Hq / p.Hkv;
+    const int n0 = nbk * kBN;
+    const int offset = p.Sk - p.Sq;
+    int mb_start = 0;
+    if (CAUSAL) mb_start = max(0, (n0 - offset) / kBM);
+    const int mb_end = (p.Sq + kBM - 1) / kBM;
+    const int tiles_per_head = max(mb_end - mb_start, 0);
+    const int total = tiles_per_head * group;
+
+    if (warp == 0 && lane == 0) {
+        ptx::prefetch_tensormap(&tmap_q);
+        ptx::prefetch_tensormap(&tmap_do);
+        ptx::prefetch_tensormap(&tmap_k);
+        ptx::prefetch_tensormap(&tmap_v);
+        ptx::prefetch_tensormap(&tmap_dq);
+        ptx::mbar_init(kv_full, 1);
+        for (int i = 0; i < 2; ++i) {
+            ptx::mbar_init(&qdo_full[i], 1);
+            ptx::mbar_init(&qdo_empty[i], 1);
+        }
+        ptx::mbar_init(st_full, 1);
+        ptx::mbar_init(st_empty, 128);
+        ptx::mbar_init(pds_full, 128);
+        ptx::mbar_init(pds_empty, 1);
+        ptx::mbar_init(dq_full, 1);
+        ptx::mbar_init(dq_empty, 128);
+        ptx::fence_barrier_init();
+    }
+    if (warp == 1) ptx::tmem_alloc<1>(tmem_ptr_smem, 512);
+    ptx::tcgen05_fence_before();
+    __syncthreads();
+    ptx::tcgen05_fence_after();
+    const uint32_t tmem_base = *tmem_ptr_smem;
+
+    if (warp == 0) {
+        // ============================ TMA producer ============================
+        if (lane == 0) {
+            int c[4];
+            ptx::mbar_arrive_expect_tx(kv_full, 2 * kBN * kD * 2);
+#pragma unroll
+            for (int g = 0; g < kD / 64; ++g) {
+                c[0] = g * 64;
+                coords(p.pos_k, n0, hkv, b, c);
+                tma_load_4d(&tmap_k, kv_full, sK + g * (kBN * 128), c[0], c[1], c[2], c[3]);
+                coords(p.pos_v, n0, hkv, b, c);
+                tma_load_4d(&tmap_v, kv_full, sV + g * (kBN * 128), c[0], c[1], c[2], c[3]);
+            }
+            for (int it = 0; it < total; ++it) {
+                const int st = it & 1;
+                const uint32_t ph = (uint32_t)(it >> 1) & 1u;
+                const int hq = hkv * group + it / tiles_per_head;
+                const int m0 = (mb_start + it % tiles_per_head) * kBM;
+                ptx::mbar_wait(&qdo_empty[st], ph ^ 1u);
+                ptx::mbar_arrive_expect_tx(&qdo_full[st], L::kTxPerStage);
+#pragma unroll
+                for (int g = 0; g < kD / 64; ++g) {
+                    c[0] = g * 64;
+                    coords(p.pos_q, m0, hq, b, c);
+                    tma_load_4d(&tmap_q, &qdo_full[st], sQ + st * L::kStageBytes + g * (kBM * 128), c[0], c[1], c[2], c[3]);
+                    coords(p.pos_do, m0, hq, b, c);
+                    tma_load_4d(&tmap_do, &qdo_full[st], sDO + st * L::kStageBytes + g * (kBM * 128), c[0], c[1], c[2],
+                                c[3]);
+                }
+                const long long row = ((long long)b * p.Hq + hq) * p.Sq_pad + m0;
+                bulk_load_1d(sLD + st * 2 * kBM, p.lse_pad + row, kBM * 4, &qdo_full[st]);
+                bulk_load_1d(sLD + st * 2 * kBM + kBM, p.delta_pad + row, kBM * 4, &qdo_full[st]);
+            }
+        }
+    } else if (warp == 1) {
+        // ============================ MMA issuer ============================
+        if (lane == 0 && total > 0) {
+            constexpr uint32_t idesc_st = ptx::make_idesc_bf16(kBN, kBM, 0, 0);   // S^T, dP^T: 128 x 64, K-major A/B
+            constexpr uint32_t idesc_kv = ptx::make_idesc_bf16(kBN, kD, 0, 1);    // dV, dK: 128 x 128, B MN-major
+            constexpr uint32_t idesc_dq = ptx::make_idesc_bf16(kD, kBM, 1, 1);    // dQ^T: 128 x 64, A and B MN-major
+            const uint32_t k_addr = ptx::smem_u32(sK), v_addr = ptx::smem_u32(sV), q_addr = ptx::smem_u32(sQ),
+                           do_addr = ptx::smem_u32(sDO), pt_addr = ptx::smem_u32(sPt), dst_addr = ptx::smem_u32(sDSt);
+            auto issue_scores = [&](int it) {
+                const int st = it & 1;
+                ptx::mbar_wait(&qdo_full[st], (uint32_t)(it >> 1) & 1u);
+                ptx::mbar_wait(st_empty, ((uint32_t)it & 1u) ^ 1u);  // S^T/dP^T of tile it-1 are in registers
+                ptx::tcgen05_fence_after();
+                const uint32_t qb = q_addr + st * L::kStageBytes, dob = do_addr + st * L::kStageBytes;
+#pragma unroll
+                for (int kk = 0; kk < kD / 16; ++kk) {
+                    const uint32_t ko = (kk >> 2) * (kBN * 128) + (kk & 3) * 32;   // K-major A: [128][64] groups
+                    const uint32_t qo = (kk >> 2) * (kBM * 128) + (kk & 3) * 32;   // K-major B: [64][64] groups
+                    ptx::umma_bf16<1>(tmem_base + kColST, ptx::make_smem_desc(k_addr + ko, 16, 1024),
+                                      ptx::make_smem_desc(qb + qo, 16, 1024), idesc_st, kk != 0 ? 1u : 0u);
+                }
+#pragma unroll
+                for (int kk = 0; kk < kD / 16; ++kk) {
+                    const uint32_t ko = (kk >> 2) * (kBN * 128) + (kk & 3) * 32;
+                    const uint32_t qo = (kk >> 2) * (kBM * 128) + (kk & 3) * 32;
+                    ptx::umma_bf16<1>(tmem_base + kColDPT, ptx::make_smem_desc(v_addr + ko, 16, 1024),
+                                      ptx::make_smem_desc(dob + qo, 16, 1024), idesc_st, kk != 0 ? 1u : 0u);
+                }
+                ptx::umma_commit(st_full);
+            };
+            ptx::mbar_wait(kv_full, 0);
+            issue_scores(0);
+            for (int it = 0; it < total; ++it) {
+                if (it + 1 < total) issue_scores(it + 1);
+                const int st = it & 1;
+                const uint32_t qb = q_addr + st * L::kStageBytes, dob = do_addr + st * L::kStageBytes;
+                ptx::mbar_wait(pds_full, (uint32_t)it & 1u);
+                ptx::tcgen05_fence_after();
+                // dV += P^T dO ; dK += dS^T Q      (contraction over the 64 q rows: 4 MMAs of K = 16 each)
+#pragma unroll
+                for (int kk = 0; kk < kBM / 16; ++kk) {
+                    ptx::umma_bf16<1>(tmem_base + kColDV, ptx::make_smem_desc(pt_addr + kk * 32, 16, 1024),
+                                      ptx::make_smem_desc(dob + kk * 2048, kBM * 128, 1024), idesc_kv,
+                                      (it | kk) != 0 ? 1u : 0u);
+                }
+#pragma unroll
+                for (int kk = 0; kk < kBM / 16; ++kk) {
+                    ptx::umma_bf16<1>(tmem_base + kColDK, ptx::make_smem_desc(dst_addr + kk * 32, 16, 1024),
+                                      ptx::make_smem_desc(qb + kk * 2048, kBM * 128, 1024), idesc_kv,
+                                      (it | kk) != 0 ? 1u : 0u);
+                }
+                ptx::umma_commit(&qdo_empty[st]);   // Q_i / dO_i no longer needed
+                // dQ^T = K^T dS^T   (contraction over the 128 kv rows: 8 MMAs); wait until dQ^T(it-1) was drained
+                ptx::mbar_wait(dq_empty, ((uint32_t)it & 1u) ^ 1u);
+                ptx::tcgen05_fence_after();
+#pragma unroll
+                for (int kk = 0; kk < kBN / 16; ++kk) {
+                    ptx::umma_bf16<1>(tmem_base + kColDQT, ptx::make_smem_desc(k_addr + kk * 2048, kBN * 128, 1024),
+                                      ptx::make_smem_desc(dst_addr + kk * 2048, kBN * 128, 1024), idesc_dq,
+                                      kk != 0 ? 1u : 0u);
+                }
+                ptx::umma_commit(pds_empty);
+                ptx::umma_commit(dq_full);
+            }
+        }
+    } else {
+        // ============================ softmax backward / dQ drain / epilogue ============================
+        const int q4 = warp & 3;
+        const int row = q4 * 32 + lane;         // K/V row inside the tile == TMEM lane (and d index for dQ^T)
+        const int krow = n0 + row;
+        const uint32_t lane_off = (uint32_t)(q4 * 32) << 16;
+        const int tid128 = threadIdx.x - 64;
+
+        auto drain_dq = [&](int it) {
+            // dQ^T(it) [d = row][64 q] -> sDQ [d group of 32][q][32 floats] (128-byte swizzled rows) -> TMA reduce-add
+            const int hq = hkv * group + it / tiles_per_head;
+            const int m0 = (mb_start + it % tiles_per_head) * kBM;
+            ptx::mbar_wait(dq_full, (uint32_t)it & 1u);
+            ptx::tcgen05_fence_after();
+            uint32_t v[64];
+            ptx::tmem_ld_32x32b_x32(tmem_base + kColDQT + lane_off, v);
+            ptx::tmem_ld_32x32b_x32(tmem_base + kColDQT + lane_off + 32, v + 32);
+            ptx::tmem_ld_wait();
+            ptx::tcgen05_fence_before();
+            ptx::mbar_arrive(dq_empty);
+            if (tid128 == 0) ptx::bulk_wait_read<0>();   // the previous reduce-add has finished reading sDQ
+            named_bar_sync(1, 128);
+            uint8_t* base = sDQ + q4 * (kBM * 128);      // d group of 32 == this warp
+#pragma unroll
+            for (int qq = 0; qq < kBM; ++qq) {
+                float* dst = reinterpret_cast<float*>(base + qq * 128 + (((lane >> 2) ^ (qq & 7)) << 4) + (lane & 3) * 4);
+                *dst = __uint_as_float(v[qq]) * p.scale;
+            }
+            ptx::fence_proxy_async();
+            named_bar_sync(1, 128);
+            if (tid128 == 0) {
+                int c[4];
+#pragma unroll
+                for (int g = 0; g < kD / 32; ++g) {
+                    c[0] = g * 32;
+                    coords(p.pos_dq, m0, hq, b, c);
+                    tma_reduce_add_4d(&tmap_dq, sDQ + g * (kBM * 128), c[0], c[1], c[2], c[3]);
+                }
+                ptx::bulk_commit();
+            }
+        };
+
+        for (int it = 0; it < total; ++it) {
+            const int st = it & 1;
+            const int m0 = (mb_start + it % tiles_per_head) * kBM;
+            ptx::mbar_wait(st_full, (uint32_t)it & 1u);
+            ptx::tcgen05_fence_after();
+            uint32_t s[kBM], dp[kBM];
+            ptx::tmem_ld_32x32b_x32(tmem_base + kColST + lane_off, s);
+            ptx::tmem_ld_32x32b_x32(tmem_base + kColST + lane_off + 32, s + 32);
+            ptx::tmem_ld_32x32b_x32(tmem_base + kColDPT + lane_off, dp);
+            ptx::tmem_ld_32x32b_x32(tmem_base + kColDPT + lane_off + 32, dp + 32);
+            ptx::tmem_ld_wait();
+            ptx::tcgen05_fence_before();
+            ptx::mbar_arrive(st_empty);
+            // L / Delta of this tile were delivered with Q_i / dO_i (the MMA warp already saw qdo_full complete;
+            // wait on it here too so that the bulk-copied bytes are visible to this thread)
+            ptx::mbar_wait(&qdo_full[st], (uint32_t)(it >> 1) & 1u);
+            const float* Ls = sLD + st * 2 * kBM;
+            const float* Ds = Ls + kBM;
+            const bool need_mask = (n0 + kBN > p.Sk) || (CAUSAL && (n0 + q4 * 32 + 31 > m0 + offset));
+            uint32_t pk[kBM / 2], dk_[kBM / 2];
+#pragma unroll
+            for (int c = 0; c < kBM; c += 2) {
+                float p0 = exp2f(__uint_as_float(s[c]) * p.scale_log2 - Ls[c]);
+                float p1 = exp2f(__uint_as_float(s[c + 1]) * p.scale_log2 - Ls[c + 1]);
+                if (need_mask) {
+                    const int mq = m0 + c;
+                    if (krow >= p.Sk || (CAUSAL && krow > mq + offset)) p0 = 0.f;
+                    if (krow >= p.Sk || (CAUSAL && krow > mq + 1 + offset)) p1 = 0.f;
+                }
+                const float d0 = p0 * (__uint_as_float(dp[c]) - Ds[c]);
+                const float d1 = p1 * (__uint_as_float(dp[c + 1]) - Ds[c + 1]);
+                bf162 tp = __floats2bfloat162_rn(p0, p1);
+                bf162 td = __floats2bfloat162_rn(d0, d1);
+                pk[c >> 1] = *reinterpret_cast<uint32_t*>(&tp);
+                dk_[c >> 1] = *reinterpret_cast<uint32_t*>(&td);
+            }
+            if (it > 0) ptx::mbar_wait(pds_empty, ((uint32_t)(it - 1)) & 1u);  // MMAs of tile it-1 finished with sPt/sDSt
+            uint8_t* prow = sPt + row * 128;
+            uint8_t* drow = sDSt + row * 128;
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+                const int sw = (c ^ (row & 7)) << 4;
+                *reinterpret_cast<uint4*>(prow + sw) = make_uint4(pk[4 * c], pk[4 * c + 1], pk[4 * c + 2], pk[4 * c + 3]);
+                *reinterpret_cast<uint4*>(drow + sw) = make_uint4(dk_[4 * c], dk_[4 * c + 1], dk_[4 * c + 2], dk_[4 * c + 3]);
+            }
+            ptx::fence_proxy_async();
+            ptx::tcgen05_fence_before();
+            ptx::mbar_arrive(pds_full);
+            if (it > 0) drain_dq(it - 1);
+        }
+        if (total > 0) {
+            drain_dq(total - 1);
+            // the commit behind dq_full(total-1) covered every earlier MMA: dK / dV are final
+        }
+        if (total == 0) ptx::mbar_wait(kv_full, 0);  // nothing consumed K/V: let their TMA land before the tiles are reused
+        if (tid128 == 0) ptx::bulk_wait_read<0>();
+        named_bar_sync(1, 128);
+        // ---- epilogue: dV, dK (x scale) -> bf16 -> smem (the dead K / V tiles) -> TMA store ----
+#pragma unroll 1
+        for (int which = 0; which < 2; ++which) {
+            uint8_t* stage = which == 0 ? sV : sK;
+            const uint32_t col = which == 0 ? kColDV : kColDK;
+            const float mul = which == 0 ? 1.f : p.scale;
+#pragma unroll 1
+            for (int g = 0; g < kD / 64; ++g) {
+                uint32_t o[64];
+                if (total > 0) {
+                    ptx::tmem_ld_32x32b_x32(tmem_base + col + lane_off + g * 64, o);
+                    ptx::tmem_ld_32x32b_x32(tmem_base + col + lane_off + g * 64 + 32, o + 32);
+                    ptx::tmem_ld_wait();
+                } else {
+#pragma unroll
+                    for (int e = 0; e < 64; ++e) o[e] = 0u;
+                }
+                uint8_t* dst = stage + g * (kBN * 128) + row * 128;
+#pragma unroll
+                for (int c = 0; c < 8; ++c) {
+                    uint32_t w[4];
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) {
+                        bf162 t = __floats2bfloat162_rn(__uint_as_float(o[8 * c + 2 * e]) * mul,
+                                                        __uint_as_float(o[8 * c + 2 * e + 1]) * mul);
+                        w[e] = *reinterpret_cast<uint32_t*>(&t);
+                    }
+                    *reinterpret_cast<uint4*>(dst + ((c ^ (row & 7)) << 4)) = make_uint4(w[0], w[1], w[2], w[3]);
+                }
+                ptx::fence_proxy_async();
+                __syncwarp();
+                if (lane == 0 && n0 + q4 * 32 < p.Sk) {
+                    int c[4];
+                    c[0] = g * 64;
+                    coords(which == 0 ? p.pos_dv : p.pos_dk, n0 + q4 * 32, hkv, b, c);
+                    tma_store_4d(which == 0 ? &tmap_dv : &tmap_dk, stage + g * (kBN * 128) + q4 * 32 * 128, c[0], c[1],
+                                 c[2], c[3]);
+                    ptx::bulk_commit();
+                }
+            }
+        }
+        if (lane == 0) ptx::bulk_wait<0>();
+    }
+    ptx::tcgen05_fence_before();
+    __syncthreads();
+    if (warp == 1) ptx::tmem_dealloc<1>(tmem_base, 512);
+}
+
+// Delta = rowsum(O * dO) and a padded copy of the LSE ([B*Hq, Sq_pad], +inf / 0 in the padding) so that the main
+// kernel can fetch 64-row slices with 256-byte bulk copies and get masking of out-of-range query rows for free.
+__global__ void fa_bwd_tc_prep_kernel(const bf16* __restrict__ o, const bf16* __restrict__ dout,
+                                      const float* __restrict__ lse, float* __restrict__ lse_pad,
+                                      float* __restrict__ delta_pad, long long o_sb, long long o_sh, long long o_ss,
+                                      long long do_sb, long long do_sh, long long do_ss, int B, int Hq, int Sq,
+                                      int Sq_pad) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const long long r = (long long)blockIdx.x * (blockDim.x >> 5) + warp;
+    const long long total = (long long)B * Hq * Sq_pad;
+    if (r >= total) return;
+    const int i = (int)(r % Sq_pad);
+    const int h = (int)((r / Sq_pad) % Hq);
+    const int b = (int)(r / ((long long)Sq_pad * Hq));
+    if (i >= Sq) {
+        if (lane == 0) {
+            lse_pad[r] = INFINITY;
+            delta_pad[r] = 0.f;
+        }
+        return;
+    }
+    const bf16* op = o + b * o_sb + h * o_sh + (long long)i * o_ss;
+    const bf16* dp = dout + b * do_sb + h * do_sh + (long long)i * do_ss;
+    float acc = 0.f;
+#pragma unroll
+    for (int c = 0; c < kD / 64; ++c) {
+        const float2 a = __bfloat1622float2(reinterpret_cast<const bf162*>(op)[lane + c * 32]);
+        const float2 g = __bfloat1622float2(reinterpret_cast<const bf162*>(dp)[lane + c * 32]);
+        acc += a.x * g.x + a.y * g.y;
+    }
+    acc = warp_sum(acc);
+    if (lane == 0) {
+        delta_pad[r] = acc;
+        lse_pad[r] = lse[((long long)b * Hq + h) * Sq + i];
+    }
+}
+
+// fp32 [B, Hq, Sq, D] accumulator -> strided bf16 dq
+__global__ void fa_bwd_tc_dq_convert_kernel(const float* __restrict__ acc, bf16* __restrict__ dq, long long sb,
+                                            long long sh, long long ss, int B, int Hq, int Sq) {
+    const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;  // one thread = 8 elements
+    const long long total = (long long)B * Hq * Sq * (kD / 8);
+    if (idx >= total) return;
+    const int c = (int)(idx % (kD / 8));
+    const long long r = idx / (kD / 8);
+    const int i = (int)(r % Sq);
+    const int h = (int)((r / Sq) % Hq);
+    const int b = (int)(r / ((long long)Sq * Hq));
+    const float4 a0 = reinterpret_cast<const float4*>(acc + r * kD)[2 * c];
+    const float4 a1 = reinterpret_cast<const float4*>(acc + r * kD)[2 * c + 1];
+    float f[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+    reinterpret_cast<bf16x8*>(dq + b * sb + h * sh + (long long)i * ss)[c] = pack8(f);
+}
+
+}  // namespace
+
+// Head dim 128 only.  scratch: lse_pad and delta_pad are [B*Hq*Sq_pad] floats (Sq_pad = Sq rounded up to 64);
+// dq_accum is a ZERO-FILLED [B, Hq, Sq, 128] fp32 buffer.  strides as nxd_flash_attn_bwd (24 values).
+NXD_API int nxd_flash_attn_bwd_tc(const void* q, const void* k, const void* v, const void* o, const void* dout,
+                                  const float* lse, float* lse_pad, float* delta_pad, float* dq_accum, void* dq,
+                                  void* dk, void* dv, const long long* strides, int B, int Hq, int Hkv, int Sq, int Sk,
+                                  int D, float scale, int causal, void* stream) {
+    NXD_REQUIRE(D == kD, "flash_attn_bwd_tc: head dim %d not supported (128 only)", D);
+    NXD_REQUIRE(B > 0 && Hq > 0 && Hkv > 0 && Sq > 0 && Sk > 0 && Hq % Hkv == 0, "flash_attn_bwd_tc: bad problem");
+    for (int i = 0; i < 24; ++i)
+        NXD_REQUIRE(strides[i] % 8 == 0, "flash_attn_bwd_tc: stride %d (=%lld) must be a multiple of 8 elements", i,
+                    strides[i]);
+    cudaStream_t st = (cudaStream_t)stream;
+    BwdParams p{};
+    p.B = B; p.Hq = Hq; p.Hkv = Hkv; p.Sq = Sq; p.Sk = Sk;
+    p.Sq_pad = (Sq + kBM - 1) / kBM * kBM;
+    p.lse_pad = lse_pad; p.delta_pad = delta_pad;
+    p.scale = scale; p.scale_log2 = scale * 1.4426950408889634f;
+    {
+        const long long rows = (long long)B * Hq * p.Sq_pad;
+        fa_bwd_tc_prep_kernel<<<(unsigned)((rows + 7) / 8), 256, 0, st>>>(
+            (const bf16*)o, (const bf16*)dout, lse, lse_pad, delta_pad, strides[9], strides[10], strides[11], strides[12],
+            strides[13], strides[14], B, Hq, Sq, p.Sq_pad);
+        NXD_LAUNCH_CHECK();
+    }
+    CUtensorMap tq, tdo, tk, tv, tdk, tdv, tdq;
+    int rc;
+    if ((rc = make_tmap_bhsd(&tq, q, D, Sq, Hq, B, strides[2], strides[1], strides[0], kBM, p.pos_q))) return rc;
+    if ((rc = make_tmap_bhsd(&tk, k, D, Sk, Hkv, B, strides[5], strides[4], strides[3], kBN, p.pos_k))) return rc;
+    if ((rc = make_tmap_bhsd(&tv, v, D, Sk, Hkv, B, strides[8], strides[7], strides[6], kBN, p.pos_v))) return rc;
+    if ((rc = make_tmap_bhsd(&tdo, dout, D, Sq, Hq, B, strides[14], strides[13], strides[12], kBM, p.pos_do))) return rc;
+    if ((rc = make_tmap_bhsd(&tdk, dk, D, Sk, Hkv, B, strides[20], strides[19], strides[18], 32, p.pos_dk))) return rc;
+    if ((rc = make_tmap_bhsd(&tdv, dv, D, Sk, Hkv, B, strides[23], strides[22], strides[21], 32, p.pos_dv))) return rc;
+    if ((rc = make_tmap_bhsd(&tdq, dq_accum, D, Sq, Hq, B, D, (long long)Sq * D, (long long)Hq * Sq * D, kBM, p.pos_dq,
+                             4)))
+        return rc;
+    dim3 grid((Sk + kBN - 1) / kBN, Hkv, B);
+    if (causal) {
+        static cudaError_t once = cudaFuncSetAttribute(fa_bwd_tc_kernel<true>,
+                                                       cudaFuncAttributeMaxDynamicSharedMemorySize, BwdSmem::kBytes);
+        NXD_CHECK_CUDA(once);
+        fa_bwd_tc_kernel<true><<<grid, kThreadsBwd, BwdSmem::kBytes, st>>>(tq, tdo, tk, tv, tdk, tdv, tdq, p);
+    } else {
+        static cudaError_t once = cudaFuncSetAttribute(fa_bwd_tc_kernel<false>,
+                                                       cudaFuncAttributeMaxDynamicSharedMemorySize, BwdSmem::kBytes);
+        NXD_CHECK_CUDA(once);
+        fa_bwd_tc_kernel<false><<<grid, kThreadsBwd, BwdSmem::kBytes, st>>>(tq, tdo, tk, tv, tdk, tdv, tdq, p);
+    }
+    NXD_LAUNCH_CHECK();
+    {
+        const long long n = (long long)B * Hq * Sq * (kD / 8);
+        fa_bwd_tc_dq_convert_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(
+            dq_accum, (bf16*)dq, strides[15], strides[16], strides[17], B, Hq, Sq);
+        NXD_LAUNCH_CHECK();
+    }
+    return 0;
+}

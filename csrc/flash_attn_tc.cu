@@ -19,11 +19,11 @@
 //             ("lazy rescale"), which is rare after the first tiles.  Epilogue: O / l -> bf16 -> smem -> TMA store.
 #include "common.cuh"
 #include "gemm_tcgen05.cuh"
+#include "attn_tc_common.cuh"
 #include "ptx.cuh"
 
-#include <cudaTypedefs.h>
-
 namespace {
+using namespace nxd_attn;
 
 constexpr int kBM = 128;
 constexpr int kBN = 64;
@@ -51,39 +51,6 @@ struct TcSmem {
     static constexpr int kBytes = kBarOff + kNumBars * 8 + 16 + 1024;  // + manual 1024-byte alignment slack
     static constexpr int kTmemCols = (D + kBN <= 128) ? 128 : 256;
 };
-
-__device__ __forceinline__ void tma_load_4d(const CUtensorMap* map, uint64_t* bar, void* dst, int c0, int c1, int c2,
-                                            int c3) {
-    asm volatile(
-        "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
-        ::"r"(ptx::smem_u32(dst)), "l"(reinterpret_cast<uint64_t>(map)), "r"(ptx::smem_u32(bar)), "r"(c0), "r"(c1),
-        "r"(c2), "r"(c3)
-        : "memory");
-}
-__device__ __forceinline__ void tma_store_4d(const CUtensorMap* map, const void* src, int c0, int c1, int c2, int c3) {
-    asm volatile("cp.async.bulk.tensor.4d.global.shared::cta.bulk_group [%0, {%2, %3, %4, %5}], [%1];" ::"l"(
-                     reinterpret_cast<uint64_t>(map)),
-                 "r"(ptx::smem_u32(src)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
-                 : "memory");
-}
-__device__ __forceinline__ void coords(const int* pos, int row, int h, int b, int* c) {
-    c[pos[0]] = row;
-    c[pos[1]] = h;
-    c[pos[2]] = b;
-}
-
-__device__ __forceinline__ void tmem_st_32x32b_x32(uint32_t taddr, const uint32_t* r) {
-    asm volatile(
-        "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
-        "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "
-        "%17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, %32};" ::"r"(taddr),
-        "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]), "r"(r[9]),
-        "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15]), "r"(r[16]), "r"(r[17]), "r"(r[18]),
-        "r"(r[19]), "r"(r[20]), "r"(r[21]), "r"(r[22]), "r"(r[23]), "r"(r[24]), "r"(r[25]), "r"(r[26]), "r"(r[27]),
-        "r"(r[28]), "r"(r[29]), "r"(r[30]), "r"(r[31])
-        : "memory");
-}
-__device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 
 template <int D, bool CAUSAL>
 __global__ void __launch_bounds__(kThreadsTc, 2)
@@ -342,58 +309,6 @@ fa_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
     ptx::tcgen05_fence_before();
     __syncthreads();
     if (warp == 1) ptx::tmem_dealloc<1>(tmem_base, L::kTmemCols);
-}
-
-PFN_cuTensorMapEncodeTiled_v12000 get_encode_fn() {
-    static PFN_cuTensorMapEncodeTiled_v12000 fn = nullptr;
-    if (fn) return fn;
-    void* ptr = nullptr;
-    cudaDriverEntryPointQueryResult q;
-    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &q) != cudaSuccess ||
-        q != cudaDriverEntryPointSuccess)
-        return nullptr;
-    fn = reinterpret_cast<PFN_cuTensorMapEncodeTiled_v12000>(ptr);
-    return fn;
-}
-
-// 4-D bf16 map over a strided [B, H, S, D] view.  The three outer dims are ordered by ascending stride (TMA wants
-// a conventional layout); pos[] returns the coordinate slot (1..3) of (row, head, batch).
-int make_tmap_bhsd(CUtensorMap* out, const void* base, int D, long long S, long long H, long long B, long long s_s,
-                   long long s_h, long long s_b, int box_rows, int* pos) {
-    auto encode = get_encode_fn();
-    NXD_REQUIRE(encode != nullptr, "cuTensorMapEncodeTiled could not be resolved from the driver");
-    struct Dim { long long size, stride; int box, id; };
-    Dim d[3] = {{S, s_s, box_rows, 0}, {H, s_h, 1, 1}, {B, s_b, 1, 2}};
-    for (int i = 0; i < 3; ++i)
-        for (int j = i + 1; j < 3; ++j) {
-            // size-1 dims carry meaningless strides: sort them last
-            const bool swap = (d[j].size > 1 && d[i].size == 1) ||
-                              (d[j].size > 1 && d[i].size > 1 && d[j].stride < d[i].stride);
-            if (swap) { Dim t = d[i]; d[i] = d[j]; d[j] = t; }
-        }
-    cuuint64_t dims[4] = {(cuuint64_t)D, 0, 0, 0};
-    cuuint64_t strides[3];
-    cuuint32_t box[4] = {64, 1, 1, 1};
-    cuuint32_t estr[4] = {1, 1, 1, 1};
-    long long prev_extent = (long long)D * 2;
-    for (int i = 0; i < 3; ++i) {
-        dims[i + 1] = (cuuint64_t)d[i].size;
-        long long st = d[i].stride * 2;
-        if (d[i].size == 1 && (st < prev_extent || st % 16)) st = prev_extent;  // any legal value
-        strides[i] = (cuuint64_t)st;
-        prev_extent = st * d[i].size;
-        box[i + 1] = (cuuint32_t)d[i].box;
-        pos[d[i].id] = i + 1;
-    }
-    CUresult r = encode(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), dims, strides, box, estr,
-                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    NXD_REQUIRE(r == CUDA_SUCCESS,
-                "cuTensorMapEncodeTiled(4d) failed (%d): dims=[%d,%llu,%llu,%llu] strides=[%llu,%llu,%llu] box_rows=%d",
-                (int)r, D, (unsigned long long)dims[1], (unsigned long long)dims[2], (unsigned long long)dims[3],
-                (unsigned long long)strides[0], (unsigned long long)strides[1], (unsigned long long)strides[2],
-                box_rows);
-    return 0;
 }
 
 template <int D>

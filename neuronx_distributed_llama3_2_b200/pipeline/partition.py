@@ -1,0 +1,153 @@
+"""Cut a traced model into pipeline stages and derive each stage's IO.
+
+Reference: ``src/neuronx_distributed/pipeline/partition.py:18-303``.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass, field
+from typing import Dict, List, Optional, Sequence, Tuple
+
+import torch
+import torch.fx as fx
+from torch.fx.passes.split_module import split_module
+
+
+@dataclass
+class PipelineIO:
+    """One value crossing a stage boundary: ``name`` is the FX node name in the split graph."""
+    name: str
+    input_idx: Optional[int] = None   # position among the consuming stage's placeholders
+    output_idx: Optional[int] = None  # position among the producing stage's outputs
+    metadata: Optional[list] = None
+    obj: Optional[object] = None
+
+    def __repr__(self):
+        return f"PipelineIO({self.name}, in={self.input_idx}, out={self.output_idx})"
+
+
+@dataclass
+class StageIO:
+    model_inputs: List[Tuple[str, int]] = field(default_factory=list)   # (model input name, placeholder index)
+    recv: List[PipelineIO] = field(default_factory=list)                # values received from the previous stage
+    send: List[PipelineIO] = field(default_factory=list)                # values sent to the next stage
+    num_placeholders: int = 0
+    returns_model_output: bool = False
+
+
+def create_partitions(num_stages: int, num_layers: int) -> List[int]:
+    """Even split of ``num_layers`` over ``num_stages``, remainder to the LATER stages; returns the 0-based index of
+    the last layer of every stage but the final one (reference ``:280-303``)."""
+    if num_stages > num_layers:
+        raise ValueError(f"cannot cut {num_layers} layers into {num_stages} stages")
+    base, rem = divmod(num_layers, num_stages)
+    sizes = [base + (1 if s >= num_stages - rem else 0) for s in range(num_stages)]
+    cuts, acc = [], 0
+    for s in sizes[:-1]:
+        acc += s
+        cuts.append(acc - 1)
+    return cuts
+
+
+def stage_to_pipeline_parallel_rank(stage: int, pp_size: int) -> int:
+    """Virtual stages are dealt round-robin (reference ``:226-229``)."""
+    return stage % pp_size
+
+
+def partition_traced_model(traced: fx.GraphModule, cut_names: Sequence[str]) -> fx.GraphModule:
+    """A new stage starts right AFTER each node whose name / call_module target is in ``cut_names``."""
+    cut_set = set(cut_names)
+    found = set()
+    stage_of: Dict[fx.Node, int] = {}
+    cur = 0
+    for node in traced.graph.nodes:
+        if node.op in ("placeholder", "output"):
+            continue
+        stage_of[node] = cur
+        key = node.target if node.op == "call_module" else node.name
+        hit = (isinstance(key, str) and key in cut_set) or node.name in cut_set
+        if hit:
+            found.add(key if isinstance(key, str) and key in cut_set else node.name)
+            cur += 1
+    missing = cut_set - found
+    if missing:
+        raise ValueError(f"pipeline cuts {sorted(missing)} not found in the traced graph; candidates: "
+                         f"{[n.target for n in traced.graph.nodes if n.op == 'call_module'][:50]}")
+    # getitem nodes that unpack a cut node's tuple output belong to the NEXT stage (they were assigned there already
+    # because they come after the cut node in topological order)
+    return split_module(traced, None, lambda n: stage_of[n])
+
+
+def analyze_pipeline_module(split: fx.GraphModule) -> Tuple[List[str], List[StageIO]]:
+    """Derive, for every ``submod_k``, which placeholders are model inputs, which values it receives from stage k-1
+    and which it sends to stage k+1 -- including PASS-THROUGH values that a later stage needs (reference
+    ``:76-107,132-223``)."""
+    model_inputs = [n.name for n in split.graph.nodes if n.op == "placeholder"]
+    calls = [n for n in split.graph.nodes if n.op == "call_module"]
+    calls.sort(key=lambda n: int(n.target.split("_")[-1]))
+    n_stages = len(calls)
+    producer: Dict[str, int] = {}
+    aliases: Dict[str, Tuple[str, Optional[int]]] = {}
+    for k, c in enumerate(calls):
+        producer[c.name] = k
+    for n in split.graph.nodes:   # getitem on a multi-output submodule
+        if n.op == "call_function" and getattr(n.target, "__name__", "") == "getitem":
+            src, idx = n.args
+            aliases[n.name] = (src.name, idx)
+            producer[n.name] = producer[src.name]
+    out_node = next(n for n in split.graph.nodes if n.op == "output")
+    final_vals = set()
+
+    def collect(a):
+        if isinstance(a, fx.Node):
+            final_vals.add(a.name)
+        elif isinstance(a, (tuple, list)):
+            for x in a:
+                collect(x)
+        elif isinstance(a, dict):
+            for x in a.values():
+                collect(x)
+
+    collect(out_node.args)
+    ios = [StageIO() for _ in range(n_stages)]
+    needed_at: Dict[str, int] = {}    # value -> last stage that consumes it
+    for k, c in enumerate(calls):
+        ios[k].num_placeholders = len(c.args)
+        for pos, a in enumerate(c.args):
+            assert isinstance(a, fx.Node), "stage inputs must be graph values"
+            if a.op == "placeholder":
+                ios[k].model_inputs.append((a.name, pos))
+            else:
+                needed_at[a.name] = max(needed_at.get(a.name, -1), k)
+    # values travel stage by stage from their producer to their last consumer
+    for name, last in needed_at.items():
+        src = producer[name]
+        for hop in range(src, last):
+            ios[hop].send.append(PipelineIO(name))
+            ios[hop + 1].recv.append(PipelineIO(name))
+    for k, c in enumerate(calls):
+        for pos, a in enumerate(c.args):
+            if a.op != "placeholder":
+                for io in ios[k].recv:
+                    if io.name == a.name:
+                        io.input_idx = pos
+        # output index of values this stage produced itself
+        for io in ios[k].send:
+            if producer[io.name] == k:
+                io.output_idx = aliases[io.name][1] if io.name in aliases else None
+        ios[k].returns_model_output = any(producer.get(v) == k for v in final_vals)
+    return model_inputs, ios
+
+
+def analyze_shared_weights_across_stages(split: fx.GraphModule) -> List[List[Tuple[str, int]]]:
+    """Parameters (same tensor object) that live in more than one stage, e.g. tied embeddings
+    (reference ``:232-277``).  Returns ``[[(local_name, stage), ...], ...]``."""
+    seen: Dict[int, List[Tuple[str, int]]] = {}
+    for cname, child in split.named_children():
+        if not cname.startswith("submod_"):
+            continue
+        stage = int(cname.split("_")[-1])
+        for pname, p in child.named_parameters(remove_duplicate=False):
+            entry = seen.setdefault(id(p), [])
+            if all(s != stage for _, s in entry):
+                entry.append((pname, stage))
+    return [v for v in seen.values() if len(v) > 1]

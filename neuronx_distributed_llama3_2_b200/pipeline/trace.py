@@ -1,0 +1,85 @@
+"""FX tracing of the user model for pipeline partitioning.
+
+Reference: ``src/neuronx_distributed/pipeline/trace.py:77-211``: the transformer layer class and the parallel
+modules are leaves, parallel functions are auto-wrapped, unused inputs become concrete ``None`` args, the traced
+graph is DCE'd and linted.  The HF tracer is used when the model is a ``transformers.PreTrainedModel``.
+"""
+from __future__ import annotations
+
+import inspect
+from typing import Any, Callable, Dict, Iterable, List, Optional, Sequence, Type
+
+import torch
+import torch.fx as fx
+
+from ..utils.logger import get_logger
+
+logger = get_logger()
+
+
+def _default_leaf_classes() -> tuple:
+    from ..modules.qkv_linear import GQAQKVColumnParallelLinear
+    from ..parallel import PARALLEL_MODULES
+    from ..parallel.layer_norm import LayerNorm, RMSNorm
+
+    return tuple(PARALLEL_MODULES) + (GQAQKVColumnParallelLinear, RMSNorm, LayerNorm)
+
+
+class NxDTracer(fx.Tracer):
+    """torch.fx tracer whose leaves are the pipeline-atomic modules."""
+
+    def __init__(self, leaf_classes: Sequence[Type[torch.nn.Module]] = (), autowrap_functions: Iterable[Callable] = (),
+                 autowrap_modules: Iterable[Any] = ()):
+        import math
+
+        super().__init__(autowrap_modules=(math, *autowrap_modules), autowrap_functions=tuple(autowrap_functions))
+        self.leaf_classes = tuple(leaf_classes)
+
+    def is_leaf_module(self, m: torch.nn.Module, module_qualified_name: str) -> bool:
+        if isinstance(m, self.leaf_classes):
+            return True
+        return super().is_leaf_module(m, module_qualified_name)
+
+
+def get_concrete_args(model: torch.nn.Module, input_names: Optional[List[str]]) -> Dict[str, Any]:
+    """Every ``forward`` parameter that is not a traced input is fixed to its default (reference ``:77-104``)."""
+    sig = inspect.signature(model.forward)
+    if input_names is None:
+        return {}
+    concrete = {}
+    for name, prm in sig.parameters.items():
+        if name in input_names or prm.kind in (prm.VAR_POSITIONAL, prm.VAR_KEYWORD):
+            continue
+        concrete[name] = None if prm.default is inspect.Parameter.empty else prm.default
+    return concrete
+
+
+def trace_model(model: torch.nn.Module, input_names: Optional[List[str]] = None,
+                leaf_modules: Optional[Sequence[Type[torch.nn.Module]]] = None,
+                autowrap_functions: Optional[Iterable[Callable]] = None, autowrap_modules: Optional[Iterable[Any]] = None,
+                autowrap_obj_methods: Optional[Dict[Any, List[str]]] = None, tracer_cls=None) -> fx.GraphModule:
+    """Symbolically trace ``model`` keeping ``leaf_modules`` (+ the parallel layers) opaque."""
+    from ..parallel import PARALLEL_FUNCTIONS
+
+    leaves = tuple(leaf_modules or ()) + _default_leaf_classes()
+    wrap_fns = list(PARALLEL_FUNCTIONS) + list(autowrap_functions or [])
+    wrap_fns += list(getattr(model, "_fx_wrap_functions", []))
+    tracer = (tracer_cls or NxDTracer)(leaf_classes=leaves, autowrap_functions=wrap_fns,
+                                       autowrap_modules=tuple(autowrap_modules or ()))
+    patched = []
+    if autowrap_obj_methods:  # reference ``:125-148``: make bound methods opaque call_function nodes
+        for obj, names in autowrap_obj_methods.items():
+            for n in names:
+                orig = getattr(obj, n)
+                fx.wrap(orig) if inspect.isfunction(orig) else None
+                patched.append((obj, n, orig))
+    try:
+        graph = tracer.trace(model, concrete_args=get_concrete_args(model, input_names))
+    finally:
+        for obj, n, orig in patched:
+            setattr(obj, n, orig)
+    gm = fx.GraphModule(tracer.root, graph, class_name=model.__class__.__name__)
+    gm.graph.eliminate_dead_code()
+    gm.graph.lint()
+    gm.recompile()
+    return gm

@@ -1,0 +1,112 @@
+"""Tensor <-> container (de)composition used by the pipeline engine.
+
+Reference: ``src/neuronx_distributed/utils/serialization.py:14-253`` -- ``SerializationManager`` strips tensors out of
+nested python containers into ``(stub, tensors, TensorMeta[])`` and rebuilds them on the receiving stage;
+``find_loss_from_output_and_spec`` locates the loss inside a model output.
+"""
+from __future__ import annotations
+
+import base64
+import pickle
+from dataclasses import dataclass
+from typing import Any, List, Optional, Tuple
+
+import torch
+
+
+def pickle_to_str(obj: Any) -> str:
+    return base64.b64encode(pickle.dumps(obj)).decode("ascii")
+
+
+def unpickle_from_str(s: str) -> Any:
+    return pickle.loads(base64.b64decode(s.encode("ascii")))
+
+
+@dataclass
+class TensorMeta:
+    tensor_index: int
+    dtype: torch.dtype
+    shape: Tuple[int, ...]
+    requires_grad: bool
+    device: Optional[str] = None
+
+    def __repr__(self):
+        return f"TensorMeta(idx={self.tensor_index}, {self.dtype}, {tuple(self.shape)}, grad={self.requires_grad})"
+
+
+class _Stub:
+    __slots__ = ("idx",)
+
+    def __init__(self, idx):
+        self.idx = idx
+
+
+class SerializationManager:
+    """``serialize(obj) -> (stub_obj, tensors, metas)``; ``deserialize(stub_obj, tensors) -> obj``."""
+
+    def serialize(self, obj: Any):
+        tensors: List[torch.Tensor] = []
+        metas: List[TensorMeta] = []
+
+        def walk(x):
+            if isinstance(x, torch.Tensor):
+                idx = len(tensors)
+                tensors.append(x)
+                metas.append(TensorMeta(idx, x.dtype, tuple(x.shape), x.requires_grad, str(x.device)))
+                return _Stub(idx)
+            if isinstance(x, dict):
+                return type(x)((k, walk(v)) for k, v in x.items())
+            if isinstance(x, tuple) and hasattr(x, "_fields"):
+                return type(x)(*[walk(v) for v in x])
+            if isinstance(x, (list, tuple)):
+                return type(x)(walk(v) for v in x)
+            if isinstance(x, slice):
+                return slice(walk(x.start), walk(x.stop), walk(x.step))
+            return x
+
+        return walk(obj), tensors, metas
+
+    def deserialize(self, stub_obj: Any, tensors: List[torch.Tensor]) -> Any:
+        def walk(x):
+            if isinstance(x, _Stub):
+                return tensors[x.idx]
+            if isinstance(x, dict):
+                return type(x)((k, walk(v)) for k, v in x.items())
+            if isinstance(x, tuple) and hasattr(x, "_fields"):
+                return type(x)(*[walk(v) for v in x])
+            if isinstance(x, (list, tuple)):
+                return type(x)(walk(v) for v in x)
+            if isinstance(x, slice):
+                return slice(walk(x.start), walk(x.stop), walk(x.step))
+            return x
+
+        return walk(stub_obj)
+
+
+def find_loss_from_output_and_spec(output_val: Any, spec_val: Any):
+    """``spec`` mirrors the output structure with ``True`` at the loss position (reference ``:36-70``); ``None``
+    / ``True`` alone means the output itself is the loss."""
+    if spec_val is None or spec_val is True:
+        if isinstance(output_val, torch.Tensor):
+            return output_val
+        if isinstance(output_val, (tuple, list)):
+            return output_val[0]
+        if isinstance(output_val, dict):
+            return output_val["loss"]
+        return getattr(output_val, "loss")
+    if spec_val is False:
+        return None
+    if isinstance(spec_val, (tuple, list)):
+        for o, s in zip(output_val, spec_val):
+            r = find_loss_from_output_and_spec(o, s)
+            if r is not None:
+                return r
+        return None
+    if isinstance(spec_val, dict):
+        for k, s in spec_val.items():
+            o = output_val[k] if isinstance(output_val, dict) else getattr(output_val, k)
+            r = find_loss_from_output_and_spec(o, s)
+            if r is not None:
+                return r
+        return None
+    raise RuntimeError(f"unsupported loss spec {spec_val!r}")

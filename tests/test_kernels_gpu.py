@@ -357,6 +357,7 @@ def test_flash_attention(S, D, impl, monkeypatch):
 
     _lib()
     monkeypatch.setenv("NXD_ATTN_FWD", impl)
+    monkeypatch.setenv("NXD_ATTN_BWD", impl)   # "tc" backward exists for D = 128; D = 64 falls back to mma.sync
     B, Hq, Hkv = 2, 6, 2
     q = torch.randn(B, Hq, S, D, device="cuda").bfloat16().requires_grad_()
     k = torch.randn(B, Hkv, S, D, device="cuda").bfloat16().requires_grad_()
@@ -392,6 +393,29 @@ def test_flash_attention_strided_layout_noncausal():
             ref = A.attention_ref(q.float(), k.float(), v.float(), causal, None)
             assert _rel_err(out, ref) < 1e-2, (impl, causal, _rel_err(out, ref))
     os.environ.pop("NXD_ATTN_FWD", None)
+
+
+@pytest.mark.parametrize("causal", [True, False])
+def test_flash_attention_bwd_tc_gqa_cross_lengths(causal):
+    """tcgen05 backward: GQA group of 3, Sq != Sk, ragged lengths, strided [S, B, H, D] storage."""
+    from neuronx_distributed_llama3_2_b200.ops import attention as A
+
+    _lib()
+    B, Hq, Hkv, Sq, Sk, D = 2, 6, 2, 200, 328, 128
+    qs = torch.randn(Sq, B, Hq, D, device="cuda").bfloat16().requires_grad_()
+    ks = torch.randn(Sk, B, Hkv, D, device="cuda").bfloat16().requires_grad_()
+    vs = torch.randn(Sk, B, Hkv, D, device="cuda").bfloat16().requires_grad_()
+    q, k, v = (t.permute(1, 2, 0, 3) for t in (qs, ks, vs))
+    do = torch.randn(B, Hq, Sq, D, device="cuda").bfloat16()
+    out = A.flash_attn_func(q, k, v, causal=causal)
+    out.backward(do)
+    qf, kf, vf = (t.detach().float().requires_grad_() for t in (q, k, v))
+    ref = A.attention_ref(qf, kf, vf, causal, None)
+    ref.backward(do.float())
+    assert _rel_err(out, ref) < 1e-2
+    assert _rel_err(qs.grad.permute(1, 2, 0, 3), qf.grad) < 2e-2
+    assert _rel_err(ks.grad.permute(1, 2, 0, 3), kf.grad) < 2e-2
+    assert _rel_err(vs.grad.permute(1, 2, 0, 3), vf.grad) < 2e-2
 
 
 def test_flash_attention_large_magnitude_rows():
