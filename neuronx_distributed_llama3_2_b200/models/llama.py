@@ -225,6 +225,40 @@ class LlamaDecoderLayer(nn.Module):
         return self.mlp(h), residual
 
 
+class RotaryTables(nn.Module):
+    """cos/sin tables ``[S, D/2]`` for the sequence length of the batch (cached per (S, device)).  A pipeline-trace
+    leaf: the FX graph only sees ``rotary(input_ids) -> (cos, sin)``."""
+
+    _nxd_fx_leaf = True
+
+    def __init__(self, config: LlamaConfig):
+        super().__init__()
+        self.head_dim, self.theta, self.scaling = config.head_dim, config.rope_theta, config.rope_scaling
+        self._cache: Dict[Tuple[int, str], Tuple[torch.Tensor, torch.Tensor]] = {}
+
+    def forward(self, input_ids: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor]:
+        key = (input_ids.shape[1], str(input_ids.device))
+        if key not in self._cache:
+            self._cache = {key: rope_ops.build_rope_cache(key[0], self.head_dim, self.theta, self.scaling,
+                                                          device=input_ids.device)}
+        return self._cache[key]
+
+
+class CausalLMLoss(nn.Module):
+    """Mean next-token loss from vocab-parallel logits ``[S, B, V/tp]`` and labels ``[B, S]`` (shifted here,
+    reference ``modeling_llama_nxd.py:733-747``).  A pipeline-trace leaf."""
+
+    _nxd_fx_leaf = True
+
+    def forward(self, logits: torch.Tensor, labels: torch.Tensor) -> torch.Tensor:
+        B, S = labels.shape
+        shifted = torch.full((S, B), -100, dtype=torch.long, device=labels.device)
+        shifted[:-1] = labels[:, 1:].t()
+        per_token = parallel_cross_entropy(logits, shifted)        # [S, B] fp32
+        valid = shifted >= 0
+        return (per_token * valid).sum() / valid.sum().clamp(min=1)
+
+
 class LlamaModel(nn.Module):
     def __init__(self, config: LlamaConfig, device=None):
         super().__init__()
@@ -237,33 +271,23 @@ class LlamaModel(nn.Module):
                                      for _ in range(config.num_hidden_layers)])
         self.norm = RMSNorm(config.hidden_size, config.rms_norm_eps,
                             sequence_parallel_enabled=config.sequence_parallel_enabled, dtype=dt, device=device)
-        self._rope: Dict[Tuple[int, str], Tuple[torch.Tensor, torch.Tensor]] = {}
-
-    def rope_tables(self, seq_len: int, device) -> Tuple[torch.Tensor, torch.Tensor]:
-        key = (seq_len, str(device))
-        if key not in self._rope:
-            self._rope = {key: rope_ops.build_rope_cache(seq_len, self.config.head_dim, self.config.rope_theta,
-                                                         self.config.rope_scaling, device=device)}
-        return self._rope[key]
+        self.rotary = RotaryTables(config)
 
     def forward(self, input_ids: torch.Tensor) -> torch.Tensor:
         """``input_ids [B, S]`` -> final normed hidden states ``[S(/tp), B, H]``."""
         cfg = self.config
-        S = input_ids.shape[1]
         hidden = self.embed_tokens(input_ids)  # [S/tp, B, H] (reduce-scatter) -- SP region entered here
         if not cfg.sequence_parallel_enabled and ps.get_tensor_model_parallel_size() > 1:
             hidden = mappings.gather_from_sequence_parallel_region(hidden, to_model_parallel=False)
-        cos, sin = self.rope_tables(S, hidden.device)
+        cos_sin = self.rotary(input_ids)
+        cos, sin = cos_sin[0], cos_sin[1]
         residual = None
         for layer in self.layers:
             if cfg.activation_checkpointing and self.training and torch.is_grad_enabled():
                 hidden, residual = checkpoint(layer, hidden, residual, cos, sin, use_reentrant=False)
             else:
                 hidden, residual = layer(hidden, residual, cos, sin)
-        if residual is None:
-            return self.norm(hidden)
-        hidden, _ = norm_ops.fused_add_rms_norm(hidden, residual, self.norm.weight, self.norm.variance_epsilon)
-        return hidden
+        return self.norm(hidden, residual)   # fused (hidden + residual) -> RMSNorm
 
 
 class LlamaForCausalLM(nn.Module):
@@ -279,6 +303,7 @@ class LlamaForCausalLM(nn.Module):
                                             init_method=_init_fn(config.initializer_range),
                                             sequence_parallel_enabled=sp, dtype=config.torch_dtype,
                                             device="meta" if config.tie_word_embeddings else device)
+        self.loss_fn = CausalLMLoss()
         if config.tie_word_embeddings:
             self.tie_weights()
 
@@ -297,12 +322,7 @@ class LlamaForCausalLM(nn.Module):
         logits = self.lm_head(hidden)                  # [S, B, V/tp]  (AG->GEMM under SP)
         if labels is None:
             return logits
-        B, S = labels.shape
-        shifted = torch.full((S, B), -100, dtype=torch.long, device=labels.device)
-        shifted[:-1] = labels[:, 1:].t()
-        per_token = parallel_cross_entropy(logits, shifted)        # [S, B] fp32
-        valid = shifted >= 0
-        return (per_token * valid).sum() / valid.sum().clamp(min=1)
+        return self.loss_fn(logits, labels)
 
 
 def flops_per_token(cfg: LlamaConfig, seq_len: int) -> float:

@@ -35,5 +35,8 @@ class RMSNorm(torch.nn.Module):
         self.sequence_parallel_enabled = sequence_parallel_enabled
         setattr(self.weight, "sequence_parallel_enabled", sequence_parallel_enabled)
 
-    def forward(self, hidden_states: torch.Tensor) -> torch.Tensor:
+    def forward(self, hidden_states: torch.Tensor, residual: torch.Tensor = None) -> torch.Tensor:
+        """``rmsnorm(hidden_states)``, or with ``residual``: ``rmsnorm(hidden_states + residual)`` in one kernel."""
+        if residual is not None:
+            return norm_ops.fused_add_rms_norm(hidden_states, residual, self.weight, self.variance_epsilon)[0]
         return norm_ops.rms_norm(hidden_states, self.weight, self.variance_epsilon)

@@ -415,6 +415,12 @@ def destroy_model_parallel() -> None:
     _NEXT_RANK_LIST = _PREV_RANK_LIST = None
     _KV_SHARED.clear()
     _CUSTOM_PGS.clear()
+    try:
+        from ..pipeline import comm as _pp_comm
+
+        _pp_comm.reset_p2p_groups()
+    except Exception:  # pragma: no cover
+        pass
     for setter in (
         set_tensor_model_parallel_size, set_tensor_model_parallel_rank,
         set_expert_model_parallel_size, set_expert_model_parallel_rank,

@@ -129,11 +129,17 @@ class PipeSchedule(ABC):
 
 
 class InferenceSchedule(PipeSchedule):
-    """Forward only: every micro-batch is receive -> compute -> send."""
+    """Forward only: every micro-batch is receive -> compute -> send.  With virtual stages the model chunks are
+    walked one after the other (all micro-batches through chunk 0, then chunk 1, ...)."""
+
+    def __init__(self, num_microbatches: int, stages: int, stage_id: int, num_model_chunks: int = 1):
+        super().__init__(num_microbatches, stages, stage_id)
+        self.num_model_chunks = num_model_chunks
 
     def steps(self):
-        for mb in range(self.num_microbatches):
-            yield [ForwardPreprocessTask(mb), ForwardStepTask(mb), ForwardPostprocessTask(mb)]
+        for chunk in range(self.num_model_chunks):
+            for mb in range(self.num_microbatches):
+                yield [ForwardPreprocessTask(mb, chunk), ForwardStepTask(mb, chunk), ForwardPostprocessTask(mb, chunk)]
 
 
 class Train1F1BSchedule(PipeSchedule):

@@ -36,7 +36,7 @@ class NxDTracer(fx.Tracer):
         self.leaf_classes = tuple(leaf_classes)
 
     def is_leaf_module(self, m: torch.nn.Module, module_qualified_name: str) -> bool:
-        if isinstance(m, self.leaf_classes):
+        if isinstance(m, self.leaf_classes) or getattr(m, "_nxd_fx_leaf", False):
             return True
         return super().is_leaf_module(m, module_qualified_name)
 

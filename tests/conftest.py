@@ -57,7 +57,7 @@ def _worker(rank, world, port, fn, args, errq):
             dist.destroy_process_group()
 
 
-def run_distributed(fn, world: int, *args, timeout: float = 240.0):
+def run_distributed(fn, world: int, *args, timeout: float = 150.0):
     """Run ``fn(rank, world, *args)`` in ``world`` gloo processes on this host; re-raise the first failure."""
     import torch.multiprocessing as mp
 

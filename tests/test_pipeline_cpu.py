@@ -1,0 +1,147 @@
+"""NxDPPModel on CPU/gloo: PP=2 (1F1B) and PP=2 x virtual 2 (interleaved) against the un-partitioned model --
+loss, grads (incl. the tied embedding living on both stages), PP-agnostic state dict names, trainer + ZeRO-1 + checkpoint."""
+from __future__ import annotations
+
+import os
+import tempfile
+
+import pytest
+import torch
+
+from conftest import run_distributed
+
+
+def _build(num_layers=4):
+    from neuronx_distributed_llama3_2_b200.models import LlamaForCausalLM, tiny_llama
+
+    torch.manual_seed(0)
+    cfg = tiny_llama(num_hidden_layers=num_layers, sequence_parallel_enabled=False)
+    return cfg, LlamaForCausalLM(cfg)
+
+
+def _pp_worker(rank, world, vp, tmp):
+    from neuronx_distributed_llama3_2_b200 import trainer as nxd
+    from neuronx_distributed_llama3_2_b200.models.llama import LlamaDecoderLayer
+    from neuronx_distributed_llama3_2_b200.parallel import parallel_state as ps
+
+    nxd_cfg = nxd.neuronx_distributed_config(
+        tensor_parallel_size=1, pipeline_parallel_size=2,
+        pipeline_config={"transformer_layer_cls": LlamaDecoderLayer, "num_microbatches": 4, "auto_partition": True,
+                         "input_names": ["input_ids", "labels"], "virtual_pipeline_size": vp},
+        optimizer_config={"zero_one_enabled": True, "grad_clipping": True, "max_grad_norm": 1.0})
+    assert ps.get_pipeline_model_parallel_size() == 2
+    cfg, ref = _build()
+    ids = torch.randint(0, cfg.vocab_size, (8, 32), generator=torch.Generator().manual_seed(3))
+    # oracle: mean over 4 micro-batches of 2 sequences each == what the pipeline computes
+    ref_losses = [ref(c, labels=c) for c in torch.chunk(ids, 4, dim=0)]
+    ref_loss = torch.stack(ref_losses).mean()
+    ref_loss.backward()
+    ref_grads = {n: p.grad.clone() for n, p in ref.named_parameters()}
+
+    model = nxd.initialize_parallel_model(nxd_cfg, lambda: _build()[1], device=torch.device("cpu"))
+    pp = model.module
+    assert pp.num_stages == 2 * vp and len(pp.local_stage_ids) == vp
+    loss = model.run_train(input_ids=ids, labels=ids)
+    if rank == world - 1:
+        assert abs(loss.item() - ref_loss.item()) < 1e-5, (loss.item(), ref_loss.item())
+    else:
+        assert loss is None
+    names = []
+    for n, p in model.named_parameters():
+        names.append(n)
+        rn = "model.embed_tokens.weight" if n == "lm_head.weight" else n   # tied: one tensor, two original names
+        assert rn in ref_grads, f"local parameter name {n} is not an original name"
+        assert p.grad is not None, n
+        torch.testing.assert_close(p.grad, ref_grads[rn], atol=2e-5, rtol=1e-3, msg=lambda m: f"{n}: {m}")
+    # the tied embedding is owned by the first stage (embed) and the last stage (lm_head): both see the SUM
+    assert any(n.endswith("embed_tokens.weight") or n.endswith("lm_head.weight") for n in names)
+    all_names = [None] * world
+    torch.distributed.all_gather_object(all_names, names)
+    covered = set(all_names[0]) | set(all_names[1])
+    assert covered >= {n for n in ref_grads if not n.startswith("lm_head")}, set(ref_grads) - covered
+
+    # optimizer + checkpoint through the trainer API
+    opt = nxd.initialize_parallel_optimizer(nxd_cfg, torch.optim.AdamW, model.parameters(), lr=1e-2)
+    for p in model.parameters():
+        p.grad = None
+    opt.zero_grad()
+    l0 = model.run_train(input_ids=ids, labels=ids)
+    opt.step()
+    opt.zero_grad()
+    l1 = model.run_train(input_ids=ids, labels=ids)
+    if rank == world - 1:
+        assert l1.item() < l0.item()
+    d = os.path.join(tmp, f"pp_ckpt_vp{vp}")
+    nxd.save_checkpoint(d, "s1", model=model, optimizer=opt)
+    assert os.path.exists(os.path.join(d, "s1", "model", f"dp_rank_00_tp_rank_00_pp_rank_{rank:02d}.pt"))
+    before = {k: v.clone() for k, v in model.state_dict().items()}
+    with torch.no_grad():
+        for p in model.parameters():
+            p.mul_(0.5)
+    nxd.load_checkpoint(d, "s1", model=model, optimizer=opt)
+    for k, v in model.state_dict().items():
+        assert torch.equal(v, before[k]), k
+    # eval path
+    outs = model.run_eval(input_ids=ids, labels=ids)
+    if rank == world - 1:
+        assert len(outs) == 4
+
+
+@pytest.mark.parametrize("vp", [1, 2])
+def test_pp2_matches_single_process(vp):
+    with tempfile.TemporaryDirectory() as tmp:
+        run_distributed(_pp_worker, 2, vp, tmp)
+
+
+def _tp_pp_worker(rank, world):
+    """BASELINE.json config #3 in miniature: TP=2 x PP=2 with sequence parallelism + activation checkpointing."""
+    from neuronx_distributed_llama3_2_b200 import trainer as nxd
+    from neuronx_distributed_llama3_2_b200.models import LlamaForCausalLM, tiny_llama
+    from neuronx_distributed_llama3_2_b200.models.llama import LlamaDecoderLayer
+    from neuronx_distributed_llama3_2_b200.parallel import parallel_state as ps
+
+    nxd_cfg = nxd.neuronx_distributed_config(
+        tensor_parallel_size=2, pipeline_parallel_size=2, sequence_parallel=True,
+        pipeline_config={"transformer_layer_cls": LlamaDecoderLayer, "num_microbatches": 2, "auto_partition": True,
+                         "input_names": ["input_ids", "labels"], "broadcast_and_average_loss": True},
+        optimizer_config={"zero_one_enabled": True, "grad_clipping": True, "max_grad_norm": 1.0},
+        activation_checkpoint_config="full")
+    assert (ps.get_tensor_model_parallel_size(), ps.get_pipeline_model_parallel_size()) == (2, 2)
+    torch.manual_seed(0)
+    model = nxd.initialize_parallel_model(
+        nxd_cfg, lambda: LlamaForCausalLM(tiny_llama(num_hidden_layers=4)), device=torch.device("cpu"))
+    opt = nxd.initialize_parallel_optimizer(nxd_cfg, torch.optim.AdamW, model.parameters(), lr=1e-2)
+    ids = torch.randint(0, 512, (4, 64), generator=torch.Generator().manual_seed(5))
+    losses = []
+    for _ in range(6):
+        opt.zero_grad()
+        losses.append(float(model.run_train(input_ids=ids, labels=ids)))
+        opt.step()
+    assert losses[-1] < losses[0] - 0.3, losses
+    gathered = [None] * world
+    torch.distributed.all_gather_object(gathered, losses)
+    assert all(abs(g[-1] - losses[-1]) < 1e-5 for g in gathered), gathered  # broadcast_and_average_loss
+
+
+def test_tp2_pp2_sp_activation_checkpointing_trains():
+    run_distributed(_tp_pp_worker, 4)
+
+
+def test_debug_mode_partition_and_names():
+    from neuronx_distributed_llama3_2_b200.models.llama import LlamaDecoderLayer
+    from neuronx_distributed_llama3_2_b200.pipeline import NxDPPModel
+    from neuronx_distributed_llama3_2_b200.pipeline.partition import create_partitions
+
+    assert create_partitions(4, 8) == [1, 3, 5]
+    assert create_partitions(3, 8) == [1, 4]      # remainder goes to the later stages: sizes 2, 3, 3
+    cfg, m = _build(num_layers=8)
+    pp = NxDPPModel(m, transformer_layer_cls=LlamaDecoderLayer, num_microbatches=2, input_names=["input_ids", "labels"],
+                    auto_partition=True, _debug_mode=True, _debug_pp_size=4, _debug_pp_rank=1)
+    assert pp.pipeline_cuts == ["model.layers.1", "model.layers.3", "model.layers.5"]
+    local = [n for n, _ in pp.local_named_parameters()]
+    assert all(n.startswith("model.layers.2.") or n.startswith("model.layers.3.") for n in local), local
+    assert set(pp.local_state_dict().keys()) == set(local)
+    # parameters of other stages were released
+    assert m.model.layers[0].mlp.down_proj.weight.numel() == 0
+    with pytest.raises(RuntimeError):
+        pp(torch.zeros(1))
