@@ -246,3 +246,93 @@ NXD_API int nxd_rmsnorm_bwd(const void* dy, const void* x, const void* w, const 
     return rmsnorm_bwd_impl(dy, x, w, rstd, dresidual, dx, dw_bf16, dw_f32, accumulate, scratch, rows, H,
                             (cudaStream_t)stream);
 }
+
+// ---------------------------------------------------------------------------------------------------------
+// Allocation-free variant of the backward pass.
+//
+// nxd_rmsnorm_bwd() asks its caller for a scratch buffer (the per-CTA partial sums of dW).  Some callers have no
+// way to provide one: a host program that handed the whole HBM pool to another allocator at start-up (so a later
+// cudaMalloc fails or fragments the pool), a latency-critical loop that cannot tolerate the device-wide
+// synchronisation cudaMalloc / cudaFree imply, or a plug-in running inside someone else's operator callback where
+// device memory may only come from that host's allocator.  For them the partial sums live in the library image
+// itself: a file-scope __device__ array of kStaticScratchFloats floats (4 MiB) that every GPU which loads the
+// library keeps until the process exits.
+//
+//   * Limit: H <= kStaticMaxH (8192).  The number of partial rows is reduced to fit (at least 128 rows of partials
+//     remain at the largest H), which changes the summation order of dW slightly but not the result beyond fp32
+//     rounding.  Larger H is rejected with an error; use nxd_rmsnorm_bwd() with your own buffer instead.
+//   * The first call on each device resolves the array's device address (cudaGetSymbolAddress with that device
+//     current).  Make that first call before you start capturing a stream into a graph.
+//   * All calls share the one array.  Nothing in it has to start at zero -- every partial row that is read is
+//     written earlier in the same call -- and its contents after a call are meaningless.  Two calls whose kernels
+//     can overlap on the GPU (different streams) race on it; serialise them.
+//   * The call itself performs no cudaMalloc / cudaFree and calls no allocating library routine.
+// ---------------------------------------------------------------------------------------------------------
+namespace {
+
+constexpr int kStaticScratchFloats = 1 << 20;
+constexpr int kStaticMaxH = 8192;
+constexpr int kStaticMaxDevices = 64;
+
+static __device__ __align__(256) float g_rmsnorm_bwd_static_scratch[kStaticScratchFloats];
+
+// In host code the name above is only a handle for the symbol, not an address the GPU can use: resolve it per device.
+int static_scratch_for_current_device(float** out) {
+    static float* ptrs[kStaticMaxDevices] = {nullptr};
+    int dev = 0;
+    NXD_CHECK_CUDA(cudaGetDevice(&dev));
+    NXD_REQUIRE(dev >= 0 && dev < kStaticMaxDevices, "rmsnorm_bwd_static: device index %d out of range", dev);
+    float* p = __atomic_load_n(&ptrs[dev], __ATOMIC_ACQUIRE);
+    if (p == nullptr) {
+        void* addr = nullptr;
+        NXD_CHECK_CUDA(cudaGetSymbolAddress(&addr, g_rmsnorm_bwd_static_scratch));
+        NXD_REQUIRE(addr != nullptr, "rmsnorm_bwd_static: could not resolve the scratch symbol on device %d", dev);
+        p = static_cast<float*>(addr);
+        __atomic_store_n(&ptrs[dev], p, __ATOMIC_RELEASE);
+    }
+    *out = p;
+    return 0;
+}
+
+int rmsnorm_bwd_static_launch(const void* dy, const void* x, const void* w, const float* rstd, const void* dresidual,
+                              void* dx, void* dw_bf16, float* dw_f32, int accumulate, float* scratch, int P, int rows,
+                              int H, cudaStream_t s) {
+    NormCfg c = pick_cfg(H);
+#define LAUNCH(V)                                                                                        \
+    rmsnorm_bwd_kernel<V><<<P, c.threads, 0, s>>>((const bf16*)dy, (const bf16*)x, (const bf16*)w, rstd, \
+                                                  (const bf16*)dresidual, (bf16*)dx, scratch, rows, H)
+    switch (c.vpt) {
+        case 1: LAUNCH(1); break;
+        case 2: LAUNCH(2); break;
+        case 4: LAUNCH(4); break;
+        default: LAUNCH(8); break;
+    }
+#undef LAUNCH
+    NXD_LAUNCH_CHECK();
+    colsum_partials_kernel<<<(H + 255) / 256, 256, 0, s>>>(scratch, P, H, (bf16*)dw_bf16, dw_f32, accumulate);
+    NXD_LAUNCH_CHECK();
+    return 0;
+}
+
+}  // namespace
+
+NXD_API int nxd_rmsnorm_bwd_static_max_h(void) { return kStaticMaxH; }
+
+NXD_API int nxd_rmsnorm_bwd_static(const void* dy, const void* x, const void* w, const float* rstd,
+                                   const void* dresidual, void* dx, void* dw_bf16, float* dw_f32, int accumulate,
+                                   int rows, int H, void* stream) {
+    NXD_REQUIRE(H % 8 == 0 && H > 0, "rmsnorm_bwd_static: H=%d must be a positive multiple of 8", H);
+    NXD_REQUIRE(H <= kStaticMaxH,
+                "rmsnorm_bwd_static: H=%d exceeds the built-in scratch limit of %d columns; call nxd_rmsnorm_bwd with a "
+                "caller-provided scratch buffer instead",
+                H, kStaticMaxH);
+    NXD_REQUIRE(rows >= 0, "rmsnorm_bwd_static: negative row count");
+    if (rows == 0) return 0;
+    float* scratch = nullptr;
+    if (int rc = static_scratch_for_current_device(&scratch)) return rc;
+    int P = nxd_rmsnorm_bwd_num_partials(rows);
+    const int fit = kStaticScratchFloats / H;
+    if (P > fit) P = fit;
+    return rmsnorm_bwd_static_launch(dy, x, w, rstd, dresidual, dx, dw_bf16, dw_f32, accumulate, scratch, P, rows, H,
+                                     (cudaStream_t)stream);
+}

@@ -42,6 +42,15 @@ int nxd_rmsnorm_bwd(const void* dy, const void* x, const void* w, const float* r
                     void* dx, void* dw_bf16, float* dw_f32, int accumulate, float* scratch, int rows, int H,
                     void* stream);
 
+/* No counterpart in the reference.  Same computation as nxd_rmsnorm_bwd for callers that cannot supply (or allocate)
+ * a scratch buffer: the dW partial sums go to a 4 MiB __device__ array inside the library.  H <= 8192 (see
+ * nxd_rmsnorm_bwd_static_max_h), larger H returns an error.  No allocation happens in the call; the first call on a
+ * device looks up the array's address, so issue it before any stream capture.  Calls share the array: do not let two
+ * of them overlap on the GPU. */
+int nxd_rmsnorm_bwd_static_max_h(void);
+int nxd_rmsnorm_bwd_static(const void* dy, const void* x, const void* w, const float* rstd, const void* dresidual,
+                           void* dx, void* dw_bf16, float* dw_f32, int accumulate, int rows, int H, void* stream);
+
 /* ---- SwiGLU / RoPE (reference: modeling_llama_nxd.py:197-208, :398-399;
  *      examples/inference/modules/attention/utils.py:27-41) ------------------------------------- */
 int nxd_swiglu_fwd(const void* gate_up, void* out, long long rows, int I, void* stream);
