@@ -1,0 +1,456 @@
+// Fused sequence-parallel ALL-GATHER -> GEMM in ONE kernel over NVLink peer memory.
+//
+// Reference: ColumnParallelLinear forward under sequence parallelism does `xm.all_gather(input)` and then
+// `matmul(total_input, W^T)` as two dependent ops (src/neuronx_distributed/parallel_layers/layers.py:312-325); the
+// RowParallel backward does the same with dY (mappings.py:307-308 + layers.py:348).  Here the gather is performed BY
+// THE GEMM KERNEL while its tensor-core tiles run:
+//
+//   Y[tp*R, N] = concat_r(X_r)[tp*R, K] * W_op        X_r = rank r's [R, K] shard (bf16), W local
+//
+//   * every rank publishes its shard in a small symmetric (peer-mapped, CUDA-IPC) slot and raises a flag on every
+//     peer's signal pad (st.release.sys through NVLink);
+//   * a few "communication clusters" of the grid (default 6 of 74 CTA pairs) run no MMA at all: one thread per CTA
+//     drives the TMA engine -- cp.async.bulk from the PEER's HBM into shared memory, cp.async.bulk out to the local
+//     gathered buffer X_total -- slab after slab in ring order (rank+1, rank+2, ...), and bumps a per-256-row
+//     counter when a chunk has landed;
+//   * the remaining clusters are the persistent tcgen05 GEMM of gemm_tcgen05.cu.  Their tile order follows the
+//     arrival order (own slab first, read straight from the local shard), and the TMA producer polls the chunk
+//     counter (ld.acquire.gpu) before it loads A tiles of a remote slab.  Math on slab d overlaps the transfer of
+//     slab d+1; the gathered X_total is a by-product kept for the weight-gradient GEMM.
+//
+// Buffer reuse needs no extra barrier: slots and flags are double-buffered / epoch-stamped, and rank A cannot finish
+// call n+1 before rank B entered call n+1 (it needs B's flag), i.e. before B finished reading slot n.
+#include "common.cuh"
+#include "gemm_tcgen05.cuh"
+#include "ptx.cuh"
+
+namespace nxd_gemm {
+
+constexpr int kMaxTp = 8;
+constexpr int kChunkRows = kTileM;       // readiness granularity = one M tile (256 rows)
+constexpr int kCommSub = 16384;          // bytes per TMA bulk op of the copy engine
+constexpr int kCommBufs = 12;            // smem ring of the copy engine (192 KB in flight per CTA)
+
+struct AgArgs {
+    const bf16* x_local;          // [R, K] this rank's shard, dense
+    bf16* x_total;                // [tp*R, K] gathered activations (local, ordinary allocation)
+    bf16* slot_local;             // this rank's symmetric shard slot for this call (peers read it)
+    const bf16* slot_peer[kMaxTp];  // peers' slots (peer-mapped addresses); [rank] unused
+    uint32_t* sig_local;          // local signal pad
+    uint32_t* sig_peer[kMaxTp];   // peers' signal pads
+    int slot_ready;               // flag index: ready[src]            (tp entries)
+    int slot_chunks;              // flag index: chunk counters        (tp * chunks_per_slab entries)
+    int slot_own;                 // flag index: own-slab publish counter (1 entry)
+    int tp, rank, R;
+    int comm_ctas;
+    uint32_t epoch;
+};
+
+__device__ __forceinline__ uint32_t ld_acquire_gpu(const uint32_t* p) {
+    uint32_t v;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+    uint32_t v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t atom_add_release_gpu(uint32_t* p, uint32_t v) {
+    uint32_t old;
+    asm volatile("atom.add.release.gpu.global.u32 %0, [%1], %2;" : "=r"(old) : "l"(p), "r"(v) : "memory");
+    return old;
+}
+__device__ __forceinline__ void fence_proxy_async_all() { asm volatile("fence.proxy.async;" ::: "memory"); }
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     ptx::smem_u32(dst)),
+                 "l"(reinterpret_cast<uint64_t>(src)), "r"(bytes), "r"(ptx::smem_u32(bar))
+                 : "memory");
+}
+__device__ __forceinline__ void bulk_s2g(void* dst, const void* src, uint32_t bytes) {
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(reinterpret_cast<uint64_t>(dst)),
+                 "r"(ptx::smem_u32(src)), "r"(bytes)
+                 : "memory");
+}
+
+// Copy `bytes` (multiple of 16) from src (local or peer global memory) to up to two local destinations through a
+// shared-memory ring, entirely on the TMA engine.  Called by ONE thread.
+__device__ void tma_copy(uint8_t* ring, uint64_t* bars, uint32_t& phase_bits, const uint8_t* src, uint8_t* dst0,
+                         uint8_t* dst1, size_t bytes) {
+    const int n = (int)((bytes + kCommSub - 1) / kCommSub);
+    auto sz = [&](int i) { return (uint32_t)min((size_t)kCommSub, bytes - (size_t)i * kCommSub); };
+    auto load = [&](int i) {
+        const int b = i % kCommBufs;
+        ptx::mbar_arrive_expect_tx(&bars[b], sz(i));
+        bulk_g2s(ring + b * kCommSub, src + (size_t)i * kCommSub, sz(i), &bars[b]);
+    };
+    for (int i = 0; i < min(n, kCommBufs); ++i) load(i);
+    for (int i = 0; i < n; ++i) {
+        const int b = i % kCommBufs;
+        ptx::mbar_wait(&bars[b], (phase_bits >> b) & 1u);
+        phase_bits ^= (1u << b);
+        bulk_s2g(dst0 + (size_t)i * kCommSub, ring + b * kCommSub, sz(i));
+        if (dst1) bulk_s2g(dst1 + (size_t)i * kCommSub, ring + b * kCommSub, sz(i));
+        ptx::bulk_commit();
+        if (i + kCommBufs < n) {
+            ptx::bulk_wait_read<0>();  // the TMA store has consumed the buffer: refill it
+            load(i + kCommBufs);
+        }
+    }
+    ptx::bulk_wait<0>();  // every byte is in global memory
+}
+
+template <int BN, bool B_MN>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
+ag_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a_local, const __grid_constant__ CUtensorMap tmap_a_total,
+               const __grid_constant__ CUtensorMap tmap_b, const __grid_constant__ CUtensorMap tmap_d,
+               const AgArgs ag, int M, int N, int K) {
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    using L = SmemLayout<BN>;
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const uint32_t cta_rank = ptx::cluster_ctarank();
+    const int num_clusters_all = gridDim.x >> 1;
+    const int comm_clusters = ag.comm_ctas >> 1;
+    const int num_clusters = num_clusters_all - comm_clusters;   // GEMM clusters
+    // the copy engine takes the LOWEST block indices so that it is scheduled first
+    const int cluster_id = (int)(blockIdx.x >> 1) - comm_clusters;
+    const int chunks_per_slab = ag.R / kChunkRows;
+    const size_t slab_bytes = (size_t)ag.R * K * 2;
+
+    if (cluster_id < 0) {
+        // =========================== communication CTAs (copy engine, no MMA) ===========================
+        if (threadIdx.x != 0) return;
+        const int cid = (int)blockIdx.x;                           // 0 .. comm_ctas-1
+        uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kCommBufs * kCommSub);
+        for (int i = 0; i < kCommBufs; ++i) ptx::mbar_init(&bars[i], 1);
+        ptx::fence_barrier_init();
+        uint32_t phases = 0;
+        // per-chunk piece of this CTA: bytes [p0, p1) of every 256-row chunk
+        const size_t chunk_bytes = (size_t)kChunkRows * K * 2;
+        const size_t piece = ((chunk_bytes / ag.comm_ctas) + 15) & ~size_t(15);
+        const size_t p0 = min((size_t)cid * piece, chunk_bytes);
+        const size_t p1 = min(p0 + piece, chunk_bytes);
+        // 1. publish the own slab: local shard -> symmetric slot (for the peers) and -> X_total (by-product)
+        for (int c = 0; c < chunks_per_slab; ++c) {
+            if (p1 > p0) {
+                const size_t off = (size_t)c * chunk_bytes + p0;
+                tma_copy(smem, bars, phases, reinterpret_cast<const uint8_t*>(ag.x_local) + off,
+                         reinterpret_cast<uint8_t*>(ag.slot_local) + off,
+                         reinterpret_cast<uint8_t*>(ag.x_total) + (size_t)ag.rank * slab_bytes + off, p1 - p0);
+            }
+        }
+        fence_proxy_async_all();
+        __threadfence_system();
+        const uint32_t done = atom_add_release_gpu(ag.sig_local + ag.slot_own, 1u) + 1u;
+        if (done == ag.epoch * (uint32_t)ag.comm_ctas) {
+            // last copy CTA of this rank: the whole slab is published -> raise my flag on every peer
+            __threadfence_system();
+            for (int d = 1; d < ag.tp; ++d) {
+                const int peer = (ag.rank + d) % ag.tp;
+                st_release_sys(ag.sig_peer[peer] + ag.slot_ready + ag.rank, ag.epoch);
+            }
+        }
+        // 2. pull the peers' slabs in ring order as ONE continuous stream of 16 KB TMA copies: loads run kCommBufs
+        //    items ahead of the stores and a chunk's counter is bumped kLag store-groups after its last store was
+        //    issued (cp.async.bulk.wait_group<kLag> guarantees that everything older has landed), so the NVLink
+        //    pipe never drains between chunks.
+        constexpr int kLag = 4;
+        const int ipp = p1 > p0 ? (int)((p1 - p0 + kCommSub - 1) / kCommSub) : 0;      // items per piece
+        const int items_per_slab = ipp * chunks_per_slab;
+        const int n_items = items_per_slab * (ag.tp - 1);
+        auto item_addr = [&](int j, const uint8_t*& src, uint8_t*& dst, uint32_t& bytes) {
+            const int d = j / items_per_slab + 1;
+            const int rem = j % items_per_slab;
+            const int c = rem / ipp, i = rem % ipp;
+            const int srank = (ag.rank + d) % ag.tp;
+            const size_t off = (size_t)c * chunk_bytes + p0 + (size_t)i * kCommSub;
+            bytes = (uint32_t)min((size_t)kCommSub, p1 - p0 - (size_t)i * kCommSub);
+            src = reinterpret_cast<const uint8_t*>(ag.slot_peer[srank]) + off;
+            dst = reinterpret_cast<uint8_t*>(ag.x_total) + (size_t)srank * slab_bytes + off;
+        };
+        auto issue_load = [&](int j) {
+            if (j % items_per_slab == 0) {  // first touch of a new peer: its shard must be published
+                const int srank = (ag.rank + j / items_per_slab + 1) % ag.tp;
+                const uint32_t* flag = ag.sig_local + ag.slot_ready + srank;
+                while ((int32_t)(ld_acquire_sys(flag) - ag.epoch) < 0) { __nanosleep(64); }
+                fence_proxy_async_all();
+            }
+            const uint8_t* src; uint8_t* dst; uint32_t bytes;
+            item_addr(j, src, dst, bytes);
+            const int b = j % kCommBufs;
+            ptx::mbar_arrive_expect_tx(&bars[b], bytes);
+            bulk_g2s(smem + b * kCommSub, src, bytes, &bars[b]);
+        };
+        auto signal_chunk = [&](int j_last) {   // j_last = index of the chunk's last item
+            const int d = j_last / items_per_slab + 1;
+            const int c = (j_last % items_per_slab) / ipp;
+            const int srank = (ag.rank + d) % ag.tp;
+            fence_proxy_async_all();
+            __threadfence();
+            atom_add_release_gpu(ag.sig_local + ag.slot_chunks + srank * chunks_per_slab + c, 1u);
+        };
+        if (n_items == 0) {
+            // this CTA has no bytes to move (more copy CTAs than 16-byte pieces): still count on every chunk
+            for (int d = 1; d < ag.tp; ++d)
+                for (int c = 0; c < chunks_per_slab; ++c)
+                    atom_add_release_gpu(ag.sig_local + ag.slot_chunks + ((ag.rank + d) % ag.tp) * chunks_per_slab + c, 1u);
+            return;
+        }
+        for (int j = 0; j < min(n_items, kCommBufs); ++j) issue_load(j);
+        int next_signal = ipp - 1;   // item index whose completion finishes the next unsignalled chunk
+        for (int j = 0; j < n_items; ++j) {
+            const int b = j % kCommBufs;
+            ptx::mbar_wait(&bars[b], (phases >> b) & 1u);
+            phases ^= (1u << b);
+            const uint8_t* src; uint8_t* dst; uint32_t bytes;
+            item_addr(j, src, dst, bytes);
+            bulk_s2g(dst, smem + b * kCommSub, bytes);
+            ptx::bulk_commit();
+            if (j + kCommBufs < n_items) {
+                ptx::bulk_wait_read<0>();
+                issue_load(j + kCommBufs);
+            }
+            while (next_signal <= j - kLag) {
+                ptx::bulk_wait<kLag>();
+                signal_chunk(next_signal);
+                next_signal += ipp;
+            }
+        }
+        ptx::bulk_wait<0>();
+        while (next_signal < n_items) {
+            signal_chunk(next_signal);
+            next_signal += ipp;
+        }
+        return;
+    }
+
+    // =========================== GEMM CTAs (same pipeline as gemm_pair_kernel) ===========================
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + L::kBarrierOffset);
+    constexpr int kStages = L::kStages;
+    uint64_t* empty_bar = full_bar + kStages;
+    uint64_t* tmem_full_bar = empty_bar + kStages;
+    uint64_t* tmem_empty_bar = tmem_full_bar + kAccStages;
+    uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(tmem_empty_bar + kAccStages);
+    const bool is_leader = cta_rank == 0;
+    const int m_tiles_per_slab = chunks_per_slab;            // kChunkRows == kTileM
+    const int num_n_tiles = (N + BN - 1) / BN;
+    const int num_tiles = ag.tp * m_tiles_per_slab * num_n_tiles;
+    const int num_k_blocks = (K + kBlockK - 1) / kBlockK;
+
+    // tile -> (slab in arrival order, m tile inside the slab, n tile); n fastest so that A rows are shared in L2
+    auto tile_coords_ag = [&](int tile, int& slab, int& mt, int& tn) {
+        tn = tile % num_n_tiles;
+        const int mg = tile / num_n_tiles;
+        mt = mg % m_tiles_per_slab;
+        slab = (ag.rank + mg / m_tiles_per_slab) % ag.tp;
+    };
+
+    if (warp == 0 && lane == 0) {
+        ptx::prefetch_tensormap(&tmap_a_local);
+        ptx::prefetch_tensormap(&tmap_a_total);
+        ptx::prefetch_tensormap(&tmap_b);
+        ptx::prefetch_tensormap(&tmap_d);
+    }
+    if (warp == 1 && lane == 0) {
+        for (int i = 0; i < kStages; ++i) {
+            ptx::mbar_init(&full_bar[i], 1);
+            ptx::mbar_init(&empty_bar[i], 1);
+        }
+        for (int i = 0; i < kAccStages; ++i) {
+            ptx::mbar_init(&tmem_full_bar[i], 1);
+            ptx::mbar_init(&tmem_empty_bar[i], 2 * kEpilogueWarps);
+        }
+        ptx::fence_barrier_init();
+    }
+    if (warp == 2) ptx::tmem_alloc<2>(tmem_ptr_smem, L::kTmemCols);
+    ptx::tcgen05_fence_before();
+    ptx::cluster_sync();
+    ptx::tcgen05_fence_after();
+    const uint32_t tmem_base = *tmem_ptr_smem;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
+                int slab, mt, tn;
+                tile_coords_ag(tile, slab, mt, tn);
+                const bool own = slab == ag.rank;
+                if (!own) {
+                    // wait until every copy CTA delivered its piece of this 256-row chunk
+                    const uint32_t* cnt = ag.sig_local + ag.slot_chunks + slab * chunks_per_slab + mt;
+                    const uint32_t want = ag.epoch * (uint32_t)ag.comm_ctas;
+                    while ((int32_t)(ld_acquire_gpu(cnt) - want) < 0) { __nanosleep(32); }
+                    fence_proxy_async_all();
+                }
+                const CUtensorMap* ma = own ? &tmap_a_local : &tmap_a_total;
+                const int m0 = (own ? 0 : slab * ag.R) + mt * kTileM + (int)cta_rank * kBlockM;
+                const int n0 = tn * BN + (int)cta_rank * (BN / 2);
+                for (int kb = 0; kb < num_k_blocks; ++kb) {
+                    ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
+                    uint8_t* sa = smem + stage * L::kStageBytes;
+                    uint8_t* sb = sa + L::kABytes;
+                    const int k0 = kb * kBlockK;
+                    if (is_leader) ptx::mbar_arrive_expect_tx(&full_bar[stage], 2 * L::kStageBytes);
+                    ptx::tma_load_2d_pair(ma, &full_bar[stage], sa, k0, m0);
+                    if constexpr (!B_MN) {
+                        ptx::tma_load_2d_pair(&tmap_b, &full_bar[stage], sb, k0, n0);
+                    } else {
+#pragma unroll
+                        for (int g = 0; g < (BN / 2) / 64; ++g)
+                            ptx::tma_load_2d_pair(&tmap_b, &full_bar[stage], sb + g * (kBlockK * 128), n0 + g * 64, k0);
+                    }
+                    if (++stage == kStages) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (is_leader && lane == 0) {
+            constexpr uint32_t idesc = ptx::make_idesc_bf16(kTileM, BN, 0, B_MN ? 1 : 0);
+            constexpr uint32_t b_lbo = B_MN ? kBlockK * 128 : 16;
+            constexpr uint32_t b_kstep = B_MN ? 2048 : 32;
+            int stage = 0;
+            uint32_t phase = 0;
+            int acc = 0;
+            uint32_t acc_phase = 0;
+            for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
+                ptx::mbar_wait_cluster(&tmem_empty_bar[acc], acc_phase ^ 1);
+                ptx::tcgen05_fence_after();
+                const uint32_t tmem_d = tmem_base + acc * BN;
+                for (int kb = 0; kb < num_k_blocks; ++kb) {
+                    ptx::mbar_wait_cluster(&full_bar[stage], phase);
+                    ptx::tcgen05_fence_after();
+                    const uint32_t sa = ptx::smem_u32(smem + stage * L::kStageBytes);
+                    const uint32_t sb = sa + L::kABytes;
+#pragma unroll
+                    for (int k = 0; k < kBlockK / 16; ++k) {
+                        const uint64_t da = ptx::make_smem_desc(sa + k * 32, 16, 1024);
+                        const uint64_t db = ptx::make_smem_desc(sb + k * b_kstep, b_lbo, 1024);
+                        ptx::umma_bf16<2>(tmem_d, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
+                    }
+                    ptx::umma_commit_pair(&empty_bar[stage], 0b11);
+                    if (++stage == kStages) { stage = 0; phase ^= 1; }
+                }
+                ptx::umma_commit_pair(&tmem_full_bar[acc], 0b11);
+                if (++acc == kAccStages) { acc = 0; acc_phase ^= 1; }
+            }
+        }
+    } else if (warp >= kFirstEpilogueWarp) {
+        const int q = warp & 3;
+        uint8_t* stg = smem + L::kStagingOffset + q * L::kStagingBytesPerWarp;
+        int buf = 0;
+        int acc = 0;
+        uint32_t acc_phase = 0;
+        for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
+            int slab, mt, tn;
+            tile_coords_ag(tile, slab, mt, tn);
+            const int row0 = slab * ag.R + mt * kTileM + (int)cta_rank * kBlockM + q * 32;
+            const int n0 = tn * BN;
+            ptx::mbar_wait(&tmem_full_bar[acc], acc_phase);
+            ptx::tcgen05_fence_after();
+            const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + acc * BN;
+#pragma unroll 1
+            for (int c = 0; c < BN / 64; ++c) {
+                if (lane == 0) ptx::bulk_wait_read<1>();
+                __syncwarp();
+                uint32_t r[64];
+                ptx::tmem_ld_32x32b_x32(taddr + c * 64, r);
+                ptx::tmem_ld_32x32b_x32(taddr + c * 64 + 32, r + 32);
+                ptx::tmem_ld_wait();
+                if (c == BN / 64 - 1) {
+                    ptx::tcgen05_fence_before();
+                    __syncwarp();
+                    if (lane == 0) ptx::mbar_arrive_cluster(&tmem_empty_bar[acc], 0);
+                }
+                uint8_t* dst = stg + buf * (32 * 128) + lane * 128;
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    bf162 p0 = __floats2bfloat162_rn(__uint_as_float(r[8 * j]), __uint_as_float(r[8 * j + 1]));
+                    bf162 p1 = __floats2bfloat162_rn(__uint_as_float(r[8 * j + 2]), __uint_as_float(r[8 * j + 3]));
+                    bf162 p2 = __floats2bfloat162_rn(__uint_as_float(r[8 * j + 4]), __uint_as_float(r[8 * j + 5]));
+                    bf162 p3 = __floats2bfloat162_rn(__uint_as_float(r[8 * j + 6]), __uint_as_float(r[8 * j + 7]));
+                    *reinterpret_cast<uint4*>(dst + ((j ^ (lane & 7)) << 4)) =
+                        make_uint4(*reinterpret_cast<uint32_t*>(&p0), *reinterpret_cast<uint32_t*>(&p1),
+                                   *reinterpret_cast<uint32_t*>(&p2), *reinterpret_cast<uint32_t*>(&p3));
+                }
+                ptx::fence_proxy_async();
+                __syncwarp();
+                if (lane == 0) {
+                    const int col0 = n0 + c * 64;
+                    if (col0 < N && row0 < M) ptx::tma_store_2d(&tmap_d, stg + buf * (32 * 128), col0, row0);
+                    ptx::bulk_commit();
+                }
+                buf ^= 1;
+            }
+            if (++acc == kAccStages) { acc = 0; acc_phase ^= 1; }
+        }
+        if (lane == 0) ptx::bulk_wait<0>();
+    }
+    ptx::tcgen05_fence_before();
+    ptx::cluster_sync();
+    if (warp == 2) ptx::tmem_dealloc<2>(tmem_base, L::kTmemCols);
+}
+
+}  // namespace nxd_gemm
+
+// layout 0 "nt": W = [N, K];  1 "nn": W = [K, N].  x_local [R, K] dense, x_total [tp*R, K] dense, y [tp*R, N] (pitch ldy).
+// slot_ptrs / sig_ptrs: HOST arrays of tp device pointers (own entry included).  R % 256 == 0, K % 64 == 0, N % 8 == 0.
+NXD_API int nxd_ag_gemm_bf16(int layout, const void* x_local, void* x_total, const void* w, void* y, int R, int N, int K,
+                             long long ldw, long long ldy, const void* const* slot_ptrs, void* const* sig_ptrs, int tp,
+                             int rank, int slot_ready, int slot_chunks, int slot_own, unsigned epoch, int comm_ctas,
+                             int block_n, void* stream) {
+    using namespace nxd_gemm;
+    NXD_REQUIRE(layout == 0 || layout == 1, "ag_gemm: layout must be 0 (nt) or 1 (nn)");
+    NXD_REQUIRE(tp >= 2 && tp <= kMaxTp && rank >= 0 && rank < tp, "ag_gemm: bad tp/rank %d/%d", tp, rank);
+    NXD_REQUIRE(R > 0 && R % kChunkRows == 0, "ag_gemm: rows per rank (%d) must be a multiple of %d", R, kChunkRows);
+    NXD_REQUIRE(K % 64 == 0 && N % 8 == 0 && ldw % 8 == 0 && ldy % 8 == 0, "ag_gemm: K %% 64, N %% 8 required");
+    NXD_REQUIRE(comm_ctas >= 2 && comm_ctas % 2 == 0, "ag_gemm: comm_ctas must be even and >= 2");
+    const int M = tp * R;
+    const int bn = block_n > 0 ? block_n : 256;
+    NXD_REQUIRE(bn == 128 || bn == 256, "ag_gemm: block_n must be 128 or 256");
+    AgArgs ag{};
+    ag.x_local = (const bf16*)x_local;
+    ag.x_total = (bf16*)x_total;
+    for (int r = 0; r < tp; ++r) {
+        ag.slot_peer[r] = (const bf16*)slot_ptrs[r];
+        ag.sig_peer[r] = (uint32_t*)sig_ptrs[r];
+    }
+    ag.slot_local = (bf16*)const_cast<void*>(slot_ptrs[rank]);
+    ag.sig_local = (uint32_t*)sig_ptrs[rank];
+    ag.slot_ready = slot_ready; ag.slot_chunks = slot_chunks; ag.slot_own = slot_own;
+    ag.tp = tp; ag.rank = rank; ag.R = R; ag.comm_ctas = comm_ctas; ag.epoch = epoch;
+    CUtensorMap ta_l, ta_t, tb, td;
+    int rc;
+    if ((rc = make_tmap_2d(&ta_l, x_local, (uint64_t)K, (uint64_t)R, (uint64_t)K, 64, kBlockM))) return rc;
+    if ((rc = make_tmap_2d(&ta_t, x_total, (uint64_t)K, (uint64_t)M, (uint64_t)K, 64, kBlockM))) return rc;
+    if (layout == 0) rc = make_tmap_2d(&tb, w, (uint64_t)K, (uint64_t)N, (uint64_t)ldw, 64, bn / 2);
+    else rc = make_tmap_2d(&tb, w, (uint64_t)N, (uint64_t)K, (uint64_t)ldw, 64, kBlockK);
+    if (rc) return rc;
+    if ((rc = make_tmap_2d(&td, y, (uint64_t)N, (uint64_t)M, (uint64_t)ldy, 64, 32, 2))) return rc;
+    const int clusters = nxd_num_sms() / 2;
+    NXD_REQUIRE(comm_ctas / 2 < clusters, "ag_gemm: too many communication CTAs");
+    cudaStream_t st = (cudaStream_t)stream;
+#define NXD_AG_LAUNCH(BN_, BMN_)                                                                              \
+    {                                                                                                         \
+        using L = SmemLayout<BN_>;                                                                            \
+        static cudaError_t once = cudaFuncSetAttribute(ag_gemm_kernel<BN_, BMN_>,                             \
+                                                       cudaFuncAttributeMaxDynamicSharedMemorySize, L::kSmemBytes); \
+        NXD_CHECK_CUDA(once);                                                                                 \
+        ag_gemm_kernel<BN_, BMN_><<<dim3(clusters * 2), dim3(kThreads), L::kSmemBytes, st>>>(ta_l, ta_t, tb, td, ag, M, \
+                                                                                             N, K);           \
+    }
+    if (bn == 256) {
+        if (layout == 0) NXD_AG_LAUNCH(256, false) else NXD_AG_LAUNCH(256, true)
+    } else {
+        if (layout == 0) NXD_AG_LAUNCH(128, false) else NXD_AG_LAUNCH(128, true)
+    }
+#undef NXD_AG_LAUNCH
+    NXD_LAUNCH_CHECK();
+    return 0;
+}

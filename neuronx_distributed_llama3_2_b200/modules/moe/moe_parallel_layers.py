@@ -1,0 +1,174 @@
+"""Expert-fused parallel linear layers and the router projection (reference
+``src/neuronx_distributed/modules/moe/moe_parallel_layers.py:52-394``).
+
+Weights are 3-D, one slab per local expert:
+  ``ExpertFusedColumnParallelLinear``  ``(E/ep, H, I/tp)``  ``partition_dim = 2``
+  ``ExpertFusedRowParallelLinear``     ``(E/ep, I/tp, H)``  ``partition_dim = 1``
+All parameters carry ``expert_model_parallel = True`` (also after ``.to()`` and inside ``state_dict``), which is how
+ZeRO-1, grad-norm and checkpoint IO tell them apart from dense parameters.
+"""
+from __future__ import annotations
+
+import math
+from typing import Callable, Optional
+
+import torch
+import torch.distributed as dist
+import torch.nn.init as init
+from torch.nn.parameter import Parameter
+
+from ...parallel import mappings
+from ...parallel import parallel_state as ps
+from ...parallel.utils import divide, set_tensor_model_parallel_attributes
+
+
+def _grouped_mm(x: torch.Tensor, w: torch.Tensor) -> torch.Tensor:
+    """``(e, c, a) @ (e, a, b) -> (e, c, b)``; extra leading dims of ``x`` are folded into ``c``."""
+    lead = x.shape[1:-1]
+    y = torch.bmm(x.reshape(x.shape[0], -1, x.shape[-1]), w)
+    return y.reshape((x.shape[0],) + tuple(lead) + (w.shape[-1],))
+
+
+class ExpertFusedLinearWithAsyncCommunication(torch.autograd.Function):
+    """Batched-over-experts linear: ``e...h,ehi->e...i`` with the TP all-reduce of the input grad (column flavour)
+    issued asynchronously and overlapped with the weight-grad batch GEMM (reference ``:52-110``)."""
+
+    @staticmethod
+    def forward(ctx, input, weight, async_grad_allreduce: bool):
+        ctx.async_grad_allreduce = async_grad_allreduce
+        ctx.save_for_backward(input, weight)
+        return _grouped_mm(input, weight)
+
+    @staticmethod
+    def backward(ctx, grad_output):
+        input, weight = ctx.saved_tensors
+        grad_input = _grouped_mm(grad_output, weight.transpose(1, 2))
+        handle = None
+        if ctx.async_grad_allreduce and ps.get_tensor_model_parallel_size() > 1:
+            grad_input = grad_input.contiguous()
+            handle = dist.all_reduce(grad_input, group=ps.get_tensor_model_parallel_group(), async_op=True)
+        e = input.shape[0]
+        x2 = input.reshape(e, -1, input.shape[-1])
+        g2 = grad_output.reshape(e, -1, grad_output.shape[-1])
+        grad_weight = torch.bmm(x2.transpose(1, 2), g2) if weight.requires_grad else None
+        if handle is not None:
+            handle.wait()
+        return grad_input, grad_weight, None
+
+
+class ExpertFusedLinear(torch.nn.Module):
+    """Mixin: marks parameters ``expert_model_parallel`` and keeps the mark through ``.to()`` / ``state_dict``."""
+
+    def _mark_expert_parallel_weights(self, iterable=None):
+        for p in (iterable if iterable is not None else self.parameters()):
+            setattr(p, "expert_model_parallel", True)
+
+    def _apply(self, fn, *a, **kw):
+        out = super()._apply(fn, *a, **kw)
+        self._mark_expert_parallel_weights()
+        return out
+
+    def _save_to_state_dict(self, destination, prefix, keep_vars):
+        super()._save_to_state_dict(destination, prefix, keep_vars)
+        for name in list(self._parameters.keys()):
+            key = prefix + name
+            if key in destination and destination[key] is not None:
+                setattr(destination[key], "expert_model_parallel", True)
+
+
+def _init_expert_weight(weight: torch.Tensor, init_method: Callable, partition_dim: int) -> None:
+    """Every expert slab is initialised like a 2-D linear weight; the TP slice is cut from a full-size draw on CPU
+    so that all TP ranks agree on the master weight."""
+    set_tensor_model_parallel_attributes(weight, True, partition_dim, 1)
+    if weight.device.type == "meta":
+        return
+    tp, rank = ps.get_tensor_model_parallel_size(), ps.get_tensor_model_parallel_rank()
+    shape = list(weight.shape)
+    shape[partition_dim] *= tp
+    with torch.no_grad():
+        full = torch.empty(shape, dtype=torch.float32)
+        for e in range(shape[0]):
+            init_method(full[e])
+        per = weight.shape[partition_dim]
+        weight.copy_(full.narrow(partition_dim, rank * per, per).to(weight.dtype))
+
+
+class ExpertFusedColumnParallelLinear(ExpertFusedLinear):
+    def __init__(self, num_experts: int, input_size: int, output_size: int, dtype: torch.dtype = torch.float32,
+                 device=None, stride: int = 1, init_method: Optional[Callable] = None, keep_master_weight: bool = False):
+        super().__init__()
+        self.num_experts = num_experts
+        self.input_size, self.output_size = input_size, output_size
+        tp, ep = ps.get_tensor_model_parallel_size(), ps.get_expert_model_parallel_size()
+        self.num_local_experts = divide(num_experts, ep)
+        self.output_size_per_partition = divide(output_size, tp)
+        self.async_tensor_model_parallel_allreduce = tp > 1
+        self.init_method = init_method or (lambda w: init.kaiming_uniform_(w, a=math.sqrt(5)))
+        self.weight = Parameter(torch.empty(self.num_local_experts, input_size, self.output_size_per_partition,
+                                            dtype=dtype, device=device))
+        _init_expert_weight(self.weight, self.init_method, 2)
+        setattr(self.weight, "partition_stride", stride)
+        self.register_parameter("bias", None)
+        self._mark_expert_parallel_weights()
+
+    def forward(self, input_: torch.Tensor, expert_indices: Optional[torch.Tensor] = None) -> torch.Tensor:
+        w = self.weight if expert_indices is None else self.weight[expert_indices]
+        return ExpertFusedLinearWithAsyncCommunication.apply(input_, w, self.async_tensor_model_parallel_allreduce)
+
+
+class ExpertFusedRowParallelLinear(ExpertFusedLinear):
+    def __init__(self, num_experts: int, input_size: int, output_size: int, reduce_output: bool = True,
+                 dtype: torch.dtype = torch.float32, device=None, stride: int = 1,
+                 init_method: Optional[Callable] = None, keep_master_weight: bool = False):
+        super().__init__()
+        self.num_experts = num_experts
+        self.input_size, self.output_size = input_size, output_size
+        self.reduce_output = reduce_output
+        tp, ep = ps.get_tensor_model_parallel_size(), ps.get_expert_model_parallel_size()
+        self.num_local_experts = divide(num_experts, ep)
+        self.input_size_per_partition = divide(input_size, tp)
+        self.init_method = init_method or (lambda w: init.kaiming_uniform_(w, a=math.sqrt(5)))
+        self.weight = Parameter(torch.empty(self.num_local_experts, self.input_size_per_partition, output_size,
+                                            dtype=dtype, device=device))
+        _init_expert_weight(self.weight, self.init_method, 1)
+        setattr(self.weight, "partition_stride", stride)
+        self.register_parameter("bias", None)
+        self._mark_expert_parallel_weights()
+
+    def forward(self, input_: torch.Tensor, expert_indices: Optional[torch.Tensor] = None) -> torch.Tensor:
+        w = self.weight if expert_indices is None else self.weight[expert_indices]
+        out = ExpertFusedLinearWithAsyncCommunication.apply(input_, w, False)
+        if self.reduce_output:
+            out = mappings.reduce_from_tensor_model_parallel_region(out)
+        return out
+
+
+class LinearWithWeightGradAR(torch.autograd.Function):
+    """Replicated router projection whose WEIGHT grad is all-reduced over TP: the MoE layer defers its output
+    reduction, so each TP rank back-propagates only a partial grad into the router (reference ``:319-394``)."""
+
+    @staticmethod
+    def forward(ctx, input, weight):
+        ctx.save_for_backward(input, weight)
+        return torch.matmul(input, weight.t())
+
+    @staticmethod
+    def backward(ctx, grad_output):
+        input, weight = ctx.saved_tensors
+        grad_input = torch.matmul(grad_output, weight)
+        gw = torch.matmul(grad_output.reshape(-1, grad_output.shape[-1]).t(), input.reshape(-1, input.shape[-1]))
+        if ps.get_tensor_model_parallel_size() > 1:
+            dist.all_reduce(gw, group=ps.get_tensor_model_parallel_group())
+        return grad_input, gw
+
+
+class LinearRouter(torch.nn.Module):
+    def __init__(self, input_size: int, output_size: int, dtype: torch.dtype = torch.float32, device=None,
+                 init_method: Optional[Callable] = None):
+        super().__init__()
+        self.weight = Parameter(torch.empty(output_size, input_size, dtype=dtype, device=device))
+        if self.weight.device.type != "meta":
+            (init_method or (lambda w: init.kaiming_uniform_(w, a=math.sqrt(5))))(self.weight)
+
+    def forward(self, input_: torch.Tensor) -> torch.Tensor:
+        return LinearWithWeightGradAR.apply(input_, self.weight)

@@ -18,6 +18,17 @@ _PARAM_TAGS = ("tensor_model_parallel", "partition_dim", "partition_stride", "nu
                "sequence_parallel_enabled", "expert_model_parallel", "shared")
 
 
+# activation registry used by the MoE modules (reference ``utils/model_utils.py:4-11``)
+ACT2FN = {
+    "gelu": torch.nn.functional.gelu,
+    "leaky_relu": torch.nn.functional.leaky_relu,
+    "relu": torch.nn.functional.relu,
+    "sigmoid": torch.sigmoid,
+    "silu": torch.nn.functional.silu,
+    "tanh": torch.tanh,
+}
+
+
 def analyze_shared_parameters(module: nn.Module) -> List[List[Tuple[nn.Module, str]]]:
     """Groups of (module, attr-name) that alias the same Parameter (tied weights)."""
     seen: Dict[int, List[Tuple[nn.Module, str]]] = {}
