@@ -77,31 +77,48 @@ __device__ __forceinline__ void bulk_s2g(void* dst, const void* src, uint32_t by
                  : "memory");
 }
 
-// Copy `bytes` (multiple of 16) from src (local or peer global memory) to up to two local destinations through a
-// shared-memory ring, entirely on the TMA engine.  Called by ONE thread.
-__device__ void tma_copy(uint8_t* ring, uint64_t* bars, uint32_t& phase_bits, const uint8_t* src, uint8_t* dst0,
-                         uint8_t* dst1, size_t bytes) {
-    const int n = (int)((bytes + kCommSub - 1) / kCommSub);
-    auto sz = [&](int i) { return (uint32_t)min((size_t)kCommSub, bytes - (size_t)i * kCommSub); };
-    auto load = [&](int i) {
-        const int b = i % kCommBufs;
-        ptx::mbar_arrive_expect_tx(&bars[b], sz(i));
-        bulk_g2s(ring + b * kCommSub, src + (size_t)i * kCommSub, sz(i), &bars[b]);
+// One continuous stream of <= 16 KB TMA copies (global -> smem ring -> global), driven by ONE thread.  Loads run
+// kCommBufs items ahead of the stores.  addr(j, src, dst, bytes) describes item j; pre(j) runs before item j's load is
+// issued (flag waits); done(j) is called for every item with (j + 1) % sig_every == 0 once its store (and all older
+// ones) has fully landed -- kLag store groups later, so the pipe never drains between signals.
+template <typename AddrFn, typename PreFn, typename DoneFn>
+__device__ __forceinline__ void tma_stream(uint8_t* ring, uint64_t* bars, uint32_t& phases, int n_items, int sig_every,
+                                           AddrFn addr, PreFn pre, DoneFn done) {
+    constexpr int kLag = 4;
+    if (n_items <= 0) return;
+    auto issue_load = [&](int j) {
+        pre(j);
+        const uint8_t* src; uint8_t* dst; uint32_t bytes;
+        addr(j, src, dst, bytes);
+        const int b = j % kCommBufs;
+        ptx::mbar_arrive_expect_tx(&bars[b], bytes);
+        bulk_g2s(ring + b * kCommSub, src, bytes, &bars[b]);
     };
-    for (int i = 0; i < min(n, kCommBufs); ++i) load(i);
-    for (int i = 0; i < n; ++i) {
-        const int b = i % kCommBufs;
-        ptx::mbar_wait(&bars[b], (phase_bits >> b) & 1u);
-        phase_bits ^= (1u << b);
-        bulk_s2g(dst0 + (size_t)i * kCommSub, ring + b * kCommSub, sz(i));
-        if (dst1) bulk_s2g(dst1 + (size_t)i * kCommSub, ring + b * kCommSub, sz(i));
+    for (int j = 0; j < min(n_items, kCommBufs); ++j) issue_load(j);
+    int next_signal = sig_every > 0 ? sig_every - 1 : n_items;
+    for (int j = 0; j < n_items; ++j) {
+        const int b = j % kCommBufs;
+        ptx::mbar_wait(&bars[b], (phases >> b) & 1u);
+        phases ^= (1u << b);
+        const uint8_t* src; uint8_t* dst; uint32_t bytes;
+        addr(j, src, dst, bytes);
+        bulk_s2g(dst, ring + b * kCommSub, bytes);
         ptx::bulk_commit();
-        if (i + kCommBufs < n) {
-            ptx::bulk_wait_read<0>();  // the TMA store has consumed the buffer: refill it
-            load(i + kCommBufs);
+        if (j + kCommBufs < n_items) {
+            ptx::bulk_wait_read<0>();   // the store has consumed the buffer: refill it
+            issue_load(j + kCommBufs);
+        }
+        while (next_signal <= j - kLag) {
+            ptx::bulk_wait<kLag>();
+            done(next_signal);
+            next_signal += sig_every;
         }
     }
-    ptx::bulk_wait<0>();  // every byte is in global memory
+    ptx::bulk_wait<0>();   // every byte is in global memory
+    while (next_signal < n_items) {
+        done(next_signal);
+        next_signal += sig_every;
+    }
 }
 
 template <int BN, bool B_MN>
@@ -136,97 +153,72 @@ ag_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a_local, const __grid_co
         const size_t piece = ((chunk_bytes / ag.comm_ctas) + 15) & ~size_t(15);
         const size_t p0 = min((size_t)cid * piece, chunk_bytes);
         const size_t p1 = min(p0 + piece, chunk_bytes);
-        // 1. publish the own slab: local shard -> symmetric slot (for the peers) and -> X_total (by-product)
-        for (int c = 0; c < chunks_per_slab; ++c) {
-            if (p1 > p0) {
-                const size_t off = (size_t)c * chunk_bytes + p0;
-                tma_copy(smem, bars, phases, reinterpret_cast<const uint8_t*>(ag.x_local) + off,
-                         reinterpret_cast<uint8_t*>(ag.slot_local) + off,
-                         reinterpret_cast<uint8_t*>(ag.x_total) + (size_t)ag.rank * slab_bytes + off, p1 - p0);
-            }
-        }
+        const int ipp = p1 > p0 ? (int)((p1 - p0 + kCommSub - 1) / kCommSub) : 0;      // items per piece
+        const int items_per_slab = ipp * chunks_per_slab;
+        auto local_off = [&](int rem, size_t& off, uint32_t& bytes) {   // rem = item index inside a slab
+            const int c = rem / ipp, i = rem % ipp;
+            off = (size_t)c * chunk_bytes + p0 + (size_t)i * kCommSub;
+            bytes = (uint32_t)min((size_t)kCommSub, p1 - p0 - (size_t)i * kCommSub);
+        };
+        auto nop_pre = [](int) {};
+        auto nop_done = [](int) {};
+        // 1. publish the own shard in the symmetric slot (one un-interrupted stream), then raise the flag on every peer
+        tma_stream(smem, bars, phases, items_per_slab, 0,
+                   [&](int j, const uint8_t*& src, uint8_t*& dst, uint32_t& bytes) {
+                       size_t off;
+                       local_off(j, off, bytes);
+                       src = reinterpret_cast<const uint8_t*>(ag.x_local) + off;
+                       dst = reinterpret_cast<uint8_t*>(ag.slot_local) + off;
+                   },
+                   nop_pre, nop_done);
         fence_proxy_async_all();
         __threadfence_system();
-        const uint32_t done = atom_add_release_gpu(ag.sig_local + ag.slot_own, 1u) + 1u;
-        if (done == ag.epoch * (uint32_t)ag.comm_ctas) {
-            // last copy CTA of this rank: the whole slab is published -> raise my flag on every peer
+        const uint32_t done_cnt = atom_add_release_gpu(ag.sig_local + ag.slot_own, 1u) + 1u;
+        if (done_cnt == ag.epoch * (uint32_t)ag.comm_ctas) {
             __threadfence_system();
             for (int d = 1; d < ag.tp; ++d) {
                 const int peer = (ag.rank + d) % ag.tp;
                 st_release_sys(ag.sig_peer[peer] + ag.slot_ready + ag.rank, ag.epoch);
             }
         }
-        // 2. pull the peers' slabs in ring order as ONE continuous stream of 16 KB TMA copies: loads run kCommBufs
-        //    items ahead of the stores and a chunk's counter is bumped kLag store-groups after its last store was
-        //    issued (cp.async.bulk.wait_group<kLag> guarantees that everything older has landed), so the NVLink
-        //    pipe never drains between chunks.
-        constexpr int kLag = 4;
-        const int ipp = p1 > p0 ? (int)((p1 - p0 + kCommSub - 1) / kCommSub) : 0;      // items per piece
-        const int items_per_slab = ipp * chunks_per_slab;
-        const int n_items = items_per_slab * (ag.tp - 1);
-        auto item_addr = [&](int j, const uint8_t*& src, uint8_t*& dst, uint32_t& bytes) {
-            const int d = j / items_per_slab + 1;
-            const int rem = j % items_per_slab;
-            const int c = rem / ipp, i = rem % ipp;
-            const int srank = (ag.rank + d) % ag.tp;
-            const size_t off = (size_t)c * chunk_bytes + p0 + (size_t)i * kCommSub;
-            bytes = (uint32_t)min((size_t)kCommSub, p1 - p0 - (size_t)i * kCommSub);
-            src = reinterpret_cast<const uint8_t*>(ag.slot_peer[srank]) + off;
-            dst = reinterpret_cast<uint8_t*>(ag.x_total) + (size_t)srank * slab_bytes + off;
-        };
-        auto issue_load = [&](int j) {
-            if (j % items_per_slab == 0) {  // first touch of a new peer: its shard must be published
-                const int srank = (ag.rank + j / items_per_slab + 1) % ag.tp;
-                const uint32_t* flag = ag.sig_local + ag.slot_ready + srank;
-                while ((int32_t)(ld_acquire_sys(flag) - ag.epoch) < 0) { __nanosleep(64); }
-                fence_proxy_async_all();
-            }
-            const uint8_t* src; uint8_t* dst; uint32_t bytes;
-            item_addr(j, src, dst, bytes);
-            const int b = j % kCommBufs;
-            ptx::mbar_arrive_expect_tx(&bars[b], bytes);
-            bulk_g2s(smem + b * kCommSub, src, bytes, &bars[b]);
-        };
-        auto signal_chunk = [&](int j_last) {   // j_last = index of the chunk's last item
-            const int d = j_last / items_per_slab + 1;
-            const int c = (j_last % items_per_slab) / ipp;
-            const int srank = (ag.rank + d) % ag.tp;
+        // 2. pull the peers' shards in ring order; a chunk's counter is bumped when this CTA's piece of it has landed
+        auto count_chunk = [&](int srank, int c) {
             fence_proxy_async_all();
             __threadfence();
             atom_add_release_gpu(ag.sig_local + ag.slot_chunks + srank * chunks_per_slab + c, 1u);
         };
-        if (n_items == 0) {
-            // this CTA has no bytes to move (more copy CTAs than 16-byte pieces): still count on every chunk
+        if (ipp == 0) {  // more copy CTAs than 16-byte pieces: nothing to move, but the counters expect every CTA
             for (int d = 1; d < ag.tp; ++d)
-                for (int c = 0; c < chunks_per_slab; ++c)
-                    atom_add_release_gpu(ag.sig_local + ag.slot_chunks + ((ag.rank + d) % ag.tp) * chunks_per_slab + c, 1u);
-            return;
+                for (int c = 0; c < chunks_per_slab; ++c) count_chunk((ag.rank + d) % ag.tp, c);
         }
-        for (int j = 0; j < min(n_items, kCommBufs); ++j) issue_load(j);
-        int next_signal = ipp - 1;   // item index whose completion finishes the next unsignalled chunk
-        for (int j = 0; j < n_items; ++j) {
-            const int b = j % kCommBufs;
-            ptx::mbar_wait(&bars[b], (phases >> b) & 1u);
-            phases ^= (1u << b);
-            const uint8_t* src; uint8_t* dst; uint32_t bytes;
-            item_addr(j, src, dst, bytes);
-            bulk_s2g(dst, smem + b * kCommSub, bytes);
-            ptx::bulk_commit();
-            if (j + kCommBufs < n_items) {
-                ptx::bulk_wait_read<0>();
-                issue_load(j + kCommBufs);
-            }
-            while (next_signal <= j - kLag) {
-                ptx::bulk_wait<kLag>();
-                signal_chunk(next_signal);
-                next_signal += ipp;
-            }
-        }
-        ptx::bulk_wait<0>();
-        while (next_signal < n_items) {
-            signal_chunk(next_signal);
-            next_signal += ipp;
-        }
+        tma_stream(smem, bars, phases, items_per_slab * (ag.tp - 1), ipp,
+                   [&](int j, const uint8_t*& src, uint8_t*& dst, uint32_t& bytes) {
+                       const int srank = (ag.rank + j / items_per_slab + 1) % ag.tp;
+                       size_t off;
+                       local_off(j % items_per_slab, off, bytes);
+                       src = reinterpret_cast<const uint8_t*>(ag.slot_peer[srank]) + off;
+                       dst = reinterpret_cast<uint8_t*>(ag.x_total) + (size_t)srank * slab_bytes + off;
+                   },
+                   [&](int j) {
+                       if (j % items_per_slab == 0) {  // first touch of a new peer: its shard must be published
+                           const int srank = (ag.rank + j / items_per_slab + 1) % ag.tp;
+                           const uint32_t* flag = ag.sig_local + ag.slot_ready + srank;
+                           while ((int32_t)(ld_acquire_sys(flag) - ag.epoch) < 0) { __nanosleep(64); }
+                           fence_proxy_async_all();
+                       }
+                   },
+                   [&](int j_last) {
+                       count_chunk((ag.rank + j_last / items_per_slab + 1) % ag.tp, (j_last % items_per_slab) / ipp);
+                   });
+        // 3. by-product for the weight-gradient GEMM: own rows of X_total (nobody waits for this)
+        tma_stream(smem, bars, phases, items_per_slab, 0,
+                   [&](int j, const uint8_t*& src, uint8_t*& dst, uint32_t& bytes) {
+                       size_t off;
+                       local_off(j, off, bytes);
+                       src = reinterpret_cast<const uint8_t*>(ag.x_local) + off;
+                       dst = reinterpret_cast<uint8_t*>(ag.x_total) + (size_t)ag.rank * slab_bytes + off;
+                   },
+                   nop_pre, nop_done);
         return;
     }
 

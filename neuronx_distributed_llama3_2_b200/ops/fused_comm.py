@@ -21,6 +21,10 @@ def _comm_ctas() -> int:
     return int(os.environ.get("NXD_AG_COMM_CTAS", "12"))
 
 
+def _host_ptrs(ctx, table: torch.Tensor, offset: int):
+    return (_c.c_void_p * ctx.world)(*[p + offset for p in table.tolist()])
+
+
 def fused_ag_gemm(ctx, x_shard: torch.Tensor, weight: torch.Tensor, layout: str = "nt"
                   ) -> Optional[Tuple[torch.Tensor, torch.Tensor]]:
     """``(all_gather_rows(x_shard) @ W_op, x_total)`` or ``None`` if unsupported.  ``x_shard [R, K]`` bf16."""
@@ -29,45 +33,72 @@ def fused_ag_gemm(ctx, x_shard: torch.Tensor, weight: torch.Tensor, layout: str 
     R, K = x_shard.shape
     N = weight.shape[0] if layout == "nt" else weight.shape[1]
     tp = ctx.world
-    if R % 256 or K % 64 or N % 8 or tp > 8 or weight.stride(1) != 1 or weight.stride(0) % 8:
+    if R % 256 or K % 64 or N % 8 or tp > 8 or weight.stride(1) != 1 or weight.stride(0) % 8 or R // 256 > 64:
         return None
     x_shard = x_shard.contiguous()
     shard_bytes = R * K * 2
-    # symmetric shard slots: two per rank (double buffering, see the kernel's header comment)
-    _, table = ctx.region("ag_slots", 2 * shard_bytes)
-    chunks = R // 256
-    if not hasattr(ctx, "_ag_state"):
-        ctx._ag_state = {"ready": ctx.signal_slots("ag_ready", 8), "own": ctx.signal_slots("ag_own", 1),
-                         "chunks": ctx.signal_slots("ag_chunks", 8 * 64), "host_tables": {}}
-    st = ctx._ag_state
-    assert chunks <= 64, "rows per rank too large for the chunk flag table"
-    epoch = ctx.next_epoch("ag_gemm")
+    comm_ctas = _comm_ctas()
+    # flags / counters / slots are per configuration: the counters accumulate a fixed amount per call
+    cfg = f"ag:{R}:{K}:{comm_ctas}"
+    _, table = ctx.region(cfg, 2 * shard_bytes)   # two symmetric shard slots per rank (double buffering)
+    st = ctx.__dict__.setdefault("_fused_state", {})
+    if cfg not in st:
+        st[cfg] = {"ready": ctx.signal_slots(cfg + ":ready", 8), "own": ctx.signal_slots(cfg + ":own", 1),
+                   "chunks": ctx.signal_slots(cfg + ":chunks", 8 * (R // 256)),
+                   "sigs": (_c.c_void_p * tp)(*ctx.sig_peers), "slots": {}}
+    s = st[cfg]
+    epoch = ctx.next_epoch(cfg)
     parity = epoch & 1
-    key = (table.data_ptr(), shard_bytes, parity)
-    if key not in st["host_tables"]:
-        peers = table.tolist()
-        slots = (_c.c_void_p * tp)(*[p + parity * shard_bytes for p in peers])
-        sigs = (_c.c_void_p * tp)(*ctx.sig_peers)
-        st["host_tables"][key] = (slots, sigs)
-    slots, sigs = st["host_tables"][key]
-    # NOTE: the chunk counters are indexed [src * chunks_per_slab + c]; they count copy CTAs across calls, so the
-    # number of copy CTAs and the chunk count must not change between calls on one context.
-    cfg = (chunks, _comm_ctas())
-    if st.setdefault("cfg", cfg) != cfg:
-        return None
+    key = (table.data_ptr(), parity)
+    if key not in s["slots"]:
+        s["slots"][key] = _host_ptrs(ctx, table, parity * shard_bytes)
     x_total = torch.empty((tp * R, K), dtype=torch.bfloat16, device=x_shard.device)
     y = torch.empty((tp * R, N), dtype=torch.bfloat16, device=x_shard.device)
     rc = _lib.lib().nxd_ag_gemm_bf16(
         _c.c_int(_LAYOUT[layout]), _lib.ptr(x_shard), _lib.ptr(x_total), _lib.ptr(weight), _lib.ptr(y), _c.c_int(R),
-        _c.c_int(N), _c.c_int(K), _c.c_longlong(weight.stride(0)), _c.c_longlong(y.stride(0)), slots, sigs,
-        _c.c_int(tp), _c.c_int(ctx.rank), _c.c_int(st["ready"]), _c.c_int(st["chunks"]), _c.c_int(st["own"]),
-        _c.c_uint(epoch), _c.c_int(cfg[1]), _c.c_int(0), _lib.stream_ptr())
+        _c.c_int(N), _c.c_int(K), _c.c_longlong(weight.stride(0)), _c.c_longlong(y.stride(0)), s["slots"][key], s["sigs"],
+        _c.c_int(tp), _c.c_int(ctx.rank), _c.c_int(s["ready"]), _c.c_int(s["chunks"]), _c.c_int(s["own"]),
+        _c.c_uint(epoch), _c.c_int(comm_ctas), _c.c_int(0), _lib.stream_ptr())
     _lib.check(rc, "nxd_ag_gemm_bf16")
     return y, x_total
 
 
-def fused_gemm_rs(ctx, x2d, weight, layout="nt"):
-    return None
+def fused_gemm_rs(ctx, x2d: torch.Tensor, weight: torch.Tensor, layout: str = "nt") -> Optional[torch.Tensor]:
+    """``reduce_scatter_rows(x2d @ W_op)`` in one kernel (``csrc/fused_gemm_rs.cu``) or ``None`` if unsupported.
+    ``x2d [tp*R, Kloc]`` bf16; returns this rank's ``[R, N]`` rows of the sum over ranks."""
+    if layout not in _LAYOUT or x2d.dtype != torch.bfloat16 or weight.dtype != torch.bfloat16:
+        return None
+    tp = ctx.world
+    M, K = x2d.shape
+    N = weight.shape[0] if layout == "nt" else weight.shape[1]
+    if M % tp:
+        return None
+    R = M // tp
+    if (R % 256 or N % 8 or K % 8 or tp > 8 or weight.stride(1) != 1 or weight.stride(0) % 8 or x2d.stride(1) != 1
+            or x2d.stride(0) % 8 or R // 256 > 64):
+        return None
+    bn = 256
+    cfg = f"rs:{R}:{N}:{bn}"
+    stage_bytes = tp * R * N * 2
+    _, table = ctx.region(cfg, 2 * stage_bytes)
+    st = ctx.__dict__.setdefault("_fused_state", {})
+    if cfg not in st:
+        st[cfg] = {"cnt": ctx.signal_slots(cfg + ":cnt", 8 * (R // 256)), "sigs": (_c.c_void_p * tp)(*ctx.sig_peers),
+                   "stages": {}}
+    s = st[cfg]
+    epoch = ctx.next_epoch(cfg)
+    parity = epoch & 1
+    key = (table.data_ptr(), parity)
+    if key not in s["stages"]:
+        s["stages"][key] = _host_ptrs(ctx, table, parity * stage_bytes)
+    out = torch.empty((R, N), dtype=torch.bfloat16, device=x2d.device)
+    rc = _lib.lib().nxd_gemm_rs_bf16(
+        _c.c_int(_LAYOUT[layout]), _lib.ptr(x2d), _lib.ptr(weight), _lib.ptr(out), _c.c_int(R), _c.c_int(N), _c.c_int(K),
+        _c.c_longlong(x2d.stride(0)), _c.c_longlong(weight.stride(0)), _c.c_longlong(out.stride(0)), s["stages"][key],
+        s["sigs"], _c.c_int(tp), _c.c_int(ctx.rank), _c.c_int(s["cnt"]), _c.c_uint((epoch + 1) // 2), _c.c_int(bn),
+        _lib.stream_ptr())
+    _lib.check(rc, "nxd_gemm_rs_bf16")
+    return out
 
 
 def fused_gemm_ar(ctx, x2d, weight, layout="nt"):

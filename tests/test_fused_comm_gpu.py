@@ -73,5 +73,29 @@ def case_ag_gemm(rank, world):
         assert _rel(y, ref) < 6e-3, (it, _rel(y, ref))
 
 
+def case_gemm_rs(rank, world):
+    import torch.distributed as dist
+
+    from neuronx_distributed_llama3_2_b200.ops.fused_comm import fused_gemm_rs
+    from neuronx_distributed_llama3_2_b200.parallel import parallel_state as ps
+
+    ctx = ps.get_symm_mem_context("tp")
+    for it, (R, K, N, layout) in enumerate([(512, 1024, 768, "nt"), (512, 1024, 768, "nt"), (512, 1024, 768, "nt"),
+                                            (512, 512, 1024, "nn"), (256, 2048, 3072, "nt"), (512, 1024, 768, "nt")]):
+        g = torch.Generator(device="cuda").manual_seed(1000 * it + rank)
+        x = torch.randn(world * R, K, device="cuda", generator=g).bfloat16()
+        w = torch.randn((N, K) if layout == "nt" else (K, N), device="cuda", generator=g).bfloat16()
+        out = fused_gemm_rs(ctx, x, w, layout)
+        assert out is not None and out.shape == (R, N)
+        partial = x.float() @ (w.float().t() if layout == "nt" else w.float())
+        dist.all_reduce(partial)
+        ref = partial[rank * R:(rank + 1) * R]
+        assert _rel(out, ref) < 8e-3, (it, _rel(out, ref))
+
+
 def test_fused_ag_gemm_tp2():
     _spawn("case_ag_gemm", 2)
+
+
+def test_fused_gemm_rs_tp2():
+    _spawn("case_gemm_rs", 2)

@@ -69,6 +69,37 @@ def main():
         res["speedup_vs_nccl"] = res["nccl_ag_plus_gemm_ms"] / res["fused_ms"]
         if rank == 0:
             print(json.dumps(res), flush=True)
+    from neuronx_distributed_llama3_2_b200.ops.fused_comm import fused_gemm_rs
+
+    for name, K, N in [("o_proj fwd", 24 * 128 // world, H), ("down fwd", I // world, H)]:
+        x = torch.randn(S, K, device="cuda").bfloat16()
+        w = torch.randn(N, K, device="cuda").bfloat16()
+        out = torch.empty(R, N, device="cuda", dtype=torch.bfloat16)
+
+        def nccl():
+            y = gemm(x, w, "nt")
+            dist.reduce_scatter_tensor(out, y)
+
+        def gemm_only():
+            return gemm(x, w, "nt")
+
+        yfull = gemm(x, w, "nt")
+
+        def rs_only():
+            dist.reduce_scatter_tensor(out, yfull)
+
+        def fused():
+            return fused_gemm_rs(ctx, x, w, "nt")
+
+        res = {"case": name, "tp": world, "R": R, "K": K, "N": N, "gemm_plus_nccl_rs_ms": timed(nccl),
+               "gemm_only_ms": timed(gemm_only), "nccl_rs_only_ms": timed(rs_only), "fused_ms": timed(fused)}
+        bytes_out = (world - 1) * R * N * 2
+        flops = 2.0 * S * K * N
+        res["roofline_ms"] = max(flops / 1373.1e12, bytes_out / 770e9) * 1e3
+        res["fused_frac_of_roofline"] = res["roofline_ms"] / res["fused_ms"]
+        res["speedup_vs_nccl"] = res["gemm_plus_nccl_rs_ms"] / res["fused_ms"]
+        if rank == 0:
+            print(json.dumps(res), flush=True)
     ps.destroy_model_parallel()
     dist.destroy_process_group()
 
