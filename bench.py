@@ -231,7 +231,7 @@ def main():
             "model_tflops_per_gpu": flops / 1e12 / world,
             "mfu_of_measured_sustained": (flops / 1e12 / world) / peaks["bf16_tflops_sustained"]
             if peaks.get("bf16_tflops_sustained") else None,
-            "loss": float(last_loss) if last_loss is not None else None,
+            "loss": float(last_loss.detach()) if isinstance(last_loss, torch.Tensor) else last_loss,
             "clocks": clocks, "e2e": e2e, "gpu_launches": launches,
         }
         if args.layers:

@@ -84,7 +84,8 @@ __device__ __forceinline__ void bulk_s2g(void* dst, const void* src, uint32_t by
 template <typename AddrFn, typename PreFn, typename DoneFn>
 __device__ __forceinline__ void tma_stream(uint8_t* ring, uint64_t* bars, uint32_t& phases, int n_items, int sig_every,
                                            AddrFn addr, PreFn pre, DoneFn done) {
-    constexpr int kLag = 4;
+    constexpr int kLag = 4;        // store groups allowed to be incomplete before a chunk is signalled
+    constexpr int kReadLag = 4;    // store groups whose smem READ may still be pending when a buffer is refilled
     if (n_items <= 0) return;
     auto issue_load = [&](int j) {
         pre(j);
@@ -94,7 +95,10 @@ __device__ __forceinline__ void tma_stream(uint8_t* ring, uint64_t* bars, uint32
         ptx::mbar_arrive_expect_tx(&bars[b], bytes);
         bulk_g2s(ring + b * kCommSub, src, bytes, &bars[b]);
     };
-    for (int j = 0; j < min(n_items, kCommBufs); ++j) issue_load(j);
+    // loads run (kCommBufs - kReadLag) items ahead; buffer of item j is refilled only after store j has READ it,
+    // which is checked kReadLag stores later so that the issuing thread never waits on a store it just launched
+    const int ahead = kCommBufs - kReadLag;
+    for (int j = 0; j < min(n_items, ahead); ++j) issue_load(j);
     int next_signal = sig_every > 0 ? sig_every - 1 : n_items;
     for (int j = 0; j < n_items; ++j) {
         const int b = j % kCommBufs;
@@ -104,9 +108,11 @@ __device__ __forceinline__ void tma_stream(uint8_t* ring, uint64_t* bars, uint32
         addr(j, src, dst, bytes);
         bulk_s2g(dst, ring + b * kCommSub, bytes);
         ptx::bulk_commit();
-        if (j + kCommBufs < n_items) {
-            ptx::bulk_wait_read<0>();   // the store has consumed the buffer: refill it
-            issue_load(j + kCommBufs);
+        if (j + ahead < n_items) {
+            // item j + ahead reuses the buffer of item j + ahead - kCommBufs = j - kReadLag: its store is at least
+            // kReadLag groups old
+            ptx::bulk_wait_read<kReadLag>();
+            issue_load(j + ahead);
         }
         while (next_signal <= j - kLag) {
             ptx::bulk_wait<kLag>();

@@ -247,27 +247,41 @@ gemm_rs_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
             while ((int32_t)(ld_acquire_sys_u32(cnt) - want) < 0) { __nanosleep(64); }
         }
         __syncthreads();
-        // 256 rows x 64 columns: 8 consecutive threads cover one 128-byte row segment, 32 rows per pass
+        // 256 rows x 64 columns: 8 consecutive threads cover one 128-byte row segment, 32 rows per pass.  All 8 passes
+        // of one source are loaded back to back (8 independent 16-byte loads in flight per thread) before they are
+        // accumulated: the loop is latency bound otherwise.
         const int col = cg * 64 + (threadIdx.x & 7) * 8;
         if (col < N) {
-#pragma unroll 2
-            for (int pass = 0; pass < kTileM / 32; ++pass) {
-                const int row = mt * kTileM + pass * 32 + (threadIdx.x >> 3);
-                float acc8[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-                for (int s = 0; s < rs.tp; ++s) {
-                    const bf16* src = rs.stage_local + ((size_t)s * rs.R + row) * N + col;
-                    bf16x8 pk;
-                    asm volatile("ld.global.cg.v4.u32 {%0,%1,%2,%3}, [%4];"
-                                 : "=r"(reinterpret_cast<uint32_t*>(&pk)[0]), "=r"(reinterpret_cast<uint32_t*>(&pk)[1]),
-                                   "=r"(reinterpret_cast<uint32_t*>(&pk)[2]), "=r"(reinterpret_cast<uint32_t*>(&pk)[3])
-                                 : "l"(src));
-                    float f[8];
-                    unpack8(pk, f);
+            constexpr int kPasses = kTileM / 32;
+            float acc8[kPasses][8];
 #pragma unroll
-                    for (int e = 0; e < 8; ++e) acc8[e] += f[e];
+            for (int pass = 0; pass < kPasses; ++pass)
+#pragma unroll
+                for (int e = 0; e < 8; ++e) acc8[pass][e] = 0.f;
+            const int row_base = mt * kTileM + (threadIdx.x >> 3);
+            for (int s = 0; s < rs.tp; ++s) {
+                bf16x8 pk[kPasses];
+#pragma unroll
+                for (int pass = 0; pass < kPasses; ++pass) {
+                    const bf16* src = rs.stage_local + ((size_t)s * rs.R + row_base + pass * 32) * N + col;
+                    asm volatile("ld.global.cg.v4.u32 {%0,%1,%2,%3}, [%4];"
+                                 : "=r"(reinterpret_cast<uint32_t*>(&pk[pass])[0]),
+                                   "=r"(reinterpret_cast<uint32_t*>(&pk[pass])[1]),
+                                   "=r"(reinterpret_cast<uint32_t*>(&pk[pass])[2]),
+                                   "=r"(reinterpret_cast<uint32_t*>(&pk[pass])[3])
+                                 : "l"(src));
                 }
-                *reinterpret_cast<bf16x8*>(rs.out + (size_t)row * rs.ldo + col) = pack8(acc8);
+#pragma unroll
+                for (int pass = 0; pass < kPasses; ++pass) {
+                    float f[8];
+                    unpack8(pk[pass], f);
+#pragma unroll
+                    for (int e = 0; e < 8; ++e) acc8[pass][e] += f[e];
+                }
             }
+#pragma unroll
+            for (int pass = 0; pass < kPasses; ++pass)
+                *reinterpret_cast<bf16x8*>(rs.out + (size_t)(row_base + pass * 32) * rs.ldo + col) = pack8(acc8[pass]);
         }
         __syncthreads();
     }

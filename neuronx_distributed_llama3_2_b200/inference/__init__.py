@@ -1,0 +1,9 @@
+"""Inference: KV-cache model, ModelBuilder with shape-routed CUDA-graph buckets, sampler, runner (reference
+``src/neuronx_distributed/trace/__init__.py:1-7`` + ``examples/inference``)."""
+from .checkpoint_sharding import _mock_parallel_state, get_sharded_checkpoint, shard_children  # noqa: F401
+from .config import InferenceConfig  # noqa: F401
+from .kv_cache import KVCache  # noqa: F401
+from .model import LlamaInferenceModel  # noqa: F401
+from .model_builder import BaseModelInstance, ModelBuilder, NxDModel  # noqa: F401
+from .sampling import Sampler  # noqa: F401
+from .trace import parallel_model_load, parallel_model_save, parallel_model_trace  # noqa: F401

@@ -1,0 +1,189 @@
+"""Llama-3.x inference model with KV cache: context encoding + token generation.
+
+Reference: ``examples/inference/modules/model_base.py:52-518`` (``NeuronBaseModel``: KV cache as aliased graph state,
+context-encoding / token-generation branches, last-token gather, on-device sampling),
+``examples/inference/modules/attention/attention_base.py:27-200`` (prefill flash attention vs decode softmax over the
+cached + the new key), ``examples/inference/llama3/neuron_modeling_llama.py`` (Llama-3 RoPE scaling, tied lm_head).
+
+The module shares its parameter names with the training model (``models/llama.py``), so trainer checkpoints load
+unchanged.  Differences from the training forward:
+  * batch-first ``[B, T, H]`` activations, no sequence parallelism; RowParallel layers all-reduce (fused GEMM->AR
+    when the symmetric-memory context is up);
+  * context encoding (T > 1): causal flash attention over the prompt, K/V written into cache rows ``[0, T)`` of cache
+    line ``seq_ids[b]`` by the in-place KV kernel;
+  * token generation (T == 1): K/V of the new token written at ``position_ids[b]``, then the split-K decode attention
+    kernel over ``[0, position_ids[b]]`` -- the reference computes scores against the whole padded cache with a mask and
+    re-emits the cache tensor every step;
+  * logits only for the last real token of every sequence; sampling happens on device.
+"""
+from __future__ import annotations
+
+from typing import Optional, Tuple
+
+import torch
+import torch.nn as nn
+
+from ..models.llama import LlamaConfig, LlamaForCausalLM
+from ..ops import activation as act_ops
+from ..ops import attention as attn_ops
+from ..ops import norm as norm_ops
+from ..ops import rope as rope_ops
+from ..parallel import mappings
+from ..parallel import parallel_state as ps
+from .config import InferenceConfig
+from .kv_cache import KVCache
+from .sampling import Sampler
+
+
+class LlamaInferenceModel(LlamaForCausalLM):
+    def __init__(self, config: LlamaConfig, inference_config: Optional[InferenceConfig] = None, device=None):
+        config.sequence_parallel_enabled = False
+        config.activation_checkpointing = False
+        super().__init__(config, device=device)
+        self.inference_config = inference_config or InferenceConfig()
+        self.kv_cache: Optional[KVCache] = None
+        self.sampler = Sampler(self.inference_config)
+        self._rope_tables = None
+        self.eval()
+
+    # -- state -------------------------------------------------------------------------------------------------
+    def init_kv_cache(self, device=None, dtype=None) -> KVCache:
+        ic, cfg = self.inference_config, self.config
+        attn0 = self.model.layers[0].self_attn
+        device = device or next(self.parameters()).device
+        self.kv_cache = KVCache(cfg.num_hidden_layers, ic.max_batch_size, attn0.kv_heads_local, ic.seq_len, cfg.head_dim,
+                                dtype=dtype or cfg.torch_dtype, device=device, paged=ic.paged_kv, page_size=ic.page_size)
+        return self.kv_cache
+
+    def _rope(self, device) -> Tuple[torch.Tensor, torch.Tensor]:
+        if self._rope_tables is None or self._rope_tables[0].device != device:
+            cfg = self.config
+            self._rope_tables = rope_ops.build_rope_cache(self.inference_config.seq_len, cfg.head_dim, cfg.rope_theta,
+                                                          cfg.rope_scaling, device=device)
+        return self._rope_tables
+
+    # -- one decoder layer ---------------------------------------------------------------------------------------
+    def _attention(self, layer_idx: int, attn, h: torch.Tensor, positions: torch.Tensor, seq_ids: torch.Tensor,
+                   lengths: torch.Tensor, prefill: bool) -> torch.Tensor:
+        B, T, _ = h.shape
+        nq, nkv, D = attn.q_heads_local, attn.kv_heads_local, attn.head_dim
+        if self.config.fuse_qkv:
+            qkv = attn.qkv_proj(h, return_fused=True)
+        else:
+            qkv = torch.cat(attn.qkv_proj(h), dim=-1)
+        qkv = qkv.reshape(B * T, nq + 2 * nkv, D)
+        cos, sin = self._rope(h.device)
+        qkv = rope_ops.rope_inplace_(qkv.contiguous(), cos, sin, nq + nkv, positions=positions.reshape(-1))
+        qkv = qkv.reshape(B, T, nq + 2 * nkv, D)
+        q = qkv[:, :, :nq]
+        k = qkv[:, :, nq:nq + nkv]
+        v = qkv[:, :, nq + nkv:]
+        ck, cv = self.kv_cache.layer(layer_idx)
+        kw = dict(block_table=self.kv_cache.block_table, page_size=self.kv_cache.page_size) if self.kv_cache.paged else {}
+        attn_ops.kv_cache_update(ck, cv, k.permute(0, 2, 1, 3), v.permute(0, 2, 1, 3), positions[:, 0], seq_ids=seq_ids,
+                                 **kw)
+        if prefill:
+            o = attn_ops.flash_attn_func(q.permute(0, 2, 1, 3), k.permute(0, 2, 1, 3), v.permute(0, 2, 1, 3), causal=True)
+            o = o.permute(0, 2, 1, 3).reshape(B, T, nq * D)
+        else:
+            if seq_ids is not None and not self.kv_cache.paged:
+                # continuous batching: rows of the step map to arbitrary cache lines
+                ck_b, cv_b = ck.index_select(0, seq_ids.long()), cv.index_select(0, seq_ids.long())
+                o = attn_ops.decode_attention(q[:, 0].contiguous(), ck_b, cv_b, lengths)
+            elif self.kv_cache.paged:
+                table = self.kv_cache.block_table if seq_ids is None else self.kv_cache.block_table[seq_ids.long()]
+                o = attn_ops.decode_attention(q[:, 0].contiguous(), ck, cv, lengths, block_table=table,
+                                              page_size=self.kv_cache.page_size)
+            else:
+                o = attn_ops.decode_attention(q[:, 0].contiguous(), ck, cv, lengths)
+            o = o.reshape(B, 1, nq * D)
+        return attn.o_proj(o)
+
+    def _layer(self, i: int, layer, hidden, residual, positions, seq_ids, lengths, prefill):
+        eps = layer.input_layernorm.variance_epsilon
+        if residual is None:
+            residual = hidden
+            h = norm_ops.rms_norm(hidden, layer.input_layernorm.weight, eps)
+        else:
+            h, residual = norm_ops.fused_add_rms_norm(hidden, residual, layer.input_layernorm.weight, eps)
+        a = self._attention(i, layer.self_attn, h, positions, seq_ids, lengths, prefill)
+        h, residual = norm_ops.fused_add_rms_norm(a, residual, layer.post_attention_layernorm.weight, eps)
+        m = layer.mlp.down_proj(act_ops.swiglu(layer.mlp.gate_up_proj(h)))
+        return m, residual
+
+    # -- graphs ----------------------------------------------------------------------------------------------------
+    @torch.no_grad()
+    def forward_infer(self, input_ids: torch.Tensor, position_ids: torch.Tensor, seq_ids: Optional[torch.Tensor] = None,
+                      last_token_index: Optional[torch.Tensor] = None, return_logits: bool = False,
+                      uniform: Optional[torch.Tensor] = None):
+        """``input_ids [B, T]``; ``position_ids [B, T]`` absolute positions; ``seq_ids [B]`` cache lines (default
+        ``arange(B)``); ``last_token_index [B]`` index (within T) of the last real prompt token (context encoding with
+        right padding).  Returns sampled tokens ``[B]`` (and the ``[B, V]`` logits with ``return_logits``)."""
+        assert self.kv_cache is not None, "call init_kv_cache() first"
+        B, T = input_ids.shape
+        prefill = T > 1
+        default_lines = seq_ids is None
+        hidden = self._embed(input_ids)
+        lengths = (position_ids[:, -1] + 1).to(torch.int32)
+        residual = None
+        sid = None if (default_lines and not prefill) else (
+            seq_ids if seq_ids is not None else torch.arange(B, device=input_ids.device, dtype=torch.int32))
+        for i, layer in enumerate(self.model.layers):
+            hidden, residual = self._layer(i, layer, hidden, residual, position_ids, sid, lengths, prefill)
+        if prefill:
+            idx = last_token_index if last_token_index is not None else torch.full((B,), T - 1, device=hidden.device)
+            rows = torch.arange(B, device=hidden.device)
+            hidden, residual = hidden[rows, idx.long()], residual[rows, idx.long()]
+        else:
+            hidden, residual = hidden[:, 0], residual[:, 0]
+        hidden, _ = norm_ops.fused_add_rms_norm(hidden.contiguous(), residual.contiguous(), self.model.norm.weight,
+                                                self.model.norm.variance_epsilon)
+        logits = self.lm_head(hidden)                                   # [B, V/tp]
+        logits = mappings.gather_from_tensor_model_parallel_region(logits)[:, : self.config.vocab_size]
+        tokens = self.sampler.sample(logits.float() if logits.dtype not in (torch.float32, torch.bfloat16) else logits,
+                                     uniform)
+        return (tokens, logits) if return_logits else tokens
+
+    def _embed(self, input_ids: torch.Tensor) -> torch.Tensor:
+        emb = self.model.embed_tokens
+        tp = ps.get_tensor_model_parallel_size()
+        w = emb.weight
+        if tp > 1:
+            mask = (input_ids < emb.start_index) | (input_ids >= emb.end_index)
+            local = (input_ids - emb.start_index).masked_fill(mask, 0)
+            out = nn.functional.embedding(local, w).masked_fill(mask.unsqueeze(-1), 0.0)
+            return mappings.reduce_from_tensor_model_parallel_region(out)
+        return nn.functional.embedding(input_ids, w)
+
+    # -- simple generation loop (the runner adds batching / bucketing / CUDA graphs on top) ---------------------------
+    @torch.no_grad()
+    def generate(self, input_ids: torch.Tensor, attention_mask: Optional[torch.Tensor] = None, max_new_tokens: int = 16,
+                 eos_token_id: Optional[int] = None) -> torch.Tensor:
+        """Greedy / sampled continuation of right-padded prompts ``[B, T]``; returns ``[B, T + max_new_tokens]``."""
+        B, T = input_ids.shape
+        dev = input_ids.device
+        if self.kv_cache is None:
+            self.init_kv_cache(device=dev)
+        if attention_mask is None:
+            attention_mask = torch.ones_like(input_ids)
+        lens = attention_mask.sum(dim=1).to(torch.long)
+        pos = torch.arange(T, device=dev).unsqueeze(0).expand(B, T)
+        tok = self.forward_infer(input_ids, pos, last_token_index=lens - 1)
+        out = [tok]
+        cur = lens.clone()
+        finished = torch.zeros(B, dtype=torch.bool, device=dev)
+        for _ in range(max_new_tokens - 1):
+            if eos_token_id is not None:
+                finished |= tok == eos_token_id
+                if bool(finished.all()):
+                    break
+            tok = self.forward_infer(tok.reshape(B, 1), cur.reshape(B, 1))
+            cur = cur + 1
+            out.append(tok)
+        gen = torch.stack(out, dim=1)
+        res = torch.full((B, T + gen.shape[1]), self.inference_config.pad_token_id, dtype=input_ids.dtype, device=dev)
+        for b in range(B):
+            L = int(lens[b])
+            res[b, :L] = input_ids[b, :L]
+            res[b, L:L + gen.shape[1]] = gen[b]
+        return res

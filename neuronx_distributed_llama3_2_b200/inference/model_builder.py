@@ -1,0 +1,194 @@
+"""Ahead-of-time inference builder: shape-routed, bucketed, CUDA-graph-captured execution.
+
+Reference: ``src/neuronx_distributed/trace/model_builder.py:37-586`` and ``trace/spmd.py:9-187``: ``ModelBuilder.add()``
+registers a model instance with example inputs per bucket, ``trace()`` spawns ``tp`` processes, emits one HLO per
+(key, bucket), compiles NEFFs (propagating the priority model's weight layout through HLO surgery,
+``hlo_utils.py``), and assembles an ``NxDModel`` that routes a call by its input-shape string to the right bucket;
+weights are shared across graphs, state (KV cache) is aliased; ``shard_checkpoint`` writes
+``tp{rank}_sharded_checkpoint.safetensors``.
+
+On B200 the same surface maps to:
+  * one process per GPU (the caller's torchrun), no spawn; "compile" = capture a CUDA graph of the module's forward for
+    every (key, bucket) with static input buffers -- NCCL collectives and our ctypes-launched kernels are all
+    stream-ordered and capturable; on CPU (tests) the graph is the eager callable;
+  * weight-layout optimisation / HLO surgery has no counterpart: the tcgen05 kernels read row-major weights through
+    UMMA descriptor major bits, so there is nothing to transform;
+  * state aliasing is real aliasing: the KV cache tensors live in the module and are updated in place.
+"""
+from __future__ import annotations
+
+import os
+from typing import Any, Callable, Dict, List, Optional, Sequence, Tuple, Union
+
+import torch
+
+from ..parallel import parallel_state as ps
+from ..utils.logger import get_logger
+from .checkpoint_sharding import _mock_parallel_state, get_sharded_checkpoint
+
+logger = get_logger()
+
+
+class BaseModelInstance:
+    """How to build the module for one sub-model (reference ``model_builder.py:37-47``)."""
+
+    def __init__(self, module_cls: Callable[[], torch.nn.Module], input_output_aliases: Optional[Dict] = None):
+        self.module_cls = module_cls
+        self.module: Optional[torch.nn.Module] = None
+        self.input_output_aliases = input_output_aliases or {}
+
+    def load_module(self) -> None:
+        self.module = self.module_cls()
+
+    def get(self, bucket_rank: int, **kwargs) -> Tuple[torch.nn.Module, Dict]:
+        return self.module, self.input_output_aliases
+
+
+def _shape_key(args: Sequence[torch.Tensor]) -> str:
+    return "|".join(f"{tuple(a.shape)}:{str(a.dtype).replace('torch.', '')}" for a in args)
+
+
+class _Bucket:
+    """One (key, bucket) executable: static inputs + (optionally) a captured CUDA graph."""
+
+    def __init__(self, fn: Callable, example_inputs: Tuple[torch.Tensor, ...], use_graph: bool):
+        self.fn = fn
+        self.static_in = [t.clone() for t in example_inputs]
+        self.graph: Optional[torch.cuda.CUDAGraph] = None
+        self.static_out = None
+        self.use_graph = use_graph and all(t.is_cuda for t in example_inputs)
+
+    def capture(self) -> None:
+        if not self.use_graph:
+            return
+        s = torch.cuda.Stream()
+        s.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(s):
+            for _ in range(2):   # warm-up outside capture (allocator, lazy inits, symmetric-memory setup)
+                self.fn(*self.static_in)
+        torch.cuda.current_stream().wait_stream(s)
+        torch.cuda.synchronize()
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph):
+            self.static_out = self.fn(*self.static_in)
+
+    def __call__(self, *args: torch.Tensor):
+        if self.graph is None:
+            return self.fn(*args)
+        for dst, src in zip(self.static_in, args):
+            dst.copy_(src, non_blocking=True)
+        self.graph.replay()
+        return self.static_out
+
+
+class NxDModel(torch.nn.Module):
+    """Routes a call by input shapes to a compiled bucket (reference ``spmd.py:82-175``)."""
+
+    def __init__(self, buckets: Dict[str, Dict[str, _Bucket]], modules: Dict[str, torch.nn.Module]):
+        super().__init__()
+        self._buckets = buckets
+        self.models = torch.nn.ModuleDict(modules)
+        self._route: Dict[str, Tuple[str, _Bucket]] = {}
+        for key, bs in buckets.items():
+            for shape_key, b in bs.items():
+                self._route[shape_key] = (key, b)
+        self.weights_initialized = True
+
+    def router(self, args: Sequence[torch.Tensor]) -> Tuple[str, _Bucket]:
+        k = _shape_key(args)
+        if k not in self._route:
+            raise RuntimeError(f"no compiled bucket for input shapes {k}; have {list(self._route)}")
+        return self._route[k]
+
+    def initialize(self, state_dict: Dict[str, torch.Tensor], strict: bool = False) -> None:
+        """Load (already sharded) weights; they are shared by every graph of a key."""
+        for m in self.models.values():
+            m.load_state_dict(state_dict, strict=strict)
+
+    def forward(self, *args: torch.Tensor):
+        _, bucket = self.router(args)
+        return bucket(*args)
+
+    def keys(self) -> List[str]:
+        return list(self._buckets)
+
+
+class ModelBuilder:
+    def __init__(self, router=None, tp_degree: int = 1, checkpoint_loader: Optional[Callable[[], Dict[str, Any]]] = None,
+                 compiler_workdir: Optional[str] = None, debug: bool = False, use_cuda_graphs: bool = True):
+        self.router = router
+        self.tp_degree = tp_degree
+        self.checkpoint_loader = checkpoint_loader
+        self.compiler_workdir = compiler_workdir
+        self.debug = debug
+        self.use_cuda_graphs = use_cuda_graphs
+        self.model_collection: Dict[str, Dict[str, Any]] = {}
+
+    def add(self, key: str, model_instance: BaseModelInstance, example_inputs: List[Tuple[torch.Tensor, ...]],
+            compiler_args: Union[str, List[str], None] = None, bucket_config=None,
+            priority_model_idx: Optional[int] = None) -> "ModelBuilder":
+        """Register a sub-model; ``example_inputs`` holds one tuple of example tensors per bucket."""
+        if key in self.model_collection:
+            raise ValueError(f"model key {key!r} already added")
+        self.model_collection[key] = {"instance": model_instance, "example_inputs": list(example_inputs),
+                                      "compiler_args": compiler_args, "bucket_config": bucket_config,
+                                      "priority_model_idx": priority_model_idx}
+        return self
+
+    def trace(self, tp_degree: Optional[int] = None, initialize_model_weights: bool = True) -> NxDModel:
+        """Build every module on this rank's device and capture one executable per (key, bucket)."""
+        tp = tp_degree or self.tp_degree
+        have = ps.get_tensor_model_parallel_size()
+        if have != tp:
+            raise RuntimeError(f"ModelBuilder(tp_degree={tp}) but the process group has tp={have}: launch one process per "
+                               "GPU (torchrun) and call initialize_model_parallel first")
+        buckets: Dict[str, Dict[str, _Bucket]] = {}
+        modules: Dict[str, torch.nn.Module] = {}
+        weights = None
+        if initialize_model_weights and self.checkpoint_loader is not None:
+            full = self.checkpoint_loader()
+            weights = full
+        # priority model first (kept for parity with the reference's compile order)
+        order = sorted(self.model_collection, key=lambda k: self.model_collection[k]["priority_model_idx"] is None)
+        for key in order:
+            entry = self.model_collection[key]
+            inst: BaseModelInstance = entry["instance"]
+            if inst.module is None:
+                inst.load_module()
+            module = inst.module
+            if weights is not None:
+                shard = get_sharded_checkpoint(weights, module, ps.get_tensor_model_parallel_rank(), tp)
+                module.load_state_dict(shard, strict=False)
+            modules[key] = module
+            buckets[key] = {}
+            for rank_idx, ex in enumerate(entry["example_inputs"]):
+                mod, _aliases = inst.get(rank_idx)
+                b = _Bucket(mod, tuple(ex), self.use_cuda_graphs)
+                b.capture()
+                buckets[key][_shape_key(ex)] = b
+        return NxDModel(buckets, modules)
+
+    def shard_checkpoint(self, serialize_path: str) -> None:
+        """Write ``tp{rank}_sharded_checkpoint.safetensors`` for every TP rank from the un-sharded checkpoint; runs in
+        a single process with mocked parallel state and meta-device modules (reference ``:263-331``)."""
+        from safetensors.torch import save_file
+
+        assert self.checkpoint_loader is not None, "shard_checkpoint needs a checkpoint_loader"
+        os.makedirs(serialize_path, exist_ok=True)
+        full = self.checkpoint_loader()
+        for rank in range(self.tp_degree):
+            merged: Dict[str, torch.Tensor] = {}
+            with _mock_parallel_state(self.tp_degree, rank):
+                for key, entry in self.model_collection.items():
+                    inst: BaseModelInstance = entry["instance"]
+                    with torch.device("meta"):
+                        module = inst.module_cls()
+                    merged.update(get_sharded_checkpoint(full, module, rank, self.tp_degree))
+            tensors = {k: v.contiguous() for k, v in merged.items() if isinstance(v, torch.Tensor)}
+            # safetensors refuses aliased storage (tied lm_head / embedding): materialise copies
+            seen = {}
+            for k, v in list(tensors.items()):
+                if v.data_ptr() in seen:
+                    tensors[k] = v.clone()
+                seen[v.data_ptr()] = k
+            save_file(tensors, os.path.join(serialize_path, f"tp{rank}_sharded_checkpoint.safetensors"))

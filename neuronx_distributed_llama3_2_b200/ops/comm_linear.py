@@ -42,7 +42,7 @@ def _fused_ctx(x: torch.Tensor, group):
     """Symmetric-memory context for the fused kernels, or None."""
     if not x.is_cuda or group is not None:
         return None
-    if os.environ.get("NXD_FUSED_COMM", "0") != "1":
+    if os.environ.get("NXD_FUSED_COMM", "1") != "1":
         return None
     if x.dtype != torch.bfloat16:
         return None

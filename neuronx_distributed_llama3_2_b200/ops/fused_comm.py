@@ -95,7 +95,7 @@ def fused_gemm_rs(ctx, x2d: torch.Tensor, weight: torch.Tensor, layout: str = "n
     rc = _lib.lib().nxd_gemm_rs_bf16(
         _c.c_int(_LAYOUT[layout]), _lib.ptr(x2d), _lib.ptr(weight), _lib.ptr(out), _c.c_int(R), _c.c_int(N), _c.c_int(K),
         _c.c_longlong(x2d.stride(0)), _c.c_longlong(weight.stride(0)), _c.c_longlong(out.stride(0)), s["stages"][key],
-        s["sigs"], _c.c_int(tp), _c.c_int(ctx.rank), _c.c_int(s["cnt"]), _c.c_uint((epoch + 1) // 2), _c.c_int(bn),
+        s["sigs"], _c.c_int(tp), _c.c_int(ctx.rank), _c.c_int(s["cnt"]), _c.c_uint(epoch), _c.c_int(bn),
         _lib.stream_ptr())
     _lib.check(rc, "nxd_gemm_rs_bf16")
     return out
