@@ -144,6 +144,11 @@ class LlamaInferenceModel(LlamaForCausalLM):
                                      uniform)
         return (tokens, logits) if return_logits else tokens
 
+    def forward(self, input_ids: torch.Tensor, position_ids: torch.Tensor, seq_ids: Optional[torch.Tensor] = None,
+                last_token_index: Optional[torch.Tensor] = None):
+        """Calling the inference model runs one graph: context encoding (T > 1) or token generation (T == 1)."""
+        return self.forward_infer(input_ids, position_ids, seq_ids, last_token_index)
+
     def _embed(self, input_ids: torch.Tensor) -> torch.Tensor:
         emb = self.model.embed_tokens
         tp = ps.get_tensor_model_parallel_size()
