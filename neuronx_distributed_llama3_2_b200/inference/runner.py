@@ -1,0 +1,172 @@
+"""``InferenceRunner``: build (trace) the two graphs, generate, check accuracy, benchmark (SURVEY C53, §3.4-3.5;
+reference ``examples/inference/runner.py:36-655`` and ``modules/model_wrapper.py:60-301``).
+
+Sub-models as in the reference: ``context_encoding_model`` (bucketed prompt lengths, produces the first token = TTFT)
+and ``token_generation_model`` (one token per call).  Both are buckets of ONE module sharing weights and KV cache;
+each bucket is a CUDA graph.  Prompts are right-padded to the bucket length, batches padded to the compiled batch.
+"""
+from __future__ import annotations
+
+import json
+import os
+from typing import Dict, List, Optional
+
+import torch
+
+from ..models.llama import LlamaConfig
+from ..parallel import parallel_state as ps
+from .benchmark import LatencyCollector, generate_report
+from .config import InferenceConfig
+from .model import LlamaInferenceModel
+from .model_builder import BaseModelInstance, ModelBuilder, NxDModel
+
+CONTEXT_ENCODING_MODEL = "context_encoding_model"
+TOKEN_GENERATION_MODEL = "token_generation_model"
+
+
+class InferenceRunner:
+    def __init__(self, model_config: LlamaConfig, inference_config: InferenceConfig, checkpoint_loader=None, device=None):
+        self.model_config = model_config
+        self.config = inference_config
+        self.checkpoint_loader = checkpoint_loader
+        self.device = device or (torch.device("cuda", torch.cuda.current_device()) if torch.cuda.is_available()
+                                 else torch.device("cpu"))
+        self.model: Optional[LlamaInferenceModel] = None
+        self.nxd_model: Optional[NxDModel] = None
+
+    # -- build --------------------------------------------------------------------------------------------------------
+    def _make_module(self) -> LlamaInferenceModel:
+        if torch.empty(0).device.type == "meta":   # shard_checkpoint builds shape-only replicas under torch.device("meta")
+            return LlamaInferenceModel(self.model_config, self.config, device="meta")
+        m = LlamaInferenceModel(self.model_config, self.config, device=self.device)
+        m.init_kv_cache(device=self.device)
+        self.model = m
+        return m
+
+    def trace(self, traced_model_path: Optional[str] = None) -> NxDModel:
+        """Compile both sub-models (reference ``runner.trace`` -> ``model.compile`` -> ``ModelBuilder.trace``) and,
+        when a path is given, write the per-rank sharded checkpoint + configs next to it."""
+        ic = self.config
+        builder = ModelBuilder(tp_degree=ic.tp_degree, checkpoint_loader=self.checkpoint_loader,
+                               use_cuda_graphs=ic.use_cuda_graphs and self.device.type == "cuda")
+        inst = BaseModelInstance(self._make_module)
+        dev = self.device
+
+        def ex(b, t):
+            return (torch.zeros(b, t, dtype=torch.long, device=dev), torch.zeros(b, t, dtype=torch.long, device=dev),
+                    torch.arange(b, dtype=torch.int32, device=dev), torch.zeros(b, dtype=torch.long, device=dev))
+
+        builder.add(CONTEXT_ENCODING_MODEL, inst, [ex(ic.ctx_batch_size, t) for t in ic.context_buckets()],
+                    priority_model_idx=0)
+        builder.add(TOKEN_GENERATION_MODEL, inst, [ex(ic.tkg_batch_size, 1)])
+        self.nxd_model = builder.trace(initialize_model_weights=self.checkpoint_loader is not None)
+        if traced_model_path:
+            os.makedirs(traced_model_path, exist_ok=True)
+            with open(os.path.join(traced_model_path, "config.json"), "w") as f:
+                json.dump({"model": self.model_config.to_dict(), "inference": self.config.__dict__}, f, indent=1,
+                          default=str)
+            if self.checkpoint_loader is not None and ps.is_global_rank_zero():
+                builder.shard_checkpoint(os.path.join(traced_model_path, "weights"))
+        return self.nxd_model
+
+    # -- generate -------------------------------------------------------------------------------------------------------
+    def _bucket_len(self, n: int) -> int:
+        for b in self.config.context_buckets():
+            if n <= b:
+                return b
+        raise ValueError(f"prompt length {n} exceeds max_context_length {self.config.max_context_length}")
+
+    @torch.no_grad()
+    def generate(self, input_ids: torch.Tensor, attention_mask: Optional[torch.Tensor] = None,
+                 max_new_tokens: Optional[int] = None, collectors: Optional[Dict[str, LatencyCollector]] = None
+                 ) -> torch.Tensor:
+        """Right-padded prompts ``[B, T]`` (B <= compiled batch) -> ``[B, T + new]`` token ids."""
+        assert self.nxd_model is not None, "call trace() first"
+        ic, dev = self.config, self.device
+        max_new = max_new_tokens or ic.max_new_tokens
+        B, T = input_ids.shape
+        if attention_mask is None:
+            attention_mask = torch.ones_like(input_ids)
+        lens = attention_mask.sum(dim=1).to(torch.long)
+        Tb = self._bucket_len(T)
+        Bc = ic.ctx_batch_size
+        ids = torch.full((Bc, Tb), ic.pad_token_id, dtype=torch.long, device=dev)
+        ids[:B, :T] = input_ids.to(dev)
+        pos = torch.arange(Tb, device=dev).unsqueeze(0).expand(Bc, Tb).contiguous()
+        last = torch.zeros(Bc, dtype=torch.long, device=dev)
+        last[:B] = lens.to(dev) - 1
+        seq = torch.arange(Bc, dtype=torch.int32, device=dev)
+        cte = collectors.get(CONTEXT_ENCODING_MODEL) if collectors else None
+        tkg = collectors.get(TOKEN_GENERATION_MODEL) if collectors else None
+        if cte:
+            cte.pre_hook()
+        tok = self.nxd_model(ids, pos, seq, last).clone()
+        if cte:
+            cte.hook()
+        outs = [tok[:B]]
+        cur = torch.zeros(ic.tkg_batch_size, dtype=torch.long, device=dev)
+        cur[:B] = lens.to(dev)
+        step_ids = torch.zeros(ic.tkg_batch_size, 1, dtype=torch.long, device=dev)
+        seq_t = torch.arange(ic.tkg_batch_size, dtype=torch.int32, device=dev)
+        zero_last = torch.zeros(ic.tkg_batch_size, dtype=torch.long, device=dev)
+        finished = torch.zeros(B, dtype=torch.bool, device=dev)
+        for _ in range(max_new - 1):
+            if ic.eos_token_id is not None:
+                finished |= outs[-1] == ic.eos_token_id
+                if bool(finished.all()):
+                    break
+            step_ids[:B, 0] = outs[-1]
+            if tkg:
+                tkg.pre_hook()
+            tok = self.nxd_model(step_ids, cur.reshape(-1, 1), seq_t, zero_last).clone()
+            if tkg:
+                tkg.hook()
+            cur = cur + 1
+            outs.append(tok[:B])
+        gen = torch.stack(outs, dim=1)
+        res = torch.full((B, T + gen.shape[1]), ic.pad_token_id, dtype=torch.long, device=dev)
+        for b in range(B):
+            L = int(lens[b])
+            res[b, :L] = input_ids[b, :L]
+            res[b, L:L + gen.shape[1]] = gen[b]
+        return res
+
+    # -- checks / benchmark ------------------------------------------------------------------------------------------------
+    @torch.no_grad()
+    def check_accuracy_logits(self, reference_model, input_ids: torch.Tensor, atol: float = 5e-2) -> bool:
+        """Compare prefill logits against a reference causal LM returning ``[S, B, V]`` logits (the training model) --
+        the reference runner compares against HF on CPU (``runner.py:313-409``)."""
+        B, T = input_ids.shape
+        pos = torch.arange(T, device=input_ids.device).unsqueeze(0).expand(B, T)
+        _, logits = self.model.forward_infer(input_ids, pos, return_logits=True)
+        ref = reference_model(input_ids).transpose(0, 1)[:, -1]
+        return bool((logits.float() - ref.float()).abs().max() <= atol)
+
+    def benchmark_sampling(self, prompt_len: Optional[int] = None, new_tokens: Optional[int] = None, n_runs: int = 20,
+                           warmup: int = 1) -> Dict:
+        """1 warm-up + ``n_runs`` timed ``generate`` calls; e2e, context-encoding (TTFT) and token-generation reports
+        (reference ``runner.py:460-535``)."""
+        ic = self.config
+        T = prompt_len or ic.max_context_length
+        new = new_tokens or ic.max_new_tokens
+        ids = torch.randint(1, self.model_config.vocab_size, (ic.ctx_batch_size, T), device=self.device)
+        for _ in range(warmup):
+            self.generate(ids, max_new_tokens=new)
+        e2e = LatencyCollector()
+        cols = {CONTEXT_ENCODING_MODEL: LatencyCollector(), TOKEN_GENERATION_MODEL: LatencyCollector()}
+        for _ in range(n_runs):
+            e2e.pre_hook()
+            self.generate(ids, max_new_tokens=new, collectors=cols)
+            e2e.hook()
+        e2e.finish()
+        for c in cols.values():
+            c.finish()
+        total_len = T + new
+        report = {"e2e_model": generate_report(e2e.latency_list, total_len, ic.ctx_batch_size, n_runs),
+                  CONTEXT_ENCODING_MODEL: generate_report(cols[CONTEXT_ENCODING_MODEL].latency_list, T, ic.ctx_batch_size,
+                                                          n_runs),
+                  TOKEN_GENERATION_MODEL: generate_report(cols[TOKEN_GENERATION_MODEL].latency_list, 1, ic.tkg_batch_size,
+                                                          len(cols[TOKEN_GENERATION_MODEL].latency_list))}
+        report["ttft_ms_p50"] = report[CONTEXT_ENCODING_MODEL]["latency_ms_p50"]
+        report["decode_tokens_per_s"] = report[TOKEN_GENERATION_MODEL]["throughput"]
+        return report

@@ -125,3 +125,32 @@ def test_model_builder_routes_by_shape_and_shards_checkpoint():
             meta = LlamaForCausalLM(tiny_llama(sequence_parallel_enabled=False))
         s1 = get_sharded_checkpoint(full_sd, meta, 1, 2)
     torch.testing.assert_close(s1["model.embed_tokens.weight"], full_sd["model.embed_tokens.weight"].chunk(2, 0)[1])
+
+
+def test_runner_generate_buckets_and_benchmark_report():
+    from neuronx_distributed_llama3_2_b200.inference import InferenceRunner
+
+    cfg, train, _ = _models()
+    sd = {k: v.clone() for k, v in train.state_dict().items()}
+    ic = InferenceConfig(batch_size=2, max_context_length=64, seq_len=128, buckets=[16, 64], max_new_tokens=5,
+                         use_cuda_graphs=False)
+    runner = InferenceRunner(tiny_llama(sequence_parallel_enabled=False), ic, checkpoint_loader=lambda: sd,
+                             device=torch.device("cpu"))
+    with tempfile.TemporaryDirectory() as d:
+        runner.trace(d)
+        assert os.path.exists(os.path.join(d, "weights", "tp0_sharded_checkpoint.safetensors"))
+        assert os.path.exists(os.path.join(d, "config.json"))
+    prompts = torch.randint(1, cfg.vocab_size, (2, 20))       # length 20 -> padded to the 64 bucket
+    mask = torch.ones_like(prompts)
+    mask[0, 13:] = 0
+    out = runner.generate(prompts, mask, max_new_tokens=5)
+    for b in range(2):
+        L = int(mask[b].sum())
+        seq = prompts[b, :L].clone()
+        for _ in range(5):
+            seq = torch.cat([seq, _full_logits(train, seq.unsqueeze(0))[0, -1].argmax().reshape(1)])
+        assert torch.equal(out[b, :L + 5], seq)
+    assert runner.check_accuracy_logits(train, prompts[:, :16], atol=1e-3)
+    rep = runner.benchmark_sampling(prompt_len=16, new_tokens=4, n_runs=2)
+    assert rep["ttft_ms_p50"] > 0 and rep["decode_tokens_per_s"] > 0
+    assert set(rep["e2e_model"]) >= {"latency_ms_p50", "latency_ms_p99", "throughput"}
