@@ -1,0 +1,87 @@
+"""ZeRO-1 over a real DP group (gloo): parity with un-sharded AdamW + clipping, checkpoint conversion between DP sizes,
+DCP save/load (reference ``test/integration/zero1/test_zero1.py``, ``convert_checkpoints/run_zero1_test.sh``,
+``zero1_dcp/test_zero1_dcp.py``)."""
+from __future__ import annotations
+
+import os
+import tempfile
+
+import torch
+
+from conftest import run_distributed
+
+
+def _net(seed=0):
+    torch.manual_seed(seed)
+    return torch.nn.Sequential(torch.nn.Linear(24, 40), torch.nn.Tanh(), torch.nn.Linear(40, 8))
+
+
+def _dp_worker(rank, world, tmp):
+    import torch.distributed as dist
+
+    from neuronx_distributed_llama3_2_b200 import trainer as nxd
+    from neuronx_distributed_llama3_2_b200.optimizer import NeuronZero1Optimizer, convert_zero_checkpoints as czc
+    from neuronx_distributed_llama3_2_b200.parallel import parallel_state as ps
+
+    cfg = nxd.neuronx_distributed_config(optimizer_config={"zero_one_enabled": True, "grad_clipping": True,
+                                                           "max_grad_norm": 0.5})
+    assert ps.get_data_parallel_size() == world
+    model = nxd.initialize_parallel_model(cfg, _net, device=torch.device("cpu"))
+    opt = nxd.initialize_parallel_optimizer(cfg, torch.optim.AdamW, model.parameters(), lr=1e-2, weight_decay=0.05)
+    assert isinstance(opt.optimizer, NeuronZero1Optimizer) and opt.optimizer.buckets[0].dp == world
+    ref = _net()
+    ref_opt = torch.optim.AdamW(ref.parameters(), lr=1e-2, weight_decay=0.05)
+    g = torch.Generator().manual_seed(5)
+    for step in range(4):
+        xs = torch.randn(world, 6, 24, generator=g)
+        ys = torch.randn(world, 6, 8, generator=g)
+        opt.zero_grad()
+        ((model(xs[rank]) - ys[rank]) ** 2).mean().backward()
+        opt.step()
+        ref_opt.zero_grad()
+        sum(((ref(xs[r]) - ys[r]) ** 2).mean() for r in range(world)).div(world).backward()
+        norm = torch.nn.utils.clip_grad_norm_(ref.parameters(), 0.5)
+        ref_opt.step()
+        assert abs(float(opt.grad_norm) - float(norm)) < 1e-4 * max(1.0, float(norm))
+        for p, q in zip(model.parameters(), ref.parameters()):
+            torch.testing.assert_close(p, q, atol=1e-5, rtol=1e-4)
+
+    # sharded save -> convert to full -> re-shard to another DP size -> merge again: identical tensors
+    d = os.path.join(tmp, "ck")
+    nxd.save_checkpoint(d, "t", model=model, optimizer=opt)
+    optim_dir = os.path.join(d, "t", "optim")
+    assert os.path.exists(os.path.join(optim_dir, f"dp_rank_{rank:02d}_tp_rank_00_pp_rank_00.pt"))
+    if rank == 0:
+        czc.convert(optim_dir, os.path.join(tmp, "full"), convert_to_full=True, num_workers=1)
+        full = torch.load(os.path.join(tmp, "full", "dp_rank_00_tp_rank_00_pp_rank_00.pt"), weights_only=False)
+        w0 = dict(ref.named_parameters())["0.weight"]
+        torch.testing.assert_close(full["base_state"][0], w0.detach(), atol=1e-5, rtol=1e-4)
+        assert full["state"][0]["exp_avg"].shape == w0.shape
+        czc.convert(os.path.join(tmp, "full"), os.path.join(tmp, "dp3"), convert_to_sharded=True, dp_size=3, num_workers=1)
+        shards = [torch.load(os.path.join(tmp, "dp3", f"dp_rank_{r:02d}_tp_rank_00_pp_rank_00.pt"), weights_only=False)
+                  for r in range(3)]
+        again = czc.merge_shards(shards)
+        for i in full["base_state"]:
+            assert torch.equal(again["base_state"][i], full["base_state"][i])
+            assert torch.equal(again["state"][i]["exp_avg_sq"], full["state"][i]["exp_avg_sq"])
+    dist.barrier()
+
+    # DCP variant: one optim/ directory with .metadata, every rank's tensors under rank-suffixed names
+    d2 = os.path.join(tmp, "ck_dcp")
+    before = opt.state_dict()
+    nxd.save_checkpoint(d2, "t", model=model, optimizer=opt, use_zero1_dcp=True)
+    assert os.path.exists(os.path.join(d2, "t", "optim", ".metadata"))
+    for b in opt.optimizer.buckets:
+        b.master.zero_()
+        b.exp_avg.zero_()
+    nxd.load_checkpoint(d2, "t", model=model, optimizer=opt, use_zero1_dcp=True)
+    after = opt.state_dict()
+    for i in before["base_state"]:
+        assert torch.equal(before["base_state"][i], after["base_state"][i])
+        if i in before["state"]:
+            assert torch.equal(before["state"][i]["exp_avg"], after["state"][i]["exp_avg"])
+
+
+def test_zero1_dp2_parity_convert_and_dcp():
+    with tempfile.TemporaryDirectory() as tmp:
+        run_distributed(_dp_worker, 2, tmp)
