@@ -1,0 +1,264 @@
+"""HF / Megatron-style FULL checkpoint <-> NxD (tp, pp)-sharded checkpoint (reference
+``src/neuronx_distributed/scripts/checkpoint_converter.py:22-739``).
+
+Direction ``convert_from_full_state``: HF names -> our model names, q/k/v fused into ``qkv_proj.weight_qkv`` (KV heads
+replicated ``kv_size_multiplier`` times, Q heads / o_proj columns re-ordered so that every TP rank's query heads sit
+next to the KV head it holds), gate/up fused into the stride-2 ``gate_up_proj``; then sliced per TP rank by
+``partition_dim`` and distributed over PP stages (even split, remainder to later stages), and written as
+``<out>/model/dp_rank_00_tp_rank_TT_pp_rank_PP.pt`` (optionally xser).  ``convert_to_full_state`` is the inverse.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import re
+from typing import Any, Dict, List, Optional, Tuple
+
+import torch
+
+from ..pipeline.partition import create_partitions
+from ..utils import xser
+
+# name -> partition dim of the TP-sharded parameters of the Llama family (reference ``:22-46``)
+PARTITION_DIMS = {
+    "embed_tokens.weight": 0, "lm_head.weight": 0, "qkv_proj.weight_qkv": 0, "qkv_proj.weight_q": 0,
+    "qkv_proj.weight_k": 0, "qkv_proj.weight_v": 0, "o_proj.weight": 1, "gate_up_proj.weight": 0, "down_proj.weight": 1,
+}
+
+
+def q_head_permutation(n_q: int, n_kv: int, tp: int, kv_mult: int) -> List[int]:
+    """Order of the query heads such that a contiguous TP split gives rank ``r`` the query heads that attend with KV
+    head ``r % n_kv`` -- the head its K/V shard holds after tiling the KV heads ``kv_mult`` times.  Identity when no
+    replication is needed."""
+    if kv_mult == 1:
+        return list(range(n_q))
+    g = n_q // n_kv
+    per = g // kv_mult
+    order: List[int] = []
+    ranks_per_head = tp // (n_kv * kv_mult) if tp >= n_kv * kv_mult else 1
+    for r in range(n_kv * kv_mult):
+        h, j = r % n_kv, r // n_kv
+        order += list(range(h * g + j * per, h * g + (j + 1) * per))
+    assert sorted(order) == list(range(n_q)) and ranks_per_head >= 1
+    return order
+
+
+class CheckpointConverterBase:
+    def __init__(self, num_layers: int, num_heads: int, num_kv_heads: int, head_dim: int, tp_size: int = 1,
+                 pp_size: int = 1, kv_size_multiplier: int = 1, fuse_qkv: bool = True, tie_word_embeddings: bool = True):
+        self.L, self.nq, self.nkv, self.D = num_layers, num_heads, num_kv_heads, head_dim
+        self.tp, self.pp, self.m = tp_size, pp_size, kv_size_multiplier
+        self.fuse_qkv, self.tied = fuse_qkv, tie_word_embeddings
+
+    # -- name maps -------------------------------------------------------------------------------------------------
+    def hf_to_nxd_full(self, hf: Dict[str, torch.Tensor]) -> Dict[str, torch.Tensor]:
+        """HF-named full state -> our names, still un-sharded (QKV / gate-up fused, heads permuted for KV replication)."""
+        out: Dict[str, torch.Tensor] = {}
+        perm = q_head_permutation(self.nq, self.nkv, self.tp, self.m)
+        rows = torch.tensor([h * self.D + d for h in perm for d in range(self.D)])
+        for k, v in hf.items():
+            m = re.match(r"(model\.layers\.\d+\.)self_attn\.([qkvo])_proj\.weight$", k)
+            if m:
+                continue
+            m = re.match(r"(model\.layers\.\d+\.)mlp\.(gate|up)_proj\.weight$", k)
+            if m:
+                continue
+            out[k] = v
+        for i in range(self.L):
+            p = f"model.layers.{i}."
+            q, k_, v_, o = (hf[p + f"self_attn.{n}_proj.weight"] for n in "qkvo")
+            q = q[rows]
+            o = o[:, rows]
+            if self.fuse_qkv:
+                out[p + "self_attn.qkv_proj.weight_qkv"] = torch.cat([q, k_, v_], dim=0)
+            else:
+                out[p + "self_attn.qkv_proj.weight_q"], out[p + "self_attn.qkv_proj.weight_k"] = q, k_
+                out[p + "self_attn.qkv_proj.weight_v"] = v_
+            out[p + "self_attn.o_proj.weight"] = o
+            out[p + "mlp.gate_up_proj.weight"] = torch.cat([hf[p + "mlp.gate_proj.weight"], hf[p + "mlp.up_proj.weight"]], 0)
+        if self.tied and "lm_head.weight" not in out and "model.embed_tokens.weight" in out:
+            out["lm_head.weight"] = out["model.embed_tokens.weight"]
+        return out
+
+    def nxd_full_to_hf(self, full: Dict[str, torch.Tensor]) -> Dict[str, torch.Tensor]:
+        out: Dict[str, torch.Tensor] = {}
+        perm = q_head_permutation(self.nq, self.nkv, self.tp, self.m)
+        inv = [0] * len(perm)
+        for new, old in enumerate(perm):
+            inv[old] = new
+        rows = torch.tensor([h * self.D + d for h in inv for d in range(self.D)])
+        qs, kvs = self.nq * self.D, self.nkv * self.D
+        for k, v in full.items():
+            if k.endswith("qkv_proj.weight_qkv"):
+                p = k[: -len("qkv_proj.weight_qkv")]
+                q, k_, v_ = torch.split(v, [qs, kvs, kvs], dim=0)
+                out[p + "q_proj.weight"], out[p + "k_proj.weight"], out[p + "v_proj.weight"] = q[rows], k_, v_
+            elif k.endswith("qkv_proj.weight_q"):
+                out[k.replace("qkv_proj.weight_q", "q_proj.weight")] = v[rows]
+            elif k.endswith("qkv_proj.weight_k"):
+                out[k.replace("qkv_proj.weight_k", "k_proj.weight")] = v
+            elif k.endswith("qkv_proj.weight_v"):
+                out[k.replace("qkv_proj.weight_v", "v_proj.weight")] = v
+            elif k.endswith("o_proj.weight"):
+                out[k] = v[:, rows]
+            elif k.endswith("gate_up_proj.weight"):
+                g, u = v.chunk(2, dim=0)
+                out[k.replace("gate_up_proj", "gate_proj")], out[k.replace("gate_up_proj", "up_proj")] = g, u
+            else:
+                out[k] = v
+        if self.tied:
+            out.pop("lm_head.weight", None)
+        return out
+
+    # -- sharding ------------------------------------------------------------------------------------------------
+    def _partition_dim(self, name: str) -> Optional[int]:
+        for suffix, dim in PARTITION_DIMS.items():
+            if name.endswith(suffix):
+                return dim
+        return None
+
+    def shard_tp(self, full: Dict[str, torch.Tensor], rank: int) -> Dict[str, torch.Tensor]:
+        out = {}
+        qs, kvs = self.nq * self.D, self.nkv * self.D
+        for k, v in full.items():
+            dim = self._partition_dim(k)
+            if dim is None:
+                out[k] = v
+            elif k.endswith("weight_qkv"):
+                q, k_, v_ = torch.split(v, [qs, kvs, kvs], dim=0)
+                rep = [self.m] + [1] * (v.dim() - 1)
+                out[k] = torch.cat([q.chunk(self.tp, 0)[rank], k_.repeat(*rep).chunk(self.tp, 0)[rank],
+                                    v_.repeat(*rep).chunk(self.tp, 0)[rank]], dim=0).contiguous()
+            elif k.endswith("weight_k") or k.endswith("weight_v"):
+                out[k] = v.repeat(self.m, 1).chunk(self.tp, 0)[rank].contiguous()
+            elif k.endswith("gate_up_proj.weight"):
+                g, u = v.chunk(2, dim=0)
+                out[k] = torch.cat([g.chunk(self.tp, 0)[rank], u.chunk(self.tp, 0)[rank]], dim=0).contiguous()
+            else:
+                out[k] = v.chunk(self.tp, dim)[rank].contiguous()
+        return out
+
+    def merge_tp(self, shards: List[Dict[str, torch.Tensor]]) -> Dict[str, torch.Tensor]:
+        out = {}
+        for k in shards[0]:
+            dim = self._partition_dim(k)
+            vs = [s[k] for s in shards]
+            if dim is None:
+                out[k] = vs[0]
+            elif k.endswith("weight_qkv"):
+                q_sz = self.nq * self.D // self.tp
+                kv_sz = self.nkv * self.D * self.m // self.tp
+                parts = [torch.split(v, [q_sz, kv_sz, kv_sz], dim=0) for v in vs]
+                q = torch.cat([p[0] for p in parts], 0)
+                k_ = torch.cat([p[1] for p in parts], 0)[: self.nkv * self.D]   # drop the replicas
+                v_ = torch.cat([p[2] for p in parts], 0)[: self.nkv * self.D]
+                out[k] = torch.cat([q, k_, v_], 0)
+            elif k.endswith("weight_k") or k.endswith("weight_v"):
+                out[k] = torch.cat(vs, 0)[: self.nkv * self.D]
+            elif k.endswith("gate_up_proj.weight"):
+                gs, us = zip(*[v.chunk(2, 0) for v in vs])
+                out[k] = torch.cat(list(gs) + list(us), 0)
+            else:
+                out[k] = torch.cat(vs, dim)
+        return out
+
+    def stage_of_key(self, key: str) -> List[int]:
+        """PP stage(s) that own ``key`` (tied embedding lives on the first AND the last stage)."""
+        if self.pp == 1:
+            return [0]
+        cuts = create_partitions(self.pp, self.L)
+        m = re.match(r"model\.layers\.(\d+)\.", key)
+        if m:
+            layer = int(m.group(1))
+            for s, c in enumerate(cuts):
+                if layer <= c:
+                    return [s]
+            return [self.pp - 1]
+        if key.startswith("model.embed_tokens"):
+            return [0]
+        return [self.pp - 1]
+
+    # -- directory level -----------------------------------------------------------------------------------------
+    @staticmethod
+    def shard_file(out_dir: str, tp: int, pp: int, ep: Optional[int] = None) -> str:
+        ep_s = f"_ep_rank_{ep:02d}" if ep is not None else ""
+        return os.path.join(out_dir, "model", f"dp_rank_00{ep_s}_tp_rank_{tp:02d}_pp_rank_{pp:02d}.pt")
+
+    def convert_from_full_state(self, hf_state: Dict[str, torch.Tensor], out_dir: str, use_xser: bool = False) -> None:
+        full = self.hf_to_nxd_full(hf_state)
+        os.makedirs(os.path.join(out_dir, "model"), exist_ok=True)
+        for t in range(self.tp):
+            shard = self.shard_tp(full, t)
+            for s in range(self.pp):
+                part = {k: v for k, v in shard.items() if s in self.stage_of_key(k)}
+                if self.tied and self.pp > 1 and s == self.pp - 1 and "lm_head.weight" not in part:
+                    part["lm_head.weight"] = shard["model.embed_tokens.weight"]
+                path = self.shard_file(out_dir, t, s)
+                if use_xser:
+                    xser.save(part, path)
+                else:
+                    torch.save(part, path)
+        for marker in ("checkpoint", "done"):
+            open(os.path.join(out_dir, marker), "w").write("1")
+
+    def convert_to_full_state(self, in_dir: str, load_xser: Optional[bool] = None) -> Dict[str, torch.Tensor]:
+        merged_stages: Dict[str, torch.Tensor] = {}
+        for s in range(self.pp):
+            shards = []
+            for t in range(self.tp):
+                path = self.shard_file(in_dir, t, s)
+                is_x = os.path.isdir(path + ".tensors") if load_xser is None else load_xser
+                shards.append(xser.load(path) if is_x else torch.load(path, map_location="cpu", weights_only=False))
+            merged_stages.update(self.merge_tp(shards))
+        return self.nxd_full_to_hf(merged_stages)
+
+    # -- CLI -------------------------------------------------------------------------------------------------------
+    @staticmethod
+    def get_arg_parser() -> argparse.ArgumentParser:
+        ap = argparse.ArgumentParser("nxd checkpoint converter")
+        ap.add_argument("--input_dir", required=True)
+        ap.add_argument("--output_dir", required=True)
+        ap.add_argument("--config", required=True, help="json with num_hidden_layers / num_attention_heads / ...")
+        ap.add_argument("--tp_size", type=int, default=1)
+        ap.add_argument("--pp_size", type=int, default=1)
+        ap.add_argument("--kv_size_multiplier", type=int, default=1)
+        ap.add_argument("--qkv_linear", type=lambda s: s.lower() != "false", default=True)
+        ap.add_argument("--convert_from_full_state", action="store_true")
+        ap.add_argument("--convert_to_full_state", action="store_true")
+        ap.add_argument("--load_xser", action="store_true")
+        ap.add_argument("--save_xser", action="store_true")
+        return ap
+
+    @classmethod
+    def run(cls, argv=None) -> None:
+        a = cls.get_arg_parser().parse_args(argv)
+        cfg = json.load(open(a.config))
+        heads = cfg["num_attention_heads"]
+        conv = cls(cfg["num_hidden_layers"], heads, cfg.get("num_key_value_heads", heads),
+                   cfg.get("head_dim", cfg["hidden_size"] // heads), a.tp_size, a.pp_size, a.kv_size_multiplier,
+                   tie_word_embeddings=cfg.get("tie_word_embeddings", False))
+        if a.convert_from_full_state:
+            path = a.input_dir
+            if os.path.isdir(path):
+                from safetensors.torch import load_file
+
+                state: Dict[str, Any] = {}
+                for f in sorted(os.listdir(path)):
+                    if f.endswith(".safetensors"):
+                        state.update(load_file(os.path.join(path, f)))
+                    elif f.endswith(".bin") or f.endswith(".pt"):
+                        state.update(torch.load(os.path.join(path, f), map_location="cpu", weights_only=False))
+            else:
+                state = torch.load(path, map_location="cpu", weights_only=False)
+            conv.convert_from_full_state(state, a.output_dir, use_xser=a.save_xser)
+        elif a.convert_to_full_state:
+            full = conv.convert_to_full_state(a.input_dir, load_xser=a.load_xser or None)
+            os.makedirs(a.output_dir, exist_ok=True)
+            torch.save(full, os.path.join(a.output_dir, "checkpoint.pt"))
+        else:
+            raise SystemExit("pass --convert_from_full_state or --convert_to_full_state")
+
+
+if __name__ == "__main__":
+    CheckpointConverterBase.run()

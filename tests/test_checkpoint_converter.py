@@ -1,0 +1,115 @@
+"""HF-named full checkpoint <-> (tp, pp)-sharded NxD checkpoint round trips, incl. KV-head replication and the match with
+what the parallel model itself would hold (reference ``scripts/checkpoint_converter.py`` behaviour)."""
+from __future__ import annotations
+
+import os
+import tempfile
+
+import torch
+
+from neuronx_distributed_llama3_2_b200.scripts.checkpoint_converter import CheckpointConverterBase, q_head_permutation
+
+
+def _hf_state(L=4, H=64, nq=8, nkv=2, D=8, I=96, V=50, tied=True):
+    torch.manual_seed(0)
+    sd = {"model.embed_tokens.weight": torch.randn(V, H), "model.norm.weight": torch.randn(H)}
+    for i in range(L):
+        p = f"model.layers.{i}."
+        sd[p + "self_attn.q_proj.weight"] = torch.randn(nq * D, H)
+        sd[p + "self_attn.k_proj.weight"] = torch.randn(nkv * D, H)
+        sd[p + "self_attn.v_proj.weight"] = torch.randn(nkv * D, H)
+        sd[p + "self_attn.o_proj.weight"] = torch.randn(H, nq * D)
+        sd[p + "mlp.gate_proj.weight"] = torch.randn(I, H)
+        sd[p + "mlp.up_proj.weight"] = torch.randn(I, H)
+        sd[p + "mlp.down_proj.weight"] = torch.randn(H, I)
+        sd[p + "input_layernorm.weight"] = torch.randn(H)
+        sd[p + "post_attention_layernorm.weight"] = torch.randn(H)
+    if not tied:
+        sd["lm_head.weight"] = torch.randn(V, H)
+    return sd
+
+
+def test_round_trip_tp2_pp2_xser_and_plain():
+    hf = _hf_state()
+    for use_xser in (False, True):
+        conv = CheckpointConverterBase(4, 8, 2, 8, tp_size=2, pp_size=2, tie_word_embeddings=True)
+        with tempfile.TemporaryDirectory() as d:
+            conv.convert_from_full_state(hf, d, use_xser=use_xser)
+            for t in range(2):
+                for s in range(2):
+                    assert os.path.exists(os.path.join(d, "model", f"dp_rank_00_tp_rank_{t:02d}_pp_rank_{s:02d}.pt"))
+            first = torch.load(os.path.join(d, "model", "dp_rank_00_tp_rank_00_pp_rank_00.pt"), weights_only=False) \
+                if not use_xser else None
+            if first is not None:
+                assert "model.embed_tokens.weight" in first and "model.layers.0.mlp.gate_up_proj.weight" in first
+                assert "model.layers.3.mlp.down_proj.weight" not in first and "model.norm.weight" not in first
+                assert first["model.layers.0.self_attn.qkv_proj.weight_qkv"].shape == ((8 + 2 + 2) * 8 // 2, 64)
+            back = conv.convert_to_full_state(d)
+        assert set(back) == set(hf)
+        for k in hf:
+            assert torch.equal(back[k], hf[k]), k
+
+
+def test_kv_replication_permutation_and_round_trip():
+    # 2 KV heads, tp = 4 -> every KV head is replicated twice; rank r holds KV head r % 2
+    perm = q_head_permutation(n_q=8, n_kv=2, tp=4, kv_mult=2)
+    assert perm == [0, 1, 4, 5, 2, 3, 6, 7]      # rank0: q0,q1 (kv0)  rank1: q4,q5 (kv1)  rank2: q2,q3 (kv0)  rank3: q6,q7
+    hf = _hf_state(tied=False)
+    conv = CheckpointConverterBase(4, 8, 2, 8, tp_size=4, pp_size=1, kv_size_multiplier=2, tie_word_embeddings=False)
+    full = conv.hf_to_nxd_full(hf)
+    r1 = conv.shard_tp(full, 1)
+    qkv = r1["model.layers.0.self_attn.qkv_proj.weight_qkv"]
+    assert qkv.shape[0] == (2 + 1 + 1) * 8
+    torch.testing.assert_close(qkv[:16], hf["model.layers.0.self_attn.q_proj.weight"][4 * 8:6 * 8])   # q heads 4, 5
+    torch.testing.assert_close(qkv[16:24], hf["model.layers.0.self_attn.k_proj.weight"][8:16])        # kv head 1
+    with tempfile.TemporaryDirectory() as d:
+        conv.convert_from_full_state(hf, d)
+        back = conv.convert_to_full_state(d)
+    for k in hf:
+        assert torch.equal(back[k], hf[k]), k
+
+
+def test_converted_shards_load_into_parallel_model():
+    """A converted tp=1 checkpoint loads into our Llama and reproduces a plain-PyTorch Llama forward on the HF weights."""
+    from neuronx_distributed_llama3_2_b200.models import LlamaForCausalLM, tiny_llama
+
+    cfg = tiny_llama(sequence_parallel_enabled=False)
+    hf = _hf_state(L=cfg.num_hidden_layers, H=cfg.hidden_size, nq=cfg.num_attention_heads, nkv=cfg.num_key_value_heads,
+                   D=cfg.head_dim, I=cfg.intermediate_size, V=cfg.vocab_size)
+    hf = {k: v * 0.05 if v.dim() == 2 else 1 + 0.1 * v for k, v in hf.items()}
+    conv = CheckpointConverterBase(cfg.num_hidden_layers, cfg.num_attention_heads, cfg.num_key_value_heads, cfg.head_dim)
+    model = LlamaForCausalLM(cfg)
+    model.load_state_dict(conv.shard_tp(conv.hf_to_nxd_full(hf), 0))
+    ids = torch.randint(0, cfg.vocab_size, (1, 10))
+    logits = model(ids)[:, 0]                                   # [S, V]
+
+    def rms(x, w):
+        return x * torch.rsqrt(x.pow(2).mean(-1, keepdim=True) + cfg.rms_norm_eps) * w
+
+    from neuronx_distributed_llama3_2_b200.ops.rope import build_rope_cache
+
+    cos, sin = build_rope_cache(10, cfg.head_dim, cfg.rope_theta, cfg.rope_scaling)
+
+    def rope(x):                                                # [S, heads, D]
+        x1, x2 = x[..., : cfg.head_dim // 2], x[..., cfg.head_dim // 2:]
+        c, s = cos[:, None], sin[:, None]
+        return torch.cat([x1 * c - x2 * s, x2 * c + x1 * s], -1)
+
+    h = hf["model.embed_tokens.weight"][ids[0]]
+    for i in range(cfg.num_hidden_layers):
+        p = f"model.layers.{i}."
+        x = rms(h, hf[p + "input_layernorm.weight"])
+        q = rope((x @ hf[p + "self_attn.q_proj.weight"].t()).view(10, cfg.num_attention_heads, cfg.head_dim))
+        k = rope((x @ hf[p + "self_attn.k_proj.weight"].t()).view(10, cfg.num_key_value_heads, cfg.head_dim))
+        v = (x @ hf[p + "self_attn.v_proj.weight"].t()).view(10, cfg.num_key_value_heads, cfg.head_dim)
+        g = cfg.num_attention_heads // cfg.num_key_value_heads
+        k, v = k.repeat_interleave(g, 1), v.repeat_interleave(g, 1)
+        s = torch.einsum("shd,thd->hst", q, k) / cfg.head_dim ** 0.5
+        s = s.masked_fill(~torch.ones(10, 10, dtype=torch.bool).tril(), float("-inf"))
+        o = torch.einsum("hst,thd->shd", torch.softmax(s, -1), v).reshape(10, -1)
+        h = h + o @ hf[p + "self_attn.o_proj.weight"].t()
+        x = rms(h, hf[p + "post_attention_layernorm.weight"])
+        h = h + (torch.nn.functional.silu(x @ hf[p + "mlp.gate_proj.weight"].t()) * (x @ hf[p + "mlp.up_proj.weight"].t())) \
+            @ hf[p + "mlp.down_proj.weight"].t()
+    ref = rms(h, hf["model.norm.weight"]) @ hf["model.embed_tokens.weight"].t()
+    torch.testing.assert_close(logits, ref, atol=2e-4, rtol=1e-3)
