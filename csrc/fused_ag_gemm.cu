@@ -7,19 +7,20 @@
 //
 //   Y[tp*R, N] = concat_r(X_r)[tp*R, K] * W_op        X_r = rank r's [R, K] shard (bf16), W local
 //
-//   * every rank publishes its shard in a small symmetric (peer-mapped, CUDA-IPC) slot and raises a flag on every
-//     peer's signal pad (st.release.sys through NVLink);
+//   * the gathered buffer X_total lives in symmetric (peer-mapped, CUDA-IPC) memory on every rank;
 //   * a few "communication clusters" of the grid (default 6 of 74 CTA pairs) run no MMA at all: one thread per CTA
-//     drives the TMA engine -- cp.async.bulk from the PEER's HBM into shared memory, cp.async.bulk out to the local
-//     gathered buffer X_total -- slab after slab in ring order (rank+1, rank+2, ...), and bumps a per-256-row
-//     counter when a chunk has landed;
+//     drives the TMA engine -- cp.async.bulk of a 16 KB piece of the LOCAL shard into shared memory, then one
+//     cp.async.bulk store of that piece into EVERY peer's X_total over NVLink (posted writes: bandwidth bound, no
+//     round trip; an earlier pull version was limited by bytes-in-flight x NVLink latency) -- and, once the stores of
+//     a 256-row chunk have landed, bumps that chunk's counter on every peer's signal pad (red.release.sys);
 //   * the remaining clusters are the persistent tcgen05 GEMM of gemm_tcgen05.cu.  Their tile order follows the
 //     arrival order (own slab first, read straight from the local shard), and the TMA producer polls the chunk
 //     counter (ld.acquire.gpu) before it loads A tiles of a remote slab.  Math on slab d overlaps the transfer of
 //     slab d+1; the gathered X_total is a by-product kept for the weight-gradient GEMM.
 //
-// Buffer reuse needs no extra barrier: slots and flags are double-buffered / epoch-stamped, and rank A cannot finish
-// call n+1 before rank B entered call n+1 (it needs B's flag), i.e. before B finished reading slot n.
+// Buffer reuse needs no extra barrier: X_total is double-buffered, counters are epoch-stamped, and rank A cannot
+// finish call n+1 before rank B entered call n+1 (A needs B's rows of that call), i.e. before B finished with the
+// buffer of call n, which is the one A's call n+2 will write.
 #include "common.cuh"
 #include "gemm_tcgen05.cuh"
 #include "ptx.cuh"
@@ -33,18 +34,24 @@ constexpr int kCommBufs = 12;            // smem ring of the copy engine (192 KB
 
 struct AgArgs {
     const bf16* x_local;          // [R, K] this rank's shard, dense
-    bf16* x_total;                // [tp*R, K] gathered activations (local, ordinary allocation)
-    bf16* slot_local;             // this rank's symmetric shard slot for this call (peers read it)
-    const bf16* slot_peer[kMaxTp];  // peers' slots (peer-mapped addresses); [rank] unused
+    bf16* xt_peer[kMaxTp];        // every rank's X_total [tp*R, K] for this call (peer-mapped; [rank] = local)
     uint32_t* sig_local;          // local signal pad
     uint32_t* sig_peer[kMaxTp];   // peers' signal pads
-    int slot_ready;               // flag index: ready[src]            (tp entries)
-    int slot_chunks;              // flag index: chunk counters        (tp * chunks_per_slab entries)
-    int slot_own;                 // flag index: own-slab publish counter (1 entry)
+    int slot_chunks;              // flag index: chunk counters [src][chunk]   (tp * chunks_per_slab entries)
     int tp, rank, R;
     int comm_ctas;
     uint32_t epoch;
+    unsigned long long* trace;    // optional: globaltimer stamps of a few events (debug)
 };
+
+__device__ __forceinline__ unsigned long long gtime() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+__device__ __forceinline__ void red_release_sys_add_u32(uint32_t* p, uint32_t v) {
+    asm volatile("red.release.sys.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
 
 __device__ __forceinline__ uint32_t ld_acquire_gpu(const uint32_t* p) {
     uint32_t v;
@@ -77,26 +84,23 @@ __device__ __forceinline__ void bulk_s2g(void* dst, const void* src, uint32_t by
                  : "memory");
 }
 
-// One continuous stream of <= 16 KB TMA copies (global -> smem ring -> global), driven by ONE thread.  Loads run
-// kCommBufs items ahead of the stores.  addr(j, src, dst, bytes) describes item j; pre(j) runs before item j's load is
-// issued (flag waits); done(j) is called for every item with (j + 1) % sig_every == 0 once its store (and all older
-// ones) has fully landed -- kLag store groups later, so the pipe never drains between signals.
-template <typename AddrFn, typename PreFn, typename DoneFn>
+// One continuous stream of <= 16 KB TMA copies (global -> smem ring -> global), driven by ONE thread.  src(j, ptr,
+// bytes) describes item j; store(j, smem, bytes) issues its bulk store(s); done(j) is called for every item with
+// (j + 1) % sig_every == 0 once its stores (and all older ones) have fully landed -- kLag store groups later, so the
+// pipe never drains between signals.  Loads run (kCommBufs - kReadLag) items ahead of the stores.
+template <typename SrcFn, typename StoreFn, typename DoneFn>
 __device__ __forceinline__ void tma_stream(uint8_t* ring, uint64_t* bars, uint32_t& phases, int n_items, int sig_every,
-                                           AddrFn addr, PreFn pre, DoneFn done) {
+                                           SrcFn src, StoreFn store, DoneFn done) {
     constexpr int kLag = 4;        // store groups allowed to be incomplete before a chunk is signalled
     constexpr int kReadLag = 4;    // store groups whose smem READ may still be pending when a buffer is refilled
     if (n_items <= 0) return;
     auto issue_load = [&](int j) {
-        pre(j);
-        const uint8_t* src; uint8_t* dst; uint32_t bytes;
-        addr(j, src, dst, bytes);
+        const uint8_t* p; uint32_t bytes;
+        src(j, p, bytes);
         const int b = j % kCommBufs;
         ptx::mbar_arrive_expect_tx(&bars[b], bytes);
-        bulk_g2s(ring + b * kCommSub, src, bytes, &bars[b]);
+        bulk_g2s(ring + b * kCommSub, p, bytes, &bars[b]);
     };
-    // loads run (kCommBufs - kReadLag) items ahead; buffer of item j is refilled only after store j has READ it,
-    // which is checked kReadLag stores later so that the issuing thread never waits on a store it just launched
     const int ahead = kCommBufs - kReadLag;
     for (int j = 0; j < min(n_items, ahead); ++j) issue_load(j);
     int next_signal = sig_every > 0 ? sig_every - 1 : n_items;
@@ -104,14 +108,12 @@ __device__ __forceinline__ void tma_stream(uint8_t* ring, uint64_t* bars, uint32
         const int b = j % kCommBufs;
         ptx::mbar_wait(&bars[b], (phases >> b) & 1u);
         phases ^= (1u << b);
-        const uint8_t* src; uint8_t* dst; uint32_t bytes;
-        addr(j, src, dst, bytes);
-        bulk_s2g(dst, ring + b * kCommSub, bytes);
+        const uint8_t* p; uint32_t bytes;
+        src(j, p, bytes);
+        store(j, ring + b * kCommSub, bytes);
         ptx::bulk_commit();
         if (j + ahead < n_items) {
-            // item j + ahead reuses the buffer of item j + ahead - kCommBufs = j - kReadLag: its store is at least
-            // kReadLag groups old
-            ptx::bulk_wait_read<kReadLag>();
+            ptx::bulk_wait_read<kReadLag>();   // the buffer about to be refilled was stored >= kReadLag groups ago
             issue_load(j + ahead);
         }
         while (next_signal <= j - kLag) {
@@ -120,7 +122,7 @@ __device__ __forceinline__ void tma_stream(uint8_t* ring, uint64_t* bars, uint32
             next_signal += sig_every;
         }
     }
-    ptx::bulk_wait<0>();   // every byte is in global memory
+    ptx::bulk_wait<0>();   // every byte is in global memory (local and peers)
     while (next_signal < n_items) {
         done(next_signal);
         next_signal += sig_every;
@@ -154,77 +156,41 @@ ag_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a_local, const __grid_co
         for (int i = 0; i < kCommBufs; ++i) ptx::mbar_init(&bars[i], 1);
         ptx::fence_barrier_init();
         uint32_t phases = 0;
-        // per-chunk piece of this CTA: bytes [p0, p1) of every 256-row chunk
+        // per-chunk piece of this CTA: bytes [p0, p1) of every 256-row chunk of the LOCAL shard
         const size_t chunk_bytes = (size_t)kChunkRows * K * 2;
         const size_t piece = ((chunk_bytes / ag.comm_ctas) + 15) & ~size_t(15);
         const size_t p0 = min((size_t)cid * piece, chunk_bytes);
         const size_t p1 = min(p0 + piece, chunk_bytes);
         const int ipp = p1 > p0 ? (int)((p1 - p0 + kCommSub - 1) / kCommSub) : 0;      // items per piece
-        const int items_per_slab = ipp * chunks_per_slab;
-        auto local_off = [&](int rem, size_t& off, uint32_t& bytes) {   // rem = item index inside a slab
-            const int c = rem / ipp, i = rem % ipp;
-            off = (size_t)c * chunk_bytes + p0 + (size_t)i * kCommSub;
-            bytes = (uint32_t)min((size_t)kCommSub, p1 - p0 - (size_t)i * kCommSub);
-        };
-        auto nop_pre = [](int) {};
-        auto nop_done = [](int) {};
-        // 1. publish the own shard in the symmetric slot (one un-interrupted stream), then raise the flag on every peer
-        tma_stream(smem, bars, phases, items_per_slab, 0,
-                   [&](int j, const uint8_t*& src, uint8_t*& dst, uint32_t& bytes) {
-                       size_t off;
-                       local_off(j, off, bytes);
-                       src = reinterpret_cast<const uint8_t*>(ag.x_local) + off;
-                       dst = reinterpret_cast<uint8_t*>(ag.slot_local) + off;
-                   },
-                   nop_pre, nop_done);
-        fence_proxy_async_all();
-        __threadfence_system();
-        const uint32_t done_cnt = atom_add_release_gpu(ag.sig_local + ag.slot_own, 1u) + 1u;
-        if (done_cnt == ag.epoch * (uint32_t)ag.comm_ctas) {
+        if (ag.trace && cid == 0) ag.trace[0] = gtime();
+        auto bump = [&](int c) {   // this CTA's piece of chunk c of MY shard has landed everywhere
+            fence_proxy_async_all();
             __threadfence_system();
             for (int d = 1; d < ag.tp; ++d) {
                 const int peer = (ag.rank + d) % ag.tp;
-                st_release_sys(ag.sig_peer[peer] + ag.slot_ready + ag.rank, ag.epoch);
+                red_release_sys_add_u32(ag.sig_peer[peer] + ag.slot_chunks + ag.rank * chunks_per_slab + c, 1u);
             }
-        }
-        // 2. pull the peers' shards in ring order; a chunk's counter is bumped when this CTA's piece of it has landed
-        auto count_chunk = [&](int srank, int c) {
-            fence_proxy_async_all();
-            __threadfence();
-            atom_add_release_gpu(ag.sig_local + ag.slot_chunks + srank * chunks_per_slab + c, 1u);
         };
         if (ipp == 0) {  // more copy CTAs than 16-byte pieces: nothing to move, but the counters expect every CTA
-            for (int d = 1; d < ag.tp; ++d)
-                for (int c = 0; c < chunks_per_slab; ++c) count_chunk((ag.rank + d) % ag.tp, c);
+            for (int c = 0; c < chunks_per_slab; ++c) bump(c);
         }
-        tma_stream(smem, bars, phases, items_per_slab * (ag.tp - 1), ipp,
-                   [&](int j, const uint8_t*& src, uint8_t*& dst, uint32_t& bytes) {
-                       const int srank = (ag.rank + j / items_per_slab + 1) % ag.tp;
-                       size_t off;
-                       local_off(j % items_per_slab, off, bytes);
-                       src = reinterpret_cast<const uint8_t*>(ag.slot_peer[srank]) + off;
-                       dst = reinterpret_cast<uint8_t*>(ag.x_total) + (size_t)srank * slab_bytes + off;
+        tma_stream(smem, bars, phases, ipp * chunks_per_slab, ipp,
+                   [&](int j, const uint8_t*& src, uint32_t& bytes) {
+                       const int c = j / ipp, i = j % ipp;
+                       bytes = (uint32_t)min((size_t)kCommSub, p1 - p0 - (size_t)i * kCommSub);
+                       src = reinterpret_cast<const uint8_t*>(ag.x_local) + (size_t)c * chunk_bytes + p0 + (size_t)i * kCommSub;
                    },
-                   [&](int j) {
-                       if (j % items_per_slab == 0) {  // first touch of a new peer: its shard must be published
-                           const int srank = (ag.rank + j / items_per_slab + 1) % ag.tp;
-                           const uint32_t* flag = ag.sig_local + ag.slot_ready + srank;
-                           while ((int32_t)(ld_acquire_sys(flag) - ag.epoch) < 0) { __nanosleep(64); }
-                           fence_proxy_async_all();
+                   [&](int j, const uint8_t* sm, uint32_t bytes) {
+                       const int c = j / ipp, i = j % ipp;
+                       const size_t off = (size_t)ag.rank * slab_bytes + (size_t)c * chunk_bytes + p0 + (size_t)i * kCommSub;
+                       // ring order: every rank starts with a different peer, so no link is a hot spot
+                       for (int d = 1; d <= ag.tp; ++d) {
+                           const int peer = (ag.rank + d) % ag.tp;   // d == tp: own X_total (by-product for wgrad)
+                           bulk_s2g(reinterpret_cast<uint8_t*>(ag.xt_peer[peer]) + off, sm, bytes);
                        }
                    },
-                   [&](int j_last) {
-                       count_chunk((ag.rank + j_last / items_per_slab + 1) % ag.tp, (j_last % items_per_slab) / ipp);
-                   });
-        // 3. by-product for the weight-gradient GEMM: own rows of X_total (nobody waits for this)
-        tma_stream(smem, bars, phases, items_per_slab, 0,
-                   [&](int j, const uint8_t*& src, uint8_t*& dst, uint32_t& bytes) {
-                       size_t off;
-                       local_off(j, off, bytes);
-                       src = reinterpret_cast<const uint8_t*>(ag.x_local) + off;
-                       dst = reinterpret_cast<uint8_t*>(ag.x_total) + (size_t)ag.rank * slab_bytes + off;
-                   },
-                   nop_pre, nop_done);
+                   [&](int j_last) { bump(j_last / ipp); });
+        if (ag.trace && cid == 0) ag.trace[1] = gtime();
         return;
     }
 
@@ -281,10 +247,14 @@ ag_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a_local, const __grid_co
                 tile_coords_ag(tile, slab, mt, tn);
                 const bool own = slab == ag.rank;
                 if (!own) {
-                    // wait until every copy CTA delivered its piece of this 256-row chunk
+                    // wait until every copy CTA of the SOURCE rank delivered its piece of this 256-row chunk
                     const uint32_t* cnt = ag.sig_local + ag.slot_chunks + slab * chunks_per_slab + mt;
                     const uint32_t want = ag.epoch * (uint32_t)ag.comm_ctas;
-                    while ((int32_t)(ld_acquire_gpu(cnt) - want) < 0) { __nanosleep(32); }
+                    const bool tr = ag.trace && cluster_id == 0 && is_leader;
+                    if (tr && ag.trace[8] == 0) ag.trace[8] = gtime();
+                    while ((int32_t)(ld_acquire_sys(cnt) - want) < 0) { __nanosleep(32); }
+                    if (tr && ag.trace[9] == 0) ag.trace[9] = gtime();
+                    if (tr) ag.trace[10] = gtime();
                     fence_proxy_async_all();
                 }
                 const CUtensorMap* ma = own ? &tmap_a_local : &tmap_a_total;
@@ -393,16 +363,18 @@ ag_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a_local, const __grid_co
     ptx::tcgen05_fence_before();
     ptx::cluster_sync();
     if (warp == 2) ptx::tmem_dealloc<2>(tmem_base, L::kTmemCols);
+    if (ag.trace && cluster_id == 0 && is_leader && threadIdx.x == 0) ag.trace[11] = gtime();
 }
 
 }  // namespace nxd_gemm
 
-// layout 0 "nt": W = [N, K];  1 "nn": W = [K, N].  x_local [R, K] dense, x_total [tp*R, K] dense, y [tp*R, N] (pitch ldy).
-// slot_ptrs / sig_ptrs: HOST arrays of tp device pointers (own entry included).  R % 256 == 0, K % 64 == 0, N % 8 == 0.
-NXD_API int nxd_ag_gemm_bf16(int layout, const void* x_local, void* x_total, const void* w, void* y, int R, int N, int K,
-                             long long ldw, long long ldy, const void* const* slot_ptrs, void* const* sig_ptrs, int tp,
-                             int rank, int slot_ready, int slot_chunks, int slot_own, unsigned epoch, int comm_ctas,
-                             int block_n, void* stream) {
+// layout 0 "nt": W = [N, K];  1 "nn": W = [K, N].  x_local [R, K] dense, y [tp*R, N] (pitch ldy).
+// xt_ptrs / sig_ptrs: HOST arrays of tp device pointers (own entry included): every rank's symmetric X_total buffer
+// [tp*R, K] for this call, and signal pad.  R % 256 == 0, K % 64 == 0, N % 8 == 0.  trace: optional 16 x u64 (device).
+NXD_API int nxd_ag_gemm_bf16(int layout, const void* x_local, const void* w, void* y, int R, int N, int K,
+                             long long ldw, long long ldy, void* const* xt_ptrs, void* const* sig_ptrs, int tp,
+                             int rank, int slot_chunks, unsigned epoch, int comm_ctas, int block_n, void* trace,
+                             void* stream) {
     using namespace nxd_gemm;
     NXD_REQUIRE(layout == 0 || layout == 1, "ag_gemm: layout must be 0 (nt) or 1 (nn)");
     NXD_REQUIRE(tp >= 2 && tp <= kMaxTp && rank >= 0 && rank < tp, "ag_gemm: bad tp/rank %d/%d", tp, rank);
@@ -414,19 +386,18 @@ NXD_API int nxd_ag_gemm_bf16(int layout, const void* x_local, void* x_total, con
     NXD_REQUIRE(bn == 128 || bn == 256, "ag_gemm: block_n must be 128 or 256");
     AgArgs ag{};
     ag.x_local = (const bf16*)x_local;
-    ag.x_total = (bf16*)x_total;
     for (int r = 0; r < tp; ++r) {
-        ag.slot_peer[r] = (const bf16*)slot_ptrs[r];
+        ag.xt_peer[r] = (bf16*)xt_ptrs[r];
         ag.sig_peer[r] = (uint32_t*)sig_ptrs[r];
     }
-    ag.slot_local = (bf16*)const_cast<void*>(slot_ptrs[rank]);
     ag.sig_local = (uint32_t*)sig_ptrs[rank];
-    ag.slot_ready = slot_ready; ag.slot_chunks = slot_chunks; ag.slot_own = slot_own;
+    ag.slot_chunks = slot_chunks;
     ag.tp = tp; ag.rank = rank; ag.R = R; ag.comm_ctas = comm_ctas; ag.epoch = epoch;
+    ag.trace = (unsigned long long*)trace;
     CUtensorMap ta_l, ta_t, tb, td;
     int rc;
     if ((rc = make_tmap_2d(&ta_l, x_local, (uint64_t)K, (uint64_t)R, (uint64_t)K, 64, kBlockM))) return rc;
-    if ((rc = make_tmap_2d(&ta_t, x_total, (uint64_t)K, (uint64_t)M, (uint64_t)K, 64, kBlockM))) return rc;
+    if ((rc = make_tmap_2d(&ta_t, xt_ptrs[rank], (uint64_t)K, (uint64_t)M, (uint64_t)K, 64, kBlockM))) return rc;
     if (layout == 0) rc = make_tmap_2d(&tb, w, (uint64_t)K, (uint64_t)N, (uint64_t)ldw, 64, bn / 2);
     else rc = make_tmap_2d(&tb, w, (uint64_t)N, (uint64_t)K, (uint64_t)ldw, 64, kBlockK);
     if (rc) return rc;

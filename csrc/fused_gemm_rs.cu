@@ -37,7 +37,14 @@ struct RsArgs {
     int slot_cnt;                   // counters [src][m tile]  (tp * m_tiles_per_slab entries)
     int tp, rank, R;
     uint32_t epoch;
+    unsigned long long* trace;      // optional: globaltimer stamps (debug)
 };
+
+__device__ __forceinline__ unsigned long long rs_gtime() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
 
 __device__ __forceinline__ void red_release_sys_add(uint32_t* p, uint32_t v) {
     asm volatile("red.release.sys.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
@@ -72,6 +79,8 @@ gemm_rs_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     const int num_k_blocks = (K + kBlockK - 1) / kBlockK;
     const int cluster_id = blockIdx.x >> 1;
     const int num_clusters = gridDim.x >> 1;
+    const bool tr = rs.trace != nullptr && blockIdx.x == 0;
+    if (tr && threadIdx.x == 0) rs.trace[0] = rs_gtime();
 
     // tile -> (destination rank in ring order, own slab last; m tile inside the slab; n tile)
     auto tile_coords_rs = [&](int tile, int& dest, int& mt, int& tn) {
@@ -221,8 +230,10 @@ gemm_rs_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
             }
             if (++acc == kAccStages) { acc = 0; acc_phase ^= 1; }
         }
+        if (tr && warp == kFirstEpilogueWarp && lane == 0) rs.trace[1] = rs_gtime();   // last tile's boxes issued
         if (lane == 0) {
             ptx::bulk_wait<0>();
+            if (tr && warp == kFirstEpilogueWarp) rs.trace[2] = rs_gtime();            // ... and landed
             if (pending) {
                 asm volatile("fence.proxy.async;" ::: "memory");
                 __threadfence_system();
@@ -240,6 +251,7 @@ gemm_rs_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     const int col_groups = (N + 63) / 64;
     const int items = m_tiles_per_slab * col_groups;
     const uint32_t want = rs.epoch * (uint32_t)(num_n_tiles * 2 * kEpilogueWarps);
+    if (tr && threadIdx.x == 0) rs.trace[3] = rs_gtime();   // GEMM phase of this CTA over
     for (int item = blockIdx.x; item < items; item += gridDim.x) {
         const int mt = item / col_groups, cg = item % col_groups;
         if (threadIdx.x < rs.tp) {
@@ -247,6 +259,7 @@ gemm_rs_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
             while ((int32_t)(ld_acquire_sys_u32(cnt) - want) < 0) { __nanosleep(64); }
         }
         __syncthreads();
+        if (tr && threadIdx.x == 0 && item == (int)blockIdx.x) rs.trace[4] = rs_gtime();   // first item's inputs complete
         // 256 rows x 64 columns: 8 consecutive threads cover one 128-byte row segment, 32 rows per pass.  All 8 passes
         // of one source are loaded back to back (8 independent 16-byte loads in flight per thread) before they are
         // accumulated: the loop is latency bound otherwise.
@@ -285,6 +298,7 @@ gemm_rs_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
         }
         __syncthreads();
     }
+    if (tr && threadIdx.x == 0) rs.trace[5] = rs_gtime();
 }
 
 }  // namespace nxd_gemm
@@ -294,7 +308,7 @@ gemm_rs_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
 // ([tp][R][N] bf16, slot index = source rank) and signal pad.  R % 256 == 0, N % 8 == 0.
 NXD_API int nxd_gemm_rs_bf16(int layout, const void* x, const void* w, void* out, int R, int N, int K, long long ldx,
                              long long ldw, long long ldo, void* const* stage_ptrs, void* const* sig_ptrs, int tp, int rank,
-                             int slot_cnt, unsigned epoch, int block_n, void* stream) {
+                             int slot_cnt, unsigned epoch, int block_n, void* trace, void* stream) {
     using namespace nxd_gemm;
     NXD_REQUIRE(layout == 0 || layout == 1, "gemm_rs: layout must be 0 (nt) or 1 (nn)");
     NXD_REQUIRE(tp >= 2 && tp <= kRsMaxTp && rank >= 0 && rank < tp, "gemm_rs: bad tp/rank %d/%d", tp, rank);
@@ -310,6 +324,7 @@ NXD_API int nxd_gemm_rs_bf16(int layout, const void* x, const void* w, void* out
     rs.sig_local = (uint32_t*)sig_ptrs[rank];
     for (int r = 0; r < tp; ++r) rs.sig_peer[r] = (uint32_t*)sig_ptrs[r];
     rs.slot_cnt = slot_cnt; rs.tp = tp; rs.rank = rank; rs.R = R; rs.epoch = epoch;
+    rs.trace = (unsigned long long*)trace;
     CUtensorMap ta, tb;
     RsTmaps td;
     int rc;

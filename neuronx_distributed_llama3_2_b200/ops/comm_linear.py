@@ -76,7 +76,7 @@ def _gemm(a, b, layout):
 
 
 def ag_gemm(x_shard2d: torch.Tensor, weight: torch.Tensor, layout: str = "nt", group=None,
-            **_) -> Tuple[torch.Tensor, torch.Tensor]:
+            persistent_total: bool = True, **_) -> Tuple[torch.Tensor, torch.Tensor]:
     """``all_gather_rows(x) @ W^T`` (``layout="nt"``) or ``@ W`` (``"nn"``).
     Returns ``(y, x_total)`` -- the gathered operand is a by-product of the fused
     kernel and is reused by wgrad."""
@@ -87,7 +87,7 @@ def ag_gemm(x_shard2d: torch.Tensor, weight: torch.Tensor, layout: str = "nt", g
     if ctx is not None:
         from .fused_comm import fused_ag_gemm
 
-        res = fused_ag_gemm(ctx, x_shard2d, weight, layout)
+        res = fused_ag_gemm(ctx, x_shard2d, weight, layout, persistent_total=persistent_total)
         if res is not None:
             return res
     total = all_gather_rows(x_shard2d, group=g)

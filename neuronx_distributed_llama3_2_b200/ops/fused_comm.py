@@ -17,17 +17,46 @@ from . import _lib
 _LAYOUT = {"nt": 0, "nn": 1}
 
 
-def _comm_ctas() -> int:
-    return int(os.environ.get("NXD_AG_COMM_CTAS", "12"))
+def _comm_ctas(tp: int) -> int:
+    """Copy-engine CTAs of the AG->GEMM kernel (even).  More ranks = more NVLink traffic per unit of math."""
+    env = os.environ.get("NXD_AG_COMM_CTAS")
+    if env:
+        return int(env)
+    return {2: 12, 4: 16}.get(tp, 24)
+
+
+_trace_on = os.environ.get("NXD_FUSED_TRACE", "0") == "1"
+_traces = []
+
+
+def _trace_buf(device, what: str):
+    if not _trace_on:
+        return None
+    t = torch.zeros(16, dtype=torch.int64, device=device)
+    _traces.append((what, t))
+    return t
+
+
+def dump_traces(limit: int = 6):
+    """Debug: print the globaltimer stamps (us, relative to the first) collected with NXD_FUSED_TRACE=1."""
+    torch.cuda.synchronize()
+    out = []
+    for what, t in _traces[-limit:]:
+        v = t.tolist()
+        base = min(x for x in v if x > 0) if any(x > 0 for x in v) else 0
+        out.append((what, [round((x - base) / 1e3, 1) if x > 0 else None for x in v[:12]]))
+    return out
 
 
 def _host_ptrs(ctx, table: torch.Tensor, offset: int):
     return (_c.c_void_p * ctx.world)(*[p + offset for p in table.tolist()])
 
 
-def fused_ag_gemm(ctx, x_shard: torch.Tensor, weight: torch.Tensor, layout: str = "nt"
+def fused_ag_gemm(ctx, x_shard: torch.Tensor, weight: torch.Tensor, layout: str = "nt", persistent_total: bool = True
                   ) -> Optional[Tuple[torch.Tensor, torch.Tensor]]:
-    """``(all_gather_rows(x_shard) @ W_op, x_total)`` or ``None`` if unsupported.  ``x_shard [R, K]`` bf16."""
+    """``(all_gather_rows(x_shard) @ W_op, x_total)`` or ``None`` if unsupported.  ``x_shard [R, K]`` bf16.
+    ``x_total`` lives in a double-buffered symmetric region: with ``persistent_total`` it is copied to a private
+    tensor (needed when it is kept for backward), otherwise the caller must consume it before the second next call."""
     if layout not in _LAYOUT or x_shard.dtype != torch.bfloat16 or weight.dtype != torch.bfloat16:
         return None
     R, K = x_shard.shape
@@ -36,31 +65,32 @@ def fused_ag_gemm(ctx, x_shard: torch.Tensor, weight: torch.Tensor, layout: str 
     if R % 256 or K % 64 or N % 8 or tp > 8 or weight.stride(1) != 1 or weight.stride(0) % 8 or R // 256 > 64:
         return None
     x_shard = x_shard.contiguous()
-    shard_bytes = R * K * 2
-    comm_ctas = _comm_ctas()
-    # flags / counters / slots are per configuration: the counters accumulate a fixed amount per call
+    total_bytes = tp * R * K * 2
+    comm_ctas = _comm_ctas(tp)
+    # counters / buffers are per configuration: the counters accumulate a fixed amount per call
     cfg = f"ag:{R}:{K}:{comm_ctas}"
-    _, table = ctx.region(cfg, 2 * shard_bytes)   # two symmetric shard slots per rank (double buffering)
+    local_ptr, table = ctx.region(cfg, 2 * total_bytes)   # X_total, double buffered
     st = ctx.__dict__.setdefault("_fused_state", {})
     if cfg not in st:
-        st[cfg] = {"ready": ctx.signal_slots(cfg + ":ready", 8), "own": ctx.signal_slots(cfg + ":own", 1),
-                   "chunks": ctx.signal_slots(cfg + ":chunks", 8 * (R // 256)),
-                   "sigs": (_c.c_void_p * tp)(*ctx.sig_peers), "slots": {}}
+        st[cfg] = {"chunks": ctx.signal_slots(cfg + ":chunks", 8 * (R // 256)),
+                   "sigs": (_c.c_void_p * tp)(*ctx.sig_peers), "bufs": {}}
     s = st[cfg]
     epoch = ctx.next_epoch(cfg)
     parity = epoch & 1
     key = (table.data_ptr(), parity)
-    if key not in s["slots"]:
-        s["slots"][key] = _host_ptrs(ctx, table, parity * shard_bytes)
-    x_total = torch.empty((tp * R, K), dtype=torch.bfloat16, device=x_shard.device)
+    if key not in s["bufs"]:
+        s["bufs"][key] = (_host_ptrs(ctx, table, parity * total_bytes),
+                          ctx.tensor_view(local_ptr + parity * total_bytes, (tp * R, K), torch.bfloat16))
+    xt_ptrs, x_total = s["bufs"][key]
     y = torch.empty((tp * R, N), dtype=torch.bfloat16, device=x_shard.device)
+    trace = _trace_buf(x_shard.device, f"ag {R}x{K}x{N}")
     rc = _lib.lib().nxd_ag_gemm_bf16(
-        _c.c_int(_LAYOUT[layout]), _lib.ptr(x_shard), _lib.ptr(x_total), _lib.ptr(weight), _lib.ptr(y), _c.c_int(R),
-        _c.c_int(N), _c.c_int(K), _c.c_longlong(weight.stride(0)), _c.c_longlong(y.stride(0)), s["slots"][key], s["sigs"],
-        _c.c_int(tp), _c.c_int(ctx.rank), _c.c_int(s["ready"]), _c.c_int(s["chunks"]), _c.c_int(s["own"]),
-        _c.c_uint(epoch), _c.c_int(comm_ctas), _c.c_int(0), _lib.stream_ptr())
+        _c.c_int(_LAYOUT[layout]), _lib.ptr(x_shard), _lib.ptr(weight), _lib.ptr(y), _c.c_int(R), _c.c_int(N),
+        _c.c_int(K), _c.c_longlong(weight.stride(0)), _c.c_longlong(y.stride(0)), xt_ptrs, s["sigs"], _c.c_int(tp),
+        _c.c_int(ctx.rank), _c.c_int(s["chunks"]), _c.c_uint(epoch), _c.c_int(comm_ctas), _c.c_int(0), _lib.ptr(trace),
+        _lib.stream_ptr())
     _lib.check(rc, "nxd_ag_gemm_bf16")
-    return y, x_total
+    return y, (x_total.clone() if persistent_total else x_total)
 
 
 def fused_gemm_rs(ctx, x2d: torch.Tensor, weight: torch.Tensor, layout: str = "nt") -> Optional[torch.Tensor]:
@@ -96,7 +126,7 @@ def fused_gemm_rs(ctx, x2d: torch.Tensor, weight: torch.Tensor, layout: str = "n
         _c.c_int(_LAYOUT[layout]), _lib.ptr(x2d), _lib.ptr(weight), _lib.ptr(out), _c.c_int(R), _c.c_int(N), _c.c_int(K),
         _c.c_longlong(x2d.stride(0)), _c.c_longlong(weight.stride(0)), _c.c_longlong(out.stride(0)), s["stages"][key],
         s["sigs"], _c.c_int(tp), _c.c_int(ctx.rank), _c.c_int(s["cnt"]), _c.c_uint(epoch), _c.c_int(bn),
-        _lib.stream_ptr())
+        _lib.ptr(_trace_buf(x2d.device, f"rs {R}x{K}x{N}")), _lib.stream_ptr())
     _lib.check(rc, "nxd_gemm_rs_bf16")
     return out
 

@@ -72,6 +72,20 @@ class SymmMemContext:
         local, peers, size, table = self._regions[name]
         return local, table
 
+    def tensor_view(self, ptr: int, shape, dtype: torch.dtype) -> torch.Tensor:
+        """Zero-copy torch tensor over symmetric memory at ``ptr`` (through ``__cuda_array_interface__``)."""
+        nbytes = torch.empty(0, dtype=dtype).element_size()
+        n = 1
+        for d in shape:
+            n *= int(d)
+
+        class _Holder:
+            __cuda_array_interface__ = {"shape": (n * nbytes,), "typestr": "|u1", "data": (int(ptr), False), "version": 2,
+                                        "strides": None}
+
+        raw = torch.as_tensor(_Holder(), device=self.device)
+        return raw.view(dtype).view(tuple(int(d) for d in shape))
+
     def signal_slots(self, name: str, count: int) -> int:
         """Reserve ``count`` uint32 flags in the signal pad (same offset on every rank); returns the slot index."""
         key = "sig:" + name

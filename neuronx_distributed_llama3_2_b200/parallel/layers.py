@@ -336,7 +336,7 @@ class _RowParallelMatmul(torch.autograd.Function):
             dy2d = dy2d.contiguous()
         if ctx.sequence_parallel_enabled:
             # dX = all_gather(dY_shard) W : fused AG->GEMM, the gathered dY is reused for wgrad
-            grad_input2d, dy_total = comm_linear.ag_gemm(dy2d, weight, layout="nn",
+            grad_input2d, dy_total = comm_linear.ag_gemm(dy2d, weight, layout="nn", persistent_total=False,
                                                          rows_per_rank_outer=grad_output.shape[0],
                                                          inner=int(math.prod(grad_output.shape[1:-1])),
                                                          group=ctx.process_group)

@@ -23,7 +23,8 @@ def main():
 
     ps.initialize_model_parallel(tensor_model_parallel_size=world)
     ctx = ps.get_symm_mem_context("tp")
-    S, H, I = 8192, 3072, 8192
+    S, H, I = int(os.environ.get("NXD_BENCH_S", 8192)), 3072, 8192
+    heads = 24 if world <= 8 else 32
     R = S // world
     cases = [("qkv fwd", H, (24 + 16) * 128 // world), ("gate_up fwd", H, 2 * I // world)]
 
@@ -58,7 +59,7 @@ def main():
             dist.all_gather_into_tensor(total, x)
 
         def fused():
-            return fused_ag_gemm(ctx, x, w, "nt")
+            return fused_ag_gemm(ctx, x, w, "nt", persistent_total=False)
 
         res = {"case": name, "tp": world, "R": R, "K": K, "N": N, "nccl_ag_plus_gemm_ms": timed(nccl),
                "gemm_only_ms": timed(gemm_only), "nccl_ag_only_ms": timed(ag_only), "fused_ms": timed(fused)}
@@ -100,6 +101,11 @@ def main():
         res["speedup_vs_nccl"] = res["gemm_plus_nccl_rs_ms"] / res["fused_ms"]
         if rank == 0:
             print(json.dumps(res), flush=True)
+    if os.environ.get("NXD_FUSED_TRACE", "0") == "1" and rank == 0:
+        from neuronx_distributed_llama3_2_b200.ops.fused_comm import dump_traces
+
+        for what, stamps in dump_traces(8):
+            print("TRACE", what, stamps, flush=True)
     ps.destroy_model_parallel()
     dist.destroy_process_group()
 
