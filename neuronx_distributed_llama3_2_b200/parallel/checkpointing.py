@@ -72,10 +72,9 @@ def save(checkpoint: dict, output_dir: str, save_serially: bool = True, save_xse
     if down_cast_bf16:
         checkpoint = cast_all(checkpoint, torch.float32, torch.bfloat16)
     if should_write:
-        ensure_directory_exists(path if not save_xser else os.path.join(path, "x"))
+        ensure_directory_exists(path)
         if save_xser:
-            os.makedirs(os.path.dirname(path), exist_ok=True)
-            xser.save(checkpoint, path)
+            xser.save(checkpoint, path)   # <path> (reference file) + <path>.tensors/tensor_N.pt
         elif save_serially:
             # stagger writers TP-rank by TP-rank to bound host memory (reference :114-134)
             cpu = move_all_tensor_to_cpu(checkpoint)
