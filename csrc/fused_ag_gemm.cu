@@ -52,6 +52,9 @@ __device__ __forceinline__ unsigned long long gtime() {
 __device__ __forceinline__ void red_release_sys_add_u32(uint32_t* p, uint32_t v) {
     asm volatile("red.release.sys.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
+__device__ __forceinline__ void red_relaxed_sys_add_u32(uint32_t* p, uint32_t v) {
+    asm volatile("red.relaxed.sys.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
 
 __device__ __forceinline__ uint32_t ld_acquire_gpu(const uint32_t* p) {
     uint32_t v;
@@ -164,11 +167,12 @@ ag_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a_local, const __grid_co
         const int ipp = p1 > p0 ? (int)((p1 - p0 + kCommSub - 1) / kCommSub) : 0;      // items per piece
         if (ag.trace && cid == 0) ag.trace[0] = gtime();
         auto bump = [&](int c) {   // this CTA's piece of chunk c of MY shard has landed everywhere
+            // ONE system-scope fence, then relaxed increments: a release per peer would pay the fence tp - 1 times
             fence_proxy_async_all();
             __threadfence_system();
             for (int d = 1; d < ag.tp; ++d) {
                 const int peer = (ag.rank + d) % ag.tp;
-                red_release_sys_add_u32(ag.sig_peer[peer] + ag.slot_chunks + ag.rank * chunks_per_slab + c, 1u);
+                red_relaxed_sys_add_u32(ag.sig_peer[peer] + ag.slot_chunks + ag.rank * chunks_per_slab + c, 1u);
             }
         };
         if (ipp == 0) {  // more copy CTAs than 16-byte pieces: nothing to move, but the counters expect every CTA

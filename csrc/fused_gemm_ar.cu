@@ -1,0 +1,294 @@
+// Decode-path fused kernels over NVLink peer memory:
+//
+//   nxd_skinny_gemm_ar_bf16   out[B, N] = all_reduce_r( X_r[B, Kloc] * W_r[N, Kloc]^T )      B <= 16 (token generation)
+//   nxd_allreduce_oneshot     out[n]    = all_reduce_r( in_r[n] )                            small messages
+//
+// Reference: RowParallelLinear forward (src/neuronx_distributed/parallel_layers/layers.py:452-468) is `matmul` then
+// `reduce_from_tensor_model_parallel_region` (mappings.py:176-190, an XLA all-reduce): two dependent ops whose cost in
+// token generation is pure latency (a [4, 3072] activation is 24 KB).  Here both halves are ONE launch:
+//
+//   * the weight matrix is streamed exactly once (the op is weight-bandwidth bound): every warp owns output columns,
+//     the B activation rows sit in shared memory, fp32 accumulation;
+//   * each CTA pushes its fp32 partial block [B, cols] into the SAME block of every peer's staging slot
+//     (slot = [parity][source rank]) with 16-byte stores over NVLink, then stamps flag [cta][my rank] on every peer
+//     with the call's epoch (st.release.sys) -- a "one-shot" all-reduce: one NVLink write latency + one flag
+//     latency, no ring steps;
+//   * the same CTA waits until its tp - 1 flags carry the epoch (stamps only grow, nothing is ever reset, calls with
+//     different grids can share the flags), adds the blocks in RANK ORDER (so every rank produces bit-identical
+//     sums, in fp32 -- NCCL's bf16 ring rounds at every hop) and writes bf16.
+//
+// No barrier is needed for buffer reuse: staging is double-buffered by call parity, and a rank cannot finish call
+// n + 1 before every peer has ENTERED call n + 1 (it needs their partials), i.e. finished reading the buffer of call n,
+// which is the one call n + 2 overwrites.  All CTAs of the grid are co-resident (the host sizes the grid from the
+// occupancy query), so the spin-wait cannot starve the producers.
+#include "common.cuh"
+
+namespace {
+
+constexpr int kMaxTp = 8;
+constexpr int kArThreads = 256;
+constexpr int kArWarps = kArThreads / 32;
+constexpr int kMaxCtas = 512;            // flags reserved per staging region: kMaxCtas * kMaxTp
+
+struct ArArgs {
+    float* stage_peer[kMaxTp];     // every rank's staging base: [2][tp][slot_elems] floats (peer-mapped, [rank] local)
+    uint32_t* sig_peer[kMaxTp];    // peers' signal pads
+    uint32_t* sig_local;
+    size_t slot_elems;             // floats per (parity, source) slot
+    int slot;                      // first flag; flag [cta][source rank]
+    int tp, rank;
+    uint32_t epoch;                // call counter of this (staging, flags) pair, starts at 1
+};
+
+__device__ __forceinline__ void ar_st_release_sys(uint32_t* p, uint32_t v) {
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ar_ld_acquire_sys(const uint32_t* p) {
+    uint32_t v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ float4 ar_ld_cg(const float4* p) {
+    float4 v;
+    asm volatile("ld.global.cg.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
+    return v;
+}
+
+// Push `n4` float4 of `part` (shared memory) into block offset `off` of my slot on every peer, signal, wait for the
+// peers' blocks, reduce in rank order.  Result (fp32) is left in `part`.
+__device__ __forceinline__ void oneshot_exchange(const ArArgs& ar, float* part, int n4, size_t off, int cta) {
+    const int parity = (int)(ar.epoch & 1u);
+    const size_t my_slot = ((size_t)parity * ar.tp + ar.rank) * ar.slot_elems + off;
+    // (peer, vector) pairs spread over the CTA: all NVLink stores are in flight at once
+    for (int i = threadIdx.x; i < n4 * (ar.tp - 1); i += blockDim.x) {
+        const int d = i / n4 + 1, v = i % n4;
+        const int peer = (ar.rank + d) % ar.tp;
+        reinterpret_cast<float4*>(ar.stage_peer[peer] + my_slot)[v] = reinterpret_cast<const float4*>(part)[v];
+    }
+    __syncthreads();
+    if (threadIdx.x < ar.tp - 1) {
+        const int peer = (ar.rank + 1 + (int)threadIdx.x) % ar.tp;
+        __threadfence_system();
+        ar_st_release_sys(ar.sig_peer[peer] + ar.slot + cta * kMaxTp + ar.rank, ar.epoch);
+        const uint32_t* flag = ar.sig_local + ar.slot + cta * kMaxTp + peer;
+        while ((int32_t)(ar_ld_acquire_sys(flag) - ar.epoch) < 0) {}
+    }
+    __syncthreads();
+    const float* mine = ar.stage_peer[ar.rank] + (size_t)parity * ar.tp * ar.slot_elems + off;
+    for (int v = threadIdx.x; v < n4; v += blockDim.x) {
+        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int r = 0; r < ar.tp; ++r) {
+            const float4 x = r == ar.rank ? reinterpret_cast<const float4*>(part)[v]
+                                          : ar_ld_cg(reinterpret_cast<const float4*>(mine + (size_t)r * ar.slot_elems) + v);
+            acc.x += x.x; acc.y += x.y; acc.z += x.z; acc.w += x.w;
+        }
+        reinterpret_cast<float4*>(part)[v] = acc;
+    }
+    __syncthreads();
+}
+
+__device__ __forceinline__ float dot8(const uint4& a, const uint4& b, float acc) {
+    const __nv_bfloat162* pa = reinterpret_cast<const __nv_bfloat162*>(&a);
+    const __nv_bfloat162* pb = reinterpret_cast<const __nv_bfloat162*>(&b);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const float2 fa = __bfloat1622float2(pa[i]), fb = __bfloat1622float2(pb[i]);
+        acc = fmaf(fa.x, fb.x, acc);
+        acc = fmaf(fa.y, fb.y, acc);
+    }
+    return acc;
+}
+
+// Shared memory: X tile [kB][K] bf16, then partial block [kB][cols] fp32.
+template <int kB>
+__global__ void __launch_bounds__(kArThreads) skinny_gemm_ar_kernel(const bf16* __restrict__ x, const bf16* __restrict__ w,
+                                                                    const bf16* __restrict__ residual, bf16* __restrict__ out,
+                                                                    int B, int N, int K, long long ldx, long long ldw,
+                                                                    long long ldo, int cols, const ArArgs ar) {
+    extern __shared__ __align__(16) uint8_t ar_smem[];
+    bf16* xs = reinterpret_cast<bf16*>(ar_smem);
+    float* part = reinterpret_cast<float*>(ar_smem + (size_t)kB * K * sizeof(bf16));
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int k8 = K / 8;
+    for (int i = threadIdx.x; i < kB * k8; i += kArThreads) {
+        const int row = i / k8, c = i % k8;
+        uint4 v = make_uint4(0u, 0u, 0u, 0u);
+        if (row < B) v = *reinterpret_cast<const uint4*>(x + (size_t)row * ldx + (size_t)c * 8);
+        reinterpret_cast<uint4*>(xs)[i] = v;
+    }
+    __syncthreads();
+    const int c0 = (int)blockIdx.x * cols;
+    const int ncols = min(cols, N - c0);
+    // two columns per warp pass: 2 x (K / 256) independent 16-byte weight loads in flight per lane
+    for (int cc = warp * 2; cc < cols; cc += kArWarps * 2) {
+        float acc0[kB], acc1[kB];
+#pragma unroll
+        for (int b = 0; b < kB; ++b) acc0[b] = acc1[b] = 0.f;
+        const bool v0 = cc < ncols, v1 = cc + 1 < ncols;
+        const bf16* w0 = w + (size_t)(c0 + cc) * ldw;
+        const bf16* w1 = w0 + ldw;
+#pragma unroll 2
+        for (int k = lane; k < k8; k += 32) {
+            const uint4 a0 = v0 ? __ldg(reinterpret_cast<const uint4*>(w0) + k) : make_uint4(0u, 0u, 0u, 0u);
+            const uint4 a1 = v1 ? __ldg(reinterpret_cast<const uint4*>(w1) + k) : make_uint4(0u, 0u, 0u, 0u);
+#pragma unroll
+            for (int b = 0; b < kB; ++b) {
+                const uint4 xv = reinterpret_cast<const uint4*>(xs)[b * k8 + k];
+                acc0[b] = dot8(a0, xv, acc0[b]);
+                acc1[b] = dot8(a1, xv, acc1[b]);
+            }
+        }
+#pragma unroll
+        for (int b = 0; b < kB; ++b) {
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                acc0[b] += __shfl_xor_sync(0xffffffffu, acc0[b], o);
+                acc1[b] += __shfl_xor_sync(0xffffffffu, acc1[b], o);
+            }
+        }
+        if (lane == 0) {
+#pragma unroll
+            for (int b = 0; b < kB; ++b) {
+                part[b * cols + cc] = acc0[b];
+                part[b * cols + cc + 1] = acc1[b];
+            }
+        }
+    }
+    __syncthreads();
+    if (ar.tp > 1) oneshot_exchange(ar, part, kB * cols / 4, (size_t)blockIdx.x * kB * cols, (int)blockIdx.x);
+    for (int i = threadIdx.x; i < B * ncols; i += kArThreads) {
+        const int b = i / ncols, c = i % ncols;
+        float v = part[b * cols + c];
+        if (residual) v += __bfloat162float(residual[(size_t)b * ldo + c0 + c]);
+        out[(size_t)b * ldo + c0 + c] = __float2bfloat16(v);
+    }
+}
+
+// Stand-alone one-shot all-reduce of n bf16 values (n % 8 == 0); every CTA owns `per_cta` elements (multiple of 8).
+__global__ void __launch_bounds__(kArThreads) allreduce_oneshot_kernel(const bf16* __restrict__ in, bf16* __restrict__ out,
+                                                                       long long n, int per_cta, const ArArgs ar) {
+    extern __shared__ __align__(16) uint8_t ar_smem[];
+    float* part = reinterpret_cast<float*>(ar_smem);
+    const long long e0 = (long long)blockIdx.x * per_cta;
+    const int cnt = (int)min((long long)per_cta, n - e0);
+    for (int i = threadIdx.x; i < per_cta / 8; i += kArThreads) {
+        float f[8];
+        if (i * 8 < cnt) {
+            const uint4 v = *reinterpret_cast<const uint4*>(in + e0 + (size_t)i * 8);
+            const __nv_bfloat162* p = reinterpret_cast<const __nv_bfloat162*>(&v);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const float2 t = __bfloat1622float2(p[j]);
+                f[2 * j] = t.x; f[2 * j + 1] = t.y;
+            }
+        } else {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) f[j] = 0.f;
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) part[i * 8 + j] = f[j];
+    }
+    __syncthreads();
+    oneshot_exchange(ar, part, per_cta / 4, (size_t)blockIdx.x * per_cta, (int)blockIdx.x);
+    for (int i = threadIdx.x; i < cnt / 8; i += kArThreads) {
+        uint4 v;
+        __nv_bfloat162* p = reinterpret_cast<__nv_bfloat162*>(&v);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) p[j] = __floats2bfloat162_rn(part[i * 8 + 2 * j], part[i * 8 + 2 * j + 1]);
+        *reinterpret_cast<uint4*>(out + e0 + (size_t)i * 8) = v;
+    }
+}
+
+int fill_args(ArArgs& ar, void* const* stage_ptrs, void* const* sig_ptrs, int tp, int rank, int slot, unsigned epoch,
+              size_t slot_elems) {
+    NXD_REQUIRE(tp >= 1 && tp <= kMaxTp && rank >= 0 && rank < tp, "oneshot all-reduce: tp %d / rank %d out of range", tp, rank);
+    NXD_REQUIRE(tp == 1 || (stage_ptrs && sig_ptrs && epoch > 0), "oneshot all-reduce: missing symmetric buffers");
+    for (int i = 0; i < tp && tp > 1; ++i) {
+        ar.stage_peer[i] = (float*)stage_ptrs[i];
+        ar.sig_peer[i] = (uint32_t*)sig_ptrs[i];
+    }
+    ar.sig_local = tp > 1 ? (uint32_t*)sig_ptrs[rank] : nullptr;
+    ar.slot_elems = slot_elems; ar.slot = slot; ar.tp = tp; ar.rank = rank; ar.epoch = epoch;
+    return 0;
+}
+
+template <int kB>
+int launch_skinny(const bf16* x, const bf16* w, const bf16* residual, bf16* out, int B, int N, int K, long long ldx,
+                  long long ldw, long long ldo, const ArArgs& ar, cudaStream_t st) {
+    // columns per CTA: multiple of 16 (8 warps x 2 columns), as few as co-residency allows
+    int dev = 0, sms = 0;
+    NXD_CHECK_CUDA(cudaGetDevice(&dev));
+    NXD_CHECK_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    int cols = 16, grid = 0;
+    size_t smem = 0;
+    for (;; cols += 16) {
+        smem = (size_t)kB * K * sizeof(bf16) + (size_t)kB * cols * sizeof(float);
+        NXD_REQUIRE(smem <= 200 * 1024, "skinny_gemm_ar: B %d x K %d does not fit shared memory", B, K);
+        NXD_CHECK_CUDA(cudaFuncSetAttribute(skinny_gemm_ar_kernel<kB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        int per_sm = 0;
+        NXD_CHECK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, skinny_gemm_ar_kernel<kB>, kArThreads, smem));
+        NXD_REQUIRE(per_sm >= 1, "skinny_gemm_ar: kernel does not fit an SM");
+        grid = (N + cols - 1) / cols;
+        if (grid <= min(min(per_sm, 2) * sms, kMaxCtas)) break;
+        NXD_REQUIRE(cols < 8192, "skinny_gemm_ar: cannot make N %d co-resident", N);
+    }
+    NXD_REQUIRE(ar.tp == 1 || (size_t)grid * kB * cols <= ar.slot_elems,
+                "skinny_gemm_ar: staging slot too small (%zu floats, need %zu)", ar.slot_elems, (size_t)grid * kB * cols);
+    skinny_gemm_ar_kernel<kB><<<grid, kArThreads, smem, st>>>(x, w, residual, out, B, N, K, ldx, ldw, ldo, cols, ar);
+    NXD_LAUNCH_CHECK();
+    return 0;
+}
+
+}  // namespace
+
+// uint32 flags a staging region needs (one per CTA and source rank).
+NXD_API int nxd_oneshot_num_flags(void) { return kMaxCtas * kMaxTp; }
+
+// out[B, N] (+ residual[B, N], same pitch as out) = sum over ranks of x[B, K] * w[N, K]^T.  B <= 16, K % 8 == 0,
+// N % 4 == 0, rows of x / w 16-byte aligned.  tp == 1: plain skinny GEMM (stage_ptrs / sig_ptrs may be NULL).
+// stage_ptrs: every rank's staging region of 2 * tp * slot_elems floats, slot_elems >= 16 * (N + 8192) is always
+// enough; sig_ptrs: signal pads; slot: first of nxd_oneshot_num_flags() flags that belong to this staging region;
+// epoch = 1, 2, 3, ... counts the calls (of either entry point) on this region.
+NXD_API int nxd_skinny_gemm_ar_bf16(const void* x, const void* w, const void* residual, void* out, int B, int N, int K,
+                                    long long ldx, long long ldw, long long ldo, void* const* stage_ptrs,
+                                    void* const* sig_ptrs, size_t slot_elems, int tp, int rank, int slot, unsigned epoch,
+                                    void* stream) {
+    NXD_REQUIRE(B >= 1 && B <= 16, "skinny_gemm_ar: B %d not in [1, 16]", B);
+    NXD_REQUIRE(K % 8 == 0 && N % 4 == 0 && ldx % 8 == 0 && ldw % 8 == 0,
+                "skinny_gemm_ar: K / ldx / ldw must be multiples of 8 and N of 4");
+    ArArgs ar{};
+    if (int rc = fill_args(ar, stage_ptrs, sig_ptrs, tp, rank, slot, epoch, slot_elems)) return rc;
+    const bf16 *xb = (const bf16*)x, *wb = (const bf16*)w, *rb = (const bf16*)residual;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (B <= 1) return launch_skinny<1>(xb, wb, rb, (bf16*)out, B, N, K, ldx, ldw, ldo, ar, st);
+    if (B <= 2) return launch_skinny<2>(xb, wb, rb, (bf16*)out, B, N, K, ldx, ldw, ldo, ar, st);
+    if (B <= 4) return launch_skinny<4>(xb, wb, rb, (bf16*)out, B, N, K, ldx, ldw, ldo, ar, st);
+    if (B <= 8) return launch_skinny<8>(xb, wb, rb, (bf16*)out, B, N, K, ldx, ldw, ldo, ar, st);
+    return launch_skinny<16>(xb, wb, rb, (bf16*)out, B, N, K, ldx, ldw, ldo, ar, st);
+}
+
+// out[n] = sum over ranks of in[n] (bf16, fp32 accumulation in rank order).  n % 8 == 0, n <= slot_elems.
+NXD_API int nxd_allreduce_oneshot(const void* in, void* out, long long n, void* const* stage_ptrs, void* const* sig_ptrs,
+                                  size_t slot_elems, int tp, int rank, int slot, unsigned epoch, void* stream) {
+    NXD_REQUIRE(n > 0 && n % 8 == 0, "allreduce_oneshot: n %lld must be a positive multiple of 8", n);
+    ArArgs ar{};
+    if (int rc = fill_args(ar, stage_ptrs, sig_ptrs, tp, rank, slot, epoch, slot_elems)) return rc;
+    if (tp == 1) {
+        if (in != out) NXD_CHECK_CUDA(cudaMemcpyAsync(out, in, (size_t)n * 2, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+        return 0;
+    }
+    int dev = 0, sms = 0;
+    NXD_CHECK_CUDA(cudaGetDevice(&dev));
+    NXD_CHECK_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    // 2048 elements (8 KB of fp32) per CTA until the grid would exceed the SM count, then larger blocks
+    int per_cta = 2048;
+    while ((n + per_cta - 1) / per_cta > min(sms, kMaxCtas)) per_cta *= 2;
+    NXD_REQUIRE((size_t)per_cta * 4 <= 160 * 1024, "allreduce_oneshot: n %lld too large for the one-shot path", n);
+    const int grid = (int)((n + per_cta - 1) / per_cta);
+    NXD_REQUIRE((size_t)grid * per_cta <= slot_elems, "allreduce_oneshot: staging slot too small");
+    const size_t smem = (size_t)per_cta * 4;
+    NXD_CHECK_CUDA(cudaFuncSetAttribute(allreduce_oneshot_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    allreduce_oneshot_kernel<<<grid, kArThreads, smem, (cudaStream_t)stream>>>((const bf16*)in, (bf16*)out, n, per_cta, ar);
+    NXD_LAUNCH_CHECK();
+    return 0;
+}

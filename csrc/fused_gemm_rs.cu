@@ -46,8 +46,9 @@ __device__ __forceinline__ unsigned long long rs_gtime() {
     return t;
 }
 
-__device__ __forceinline__ void red_release_sys_add(uint32_t* p, uint32_t v) {
-    asm volatile("red.release.sys.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+// increment after an explicit __threadfence_system(): fence + relaxed atomic = release, but the fence is paid once
+__device__ __forceinline__ void red_relaxed_sys_add(uint32_t* p, uint32_t v) {
+    asm volatile("red.relaxed.sys.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 __device__ __forceinline__ uint32_t ld_acquire_sys_u32(const uint32_t* p) {
     uint32_t v;
@@ -224,7 +225,7 @@ gemm_rs_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                     ptx::bulk_wait<kGroupsPerTile>();   // everything older than this tile's groups has landed
                     asm volatile("fence.proxy.async;" ::: "memory");
                     __threadfence_system();
-                    red_release_sys_add(pending, 1u);
+                    red_relaxed_sys_add(pending, 1u);
                 }
                 pending = rs.sig_peer[dest] + rs.slot_cnt + rs.rank * m_tiles_per_slab + mt;
             }
@@ -237,7 +238,7 @@ gemm_rs_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
             if (pending) {
                 asm volatile("fence.proxy.async;" ::: "memory");
                 __threadfence_system();
-                red_release_sys_add(pending, 1u);
+                red_relaxed_sys_add(pending, 1u);
             }
         }
     }
@@ -272,24 +273,36 @@ gemm_rs_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
 #pragma unroll
                 for (int e = 0; e < 8; ++e) acc8[pass][e] = 0.f;
             const int row_base = mt * kTileM + (threadIdx.x >> 3);
-            for (int s = 0; s < rs.tp; ++s) {
-                bf16x8 pk[kPasses];
+            // two sources per round: 16 independent 16-byte loads in flight per thread
+            for (int s = 0; s < rs.tp; s += 2) {
+                bf16x8 pk[2][kPasses];
+                const int ns = min(2, rs.tp - s);
 #pragma unroll
-                for (int pass = 0; pass < kPasses; ++pass) {
-                    const bf16* src = rs.stage_local + ((size_t)s * rs.R + row_base + pass * 32) * N + col;
-                    asm volatile("ld.global.cg.v4.u32 {%0,%1,%2,%3}, [%4];"
-                                 : "=r"(reinterpret_cast<uint32_t*>(&pk[pass])[0]),
-                                   "=r"(reinterpret_cast<uint32_t*>(&pk[pass])[1]),
-                                   "=r"(reinterpret_cast<uint32_t*>(&pk[pass])[2]),
-                                   "=r"(reinterpret_cast<uint32_t*>(&pk[pass])[3])
-                                 : "l"(src));
+                for (int u = 0; u < 2; ++u) {
+                    if (u < ns) {
+#pragma unroll
+                        for (int pass = 0; pass < kPasses; ++pass) {
+                            const bf16* src = rs.stage_local + ((size_t)(s + u) * rs.R + row_base + pass * 32) * N + col;
+                            asm volatile("ld.global.cg.v4.u32 {%0,%1,%2,%3}, [%4];"
+                                         : "=r"(reinterpret_cast<uint32_t*>(&pk[u][pass])[0]),
+                                           "=r"(reinterpret_cast<uint32_t*>(&pk[u][pass])[1]),
+                                           "=r"(reinterpret_cast<uint32_t*>(&pk[u][pass])[2]),
+                                           "=r"(reinterpret_cast<uint32_t*>(&pk[u][pass])[3])
+                                         : "l"(src));
+                        }
+                    }
                 }
 #pragma unroll
-                for (int pass = 0; pass < kPasses; ++pass) {
-                    float f[8];
-                    unpack8(pk[pass], f);
+                for (int u = 0; u < 2; ++u) {
+                    if (u < ns) {
 #pragma unroll
-                    for (int e = 0; e < 8; ++e) acc8[pass][e] += f[e];
+                        for (int pass = 0; pass < kPasses; ++pass) {
+                            float f[8];
+                            unpack8(pk[u][pass], f);
+#pragma unroll
+                            for (int e = 0; e < 8; ++e) acc8[pass][e] += f[e];
+                        }
+                    }
                 }
             }
 #pragma unroll

@@ -99,6 +99,58 @@ int nxd_embedding_fwd(const long long* ids, const void* weight, void* out, long 
 int nxd_embedding_bwd(const long long* ids, const void* dy, float* dw, long long T, int H, int vocab_start,
                       int vocab_local, int B, int S, int seq_first_in, void* stream);
 
+/* ---- flash attention (reference: kernels/flash_attn.py nki_flash_attn_func; attention_base.py prefill) ----------
+ * bf16 tensors addressed as (batch, head, row) element strides with unit stride on the head dimension:
+ * strides = {q_b,q_h,q_s, k_b,k_h,k_s, v_b,v_h,v_s, o_b,o_h,o_s} (forward, 12 entries) followed in the backward
+ * by the same triple for dout, dq, dk, dv (24 entries).  lse: [B, Hq, Sq] floats (natural log).  GQA: Hq % Hkv == 0.
+ * *_tc = tcgen05 / TMEM / TMA kernels (forward D = 64 or 128; backward D = 128), the others are the portable
+ * mma.sync kernels (D = 64 or 128). */
+int nxd_flash_attn_fwd(const void* q, const void* k, const void* v, void* o, float* lse, const long long* strides,
+                       int B, int Hq, int Hkv, int Sq, int Sk, int D, float scale, int causal, void* stream);
+/* delta: [B, Hq, Sq] floats of scratch */
+int nxd_flash_attn_bwd(const void* q, const void* k, const void* v, const void* o, const void* dout,
+                       const float* lse, float* delta, void* dq, void* dk, void* dv, const long long* strides, int B,
+                       int Hq, int Hkv, int Sq, int Sk, int D, float scale, int causal, void* stream);
+int nxd_flash_attn_fwd_tc(const void* q, const void* k, const void* v, void* o, float* lse,
+                          const long long* strides, int B, int Hq, int Hkv, int Sq, int Sk, int D, float scale,
+                          int causal, void* stream);
+/* scratch: lse_pad, delta_pad = B * Hq * roundup(Sq, 64) floats each; dq_accum = B * Hq * Sq * 128 floats, ZEROED
+ * by the caller before the call (dQ is accumulated with TMA reduce-add). */
+int nxd_flash_attn_bwd_tc(const void* q, const void* k, const void* v, const void* o, const void* dout,
+                          const float* lse, float* lse_pad, float* delta_pad, float* dq_accum, void* dq, void* dk,
+                          void* dv, const long long* strides, int B, int Hq, int Hkv, int Sq, int Sk, int D,
+                          float scale, int causal, void* stream);
+
+/* ---- symmetric (peer-mapped) memory over CUDA IPC + fused compute/collective kernels ---------------------------
+ * No counterpart in the reference (its collectives are XLA ops).  One process per GPU: every rank allocates a
+ * region, exchanges the 64-byte handles out of band (torch.distributed), opens the peers' handles and passes the
+ * resulting pointer tables to the kernels.  A signal pad (uint32 flags, zero-initialised) is one more such region. */
+int nxd_symm_handle_bytes(void);
+int nxd_symm_alloc(size_t bytes, void** ptr, unsigned char* handle_out);   /* cudaMalloc + memset 0 + export */
+int nxd_symm_open(const unsigned char* handle, void** ptr);                /* map a peer's region */
+int nxd_symm_close(void* ptr);
+int nxd_symm_free(void* ptr);
+/* all ranks rendezvous on the device: flag `slot` of every pad, `epoch` strictly increasing per slot */
+int nxd_symm_barrier(void* const* sig_peers, void* sig_local, int world, int rank, int slot, unsigned epoch,
+                     void* stream);
+/* Y[tp*R, N] = all_gather_r(X_r[R, K]) * op(W)  (reference: layers.py:312-325 all_gather then matmul).
+ * layout 0: W is [N, K] (nt); 1: W is [K, N] (nn).  xt_ptrs: tp pointers to every rank's gathered buffer
+ * [tp*R, K] (symmetric memory; on return the local one holds the gathered input), sig_ptrs: tp signal pads,
+ * slot_chunks: first of tp * R/256 flags, epoch: call counter of this (buffer, flags) pair starting at 1,
+ * comm_ctas: even number of CTAs that drive the copy engine, block_n: 0 = auto, trace: NULL or 16 x u64. */
+int nxd_ag_gemm_bf16(int layout, const void* x_local, const void* w, void* y, int R, int N, int K, long long ldw,
+                     long long ldy, void* const* xt_ptrs, void* const* sig_ptrs, int tp, int rank, int slot_chunks,
+                     unsigned epoch, int comm_ctas, int block_n, void* trace, void* stream);
+/* out[R, N] = reduce_scatter_r(X[tp*R, K] * op(W))  (reference: layers.py:452-461 matmul then reduce_scatter).
+ * stage_ptrs: tp pointers to every rank's staging region [tp][R][N] bf16 (double-buffered by the caller through
+ * epoch parity), slot_cnt: first of tp * R/256 flags. */
+int nxd_gemm_rs_bf16(int layout, const void* x, const void* w, void* out, int R, int N, int K, long long ldx,
+                     long long ldw, long long ldo, void* const* stage_ptrs, void* const* sig_ptrs, int tp, int rank,
+                     int slot_cnt, unsigned epoch, int block_n, void* trace, void* stream);
+/* tooling: NVLink push-bandwidth probe (tools/bench_p2p.py) */
+int nxd_p2p_push_probe(int mode, const void* src, const void* const* dst_ptrs, int n_dst, size_t bytes, int ctas,
+                       int chunk, int bufs, int read_lag, int sig_mode, int sig_every, size_t flag_off, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

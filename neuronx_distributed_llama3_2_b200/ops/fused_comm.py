@@ -37,7 +37,7 @@ def _trace_buf(device, what: str):
     return t
 
 
-def dump_traces(limit: int = 6):
+def dump_traces(limit: int = 6):  # noqa: D401
     """Debug: print the globaltimer stamps (us, relative to the first) collected with NXD_FUSED_TRACE=1."""
     torch.cuda.synchronize()
     out = []
@@ -131,5 +131,91 @@ def fused_gemm_rs(ctx, x2d: torch.Tensor, weight: torch.Tensor, layout: str = "n
     return out
 
 
-def fused_gemm_ar(ctx, x2d, weight, layout="nt"):
-    return None
+# ---- decode path: one-shot all-reduce and skinny GEMM -> all-reduce (csrc/fused_gemm_ar.cu) -----------------------------
+_AR_SLOT_ELEMS = 1 << 20           # floats per (parity, source) staging slot: messages up to 2 MB of bf16
+_SKINNY_MAX_ROWS = 16
+
+
+def _ar_state(ctx):
+    st = ctx.__dict__.setdefault("_fused_state", {})
+    if "ar" not in st:
+        tp = ctx.world
+        _, table = ctx.region("ar", 2 * tp * _AR_SLOT_ELEMS * 4)
+        st["ar"] = {"slot": ctx.signal_slots("ar:flags", int(_lib.lib().nxd_oneshot_num_flags())),
+                    "sigs": (_c.c_void_p * tp)(*ctx.sig_peers), "stages": _host_ptrs(ctx, table, 0)}
+    return st["ar"]
+
+
+def oneshot_all_reduce(ctx, x: torch.Tensor, out: Optional[torch.Tensor] = None) -> Optional[torch.Tensor]:
+    """Sum of ``x`` (bf16, contiguous, numel % 8 == 0, <= 1 Mi elements) over the ranks of ``ctx`` in ONE kernel: every
+    rank pushes its values into all peers' staging slots and adds the tp slots in rank order (fp32).  ``None`` when
+    the message does not qualify (caller falls back to NCCL)."""
+    n = x.numel()
+    if x.dtype != torch.bfloat16 or not x.is_contiguous() or n % 8 or n == 0 or ctx.world > 8:
+        return None
+    per_cta = 2048
+    while (n + per_cta - 1) // per_cta > 132:
+        per_cta *= 2
+    if per_cta * 4 > 160 * 1024 or ((n + per_cta - 1) // per_cta) * per_cta > _AR_SLOT_ELEMS:
+        return None
+    s = _ar_state(ctx)
+    out = torch.empty_like(x) if out is None else out
+    epoch = ctx.next_epoch("ar")
+    rc = _lib.lib().nxd_allreduce_oneshot(_lib.ptr(x), _lib.ptr(out), _c.c_longlong(n), s["stages"], s["sigs"],
+                                          _c.c_size_t(_AR_SLOT_ELEMS), _c.c_int(ctx.world), _c.c_int(ctx.rank),
+                                          _c.c_int(s["slot"]), _c.c_uint(epoch), _lib.stream_ptr())
+    _lib.check(rc, "nxd_allreduce_oneshot")
+    return out
+
+
+def skinny_gemm(x2d: torch.Tensor, weight: torch.Tensor, residual: Optional[torch.Tensor] = None, ctx=None
+                ) -> Optional[torch.Tensor]:
+    """``x2d[B, K] @ weight[N, K]^T (+ residual)`` for B <= 16 rows, summed over the ranks of ``ctx`` when given: the
+    weight-streaming kernel of the token-generation path.  ``None`` when the shape does not qualify."""
+    B, K = x2d.shape
+    N = weight.shape[0]
+    if (B > _SKINNY_MAX_ROWS or B == 0 or x2d.dtype != torch.bfloat16 or weight.dtype != torch.bfloat16 or K % 8 or N % 4
+            or x2d.stride(1) != 1 or weight.stride(1) != 1 or x2d.stride(0) % 8 or weight.stride(0) % 8):
+        return None
+    kb = 1 if B <= 1 else 2 if B <= 2 else 4 if B <= 4 else 8 if B <= 8 else 16
+    if kb * K * 2 + kb * 64 * 4 > 160 * 1024:
+        return None
+    tp = 1 if ctx is None else ctx.world
+    if tp > 8 or (tp > 1 and kb * (N + 8192) > _AR_SLOT_ELEMS):
+        return None
+    out = torch.empty((B, N), dtype=torch.bfloat16, device=x2d.device)
+    if residual is not None:
+        residual = residual.reshape(B, N)
+        if residual.stride(1) != 1 or residual.stride(0) != out.stride(0):
+            residual = residual.contiguous()
+    if tp > 1:
+        s = _ar_state(ctx)
+        epoch = ctx.next_epoch("ar")
+        stages, sigs, slot, rank = s["stages"], s["sigs"], s["slot"], ctx.rank
+    else:
+        stages = sigs = None
+        slot = rank = epoch = 0
+    rc = _lib.lib().nxd_skinny_gemm_ar_bf16(
+        _lib.ptr(x2d), _lib.ptr(weight), _lib.ptr(residual), _lib.ptr(out), _c.c_int(B), _c.c_int(N), _c.c_int(K),
+        _c.c_longlong(x2d.stride(0)), _c.c_longlong(weight.stride(0)), _c.c_longlong(out.stride(0)), stages, sigs,
+        _c.c_size_t(_AR_SLOT_ELEMS), _c.c_int(tp), _c.c_int(rank), _c.c_int(slot), _c.c_uint(epoch), _lib.stream_ptr())
+    _lib.check(rc, "nxd_skinny_gemm_ar_bf16")
+    return out
+
+
+def fused_gemm_ar(ctx, x2d: torch.Tensor, weight: torch.Tensor, layout: str = "nt") -> Optional[torch.Tensor]:
+    """``all_reduce(x2d @ W_op)``: one kernel for token generation (<= 16 rows), tcgen05 GEMM + one-shot all-reduce
+    for messages up to 2 MB (short prefill), ``None`` beyond (NCCL's ring / NVLS wins on bandwidth there)."""
+    if x2d.dtype != torch.bfloat16 or weight.dtype != torch.bfloat16:
+        return None
+    if layout == "nt" and x2d.shape[0] <= _SKINNY_MAX_ROWS:
+        res = skinny_gemm(x2d, weight, ctx=ctx)
+        if res is not None:
+            return res
+    N = weight.shape[0] if layout == "nt" else weight.shape[1]
+    if x2d.shape[0] * N > _AR_SLOT_ELEMS or (x2d.shape[0] * N) % 8:
+        return None
+    from . import linear as gemm_ops
+
+    y = gemm_ops.gemm_nt(x2d, weight) if layout == "nt" else gemm_ops.gemm_nn(x2d, weight)
+    return oneshot_all_reduce(ctx, y.contiguous(), out=y if y.is_contiguous() else None)

@@ -93,9 +93,58 @@ def case_gemm_rs(rank, world):
         assert _rel(out, ref) < 8e-3, (it, _rel(out, ref))
 
 
+def case_gemm_ar(rank, world):
+    import torch.distributed as dist
+
+    from neuronx_distributed_llama3_2_b200.ops.fused_comm import fused_gemm_ar, oneshot_all_reduce, skinny_gemm
+    from neuronx_distributed_llama3_2_b200.parallel import parallel_state as ps
+
+    ctx = ps.get_symm_mem_context("tp")
+    # token generation shapes (skinny GEMM -> one-shot all-reduce in one kernel), repeated to exercise both parities
+    for it, (B, K, N) in enumerate([(4, 1024, 3072), (1, 512, 2048), (16, 4096, 3072), (3, 1024, 3080), (4, 1024, 3072),
+                                    (8, 384, 3072)]):
+        g = torch.Generator(device="cuda").manual_seed(31 * it + rank)
+        x = torch.randn(B, K, device="cuda", generator=g).bfloat16()
+        w = (torch.randn(N, K, device="cuda", generator=g) * 0.05).bfloat16()
+        out = fused_gemm_ar(ctx, x, w, "nt")
+        assert out is not None and out.shape == (B, N)
+        ref = x.float() @ w.float().t()
+        dist.all_reduce(ref)
+        assert _rel(out, ref) < 4e-3, (it, _rel(out, ref))
+        gathered = [torch.empty_like(out) for _ in range(world)]
+        dist.all_gather(gathered, out)
+        assert all(torch.equal(gathered[0], t) for t in gathered), "ranks disagree bitwise"
+    # with the residual add fused into the epilogue
+    x = torch.randn(4, 1024, device="cuda").bfloat16()
+    w = (torch.randn(3072, 1024, device="cuda") * 0.05).bfloat16()
+    res = torch.randn(4, 3072, device="cuda").bfloat16()
+    dist.broadcast(res, 0)
+    out = skinny_gemm(x, w, residual=res, ctx=ctx)
+    ref = x.float() @ w.float().t()
+    dist.all_reduce(ref)
+    assert _rel(out, ref + res.float()) < 4e-3
+    # short-prefill shape: tcgen05 GEMM + one-shot all-reduce
+    x = torch.randn(128, 1024, device="cuda").bfloat16()
+    out = fused_gemm_ar(ctx, x, w, "nt")
+    ref = x.float() @ w.float().t()
+    dist.all_reduce(ref)
+    assert out is not None and _rel(out, ref) < 8e-3
+    # stand-alone one-shot all-reduce, several sizes
+    for n in (8, 4096, 24576, 1 << 19, 1000 * 8):
+        t = torch.randn(n, device="cuda").bfloat16()
+        got = oneshot_all_reduce(ctx, t)
+        ref = t.float()
+        dist.all_reduce(ref)
+        assert got is not None and _rel(got, ref) < 4e-3, n
+
+
 def test_fused_ag_gemm_tp2():
     _spawn("case_ag_gemm", 2)
 
 
 def test_fused_gemm_rs_tp2():
     _spawn("case_gemm_rs", 2)
+
+
+def test_fused_gemm_ar_tp2():
+    _spawn("case_gemm_ar", 2)

@@ -431,3 +431,19 @@ def test_flash_attention_large_magnitude_rows():
     out = A.flash_attn_func(q, k, v, causal=False)
     ref = A.attention_ref(q.float(), k.float(), v.float(), False, None)
     assert _rel_err(out, ref) < 1.5e-2
+
+
+@pytest.mark.parametrize("B,K,N", [(1, 2048, 512), (4, 3072, 1024), (5, 1024, 3080), (16, 4096, 256)])
+def test_skinny_gemm(B, K, N):
+    from neuronx_distributed_llama3_2_b200.ops.fused_comm import skinny_gemm
+
+    x = torch.randn(B, K, device="cuda").bfloat16()
+    w = (torch.randn(N, K, device="cuda") * 0.05).bfloat16()
+    res = torch.randn(B, N, device="cuda").bfloat16()
+    out = skinny_gemm(x, w)
+    ref = x.float() @ w.float().t()
+    assert out is not None
+    assert ((out.float() - ref).norm() / ref.norm()).item() < 4e-3
+    out = skinny_gemm(x, w, residual=res)
+    ref = ref + res.float()
+    assert ((out.float() - ref).norm() / ref.norm()).item() < 4e-3
