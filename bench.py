@@ -43,6 +43,8 @@ def parse_args():
     ap.add_argument("--micro-batch", type=int, default=int(os.environ.get("NXD_BENCH_MB", 1)))
     ap.add_argument("--layers", type=int, default=0, help="debug only: override the layer count (marks the run invalid)")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--profile", default="", help="diagnosis only: write a kernel timeline summary of 2 steps (rank 0) "
+                    "to this file instead of timing (numbers under a profiler are never bench values)")
     return ap.parse_args()
 
 
@@ -101,6 +103,51 @@ class ClockSampler:
                     reasons.add(n)
         return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
                 "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def profile_steps(args, step, barrier, rank, world):
+    """Kernel timeline of two steps through CUPTI (torch.profiler): per-kernel totals, GPU busy time and idle gaps."""
+    import torch
+    from torch.profiler import ProfilerActivity, profile
+
+    barrier()
+    with profile(activities=[ProfilerActivity.CUDA, ProfilerActivity.CPU]) as prof:
+        for i in range(2):
+            step(i)
+        torch.cuda.synchronize()
+    barrier()
+    if rank != 0:
+        return
+    evs = [e for e in prof.events() if e.device_type == torch.autograd.DeviceType.CUDA]
+    spans = sorted((e.time_range.start, e.time_range.end, e.name) for e in evs)
+    by_name = {}
+    for a, b, n in spans:
+        d = by_name.setdefault(n[:90], [0.0, 0])
+        d[0] += b - a
+        d[1] += 1
+    busy, cur_a, cur_b = 0.0, None, None
+    gaps = []
+    for a, b, _ in spans:
+        if cur_b is None:
+            cur_a, cur_b = a, b
+        elif a <= cur_b:
+            cur_b = max(cur_b, b)
+        else:
+            busy += cur_b - cur_a
+            gaps.append(a - cur_b)
+            cur_a, cur_b = a, b
+    if cur_b is not None:
+        busy += cur_b - cur_a
+    wall = spans[-1][1] - spans[0][0] if spans else 0.0
+    lines = [f"# 2 steps, rank 0 of {world}, impl={args.impl}; times in us (CUPTI, profiler overhead included)",
+             f"wall {wall:.0f}  gpu_busy {busy:.0f}  idle {wall - busy:.0f}  kernels {len(spans)}  "
+             f"gaps>5us {sum(1 for g in gaps if g > 5)} totalling {sum(g for g in gaps if g > 5):.0f}"]
+    for n, (t, c) in sorted(by_name.items(), key=lambda kv: -kv[1][0])[:45]:
+        lines.append(f"{t:10.0f} us  {c:6d} x  {t / c:8.1f}  {n}")
+    os.makedirs(os.path.dirname(os.path.abspath(args.profile)), exist_ok=True)
+    with open(args.profile, "w") as f:
+        f.write("\n".join(lines) + "\n")
+    print(json.dumps({"profile": args.profile, "invalid": "profiler run"}))
 
 
 def main():
@@ -197,8 +244,13 @@ def main():
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t[0]), launches, clocks, last
 
+    first_loss = first_norm = None
     for i in range(max(args.warmup, 0)):
-        step_dev(i)
+        l = step_dev(i)
+        if i == 0:   # parity probe: identical weights and batch in every arm with the same seed / tp
+            first_loss, first_norm = float(l.detach()), float(opt.grad_norm)
+    if args.profile:
+        return profile_steps(args, step_dev, barrier, rank, world)
     ms, launches, clocks, last_loss = timed(step_dev, args.steps)
     tokens = B * S * args.steps
     value = tokens / (ms / 1e3)
@@ -232,6 +284,7 @@ def main():
             "mfu_of_measured_sustained": (flops / 1e12 / world) / peaks["bf16_tflops_sustained"]
             if peaks.get("bf16_tflops_sustained") else None,
             "loss": float(last_loss.detach()) if isinstance(last_loss, torch.Tensor) else last_loss,
+            "first_step_loss": first_loss, "first_step_grad_norm": first_norm,
             "clocks": clocks, "e2e": e2e, "gpu_launches": launches,
         }
         if args.layers:

@@ -1,4 +1,4 @@
-// Flash attention BACKWARD on 5th-gen tensor cores (tcgen05 + TMEM + TMA), sm_100a, head dim 128.
+// Flash attention BACKWARD on 5th-gen tensor cores (tcgen05 + TMEM + TMA), sm_100a, head dim 128 or 64.
 //
 // Same contract as nxd_flash_attn_bwd in flash_attn.cu (reference: the external NKI `flash_attn_bwd` kernel behind
 // src/neuronx_distributed/kernels/flash_attn.py:19-28,103-148).
@@ -18,6 +18,10 @@
 // TMEM -> smem (transposed back) and added into an fp32 dQ accumulator with TMA reduce-add; dK (x scale) and dV
 // leave through smem + TMA store.  The GQA reduction of dK/dV over the q-head group happens in TMEM for free.
 //
+// Head dim 64 (Llama-3.2-1B) runs the same pipeline with one 64-column group per tile.  Its dQ^T MMA keeps M = 128:
+// the MN-major A descriptor then walks 64 rows past the K tile into the V tile, which fills TMEM lanes 64..127 with
+// finite garbage that nobody reads -- cheaper than a second code path for the M = 64 TMEM layout.
+//
 // warp 0: TMA producer (K, V once; Q_i, dO_i, L_i, Delta_i through a 2-stage ring)   warp 1: TMEM alloc + MMA issue
 // warps 2-5: softmax-backward math, dQ drain, epilogue.
 #include "attn_tc_common.cuh"
@@ -29,19 +33,20 @@ using namespace nxd_attn;
 
 constexpr int kBN = 128;  // K/V rows per CTA
 constexpr int kBM = 64;   // query rows per tile
-constexpr int kD = 128;
 constexpr int kThreadsBwd = 192;
 
 struct BwdParams {
     const float* lse_pad;    // [B*Hq, Sq_pad] log2-domain LSE, +inf in the padding
     const float* delta_pad;  // [B*Hq, Sq_pad]
     int B, Hq, Hkv, Sq, Sk, Sq_pad;
-    int pos_q[3], pos_do[3], pos_k[3], pos_v[3], pos_dk[3], pos_dv[3], pos_dq[3];
+    int nsplit;              // CTAs that share one (kv block, kv head): each walks 1/nsplit of the (q head, q tile) list
+    int pos_q[3], pos_do[3], pos_k[3], pos_v[3], pos_dk[3], pos_dv[3], pos_dq[3], pos_acc[3];
     float scale, scale_log2;
 };
 
+template <int kD>
 struct BwdSmem {
-    static constexpr int kKOff = 0;                       // [2 groups][128 rows][64]   32 KB
+    static constexpr int kKOff = 0;                       // [kD / 64 groups][128 rows][64]   32 KB at D = 128
     static constexpr int kVOff = kKOff + kBN * kD * 2;    // 32 KB
     static constexpr int kQOff = kVOff + kBN * kD * 2;    // 2 stages x [2 groups][64 rows][64]   32 KB
     static constexpr int kDOOff = kQOff + 2 * kBM * kD * 2;   // 32 KB
@@ -51,21 +56,23 @@ struct BwdSmem {
     static constexpr int kLOff = kDQOff + kBM * kD * 4;       // 2 stages x (64 L + 64 Delta) floats   1 KB
     static constexpr int kBarOff = kLOff + 2 * 2 * kBM * 4;
     static constexpr int kNumBars = 1 + 2 + 2 + 6;
-    static constexpr int kBytes = kBarOff + kNumBars * 8 + 16 + 1024;
+    // at least 120 KB so that only ONE CTA fits an SM: each CTA allocates all 512 TMEM columns
+    static constexpr int kUsed = kBarOff + kNumBars * 8 + 16 + 1024;
+    static constexpr int kBytes = kUsed < 120 * 1024 ? 120 * 1024 : kUsed;
     static constexpr int kStageBytes = kBM * kD * 2;          // one Q (or dO) tile
     static constexpr int kTxPerStage = 2 * kStageBytes + 2 * kBM * 4;
 };
-static_assert(BwdSmem::kBytes <= 232448, "shared memory budget exceeded");
+static_assert(BwdSmem<128>::kBytes <= 232448, "shared memory budget exceeded");
 
-constexpr uint32_t kColDK = 0, kColDV = 128, kColST = 256, kColDPT = 320, kColDQT = 384;
-
-template <bool CAUSAL>
+template <int kD, bool CAUSAL>
 __global__ void __launch_bounds__(kThreadsBwd, 1)
 fa_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_do,
                  const __grid_constant__ CUtensorMap tmap_k, const __grid_constant__ CUtensorMap tmap_v,
                  const __grid_constant__ CUtensorMap tmap_dk, const __grid_constant__ CUtensorMap tmap_dv,
-                 const __grid_constant__ CUtensorMap tmap_dq, const BwdParams p) {
-    using L = BwdSmem;
+                 const __grid_constant__ CUtensorMap tmap_dq, const __grid_constant__ CUtensorMap tmap_dk_acc,
+                 const __grid_constant__ CUtensorMap tmap_dv_acc, const BwdParams p) {
+    using L = BwdSmem<kD>;
+    constexpr uint32_t kColDK = 0, kColDV = kD, kColST = 2 * kD, kColDPT = 2 * kD + 64, kColDQT = 2 * kD + 128;
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* sK = smem + L::kKOff;
@@ -89,7 +96,7 @@ fa_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
     uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bars + L::kNumBars);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int nbk = blockIdx.x, hkv = blockIdx.y, b = blockIdx.z;
+    const int nbk = blockIdx.x, hkv = blockIdx.y / p.nsplit, split = blockIdx.y % p.nsplit, b = blockIdx.z;
     const int group = p.Hq / p.Hkv;
     const int n0 = nbk * kBN;
     const int offset = p.Sk - p.Sq;
@@ -97,7 +104,11 @@ fa_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
     if (CAUSAL) mb_start = max(0, (n0 - offset) / kBM);
     const int mb_end = (p.Sq + kBM - 1) / kBM;
     const int tiles_per_head = max(mb_end - mb_start, 0);
-    const int total = tiles_per_head * group;
+    // (q head of the group, q tile) pairs of this K/V block, flattened; this CTA owns the slice [it0, it0 + total)
+    const int all_tiles = tiles_per_head * group;
+    const int it0 = (int)((long long)all_tiles * split / p.nsplit);
+    const int total = (int)((long long)all_tiles * (split + 1) / p.nsplit) - it0;
+    if (p.nsplit > 1 && total == 0) return;   // nothing to add into the shared dK / dV accumulators
 
     if (warp == 0 && lane == 0) {
         ptx::prefetch_tensormap(&tmap_q);
@@ -140,8 +151,8 @@ fa_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
             for (int it = 0; it < total; ++it) {
                 const int st = it & 1;
                 const uint32_t ph = (uint32_t)(it >> 1) & 1u;
-                const int hq = hkv * group + it / tiles_per_head;
-                const int m0 = (mb_start + it % tiles_per_head) * kBM;
+                const int hq = hkv * group + (it0 + it) / tiles_per_head;
+                const int m0 = (mb_start + (it0 + it) % tiles_per_head) * kBM;
                 ptx::mbar_wait(&qdo_empty[st], ph ^ 1u);
                 ptx::mbar_arrive_expect_tx(&qdo_full[st], L::kTxPerStage);
 #pragma unroll
@@ -163,7 +174,7 @@ fa_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
         if (lane == 0 && total > 0) {
             constexpr uint32_t idesc_st = ptx::make_idesc_bf16(kBN, kBM, 0, 0);   // S^T, dP^T: 128 x 64, K-major A/B
             constexpr uint32_t idesc_kv = ptx::make_idesc_bf16(kBN, kD, 0, 1);    // dV, dK: 128 x 128, B MN-major
-            constexpr uint32_t idesc_dq = ptx::make_idesc_bf16(kD, kBM, 1, 1);    // dQ^T: 128 x 64, A and B MN-major
+            constexpr uint32_t idesc_dq = ptx::make_idesc_bf16(128, kBM, 1, 1);   // dQ^T: 128 x 64, A and B MN-major
             const uint32_t k_addr = ptx::smem_u32(sK), v_addr = ptx::smem_u32(sV), q_addr = ptx::smem_u32(sQ),
                            do_addr = ptx::smem_u32(sDO), pt_addr = ptx::smem_u32(sPt), dst_addr = ptx::smem_u32(sDSt);
             auto issue_scores = [&](int it) {
@@ -233,23 +244,29 @@ fa_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
 
         auto drain_dq = [&](int it) {
             // dQ^T(it) [d = row][64 q] -> sDQ [d group of 32][q][32 floats] (128-byte swizzled rows) -> TMA reduce-add
-            const int hq = hkv * group + it / tiles_per_head;
-            const int m0 = (mb_start + it % tiles_per_head) * kBM;
+            const int hq = hkv * group + (it0 + it) / tiles_per_head;
+            const int m0 = (mb_start + (it0 + it) % tiles_per_head) * kBM;
             ptx::mbar_wait(dq_full, (uint32_t)it & 1u);
             ptx::tcgen05_fence_after();
+            const bool has_rows = q4 * 32 < kD;          // head dim 64: TMEM lanes 64..127 of dQ^T are padding
             uint32_t v[64];
-            ptx::tmem_ld_32x32b_x32(tmem_base + kColDQT + lane_off, v);
-            ptx::tmem_ld_32x32b_x32(tmem_base + kColDQT + lane_off + 32, v + 32);
-            ptx::tmem_ld_wait();
+            if (has_rows) {
+                ptx::tmem_ld_32x32b_x32(tmem_base + kColDQT + lane_off, v);
+                ptx::tmem_ld_32x32b_x32(tmem_base + kColDQT + lane_off + 32, v + 32);
+                ptx::tmem_ld_wait();
+            }
             ptx::tcgen05_fence_before();
             ptx::mbar_arrive(dq_empty);
             if (tid128 == 0) ptx::bulk_wait_read<0>();   // the previous reduce-add has finished reading sDQ
             named_bar_sync(1, 128);
-            uint8_t* base = sDQ + q4 * (kBM * 128);      // d group of 32 == this warp
+            if (has_rows) {
+                uint8_t* base = sDQ + q4 * (kBM * 128);      // d group of 32 == this warp
 #pragma unroll
-            for (int qq = 0; qq < kBM; ++qq) {
-                float* dst = reinterpret_cast<float*>(base + qq * 128 + (((lane >> 2) ^ (qq & 7)) << 4) + (lane & 3) * 4);
-                *dst = __uint_as_float(v[qq]) * p.scale;
+                for (int qq = 0; qq < kBM; ++qq) {
+                    float* dst =
+                        reinterpret_cast<float*>(base + qq * 128 + (((lane >> 2) ^ (qq & 7)) << 4) + (lane & 3) * 4);
+                    *dst = __uint_as_float(v[qq]) * p.scale;
+                }
             }
             ptx::fence_proxy_async();
             named_bar_sync(1, 128);
@@ -267,7 +284,7 @@ fa_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
 
         for (int it = 0; it < total; ++it) {
             const int st = it & 1;
-            const int m0 = (mb_start + it % tiles_per_head) * kBM;
+            const int m0 = (mb_start + (it0 + it) % tiles_per_head) * kBM;
             ptx::mbar_wait(st_full, (uint32_t)it & 1u);
             ptx::tcgen05_fence_after();
             uint32_t s[kBM], dp[kBM];
@@ -322,44 +339,83 @@ fa_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
         if (total == 0) ptx::mbar_wait(kv_full, 0);  // nothing consumed K/V: let their TMA land before the tiles are reused
         if (tid128 == 0) ptx::bulk_wait_read<0>();
         named_bar_sync(1, 128);
-        // ---- epilogue: dV, dK (x scale) -> bf16 -> smem (the dead K / V tiles) -> TMA store ----
+        if (p.nsplit > 1) {
+            // ---- split epilogue: this CTA holds PARTIAL dV / dK -> fp32 -> smem -> TMA reduce-add into the accumulators
+            // (32 rows x 32 columns per warp and step, two 4 KB staging buffers per warp in the dead K / V tiles)
+            uint8_t* stg = sK + q4 * 8192;
+            int buf = 0;
 #pragma unroll 1
-        for (int which = 0; which < 2; ++which) {
-            uint8_t* stage = which == 0 ? sV : sK;
-            const uint32_t col = which == 0 ? kColDV : kColDK;
-            const float mul = which == 0 ? 1.f : p.scale;
+            for (int which = 0; which < 2; ++which) {
+                const uint32_t col = which == 0 ? kColDV : kColDK;
+                const float mul = which == 0 ? 1.f : p.scale;
 #pragma unroll 1
-            for (int g = 0; g < kD / 64; ++g) {
-                uint32_t o[64];
-                if (total > 0) {
-                    ptx::tmem_ld_32x32b_x32(tmem_base + col + lane_off + g * 64, o);
-                    ptx::tmem_ld_32x32b_x32(tmem_base + col + lane_off + g * 64 + 32, o + 32);
+                for (int g = 0; g < kD / 32; ++g) {
+                    uint32_t o[32];
+                    ptx::tmem_ld_32x32b_x32(tmem_base + col + lane_off + g * 32, o);
                     ptx::tmem_ld_wait();
-                } else {
+                    if (lane == 0) ptx::bulk_wait_read<1>();
+                    __syncwarp();
+                    uint8_t* dst = stg + buf * 4096 + lane * 128;
 #pragma unroll
-                    for (int e = 0; e < 64; ++e) o[e] = 0u;
-                }
-                uint8_t* dst = stage + g * (kBN * 128) + row * 128;
-#pragma unroll
-                for (int c = 0; c < 8; ++c) {
-                    uint32_t w[4];
-#pragma unroll
-                    for (int e = 0; e < 4; ++e) {
-                        bf162 t = __floats2bfloat162_rn(__uint_as_float(o[8 * c + 2 * e]) * mul,
-                                                        __uint_as_float(o[8 * c + 2 * e + 1]) * mul);
-                        w[e] = *reinterpret_cast<uint32_t*>(&t);
+                    for (int c = 0; c < 8; ++c)
+                        *reinterpret_cast<float4*>(dst + ((c ^ (lane & 7)) << 4)) =
+                            make_float4(__uint_as_float(o[4 * c]) * mul, __uint_as_float(o[4 * c + 1]) * mul,
+                                        __uint_as_float(o[4 * c + 2]) * mul, __uint_as_float(o[4 * c + 3]) * mul);
+                    ptx::fence_proxy_async();
+                    __syncwarp();
+                    if (lane == 0) {
+                        if (n0 + q4 * 32 < p.Sk) {
+                            int c[4];
+                            c[0] = g * 32;
+                            coords(p.pos_acc, n0 + q4 * 32, hkv, b, c);
+                            tma_reduce_add_4d(which == 0 ? &tmap_dv_acc : &tmap_dk_acc, stg + buf * 4096, c[0], c[1], c[2],
+                                              c[3]);
+                        }
+                        ptx::bulk_commit();
                     }
-                    *reinterpret_cast<uint4*>(dst + ((c ^ (row & 7)) << 4)) = make_uint4(w[0], w[1], w[2], w[3]);
+                    buf ^= 1;
                 }
-                ptx::fence_proxy_async();
-                __syncwarp();
-                if (lane == 0 && n0 + q4 * 32 < p.Sk) {
-                    int c[4];
-                    c[0] = g * 64;
-                    coords(which == 0 ? p.pos_dv : p.pos_dk, n0 + q4 * 32, hkv, b, c);
-                    tma_store_4d(which == 0 ? &tmap_dv : &tmap_dk, stage + g * (kBN * 128) + q4 * 32 * 128, c[0], c[1],
-                                 c[2], c[3]);
-                    ptx::bulk_commit();
+            }
+        } else {
+            // ---- epilogue: dV, dK (x scale) -> bf16 -> smem (the dead K / V tiles) -> TMA store ----
+    #pragma unroll 1
+            for (int which = 0; which < 2; ++which) {
+                uint8_t* stage = which == 0 ? sV : sK;
+                const uint32_t col = which == 0 ? kColDV : kColDK;
+                const float mul = which == 0 ? 1.f : p.scale;
+    #pragma unroll 1
+                for (int g = 0; g < kD / 64; ++g) {
+                    uint32_t o[64];
+                    if (total > 0) {
+                        ptx::tmem_ld_32x32b_x32(tmem_base + col + lane_off + g * 64, o);
+                        ptx::tmem_ld_32x32b_x32(tmem_base + col + lane_off + g * 64 + 32, o + 32);
+                        ptx::tmem_ld_wait();
+                    } else {
+    #pragma unroll
+                        for (int e = 0; e < 64; ++e) o[e] = 0u;
+                    }
+                    uint8_t* dst = stage + g * (kBN * 128) + row * 128;
+    #pragma unroll
+                    for (int c = 0; c < 8; ++c) {
+                        uint32_t w[4];
+    #pragma unroll
+                        for (int e = 0; e < 4; ++e) {
+                            bf162 t = __floats2bfloat162_rn(__uint_as_float(o[8 * c + 2 * e]) * mul,
+                                                            __uint_as_float(o[8 * c + 2 * e + 1]) * mul);
+                            w[e] = *reinterpret_cast<uint32_t*>(&t);
+                        }
+                        *reinterpret_cast<uint4*>(dst + ((c ^ (row & 7)) << 4)) = make_uint4(w[0], w[1], w[2], w[3]);
+                    }
+                    ptx::fence_proxy_async();
+                    __syncwarp();
+                    if (lane == 0 && n0 + q4 * 32 < p.Sk) {
+                        int c[4];
+                        c[0] = g * 64;
+                        coords(which == 0 ? p.pos_dv : p.pos_dk, n0 + q4 * 32, hkv, b, c);
+                        tma_store_4d(which == 0 ? &tmap_dv : &tmap_dk, stage + g * (kBN * 128) + q4 * 32 * 128, c[0], c[1],
+                                     c[2], c[3]);
+                        ptx::bulk_commit();
+                    }
                 }
             }
         }
@@ -376,7 +432,7 @@ __global__ void fa_bwd_tc_prep_kernel(const bf16* __restrict__ o, const bf16* __
                                       const float* __restrict__ lse, float* __restrict__ lse_pad,
                                       float* __restrict__ delta_pad, long long o_sb, long long o_sh, long long o_ss,
                                       long long do_sb, long long do_sh, long long do_ss, int B, int Hq, int Sq,
-                                      int Sq_pad) {
+                                      int Sq_pad, int D) {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const long long r = (long long)blockIdx.x * (blockDim.x >> 5) + warp;
     const long long total = (long long)B * Hq * Sq_pad;
@@ -394,8 +450,7 @@ __global__ void fa_bwd_tc_prep_kernel(const bf16* __restrict__ o, const bf16* __
     const bf16* op = o + b * o_sb + h * o_sh + (long long)i * o_ss;
     const bf16* dp = dout + b * do_sb + h * do_sh + (long long)i * do_ss;
     float acc = 0.f;
-#pragma unroll
-    for (int c = 0; c < kD / 64; ++c) {
+    for (int c = 0; c < D / 64; ++c) {
         const float2 a = __bfloat1622float2(reinterpret_cast<const bf162*>(op)[lane + c * 32]);
         const float2 g = __bfloat1622float2(reinterpret_cast<const bf162*>(dp)[lane + c * 32]);
         acc += a.x * g.x + a.y * g.y;
@@ -409,7 +464,7 @@ __global__ void fa_bwd_tc_prep_kernel(const bf16* __restrict__ o, const bf16* __
 
 // fp32 [B, Hq, Sq, D] accumulator -> strided bf16 dq
 __global__ void fa_bwd_tc_dq_convert_kernel(const float* __restrict__ acc, bf16* __restrict__ dq, long long sb,
-                                            long long sh, long long ss, int B, int Hq, int Sq) {
+                                            long long sh, long long ss, int B, int Hq, int Sq, int kD) {
     const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;  // one thread = 8 elements
     const long long total = (long long)B * Hq * Sq * (kD / 8);
     if (idx >= total) return;
@@ -424,15 +479,45 @@ __global__ void fa_bwd_tc_dq_convert_kernel(const float* __restrict__ acc, bf16*
     reinterpret_cast<bf16x8*>(dq + b * sb + h * sh + (long long)i * ss)[c] = pack8(f);
 }
 
+template <int kD, bool CAUSAL>
+int launch_bwd_tc(dim3 grid, cudaStream_t st, const CUtensorMap& tq, const CUtensorMap& tdo, const CUtensorMap& tk,
+                  const CUtensorMap& tv, const CUtensorMap& tdk, const CUtensorMap& tdv, const CUtensorMap& tdq,
+                  const CUtensorMap& tdka, const CUtensorMap& tdva, const BwdParams& p) {
+    static cudaError_t once = cudaFuncSetAttribute(fa_bwd_tc_kernel<kD, CAUSAL>,
+                                                   cudaFuncAttributeMaxDynamicSharedMemorySize, BwdSmem<kD>::kBytes);
+    NXD_CHECK_CUDA(once);
+    fa_bwd_tc_kernel<kD, CAUSAL><<<grid, kThreadsBwd, BwdSmem<kD>::kBytes, st>>>(tq, tdo, tk, tv, tdk, tdv, tdq, tdka, tdva, p);
+    NXD_LAUNCH_CHECK();
+    return 0;
+}
+
 }  // namespace
 
-// Head dim 128 only.  scratch: lse_pad and delta_pad are [B*Hq*Sq_pad] floats (Sq_pad = Sq rounded up to 64);
-// dq_accum is a ZERO-FILLED [B, Hq, Sq, 128] fp32 buffer.  strides as nxd_flash_attn_bwd (24 values).
+// Number of CTAs that should share one (K/V block, kv head) so that the grid fills the GPU: 1 = every CTA owns its
+// dK / dV tile (no accumulators needed), > 1 = pass `dkv_accum` to nxd_flash_attn_bwd_tc.
+NXD_API int nxd_flash_attn_bwd_tc_num_splits(int B, int Hq, int Hkv, int Sq, int Sk) {
+    int dev = 0, sms = 148;
+    if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const long long ctas = (long long)((Sk + kBN - 1) / kBN) * Hkv * B;
+    if (ctas >= 2LL * sms) return 1;
+    const int group = Hq / (Hkv > 0 ? Hkv : 1);
+    const long long iters = (long long)((Sq + kBM - 1) / kBM) * group;     // longest (q head, q tile) list of a CTA
+    long long n = (4LL * sms + ctas - 1) / ctas;
+    if (n > iters / 8) n = iters / 8;                                      // keep >= 8 tiles per CTA (prologue / epilogue)
+    if (n > 16) n = 16;
+    return n < 1 ? 1 : (int)n;
+}
+
+// Head dim 128 or 64.  scratch: lse_pad and delta_pad are [B*Hq*Sq_pad] floats (Sq_pad = Sq rounded up to 64);
+// dq_accum is a ZERO-FILLED [B, Hq, Sq, D] fp32 buffer.  dkv_accum: NULL, or a ZERO-FILLED [2, B, Hkv, Sk, D] fp32
+// buffer -- then nxd_flash_attn_bwd_tc_num_splits() CTAs share every K/V block (small batch x heads: tensor
+// parallel shards, long sequences) and add their partial dK / dV with TMA reduce-add.  strides as nxd_flash_attn_bwd
+// (24 values).
 NXD_API int nxd_flash_attn_bwd_tc(const void* q, const void* k, const void* v, const void* o, const void* dout,
-                                  const float* lse, float* lse_pad, float* delta_pad, float* dq_accum, void* dq,
-                                  void* dk, void* dv, const long long* strides, int B, int Hq, int Hkv, int Sq, int Sk,
-                                  int D, float scale, int causal, void* stream) {
-    NXD_REQUIRE(D == kD, "flash_attn_bwd_tc: head dim %d not supported (128 only)", D);
+                                  const float* lse, float* lse_pad, float* delta_pad, float* dq_accum, float* dkv_accum,
+                                  void* dq, void* dk, void* dv, const long long* strides, int B, int Hq, int Hkv, int Sq,
+                                  int Sk, int D, float scale, int causal, void* stream) {
+    NXD_REQUIRE(D == 128 || D == 64, "flash_attn_bwd_tc: head dim %d not supported (64 or 128)", D);
     NXD_REQUIRE(B > 0 && Hq > 0 && Hkv > 0 && Sq > 0 && Sk > 0 && Hq % Hkv == 0, "flash_attn_bwd_tc: bad problem");
     for (int i = 0; i < 24; ++i)
         NXD_REQUIRE(strides[i] % 8 == 0, "flash_attn_bwd_tc: stride %d (=%lld) must be a multiple of 8 elements", i,
@@ -443,14 +528,15 @@ NXD_API int nxd_flash_attn_bwd_tc(const void* q, const void* k, const void* v, c
     p.Sq_pad = (Sq + kBM - 1) / kBM * kBM;
     p.lse_pad = lse_pad; p.delta_pad = delta_pad;
     p.scale = scale; p.scale_log2 = scale * 1.4426950408889634f;
+    p.nsplit = dkv_accum ? nxd_flash_attn_bwd_tc_num_splits(B, Hq, Hkv, Sq, Sk) : 1;
     {
         const long long rows = (long long)B * Hq * p.Sq_pad;
         fa_bwd_tc_prep_kernel<<<(unsigned)((rows + 7) / 8), 256, 0, st>>>(
             (const bf16*)o, (const bf16*)dout, lse, lse_pad, delta_pad, strides[9], strides[10], strides[11], strides[12],
-            strides[13], strides[14], B, Hq, Sq, p.Sq_pad);
+            strides[13], strides[14], B, Hq, Sq, p.Sq_pad, D);
         NXD_LAUNCH_CHECK();
     }
-    CUtensorMap tq, tdo, tk, tv, tdk, tdv, tdq;
+    CUtensorMap tq, tdo, tk, tv, tdk, tdv, tdq, tdka, tdva;
     int rc;
     if ((rc = make_tmap_bhsd(&tq, q, D, Sq, Hq, B, strides[2], strides[1], strides[0], kBM, p.pos_q))) return rc;
     if ((rc = make_tmap_bhsd(&tk, k, D, Sk, Hkv, B, strides[5], strides[4], strides[3], kBN, p.pos_k))) return rc;
@@ -461,23 +547,38 @@ NXD_API int nxd_flash_attn_bwd_tc(const void* q, const void* k, const void* v, c
     if ((rc = make_tmap_bhsd(&tdq, dq_accum, D, Sq, Hq, B, D, (long long)Sq * D, (long long)Hq * Sq * D, kBM, p.pos_dq,
                              4)))
         return rc;
-    dim3 grid((Sk + kBN - 1) / kBN, Hkv, B);
-    if (causal) {
-        static cudaError_t once = cudaFuncSetAttribute(fa_bwd_tc_kernel<true>,
-                                                       cudaFuncAttributeMaxDynamicSharedMemorySize, BwdSmem::kBytes);
-        NXD_CHECK_CUDA(once);
-        fa_bwd_tc_kernel<true><<<grid, kThreadsBwd, BwdSmem::kBytes, st>>>(tq, tdo, tk, tv, tdk, tdv, tdq, p);
+    const long long kv_elems = (long long)B * Hkv * Sk * D;
+    float* dk_acc = p.nsplit > 1 ? dkv_accum : dq_accum;   // unused maps still have to be valid
+    float* dv_acc = p.nsplit > 1 ? dkv_accum + kv_elems : dq_accum;
+    if (p.nsplit > 1) {
+        if ((rc = make_tmap_bhsd(&tdka, dk_acc, D, Sk, Hkv, B, D, (long long)Sk * D, (long long)Hkv * Sk * D, 32, p.pos_acc, 4)))
+            return rc;
+        if ((rc = make_tmap_bhsd(&tdva, dv_acc, D, Sk, Hkv, B, D, (long long)Sk * D, (long long)Hkv * Sk * D, 32, p.pos_acc, 4)))
+            return rc;
     } else {
-        static cudaError_t once = cudaFuncSetAttribute(fa_bwd_tc_kernel<false>,
-                                                       cudaFuncAttributeMaxDynamicSharedMemorySize, BwdSmem::kBytes);
-        NXD_CHECK_CUDA(once);
-        fa_bwd_tc_kernel<false><<<grid, kThreadsBwd, BwdSmem::kBytes, st>>>(tq, tdo, tk, tv, tdk, tdv, tdq, p);
+        tdka = tdq;
+        tdva = tdq;
     }
-    NXD_LAUNCH_CHECK();
+    dim3 grid((Sk + kBN - 1) / kBN, Hkv * p.nsplit, B);
+    if (D == 128)
+        rc = causal ? launch_bwd_tc<128, true>(grid, st, tq, tdo, tk, tv, tdk, tdv, tdq, tdka, tdva, p)
+                    : launch_bwd_tc<128, false>(grid, st, tq, tdo, tk, tv, tdk, tdv, tdq, tdka, tdva, p);
+    else
+        rc = causal ? launch_bwd_tc<64, true>(grid, st, tq, tdo, tk, tv, tdk, tdv, tdq, tdka, tdva, p)
+                    : launch_bwd_tc<64, false>(grid, st, tq, tdo, tk, tv, tdk, tdv, tdq, tdka, tdva, p);
+    if (rc) return rc;
+    if (p.nsplit > 1) {
+        const long long n = kv_elems / 8;
+        fa_bwd_tc_dq_convert_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(dk_acc, (bf16*)dk, strides[18], strides[19],
+                                                                                strides[20], B, Hkv, Sk, D);
+        fa_bwd_tc_dq_convert_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(dv_acc, (bf16*)dv, strides[21], strides[22],
+                                                                                strides[23], B, Hkv, Sk, D);
+        NXD_LAUNCH_CHECK();
+    }
     {
-        const long long n = (long long)B * Hq * Sq * (kD / 8);
+        const long long n = (long long)B * Hq * Sq * (D / 8);
         fa_bwd_tc_dq_convert_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(
-            dq_accum, (bf16*)dq, strides[15], strides[16], strides[17], B, Hq, Sq);
+            dq_accum, (bf16*)dq, strides[15], strides[16], strides[17], B, Hq, Sq, D);
         NXD_LAUNCH_CHECK();
     }
     return 0;

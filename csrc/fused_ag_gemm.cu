@@ -211,12 +211,20 @@ ag_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a_local, const __grid_co
     const int num_tiles = ag.tp * m_tiles_per_slab * num_n_tiles;
     const int num_k_blocks = (K + kBlockK - 1) / kBlockK;
 
-    // tile -> (slab in arrival order, m tile inside the slab, n tile); n fastest so that A rows are shared in L2
+    // tile -> (slab, m tile inside the slab, n tile) in ARRIVAL order; n fastest so that A rows are shared in L2.
+    // Own slab first (no wait).  Every peer pushes chunk c of its shard to all ranks at the same time, so the remote
+    // rows arrive chunk-major: chunk 0 of every slab, then chunk 1 of every slab, ...
     auto tile_coords_ag = [&](int tile, int& slab, int& mt, int& tn) {
         tn = tile % num_n_tiles;
         const int mg = tile / num_n_tiles;
-        mt = mg % m_tiles_per_slab;
-        slab = (ag.rank + mg / m_tiles_per_slab) % ag.tp;
+        if (mg < m_tiles_per_slab) {
+            mt = mg;
+            slab = ag.rank;
+        } else {
+            const int idx = mg - m_tiles_per_slab;
+            mt = idx / (ag.tp - 1);
+            slab = (ag.rank + 1 + idx % (ag.tp - 1)) % ag.tp;
+        }
     };
 
     if (warp == 0 && lane == 0) {

@@ -37,7 +37,7 @@ struct ArArgs {
     size_t slot_elems;             // floats per (parity, source) slot
     int slot;                      // first flag; flag [cta][source rank]
     int tp, rank;
-    uint32_t epoch;                // call counter of this (staging, flags) pair, starts at 1
+    uint32_t* state;               // local device memory: [0] = calls completed on this staging region, [1] = CTAs done
 };
 
 __device__ __forceinline__ void ar_st_release_sys(uint32_t* p, uint32_t v) {
@@ -56,8 +56,9 @@ __device__ __forceinline__ float4 ar_ld_cg(const float4* p) {
 
 // Push `n4` float4 of `part` (shared memory) into block offset `off` of my slot on every peer, signal, wait for the
 // peers' blocks, reduce in rank order.  Result (fp32) is left in `part`.
-__device__ __forceinline__ void oneshot_exchange(const ArArgs& ar, float* part, int n4, size_t off, int cta) {
-    const int parity = (int)(ar.epoch & 1u);
+__device__ __forceinline__ void oneshot_exchange(const ArArgs& ar, uint32_t epoch, float* part, int n4, size_t off,
+                                                 int cta) {
+    const int parity = (int)(epoch & 1u);
     const size_t my_slot = ((size_t)parity * ar.tp + ar.rank) * ar.slot_elems + off;
     // (peer, vector) pairs spread over the CTA: all NVLink stores are in flight at once
     for (int i = threadIdx.x; i < n4 * (ar.tp - 1); i += blockDim.x) {
@@ -69,9 +70,9 @@ __device__ __forceinline__ void oneshot_exchange(const ArArgs& ar, float* part, 
     if (threadIdx.x < ar.tp - 1) {
         const int peer = (ar.rank + 1 + (int)threadIdx.x) % ar.tp;
         __threadfence_system();
-        ar_st_release_sys(ar.sig_peer[peer] + ar.slot + cta * kMaxTp + ar.rank, ar.epoch);
+        ar_st_release_sys(ar.sig_peer[peer] + ar.slot + cta * kMaxTp + ar.rank, epoch);
         const uint32_t* flag = ar.sig_local + ar.slot + cta * kMaxTp + peer;
-        while ((int32_t)(ar_ld_acquire_sys(flag) - ar.epoch) < 0) {}
+        while ((int32_t)(ar_ld_acquire_sys(flag) - epoch) < 0) {}
     }
     __syncthreads();
     const float* mine = ar.stage_peer[ar.rank] + (size_t)parity * ar.tp * ar.slot_elems + off;
@@ -85,6 +86,26 @@ __device__ __forceinline__ void oneshot_exchange(const ArArgs& ar, float* part, 
         reinterpret_cast<float4*>(part)[v] = acc;
     }
     __syncthreads();
+}
+
+// The call counter lives in device memory so that a CUDA graph that captured the launch replays correctly: every CTA
+// reads it on entry, the last CTA to finish advances it (kernels of one stream do not overlap).
+__device__ __forceinline__ uint32_t ar_begin(const ArArgs& ar) {
+    __shared__ uint32_t s_epoch;
+    if (threadIdx.x == 0) s_epoch = *reinterpret_cast<volatile uint32_t*>(ar.state) + 1u;
+    __syncthreads();
+    return s_epoch;
+}
+__device__ __forceinline__ void ar_end(const ArArgs& ar, uint32_t epoch) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        if (atomicAdd(ar.state + 1, 1u) == gridDim.x - 1) {
+            ar.state[1] = 0u;
+            __threadfence();
+            *reinterpret_cast<volatile uint32_t*>(ar.state) = epoch;
+        }
+    }
 }
 
 __device__ __forceinline__ float dot8(const uint4& a, const uint4& b, float acc) {
@@ -155,13 +176,18 @@ __global__ void __launch_bounds__(kArThreads) skinny_gemm_ar_kernel(const bf16* 
         }
     }
     __syncthreads();
-    if (ar.tp > 1) oneshot_exchange(ar, part, kB * cols / 4, (size_t)blockIdx.x * kB * cols, (int)blockIdx.x);
+    uint32_t epoch = 0;
+    if (ar.tp > 1) {
+        epoch = ar_begin(ar);
+        oneshot_exchange(ar, epoch, part, kB * cols / 4, (size_t)blockIdx.x * kB * cols, (int)blockIdx.x);
+    }
     for (int i = threadIdx.x; i < B * ncols; i += kArThreads) {
         const int b = i / ncols, c = i % ncols;
         float v = part[b * cols + c];
         if (residual) v += __bfloat162float(residual[(size_t)b * ldo + c0 + c]);
         out[(size_t)b * ldo + c0 + c] = __float2bfloat16(v);
     }
+    if (ar.tp > 1) ar_end(ar, epoch);
 }
 
 // Stand-alone one-shot all-reduce of n bf16 values (n % 8 == 0); every CTA owns `per_cta` elements (multiple of 8).
@@ -188,8 +214,8 @@ __global__ void __launch_bounds__(kArThreads) allreduce_oneshot_kernel(const bf1
 #pragma unroll
         for (int j = 0; j < 8; ++j) part[i * 8 + j] = f[j];
     }
-    __syncthreads();
-    oneshot_exchange(ar, part, per_cta / 4, (size_t)blockIdx.x * per_cta, (int)blockIdx.x);
+    const uint32_t epoch = ar_begin(ar);
+    oneshot_exchange(ar, epoch, part, per_cta / 4, (size_t)blockIdx.x * per_cta, (int)blockIdx.x);
     for (int i = threadIdx.x; i < cnt / 8; i += kArThreads) {
         uint4 v;
         __nv_bfloat162* p = reinterpret_cast<__nv_bfloat162*>(&v);
@@ -197,18 +223,19 @@ __global__ void __launch_bounds__(kArThreads) allreduce_oneshot_kernel(const bf1
         for (int j = 0; j < 4; ++j) p[j] = __floats2bfloat162_rn(part[i * 8 + 2 * j], part[i * 8 + 2 * j + 1]);
         *reinterpret_cast<uint4*>(out + e0 + (size_t)i * 8) = v;
     }
+    ar_end(ar, epoch);
 }
 
-int fill_args(ArArgs& ar, void* const* stage_ptrs, void* const* sig_ptrs, int tp, int rank, int slot, unsigned epoch,
+int fill_args(ArArgs& ar, void* const* stage_ptrs, void* const* sig_ptrs, int tp, int rank, int slot, void* state,
               size_t slot_elems) {
     NXD_REQUIRE(tp >= 1 && tp <= kMaxTp && rank >= 0 && rank < tp, "oneshot all-reduce: tp %d / rank %d out of range", tp, rank);
-    NXD_REQUIRE(tp == 1 || (stage_ptrs && sig_ptrs && epoch > 0), "oneshot all-reduce: missing symmetric buffers");
+    NXD_REQUIRE(tp == 1 || (stage_ptrs && sig_ptrs && state), "oneshot all-reduce: missing symmetric buffers / state");
     for (int i = 0; i < tp && tp > 1; ++i) {
         ar.stage_peer[i] = (float*)stage_ptrs[i];
         ar.sig_peer[i] = (uint32_t*)sig_ptrs[i];
     }
     ar.sig_local = tp > 1 ? (uint32_t*)sig_ptrs[rank] : nullptr;
-    ar.slot_elems = slot_elems; ar.slot = slot; ar.tp = tp; ar.rank = rank; ar.epoch = epoch;
+    ar.slot_elems = slot_elems; ar.slot = slot; ar.tp = tp; ar.rank = rank; ar.state = (uint32_t*)state;
     return 0;
 }
 
@@ -248,16 +275,17 @@ NXD_API int nxd_oneshot_num_flags(void) { return kMaxCtas * kMaxTp; }
 // N % 4 == 0, rows of x / w 16-byte aligned.  tp == 1: plain skinny GEMM (stage_ptrs / sig_ptrs may be NULL).
 // stage_ptrs: every rank's staging region of 2 * tp * slot_elems floats, slot_elems >= 16 * (N + 8192) is always
 // enough; sig_ptrs: signal pads; slot: first of nxd_oneshot_num_flags() flags that belong to this staging region;
-// epoch = 1, 2, 3, ... counts the calls (of either entry point) on this region.
+// state: 2 zero-initialised uint32 in LOCAL device memory owned by this staging region (call counter + CTA counter;
+// kept on the device so that the launch can be captured in a CUDA graph and replayed).
 NXD_API int nxd_skinny_gemm_ar_bf16(const void* x, const void* w, const void* residual, void* out, int B, int N, int K,
                                     long long ldx, long long ldw, long long ldo, void* const* stage_ptrs,
-                                    void* const* sig_ptrs, size_t slot_elems, int tp, int rank, int slot, unsigned epoch,
+                                    void* const* sig_ptrs, size_t slot_elems, int tp, int rank, int slot, void* state,
                                     void* stream) {
     NXD_REQUIRE(B >= 1 && B <= 16, "skinny_gemm_ar: B %d not in [1, 16]", B);
     NXD_REQUIRE(K % 8 == 0 && N % 4 == 0 && ldx % 8 == 0 && ldw % 8 == 0,
                 "skinny_gemm_ar: K / ldx / ldw must be multiples of 8 and N of 4");
     ArArgs ar{};
-    if (int rc = fill_args(ar, stage_ptrs, sig_ptrs, tp, rank, slot, epoch, slot_elems)) return rc;
+    if (int rc = fill_args(ar, stage_ptrs, sig_ptrs, tp, rank, slot, state, slot_elems)) return rc;
     const bf16 *xb = (const bf16*)x, *wb = (const bf16*)w, *rb = (const bf16*)residual;
     cudaStream_t st = (cudaStream_t)stream;
     if (B <= 1) return launch_skinny<1>(xb, wb, rb, (bf16*)out, B, N, K, ldx, ldw, ldo, ar, st);
@@ -269,10 +297,10 @@ NXD_API int nxd_skinny_gemm_ar_bf16(const void* x, const void* w, const void* re
 
 // out[n] = sum over ranks of in[n] (bf16, fp32 accumulation in rank order).  n % 8 == 0, n <= slot_elems.
 NXD_API int nxd_allreduce_oneshot(const void* in, void* out, long long n, void* const* stage_ptrs, void* const* sig_ptrs,
-                                  size_t slot_elems, int tp, int rank, int slot, unsigned epoch, void* stream) {
+                                  size_t slot_elems, int tp, int rank, int slot, void* state, void* stream) {
     NXD_REQUIRE(n > 0 && n % 8 == 0, "allreduce_oneshot: n %lld must be a positive multiple of 8", n);
     ArArgs ar{};
-    if (int rc = fill_args(ar, stage_ptrs, sig_ptrs, tp, rank, slot, epoch, slot_elems)) return rc;
+    if (int rc = fill_args(ar, stage_ptrs, sig_ptrs, tp, rank, slot, state, slot_elems)) return rc;
     if (tp == 1) {
         if (in != out) NXD_CHECK_CUDA(cudaMemcpyAsync(out, in, (size_t)n * 2, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
         return 0;

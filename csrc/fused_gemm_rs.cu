@@ -176,7 +176,6 @@ gemm_rs_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
         int buf = 0;
         int acc = 0;
         uint32_t acc_phase = 0;
-        uint32_t* pending = nullptr;   // counter of the previous tile, bumped once its boxes have landed
         constexpr int kGroupsPerTile = BN / 64;
         for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
             int dest, mt, tn;
@@ -220,25 +219,22 @@ gemm_rs_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                 }
                 buf ^= 1;
             }
-            if (lane == 0) {
-                if (pending) {
-                    ptx::bulk_wait<kGroupsPerTile>();   // everything older than this tile's groups has landed
-                    asm volatile("fence.proxy.async;" ::: "memory");
-                    __threadfence_system();
-                    red_relaxed_sys_add(pending, 1u);
-                }
-                pending = rs.sig_peer[dest] + rs.slot_cnt + rs.rank * m_tiles_per_slab + mt;
-            }
             if (++acc == kAccStages) { acc = 0; acc_phase ^= 1; }
         }
         if (tr && warp == kFirstEpilogueWarp && lane == 0) rs.trace[1] = rs_gtime();   // last tile's boxes issued
         if (lane == 0) {
+            // ONE system fence per warp for the whole GEMM phase, then a relaxed increment per tile: a fence per tile
+            // drains the in-flight NVLink stores every time (tools/bench_p2p.py: 4x lower push bandwidth), and the
+            // consumers -- the reduction below, on CTAs that are busy with GEMM tiles until now anyway -- gain nothing
+            // from earlier signals.
             ptx::bulk_wait<0>();
             if (tr && warp == kFirstEpilogueWarp) rs.trace[2] = rs_gtime();            // ... and landed
-            if (pending) {
-                asm volatile("fence.proxy.async;" ::: "memory");
-                __threadfence_system();
-                red_relaxed_sys_add(pending, 1u);
+            asm volatile("fence.proxy.async;" ::: "memory");
+            __threadfence_system();
+            for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
+                int dest, mt, tn;
+                tile_coords_rs(tile, dest, mt, tn);
+                red_relaxed_sys_add(rs.sig_peer[dest] + rs.slot_cnt + rs.rank * m_tiles_per_slab + mt, 1u);
             }
         }
     }

@@ -114,12 +114,15 @@ int nxd_flash_attn_bwd(const void* q, const void* k, const void* v, const void* 
 int nxd_flash_attn_fwd_tc(const void* q, const void* k, const void* v, void* o, float* lse,
                           const long long* strides, int B, int Hq, int Hkv, int Sq, int Sk, int D, float scale,
                           int causal, void* stream);
-/* scratch: lse_pad, delta_pad = B * Hq * roundup(Sq, 64) floats each; dq_accum = B * Hq * Sq * 128 floats, ZEROED
- * by the caller before the call (dQ is accumulated with TMA reduce-add). */
+/* scratch: lse_pad, delta_pad = B * Hq * roundup(Sq, 64) floats each; dq_accum = B * Hq * Sq * D floats, ZEROED
+ * by the caller before the call (dQ is accumulated with TMA reduce-add).  dkv_accum: NULL, or 2 * B * Hkv * Sk * D
+ * ZEROED floats: then nxd_flash_attn_bwd_tc_num_splits() CTAs share each K/V block and reduce-add their partial
+ * dK / dV (few heads per GPU under tensor parallelism would otherwise leave most SMs idle). */
+int nxd_flash_attn_bwd_tc_num_splits(int B, int Hq, int Hkv, int Sq, int Sk);
 int nxd_flash_attn_bwd_tc(const void* q, const void* k, const void* v, const void* o, const void* dout,
-                          const float* lse, float* lse_pad, float* delta_pad, float* dq_accum, void* dq, void* dk,
-                          void* dv, const long long* strides, int B, int Hq, int Hkv, int Sq, int Sk, int D,
-                          float scale, int causal, void* stream);
+                          const float* lse, float* lse_pad, float* delta_pad, float* dq_accum, float* dkv_accum,
+                          void* dq, void* dk, void* dv, const long long* strides, int B, int Hq, int Hkv, int Sq,
+                          int Sk, int D, float scale, int causal, void* stream);
 
 /* ---- symmetric (peer-mapped) memory over CUDA IPC + fused compute/collective kernels ---------------------------
  * No counterpart in the reference (its collectives are XLA ops).  One process per GPU: every rank allocates a
@@ -147,6 +150,27 @@ int nxd_ag_gemm_bf16(int layout, const void* x_local, const void* w, void* y, in
 int nxd_gemm_rs_bf16(int layout, const void* x, const void* w, void* out, int R, int N, int K, long long ldx,
                      long long ldw, long long ldo, void* const* stage_ptrs, void* const* sig_ptrs, int tp, int rank,
                      int slot_cnt, unsigned epoch, int block_n, void* trace, void* stream);
+/* Token-generation path (reference: RowParallelLinear matmul + all-reduce, layers.py:452-468 / mappings.py:176-190):
+ * out[B, N] (+ residual) = sum over ranks of x[B, K] * w[N, K]^T in ONE launch, B <= 16; the fp32 partial blocks are
+ * pushed into every peer's staging slot and added in rank order (bit-identical on all ranks).  stage_ptrs: tp regions
+ * of 2 * tp * slot_elems floats; slot: first of nxd_oneshot_num_flags() flags; state: 2 zeroed uint32 of local device
+ * memory per staging region (call counter, kept on the device so that CUDA-graph replays stay correct).
+ * tp == 1 is a plain weight-streaming skinny GEMM (no symmetric memory needed). */
+int nxd_oneshot_num_flags(void);
+int nxd_skinny_gemm_ar_bf16(const void* x, const void* w, const void* residual, void* out, int B, int N, int K,
+                            long long ldx, long long ldw, long long ldo, void* const* stage_ptrs,
+                            void* const* sig_ptrs, size_t slot_elems, int tp, int rank, int slot, void* state,
+                            void* stream);
+/* out[n] = sum over ranks of in[n] (bf16, n % 8 == 0, n <= slot_elems): one-shot all-reduce for small messages */
+int nxd_allreduce_oneshot(const void* in, void* out, long long n, void* const* stage_ptrs, void* const* sig_ptrs,
+                          size_t slot_elems, int tp, int rank, int slot, void* state, void* stream);
+/* Sequence-parallel embedding forward without the reduce-scatter of a mostly-zero tensor (reference: layers.py:215-238
+ * + mappings.py reduce_scatter): the rank that owns a token's vocab row writes it into the output shard
+ * [S/tp, B, H] of the rank that owns the sequence position (symmetric memory), then the ranks exchange flags.
+ * ids: all B*S ids, identical on every rank; done: one zeroed uint32 of local device memory. */
+int nxd_embedding_fwd_sp_push(const long long* ids, const void* weight, void* const* out_ptrs, void* const* sig_ptrs,
+                              void* done, long long T, int H, int vocab_start, int vocab_local, int B, int S, int tp,
+                              int rank, int slot, unsigned epoch, void* stream);
 /* tooling: NVLink push-bandwidth probe (tools/bench_p2p.py) */
 int nxd_p2p_push_probe(int mode, const void* src, const void* const* dst_ptrs, int n_dst, size_t bytes, int ctas,
                        int chunk, int bufs, int read_lag, int sig_mode, int sig_every, size_t flag_off, void* stream);

@@ -26,6 +26,7 @@ import torch.nn as nn
 from ..models.llama import LlamaConfig, LlamaForCausalLM
 from ..ops import activation as act_ops
 from ..ops import attention as attn_ops
+from ..ops import comm_linear
 from ..ops import norm as norm_ops
 from ..ops import rope as rope_ops
 from ..parallel import mappings
@@ -157,7 +158,7 @@ class LlamaInferenceModel(LlamaForCausalLM):
             mask = (input_ids < emb.start_index) | (input_ids >= emb.end_index)
             local = (input_ids - emb.start_index).masked_fill(mask, 0)
             out = nn.functional.embedding(local, w).masked_fill(mask.unsqueeze(-1), 0.0)
-            return mappings.reduce_from_tensor_model_parallel_region(out)
+            return comm_linear.all_reduce_small(out)
         return nn.functional.embedding(input_ids, w)
 
     # -- simple generation loop (the runner adds batching / bucketing / CUDA graphs on top) ---------------------------

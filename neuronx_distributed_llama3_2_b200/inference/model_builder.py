@@ -58,6 +58,10 @@ class _Bucket:
         self.static_out = None
         self.use_graph = use_graph and all(t.is_cuda for t in example_inputs)
 
+    @property
+    def first_input_shape(self) -> Optional[Tuple[int, ...]]:
+        return tuple(self.static_in[0].shape) if self.static_in else None
+
     def capture(self) -> None:
         if not self.use_graph:
             return
@@ -89,21 +93,82 @@ class NxDModel(torch.nn.Module):
         self._buckets = buckets
         self.models = torch.nn.ModuleDict(modules)
         self._route: Dict[str, Tuple[str, _Bucket]] = {}
+        self._graphs: List[Tuple[str, str, _Bucket]] = []
         for key, bs in buckets.items():
             for shape_key, b in bs.items():
                 self._route[shape_key] = (key, b)
+                self._graphs.append((key, shape_key, b))
         self.weights_initialized = True
+        self._native = self._build_native_router()
+
+    def _build_native_router(self):
+        """(batch, seq) of the first input -> bucket in the C++ runtime (``csrc/runtime/nxd_runtime.cpp``); the Python
+        dict stays as the general path (arbitrary argument shapes, no compiler on the box)."""
+        try:
+            from ..runtime import NativeRouter, available
+
+            if not available():
+                return None
+            r = NativeRouter()
+            for i, (key, _, b) in enumerate(self._graphs):
+                shp = b.first_input_shape
+                if shp is None or len(shp) != 2:
+                    return None
+                r.add(key, int(shp[0]), int(shp[1]), i)
+            return r
+        except Exception:  # noqa: BLE001 - e.g. two models with the same first-input shape: keep the dict router
+            return None
 
     def router(self, args: Sequence[torch.Tensor]) -> Tuple[str, _Bucket]:
+        if self._native is not None and args and args[0].dim() == 2:
+            g = self._native.route_exact(int(args[0].shape[0]), int(args[0].shape[1]))
+            if g >= 0:
+                key, shape_key, b = self._graphs[g]
+                if shape_key == _shape_key(args):
+                    return key, b
         k = _shape_key(args)
         if k not in self._route:
             raise RuntimeError(f"no compiled bucket for input shapes {k}; have {list(self._route)}")
         return self._route[k]
 
+    def route_padded(self, key: str, batch: int, seq: int) -> Optional[Tuple[int, int]]:
+        """Smallest compiled bucket ``(batch', seq')`` of sub-model ``key`` that covers a ``[batch, seq]`` request
+        (the runner pads prompts up to it), or ``None``."""
+        if self._native is not None:
+            g, b, s = self._native.route_padded(key, batch, seq)
+            return (b, s) if g >= 0 else None
+        best = None
+        for k, _, bk in self._graphs:
+            shp = bk.first_input_shape
+            if k != key or shp is None or len(shp) != 2 or shp[0] < batch or shp[1] < seq:
+                continue
+            if best is None or shp[0] * shp[1] < best[0] * best[1]:
+                best = (int(shp[0]), int(shp[1]))
+        return best
+
     def initialize(self, state_dict: Dict[str, torch.Tensor], strict: bool = False) -> None:
         """Load (already sharded) weights; they are shared by every graph of a key."""
         for m in self.models.values():
             m.load_state_dict(state_dict, strict=strict)
+
+    def load_sharded_checkpoint(self, serialize_path: str, rank: Optional[int] = None, strict: bool = False) -> None:
+        """Load ``tp{rank}_sharded_checkpoint.safetensors`` written by ``ModelBuilder.shard_checkpoint`` (reference
+        ``model_builder.py:302-321``).  The file is read by the C++ runtime (mmap + a pool of copy threads into pinned
+        memory) and moved to the device with non-blocking copies; falls back to the safetensors package."""
+        rank = ps.get_tensor_model_parallel_rank() if rank is None else rank
+        path = os.path.join(serialize_path, f"tp{rank}_sharded_checkpoint.safetensors")
+        dev = next(iter(self.models.values())).parameters().__next__().device
+        try:
+            from ..runtime import available, load_safetensors
+
+            if not available():
+                raise RuntimeError("no native runtime")
+            sd = load_safetensors(path, device=dev)
+        except (RuntimeError, OSError, KeyError):
+            from safetensors.torch import load_file
+
+            sd = load_file(path, device=str(dev))
+        self.initialize(sd, strict=strict)
 
     def forward(self, *args: torch.Tensor):
         _, bucket = self.router(args)

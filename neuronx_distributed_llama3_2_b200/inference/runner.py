@@ -71,6 +71,10 @@ class InferenceRunner:
 
     # -- generate -------------------------------------------------------------------------------------------------------
     def _bucket_len(self, n: int) -> int:
+        if self.nxd_model is not None:
+            hit = self.nxd_model.route_padded(CONTEXT_ENCODING_MODEL, self.config.ctx_batch_size, n)
+            if hit is not None:
+                return hit[1]
         for b in self.config.context_buckets():
             if n <= b:
                 return b

@@ -89,8 +89,11 @@ def kv_cache_update(cache_k: torch.Tensor, cache_v: torch.Tensor, new_k: torch.T
         pos = positions.to(torch.int32).contiguous()
         sid = seq_ids.to(torch.int32).contiguous() if seq_ids is not None else None
         bt = block_table.to(torch.int32).contiguous() if block_table is not None else None
+        # keep the contiguous copies alive until the launch: two temporaries of equal size would otherwise share one
+        # allocator block (the first is freed before the second is made) and K would be read from V's bytes
+        nk, nv = new_k.contiguous(), new_v.contiguous()
         rc = _lib.lib().nxd_kv_cache_update(
-            _lib.ptr(new_k.contiguous()), _lib.ptr(new_v.contiguous()), _lib.ptr(cache_k), _lib.ptr(cache_v),
+            _lib.ptr(nk), _lib.ptr(nv), _lib.ptr(cache_k), _lib.ptr(cache_v),
             _lib.ptr(pos), _lib.ptr(sid), _lib.ptr(bt), _c.c_longlong(cache_k.stride(0)),
             _c.c_longlong(cache_k.stride(1)), _c.c_int(page_size), _c.c_int(bt.shape[1] if bt is not None else 0),
             _c.c_int(B), _c.c_int(Hkv), _c.c_int(T), _c.c_int(D), _lib.stream_ptr())
@@ -130,8 +133,9 @@ def decode_attention(q: torch.Tensor, cache_k: torch.Tensor, cache_v: torch.Tens
             _decode_scratch[key] = scratch
         out = torch.empty_like(q)
         bt = block_table.to(torch.int32).contiguous() if block_table is not None else None
+        qc = q.contiguous()
         rc = _lib.lib().nxd_decode_attn(
-            _lib.ptr(q.contiguous()), _lib.ptr(cache_k), _lib.ptr(cache_v), _lib.ptr(lens), _lib.ptr(bt),
+            _lib.ptr(qc), _lib.ptr(cache_k), _lib.ptr(cache_v), _lib.ptr(lens), _lib.ptr(bt),
             _c.c_longlong(cache_k.stride(0)), _c.c_longlong(cache_k.stride(1)), _c.c_int(page_size),
             _c.c_int(bt.shape[1] if bt is not None else 0), _lib.ptr(out), _lib.ptr(scratch), _c.c_int(B),
             _c.c_int(Hq), _c.c_int(Hkv), _c.c_int(D), _c.c_int(n_splits), _c.c_float(scale), _lib.stream_ptr())

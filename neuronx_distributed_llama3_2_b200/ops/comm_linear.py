@@ -126,6 +126,23 @@ def gemm_ar(x2d: torch.Tensor, weight: torch.Tensor, layout: str = "nt", group=N
     return y
 
 
+def all_reduce_small(t: torch.Tensor, group=None) -> torch.Tensor:
+    """Sum ``t`` over the TP group (no autograd): one-shot NVLink kernel for messages up to 2 MB, NCCL beyond."""
+    g = _group(group)
+    if g is None:
+        return t
+    ctx = _fused_ctx(t, group)
+    if ctx is not None and t.is_contiguous():
+        from .fused_comm import oneshot_all_reduce
+
+        res = oneshot_all_reduce(ctx, t)
+        if res is not None:
+            return res
+    t = t.contiguous()
+    dist.all_reduce(t, group=g)
+    return t
+
+
 class _Done:
     def wait(self):
         return None

@@ -60,15 +60,21 @@ class _FlashAttnFn(torch.autograd.Function):
         B, Hq, Sq, D = q.shape
         Hkv, Sk = k.shape[1], k.shape[2]
         dq, dk, dv = _dense_like(q), _dense_like(k), _dense_like(v)
-        if D == 128 and os.environ.get("NXD_ATTN_BWD", "tc") == "tc":
+        if D in (64, 128) and os.environ.get("NXD_ATTN_BWD", "tc") == "tc":
             # tcgen05 backward (csrc/flash_attn_bwd_tc.cu): dQ is accumulated in fp32 through TMA reduce-add
             sq_pad = (Sq + 63) // 64 * 64
             lse_pad = torch.empty(B * Hq * sq_pad, dtype=torch.float32, device=q.device)
             delta_pad = torch.empty_like(lse_pad)
             dq_acc = torch.zeros((B, Hq, Sq, D), dtype=torch.float32, device=q.device)
+            # few (kv block, kv head) pairs per GPU (tensor-parallel shards): several CTAs share a K/V block and
+            # reduce-add partial dK / dV into fp32 accumulators
+            nsplit = int(_lib.lib().nxd_flash_attn_bwd_tc_num_splits(_c.c_int(B), _c.c_int(Hq), _c.c_int(Hkv),
+                                                                     _c.c_int(Sq), _c.c_int(Sk)))
+            dkv_acc = (torch.zeros((2, B, Hkv, Sk, D), dtype=torch.float32, device=q.device)
+                       if nsplit > 1 and os.environ.get("NXD_ATTN_BWD_SPLIT", "1") == "1" else None)
             rc = _lib.lib().nxd_flash_attn_bwd_tc(
                 _lib.ptr(q), _lib.ptr(k), _lib.ptr(v), _lib.ptr(o), _lib.ptr(do), _lib.ptr(lse), _lib.ptr(lse_pad),
-                _lib.ptr(delta_pad), _lib.ptr(dq_acc), _lib.ptr(dq), _lib.ptr(dk), _lib.ptr(dv),
+                _lib.ptr(delta_pad), _lib.ptr(dq_acc), _lib.ptr(dkv_acc), _lib.ptr(dq), _lib.ptr(dk), _lib.ptr(dv),
                 _strides(q, k, v, o, do, dq, dk, dv), _c.c_int(B), _c.c_int(Hq), _c.c_int(Hkv), _c.c_int(Sq),
                 _c.c_int(Sk), _c.c_int(D), _c.c_float(ctx.scale), _c.c_int(1 if ctx.causal else 0), _lib.stream_ptr())
             _lib.check(rc, "nxd_flash_attn_bwd_tc")

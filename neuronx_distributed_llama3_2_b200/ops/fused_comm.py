@@ -142,7 +142,9 @@ def _ar_state(ctx):
         tp = ctx.world
         _, table = ctx.region("ar", 2 * tp * _AR_SLOT_ELEMS * 4)
         st["ar"] = {"slot": ctx.signal_slots("ar:flags", int(_lib.lib().nxd_oneshot_num_flags())),
-                    "sigs": (_c.c_void_p * tp)(*ctx.sig_peers), "stages": _host_ptrs(ctx, table, 0)}
+                    "sigs": (_c.c_void_p * tp)(*ctx.sig_peers), "stages": _host_ptrs(ctx, table, 0),
+                    # call counter + CTA counter on the device: launches stay valid when replayed from a CUDA graph
+                    "state": torch.zeros(2, dtype=torch.int32, device=ctx.device)}
     return st["ar"]
 
 
@@ -160,10 +162,9 @@ def oneshot_all_reduce(ctx, x: torch.Tensor, out: Optional[torch.Tensor] = None)
         return None
     s = _ar_state(ctx)
     out = torch.empty_like(x) if out is None else out
-    epoch = ctx.next_epoch("ar")
     rc = _lib.lib().nxd_allreduce_oneshot(_lib.ptr(x), _lib.ptr(out), _c.c_longlong(n), s["stages"], s["sigs"],
                                           _c.c_size_t(_AR_SLOT_ELEMS), _c.c_int(ctx.world), _c.c_int(ctx.rank),
-                                          _c.c_int(s["slot"]), _c.c_uint(epoch), _lib.stream_ptr())
+                                          _c.c_int(s["slot"]), _lib.ptr(s["state"]), _lib.stream_ptr())
     _lib.check(rc, "nxd_allreduce_oneshot")
     return out
 
@@ -190,15 +191,14 @@ def skinny_gemm(x2d: torch.Tensor, weight: torch.Tensor, residual: Optional[torc
             residual = residual.contiguous()
     if tp > 1:
         s = _ar_state(ctx)
-        epoch = ctx.next_epoch("ar")
-        stages, sigs, slot, rank = s["stages"], s["sigs"], s["slot"], ctx.rank
+        stages, sigs, slot, rank, state = s["stages"], s["sigs"], s["slot"], ctx.rank, s["state"]
     else:
-        stages = sigs = None
-        slot = rank = epoch = 0
+        stages = sigs = state = None
+        slot = rank = 0
     rc = _lib.lib().nxd_skinny_gemm_ar_bf16(
         _lib.ptr(x2d), _lib.ptr(weight), _lib.ptr(residual), _lib.ptr(out), _c.c_int(B), _c.c_int(N), _c.c_int(K),
         _c.c_longlong(x2d.stride(0)), _c.c_longlong(weight.stride(0)), _c.c_longlong(out.stride(0)), stages, sigs,
-        _c.c_size_t(_AR_SLOT_ELEMS), _c.c_int(tp), _c.c_int(rank), _c.c_int(slot), _c.c_uint(epoch), _lib.stream_ptr())
+        _c.c_size_t(_AR_SLOT_ELEMS), _c.c_int(tp), _c.c_int(rank), _c.c_int(slot), _lib.ptr(state), _lib.stream_ptr())
     _lib.check(rc, "nxd_skinny_gemm_ar_bf16")
     return out
 

@@ -84,6 +84,8 @@ def gemm_tn(a: torch.Tensor, b: torch.Tensor, out: Optional[torch.Tensor] = None
         from .gemm import gemm
 
         return gemm(a, b, "tn", out=out, out_dtype=out_dtype, accumulate=accumulate)
+    if out is not None and not accumulate and out.dtype == a.dtype and out.is_contiguous():
+        return torch.mm(a.t(), b, out=out)
     res = torch.matmul(a.t(), b)
     return _finish(res, out, out_dtype, accumulate)
 

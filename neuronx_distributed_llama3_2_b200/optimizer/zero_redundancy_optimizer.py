@@ -94,6 +94,7 @@ class _Bucket:
             gview = self.flat_grad[o:o + n].view(p.shape)
             if gdt == p.dtype:
                 p.grad = gview
+                p._nxd_flat_grad = gview   # wgrad GEMMs write here directly when ``p.grad is None`` (layers.py)
             else:
                 p.main_grad = gview  # fp32 accumulation target (GEMM epilogue / hook), reference use_grad_acc_hook
         self.master = self.flat_param[self.lo:self.hi].to(optimizer_dtype).clone()
@@ -207,7 +208,13 @@ class NeuronZero1Optimizer(torch.optim.Optimizer):
         if not self._inited:
             return super().zero_grad(set_to_none=True)
         for b in self.buckets:
-            b.flat_grad.zero_()
+            if b.flat_grad.dtype != b.dtype:
+                b.flat_grad.zero_()          # fp32 accumulation buffer (main_grad): the GEMM epilogues add into it
+                continue
+            # No fill kernel: the first gradient of a parameter OVERWRITES its slice of the flat buffer (the wgrad
+            # GEMM stores straight into it, other grads are copied in by _sync_grad_views), later ones accumulate.
+            for p in b.params:
+                p.grad = None
 
     def _norm_groups(self):
         groups = []
@@ -226,6 +233,7 @@ class NeuronZero1Optimizer(torch.optim.Optimizer):
                 and ps.get_tensor_model_parallel_size() > 1):
             return
         g = ps.get_tensor_model_parallel_group()
+        self._sync_grad_views()
         for b in self.buckets:
             if b.dup_other_begin > b.sp_begin:
                 dist.all_reduce(b.flat_grad[b.sp_begin:b.dup_other_begin], group=g)
@@ -236,16 +244,22 @@ class NeuronZero1Optimizer(torch.optim.Optimizer):
         for b in self.buckets:
             if b.flat_grad.dtype != b.dtype:
                 continue
+            zero, dst, src = [], [], []
             for p, o in zip(b.params, b.offsets):
                 view = b.flat_grad[o:o + p.numel()].view(p.shape)
                 g = p.grad
                 if g is None:
-                    view.zero_()
+                    zero.append(view)
                 elif g.data_ptr() != view.data_ptr():
-                    view.copy_(g)
+                    dst.append(view)
+                    src.append(g if g.dtype == view.dtype else g.to(view.dtype))
                 else:
                     continue
                 p.grad = view
+            if zero:
+                torch._foreach_zero_(zero)
+            if dst:
+                torch._foreach_copy_(dst, src)
 
     def _reduce_scatter_grads(self) -> None:
         self._sync_grad_views()
@@ -453,6 +467,7 @@ class NeuronEPZero1Optimizer(torch.optim.Optimizer):
         # expert grads: the EP ranks hold different experts, so the expert-DP reduce-scatter averages over
         # exp_dp only while the batch was split over dp = exp_dp * ep -> scale by 1/ep (reference :231-268)
         if self.ep_zero_optimizer is not None and self._ep_size > 1:
+            self.ep_zero_optimizer._sync_grad_views()
             for b in self.ep_zero_optimizer.buckets:
                 b.flat_grad.mul_(1.0 / self._ep_size)
         for o in self._opts:

@@ -173,8 +173,13 @@ class ParallelEmbedding(torch.nn.Module):
         if (w.is_cuda and w.dtype == torch.bfloat16 and self.max_norm is None and self.padding_idx is None
                 and input_.dim() == 2):
             # sm_100a gather kernel: masks out-of-shard ids and writes [S, B, H] directly when SP is on
-            from ..ops.embedding import vocab_parallel_embedding
+            from ..ops.embedding import sp_embedding_push, vocab_parallel_embedding
 
+            if self.sequence_parallel_enabled and tp > 1 and input_.shape[1] % tp == 0 and w.shape[1] % 8 == 0:
+                sym = comm_linear._fused_ctx(w, None)
+                if sym is not None:
+                    # the owner of a vocab row writes it straight into the sequence shard of the rank that needs it
+                    return sp_embedding_push(input_, w, self.start_index, sym)
             out = vocab_parallel_embedding(input_, w, self.start_index if tp > 1 else 0,
                                            seq_first_out=self.sequence_parallel_enabled)
             if self.sequence_parallel_enabled:
@@ -222,6 +227,12 @@ def _accumulate_wgrad(weight: torch.Tensor, dy2d: torch.Tensor, x2d: torch.Tenso
     if main_grad is not None:
         gemm_ops.gemm_tn(dy2d, x2d, out=main_grad, accumulate=True)
         return None
+    flat = getattr(weight, "_nxd_flat_grad", None)
+    if flat is not None and weight.grad is None and flat.dtype == weight.dtype and flat.shape == weight.shape:
+        # first gradient after zero_grad(): the GEMM stores straight into the ZeRO-1 flat gradient buffer (no zero
+        # fill before, no add after).  A fresh view object is returned so that autograd adopts it as ``.grad``.
+        gemm_ops.gemm_tn(dy2d, x2d, out=flat)
+        return flat.view(flat.shape)
     return gemm_ops.gemm_tn(dy2d, x2d, out_dtype=weight.dtype)
 
 

@@ -138,6 +138,35 @@ def case_gemm_ar(rank, world):
         assert got is not None and _rel(got, ref) < 4e-3, n
 
 
+def case_sp_embedding(rank, world):
+    import torch.distributed as dist
+
+    from neuronx_distributed_llama3_2_b200.parallel.layers import ParallelEmbedding
+
+    V, H, B, S = 1024, 512, 2, 256
+    emb = ParallelEmbedding(V, H, dtype=torch.bfloat16, device=torch.device("cuda"), sequence_parallel_enabled=True)
+    full = torch.empty(V, H, device="cuda", dtype=torch.bfloat16)
+    dist.all_gather_into_tensor(full, emb.weight.data.contiguous())
+    for it in range(4):
+        g = torch.Generator(device="cpu").manual_seed(50 + it)
+        ids = torch.randint(0, V, (B, S), generator=g).cuda()
+        os.environ["NXD_FUSED_COMM"] = "1"
+        out = emb(ids)                                   # [S/tp, B, H] through the push kernel
+        ref = full[ids].transpose(0, 1)[rank * (S // world):(rank + 1) * (S // world)]
+        assert out.shape == ref.shape and torch.equal(out, ref), it
+        dy = torch.randn_like(out)
+        emb.weight.grad = None
+        out.backward(dy)
+        g_push = emb.weight.grad.clone()
+        os.environ["NXD_FUSED_COMM"] = "0"
+        emb.weight.grad = None
+        out2 = emb(ids)                                  # NCCL reduce-scatter path
+        assert torch.equal(out2, ref)
+        out2.backward(dy)
+        assert _rel(g_push, emb.weight.grad) < 1e-3
+    os.environ["NXD_FUSED_COMM"] = "1"
+
+
 def test_fused_ag_gemm_tp2():
     _spawn("case_ag_gemm", 2)
 
@@ -148,3 +177,7 @@ def test_fused_gemm_rs_tp2():
 
 def test_fused_gemm_ar_tp2():
     _spawn("case_gemm_ar", 2)
+
+
+def test_sp_embedding_push_tp2():
+    _spawn("case_sp_embedding", 2)

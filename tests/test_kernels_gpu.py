@@ -357,7 +357,7 @@ def test_flash_attention(S, D, impl, monkeypatch):
 
     _lib()
     monkeypatch.setenv("NXD_ATTN_FWD", impl)
-    monkeypatch.setenv("NXD_ATTN_BWD", impl)   # "tc" backward exists for D = 128; D = 64 falls back to mma.sync
+    monkeypatch.setenv("NXD_ATTN_BWD", impl)
     B, Hq, Hkv = 2, 6, 2
     q = torch.randn(B, Hq, S, D, device="cuda").bfloat16().requires_grad_()
     k = torch.randn(B, Hkv, S, D, device="cuda").bfloat16().requires_grad_()
@@ -395,13 +395,17 @@ def test_flash_attention_strided_layout_noncausal():
     os.environ.pop("NXD_ATTN_FWD", None)
 
 
+@pytest.mark.parametrize("split", ["1", "0"])
+@pytest.mark.parametrize("D", [128, 64])
 @pytest.mark.parametrize("causal", [True, False])
-def test_flash_attention_bwd_tc_gqa_cross_lengths(causal):
-    """tcgen05 backward: GQA group of 3, Sq != Sk, ragged lengths, strided [S, B, H, D] storage."""
+def test_flash_attention_bwd_tc_gqa_cross_lengths(causal, D, split, monkeypatch):
+    """tcgen05 backward: GQA group of 3, Sq != Sk, ragged lengths, strided [S, B, H, D] storage; with and without
+    several CTAs sharing a K/V block (partial dK / dV reduce-added into fp32 accumulators)."""
     from neuronx_distributed_llama3_2_b200.ops import attention as A
 
     _lib()
-    B, Hq, Hkv, Sq, Sk, D = 2, 6, 2, 200, 328, 128
+    monkeypatch.setenv("NXD_ATTN_BWD_SPLIT", split)
+    B, Hq, Hkv, Sq, Sk = 2, 6, 2, 1224, 1352
     qs = torch.randn(Sq, B, Hq, D, device="cuda").bfloat16().requires_grad_()
     ks = torch.randn(Sk, B, Hkv, D, device="cuda").bfloat16().requires_grad_()
     vs = torch.randn(Sk, B, Hkv, D, device="cuda").bfloat16().requires_grad_()
