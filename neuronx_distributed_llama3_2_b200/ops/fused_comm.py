@@ -133,7 +133,7 @@ def fused_gemm_rs(ctx, x2d: torch.Tensor, weight: torch.Tensor, layout: str = "n
 
 # ---- decode path: one-shot all-reduce and skinny GEMM -> all-reduce (csrc/fused_gemm_ar.cu) -----------------------------
 _AR_SLOT_ELEMS = 1 << 20           # floats per (parity, source) staging slot: messages up to 2 MB of bf16
-_SKINNY_MAX_ROWS = 16
+_SKINNY_MAX_ROWS = 8              # above this the tensor-core GEMM wins: the FMA loop re-reads X from shared memory per row
 
 
 def _ar_state(ctx):

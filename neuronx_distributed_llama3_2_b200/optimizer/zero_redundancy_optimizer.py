@@ -54,8 +54,10 @@ class _Bucket:
     """One flat (param, grad) buffer pair and this rank's optimizer-state slice of it."""
 
     def __init__(self, params: List[torch.nn.Parameter], group_idx: int, shard_group, optimizer_dtype: torch.dtype,
-                 grad_dtype: Optional[torch.dtype]):
+                 grad_dtype: Optional[torch.dtype], symm=None, name: str = "zero1"):
         self.group_idx = group_idx
+        self.symm = None
+        self.param_ptrs = self.grad_ptrs = None
         self.shard_group = shard_group
         self.dp = _group_size(shard_group)
         self.dp_rank = _group_rank(shard_group)
@@ -82,9 +84,26 @@ class _Bucket:
         self.lo = self.dp_rank * self.shard_size
         self.hi = self.lo + self.shard_size
 
-        self.flat_param = torch.zeros(self.total, dtype=self.dtype, device=self.device)
         gdt = grad_dtype or self.dtype
-        self.flat_grad = torch.zeros(self.total, dtype=gdt, device=self.device)
+        if (symm is not None and self.dp > 1 and self.dp <= 8 and self.device.type == "cuda"
+                and self.dtype == torch.bfloat16 and gdt in (torch.bfloat16, torch.float32)
+                and optimizer_dtype == torch.float32):
+            # fused step (csrc/fused_zero1.cu): both flat buffers live in peer-mapped memory of the shard group
+            import ctypes as _c
+
+            esz = {torch.bfloat16: 2, torch.float32: 4}
+            lp, ptab = symm.region(f"{name}:param", self.total * esz[self.dtype])
+            lg, gtab = symm.region(f"{name}:grad", self.total * esz[gdt])
+            self.flat_param = symm.tensor_view(lp, (self.total,), self.dtype)
+            self.flat_grad = symm.tensor_view(lg, (self.total,), gdt)
+            self.flat_param.zero_()
+            self.flat_grad.zero_()
+            self.param_ptrs = (_c.c_void_p * self.dp)(*[int(v) for v in ptab.tolist()])
+            self.grad_ptrs = (_c.c_void_p * self.dp)(*[int(v) for v in gtab.tolist()])
+            self.symm = symm
+        else:
+            self.flat_param = torch.zeros(self.total, dtype=self.dtype, device=self.device)
+            self.flat_grad = torch.zeros(self.total, dtype=gdt, device=self.device)
         for p, o in zip(self.params, self.offsets):
             n = p.numel()
             view = self.flat_param[o:o + n].view(p.shape)
@@ -101,7 +120,7 @@ class _Bucket:
         self.exp_avg: Optional[torch.Tensor] = None
         self.exp_avg_sq: Optional[torch.Tensor] = None
         self.grad_shard = self.flat_grad[self.lo:self.hi] if self.dp == 1 else torch.zeros(
-            self.shard_size, dtype=gdt, device=self.device)
+            self.shard_size, dtype=torch.float32 if self.symm is not None else gdt, device=self.device)
 
     def init_state(self, optimizer_dtype):
         if self.exp_avg is None:
@@ -168,7 +187,8 @@ class NeuronZero1Optimizer(torch.optim.Optimizer):
                     by_dtype.setdefault((p.dtype, p.device), []).append(p)
             for (dt, _), plist in by_dtype.items():
                 gdt = torch.float32 if (self.use_grad_acc_hook and dt != torch.float32) else None
-                b = _Bucket(plist, gi, self._shard_group, self.optimizer_dtype, gdt)
+                b = _Bucket(plist, gi, self._shard_group, self.optimizer_dtype, gdt, symm=self._symm_context(),
+                            name=f"zero1:{id(self) & 0xffffff:x}:{len(self.buckets)}")
                 if gdt is not None:
                     self._install_grad_acc_hooks(b)
                 self.buckets.append(b)
@@ -187,6 +207,23 @@ class NeuronZero1Optimizer(torch.optim.Optimizer):
         dev = self.buckets[0].device if self.buckets else torch.device("cpu")
         for name in ("sumsq", "sumsq_dup", "coef", "norm"):
             self._scalars[name] = torch.zeros(1, dtype=torch.float32, device=dev)
+
+    def _symm_context(self):
+        """Peer-mapped memory context of the shard group for the fused step, or ``None`` (CPU, single rank, a custom
+        shard group, ranks that cannot map each other's memory, ``NXD_FUSED_ZERO1=0``)."""
+        import os
+
+        if (os.environ.get("NXD_FUSED_ZERO1", "1") != "1" or not self._fused or self._shard_group is None
+                or not torch.cuda.is_available() or not ps.model_parallel_is_initialized()):
+            return None
+        try:
+            if self._shard_group is ps.get_data_parallel_group():
+                return ps.get_symm_mem_context("dp")
+            if ps.get_expert_model_parallel_size() > 1 and self._shard_group is ps.get_expert_data_parallel_group():
+                return ps.get_symm_mem_context("exp_dp")
+        except Exception as e:  # noqa: BLE001 - e.g. DP ranks on different nodes: CUDA IPC cannot map them
+            logger.warning("fused ZeRO-1 step unavailable (%s); using NCCL collectives", e)
+        return None
 
     def _install_grad_acc_hooks(self, b: _Bucket) -> None:
         """fp32 gradient accumulation (reference ``use_grad_acc_hook`` + ``higher_cc_precision``): params whose
@@ -263,8 +300,20 @@ class NeuronZero1Optimizer(torch.optim.Optimizer):
 
     def _reduce_scatter_grads(self) -> None:
         self._sync_grad_views()
+        fused = [b for b in self.buckets if b.symm is not None]
+        if fused:
+            from ..ops import _lib
+            import ctypes as _c
+
+            fused[0].symm.barrier()      # every rank's gradients are complete before anyone pulls them
+            for b in fused:
+                rc = _lib.lib().nxd_zero1_reduce_shard(
+                    b.grad_ptrs, _c.c_int(1 if b.flat_grad.dtype == torch.bfloat16 else 0), _c.c_longlong(b.lo),
+                    _c.c_longlong(b.shard_size), _lib.ptr(b.grad_shard), _c.c_int(b.dp), _c.c_int(b.dp_rank),
+                    _lib.stream_ptr())
+                _lib.check(rc, "nxd_zero1_reduce_shard")
         for b in self.buckets:
-            if b.dp == 1:
+            if b.dp == 1 or b.symm is not None:
                 continue
             src = b.flat_grad
             if self.higher_cc_precision and src.dtype != torch.float32:
@@ -316,6 +365,19 @@ class NeuronZero1Optimizer(torch.optim.Optimizer):
                 out = b.flat_param[b.lo:b.hi]
                 if not self._decoupled and group["weight_decay"] != 0.0:
                     b.grad_shard.add_(b.master.to(b.grad_shard.dtype), alpha=group["weight_decay"] / scale)
+                if b.symm is not None:
+                    # AdamW on the shard; the bf16 parameters are stored into every rank's flat buffer (= all-gather)
+                    from ..ops import _lib
+                    import ctypes as _c
+
+                    rc = _lib.lib().nxd_zero1_adamw_allgather(
+                        _lib.ptr(b.master), _lib.ptr(b.exp_avg), _lib.ptr(b.exp_avg_sq), _lib.ptr(b.grad_shard),
+                        b.param_ptrs, _c.c_longlong(b.lo), _c.c_longlong(b.shard_size), _c.c_float(group["lr"]),
+                        _c.c_float(beta1), _c.c_float(beta2), _c.c_float(group["eps"]),
+                        _c.c_float(group["weight_decay"] if self._decoupled else 0.0), _c.c_int(self._step_count),
+                        _c.c_float(scale), _lib.ptr(coef), _c.c_int(b.dp), _c.c_int(b.dp_rank), _lib.stream_ptr())
+                    _lib.check(rc, "nxd_zero1_adamw_allgather")
+                    continue
                 optim_ops.adamw_step_(b.master, b.exp_avg, b.exp_avg_sq, b.grad_shard,
                                       None if out.dtype == b.master.dtype else out, group["lr"], beta1, beta2,
                                       group["eps"], group["weight_decay"] if self._decoupled else 0.0,
@@ -336,9 +398,14 @@ class NeuronZero1Optimizer(torch.optim.Optimizer):
             for b in self.buckets:
                 b.flat_param[b.lo:b.hi].copy_(b.master_param.data)
                 b.master_param.grad = None
+        pushed = None
         for b in self.buckets:
-            if b.dp > 1:
+            if b.dp > 1 and b.symm is not None and self._fused:
+                pushed = b.symm
+            elif b.dp > 1:
                 dist.all_gather_into_tensor(b.flat_param, b.flat_param[b.lo:b.hi].clone(), group=b.shard_group)
+        if pushed is not None:
+            pushed.barrier()             # every rank's parameter slices have landed before the next forward
         return loss
 
     # ------------------------------------------------------------------------------------------

@@ -107,19 +107,23 @@ def _tp_worker(rank, world, port):
                       LOCAL_RANK=str(rank))
     torch.cuda.set_device(rank)
     dev = torch.device("cuda", rank)
-    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
     from neuronx_distributed_llama3_2_b200.inference import InferenceConfig, InferenceRunner
     from neuronx_distributed_llama3_2_b200.models import LlamaForCausalLM
     from neuronx_distributed_llama3_2_b200.parallel import parallel_state as ps
 
+    # full (tp = 1) weights, identical on every rank, built BEFORE the process group exists (sizes are all 1 then);
+    # the runner shards them
+    torch.manual_seed(3)
+    full = LlamaForCausalLM(_cfg(), device=torch.device("cpu"))
+    sd = {k: v.detach().clone() for k, v in full.state_dict().items()}
+    g = torch.Generator(device="cpu").manual_seed(9)
+    prompts = torch.randint(1, 1024, (2, 60), generator=g).to(dev)
+    with torch.no_grad():   # single-process forward of the unsharded model = the oracle for the prefill logits
+        ref = full.to(dev)(prompts).transpose(0, 1)[:, -1].float()
+    del full
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
     try:
-        # full (tp = 1) weights, identical on every rank; the runner shards them
-        torch.manual_seed(3)
-        full = LlamaForCausalLM(_cfg(), device=torch.device("cpu"))
-        sd = {k: v.detach().clone() for k, v in full.state_dict().items()}
         ps.initialize_model_parallel(tensor_model_parallel_size=world)
-        g = torch.Generator(device="cpu").manual_seed(9)
-        prompts = torch.randint(1, 1024, (2, 60), generator=g).to(dev)
         res = {}
         for name, fused, graphs in (("nccl_eager", "0", False), ("fused_eager", "1", False), ("fused_graphs", "1", True)):
             os.environ["NXD_FUSED_COMM"] = fused
@@ -133,8 +137,6 @@ def _tp_worker(rank, world, port):
             # prefill logits against the unsharded model
             pos = torch.arange(60, device=dev).unsqueeze(0).expand(2, 60)
             _, logits = runner.model.forward_infer(prompts, pos, return_logits=True)
-            with torch.no_grad():
-                ref = full.to(dev)(prompts).transpose(0, 1)[:, -1].float()
             assert (logits.float() - ref).abs().max().item() < 0.1, name
             gathered = [torch.empty_like(res[name]) for _ in range(world)]
             dist.all_gather(gathered, res[name])

@@ -25,6 +25,7 @@ def main():
     ap.add_argument("--new", type=int, default=128)
     ap.add_argument("--runs", type=int, default=5)
     ap.add_argument("--no-graphs", action="store_true")
+    ap.add_argument("--profile", default="", help="diagnosis: write a kernel summary of one generate() to this file")
     args = ap.parse_args()
     if args.impl == "baseline":
         os.environ["NXD_GEMM_BACKEND"] = "cublas"
@@ -46,6 +47,27 @@ def main():
                              buckets=[args.prompt], max_new_tokens=args.new, use_cuda_graphs=not args.no_graphs)
         runner = InferenceRunner(cfg, ic, device=dev)
         runner.trace()
+        if args.profile:
+            from torch.profiler import ProfilerActivity, profile
+
+            ids = torch.randint(1, cfg.vocab_size, (B, args.prompt), device=dev)
+            runner.generate(ids, max_new_tokens=args.new)
+            torch.cuda.synchronize()
+            with profile(activities=[ProfilerActivity.CUDA]) as prof:
+                runner.generate(ids, max_new_tokens=args.new)
+                torch.cuda.synchronize()
+            if rank == 0:
+                by = {}
+                for e in prof.events():
+                    if e.device_type == torch.autograd.DeviceType.CUDA:
+                        d = by.setdefault(e.name[:100], [0.0, 0])
+                        d[0] += e.time_range.end - e.time_range.start
+                        d[1] += 1
+                with open(args.profile, "a") as f:
+                    f.write(f"# {args.model} tp{world} batch {B} prompt {args.prompt} new {args.new} impl {args.impl} (us, CUPTI)\n")
+                    for n, (t, c) in sorted(by.items(), key=lambda kv: -kv[1][0])[:40]:
+                        f.write(f"{t:10.0f} us {c:6d} x {t / c:8.2f}  {n}\n")
+            continue
         rep = runner.benchmark_sampling(prompt_len=args.prompt, new_tokens=args.new, n_runs=args.runs)
         tkg = rep["token_generation_model"]
         out = {"metric": f"{args.model} decode tokens/s + p50 TTFT", "impl": args.impl, "n_gpus": world, "batch": B,
