@@ -42,6 +42,10 @@ struct AgArgs {
     int comm_ctas;
     uint32_t epoch;
     unsigned long long* trace;    // optional: globaltimer stamps of a few events (debug)
+    // expert-parallel dispatch (all-to-all -> grouped GEMM): x_local is [tp][R, K] (slab d goes to rank d
+    // only), a slab holds R / expert_rows experts and expert e multiplies weight rows [e * w_expert_stride, ...)
+    int expert_rows;              // 0 = all-gather mode
+    int w_expert_stride;
 };
 
 __device__ __forceinline__ unsigned long long gtime() {
@@ -178,22 +182,43 @@ ag_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a_local, const __grid_co
         if (ipp == 0) {  // more copy CTAs than 16-byte pieces: nothing to move, but the counters expect every CTA
             for (int c = 0; c < chunks_per_slab; ++c) bump(c);
         }
-        tma_stream(smem, bars, phases, ipp * chunks_per_slab, ipp,
-                   [&](int j, const uint8_t*& src, uint32_t& bytes) {
-                       const int c = j / ipp, i = j % ipp;
-                       bytes = (uint32_t)min((size_t)kCommSub, p1 - p0 - (size_t)i * kCommSub);
-                       src = reinterpret_cast<const uint8_t*>(ag.x_local) + (size_t)c * chunk_bytes + p0 + (size_t)i * kCommSub;
-                   },
-                   [&](int j, const uint8_t* sm, uint32_t bytes) {
-                       const int c = j / ipp, i = j % ipp;
-                       const size_t off = (size_t)ag.rank * slab_bytes + (size_t)c * chunk_bytes + p0 + (size_t)i * kCommSub;
-                       // ring order: every rank starts with a different peer, so no link is a hot spot
-                       for (int d = 1; d <= ag.tp; ++d) {
-                           const int peer = (ag.rank + d) % ag.tp;   // d == tp: own X_total (by-product for wgrad)
+        if (ag.expert_rows == 0) {
+            tma_stream(smem, bars, phases, ipp * chunks_per_slab, ipp,
+                       [&](int j, const uint8_t*& src, uint32_t& bytes) {
+                           const int c = j / ipp, i = j % ipp;
+                           bytes = (uint32_t)min((size_t)kCommSub, p1 - p0 - (size_t)i * kCommSub);
+                           src = reinterpret_cast<const uint8_t*>(ag.x_local) + (size_t)c * chunk_bytes + p0 + (size_t)i * kCommSub;
+                       },
+                       [&](int j, const uint8_t* sm, uint32_t bytes) {
+                           const int c = j / ipp, i = j % ipp;
+                           const size_t off = (size_t)ag.rank * slab_bytes + (size_t)c * chunk_bytes + p0 + (size_t)i * kCommSub;
+                           // ring order: every rank starts with a different peer, so no link is a hot spot
+                           for (int d = 1; d <= ag.tp; ++d) {
+                               const int peer = (ag.rank + d) % ag.tp;   // d == tp: own X_total (by-product for wgrad)
+                               bulk_s2g(reinterpret_cast<uint8_t*>(ag.xt_peer[peer]) + off, sm, bytes);
+                           }
+                       },
+                       [&](int j_last) { bump(j_last / ipp); });
+        } else {
+            // all-to-all: item = (chunk, destination, piece); slab d of x_local goes to rank d only (own slab too: the
+            // gathered buffer is kept for the weight gradient)
+            const int per_chunk = ipp * ag.tp;
+            tma_stream(smem, bars, phases, per_chunk * chunks_per_slab, per_chunk,
+                       [&](int j, const uint8_t*& src, uint32_t& bytes) {
+                           const int c = j / per_chunk, r = j % per_chunk, d = r / ipp, i = r % ipp;
+                           const int peer = (ag.rank + 1 + d) % ag.tp;
+                           bytes = (uint32_t)min((size_t)kCommSub, p1 - p0 - (size_t)i * kCommSub);
+                           src = reinterpret_cast<const uint8_t*>(ag.x_local) + (size_t)peer * slab_bytes +
+                                 (size_t)c * chunk_bytes + p0 + (size_t)i * kCommSub;
+                       },
+                       [&](int j, const uint8_t* sm, uint32_t bytes) {
+                           const int c = j / per_chunk, r = j % per_chunk, d = r / ipp, i = r % ipp;
+                           const int peer = (ag.rank + 1 + d) % ag.tp;
+                           const size_t off = (size_t)ag.rank * slab_bytes + (size_t)c * chunk_bytes + p0 + (size_t)i * kCommSub;
                            bulk_s2g(reinterpret_cast<uint8_t*>(ag.xt_peer[peer]) + off, sm, bytes);
-                       }
-                   },
-                   [&](int j_last) { bump(j_last / ipp); });
+                       },
+                       [&](int j_last) { bump(j_last / per_chunk); });
+        }
         if (ag.trace && cid == 0) ag.trace[1] = gtime();
         return;
     }
@@ -270,8 +295,10 @@ ag_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a_local, const __grid_co
                     fence_proxy_async_all();
                 }
                 const CUtensorMap* ma = own ? &tmap_a_local : &tmap_a_total;
-                const int m0 = (own ? 0 : slab * ag.R) + mt * kTileM + (int)cta_rank * kBlockM;
+                // dispatch mode: x_local holds one slab per destination, the own one at row rank * R
+                const int m0 = ((own && ag.expert_rows == 0) ? 0 : slab * ag.R) + mt * kTileM + (int)cta_rank * kBlockM;
                 const int n0 = tn * BN + (int)cta_rank * (BN / 2);
+                const int w_off = ag.expert_rows > 0 ? (mt * kTileM / ag.expert_rows) * ag.w_expert_stride : 0;
                 for (int kb = 0; kb < num_k_blocks; ++kb) {
                     ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
                     uint8_t* sa = smem + stage * L::kStageBytes;
@@ -280,11 +307,12 @@ ag_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a_local, const __grid_co
                     if (is_leader) ptx::mbar_arrive_expect_tx(&full_bar[stage], 2 * L::kStageBytes);
                     ptx::tma_load_2d_pair(ma, &full_bar[stage], sa, k0, m0);
                     if constexpr (!B_MN) {
-                        ptx::tma_load_2d_pair(&tmap_b, &full_bar[stage], sb, k0, n0);
+                        ptx::tma_load_2d_pair(&tmap_b, &full_bar[stage], sb, k0, n0 + w_off);
                     } else {
 #pragma unroll
                         for (int g = 0; g < (BN / 2) / 64; ++g)
-                            ptx::tma_load_2d_pair(&tmap_b, &full_bar[stage], sb + g * (kBlockK * 128), n0 + g * 64, k0);
+                            ptx::tma_load_2d_pair(&tmap_b, &full_bar[stage], sb + g * (kBlockK * 128), n0 + g * 64,
+                                                  k0 + w_off);
                     }
                     if (++stage == kStages) { stage = 0; phase ^= 1; }
                 }
@@ -383,11 +411,13 @@ ag_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a_local, const __grid_co
 // layout 0 "nt": W = [N, K];  1 "nn": W = [K, N].  x_local [R, K] dense, y [tp*R, N] (pitch ldy).
 // xt_ptrs / sig_ptrs: HOST arrays of tp device pointers (own entry included): every rank's symmetric X_total buffer
 // [tp*R, K] for this call, and signal pad.  R % 256 == 0, K % 64 == 0, N % 8 == 0.  trace: optional 16 x u64 (device).
-NXD_API int nxd_ag_gemm_bf16(int layout, const void* x_local, const void* w, void* y, int R, int N, int K,
-                             long long ldw, long long ldy, void* const* xt_ptrs, void* const* sig_ptrs, int tp,
-                             int rank, int slot_chunks, unsigned epoch, int comm_ctas, int block_n, void* trace,
-                             void* stream) {
+static int ag_gemm_impl(int layout, const void* x_local, const void* w, void* y, int R, int N, int K, long long ldw,
+                        long long ldy, void* const* xt_ptrs, void* const* sig_ptrs, int tp, int rank, int slot_chunks,
+                        unsigned epoch, int comm_ctas, int block_n, void* trace, int expert_rows, void* stream) {
     using namespace nxd_gemm;
+    NXD_REQUIRE(expert_rows == 0 || (expert_rows % kChunkRows == 0 && R % expert_rows == 0),
+                "a2a_gemm: rows per expert (%d) must be a multiple of %d and divide the slab (%d)", expert_rows, kChunkRows, R);
+    const int experts = expert_rows > 0 ? R / expert_rows : 1;
     NXD_REQUIRE(layout == 0 || layout == 1, "ag_gemm: layout must be 0 (nt) or 1 (nn)");
     NXD_REQUIRE(tp >= 2 && tp <= kMaxTp && rank >= 0 && rank < tp, "ag_gemm: bad tp/rank %d/%d", tp, rank);
     NXD_REQUIRE(R > 0 && R % kChunkRows == 0, "ag_gemm: rows per rank (%d) must be a multiple of %d", R, kChunkRows);
@@ -406,12 +436,15 @@ NXD_API int nxd_ag_gemm_bf16(int layout, const void* x_local, const void* w, voi
     ag.slot_chunks = slot_chunks;
     ag.tp = tp; ag.rank = rank; ag.R = R; ag.comm_ctas = comm_ctas; ag.epoch = epoch;
     ag.trace = (unsigned long long*)trace;
+    ag.expert_rows = expert_rows;
+    ag.w_expert_stride = layout == 0 ? N : K;     // stacked expert weights: [E * N, K] (nt) or [E * K, N] (nn)
     CUtensorMap ta_l, ta_t, tb, td;
     int rc;
-    if ((rc = make_tmap_2d(&ta_l, x_local, (uint64_t)K, (uint64_t)R, (uint64_t)K, 64, kBlockM))) return rc;
+    if ((rc = make_tmap_2d(&ta_l, x_local, (uint64_t)K, (uint64_t)(expert_rows > 0 ? M : R), (uint64_t)K, 64, kBlockM)))
+        return rc;
     if ((rc = make_tmap_2d(&ta_t, xt_ptrs[rank], (uint64_t)K, (uint64_t)M, (uint64_t)K, 64, kBlockM))) return rc;
-    if (layout == 0) rc = make_tmap_2d(&tb, w, (uint64_t)K, (uint64_t)N, (uint64_t)ldw, 64, bn / 2);
-    else rc = make_tmap_2d(&tb, w, (uint64_t)N, (uint64_t)K, (uint64_t)ldw, 64, kBlockK);
+    if (layout == 0) rc = make_tmap_2d(&tb, w, (uint64_t)K, (uint64_t)N * experts, (uint64_t)ldw, 64, bn / 2);
+    else rc = make_tmap_2d(&tb, w, (uint64_t)N, (uint64_t)K * experts, (uint64_t)ldw, 64, kBlockK);
     if (rc) return rc;
     if ((rc = make_tmap_2d(&td, y, (uint64_t)N, (uint64_t)M, (uint64_t)ldy, 64, 32, 2))) return rc;
     const int clusters = nxd_num_sms() / 2;
@@ -434,4 +467,27 @@ NXD_API int nxd_ag_gemm_bf16(int layout, const void* x_local, const void* w, voi
 #undef NXD_AG_LAUNCH
     NXD_LAUNCH_CHECK();
     return 0;
+}
+
+NXD_API int nxd_ag_gemm_bf16(int layout, const void* x_local, const void* w, void* y, int R, int N, int K,
+                             long long ldw, long long ldy, void* const* xt_ptrs, void* const* sig_ptrs, int tp,
+                             int rank, int slot_chunks, unsigned epoch, int comm_ctas, int block_n, void* trace,
+                             void* stream) {
+    return ag_gemm_impl(layout, x_local, w, y, R, N, K, ldw, ldy, xt_ptrs, sig_ptrs, tp, rank, slot_chunks, epoch,
+                        comm_ctas, block_n, trace, 0, stream);
+}
+
+// Expert-parallel DISPATCH fused with the first expert GEMM (reference: modules/moe/experts.py:121-128
+// `enter_expert_parallel_region` all-to-all, then the expert matmul): x_local is [ep][E_loc, C, K] (slab d = the
+// tokens this rank routed to the experts of rank d), every rank ends up with X_total = [ep(source)][E_loc, C, K] in
+// its symmetric buffer and y[(s, e, c), :] = X_total[s, e, c, :] * W_e.  W: stacked expert weights, layout 0 = [E_loc * N, K]
+// (each expert [N, K]), 1 = [E_loc * K, N].  R = E_loc * C rows per slab, C % 256 == 0.  Other arguments as
+// nxd_ag_gemm_bf16 (tp = ep).
+NXD_API int nxd_a2a_gemm_bf16(int layout, const void* x_local, const void* w, void* y, int R, int C, int N, int K,
+                              long long ldw, long long ldy, void* const* xt_ptrs, void* const* sig_ptrs, int ep,
+                              int rank, int slot_chunks, unsigned epoch, int comm_ctas, int block_n, void* trace,
+                              void* stream) {
+    NXD_REQUIRE(C > 0, "a2a_gemm: capacity must be positive");
+    return ag_gemm_impl(layout, x_local, w, y, R, N, K, ldw, ldy, xt_ptrs, sig_ptrs, ep, rank, slot_chunks, epoch,
+                        comm_ctas, block_n, trace, C, stream);
 }

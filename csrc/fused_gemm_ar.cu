@@ -148,7 +148,8 @@ __global__ void __launch_bounds__(kArThreads) skinny_gemm_ar_kernel(const bf16* 
         const bool v0 = cc < ncols, v1 = cc + 1 < ncols;
         const bf16* w0 = w + (size_t)(c0 + cc) * ldw;
         const bf16* w1 = w0 + ldw;
-#pragma unroll 2
+        // issue the weight loads of several k steps back to back: the loop is bound by load latency, not by math
+#pragma unroll (kB <= 2 ? 8 : kB <= 4 ? 4 : 2)
         for (int k = lane; k < k8; k += 32) {
             const uint4 a0 = v0 ? __ldg(reinterpret_cast<const uint4*>(w0) + k) : make_uint4(0u, 0u, 0u, 0u);
             const uint4 a1 = v1 ? __ldg(reinterpret_cast<const uint4*>(w1) + k) : make_uint4(0u, 0u, 0u, 0u);
@@ -256,6 +257,7 @@ int launch_skinny(const bf16* x, const bf16* w, const bf16* residual, bf16* out,
         NXD_CHECK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, skinny_gemm_ar_kernel<kB>, kArThreads, smem));
         NXD_REQUIRE(per_sm >= 1, "skinny_gemm_ar: kernel does not fit an SM");
         grid = (N + cols - 1) / cols;
+        if (ar.tp == 1) break;            // no spin-wait, no flags: any grid works, one column pair per warp
         if (grid <= min(min(per_sm, 2) * sms, kMaxCtas)) break;
         NXD_REQUIRE(cols < 8192, "skinny_gemm_ar: cannot make N %d co-resident", N);
     }

@@ -38,6 +38,11 @@ struct RsArgs {
     int tp, rank, R;
     uint32_t epoch;
     unsigned long long* trace;      // optional: globaltimer stamps (debug)
+    // expert-parallel COMBINE (grouped GEMM -> all-to-all): row block `dest` of x holds the tokens that came
+    // from rank `dest`; its result tiles go back to that rank and NOTHING is summed (the staging buffer [src][R][N] of
+    // the destination IS its output [E, C, N]).  expert e of a slab uses weight rows [e * w_expert_stride, ...).
+    int expert_rows;                // 0 = reduce-scatter mode
+    int w_expert_stride;
 };
 
 __device__ __forceinline__ unsigned long long rs_gtime() {
@@ -121,6 +126,7 @@ gemm_rs_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                 tile_coords_rs(tile, dest, mt, tn);
                 const int m0 = dest * rs.R + mt * kTileM + (int)cta_rank * kBlockM;
                 const int n0 = tn * BN + (int)cta_rank * (BN / 2);
+                const int w_off = rs.expert_rows > 0 ? (mt * kTileM / rs.expert_rows) * rs.w_expert_stride : 0;
                 for (int kb = 0; kb < num_k_blocks; ++kb) {
                     ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
                     uint8_t* sa = smem + stage * L::kStageBytes;
@@ -129,11 +135,12 @@ gemm_rs_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                     if (is_leader) ptx::mbar_arrive_expect_tx(&full_bar[stage], 2 * L::kStageBytes);
                     ptx::tma_load_2d_pair(&tmap_a, &full_bar[stage], sa, k0, m0);
                     if constexpr (!B_MN) {
-                        ptx::tma_load_2d_pair(&tmap_b, &full_bar[stage], sb, k0, n0);
+                        ptx::tma_load_2d_pair(&tmap_b, &full_bar[stage], sb, k0, n0 + w_off);
                     } else {
 #pragma unroll
                         for (int g = 0; g < (BN / 2) / 64; ++g)
-                            ptx::tma_load_2d_pair(&tmap_b, &full_bar[stage], sb + g * (kBlockK * 128), n0 + g * 64, k0);
+                            ptx::tma_load_2d_pair(&tmap_b, &full_bar[stage], sb + g * (kBlockK * 128), n0 + g * 64,
+                                                  k0 + w_off);
                     }
                     if (++stage == kStages) { stage = 0; phase ^= 1; }
                 }
@@ -249,6 +256,15 @@ gemm_rs_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     const int items = m_tiles_per_slab * col_groups;
     const uint32_t want = rs.epoch * (uint32_t)(num_n_tiles * 2 * kEpilogueWarps);
     if (tr && threadIdx.x == 0) rs.trace[3] = rs_gtime();   // GEMM phase of this CTA over
+    if (rs.expert_rows > 0) {
+        // combine mode: nothing to add -- the kernel only has to outlive the arrival of every source's tiles, so that
+        // its completion means "the local output is complete"
+        for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < rs.tp * m_tiles_per_slab; i += gridDim.x * blockDim.x) {
+            const uint32_t* cnt = rs.sig_local + rs.slot_cnt + i;
+            while ((int32_t)(ld_acquire_sys_u32(cnt) - want) < 0) { __nanosleep(64); }
+        }
+        return;
+    }
     for (int item = blockIdx.x; item < items; item += gridDim.x) {
         const int mt = item / col_groups, cg = item % col_groups;
         if (threadIdx.x < rs.tp) {
@@ -315,10 +331,13 @@ gemm_rs_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
 // layout 0 "nt": W = [N, K];  1 "nn": W = [K, N].  x [tp*R, K] (pitch ldx), out [R, N] (pitch ldo).
 // stage_ptrs / sig_ptrs: HOST arrays of tp device pointers: every rank's staging buffer for THIS call
 // ([tp][R][N] bf16, slot index = source rank) and signal pad.  R % 256 == 0, N % 8 == 0.
-NXD_API int nxd_gemm_rs_bf16(int layout, const void* x, const void* w, void* out, int R, int N, int K, long long ldx,
-                             long long ldw, long long ldo, void* const* stage_ptrs, void* const* sig_ptrs, int tp, int rank,
-                             int slot_cnt, unsigned epoch, int block_n, void* trace, void* stream) {
+static int gemm_rs_impl(int layout, const void* x, const void* w, void* out, int R, int N, int K, long long ldx,
+                        long long ldw, long long ldo, void* const* stage_ptrs, void* const* sig_ptrs, int tp, int rank,
+                        int slot_cnt, unsigned epoch, int block_n, void* trace, int expert_rows, void* stream) {
     using namespace nxd_gemm;
+    NXD_REQUIRE(expert_rows == 0 || (expert_rows % kTileM == 0 && R % expert_rows == 0),
+                "gemm_a2a: rows per expert (%d) must be a multiple of %d and divide the slab (%d)", expert_rows, kTileM, R);
+    const int experts = expert_rows > 0 ? R / expert_rows : 1;
     NXD_REQUIRE(layout == 0 || layout == 1, "gemm_rs: layout must be 0 (nt) or 1 (nn)");
     NXD_REQUIRE(tp >= 2 && tp <= kRsMaxTp && rank >= 0 && rank < tp, "gemm_rs: bad tp/rank %d/%d", tp, rank);
     NXD_REQUIRE(R > 0 && R % kTileM == 0, "gemm_rs: rows per rank (%d) must be a multiple of %d", R, kTileM);
@@ -334,12 +353,14 @@ NXD_API int nxd_gemm_rs_bf16(int layout, const void* x, const void* w, void* out
     for (int r = 0; r < tp; ++r) rs.sig_peer[r] = (uint32_t*)sig_ptrs[r];
     rs.slot_cnt = slot_cnt; rs.tp = tp; rs.rank = rank; rs.R = R; rs.epoch = epoch;
     rs.trace = (unsigned long long*)trace;
+    rs.expert_rows = expert_rows;
+    rs.w_expert_stride = layout == 0 ? N : K;
     CUtensorMap ta, tb;
     RsTmaps td;
     int rc;
     if ((rc = make_tmap_2d(&ta, x, (uint64_t)K, (uint64_t)M, (uint64_t)ldx, 64, kBlockM))) return rc;
-    if (layout == 0) rc = make_tmap_2d(&tb, w, (uint64_t)K, (uint64_t)N, (uint64_t)ldw, 64, bn / 2);
-    else rc = make_tmap_2d(&tb, w, (uint64_t)N, (uint64_t)K, (uint64_t)ldw, 64, kBlockK);
+    if (layout == 0) rc = make_tmap_2d(&tb, w, (uint64_t)K, (uint64_t)N * experts, (uint64_t)ldw, 64, bn / 2);
+    else rc = make_tmap_2d(&tb, w, (uint64_t)N, (uint64_t)K * experts, (uint64_t)ldw, 64, kBlockK);
     if (rc) return rc;
     for (int r = 0; r < tp; ++r) {
         const bf16* base = (const bf16*)stage_ptrs[r] + (size_t)rank * R * N;   // my slot on rank r
@@ -364,4 +385,24 @@ NXD_API int nxd_gemm_rs_bf16(int layout, const void* x, const void* w, void* out
 #undef NXD_RS_LAUNCH
     NXD_LAUNCH_CHECK();
     return 0;
+}
+
+NXD_API int nxd_gemm_rs_bf16(int layout, const void* x, const void* w, void* out, int R, int N, int K, long long ldx,
+                             long long ldw, long long ldo, void* const* stage_ptrs, void* const* sig_ptrs, int tp, int rank,
+                             int slot_cnt, unsigned epoch, int block_n, void* trace, void* stream) {
+    return gemm_rs_impl(layout, x, w, out, R, N, K, ldx, ldw, ldo, stage_ptrs, sig_ptrs, tp, rank, slot_cnt, epoch,
+                        block_n, trace, 0, stream);
+}
+
+// Second expert GEMM fused with the expert-parallel COMBINE (reference: expert matmul then
+// `exit_expert_parallel_region` all-to-all, modules/moe/experts.py:145-152): x is [ep(source)][E_loc, C, K], slab s
+// holds the tokens that rank s dispatched here; tile results are TMA-stored straight into rank s's output
+// [ep(owner)][E_loc, C, N] = [E, C, N] (out_ptrs: every rank's symmetric output buffer of THIS call).  When the kernel
+// completes, out_ptrs[rank] is complete.  W: stacked expert weights as in nxd_a2a_gemm_bf16.  C % 256 == 0.
+NXD_API int nxd_gemm_a2a_bf16(int layout, const void* x, const void* w, int R, int C, int N, int K, long long ldx,
+                              long long ldw, void* const* out_ptrs, void* const* sig_ptrs, int ep, int rank, int slot_cnt,
+                              unsigned epoch, int block_n, void* trace, void* stream) {
+    NXD_REQUIRE(C > 0, "gemm_a2a: capacity must be positive");
+    return gemm_rs_impl(layout, x, w, out_ptrs[rank], R, N, K, ldx, ldw, (long long)N, out_ptrs, sig_ptrs, ep, rank, slot_cnt,
+                        epoch, block_n, trace, C, stream);
 }

@@ -127,7 +127,10 @@ class LlamaInferenceModel(LlamaForCausalLM):
         hidden = self._embed(input_ids)
         lengths = (position_ids[:, -1] + 1).to(torch.int32)
         residual = None
-        sid = None if (default_lines and not prefill) else (
+        # token generation without continuous batching: row b IS cache line b -- never gather cache lines by seq_ids
+        # (an index_select of a [B, Hkv, S, D] cache per layer and token costs more than the attention itself)
+        identity = default_lines or not self.inference_config.is_continuous_batching
+        sid = None if (identity and not prefill) else (
             seq_ids if seq_ids is not None else torch.arange(B, device=input_ids.device, dtype=torch.int32))
         for i, layer in enumerate(self.model.layers):
             hidden, residual = self._layer(i, layer, hidden, residual, position_ids, sid, lengths, prefill)

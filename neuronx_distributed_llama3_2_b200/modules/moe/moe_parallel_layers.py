@@ -22,11 +22,42 @@ from ...parallel import parallel_state as ps
 from ...parallel.utils import divide, set_tensor_model_parallel_attributes
 
 
-def _grouped_mm(x: torch.Tensor, w: torch.Tensor) -> torch.Tensor:
-    """``(e, c, a) @ (e, a, b) -> (e, c, b)``; extra leading dims of ``x`` are folded into ``c``."""
+def _use_tc(*ts: torch.Tensor) -> bool:
+    """tcgen05 GEMM per expert (bf16 on the GPU, TMA-compatible shapes); otherwise torch.bmm (CPU tests, fp32)."""
+    from ...ops import linear as gemm_ops
+
+    if not all(t.is_cuda and t.dtype == torch.bfloat16 for t in ts) or gemm_ops._backend() != "tcgen05":
+        return False
+    return all(d % 8 == 0 for t in ts for d in t.shape[-2:])
+
+
+def _grouped_mm(x: torch.Tensor, w: torch.Tensor, layout: str = "nn") -> torch.Tensor:
+    """Per-expert GEMM.  ``nn``: ``(e, c, a) @ (e, a, b) -> (e, c, b)``; ``nt``: ``(e, c, b) @ (e, a, b)^T -> (e, c, a)``;
+    ``tn``: ``(e, c, a)^T @ (e, c, b) -> (e, a, b)``.  Extra leading dims of ``x`` are folded into ``c``."""
+    e = x.shape[0]
     lead = x.shape[1:-1]
-    y = torch.bmm(x.reshape(x.shape[0], -1, x.shape[-1]), w)
-    return y.reshape((x.shape[0],) + tuple(lead) + (w.shape[-1],))
+    x3 = x.reshape(e, -1, x.shape[-1])
+    if layout == "tn":
+        w3 = w.reshape(e, -1, w.shape[-1])
+        if _use_tc(x3, w3):
+            from ...ops.gemm import gemm
+
+            y = torch.empty((e, x3.shape[2], w3.shape[2]), dtype=x.dtype, device=x.device)
+            for i in range(e):
+                gemm(x3[i], w3[i], "tn", out=y[i])
+            return y
+        return torch.bmm(x3.transpose(1, 2), w3)
+    n_out = w.shape[-1] if layout == "nn" else w.shape[-2]
+    if _use_tc(x3, w):
+        from ...ops.gemm import gemm
+
+        x3 = x3.contiguous()
+        y = torch.empty((e, x3.shape[1], n_out), dtype=x.dtype, device=x.device)
+        for i in range(e):
+            gemm(x3[i], w[i], layout, out=y[i])
+    else:
+        y = torch.bmm(x3, w if layout == "nn" else w.transpose(1, 2))
+    return y.reshape((e,) + tuple(lead) + (n_out,))
 
 
 class ExpertFusedLinearWithAsyncCommunication(torch.autograd.Function):
@@ -42,15 +73,12 @@ class ExpertFusedLinearWithAsyncCommunication(torch.autograd.Function):
     @staticmethod
     def backward(ctx, grad_output):
         input, weight = ctx.saved_tensors
-        grad_input = _grouped_mm(grad_output, weight.transpose(1, 2))
+        grad_input = _grouped_mm(grad_output, weight, "nt")
         handle = None
         if ctx.async_grad_allreduce and ps.get_tensor_model_parallel_size() > 1:
             grad_input = grad_input.contiguous()
             handle = dist.all_reduce(grad_input, group=ps.get_tensor_model_parallel_group(), async_op=True)
-        e = input.shape[0]
-        x2 = input.reshape(e, -1, input.shape[-1])
-        g2 = grad_output.reshape(e, -1, grad_output.shape[-1])
-        grad_weight = torch.bmm(x2.transpose(1, 2), g2) if weight.requires_grad else None
+        grad_weight = _grouped_mm(input, grad_output, "tn") if weight.requires_grad else None
         if handle is not None:
             handle.wait()
         return grad_input, grad_weight, None

@@ -219,3 +219,98 @@ def fused_gemm_ar(ctx, x2d: torch.Tensor, weight: torch.Tensor, layout: str = "n
 
     y = gemm_ops.gemm_nt(x2d, weight) if layout == "nt" else gemm_ops.gemm_nn(x2d, weight)
     return oneshot_all_reduce(ctx, y.contiguous(), out=y if y.is_contiguous() else None)
+
+
+# ---- expert parallelism: dispatch / combine all-to-all fused with the expert GEMMs (csrc/fused_ag_gemm.cu, fused_gemm_rs.cu) ---
+def _expert_weight_2d(weight: torch.Tensor, layout: str) -> Optional[torch.Tensor]:
+    """Stacked expert weights ``[E_loc, a, b]`` as the 2-D operand of the fused kernels (``nn``: each expert is
+    ``[K, N]``; ``nt``: each expert is ``[N, K]``)."""
+    if weight.dim() != 3 or not weight.is_contiguous() or weight.dtype != torch.bfloat16:
+        return None
+    return weight.reshape(weight.shape[0] * weight.shape[1], weight.shape[2])
+
+
+def fused_a2a_gemm(ctx, x: torch.Tensor, weight: torch.Tensor, layout: str = "nn"
+                   ) -> Optional[Tuple[torch.Tensor, torch.Tensor]]:
+    """Expert-parallel dispatch + expert GEMM in one kernel.  ``x [ep, E_loc, C, K]``: slab ``d`` = tokens routed to
+    the experts of EP rank ``d``.  Returns ``(y [ep(src), E_loc, C, N], x_total [ep(src), E_loc, C, K])`` -- the
+    received tokens are a by-product kept for the weight gradient (a private copy) -- or ``None`` if unsupported."""
+    if layout not in _LAYOUT or x.dtype != torch.bfloat16 or x.dim() != 4:
+        return None
+    ep, e_loc, C, K = x.shape
+    w2d = _expert_weight_2d(weight, layout)
+    if w2d is None or ep != ctx.world or ep > 8 or weight.shape[0] != e_loc:
+        return None
+    N = weight.shape[2] if layout == "nn" else weight.shape[1]
+    if (weight.shape[1] if layout == "nn" else weight.shape[2]) != K:
+        return None
+    R = e_loc * C
+    if C % 256 or K % 64 or N % 8 or R // 256 > 64:
+        return None
+    x = x.contiguous()
+    total_bytes = ep * R * K * 2
+    comm_ctas = _comm_ctas(ep)
+    cfg = f"a2a:{R}:{K}:{comm_ctas}"
+    local_ptr, table = ctx.region(cfg, 2 * total_bytes)
+    st = ctx.__dict__.setdefault("_fused_state", {})
+    if cfg not in st:
+        st[cfg] = {"chunks": ctx.signal_slots(cfg + ":chunks", 8 * (R // 256)),
+                   "sigs": (_c.c_void_p * ep)(*ctx.sig_peers), "bufs": {}}
+    s = st[cfg]
+    epoch = ctx.next_epoch(cfg)
+    parity = epoch & 1
+    key = (table.data_ptr(), parity)
+    if key not in s["bufs"]:
+        s["bufs"][key] = (_host_ptrs(ctx, table, parity * total_bytes),
+                          ctx.tensor_view(local_ptr + parity * total_bytes, (ep, e_loc, C, K), torch.bfloat16))
+    xt_ptrs, x_total = s["bufs"][key]
+    y = torch.empty((ep, e_loc, C, N), dtype=torch.bfloat16, device=x.device)
+    rc = _lib.lib().nxd_a2a_gemm_bf16(
+        _c.c_int(_LAYOUT[layout]), _lib.ptr(x), _lib.ptr(w2d), _lib.ptr(y), _c.c_int(R), _c.c_int(C), _c.c_int(N),
+        _c.c_int(K), _c.c_longlong(w2d.stride(0)), _c.c_longlong(N), xt_ptrs, s["sigs"], _c.c_int(ep),
+        _c.c_int(ctx.rank), _c.c_int(s["chunks"]), _c.c_uint(epoch), _c.c_int(comm_ctas), _c.c_int(0), None,
+        _lib.stream_ptr())
+    _lib.check(rc, "nxd_a2a_gemm_bf16")
+    return y, x_total.clone()
+
+
+def fused_gemm_a2a(ctx, x: torch.Tensor, weight: torch.Tensor, layout: str = "nn") -> Optional[torch.Tensor]:
+    """Expert GEMM + expert-parallel combine in one kernel.  ``x [ep(src), E_loc, C, K]`` (slab ``s`` = tokens that came
+    from EP rank ``s``); every result tile is stored straight into the output of the rank the tokens came from.
+    Returns this rank's ``[E, C, N]`` (``E = ep * E_loc``, expert-major as before the dispatch) or ``None``."""
+    if layout not in _LAYOUT or x.dtype != torch.bfloat16 or x.dim() != 4:
+        return None
+    ep, e_loc, C, K = x.shape
+    w2d = _expert_weight_2d(weight, layout)
+    if w2d is None or ep != ctx.world or ep > 8 or weight.shape[0] != e_loc:
+        return None
+    N = weight.shape[2] if layout == "nn" else weight.shape[1]
+    if (weight.shape[1] if layout == "nn" else weight.shape[2]) != K:
+        return None
+    R = e_loc * C
+    if C % 256 or K % 8 or N % 8 or R // 256 > 64:
+        return None
+    x = x.contiguous()
+    bn = 256
+    cfg = f"ga2a:{R}:{N}:{bn}"
+    out_bytes = ep * R * N * 2
+    local_ptr, table = ctx.region(cfg, 2 * out_bytes)
+    st = ctx.__dict__.setdefault("_fused_state", {})
+    if cfg not in st:
+        st[cfg] = {"cnt": ctx.signal_slots(cfg + ":cnt", 8 * (R // 256)), "sigs": (_c.c_void_p * ep)(*ctx.sig_peers),
+                   "outs": {}}
+    s = st[cfg]
+    epoch = ctx.next_epoch(cfg)
+    parity = epoch & 1
+    key = (table.data_ptr(), parity)
+    if key not in s["outs"]:
+        s["outs"][key] = (_host_ptrs(ctx, table, parity * out_bytes),
+                          ctx.tensor_view(local_ptr + parity * out_bytes, (ep * e_loc, C, N), torch.bfloat16))
+    out_ptrs, out = s["outs"][key]
+    x2d = x.reshape(ep * R, K)
+    rc = _lib.lib().nxd_gemm_a2a_bf16(
+        _c.c_int(_LAYOUT[layout]), _lib.ptr(x2d), _lib.ptr(w2d), _c.c_int(R), _c.c_int(C), _c.c_int(N), _c.c_int(K),
+        _c.c_longlong(x2d.stride(0)), _c.c_longlong(w2d.stride(0)), out_ptrs, s["sigs"], _c.c_int(ep),
+        _c.c_int(ctx.rank), _c.c_int(s["cnt"]), _c.c_uint(epoch), _c.c_int(bn), None, _lib.stream_ptr())
+    _lib.check(rc, "nxd_gemm_a2a_bf16")
+    return out.clone()      # the symmetric buffer is rewritten two calls later

@@ -92,3 +92,25 @@ def _reset_parallel_state():
             ps.destroy_model_parallel()
     except Exception:
         pass
+
+
+def spawn_gpu_workers(fn, args, nprocs: int, deadline_s: float = 150.0) -> None:
+    """``torch.multiprocessing.spawn`` with a hard deadline: a rank that spins on a flag of a dead peer would otherwise
+    hold the GPUs until the outer job limit.  On expiry the workers (exact PIDs) are killed and the test fails."""
+    import os
+    import signal
+    import time
+
+    import torch.multiprocessing as mp
+
+    ctx = mp.spawn(fn, args=args, nprocs=nprocs, join=False)
+    t0 = time.time()
+    try:
+        while not ctx.join(timeout=2.0):
+            if time.time() - t0 > deadline_s:
+                raise TimeoutError(f"GPU workers still running after {deadline_s:.0f} s")
+    except BaseException:
+        for proc in ctx.processes:
+            if proc.is_alive():
+                os.kill(proc.pid, signal.SIGKILL)
+        raise

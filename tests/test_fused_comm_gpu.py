@@ -39,9 +39,9 @@ def _worker(rank, world, port, case):
 def _spawn(case, world=2):
     if torch.cuda.device_count() < world:
         pytest.skip(f"needs {world} GPUs")
-    import torch.multiprocessing as mp
+    from conftest import spawn_gpu_workers
 
-    mp.spawn(_worker, args=(world, _free_port(), case), nprocs=world, join=True)
+    spawn_gpu_workers(_worker, (world, _free_port(), case), world)
 
 
 def _rel(a, b):
@@ -224,6 +224,58 @@ def case_zero1_fused(rank, world):
     assert _rel(got, ref) < 5e-3, _rel(got, ref)
 
 
+def _worker_ep(rank, world, port, case):
+    import torch.distributed as dist
+
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world),
+                      LOCAL_RANK=str(rank))
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    from neuronx_distributed_llama3_2_b200.parallel import parallel_state as ps
+
+    ps.initialize_model_parallel(tensor_model_parallel_size=1, expert_model_parallel_size=world)
+    try:
+        globals()[case](rank, world)
+        torch.cuda.synchronize()
+        dist.barrier()
+    finally:
+        ps.destroy_model_parallel()
+        dist.destroy_process_group()
+
+
+def case_moe_fused(rank, world):
+    """Expert-parallel dispatch + GEMM and GEMM + combine kernels against the NCCL all-to-all + per-expert GEMM path."""
+    from neuronx_distributed_llama3_2_b200.modules.moe.experts import Experts
+
+    E, C, H, I = 4, 256, 256, 512
+    torch.manual_seed(5)
+    experts = Experts(E, H, I, glu=True, activation_fn=torch.nn.functional.silu, dtype=torch.bfloat16,
+                      device=torch.device("cuda"))
+    with torch.no_grad():
+        for p in experts.parameters():
+            p.mul_(0.5)
+    res = {}
+    for it in range(3):                                   # three rounds: both buffer parities are reused
+        g = torch.Generator(device="cuda").manual_seed(70 + 10 * it + rank)
+        x = torch.randn(E, C, H, device="cuda", generator=g).bfloat16()
+        dy = torch.randn(E, C, H, device="cuda", generator=g).bfloat16()
+        for fused in ("0", "1"):
+            os.environ["NXD_FUSED_MOE"] = fused
+            xr = x.clone().requires_grad_()
+            for p in experts.parameters():
+                p.grad = None
+            out = experts(xr)
+            out.backward(dy)
+            res[fused] = (out.detach(), xr.grad.clone(), [p.grad.clone() for p in experts.parameters()])
+        o0, gx0, gw0 = res["0"]
+        o1, gx1, gw1 = res["1"]
+        assert _rel(o1, o0) < 1e-2, (it, _rel(o1, o0))
+        assert _rel(gx1, gx0) < 1e-2, (it, _rel(gx1, gx0))
+        for a, b in zip(gw1, gw0):
+            assert _rel(a, b) < 1e-2, (it, _rel(a, b))
+    os.environ["NXD_FUSED_MOE"] = "1"
+
+
 def test_fused_ag_gemm_tp2():
     _spawn("case_ag_gemm", 2)
 
@@ -243,6 +295,14 @@ def test_sp_embedding_push_tp2():
 def test_zero1_fused_step_dp2():
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs")
-    import torch.multiprocessing as mp
+    from conftest import spawn_gpu_workers
 
-    mp.spawn(_worker_dp, args=(2, _free_port(), "case_zero1_fused"), nprocs=2, join=True)
+    spawn_gpu_workers(_worker_dp, (2, _free_port(), "case_zero1_fused"), 2)
+
+
+def test_moe_fused_dispatch_combine_ep2():
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    from conftest import spawn_gpu_workers
+
+    spawn_gpu_workers(_worker_ep, (2, _free_port(), "case_moe_fused"), 2, deadline_s=90.0)

@@ -100,7 +100,7 @@ def _free_port():
         return s.getsockname()[1]
 
 
-def _tp_worker(rank, world, port):
+def _tp_worker(rank, world, port, modes):
     import torch.distributed as dist
 
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world),
@@ -125,7 +125,9 @@ def _tp_worker(rank, world, port):
     try:
         ps.initialize_model_parallel(tensor_model_parallel_size=world)
         res = {}
-        for name, fused, graphs in (("nccl_eager", "0", False), ("fused_eager", "1", False), ("fused_graphs", "1", True)):
+        table = {"nccl_eager": ("0", False), "fused_eager": ("1", False), "fused_graphs": ("1", True)}
+        for name in modes:
+            fused, graphs = table[name]
             os.environ["NXD_FUSED_COMM"] = fused
             ic = InferenceConfig(tp_degree=world, batch_size=2, max_context_length=128, seq_len=256, buckets=[64, 128],
                                  max_new_tokens=8, use_cuda_graphs=graphs)
@@ -141,7 +143,10 @@ def _tp_worker(rank, world, port):
             gathered = [torch.empty_like(res[name]) for _ in range(world)]
             dist.all_gather(gathered, res[name])
             assert all(torch.equal(gathered[0], t) for t in gathered), f"{name}: ranks generated different tokens"
-        assert torch.equal(res["fused_eager"], res["fused_graphs"])
+        if "fused_eager" in res and "fused_graphs" in res:
+            assert torch.equal(res["fused_eager"], res["fused_graphs"])
+        if "fused_eager" in res and "nccl_eager" in res:   # greedy tokens may differ only through bf16 ties
+            assert (res["fused_eager"] == res["nccl_eager"]).float().mean().item() > 0.9
         torch.cuda.synchronize()
         dist.barrier()
     finally:
@@ -149,9 +154,11 @@ def _tp_worker(rank, world, port):
         dist.destroy_process_group()
 
 
-def test_tp2_inference_fused_allreduce_and_graphs():
+@pytest.mark.parametrize("modes", [("nccl_eager", "fused_eager"), ("fused_eager", "fused_graphs")],
+                         ids=["eager", "graphs"])
+def test_tp2_inference_fused_allreduce(modes):
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs")
-    import torch.multiprocessing as mp
+    from conftest import spawn_gpu_workers
 
-    mp.spawn(_tp_worker, args=(2, _free_port()), nprocs=2, join=True)
+    spawn_gpu_workers(_tp_worker, (2, _free_port(), modes), 2, deadline_s=90.0)

@@ -67,7 +67,9 @@ def main():
                     f.write(f"# {args.model} tp{world} batch {B} prompt {args.prompt} new {args.new} impl {args.impl} (us, CUPTI)\n")
                     for n, (t, c) in sorted(by.items(), key=lambda kv: -kv[1][0])[:40]:
                         f.write(f"{t:10.0f} us {c:6d} x {t / c:8.2f}  {n}\n")
-            continue
+            if world > 1:
+                dist.barrier()
+            os._exit(0)          # CUPTI + communicator teardown can hang; the summary is on disk
         rep = runner.benchmark_sampling(prompt_len=args.prompt, new_tokens=args.new, n_runs=args.runs)
         tkg = rep["token_generation_model"]
         out = {"metric": f"{args.model} decode tokens/s + p50 TTFT", "impl": args.impl, "n_gpus": world, "batch": B,
