@@ -8,6 +8,14 @@
 namespace nxd_gemm {
 
 static PFN_cuTensorMapEncodeTiled_v12000 get_encode() {
+    // The encode call is a DRIVER entry point and needs a current context on the calling thread.  A thread that has
+    // made no runtime call yet (an autograd worker whose first CUDA work is one of our launches) has none: bind the
+    // primary context of the thread's device once per thread.
+    static thread_local bool ctx_bound = false;
+    if (!ctx_bound) {
+        cudaFree(nullptr);
+        ctx_bound = true;
+    }
     static PFN_cuTensorMapEncodeTiled_v12000 fn = nullptr;
     if (fn) return fn;
     void* p = nullptr;

@@ -76,6 +76,7 @@ def main():
         rep = runner.benchmark_sampling()
         if ps.is_global_rank_zero():
             print(json.dumps(rep, indent=1))
+    runner.close()
     if world > 1:
         dist.destroy_process_group()
 

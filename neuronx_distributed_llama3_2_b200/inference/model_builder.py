@@ -174,6 +174,14 @@ class NxDModel(torch.nn.Module):
         _, bucket = self.router(args)
         return bucket(*args)
 
+    def release_graphs(self) -> None:
+        """Destroy the captured CUDA graphs (buckets fall back to eager execution).  Call this -- or drop the model --
+        BEFORE ``torch.distributed.destroy_process_group()``: NCCL keeps a communicator alive while a CUDA graph that
+        captured one of its collectives exists, and the destroy call then waits forever."""
+        for _, _, b in self._graphs:
+            b.graph = None
+            b.static_out = None
+
     def keys(self) -> List[str]:
         return list(self._buckets)
 

@@ -69,6 +69,11 @@ class InferenceRunner:
                 builder.shard_checkpoint(os.path.join(traced_model_path, "weights"))
         return self.nxd_model
 
+    def close(self) -> None:
+        """Release the CUDA graphs (required before the process group is destroyed, see ``NxDModel.release_graphs``)."""
+        if self.nxd_model is not None:
+            self.nxd_model.release_graphs()
+
     # -- generate -------------------------------------------------------------------------------------------------------
     def _bucket_len(self, n: int) -> int:
         if self.nxd_model is not None:

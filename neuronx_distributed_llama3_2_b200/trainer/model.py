@@ -14,6 +14,16 @@ class NxDModel(torch.nn.Module):
         self.nxd_config = nxd_config
         self.pp_enabled = nxd_config["pipeline_parallel_size"] > 1
 
+    def local_modules(self):
+        """Modules that live on this rank: the local pipeline-stage modules under PP, else the whole model
+        (reference ``trainer/model.py:24-27``)."""
+        if hasattr(self.module, "local_stage_modules"):
+            return self.module.local_stage_modules
+        return [self.module]
+
+    def __repr__(self):
+        return "NxDModel(" + self.module.__repr__() + ")"
+
     def original_module(self):
         return self.module.original_torch_module if self.pp_enabled else self.module
 

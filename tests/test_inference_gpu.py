@@ -143,6 +143,7 @@ def _tp_worker(rank, world, port, modes):
             gathered = [torch.empty_like(res[name]) for _ in range(world)]
             dist.all_gather(gathered, res[name])
             assert all(torch.equal(gathered[0], t) for t in gathered), f"{name}: ranks generated different tokens"
+            runner.close()      # graphs that captured NCCL collectives must be gone before the group is destroyed
         if "fused_eager" in res and "fused_graphs" in res:
             assert torch.equal(res["fused_eager"], res["fused_graphs"])
         if "fused_eager" in res and "nccl_eager" in res:   # greedy tokens may differ only through bf16 ties

@@ -89,3 +89,31 @@ def test_training_utils():
     it = SyntheticTokens(100, 2, 8, "cpu", n_batches=2)
     a, b, c = next(it), next(it), next(it)
     assert a.shape == (2, 8) and torch.equal(a, c) and not torch.equal(a, b)
+
+
+def test_utils_namespace_matches_reference_modules():
+    """``utils/{timeline,sampling,speculative_decoding,medusa_utils,tensor_utils}`` exist with the reference names."""
+    import torch
+
+    from neuronx_distributed_llama3_2_b200.modules.moe import ACT2FN
+    from neuronx_distributed_llama3_2_b200.utils import medusa_utils, sampling, speculative_decoding, tensor_utils, timeline
+
+    assert "silu" in ACT2FN and callable(ACT2FN["silu"])
+    assert timeline.Event("fwd", 1, 10, 25).as_chrome_event()["dur"] == 15 and hasattr(timeline, "Timeline")
+    assert hasattr(sampling, "Sampler") and hasattr(speculative_decoding, "NeuronSpeculation")
+    x = torch.arange(12).reshape(3, 4)
+    assert torch.equal(tensor_utils.cumsum(x, dim=1), torch.cumsum(x, 1))
+    assert medusa_utils.pad_path([1, 2, 3], 5) == [1, 2, 3, -2, -2] and medusa_utils.pad_path([1, 2], 1) == [1, 2]
+    bufs = medusa_utils.generate_medusa_buffers([[0], [1], [0, 0], [0, 1], [1, 0]])
+    ri = bufs["retrieve_indices"]
+    assert bufs["tree_indices"].shape[0] == 6 and ri.shape[1] == 3
+    # accept two speculated tokens of path 0: ids grow by 3, logits are cut to the position after the accepted prefix
+    V, heads = 7, 2
+    ids = torch.tensor([[5, 6, 7]])
+    cands = torch.tensor([[1, 2, 3], [1, 4, 0], [1, 5, 6]])
+    logits = torch.randn(3, 3, V)
+    mlog = torch.randn(heads, 3, 3, V)
+    ids2, l2, m2, n_new, sel = medusa_utils.update_inference_inputs(ids, cands, 0, 2, ri, logits, mlog, 0)
+    assert ids2.tolist() == [[5, 6, 7, 1, 2, 3]] and n_new == 3
+    assert l2.shape == (1, 1, V) and torch.equal(l2[0, 0], logits[0, 2]) and m2.shape == (heads, 1, 1, V)
+    assert torch.equal(sel, ri[0, :3] + 3)

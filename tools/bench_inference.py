@@ -84,6 +84,7 @@ def main():
             out["decode_tokens_per_s"] = B * 1e3 / float(t[1])
         if rank == 0:
             print(json.dumps(out), flush=True)
+        runner.close()
         del runner
         torch.cuda.empty_cache()
     if world > 1:
