@@ -43,6 +43,9 @@ def parse_args():
     ap.add_argument("--micro-batch", type=int, default=int(os.environ.get("NXD_BENCH_MB", 1)))
     ap.add_argument("--layers", type=int, default=0, help="debug only: override the layer count (marks the run invalid)")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-inference", action="store_true",
+                    help="skip the second half of the headline metric (Llama-3.2-1B TTFT / decode tokens/s, reported "
+                         "under the extra key \"inference\")")
     ap.add_argument("--profile", default="", help="diagnosis only: write a kernel timeline summary of 2 steps (rank 0) "
                     "to this file instead of timing (numbers under a profiler are never bench values)")
     return ap.parse_args()
@@ -148,6 +151,35 @@ def profile_steps(args, step, barrier, rank, world):
     with open(args.profile, "w") as f:
         f.write("\n".join(lines) + "\n")
     print(json.dumps({"profile": args.profile, "invalid": "profiler run"}))
+
+
+def inference_metric(args, dev, world, rank):
+    """Llama-3.2-1B, TP = world, prompt 2048, 64 new tokens, CUDA-graph buckets: p50 TTFT and decode tokens/s
+    (BASELINE.json metric, second half; random-init weights, synthetic prompts).  Device-timed, max over ranks."""
+    import torch
+    import torch.distributed as dist
+
+    from neuronx_distributed_llama3_2_b200.inference import InferenceConfig, InferenceRunner
+    from neuronx_distributed_llama3_2_b200.models import PRESETS
+
+    res = {"model": "llama3.2-1b", "prompt_len": 2048, "new_tokens": 64, "parallelism": f"tp{world}", "cuda_graphs": True}
+    for B in (1, 16):
+        cfg = PRESETS["llama3.2-1b"](sequence_parallel_enabled=False)
+        ic = InferenceConfig(tp_degree=world, batch_size=B, max_context_length=2048, seq_len=4096, buckets=[2048],
+                             max_new_tokens=64, use_cuda_graphs=True)
+        runner = InferenceRunner(cfg, ic, device=dev)
+        runner.trace()
+        rep = runner.benchmark_sampling(prompt_len=2048, new_tokens=64, n_runs=3)
+        t = torch.tensor([rep["ttft_ms_p50"], rep["token_generation_model"]["latency_ms_p50"]], device=dev,
+                         dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        res[f"batch{B}"] = {"ttft_ms_p50": float(t[0]), "decode_ms_per_token_p50": float(t[1]),
+                            "decode_tokens_per_s": B * 1e3 / float(t[1])}
+        runner.close()
+        del runner
+        torch.cuda.empty_cache()
+    return res
 
 
 def main():
@@ -289,7 +321,34 @@ def main():
         }
         if args.layers:
             out["invalid"] = "debug run with a truncated model"
-        print(json.dumps(out))
+    else:
+        out = None
+    # second half of the headline metric: Llama-3.2-1B TTFT + decode tokens/s on the same N GPUs (TP = N).  The training
+    # numbers above are final; a watchdog prints them and ends the process if the inference part does not return.
+    if not args.no_inference and os.environ.get("NXD_BENCH_INFERENCE", "1") == "1":
+        import threading
+
+        def bail():
+            if rank == 0:
+                out["inference"] = {"error": "timed out"}
+                print(json.dumps(out), flush=True)
+            os._exit(0)
+
+        dog = threading.Timer(float(os.environ.get("NXD_BENCH_INFERENCE_TIMEOUT", "150")), bail)
+        dog.daemon = True
+        dog.start()
+        try:
+            last_loss = None
+            del model, opt
+            torch.cuda.empty_cache()
+            inf = inference_metric(args, dev, world, rank)
+        except Exception as e:  # noqa: BLE001 - the training number must survive
+            inf = {"error": f"{type(e).__name__}: {e}"[:300]}
+        dog.cancel()
+        if rank == 0:
+            out["inference"] = inf
+    if rank == 0:
+        print(json.dumps(out), flush=True)
     if world > 1:
         dist.destroy_process_group()
 
