@@ -4,7 +4,7 @@
 from __future__ import annotations
 
 import contextlib
-from typing import Any, Dict, Optional
+from typing import Any, Dict
 
 import torch
 

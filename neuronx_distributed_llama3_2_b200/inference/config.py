@@ -1,7 +1,7 @@
 """Inference configuration (reference ``examples/inference/modules/config.py:4-68``)."""
 from __future__ import annotations
 
-from dataclasses import dataclass, field
+from dataclasses import dataclass
 from typing import List, Optional
 
 

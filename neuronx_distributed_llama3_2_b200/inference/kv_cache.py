@@ -7,7 +7,7 @@ Here the cache is a plain device allocation per layer that the kernels update IN
 """
 from __future__ import annotations
 
-from typing import List, Optional, Tuple
+from typing import List, Tuple
 
 import torch
 

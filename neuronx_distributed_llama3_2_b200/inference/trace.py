@@ -4,7 +4,7 @@ compiles one TorchScript per rank; here every rank already is a process, "tracin
 from __future__ import annotations
 
 import os
-from typing import Any, Callable, Dict, Sequence, Tuple
+from typing import Any, Callable, Sequence
 
 import torch
 

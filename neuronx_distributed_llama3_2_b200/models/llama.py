@@ -20,7 +20,6 @@ B200 design notes
 """
 from __future__ import annotations
 
-import math
 from dataclasses import asdict, dataclass, field
 from typing import Any, Dict, Optional, Tuple
 

@@ -1,7 +1,7 @@
 """``LoraConfig`` (reference ``src/neuronx_distributed/modules/lora/config.py:5-145``)."""
 from __future__ import annotations
 
-from dataclasses import asdict, dataclass, field
+from dataclasses import asdict, dataclass
 from typing import List, Literal, Optional
 
 

@@ -4,7 +4,6 @@ from __future__ import annotations
 
 import os
 import re
-from dataclasses import asdict
 from typing import Any, Dict, List, Optional
 
 import torch

@@ -18,7 +18,7 @@ by-product reused by the other projections and by wgrad.
 from __future__ import annotations
 
 import math
-from typing import Callable, Optional, Tuple
+from typing import Callable, Optional
 
 import torch
 import torch.distributed as dist

@@ -16,7 +16,7 @@ Dispatch (per call):
 from __future__ import annotations
 
 import os
-from typing import Optional, Tuple
+from typing import Tuple
 
 import torch
 import torch.distributed as dist

@@ -2,7 +2,7 @@
 from __future__ import annotations
 
 import ctypes as _c
-from typing import Optional, Tuple
+from typing import Tuple
 
 import torch
 

@@ -27,8 +27,7 @@ Checkpoint state has the reference's top-level keys (``state``, ``base_state``, 
 """
 from __future__ import annotations
 
-import math
-from typing import Any, Dict, Iterable, List, Optional
+from typing import Any, Dict, List, Optional
 
 import torch
 import torch.distributed as dist

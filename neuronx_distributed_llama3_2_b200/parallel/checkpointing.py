@@ -10,14 +10,14 @@ from __future__ import annotations
 
 import gc
 import os
-from typing import Any, Callable, Dict, Optional
+from typing import Any, Dict, Optional
 
 import torch
 
 from ..utils import xser
 from ..utils.logger import get_logger
 from . import parallel_state as ps
-from .utils import add_barrier, cast_all, get_local_world_size, move_all_tensor_to_cpu
+from .utils import add_barrier, cast_all, move_all_tensor_to_cpu
 
 logger = get_logger()
 NXD_SKIP_RENDEZVOUS = "NXD_SKIP_RENDEZVOUS"

@@ -12,14 +12,13 @@ device (``torch.where``-free, no host sync), as the reference's branch-free form
 from __future__ import annotations
 
 import os
-from typing import Iterable, List, Optional, Union
+from typing import Iterable, List, Union
 
 import torch
 import torch.distributed as dist
 
 from ..ops import optim as optim_ops
 from . import parallel_state as ps
-from .utils import param_is_not_tensor_parallel_duplicate
 
 
 def param_is_not_shared(param: torch.Tensor) -> bool:

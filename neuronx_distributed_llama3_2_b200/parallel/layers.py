@@ -19,7 +19,7 @@ from __future__ import annotations
 
 import math
 import os
-from typing import Any, Callable, Optional, Tuple
+from typing import Callable, Optional, Tuple
 
 import torch
 import torch.nn.functional as F
@@ -30,7 +30,6 @@ from ..ops import comm_linear
 from ..ops import linear as gemm_ops
 from . import mappings
 from .parallel_state import (
-    get_tensor_model_parallel_group,
     get_tensor_model_parallel_rank,
     get_tensor_model_parallel_size,
 )

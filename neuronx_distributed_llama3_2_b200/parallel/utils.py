@@ -9,7 +9,7 @@ verbatim; everything XLA-specific (``mark_step`` syncs, fp64 tricks) is gone.
 from __future__ import annotations
 
 import os
-from typing import Any, Dict, List, Sequence
+from typing import Any, Sequence
 
 import torch
 

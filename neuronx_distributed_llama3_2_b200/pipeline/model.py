@@ -15,7 +15,7 @@ What is different on B200 / eager CUDA:
 from __future__ import annotations
 
 from collections import OrderedDict
-from typing import Any, Dict, Iterable, Iterator, List, Optional, Tuple
+from typing import Any, Dict, Iterator, List, Optional, Tuple
 
 import torch
 import torch.distributed as dist

@@ -7,7 +7,6 @@ from __future__ import annotations
 from dataclasses import dataclass, field
 from typing import Dict, List, Optional, Sequence, Tuple
 
-import torch
 import torch.fx as fx
 from torch.fx.passes.split_module import split_module
 

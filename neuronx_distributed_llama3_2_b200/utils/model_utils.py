@@ -4,12 +4,11 @@ shared-parameter analysis."""
 from __future__ import annotations
 
 import contextlib
-from typing import Any, Callable, Dict, List, Optional, Set, Tuple
+from typing import Any, Callable, Dict, List, Optional, Tuple
 
 import torch
 import torch.nn as nn
 
-from ..parallel.utils import copy_tensor_model_parallel_attributes
 from .logger import get_logger
 
 logger = get_logger()

@@ -18,7 +18,7 @@ from __future__ import annotations
 import os
 import sys
 import types
-from typing import Any, Callable, Dict, List, Tuple
+from typing import Any, Callable, List, Tuple
 
 import torch
 

@@ -16,7 +16,6 @@ def main():
     rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
     torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", rank)))
     dist.init_process_group("nccl", device_id=torch.device("cuda", torch.cuda.current_device()))
-    from neuronx_distributed_llama3_2_b200.ops import comm_linear
     from neuronx_distributed_llama3_2_b200.ops.fused_comm import fused_ag_gemm
     from neuronx_distributed_llama3_2_b200.ops.gemm import gemm
     from neuronx_distributed_llama3_2_b200.parallel import parallel_state as ps
