@@ -24,6 +24,7 @@ import torch
 import torch.nn as nn
 
 from ..models.llama import LlamaConfig, LlamaForCausalLM
+from ..models.mixtral import MixtralConfig, MixtralForCausalLM
 from ..ops import activation as act_ops
 from ..ops import attention as attn_ops
 from ..ops import comm_linear
@@ -36,21 +37,35 @@ from .kv_cache import KVCache
 from .sampling import Sampler
 
 
-class LlamaInferenceModel(LlamaForCausalLM):
-    def __init__(self, config: LlamaConfig, inference_config: Optional[InferenceConfig] = None, device=None):
-        config.sequence_parallel_enabled = False
-        config.activation_checkpointing = False
-        super().__init__(config, device=device)
+class KVCacheInferenceMixin:
+    """Context-encoding / token-generation forward over a KV cache, shared by the model families.  The host class is a
+    training model (same parameter names, so trainer checkpoints load unchanged); it tells the mixin where its pieces
+    are through ``_decoder_layers / _embedding / _final_norm`` and how a layer's feed-forward runs (``_mlp``)."""
+
+    def _init_inference(self, inference_config: Optional[InferenceConfig]) -> None:
         self.inference_config = inference_config or InferenceConfig()
         self.kv_cache: Optional[KVCache] = None
         self.sampler = Sampler(self.inference_config)
         self._rope_tables = None
         self.eval()
 
+    # -- where the host model keeps its modules (Llama layout by default) ------------------------------------------
+    def _decoder_layers(self):
+        return self.model.layers
+
+    def _embedding(self):
+        return self.model.embed_tokens
+
+    def _final_norm(self):
+        return self.model.norm
+
+    def _mlp(self, layer, h: torch.Tensor) -> torch.Tensor:
+        return layer.mlp.down_proj(act_ops.swiglu(layer.mlp.gate_up_proj(h)))
+
     # -- state -------------------------------------------------------------------------------------------------
     def init_kv_cache(self, device=None, dtype=None) -> KVCache:
         ic, cfg = self.inference_config, self.config
-        attn0 = self.model.layers[0].self_attn
+        attn0 = self._decoder_layers()[0].self_attn
         device = device or next(self.parameters()).device
         self.kv_cache = KVCache(cfg.num_hidden_layers, ic.max_batch_size, attn0.kv_heads_local, ic.seq_len, cfg.head_dim,
                                 dtype=dtype or cfg.torch_dtype, device=device, paged=ic.paged_kv, page_size=ic.page_size)
@@ -109,8 +124,7 @@ class LlamaInferenceModel(LlamaForCausalLM):
             h, residual = norm_ops.fused_add_rms_norm(hidden, residual, layer.input_layernorm.weight, eps)
         a = self._attention(i, layer.self_attn, h, positions, seq_ids, lengths, prefill)
         h, residual = norm_ops.fused_add_rms_norm(a, residual, layer.post_attention_layernorm.weight, eps)
-        m = layer.mlp.down_proj(act_ops.swiglu(layer.mlp.gate_up_proj(h)))
-        return m, residual
+        return self._mlp(layer, h), residual
 
     # -- graphs ----------------------------------------------------------------------------------------------------
     @torch.no_grad()
@@ -132,7 +146,7 @@ class LlamaInferenceModel(LlamaForCausalLM):
         identity = default_lines or not self.inference_config.is_continuous_batching
         sid = None if (identity and not prefill) else (
             seq_ids if seq_ids is not None else torch.arange(B, device=input_ids.device, dtype=torch.int32))
-        for i, layer in enumerate(self.model.layers):
+        for i, layer in enumerate(self._decoder_layers()):
             hidden, residual = self._layer(i, layer, hidden, residual, position_ids, sid, lengths, prefill)
         if prefill:
             idx = last_token_index if last_token_index is not None else torch.full((B,), T - 1, device=hidden.device)
@@ -140,8 +154,9 @@ class LlamaInferenceModel(LlamaForCausalLM):
             hidden, residual = hidden[rows, idx.long()], residual[rows, idx.long()]
         else:
             hidden, residual = hidden[:, 0], residual[:, 0]
-        hidden, _ = norm_ops.fused_add_rms_norm(hidden.contiguous(), residual.contiguous(), self.model.norm.weight,
-                                                self.model.norm.variance_epsilon)
+        norm = self._final_norm()
+        hidden, _ = norm_ops.fused_add_rms_norm(hidden.contiguous(), residual.contiguous(), norm.weight,
+                                                norm.variance_epsilon)
         logits = self.lm_head(hidden)                                   # [B, V/tp]
         logits = mappings.gather_from_tensor_model_parallel_region(logits)[:, : self.config.vocab_size]
         tokens = self.sampler.sample(logits.float() if logits.dtype not in (torch.float32, torch.bfloat16) else logits,
@@ -154,7 +169,7 @@ class LlamaInferenceModel(LlamaForCausalLM):
         return self.forward_infer(input_ids, position_ids, seq_ids, last_token_index)
 
     def _embed(self, input_ids: torch.Tensor) -> torch.Tensor:
-        emb = self.model.embed_tokens
+        emb = self._embedding()
         tp = ps.get_tensor_model_parallel_size()
         w = emb.weight
         if tp > 1:
@@ -196,3 +211,38 @@ class LlamaInferenceModel(LlamaForCausalLM):
             res[b, :L] = input_ids[b, :L]
             res[b, L:L + gen.shape[1]] = gen[b]
         return res
+
+
+class LlamaInferenceModel(KVCacheInferenceMixin, LlamaForCausalLM):
+    def __init__(self, config: LlamaConfig, inference_config: Optional[InferenceConfig] = None, device=None):
+        config.sequence_parallel_enabled = False
+        config.activation_checkpointing = False
+        LlamaForCausalLM.__init__(self, config, device=device)
+        self._init_inference(inference_config)
+
+
+class MixtralInferenceModel(KVCacheInferenceMixin, MixtralForCausalLM):
+    """Mixtral-style MoE decoder with a KV cache (reference ``examples/inference/mixtral`` + ``modules/moe`` inference
+    paths): context encoding runs the capacity-free all-experts path, token generation loads only the selected experts
+    (``ExpertMLPs.forward_selective_loading``)."""
+
+    def __init__(self, config: MixtralConfig, inference_config: Optional[InferenceConfig] = None, device=None):
+        config.sequence_parallel_enabled = False
+        config.activation_checkpointing = False
+        MixtralForCausalLM.__init__(self, config, device=device)
+        self._init_inference(inference_config)
+
+    def _decoder_layers(self):
+        return self.layers
+
+    def _embedding(self):
+        return self.embed_tokens
+
+    def _final_norm(self):
+        return self.norm
+
+    def _mlp(self, layer, h: torch.Tensor) -> torch.Tensor:
+        if not layer.is_moe:
+            return layer.mlp.down_proj(act_ops.swiglu(layer.mlp.gate_up_proj(h)))
+        out = layer.mlp(h.transpose(0, 1))[0]          # the MoE block is sequence-first: [T, B, H]
+        return out.transpose(0, 1)

@@ -154,3 +154,119 @@ def test_runner_generate_buckets_and_benchmark_report():
     rep = runner.benchmark_sampling(prompt_len=16, new_tokens=4, n_runs=2)
     assert rep["ttft_ms_p50"] > 0 and rep["decode_tokens_per_s"] > 0
     assert set(rep["e2e_model"]) >= {"latency_ms_p50", "latency_ms_p99", "throughput"}
+
+
+def _attention(x, q, k, v, o, hq, hkv, d):
+    """Plain GQA attention (no mask) from projection weights: the oracle for the head-rewrite check."""
+    B, T, _ = x.shape
+    Q = (x @ q.t()).reshape(B, T, hq, d).transpose(1, 2)
+    K = (x @ k.t()).reshape(B, T, hkv, d).transpose(1, 2)
+    V = (x @ v.t()).reshape(B, T, hkv, d).transpose(1, 2)
+    rep = hq // hkv
+    K, V = K.repeat_interleave(rep, 1), V.repeat_interleave(rep, 1)
+    att = torch.softmax(Q @ K.transpose(-1, -2) / d ** 0.5, -1) @ V
+    return att.transpose(1, 2).reshape(B, T, hq * d) @ o.t()
+
+
+def test_gqa_sharding_strategies_preserve_attention():
+    from neuronx_distributed_llama3_2_b200.inference.gqa import (GQA, determine_sharding_strategy,
+                                                                  get_shardable_head_counts, transform_attention_weights)
+
+    assert determine_sharding_strategy(32, 8) is GQA.REPLICATE_TO_TP_DEGREE
+    assert determine_sharding_strategy(12, 8) is GQA.CONVERT_TO_MHA
+    assert get_shardable_head_counts(32, 56, 8, GQA.REPLICATE_TO_TP_DEGREE) == (64, 32)
+    assert get_shardable_head_counts(32, 56, 8, GQA.CONVERT_TO_MHA) == (64, 64)
+    assert get_shardable_head_counts(8, 32, 8, GQA.REPLICATE_TO_TP_DEGREE) == (32, 8)
+    torch.manual_seed(0)
+    hidden, d = 48, 8
+    x = torch.randn(2, 5, hidden, dtype=torch.float64)
+    for hq, hkv, tp, want in ((6, 2, 4, GQA.REPLICATE_TO_TP_DEGREE), (6, 2, 3, GQA.CONVERT_TO_MHA),
+                              (6, 6, 4, GQA.REPLICATE_TO_TP_DEGREE), (8, 2, 2, GQA.REPLICATE_TO_TP_DEGREE)):
+        q = torch.randn(hq * d, hidden, dtype=torch.float64)
+        k = torch.randn(hkv * d, hidden, dtype=torch.float64)
+        v = torch.randn(hkv * d, hidden, dtype=torch.float64)
+        o = torch.randn(hidden, hq * d, dtype=torch.float64)
+        ref = _attention(x, q, k, v, o, hq, hkv, d)
+        r = transform_attention_weights(q, k, v, o, tp, hq, hkv)
+        nq, nkv = r["num_attention_heads"], r["num_key_value_heads"]
+        assert nq % tp == 0 and (nkv % tp == 0) and nq % nkv == 0, (hq, hkv, tp, nq, nkv)
+        if hq != hkv and tp % hkv == 0 and hkv < tp:
+            assert r["strategy"] is want and nkv == tp
+        got = _attention(x, r["q"], r["k"], r["v"], r["o"], nq, nkv, d)
+        torch.testing.assert_close(got, ref, atol=1e-9, rtol=1e-9)
+
+
+def test_autobucketing_generate_and_fit():
+    from neuronx_distributed_llama3_2_b200.inference.autobucketing import (context_encoder_bk, generate_buckets,
+                                                                            select_bucket, token_generation_bk)
+
+    assert generate_buckets(128, 2048) == [128, 256, 512, 1024, 2048]
+    assert generate_buckets(128, 1100) == [128, 256, 512, 1100]
+    assert generate_buckets(128, 1500) == [128, 256, 512, 1024, 1500]
+    assert generate_buckets(64, 64) == [64]
+    buckets = [16, 32, 64]
+    assert select_bucket(buckets, 16) == 0 and select_bucket(buckets, 17) == 1
+    ids = torch.arange(1, 21).reshape(1, 20).repeat(2, 1)
+    mask = torch.ones(2, 20, dtype=torch.long)
+    mask[1, 12:] = 0
+    pos = torch.arange(20).unsqueeze(0).repeat(2, 1)
+    (i2, m2, p2), idx = context_encoder_bk([ids, mask, pos], buckets, "right", pad_token=0)
+    assert idx == 1 and i2.shape == (2, 32) and torch.equal(i2[:, :20], ids) and int(i2[:, 20:].abs().sum()) == 0
+    assert int(m2[:, 20:].sum()) == 0 and torch.equal(p2[0], torch.arange(32))
+    (i3, _, _), idx = context_encoder_bk([ids[:, :20], torch.cat([mask[:, :10], mask[:, :10] * 0], 1), pos], buckets)
+    assert idx == 0 and i3.shape == (2, 16)                       # longest real prompt is 10 tokens: sliced to bucket 16
+    cache_mask = torch.ones(2, 64, dtype=torch.long)
+    (_, m4, _), idx = token_generation_bk([ids[:, :1], cache_mask, torch.tensor([[20], [12]])], buckets)
+    assert idx == 1 and m4.shape == (2, 32)
+
+
+def test_hf_checkpoint_directory_formats(tmp_path):
+    from neuronx_distributed_llama3_2_b200.inference.checkpoint import load_state_dict, save_state_dict_safetensors
+
+    torch.manual_seed(0)
+    sd = {f"layer.{i}.w": torch.randn(64, 32) for i in range(6)}
+    sd["tied"] = sd["layer.0.w"]
+    one = tmp_path / "one"
+    save_state_dict_safetensors(sd, str(one))
+    assert sorted(os.listdir(one)) == ["model.safetensors"]
+    back = load_state_dict(str(one))
+    assert "tied" not in back and all(torch.equal(back[k], sd[k]) for k in back) and len(back) == 6
+    many = tmp_path / "many"
+    save_state_dict_safetensors(sd, str(many), max_shard_size="20KB")          # 8 KB per tensor -> 2 per shard
+    names = sorted(os.listdir(many))
+    assert "model.safetensors.index.json" in names and sum(n.endswith(".safetensors") for n in names) == 3
+    back = load_state_dict(str(many))
+    assert len(back) == 6 and all(torch.equal(back[k], sd[k]) for k in back)
+    binv = tmp_path / "bin"
+    os.makedirs(binv)
+    torch.save({k: v for k, v in sd.items() if k != "tied"}, binv / "pytorch_model.bin")
+    assert torch.equal(load_state_dict(str(binv))["layer.3.w"], sd["layer.3.w"])
+    try:
+        load_state_dict(str(tmp_path))
+        raise AssertionError("empty directory must fail")
+    except FileNotFoundError:
+        pass
+
+
+def test_mixtral_kv_cache_generation_matches_full_recompute():
+    from neuronx_distributed_llama3_2_b200.inference import MixtralInferenceModel
+    from neuronx_distributed_llama3_2_b200.models import MixtralForCausalLM, tiny_mixtral
+
+    torch.manual_seed(0)
+    cfg = tiny_mixtral(sequence_parallel_enabled=False)
+    train = MixtralForCausalLM(cfg).eval()
+    inf = MixtralInferenceModel(tiny_mixtral(sequence_parallel_enabled=False),
+                                InferenceConfig(batch_size=2, max_context_length=32, seq_len=64))
+    inf.load_state_dict(train.state_dict())
+    prompts = torch.randint(1, cfg.vocab_size, (2, 10))
+    mask = torch.ones_like(prompts)
+    mask[1, 7:] = 0
+    out = inf.generate(prompts, mask, max_new_tokens=5)
+    for b in range(2):
+        L = int(mask[b].sum())
+        seq = prompts[b, :L].clone()
+        for _ in range(5):
+            with torch.no_grad():
+                nxt = train(seq.unsqueeze(0)).transpose(0, 1)[0, -1].argmax()
+            seq = torch.cat([seq, nxt.reshape(1)])
+        assert torch.equal(out[b, :L + 5], seq), (b, out[b, :L + 5], seq)
