@@ -270,3 +270,37 @@ def test_mixtral_kv_cache_generation_matches_full_recompute():
                 nxt = train(seq.unsqueeze(0)).transpose(0, 1)[0, -1].argmax()
             seq = torch.cat([seq, nxt.reshape(1)])
         assert torch.equal(out[b, :L + 5], seq), (b, out[b, :L + 5], seq)
+
+
+def test_model_wrapper_pads_splits_and_reorders():
+    from neuronx_distributed_llama3_2_b200.inference.model_wrapper import ModelWrapper
+
+    cfg, train, _ = _models()
+    ic = InferenceConfig(batch_size=2, max_batch_size=5, max_context_length=32, seq_len=64, is_continuous_batching=True)
+    inf = LlamaInferenceModel(tiny_llama(sequence_parallel_enabled=False), ic)
+    inf.load_state_dict(train.state_dict())
+    inf.init_kv_cache()
+    calls = []
+
+    def fn(ids, pos, seq, last):
+        calls.append((tuple(ids.shape), seq.tolist()))
+        return inf.forward_infer(ids, pos, seq, last)
+
+    cte = ModelWrapper(fn, batch_size=2, buckets=[16, 32], is_continuous_batching=True)
+    tkg = ModelWrapper(fn, batch_size=2, buckets=[1], tag="token_generation_model", is_continuous_batching=True)
+    prompts = torch.randint(1, cfg.vocab_size, (3, 11))              # 3 requests on a batch-2 graph, 11 tokens -> bucket 16
+    pos = torch.arange(11).unsqueeze(0).expand(3, 11)
+    lines = torch.tensor([4, 0, 2], dtype=torch.int32)               # cache lines out of order
+    tok = cte(prompts, pos, lines)
+    assert [c[0] for c in calls] == [(2, 16), (2, 16)]               # split 2 + 1 (the single row padded by repetition)
+    assert calls[0][1] == [0, 2] and calls[1][1] == [4, 4]            # sorted by cache line
+    ref = _full_logits(train, prompts)[:, -1].argmax(-1)
+    assert torch.equal(tok, ref)                                      # caller's row order restored
+    tok2 = tkg(tok.reshape(3, 1), torch.full((3, 1), 11), lines)
+    ref2 = _full_logits(train, torch.cat([prompts, tok.reshape(3, 1)], 1))[:, -1].argmax(-1)
+    assert torch.equal(tok2, ref2)
+    try:
+        cte(torch.zeros(1, 40, dtype=torch.long), torch.arange(40).unsqueeze(0))
+        raise AssertionError("longer than the largest bucket must fail")
+    except ValueError:
+        pass
