@@ -23,7 +23,10 @@
 // finite garbage that nobody reads -- cheaper than a second code path for the M = 64 TMEM layout.
 //
 // warp 0: TMA producer (K, V once; Q_i, dO_i, L_i, Delta_i through a 2-stage ring)   warp 1: TMEM alloc + MMA issue
-// warps 2-5: softmax-backward math, dQ drain, epilogue.
+// warps 2-9: softmax-backward math, dQ drain, epilogue.  Two math warps share every TMEM lane quadrant (warp % 4) and
+// split the 64 query columns of a tile between them: half the serial work per warp and twice the warps to hide the
+// TMEM-load / exp2 / shared-store latencies behind (the 4-warp version ran one warp per SM sub-partition and was
+// latency bound); in the epilogue one half stores dV while the other stores dK.
 #include "attn_tc_common.cuh"
 #include "gemm_tcgen05.cuh"
 #include "ptx.cuh"
@@ -33,7 +36,8 @@ using namespace nxd_attn;
 
 constexpr int kBN = 128;  // K/V rows per CTA
 constexpr int kBM = 64;   // query rows per tile
-constexpr int kThreadsBwd = 192;
+constexpr int kThreadsBwd = 320;      // TMA warp + MMA warp + 8 math warps
+constexpr int kMathThreads = 256;
 
 struct BwdParams {
     const float* lse_pad;    // [B*Hq, Sq_pad] log2-domain LSE, +inf in the padding
@@ -122,11 +126,11 @@ fa_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
             ptx::mbar_init(&qdo_empty[i], 1);
         }
         ptx::mbar_init(st_full, 1);
-        ptx::mbar_init(st_empty, 128);
-        ptx::mbar_init(pds_full, 128);
+        ptx::mbar_init(st_empty, kMathThreads);
+        ptx::mbar_init(pds_full, kMathThreads);
         ptx::mbar_init(pds_empty, 1);
         ptx::mbar_init(dq_full, 1);
-        ptx::mbar_init(dq_empty, 128);
+        ptx::mbar_init(dq_empty, kMathThreads);
         ptx::fence_barrier_init();
     }
     if (warp == 1) ptx::tmem_alloc<1>(tmem_ptr_smem, 512);
@@ -240,7 +244,9 @@ fa_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
         const int row = q4 * 32 + lane;         // K/V row inside the tile == TMEM lane (and d index for dQ^T)
         const int krow = n0 + row;
         const uint32_t lane_off = (uint32_t)(q4 * 32) << 16;
-        const int tid128 = threadIdx.x - 64;
+        const int tidm = threadIdx.x - 64;       // 0 .. 255 inside the math group
+        const int half = (warp - 2) >> 2;        // which 32 of the 64 query columns this warp handles
+        const int c0h = half * 32;
 
         auto drain_dq = [&](int it) {
             // dQ^T(it) [d = row][64 q] -> sDQ [d group of 32][q][32 floats] (128-byte swizzled rows) -> TMA reduce-add
@@ -249,28 +255,28 @@ fa_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
             ptx::mbar_wait(dq_full, (uint32_t)it & 1u);
             ptx::tcgen05_fence_after();
             const bool has_rows = q4 * 32 < kD;          // head dim 64: TMEM lanes 64..127 of dQ^T are padding
-            uint32_t v[64];
+            uint32_t v[32];
             if (has_rows) {
-                ptx::tmem_ld_32x32b_x32(tmem_base + kColDQT + lane_off, v);
-                ptx::tmem_ld_32x32b_x32(tmem_base + kColDQT + lane_off + 32, v + 32);
+                ptx::tmem_ld_32x32b_x32(tmem_base + kColDQT + lane_off + c0h, v);
                 ptx::tmem_ld_wait();
             }
             ptx::tcgen05_fence_before();
             ptx::mbar_arrive(dq_empty);
-            if (tid128 == 0) ptx::bulk_wait_read<0>();   // the previous reduce-add has finished reading sDQ
-            named_bar_sync(1, 128);
+            if (tidm == 0) ptx::bulk_wait_read<0>();     // the previous reduce-add has finished reading sDQ
+            named_bar_sync(1, kMathThreads);
             if (has_rows) {
-                uint8_t* base = sDQ + q4 * (kBM * 128);      // d group of 32 == this warp
+                uint8_t* base = sDQ + q4 * (kBM * 128);      // d group of 32 == this TMEM lane quadrant
 #pragma unroll
-                for (int qq = 0; qq < kBM; ++qq) {
+                for (int j = 0; j < 32; ++j) {
+                    const int qq = c0h + j;
                     float* dst =
                         reinterpret_cast<float*>(base + qq * 128 + (((lane >> 2) ^ (qq & 7)) << 4) + (lane & 3) * 4);
-                    *dst = __uint_as_float(v[qq]) * p.scale;
+                    *dst = __uint_as_float(v[j]) * p.scale;
                 }
             }
             ptx::fence_proxy_async();
-            named_bar_sync(1, 128);
-            if (tid128 == 0) {
+            named_bar_sync(1, kMathThreads);
+            if (tidm == 0) {
                 int c[4];
 #pragma unroll
                 for (int g = 0; g < kD / 32; ++g) {
@@ -287,11 +293,9 @@ fa_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
             const int m0 = (mb_start + (it0 + it) % tiles_per_head) * kBM;
             ptx::mbar_wait(st_full, (uint32_t)it & 1u);
             ptx::tcgen05_fence_after();
-            uint32_t s[kBM], dp[kBM];
-            ptx::tmem_ld_32x32b_x32(tmem_base + kColST + lane_off, s);
-            ptx::tmem_ld_32x32b_x32(tmem_base + kColST + lane_off + 32, s + 32);
-            ptx::tmem_ld_32x32b_x32(tmem_base + kColDPT + lane_off, dp);
-            ptx::tmem_ld_32x32b_x32(tmem_base + kColDPT + lane_off + 32, dp + 32);
+            uint32_t s[32], dp[32];
+            ptx::tmem_ld_32x32b_x32(tmem_base + kColST + lane_off + c0h, s);
+            ptx::tmem_ld_32x32b_x32(tmem_base + kColDPT + lane_off + c0h, dp);
             ptx::tmem_ld_wait();
             ptx::tcgen05_fence_before();
             ptx::mbar_arrive(st_empty);
@@ -301,18 +305,19 @@ fa_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
             const float* Ls = sLD + st * 2 * kBM;
             const float* Ds = Ls + kBM;
             const bool need_mask = (n0 + kBN > p.Sk) || (CAUSAL && (n0 + q4 * 32 + 31 > m0 + offset));
-            uint32_t pk[kBM / 2], dk_[kBM / 2];
+            uint32_t pk[16], dk_[16];
 #pragma unroll
-            for (int c = 0; c < kBM; c += 2) {
-                float p0 = exp2f(__uint_as_float(s[c]) * p.scale_log2 - Ls[c]);
-                float p1 = exp2f(__uint_as_float(s[c + 1]) * p.scale_log2 - Ls[c + 1]);
+            for (int c = 0; c < 32; c += 2) {
+                const int cg = c0h + c;                  // query column inside the 64-row tile
+                float p0 = exp2f(__uint_as_float(s[c]) * p.scale_log2 - Ls[cg]);
+                float p1 = exp2f(__uint_as_float(s[c + 1]) * p.scale_log2 - Ls[cg + 1]);
                 if (need_mask) {
-                    const int mq = m0 + c;
+                    const int mq = m0 + cg;
                     if (krow >= p.Sk || (CAUSAL && krow > mq + offset)) p0 = 0.f;
                     if (krow >= p.Sk || (CAUSAL && krow > mq + 1 + offset)) p1 = 0.f;
                 }
-                const float d0 = p0 * (__uint_as_float(dp[c]) - Ds[c]);
-                const float d1 = p1 * (__uint_as_float(dp[c + 1]) - Ds[c + 1]);
+                const float d0 = p0 * (__uint_as_float(dp[c]) - Ds[cg]);
+                const float d1 = p1 * (__uint_as_float(dp[c + 1]) - Ds[cg + 1]);
                 bf162 tp = __floats2bfloat162_rn(p0, p1);
                 bf162 td = __floats2bfloat162_rn(d0, d1);
                 pk[c >> 1] = *reinterpret_cast<uint32_t*>(&tp);
@@ -322,8 +327,8 @@ fa_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
             uint8_t* prow = sPt + row * 128;
             uint8_t* drow = sDSt + row * 128;
 #pragma unroll
-            for (int c = 0; c < 8; ++c) {
-                const int sw = (c ^ (row & 7)) << 4;
+            for (int c = 0; c < 4; ++c) {                // this warp's 4 of the row's 8 sixteen-byte chunks
+                const int sw = ((half * 4 + c) ^ (row & 7)) << 4;
                 *reinterpret_cast<uint4*>(prow + sw) = make_uint4(pk[4 * c], pk[4 * c + 1], pk[4 * c + 2], pk[4 * c + 3]);
                 *reinterpret_cast<uint4*>(drow + sw) = make_uint4(dk_[4 * c], dk_[4 * c + 1], dk_[4 * c + 2], dk_[4 * c + 3]);
             }
@@ -337,15 +342,16 @@ fa_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
             // the commit behind dq_full(total-1) covered every earlier MMA: dK / dV are final
         }
         if (total == 0) ptx::mbar_wait(kv_full, 0);  // nothing consumed K/V: let their TMA land before the tiles are reused
-        if (tid128 == 0) ptx::bulk_wait_read<0>();
-        named_bar_sync(1, 128);
+        if (tidm == 0) ptx::bulk_wait_read<0>();
+        named_bar_sync(1, kMathThreads);
         if (p.nsplit > 1) {
             // ---- split epilogue: this CTA holds PARTIAL dV / dK -> fp32 -> smem -> TMA reduce-add into the accumulators
-            // (32 rows x 32 columns per warp and step, two 4 KB staging buffers per warp in the dead K / V tiles)
-            uint8_t* stg = sK + q4 * 8192;
+            // (32 rows x 32 columns per warp and step, two 4 KB staging buffers per warp in the dead K / V / Q / dO
+            // tiles: 64 KB contiguous from sK for either head dim); warps 2-5 add dV, warps 6-9 add dK
+            uint8_t* stg = sK + (half * 4 + q4) * 8192;
             int buf = 0;
-#pragma unroll 1
-            for (int which = 0; which < 2; ++which) {
+            {
+                const int which = half;
                 const uint32_t col = which == 0 ? kColDV : kColDK;
                 const float mul = which == 0 ? 1.f : p.scale;
 #pragma unroll 1
@@ -377,9 +383,9 @@ fa_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
                 }
             }
         } else {
-            // ---- epilogue: dV, dK (x scale) -> bf16 -> smem (the dead K / V tiles) -> TMA store ----
-    #pragma unroll 1
-            for (int which = 0; which < 2; ++which) {
+            // ---- epilogue: dV (warps 2-5), dK x scale (warps 6-9) -> bf16 -> smem (the dead V / K tiles) -> TMA store ----
+            {
+                const int which = half;
                 uint8_t* stage = which == 0 ? sV : sK;
                 const uint32_t col = which == 0 ? kColDV : kColDK;
                 const float mul = which == 0 ? 1.f : p.scale;
