@@ -37,6 +37,39 @@ __device__ __forceinline__ const bf16* row_ptr(const bf16* base, const CacheView
     return base + (size_t)b * c.stride_b + (size_t)h * c.stride_h + (size_t)pos * D;
 }
 
+// Block-wide max / sum of kMaxGroup values at once: one shared-memory exchange (two barriers) for the whole group
+// instead of one per query head.  red: kMaxGroup * 8 floats (8 warps).
+template <bool kMax>
+__device__ __forceinline__ void block_reduce_group(float (&v)[kMaxGroup], int group, float (*red)[kChunk / 32]) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+    for (int g = 0; g < kMaxGroup; ++g) {
+        if (g < group) {
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                const float t = __shfl_xor_sync(0xffffffffu, v[g], o);
+                v[g] = kMax ? fmaxf(v[g], t) : v[g] + t;
+            }
+        }
+    }
+    __syncthreads();   // protect `red` from its previous use
+    if (lane == 0) {
+#pragma unroll
+        for (int g = 0; g < kMaxGroup; ++g)
+            if (g < group) red[g][warp] = v[g];
+    }
+    __syncthreads();
+#pragma unroll
+    for (int g = 0; g < kMaxGroup; ++g) {
+        if (g < group) {
+            float r = red[g][0];
+#pragma unroll
+            for (int w = 1; w < kChunk / 32; ++w) r = kMax ? fmaxf(r, red[g][w]) : r + red[g][w];
+            v[g] = r;
+        }
+    }
+}
+
 template <int D>
 __global__ void __launch_bounds__(kChunk) decode_attn_split_kernel(
     const bf16* __restrict__ q,  // [B, n_q, D]
@@ -53,10 +86,12 @@ __global__ void __launch_bounds__(kChunk) decode_attn_split_kernel(
     const int end = min(len, start + per);
     const int tid = threadIdx.x;
 
+    constexpr int kLanesPerRow = D / 2;                  // PV phase: a thread owns two channels (one bf162 load per key)
+    constexpr int kParts = kChunk / kLanesPerRow;        // key partitions: 8 for D = 64, 4 for D = 128
     __shared__ float sq[kMaxGroup][D];
     __shared__ float sp[kMaxGroup][kChunk];
-    __shared__ float red[32];
-    __shared__ float so[kChunk / D > 0 ? kChunk / D : 1][kMaxGroup][D];
+    __shared__ float red[kMaxGroup][kChunk / 32];
+    __shared__ float2 so[kParts][kMaxGroup][kLanesPerRow];
 
     for (int i = tid; i < group * D; i += kChunk) {
         const int g = i / D, d = i % D;
@@ -64,12 +99,12 @@ __global__ void __launch_bounds__(kChunk) decode_attn_split_kernel(
     }
     __syncthreads();
 
-    float m_run[kMaxGroup], l_run[kMaxGroup], o_acc[kMaxGroup];
+    float m_run[kMaxGroup], l_run[kMaxGroup];
+    float2 o_acc[kMaxGroup];
 #pragma unroll
-    for (int g = 0; g < kMaxGroup; ++g) { m_run[g] = -INFINITY; l_run[g] = 0.f; o_acc[g] = 0.f; }
-    constexpr int kParts = kChunk / D;  // key partitions for the PV phase (2 for D=128, 4 for D=64)
-    const int d = tid % D;
-    const int part = tid / D;
+    for (int g = 0; g < kMaxGroup; ++g) { m_run[g] = -INFINITY; l_run[g] = 0.f; o_acc[g] = make_float2(0.f, 0.f); }
+    const int d2 = tid % kLanesPerRow;
+    const int part = tid / kLanesPerRow;
 
     for (int c0 = start; c0 < end; c0 += kChunk) {
         const int pos = c0 + tid;
@@ -93,42 +128,66 @@ __global__ void __launch_bounds__(kChunk) decode_attn_split_kernel(
                 }
             }
         }
-        // chunk softmax per head (online across chunks)
-        float alpha[kMaxGroup];
-        for (int g = 0; g < group; ++g) {
-            const float sv = valid ? s[g] : -INFINITY;
-            const float cm = block_max(sv, red);
-            const float nm = fmaxf(m_run[g], cm);
-            const float p = valid ? __expf(sv - nm) : 0.f;
-            const float cs = block_sum(p, red);
-            alpha[g] = __expf(m_run[g] - nm);
-            l_run[g] = l_run[g] * alpha[g] + cs;
-            m_run[g] = nm;
-            sp[g][tid] = p;
+        // chunk softmax for all heads of the group (online across chunks)
+        float cm[kMaxGroup], pv[kMaxGroup], alpha[kMaxGroup];
+#pragma unroll
+        for (int g = 0; g < kMaxGroup; ++g) cm[g] = valid ? s[g] : -INFINITY;
+        block_reduce_group<true>(cm, group, red);
+#pragma unroll
+        for (int g = 0; g < kMaxGroup; ++g) {
+            if (g < group) {
+                const float nm = fmaxf(m_run[g], cm[g]);
+                pv[g] = valid ? __expf(s[g] - nm) : 0.f;
+                alpha[g] = __expf(m_run[g] - nm);
+                m_run[g] = nm;
+                sp[g][tid] = pv[g];
+            }
         }
-        __syncthreads();
-        // PV: thread (part, d) accumulates keys j = part, part + kParts, ...
+        block_reduce_group<false>(pv, group, red);        // its barriers also publish sp[][] to the block
+#pragma unroll
+        for (int g = 0; g < kMaxGroup; ++g) {
+            if (g < group) {
+                l_run[g] = l_run[g] * alpha[g] + pv[g];
+                o_acc[g].x *= alpha[g];
+                o_acc[g].y *= alpha[g];
+            }
+        }
+        // PV: thread (part, d2) accumulates keys j = part, part + kParts, ... for channels 2 d2, 2 d2 + 1
         const int nk = min(kChunk, end - c0);
-        for (int g = 0; g < group; ++g) o_acc[g] *= alpha[g];
         for (int j = part; j < nk; j += kParts) {
-            const float vv = __bfloat162float(row_ptr(cache.v, cache, b, hk, c0 + j, D)[d]);
-            for (int g = 0; g < group; ++g) o_acc[g] += sp[g][j] * vv;
+            const float2 vv = __bfloat1622float2(
+                reinterpret_cast<const bf162*>(row_ptr(cache.v, cache, b, hk, c0 + j, D))[d2]);
+#pragma unroll
+            for (int g = 0; g < kMaxGroup; ++g) {
+                if (g < group) {
+                    const float w = sp[g][j];
+                    o_acc[g].x += w * vv.x;
+                    o_acc[g].y += w * vv.y;
+                }
+            }
         }
-        __syncthreads();
+        __syncthreads();     // sp[][] is rewritten by the next chunk
     }
     // merge the kParts partial accumulators
-    for (int g = 0; g < group; ++g) so[part][g][d] = o_acc[g];
-    __syncthreads();
-    for (int i = tid; i < group * D; i += kChunk) {
-        const int g = i / D, dd = i % D;
-        float acc = 0.f;
+    __shared__ float sml[kMaxGroup][2];
 #pragma unroll
-        for (int p = 0; p < kParts; ++p) acc += so[p][g][dd];
+    for (int g = 0; g < kMaxGroup; ++g) {
+        if (g < group) {
+            so[part][g][d2] = o_acc[g];
+            if (tid == 0) { sml[g][0] = m_run[g]; sml[g][1] = l_run[g]; }
+        }
+    }
+    __syncthreads();
+    for (int i = tid; i < group * kLanesPerRow; i += kChunk) {
+        const int g = i / kLanesPerRow, dd = i % kLanesPerRow;
+        float2 acc = make_float2(0.f, 0.f);
+#pragma unroll
+        for (int p = 0; p < kParts; ++p) { acc.x += so[p][g][dd].x; acc.y += so[p][g][dd].y; }
         const size_t base = (((size_t)b * n_q + hk * group + g) * n_splits + split);
-        part_o[base * D + dd] = acc;
+        reinterpret_cast<float2*>(part_o + base * D)[dd] = acc;
         if (dd == 0) {
-            part_ml[base * 2 + 0] = m_run[g];
-            part_ml[base * 2 + 1] = l_run[g];
+            part_ml[base * 2 + 0] = sml[g][0];
+            part_ml[base * 2 + 1] = sml[g][1];
         }
     }
 }
