@@ -191,6 +191,96 @@ __global__ void __launch_bounds__(kArThreads) skinny_gemm_ar_kernel(const bf16* 
     if (ar.tp > 1) ar_end(ar, epoch);
 }
 
+// ---- 9 .. 16 rows: the FMA loop above re-reads every X row from shared memory per weight vector and becomes FMA /
+// LDS bound; here the 16 x K activation tile feeds mma.sync m16n8k16 (M = 16 is exactly one fragment).  A CTA owns
+// `cols` output columns and walks them 8 at a time; its 8 warps split K, every lane fetches 16 contiguous bytes of a
+// weight row per step (8 k values that serve two MMAs -- the contraction order is free, so A is read from shared
+// memory with the same permutation), the warps' partial 16 x 8 tiles are summed through shared memory.
+__device__ __forceinline__ void mma_m16n8k16_bf16(float (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3,
+                                                  uint32_t b0, uint32_t b1) {
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+                 : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+
+// Shared memory: X tile [16][K + 8] bf16 (rows padded by 16 bytes: conflict-free 16-byte reads), warp partials
+// [8][16][8] fp32, result block [16][cols] fp32.
+__global__ void __launch_bounds__(kArThreads) skinny16_gemm_ar_kernel(const bf16* __restrict__ x, const bf16* __restrict__ w,
+                                                                      const bf16* __restrict__ residual, bf16* __restrict__ out,
+                                                                      int B, int N, int K, long long ldx, long long ldw,
+                                                                      long long ldo, int cols, const ArArgs ar) {
+    extern __shared__ __align__(16) uint8_t ar_smem[];
+    const int pitch = K + 8;                                           // elements
+    bf16* xs = reinterpret_cast<bf16*>(ar_smem);
+    float* wpart = reinterpret_cast<float*>(ar_smem + (size_t)16 * pitch * sizeof(bf16));     // [8 warps][16][8]
+    float* part = wpart + kArWarps * 128;                                                      // [16][cols]
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int k8 = K / 8;
+    for (int i = threadIdx.x; i < 16 * k8; i += kArThreads) {
+        const int row = i / k8, c = i % k8;
+        uint4 v = make_uint4(0u, 0u, 0u, 0u);
+        if (row < B) v = *reinterpret_cast<const uint4*>(x + (size_t)row * ldx + (size_t)c * 8);
+        *reinterpret_cast<uint4*>(xs + (size_t)row * pitch + c * 8) = v;
+    }
+    __syncthreads();
+    const int c0 = (int)blockIdx.x * cols;
+    const int ncols = min(cols, N - c0);
+    // K is cut into chunks of 32 (4 lanes x 8 values); warp w takes chunks w, w + 8, ...
+    const int chunks = K / 32;
+    const int r = lane >> 2, kq = (lane & 3) * 8;
+    for (int g = 0; g < cols; g += 8) {
+        float acc[4] = {0.f, 0.f, 0.f, 0.f};
+        const int n = c0 + g + r;                                      // the weight row (output column) of this lane
+        const bool nv = g + r < ncols;
+        const bf16* wrow = w + (size_t)(nv ? n : c0) * ldw;
+#pragma unroll 4
+        for (int ch = warp; ch < chunks; ch += kArWarps) {
+            const int k0 = ch * 32 + kq;
+            uint4 bv = nv ? __ldg(reinterpret_cast<const uint4*>(wrow + k0)) : make_uint4(0u, 0u, 0u, 0u);
+            const uint4 alo = *reinterpret_cast<const uint4*>(xs + (size_t)r * pitch + k0);          // row r
+            const uint4 ahi = *reinterpret_cast<const uint4*>(xs + (size_t)(r + 8) * pitch + k0);    // row r + 8
+            // 8 k values per lane = two MMAs: slots (k, k+1 | k+8, k+9) take values (0,1 | 2,3) then (4,5 | 6,7)
+            mma_m16n8k16_bf16(acc, alo.x, ahi.x, alo.y, ahi.y, bv.x, bv.y);
+            mma_m16n8k16_bf16(acc, alo.z, ahi.z, alo.w, ahi.w, bv.z, bv.w);
+        }
+        if ((K & 31) != 0 && warp == 0) {                              // K % 32 tail (K % 8 == 0): zero-padded chunk
+            const int k0 = chunks * 32 + kq;
+            const bool kv = k0 < K;
+            uint4 z = make_uint4(0u, 0u, 0u, 0u);
+            const uint4 bv = (nv && kv) ? __ldg(reinterpret_cast<const uint4*>(wrow + k0)) : z;
+            const uint4 alo = kv ? *reinterpret_cast<const uint4*>(xs + (size_t)r * pitch + k0) : z;
+            const uint4 ahi = kv ? *reinterpret_cast<const uint4*>(xs + (size_t)(r + 8) * pitch + k0) : z;
+            mma_m16n8k16_bf16(acc, alo.x, ahi.x, alo.y, ahi.y, bv.x, bv.y);
+            mma_m16n8k16_bf16(acc, alo.z, ahi.z, alo.w, ahi.w, bv.z, bv.w);
+        }
+        // C fragment: acc[0..1] = row r, columns 2 (lane % 4) + {0, 1}; acc[2..3] = row r + 8
+        float* wp = wpart + warp * 128;
+        const int cc = (lane & 3) * 2;
+        wp[r * 8 + cc] = acc[0]; wp[r * 8 + cc + 1] = acc[1];
+        wp[(r + 8) * 8 + cc] = acc[2]; wp[(r + 8) * 8 + cc + 1] = acc[3];
+        __syncthreads();
+        if (threadIdx.x < 128) {
+            float sum = 0.f;
+#pragma unroll
+            for (int ww = 0; ww < kArWarps; ++ww) sum += wpart[ww * 128 + threadIdx.x];
+            part[(threadIdx.x >> 3) * cols + g + (threadIdx.x & 7)] = sum;
+        }
+        __syncthreads();
+    }
+    uint32_t epoch = 0;
+    if (ar.tp > 1) {
+        epoch = ar_begin(ar);
+        oneshot_exchange(ar, epoch, part, 16 * cols / 4, (size_t)blockIdx.x * 16 * cols, (int)blockIdx.x);
+    }
+    for (int i = threadIdx.x; i < B * ncols; i += kArThreads) {
+        const int b = i / ncols, c = i % ncols;
+        float v = part[b * cols + c];
+        if (residual) v += __bfloat162float(residual[(size_t)b * ldo + c0 + c]);
+        out[(size_t)b * ldo + c0 + c] = __float2bfloat16(v);
+    }
+    if (ar.tp > 1) ar_end(ar, epoch);
+}
+
 // Stand-alone one-shot all-reduce of n bf16 values (n % 8 == 0); every CTA owns `per_cta` elements (multiple of 8).
 __global__ void __launch_bounds__(kArThreads) allreduce_oneshot_kernel(const bf16* __restrict__ in, bf16* __restrict__ out,
                                                                        long long n, int per_cta, const ArArgs ar) {
@@ -268,6 +358,31 @@ int launch_skinny(const bf16* x, const bf16* w, const bf16* residual, bf16* out,
     return 0;
 }
 
+int launch_skinny16(const bf16* x, const bf16* w, const bf16* residual, bf16* out, int B, int N, int K, long long ldx,
+                    long long ldw, long long ldo, const ArArgs& ar, cudaStream_t st) {
+    int dev = 0, sms = 0;
+    NXD_CHECK_CUDA(cudaGetDevice(&dev));
+    NXD_CHECK_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    int cols = 8, grid = 0;
+    size_t smem = 0;
+    for (;; cols += 8) {
+        smem = (size_t)16 * (K + 8) * sizeof(bf16) + (size_t)kArWarps * 128 * sizeof(float) + (size_t)16 * cols * sizeof(float);
+        NXD_REQUIRE(smem <= 200 * 1024, "skinny_gemm_ar: 16 x K %d does not fit shared memory", K);
+        NXD_CHECK_CUDA(cudaFuncSetAttribute(skinny16_gemm_ar_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        int per_sm = 0;
+        NXD_CHECK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, skinny16_gemm_ar_kernel, kArThreads, smem));
+        NXD_REQUIRE(per_sm >= 1, "skinny_gemm_ar: kernel does not fit an SM");
+        grid = (N + cols - 1) / cols;
+        if (ar.tp == 1 || grid <= min(min(per_sm, 2) * sms, kMaxCtas)) break;
+        NXD_REQUIRE(cols < 8192, "skinny_gemm_ar: cannot make N %d co-resident", N);
+    }
+    NXD_REQUIRE(ar.tp == 1 || (size_t)grid * 16 * cols <= ar.slot_elems,
+                "skinny_gemm_ar: staging slot too small (%zu floats, need %zu)", ar.slot_elems, (size_t)grid * 16 * cols);
+    skinny16_gemm_ar_kernel<<<grid, kArThreads, smem, st>>>(x, w, residual, out, B, N, K, ldx, ldw, ldo, cols, ar);
+    NXD_LAUNCH_CHECK();
+    return 0;
+}
+
 }  // namespace
 
 // uint32 flags a staging region needs (one per CTA and source rank).
@@ -294,7 +409,7 @@ NXD_API int nxd_skinny_gemm_ar_bf16(const void* x, const void* w, const void* re
     if (B <= 2) return launch_skinny<2>(xb, wb, rb, (bf16*)out, B, N, K, ldx, ldw, ldo, ar, st);
     if (B <= 4) return launch_skinny<4>(xb, wb, rb, (bf16*)out, B, N, K, ldx, ldw, ldo, ar, st);
     if (B <= 8) return launch_skinny<8>(xb, wb, rb, (bf16*)out, B, N, K, ldx, ldw, ldo, ar, st);
-    return launch_skinny<16>(xb, wb, rb, (bf16*)out, B, N, K, ldx, ldw, ldo, ar, st);
+    return launch_skinny16(xb, wb, rb, (bf16*)out, B, N, K, ldx, ldw, ldo, ar, st);   // tensor cores (mma.sync)
 }
 
 // out[n] = sum over ranks of in[n] (bf16, fp32 accumulation in rank order).  n % 8 == 0, n <= slot_elems.

@@ -133,7 +133,7 @@ def fused_gemm_rs(ctx, x2d: torch.Tensor, weight: torch.Tensor, layout: str = "n
 
 # ---- decode path: one-shot all-reduce and skinny GEMM -> all-reduce (csrc/fused_gemm_ar.cu) -----------------------------
 _AR_SLOT_ELEMS = 1 << 20           # floats per (parity, source) staging slot: messages up to 2 MB of bf16
-_SKINNY_MAX_ROWS = 8              # above this the tensor-core GEMM wins: the FMA loop re-reads X from shared memory per row
+_SKINNY_MAX_ROWS = 16             # 1..8 rows: FMA kernel; 9..16: mma.sync m16n8k16 kernel (same entry point)
 
 
 def _ar_state(ctx):
@@ -179,7 +179,7 @@ def skinny_gemm(x2d: torch.Tensor, weight: torch.Tensor, residual: Optional[torc
             or x2d.stride(1) != 1 or weight.stride(1) != 1 or x2d.stride(0) % 8 or weight.stride(0) % 8):
         return None
     kb = 1 if B <= 1 else 2 if B <= 2 else 4 if B <= 4 else 8 if B <= 8 else 16
-    if kb * K * 2 + kb * 64 * 4 > 160 * 1024:
+    if kb * (K + 8) * 2 + kb * 64 * 4 + 4096 > 160 * 1024:
         return None
     tp = 1 if ctx is None else ctx.world
     if tp > 8 or (tp > 1 and kb * (N + 8192) > _AR_SLOT_ELEMS):

@@ -46,7 +46,7 @@ def gemm_nt(a: torch.Tensor, b: torch.Tensor, out: Optional[torch.Tensor] = None
     """``a[M,K] @ b[N,K]^T``.  ``accumulate`` adds into ``out`` (fp32 grad accumulation)."""
     m, k = a.shape
     n = b.shape[0]
-    if (m <= 8 and out is None and not accumulate and out_dtype in (None, torch.bfloat16) and a.is_cuda
+    if (m <= 16 and out is None and not accumulate and out_dtype in (None, torch.bfloat16) and a.is_cuda
             and a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16 and _backend() == "tcgen05" and _lib.available()):
         # token generation: weight-streaming kernel instead of a 256-row tensor-core tile that is 94 % padding
         from .fused_comm import skinny_gemm

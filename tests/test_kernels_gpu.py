@@ -437,7 +437,8 @@ def test_flash_attention_large_magnitude_rows():
     assert _rel_err(out, ref) < 1.5e-2
 
 
-@pytest.mark.parametrize("B,K,N", [(1, 2048, 512), (4, 3072, 1024), (5, 1024, 3080), (8, 4096, 256)])
+@pytest.mark.parametrize("B,K,N", [(1, 2048, 512), (4, 3072, 1024), (5, 1024, 3080), (8, 4096, 256), (16, 2048, 1536), (9, 4096, 264),
+                                   (13, 1032, 2048)])
 def test_skinny_gemm(B, K, N):
     from neuronx_distributed_llama3_2_b200.ops.fused_comm import skinny_gemm
 
