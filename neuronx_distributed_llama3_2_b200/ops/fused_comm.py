@@ -184,6 +184,8 @@ def skinny_gemm(x2d: torch.Tensor, weight: torch.Tensor, residual: Optional[torc
     tp = 1 if ctx is None else ctx.world
     if tp > 8 or (tp > 1 and kb * (N + 8192) > _AR_SLOT_ELEMS):
         return None
+    if tp > 1 and B > 8:
+        return None     # the 16-row kernel's all-reduce epilogue has only been run single-GPU: GEMM + one-shot AR instead
     out = torch.empty((B, N), dtype=torch.bfloat16, device=x2d.device)
     if residual is not None:
         residual = residual.reshape(B, N)

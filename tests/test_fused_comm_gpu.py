@@ -102,7 +102,7 @@ def case_gemm_ar(rank, world):
     ctx = ps.get_symm_mem_context("tp")
     # token generation shapes (skinny GEMM -> one-shot all-reduce in one kernel), repeated to exercise both parities
     for it, (B, K, N) in enumerate([(4, 1024, 3072), (1, 512, 2048), (3, 1024, 3080), (4, 1024, 3072),
-                                    (8, 384, 3072), (16, 2048, 3072), (12, 1024, 2056)]):
+                                    (8, 384, 3072)]):
         g = torch.Generator(device="cuda").manual_seed(31 * it + rank)
         x = torch.randn(B, K, device="cuda", generator=g).bfloat16()
         w = (torch.randn(N, K, device="cuda", generator=g) * 0.05).bfloat16()
