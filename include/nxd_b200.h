@@ -150,6 +150,30 @@ int nxd_ag_gemm_bf16(int layout, const void* x_local, const void* w, void* y, in
 int nxd_gemm_rs_bf16(int layout, const void* x, const void* w, void* out, int R, int N, int K, long long ldx,
                      long long ldw, long long ldo, void* const* stage_ptrs, void* const* sig_ptrs, int tp, int rank,
                      int slot_cnt, unsigned epoch, int block_n, void* trace, void* stream);
+/* Expert parallelism (reference: modules/moe/experts.py:121-152, enter / exit_expert_parallel_region all-to-all around
+ * the expert matmuls).  Dispatch: x_local is [ep][E_loc, C, K] (slab d = tokens routed to the experts of rank d); every
+ * rank receives X_total = [ep(source)][E_loc, C, K] in its symmetric buffer and y[(s, e, c), :] = X_total[s, e, c, :] * W_e.
+ * Combine: x is [ep(source)][E_loc, C, K]; result tiles are stored straight into the token owner's output
+ * [E, C, N] (out_ptrs: every rank's symmetric output buffer of this call), nothing is reduced.
+ * W: stacked expert weights, layout 0 = [E_loc * N, K], 1 = [E_loc * K, N].  R = E_loc * C, C % 256 == 0. */
+int nxd_a2a_gemm_bf16(int layout, const void* x_local, const void* w, void* y, int R, int C, int N, int K,
+                      long long ldw, long long ldy, void* const* xt_ptrs, void* const* sig_ptrs, int ep, int rank,
+                      int slot_chunks, unsigned epoch, int comm_ctas, int block_n, void* trace, void* stream);
+int nxd_gemm_a2a_bf16(int layout, const void* x, const void* w, int R, int C, int N, int K, long long ldx,
+                      long long ldw, void* const* out_ptrs, void* const* sig_ptrs, int ep, int rank, int slot_cnt,
+                      unsigned epoch, int block_n, void* trace, void* stream);
+/* ZeRO-1 step over peer memory (reference: the ZeRO-1 optimizer configured in trainer/trainer.py:244-269: reduce-scatter
+ * of the gradient bucket, inner optimizer on the shard, all-gather of the parameters).  grad_ptrs / param_ptrs: dp
+ * pointers to every rank's flat gradient / parameter buffer (symmetric memory).  reduce_shard: out[0..n) (fp32) = sum
+ * over ranks of grad_r[lo..lo+n) in rank order (grad_dtype 0 = fp32, 1 = bf16).  adamw_allgather: AdamW on the shard,
+ * the bf16 result is stored into param_r[lo..lo+n) of EVERY rank.  lo, n in elements, multiples of 8.  The caller
+ * brackets the pair with nxd_symm_barrier. */
+int nxd_zero1_reduce_shard(void* const* grad_ptrs, int grad_dtype, long long lo, long long n, float* out, int dp, int rank,
+                           void* stream);
+int nxd_zero1_adamw_allgather(float* master, float* exp_avg, float* exp_avg_sq, const float* grad,
+                              void* const* param_ptrs, long long lo, long long n, float lr, float beta1, float beta2,
+                              float eps, float weight_decay, int step, float grad_scale, const float* clip_coef, int dp,
+                              int rank, void* stream);
 /* Token-generation path (reference: RowParallelLinear matmul + all-reduce, layers.py:452-468 / mappings.py:176-190):
  * out[B, N] (+ residual) = sum over ranks of x[B, K] * w[N, K]^T in ONE launch, B <= 16; the fp32 partial blocks are
  * pushed into every peer's staging slot and added in rank order (bit-identical on all ranks).  stage_ptrs: tp regions
