@@ -4,7 +4,7 @@ from __future__ import annotations
 
 import os
 import re
-from typing import Any, Dict, List, Optional
+from typing import Tuple, Any, Dict, List, Optional
 
 import torch
 import torch.nn as nn
@@ -206,9 +206,66 @@ class LoraModel(nn.Module):
         except AttributeError:
             return getattr(self.module, name)
 
-    def print_trainable_parameters(self) -> str:
+    def get_nb_trainable_parameters(self) -> Tuple[int, int]:
+        """``(trainable, all)`` parameter counts (reference ``:735-747``)."""
         t = sum(p.numel() for p in self.parameters() if p.requires_grad)
-        n = sum(p.numel() for p in self.parameters())
+        return t, sum(p.numel() for p in self.parameters())
+
+    def module_state_dict(self) -> Dict[str, Any]:
+        """State dict of the wrapped model with the LoRA wrappers still in the key names (reference ``:641-645``)."""
+        return self.module.local_state_dict() if hasattr(self.module, "local_state_dict") else self.module.state_dict()
+
+    def update_state_dict_keys(self, state_dict: Dict[str, Any]) -> Dict[str, Any]:
+        """Map the keys of a BASE-model checkpoint onto the wrapped model: ``...q_proj.weight`` becomes
+        ``...q_proj.base_layer.weight`` for every module that now carries an adapter (reference ``:617-630``)."""
+        wrapped = {name for name, m in self.module.named_modules() if hasattr(m, "base_layer")}
+        out = {}
+        for k, v in state_dict.items():
+            if isinstance(k, str) and "." in k and LORA_PREFIX not in k and ".base_layer." not in k:
+                mod, leaf = k.rsplit(".", 1)
+                if mod in wrapped:
+                    k = f"{mod}.base_layer.{leaf}"
+            out[k] = v
+        return out
+
+    def save_config(self, save_dir: Optional[str] = None, filename: str = "adapter_config.json") -> str:
+        """The adapter configuration as JSON next to the adapter weights (reference ``:446-465``)."""
+        import json
+
+        save_dir = save_dir or self.lora_config.lora_save_dir
+        os.makedirs(save_dir, exist_ok=True)
+        path = os.path.join(save_dir, filename)
+        with open(path, "w") as f:
+            json.dump(self.lora_config.selected_fields_to_save(), f, indent=2, sort_keys=True, default=str)
+        return path
+
+    def load_checkpoint(self, lora_config: Optional[LoraConfig] = None) -> Dict[str, Any]:
+        """Read the adapter checkpoint named by ``lora_config`` (``lora_save_dir`` / ``lora_load_tag``) and adopt the
+        configuration stored inside it, without touching the weights yet (reference ``:494-557``)."""
+        config = lora_config or self.lora_config
+        path = os.path.join(config.lora_save_dir, f"{config.lora_load_tag or 'lora_adapter'}.pt")
+        sd = torch.load(path, map_location="cpu", weights_only=False)
+        saved = sd.get("lora_config")
+        if saved is not None and self.lora_config is not None:
+            for k, v in saved.items():
+                setattr(self.lora_config, k, v)
+        self._loaded_adapter = sd
+        return sd
+
+    def load_lora_adapter(self) -> None:
+        """Apply the adapter weights fetched by ``load_checkpoint`` (reference ``:605-615``)."""
+        sd = getattr(self, "_loaded_adapter", None)
+        if sd is None:
+            sd = self.load_checkpoint()
+        self.load_state_dict(sd, strict=False)
+        self._loaded_adapter = None
+
+    def generate(self, *args, **kwargs):
+        """Delegate to the wrapped model's ``generate`` (reference ``:132-139``)."""
+        return self.module.generate(*args, **kwargs)
+
+    def print_trainable_parameters(self) -> str:
+        t, n = self.get_nb_trainable_parameters()
         msg = f"trainable params: {t:,d} || all params: {n:,d} || trainable%: {100 * t / max(n, 1):.4f}"
         logger.info(msg)
         return msg

@@ -21,6 +21,58 @@ from .dequantize import direct_cast_dequantize, scale_dequantize
 from .quantization_config import QuantizationType, QuantizedDtype
 
 
+class QuantizedParallelLinearLayerStateDictAdaptor:
+    """Reads / writes the three tensors of a quantized linear layer in a state dict whatever produced it (reference
+    ``quantization_layers.py:252-339``): plain ``{prefix}weight`` (int8) + ``{prefix}scale``, or a torch
+    ``{prefix}_packed_params._packed_params`` tuple ``(qint8 weight, bias)`` from ``torch.ao`` dynamic quantization.
+    (The reference's ``get_bias_from_state_dict`` returns the weight for packed params -- SURVEY appendix B; here it
+    returns the bias.)"""
+
+    @staticmethod
+    def _packed(prefix: str, state_dict: dict):
+        return state_dict.get(prefix + "_packed_params._packed_params")
+
+    @staticmethod
+    def get_weight_from_state_dict(prefix: str, state_dict: dict) -> torch.Tensor:
+        packed = QuantizedParallelLinearLayerStateDictAdaptor._packed(prefix, state_dict)
+        w = packed[0] if packed is not None else state_dict[prefix + "weight"]
+        return w.int_repr() if w.is_quantized else w
+
+    @staticmethod
+    def set_weight_to_state_dict(prefix: str, tensor: torch.Tensor, state_dict: dict) -> None:
+        state_dict[prefix + "weight"] = tensor
+        state_dict.pop(prefix + "_packed_params._packed_params", None)
+        state_dict.pop(prefix + "_packed_params.dtype", None)
+
+    @staticmethod
+    def get_bias_from_state_dict(prefix: str, state_dict: dict) -> Optional[torch.Tensor]:
+        packed = QuantizedParallelLinearLayerStateDictAdaptor._packed(prefix, state_dict)
+        if packed is not None:
+            return packed[1]
+        return state_dict.get(prefix + "bias")
+
+    @staticmethod
+    def set_bias_to_state_dict(prefix: str, tensor: Optional[torch.Tensor], state_dict: dict) -> None:
+        if tensor is not None:
+            state_dict[prefix + "bias"] = tensor
+
+    @staticmethod
+    def get_scale_from_state_dict(prefix: str, state_dict: dict) -> torch.Tensor:
+        packed = QuantizedParallelLinearLayerStateDictAdaptor._packed(prefix, state_dict)
+        if packed is None:
+            return state_dict[prefix + "scale"]
+        w = packed[0]
+        if w.qscheme() in (torch.per_channel_symmetric, torch.per_channel_affine):
+            shape = [1] * w.dim()
+            shape[w.q_per_channel_axis()] = -1
+            return w.q_per_channel_scales().to(torch.float32).reshape(shape)
+        return torch.tensor([w.q_scale()], dtype=torch.float32)
+
+    @staticmethod
+    def set_scale_to_state_dict(prefix: str, tensor: torch.Tensor, state_dict: dict) -> None:
+        state_dict[prefix + "scale"] = tensor
+
+
 class BaseQuantizeParallelLinear(torch.nn.Module):
     def _setup_scale(self, weight_shape, partition_dim: int, quantization_type: QuantizationType,
                      per_channel_axis: Optional[int], device, expert_dims: int = 0) -> None:

@@ -87,3 +87,41 @@ def test_lora_on_tensor_parallel_llama():
     torch.testing.assert_close(model(ids, labels=ids), changed, atol=1e-4, rtol=1e-4)
     model.unmerge_lora()
     assert "trainable params" in model.print_trainable_parameters()
+
+
+def test_lora_model_helpers_base_checkpoint_keys_config_and_two_step_load():
+    import json
+
+    torch.manual_seed(0)
+    base = _Tiny()
+    plain_state = {k: v.clone() for k, v in base.state_dict().items()}
+    cfg = LoraConfig(enable_lora=True, lora_rank=2, lora_alpha=4, target_modules=["q_proj", "v_proj"])
+    model = get_lora_model(base, cfg)
+    t, n = model.get_nb_trainable_parameters()
+    assert 0 < t < n and f"{t:,d}" in model.print_trainable_parameters()
+    # a BASE checkpoint loads into the wrapped model after its keys are re-pointed at ``base_layer``
+    mapped = model.update_state_dict_keys(plain_state)
+    assert "q_proj.base_layer.weight" in mapped and "out.weight" in mapped and "q_proj.weight" not in mapped
+    missing = model.get_base_model().load_state_dict(mapped, strict=False).missing_keys
+    assert missing and all("lora_" in k for k in missing)
+    assert any("base_layer" in k for k in model.module_state_dict())
+    with torch.no_grad():
+        base.v_proj.lora_B.weight.normal_()
+    ids = torch.randint(0, 20, (2, 4))
+    want = model(ids)
+    with tempfile.TemporaryDirectory() as d:
+        cfg.lora_save_dir = d
+        model.save_lora()
+        cfg_path = model.save_config()
+        with open(cfg_path) as f:
+            saved = json.load(f)
+        assert saved["lora_rank"] == 2 and "target_modules" in saved
+        fresh = _Tiny()
+        fresh.load_state_dict(plain_state)
+        m2 = LoraModel(fresh, LoraConfig(enable_lora=True, lora_rank=2, lora_alpha=4, target_modules=["q_proj", "v_proj"],
+                                         lora_save_dir=d))
+        assert not torch.allclose(m2(ids), want)
+        sd = m2.load_checkpoint()                    # step 1: read the file, adopt its configuration
+        assert "lora_config" in sd
+        m2.load_lora_adapter()                       # step 2: apply the adapter weights
+        torch.testing.assert_close(m2(ids), want, atol=1e-6, rtol=1e-6)

@@ -2,6 +2,7 @@
 (reference ``test/unit_test/quantization/test_*.py``)."""
 from __future__ import annotations
 
+import pytest
 import torch
 
 from neuronx_distributed_llama3_2_b200 import quantization as Q
@@ -60,3 +61,25 @@ def test_convert_and_numerics_per_channel_and_per_tensor():
         qm.load_state_dict(sd)
         out = qm(x)
         assert ((out - ref).norm() / ref.norm()).item() < (0.02 if per_channel else 0.04)
+
+
+def test_state_dict_adaptor_class_reads_plain_and_packed_layouts():
+    from neuronx_distributed_llama3_2_b200.quantization.quantization_layers import (
+        QuantizedParallelLinearLayerStateDictAdaptor as A)
+
+    w = torch.randn(6, 4)
+    qw = torch.quantize_per_channel(w, torch.full((6,), 0.05), torch.zeros(6, dtype=torch.int64), 0, torch.qint8)
+    bias = torch.arange(6.0)
+    packed = {"fc._packed_params._packed_params": (qw, bias), "fc._packed_params.dtype": torch.qint8}
+    assert A.get_weight_from_state_dict("fc.", packed).dtype == torch.int8
+    assert torch.equal(A.get_bias_from_state_dict("fc.", packed), bias)          # the bias, not the weight
+    assert A.get_scale_from_state_dict("fc.", packed).shape == (6, 1)
+    plain = {}
+    A.set_weight_to_state_dict("fc.", qw.int_repr(), plain)
+    A.set_scale_to_state_dict("fc.", torch.full((6, 1), 0.05), plain)
+    A.set_bias_to_state_dict("fc.", bias, plain)
+    assert set(plain) == {"fc.weight", "fc.scale", "fc.bias"}
+    assert torch.equal(A.get_weight_from_state_dict("fc.", plain), qw.int_repr())
+    assert float(A.get_scale_from_state_dict("fc.", plain)[0]) == pytest.approx(0.05)
+    qt = torch.quantize_per_tensor(w, 0.1, 0, torch.qint8)
+    assert A.get_scale_from_state_dict("g.", {"g._packed_params._packed_params": (qt, None)}).shape == (1,)
