@@ -265,3 +265,49 @@ class ModelBuilder:
                     tensors[k] = v.clone()
                 seen[v.data_ptr()] = k
             save_file(tensors, os.path.join(serialize_path, f"tp{rank}_sharded_checkpoint.safetensors"))
+
+
+# ---- names of the reference's SPMD runtime classes (``trace/spmd.py``, ``trace/model_builder.py``) ---------------------
+# SPMDBucketModel = one compiled bucket (NEFF there, captured CUDA graph here); NxDModelExecutor = the object that runs
+# the routed bucket; StateInitializer allocated the aliased KV state per rank (``KVCache`` does that here).
+SPMDBucketModel = _Bucket
+SPMDBucketModelScript = _Bucket
+NxDModelExecutor = NxDModel
+
+
+def default_bucket_kernel(inputs: List[torch.Tensor]):
+    """Single-bucket "kernel" of the reference (``spmd.py``): inputs unchanged, bucket 0."""
+    return inputs, torch.tensor(0)
+
+
+class StateInitializer(torch.nn.Module):
+    """Allocates the per-rank state tensors of a traced model from ``{name: (shape, dtype)}`` (reference
+    ``spmd.py:63-80`` builds them from the metaneff); used for KV caches that live outside ``KVCache``."""
+
+    def __init__(self, shapes: Dict[str, Any], dtypes: Dict[str, torch.dtype], local_ranks_size: int = 1):
+        super().__init__()
+        self.shapes, self.dtypes, self.local_ranks_size = shapes, dtypes, local_ranks_size
+
+    def forward(self, device=None) -> Dict[str, torch.Tensor]:
+        return {k: torch.zeros(tuple(shape), dtype=self.dtypes[k], device=device) for k, shape in self.shapes.items()}
+
+
+class ModelContainer:
+    """One registered sub-model of ``ModelBuilder`` (reference ``model_builder.py``)."""
+
+    def __init__(self, model_instance: "BaseModelInstance", example_inputs, compiler_args=None, bucket_config=None,
+                 priority_model_idx=None):
+        self.model_instance, self.example_inputs = model_instance, example_inputs
+        self.compiler_args, self.bucket_config, self.priority_model_idx = compiler_args, bucket_config, priority_model_idx
+
+
+class JITWrapper(torch.nn.Module):
+    """Makes a function traceable as a module (reference ``model_builder.py``: ``torch.jit.trace`` needs an
+    ``nn.Module``); here it only forwards."""
+
+    def __init__(self, func: Callable, is_torchscript_model: bool = False):
+        super().__init__()
+        self.func, self.is_torchscript_model = func, is_torchscript_model
+
+    def forward(self, *inputs):
+        return self.func(*inputs)

@@ -55,3 +55,68 @@ def parallel_model_load(model_or_func, load_dir: str, example_inputs: Sequence[t
     sd = torch.load(os.path.join(load_dir, f"tp_{rank}.pt"), map_location="cpu", weights_only=False)
     model.module.load_state_dict(sd)
     return model
+
+
+# ---- names of the reference's trace module (``trace/trace.py``) -----------------------------------------------------
+from .checkpoint_sharding import (_mock_parallel_state, get_sharded_checkpoint, invoke_preshard_hook,  # noqa: E402,F401
+                                  shard_children)
+
+ParallelModel = TensorParallelModel
+TensorParallelNeuronModel = TensorParallelModel     # reference: thread pool over per-rank NEFFs in ONE process; here one
+                                                    # process per GPU runs its own rank
+
+
+def generate_ranked_folder(tp_rank: int, bucket_rank: int, bucket_degree: int) -> str:
+    """Folder suffix of one (rank, bucket) artefact (reference ``:162-163``)."""
+    return f"_tp{tp_rank}" + (f"_bk{bucket_rank}" if bucket_degree > 1 else "")
+
+
+def find_unique_dtypes(model: torch.nn.Module) -> dict:
+    """``{dtype: number of state-dict entries}`` (reference ``:372-377``)."""
+    out: dict = {}
+    for v in model.state_dict().values():
+        out[v.dtype] = out.get(v.dtype, 0) + 1
+    return out
+
+
+def create_local_weight(rank: int, world_size: int, full_weight: torch.Tensor, partition_dim: int, per_partition_size: int,
+                        stride: int, out_weight: torch.Tensor = None) -> torch.Tensor:
+    """Slice of ``full_weight`` owned by ``rank`` (strided column groups honoured), reference argument order
+    (``:643-669``)."""
+    from ..parallel.layers import create_local_weight as _clw
+
+    w = _clw(full_weight, partition_dim, per_partition_size, stride, rank=rank, world_size=world_size)
+    if out_weight is not None:
+        out_weight.copy_(w)
+        return out_weight
+    return w
+
+
+def create_local_weight_qkv(rank: int, world_size: int, full_weight: torch.Tensor, partition_dim: int, q_len: int,
+                            kv_len: int, out_weight: torch.Tensor = None) -> torch.Tensor:
+    """Fused ``[q | k | v]`` weight: every part is sharded on its own, then the rank's three slices are re-fused
+    (reference ``:629-641``)."""
+    q, k, v = torch.split(full_weight, [q_len, kv_len, kv_len], dim=partition_dim)
+    parts = [torch.chunk(t, world_size, dim=partition_dim)[rank] for t in (q, k, v)]
+    w = torch.cat(parts, dim=partition_dim)
+    if out_weight is not None:
+        out_weight.copy_(w)
+        return out_weight
+    return w
+
+
+def collect_tp_neuron_models(models: list, results, bucket_config=None, tp_degree: int = 1) -> None:
+    """Gather per-rank artefacts produced by tracing workers into ``models[tp_rank]`` (reference ``:115-120`` drains a
+    multiprocessing queue of NEFFs; here ``results`` is any iterable of ``(tp_rank, model)``)."""
+    for tp_rank, model in results:
+        models[tp_rank] = model
+
+
+def collect_tp_bucket_neuron_models(models: list, results, bucket_config=None, tp_degree: int = 1) -> None:
+    """Same for bucketed models: ``results`` yields ``(tp_rank, bucket_rank, model)``; ``models[tp_rank]`` becomes the
+    list of that rank's buckets in bucket order."""
+    per_rank: dict = {}
+    for tp_rank, bucket_rank, model in results:
+        per_rank.setdefault(tp_rank, {})[bucket_rank] = model
+    for tp_rank, buckets in per_rank.items():
+        models[tp_rank] = [buckets[b] for b in sorted(buckets)]

@@ -356,3 +356,17 @@ class GQAQKVColumnParallelLinear(torch.nn.Module):
             k = mappings.gather_from_tensor_model_parallel_region(k)
             v = mappings.gather_from_tensor_model_parallel_region(v)
         return q, k, v
+
+
+def destroy_kv_group() -> None:
+    """Forget the cached KV-sharing groups (reference ``qkv_linear.py:81-85``); they live in ``parallel_state`` here."""
+    ps.destroy_kv_shared_groups() if hasattr(ps, "destroy_kv_shared_groups") else None
+
+
+def check_requires_grad(weight_qkv, fuse_qkv: bool, weight_q) -> bool:
+    return bool(weight_qkv.requires_grad if fuse_qkv else weight_q.requires_grad)
+
+
+def check_use_bias(weight_qkv, fuse_qkv: bool, weight_q, bias_q, bias_qkv) -> bool:
+    has_bias = (bias_qkv is not None) if fuse_qkv else (bias_q is not None)
+    return has_bias and check_requires_grad(weight_qkv, fuse_qkv, weight_q)

@@ -163,3 +163,11 @@ def decode_attention_ref(q, cache_k, cache_v, lengths, scale, block_table=None, 
         p = torch.softmax(s, dim=-1)
         outs.append(torch.einsum("hl,hld->hd", p, vv))
     return torch.stack(outs).to(q.dtype)
+
+
+def __getattr__(name):   # ``NKIAttnFunc``: the autograd function behind ``flash_attn_func`` (reference kernels/flash_attn.py:56)
+    if name == "NKIAttnFunc":
+        from .flash_attn import _FlashAttnFn
+
+        return _FlashAttnFn
+    raise AttributeError(name)

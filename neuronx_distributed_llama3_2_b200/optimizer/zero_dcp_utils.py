@@ -59,3 +59,18 @@ def load_optim_state_dict(path: str, template: Dict[str, Any]) -> Dict[str, Any]
     except FileNotFoundError:
         pass
     return template
+
+
+def get_dcp_aux_infos(model: torch.nn.Module, optim: torch.optim.Optimizer) -> Dict[str, Any]:
+    """What a DCP save needs to know besides the tensors (reference ``:374-382``): optimizer parameter ids -> parameters
+    and -> names, and the un-sharded shape of every parameter."""
+    names = {id(p): n for n, p in model.named_parameters()}
+    pid_to_params, pid_to_names, pid = {}, {}, 0
+    for group in optim.param_groups:
+        for p in group["params"]:
+            pid_to_params[pid] = p
+            pid_to_names[pid] = names.get(id(p), f"param_{pid}")
+            pid += 1
+    sd = optim.state_dict()
+    return {"optim_pid_to_params": pid_to_params, "optim_pid_to_pnames": pid_to_names,
+            "shape_info": sd.get("shape_info", {i: tuple(p.shape) for i, p in pid_to_params.items()})}

@@ -564,6 +564,42 @@ class Conv2dWithInputGradAllReduce(torch.autograd.Function):
         return grad_input, grad_weight, grad_bias, None, None, None
 
 
+class Conv2dWithWeightGradAllReduce(torch.autograd.Function):
+    """Conv2d over a TP-sharded INPUT (the weight is replicated along the sharded dim of the activations): the weight /
+    bias gradients are partial on every rank and all-reduced over TP (reference ``layers.py:877-930``)."""
+
+    @staticmethod
+    def forward(ctx, input, weight, bias, stride, padding, allreduce_weight_grad):
+        ctx.stride, ctx.padding = stride, padding
+        ctx.allreduce_weight_grad = allreduce_weight_grad
+        ctx.use_bias = bias is not None
+        ctx.save_for_backward(input, weight)
+        return F.conv2d(input, weight, bias, stride, padding)
+
+    @staticmethod
+    def backward(ctx, grad_output):
+        input, weight = ctx.saved_tensors
+        grad_weight = torch.nn.grad.conv2d_weight(input, weight.shape, grad_output, ctx.stride, ctx.padding)
+        grad_bias = grad_output.sum(dim=(0, 2, 3)) if ctx.use_bias else None
+        handles = []
+        if ctx.allreduce_weight_grad and get_tensor_model_parallel_size() > 1:
+            handles.append(comm_linear.all_reduce_async(grad_weight))
+            if grad_bias is not None:
+                handles.append(comm_linear.all_reduce_async(grad_bias))
+        grad_input = torch.nn.grad.conv2d_input(input.shape, weight, grad_output, ctx.stride, ctx.padding)
+        for h in handles:
+            h.wait()
+        return grad_input, grad_weight, grad_bias, None, None, None
+
+
+def conv2d_with_weight_grad_allreduce(input: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor],
+                                      stride: Tuple[int, int], padding: Tuple[int, int],
+                                      allreduce_weight_grad: bool) -> torch.Tensor:
+    args = cast_if_autocast_enabled(input, weight, bias, stride, padding, allreduce_weight_grad)
+    with torch.amp.autocast("cuda", enabled=False):
+        return Conv2dWithWeightGradAllReduce.apply(*args)
+
+
 def _pair(v) -> Tuple[int, int]:
     return (v, v) if isinstance(v, int) else tuple(v)
 

@@ -344,3 +344,17 @@ def exit_expert_parallel_region(x: torch.Tensor, scatter_gather: bool = False) -
     if scatter_gather:
         x = gather_from_tensor_model_parallel_region_with_dim(x, 1)
     return x
+
+
+def nonzero_partition_dim_swap(func):
+    """Decorator for ``f(x, partition_dim)``: the wrapped function always sees the partition dim at position 0 (pre- and
+    post-transpose), callers keep their own dim (reference ``mappings.py:24-39``)."""
+    import functools
+
+    @functools.wraps(func)
+    def wrapped(x: torch.Tensor, partition_dim: int) -> torch.Tensor:
+        xt = x.transpose(0, partition_dim) if partition_dim != 0 else x
+        yt = func(xt, partition_dim=0)
+        return yt.transpose(0, partition_dim) if partition_dim != 0 else yt
+
+    return wrapped

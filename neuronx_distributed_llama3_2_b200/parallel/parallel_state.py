@@ -528,3 +528,13 @@ def get_symm_mem_context(kind: str = "tp"):
     ctx = SymmMemContext(info.group, info.ranks)
     _SYMM_CTX[kind] = ctx
     return ctx
+
+
+def try_set_nki_parallel_state(parallel_state=None) -> bool:
+    """The reference hands the TP topology to its NKI kernels (``parallel_state.py:425-444``).  The sm_100a kernels get
+    theirs through the symmetric-memory context (peer pointers, rank, world); this call builds it eagerly and reports
+    whether the fused kernels are available."""
+    try:
+        return get_symm_mem_context("tp") is not None
+    except Exception:  # noqa: BLE001 - ranks that cannot map each other's memory
+        return False

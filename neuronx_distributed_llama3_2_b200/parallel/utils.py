@@ -159,3 +159,32 @@ def add_barrier(name: str = "nxd-barrier") -> None:
         if os.environ.get("NXD_SKIP_RENDEZVOUS", "0") == "1":
             return
         dist.barrier()
+
+
+def ensure_divisibility(numerator: int, denominator: int) -> None:
+    """Assert that ``numerator`` is divisible by ``denominator`` (reference ``utils.py:78-80``)."""
+    assert numerator % denominator == 0, f"{numerator} is not divisible by {denominator}"
+
+
+def is_pjrt_device() -> bool:
+    """The reference asks whether torch_xla runs on the PJRT runtime (``utils.py``); there is no XLA here."""
+    return False
+
+
+def verify_casted_dtype(value) -> None:
+    """Under autocast, check that every tensor inside ``value`` already has the autocast dtype (reference
+    ``utils.py:249-266``; used after ``cast_if_autocast_enabled``)."""
+    import collections.abc
+
+    if not torch.is_autocast_enabled():
+        return
+    want = torch.get_autocast_gpu_dtype()
+    if isinstance(value, torch.Tensor):
+        assert not value.is_floating_point() or value.dtype == want, f"expected {want}, got {value.dtype}"
+    elif isinstance(value, collections.abc.Mapping):
+        for k, v in value.items():
+            verify_casted_dtype(k)
+            verify_casted_dtype(v)
+    elif isinstance(value, (list, tuple)):
+        for v in value:
+            verify_casted_dtype(v)

@@ -6,6 +6,8 @@ graph is DCE'd and linted.  The HF tracer is used when the model is a ``transfor
 """
 from __future__ import annotations
 
+import contextlib
+
 import inspect
 from typing import Any, Callable, Dict, Iterable, List, Optional, Sequence, Type
 
@@ -83,3 +85,43 @@ def trace_model(model: torch.nn.Module, input_names: Optional[List[str]] = None,
     gm.graph.lint()
     gm.recompile()
     return gm
+
+
+class TorchTracerWrapper(NxDTracer):
+    """Name of the reference's torch.fx tracer (``pipeline/trace.py:57-76``): ``NxDTracer`` with keyword configuration."""
+
+    def __init__(self, **config):
+        super().__init__(leaf_classes=tuple(config.get("leaf_modules", config.get("leaf_classes", ()))),
+                         autowrap_functions=tuple(config.get("autowrap_functions", ())),
+                         autowrap_modules=tuple(config.get("autowrap_modules", ())))
+
+
+def get_tracer_class(model: torch.nn.Module = None, tracer_cls=None):
+    """``None`` / ``"torch"`` -> the torch.fx based tracer; a class is returned unchanged.  The reference also offers
+    ``"hf"`` (transformers' HFTracer); HF models trace through the same torch.fx path here because the transformer
+    layer class is a leaf."""
+    if tracer_cls is None or tracer_cls == "torch" or tracer_cls == "hf":
+        return TorchTracerWrapper
+    if isinstance(tracer_cls, str):
+        raise ValueError(f"Unsupported tracer_cls {tracer_cls}")
+    return tracer_cls
+
+
+@contextlib.contextmanager
+def patch_obj_method(autowrap_obj_methods: Optional[Dict[Any, List[str]]]):
+    """Inside the context the listed bound methods are opaque to ``torch.fx`` symbolic tracing: a call on a Proxy is
+    recorded as ONE ``call_function`` node instead of being traced through (reference ``:126-148``)."""
+    originals = []
+    try:
+        for obj, names in (autowrap_obj_methods or {}).items():
+            assert isinstance(names, list), f"autowrap_obj_methods values must be lists, got {type(names)}"
+            for name in names:
+                if not hasattr(obj, name):
+                    raise ValueError(f"{type(obj)} has no method {name}")
+                fn = getattr(obj, name)
+                originals.append((obj, name, fn))
+                setattr(obj, name, fx._symbolic_trace._create_wrapped_func(fn))
+        yield
+    finally:
+        for obj, name, fn in reversed(originals):
+            setattr(obj, name, fn)

@@ -34,5 +34,12 @@ class PerChannelAbsMaxObserver(torch.nn.Module):
         scale = torch.clamp(self.max_val / float(self.quant_max), min=self.eps)
         return scale, torch.zeros_like(scale, dtype=torch.int64)
 
+    @classmethod
+    def with_args(cls, **kwargs):
+        """``torch.ao`` observer-factory protocol: ``QConfig(weight=PerChannelAbsMaxObserver.with_args(...))``."""
+        from torch.ao.quantization.observer import _with_args
+
+        return _with_args(cls, **kwargs)
+
     def extra_repr(self) -> str:
         return f"max_val={self.max_val}"

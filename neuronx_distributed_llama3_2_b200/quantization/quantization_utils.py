@@ -27,7 +27,20 @@ def quantize_per_channel_symmetric(w: torch.Tensor, ch_axis: int = 0) -> Tuple[t
 def convert_qint8_to_int8_state_dict(state_dict: Dict[str, torch.Tensor]) -> Dict[str, torch.Tensor]:
     """torch ``qint8`` tensors -> plain ``int8`` + ``<name>.scale`` entries (reference ``:55-86``)."""
     out = {}
+    packed_suffix = "_packed_params._packed_params"
     for name, t in state_dict.items():
+        if name.endswith(packed_suffix):          # torch.ao dynamic-quantized Linear: (qint8 weight, bias) tuple
+            prefix = name[: -len(packed_suffix)]
+            qw, bias = t
+            out[prefix + "weight"] = qw.int_repr()
+            out[prefix + "scale"] = extract_q_scale(qw).to(torch.float32)
+            if bias is not None:
+                out[prefix + "bias"] = bias
+            continue
+        if name.endswith("_packed_params.dtype") or (name.endswith(".zero_point") and name[:-10] + packed_suffix[:0] + "_packed_params._packed_params" in state_dict):
+            continue
+        if name.endswith(".scale") and name[:-5] + "_packed_params._packed_params" in state_dict:
+            continue                              # activation scale of the dynamic module: recomputed at run time
         if isinstance(t, torch.Tensor) and t.is_quantized:
             out[name] = t.int_repr()
             if t.qscheme() in (torch.per_channel_symmetric, torch.per_channel_affine):
@@ -57,3 +70,46 @@ def quantize_state_dict(state_dict: Dict[str, torch.Tensor], per_channel: bool =
         out[name] = q
         out[name[: -len("weight")] + "scale"] = s
     return out
+
+
+def extract_q_scale_per_tensor(q_tensor: torch.Tensor) -> torch.Tensor:
+    """Scale of a per-tensor quantized tensor, shape ``[1]`` (reference ``:11-21``)."""
+    assert q_tensor.qscheme() in (torch.per_tensor_affine, torch.per_tensor_symmetric)
+    return torch.tensor([q_tensor.q_scale()])
+
+
+def extract_q_scale_per_channel(q_tensor: torch.Tensor) -> torch.Tensor:
+    """Per-channel scales shaped to broadcast against the weight (reference ``:24-43``)."""
+    assert q_tensor.qscheme() in (torch.per_channel_affine, torch.per_channel_symmetric)
+    shape = [1] * q_tensor.dim()
+    shape[q_tensor.q_per_channel_axis()] = q_tensor.shape[q_tensor.q_per_channel_axis()]
+    return q_tensor.q_per_channel_scales().to(torch.float32).reshape(shape)
+
+
+def extract_q_scale(q_tensor: torch.Tensor) -> torch.Tensor:
+    if q_tensor.qscheme() in (torch.per_tensor_affine, torch.per_tensor_symmetric):
+        return extract_q_scale_per_tensor(q_tensor)
+    if q_tensor.qscheme() in (torch.per_channel_affine, torch.per_channel_symmetric):
+        return extract_q_scale_per_channel(q_tensor)
+    raise ValueError(f"qscheme {q_tensor.qscheme()} is not supported")
+
+
+def quantize_pytorch_model_per_tensor_symmetric(float_model: torch.nn.Module, inplace: bool = False) -> torch.nn.Module:
+    """``torch.ao`` dynamic quantization of every ``nn.Linear`` with one symmetric int8 scale per weight (reference
+    ``:89-95``); its state dict feeds ``convert_qint8_to_int8_state_dict``."""
+    from torch.ao.quantization import default_dynamic_qconfig, quantize_dynamic
+
+    return quantize_dynamic(float_model, qconfig_spec={torch.nn.Linear: default_dynamic_qconfig}, dtype=torch.qint8,
+                            inplace=inplace)
+
+
+def quantize_pytorch_model_per_channel_symmetric(float_model: torch.nn.Module, inplace: bool = False) -> torch.nn.Module:
+    """Same with one scale per output channel, from ``PerChannelAbsMaxObserver`` (reference ``:98-110``)."""
+    from torch.ao.quantization import QConfig, default_observer, quantize_dynamic
+
+    from .observer import PerChannelAbsMaxObserver
+
+    qconfig = QConfig(activation=default_observer,
+                      weight=PerChannelAbsMaxObserver.with_args(dtype=torch.qint8, qscheme=torch.per_channel_symmetric,
+                                                                ch_axis=0))
+    return quantize_dynamic(float_model, qconfig_spec={torch.nn.Linear: qconfig}, dtype=torch.qint8, inplace=inplace)

@@ -164,3 +164,18 @@ def initialize_parallel_optimizer(nxd_config: Dict[str, Any], optimizer_class, p
     parameters = list(parameters)
     optimizer = initialize_optimizer_from_class(nxd_config, optimizer_class, parameters, **defaults)
     return NxDOptimizer(optimizer, nxd_config)
+
+
+def filter_to_local_parameter_group(optimizer, model) -> None:
+    """Keep only the parameters that live on THIS pipeline stage in the optimizer's param groups (reference
+    ``:293-303``: with delayed materialisation the optimizer is built from meta parameters and re-pointed at the local,
+    materialised ones)."""
+    pmap = getattr(model, "meta_device_parameter_map", None)
+    local = {id(p) for p in model.parameters()}
+    for group in optimizer.param_groups:
+        kept = []
+        for p in group["params"]:
+            q = pmap.get(p, p) if pmap is not None else p
+            if q.device.type != "meta" and (pmap is not None or id(q) in local):
+                kept.append(q)
+        group["params"] = kept

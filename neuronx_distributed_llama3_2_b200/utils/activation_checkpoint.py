@@ -48,3 +48,40 @@ def apply_activation_checkpointing(model: torch.nn.Module, check_fn: Callable[[t
             continue
         checkpoint_wrapper(m)
         wrapped.append(m)
+
+
+class NxDCheckpointWrapper(torch.nn.Module):
+    """Module form of ``checkpoint_wrapper`` (reference ``utils/activation_checkpoint.py``: a
+    ``CheckpointWrapper`` subclass whose state-dict keys do not carry the wrapper prefix): parameters and
+    ``state_dict`` of the wrapped module appear under their ORIGINAL names, so checkpoints are interchangeable between
+    runs with and without activation checkpointing."""
+
+    def __init__(self, module: torch.nn.Module):
+        super().__init__()
+        self._checkpoint_wrapped_module = module
+
+    def forward(self, *args, **kwargs):
+        inner = self._checkpoint_wrapped_module
+        if not (self.training and torch.is_grad_enabled()):
+            return inner(*args, **kwargs)
+        return checkpoint(inner, *args, use_reentrant=False, **kwargs)
+
+    def __getattr__(self, name):
+        try:
+            return super().__getattr__(name)
+        except AttributeError:
+            return getattr(self._checkpoint_wrapped_module, name)
+
+    def named_parameters(self, prefix: str = "", recurse: bool = True, remove_duplicate: bool = True):
+        for n, p in super().named_parameters(prefix=prefix, recurse=recurse, remove_duplicate=remove_duplicate):
+            yield n.replace("_checkpoint_wrapped_module.", ""), p
+
+    def state_dict(self, *args, **kwargs):
+        sd = super().state_dict(*args, **kwargs)
+        return type(sd)((k.replace("_checkpoint_wrapped_module.", ""), v) for k, v in sd.items())
+
+    def _load_from_state_dict(self, state_dict, prefix, *args, **kwargs):
+        inner_prefix = prefix + "_checkpoint_wrapped_module."
+        for k in [k for k in state_dict if k.startswith(prefix) and not k.startswith(inner_prefix)]:
+            state_dict[inner_prefix + k[len(prefix):]] = state_dict.pop(k)
+        super()._load_from_state_dict(state_dict, prefix, *args, **kwargs)

@@ -19,6 +19,21 @@ _LEVELS = {
     "off": logging.FATAL + 10,
 }
 logging.addLevelName(_LEVELS["trace"], "TRACE")
+
+
+class PackagePathFilter(logging.Filter):
+    """Adds ``record.relativepath`` = the source path relative to the first ``sys.path`` entry that contains it, for
+    compact ``%(relativepath)s:%(lineno)d`` log formats (reference ``utils/logger.py:16-32``)."""
+
+    def filter(self, record: logging.LogRecord) -> bool:
+        path = record.pathname
+        record.relativepath = path
+        for root in sorted((p for p in sys.path if p), key=len, reverse=True):
+            root = root if root.endswith(os.sep) else root + os.sep
+            if path.startswith(root):
+                record.relativepath = os.path.relpath(path, root)
+                break
+        return True
 _LOGGERS = {}
 
 

@@ -172,3 +172,85 @@ def check_delay_tracing(nxd_config: dict) -> bool:
 
 def get_delay_tracing(arg) -> bool:
     return False
+
+
+# ---- environment probes and attribute-preserving contexts (reference ``utils/model_utils.py:91-241``) -------------------
+def is_hf_transformers_available() -> bool:
+    try:
+        import transformers  # noqa: F401
+        return True
+    except Exception:  # noqa: BLE001
+        return False
+
+
+def is_hf_accelerate_available() -> bool:
+    try:
+        import accelerate  # noqa: F401
+        return True
+    except Exception:  # noqa: BLE001
+        return False
+
+
+def is_hf_pretrained_model(model) -> bool:
+    if not is_hf_transformers_available():
+        return False
+    from transformers import PreTrainedModel
+
+    return isinstance(model, PreTrainedModel)
+
+
+def is_nxdt_available() -> bool:
+    """NeuronxDistributedTraining (Megatron-style modules) is a Neuron-only package."""
+    return False
+
+
+def is_nxdt_pretrained_model(model) -> bool:
+    return False
+
+
+@contextlib.contextmanager
+def preserve_shared_weights(model: nn.Module, ignore_hf: bool = False):
+    """Re-tie shared parameters (e.g. embedding / lm_head) after the body replaced them -- moving a model between
+    devices or materialising it creates new Parameter objects and silently unties them."""
+    hf = is_hf_pretrained_model(model) and not ignore_hf
+    groups = None if hf else analyze_shared_parameters(model)
+    try:
+        yield
+    finally:
+        if hf:
+            model.tie_weights()
+        elif groups:
+            retie_shared_weights(groups)
+
+
+_PARALLEL_ATTRS = ("tensor_model_parallel", "partition_dim", "partition_stride", "num_partitions", "expert_model_parallel",
+                   "sequence_parallel_enabled", "shared")
+
+
+@contextlib.contextmanager
+def preserve_parallel_attributes(model: nn.Module):
+    """Parameters recreated inside the body (materialisation, ``.to()`` of meta tensors) lose the python attributes the
+    framework hangs on them; record them by name and put them back."""
+    saved = {n: {a: getattr(p, a) for a in _PARALLEL_ATTRS if hasattr(p, a)} for n, p in model.named_parameters()}
+    try:
+        yield
+    finally:
+        for n, p in model.named_parameters():
+            for a, v in saved.get(n, {}).items():
+                setattr(p, a, v)
+
+
+def has_fake_tensors(model: nn.Module, ignored_params=()) -> bool:
+    """Meta-device parameters are this framework's deferred-initialisation "fake tensors" (the reference uses
+    torchdistx fakes)."""
+    ignored = {id(p) for p in ignored_params}
+    return any(p.device.type == "meta" and id(p) not in ignored for p in model.parameters())
+
+
+def maybe_materalize_model(model: nn.Module, device=None) -> None:
+    """Materialise a model built on the meta device (name kept from the reference, typo included)."""
+    if not has_fake_tensors(model):
+        return
+    device = device or (torch.device("cuda", torch.cuda.current_device()) if torch.cuda.is_available() else torch.device("cpu"))
+    with preserve_parallel_attributes(model), preserve_shared_weights(model, ignore_hf=True):
+        reinit_model(model, device)

@@ -83,3 +83,19 @@ def test_state_dict_adaptor_class_reads_plain_and_packed_layouts():
     assert float(A.get_scale_from_state_dict("fc.", plain)[0]) == pytest.approx(0.05)
     qt = torch.quantize_per_tensor(w, 0.1, 0, torch.qint8)
     assert A.get_scale_from_state_dict("g.", {"g._packed_params._packed_params": (qt, None)}).shape == (1,)
+
+
+def test_torch_ao_quantized_models_convert_to_int8_state_dicts():
+    torch.manual_seed(0)
+    lin = torch.nn.Sequential(torch.nn.Linear(16, 12), torch.nn.ReLU(), torch.nn.Linear(12, 4))
+    for fn, scale_shape in ((Q.quantize_pytorch_model_per_channel_symmetric, (12, 1)),
+                            (Q.quantize_pytorch_model_per_tensor_symmetric, (1,))):
+        qm = fn(lin)
+        qw = qm[0].weight()
+        assert Q.extract_q_scale(qw).shape == scale_shape
+        assert (qw.dequantize() - lin[0].weight).abs().max().item() < 0.01
+        sd = Q.convert_qint8_to_int8_state_dict(qm.state_dict())
+        assert set(sd) == {"0.weight", "0.scale", "0.bias", "2.weight", "2.scale", "2.bias"}
+        assert sd["0.weight"].dtype == torch.int8 and sd["0.scale"].shape == scale_shape
+        deq = sd["0.weight"].float() * sd["0.scale"]
+        assert (deq - lin[0].weight).abs().max().item() < 0.01
