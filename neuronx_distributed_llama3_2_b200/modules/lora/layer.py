@@ -50,6 +50,39 @@ class LoraLayer:
     def get_delta_weight(self) -> torch.Tensor:
         raise NotImplementedError
 
+    # -- reference method names (``layer.py:55-110``) -----------------------------------------------------------------
+    def _adapter_pairs(self):
+        """(A, B, is_embedding) weight pairs of this wrapper; TP wrappers with several B matrices override."""
+        if hasattr(self, "lora_embedding_A"):
+            return [(self.lora_embedding_A, self.lora_embedding_B, True)]
+        return [(self.lora_A.weight, self.lora_B.weight, False)]
+
+    def init_lora_parameters(self, init_lora_weights=None) -> None:
+        """(Re-)initialise the adapter: ``"default"`` = Kaiming-uniform A, zero B; ``"gaussian"`` = N(0, 1/r) A, zero B
+        (embeddings: zero A, N(0, 1) B).  ``None`` keeps the mode of the stored configuration."""
+        if init_lora_weights is not None:
+            self.lora_config.init_lora_weights = init_lora_weights
+        for a, b, emb in self._adapter_pairs():
+            self.reset_lora_parameters(a, b, embedding=emb)
+
+    def update_layer(self, lora_config=None) -> None:
+        """Rebuild the adapter for a (new) configuration -- rank, alpha, dropout, init mode -- around the same base
+        layer.  A merged adapter is unmerged first so that the base weight is not left modified."""
+        if self.merged:
+            self.unmerge()
+        base = self.base_layer
+        for name in list(self._modules):
+            if name.startswith("lora_"):
+                del self._modules[name]
+        for name in list(self._parameters):
+            if name.startswith("lora_"):
+                del self._parameters[name]
+        type(self).__init__(self, base, lora_config or self.lora_config)
+
+    def transpose(self, weight: torch.Tensor) -> torch.Tensor:
+        """``weight.T`` when the base layer stores ``(in, out)`` (``fan_in_fan_out``, e.g. GPT-2 Conv1D)."""
+        return weight.T if getattr(self.lora_config, "fan_in_fan_out", False) else weight
+
     def merge(self) -> None:
         if self.merged:
             return

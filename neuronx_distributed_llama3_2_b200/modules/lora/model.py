@@ -206,6 +206,21 @@ class LoraModel(nn.Module):
         except AttributeError:
             return getattr(self.module, name)
 
+    @property
+    def dtype(self):
+        return getattr(self.module, "dtype", None) or next(self.module.parameters()).dtype
+
+    @property
+    def config(self):
+        return getattr(self.module, "config", None)
+
+    def print_model_info(self) -> None:
+        """Model, adapter configuration and trainable-parameter summary (reference ``:690-694``)."""
+        if getattr(self.lora_config, "lora_verbose", False):
+            logger.info("LoRA model: %s", self.module)
+            logger.info("LoRA configuration: %s", self.lora_config)
+        self.print_trainable_parameters()
+
     def get_nb_trainable_parameters(self) -> Tuple[int, int]:
         """``(trainable, all)`` parameter counts (reference ``:735-747``)."""
         t = sum(p.numel() for p in self.parameters() if p.requires_grad)

@@ -85,9 +85,19 @@ class LoraGQAQKVParallelLinear(nn.Module, LoraLayer):
         for b in (self.lora_B_q, self.lora_B_k, self.lora_B_v):
             self.reset_lora_parameters(self.lora_A.weight, b.weight)
 
+    def get_qkv(self, layer=None):
+        """The three B matrices (reference ``tp_layer.py:148-149`` reads them off a GQA-QKV adapter layer)."""
+        layer = layer or self
+        if hasattr(layer, "lora_B_q"):
+            return layer.lora_B_q.weight, layer.lora_B_k.weight, layer.lora_B_v.weight
+        return layer.weight_q, layer.weight_k, layer.weight_v
+
+    def _adapter_pairs(self):
+        return [(self.lora_A.weight, b, False) for b in self.get_qkv()]
+
     def get_delta_weight(self):
         a = self.lora_A.weight.float()
-        return tuple((b.weight.float() @ a) * self.scaling for b in (self.lora_B_q, self.lora_B_k, self.lora_B_v))
+        return tuple((b.float() @ a) * self.scaling for b in self.get_qkv())
 
     def merge(self) -> None:
         if self.merged:

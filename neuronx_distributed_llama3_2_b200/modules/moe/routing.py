@@ -36,6 +36,12 @@ class RouterBase(torch.nn.Module, ABC):
         aff = torch.sigmoid(x) if self.act_fn == "sigmoid" else F.softmax(x, dim=1)
         return aff
 
+    def get_router_logits_and_expert_affinities(self, hidden_states: torch.Tensor):
+        """``(router_logits (T, E), expert_affinities (T, E) in the dtype of hidden_states)`` -- the activation runs in
+        fp32 (the reference upcasts to fp64 only to dodge XLA's auto-downcast; ``routing.py:50-67``)."""
+        router_logits = self.get_router_logits(hidden_states)
+        return router_logits, self.apply_activation_fn(router_logits).to(hidden_states.dtype)
+
     @abstractmethod
     def forward(self, hidden_states):
         ...

@@ -149,6 +149,11 @@ class ParallelEmbedding(torch.nn.Module):
         self.weight = Parameter(torch.empty(*shape, device=device, dtype=dtype))
         self.init_weight_cpu_or_device()
 
+    def init_weight_cpu(self) -> None:
+        """Master-weight initialisation on the CPU (reference ``layers.py:207-213``)."""
+        _initialize_parameter_cpu(self.weight, self.weight_partition_dim, self.init_method, param_dtype=self.weight.dtype,
+                                  stride=self.stride)
+
     def init_weight_cpu_or_device(self):
         w = self.weight
         if w.device.type == "meta":
@@ -373,6 +378,39 @@ def linear_with_async_allreduce(input: torch.Tensor, weight: torch.Tensor, bias:
 # ---------------------------------------------------------------------------
 
 class BaseParallelLinear(torch.nn.Module):
+    """Template methods of the reference (``layers.py:420-457``): ``set_weight_and_bias_config`` decides shapes and the
+    partition dim, ``initialize_weight_and_bias`` creates and initialises the parameters on ``self.device`` (meta: only
+    the TP attributes; cpu: master-weight slice, ``init_weight_cpu``; cuda: direct init under the TP RNG tracker).
+    Quantized / LoRA / expert-fused layers override the first and reuse the second."""
+
+    def set_weight_and_bias_config(self) -> None:
+        raise NotImplementedError
+
+    def _bias_tp_attrs(self, bias: torch.Tensor) -> None:
+        """Subclass hook: parallel attributes of the freshly created bias."""
+
+    def init_weight_cpu(self) -> None:
+        self.master_weight = _initialize_parameter_cpu(self.weight, self.weight_partition_dim, self.init_method,
+                                                       param_dtype=self.weight.dtype, stride=self.stride,
+                                                       return_master_param=self.keep_master_weight)
+
+    def initialize_weight_and_bias(self) -> None:
+        self.set_weight_and_bias_config()
+        self.weight = Parameter(torch.empty(*self.weight_shape, dtype=self.dtype, device=self.device))
+        self.device = self.weight.device
+        self.master_weight = None
+        if self.device.type == "meta":
+            set_tensor_model_parallel_attributes(self.weight, True, self.weight_partition_dim, self.stride)
+        elif self.device.type == "cpu":
+            self.init_weight_cpu()
+        else:
+            _initialize_affine_weight(self.weight, self.init_method, self.weight_partition_dim, self.stride)
+        if self.bias_shape is not None:
+            self.bias = Parameter(torch.zeros(*self.bias_shape, dtype=self.dtype, device=self.device))
+            self._bias_tp_attrs(self.bias)
+        else:
+            self.register_parameter("bias", None)
+
     def _init_weight(self, weight: torch.Tensor, partition_dim: int):
         if weight.device.type == "meta":
             set_tensor_model_parallel_attributes(weight, True, partition_dim, self.stride)
@@ -416,16 +454,18 @@ class ColumnParallelLinear(BaseParallelLinear):
         if self.sequence_parallel_enabled and world <= 1:
             self.sequence_parallel_enabled = False
         self.dtype = dtype
-        self.use_bias = bias
+        self.device = device
+        self.use_bias = self.add_bias = bias
+        self.initialize_weight_and_bias()
+
+    def set_weight_and_bias_config(self) -> None:
+        # F.linear computes X A^T + b: the weight is stored transposed, [out / tp, in]
+        self.weight_shape = (self.output_size_per_partition, self.input_size)
         self.weight_partition_dim = 0
-        self.weight = Parameter(torch.empty(self.output_size_per_partition, self.input_size, dtype=dtype,
-                                            device=device))
-        self.master_weight = self._init_weight(self.weight, self.weight_partition_dim)
-        if bias:
-            self.bias = Parameter(torch.zeros(self.output_size_per_partition, dtype=dtype, device=device))
-            set_tensor_model_parallel_attributes(self.bias, True, 0, stride=stride)
-        else:
-            self.register_parameter("bias", None)
+        self.bias_shape = (self.output_size_per_partition,) if self.add_bias else None
+
+    def _bias_tp_attrs(self, bias: torch.Tensor) -> None:
+        set_tensor_model_parallel_attributes(bias, True, 0, stride=self.stride)
 
     def forward(self, input: torch.Tensor):
         if self.pad and self.training:
@@ -493,16 +533,18 @@ class RowParallelLinear(BaseParallelLinear):
         if self.sequence_parallel_enabled and world <= 1:
             self.sequence_parallel_enabled = False
         self.dtype = dtype
-        self.use_bias = bias
+        self.device = device
+        self.use_bias = self.add_bias = bias
+        self.initialize_weight_and_bias()
+
+    def set_weight_and_bias_config(self) -> None:
+        self.weight_shape = (self.output_size, self.input_size_per_partition)
         self.weight_partition_dim = 1
-        self.weight = Parameter(torch.empty(self.output_size, self.input_size_per_partition, dtype=dtype,
-                                            device=device))
-        self.master_weight = self._init_weight(self.weight, self.weight_partition_dim)
-        if bias:
-            self.bias = Parameter(torch.zeros(self.output_size, dtype=dtype, device=device))
-            setattr(self.bias, "sequence_parallel_enabled", self.sequence_parallel_enabled)
-        else:
-            self.register_parameter("bias", None)
+        self.bias_shape = (self.output_size,) if self.add_bias else None
+
+    def _bias_tp_attrs(self, bias: torch.Tensor) -> None:
+        # the bias is replicated; under SP every rank adds it to its sequence shard only -> gradient needs the TP sum
+        setattr(bias, "sequence_parallel_enabled", self.sequence_parallel_enabled)
 
     def forward(self, input_: torch.Tensor):
         if self.pad and self.training:

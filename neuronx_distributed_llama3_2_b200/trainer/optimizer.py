@@ -18,14 +18,32 @@ class NxDOptimizer(torch.optim.Optimizer):
         self.optimizer = optimizer
         self.nxd_config = nxd_config
         self._grad_norm = None
-        self.param_groups = optimizer.param_groups
-        self.defaults = optimizer.defaults
         self._optimizer_step_pre_hooks = getattr(optimizer, "_optimizer_step_pre_hooks", {})
         self._optimizer_step_post_hooks = getattr(optimizer, "_optimizer_step_post_hooks", {})
 
     @property
     def state(self):
         return self.optimizer.state
+
+    # param_groups / defaults are the inner optimizer's objects: LR schedulers that assign a new list keep working
+    @property
+    def param_groups(self):
+        return self.optimizer.param_groups
+
+    @param_groups.setter
+    def param_groups(self, param_groups):
+        self.optimizer.param_groups = param_groups
+
+    @property
+    def defaults(self):
+        return self.optimizer.defaults
+
+    @defaults.setter
+    def defaults(self, defaults):
+        self.optimizer.defaults = defaults
+
+    def add_param_group(self, param_group):
+        self.optimizer.add_param_group(param_group)
 
     @property
     def params(self):
@@ -89,6 +107,15 @@ class NxDOptimizer(torch.optim.Optimizer):
 
     def load_state_dict(self, state_dict):
         return self.optimizer.load_state_dict(state_dict)
+
+    # deprecated per-rank sharded save / load of the ZeRO-1 state (reference ``:141-154``; use nxd.save_checkpoint)
+    def save_state_dict(self, output_dir: str, num_workers_per_step: int = 8) -> None:
+        assert self.zero1, "save_state_dict needs optimizer_config['zero_one_enabled']"
+        self.optimizer.save_sharded_state_dict(output_dir, num_workers_per_step)
+
+    def load_state_dict_from(self, output_dir: str, num_workers_per_step: int = 8) -> None:
+        assert self.zero1, "load_state_dict_from needs optimizer_config['zero_one_enabled']"
+        self.optimizer.load_sharded_state_dict(output_dir, num_workers_per_step)
 
     def __getattr__(self, name):
         return getattr(self.__dict__["optimizer"], name)

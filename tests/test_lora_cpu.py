@@ -125,3 +125,26 @@ def test_lora_model_helpers_base_checkpoint_keys_config_and_two_step_load():
         assert "lora_config" in sd
         m2.load_lora_adapter()                       # step 2: apply the adapter weights
         torch.testing.assert_close(m2(ids), want, atol=1e-6, rtol=1e-6)
+
+
+def test_lora_layer_update_init_and_model_properties():
+    torch.manual_seed(0)
+    base = _Tiny()
+    cfg = LoraConfig(enable_lora=True, lora_rank=4, lora_alpha=8, target_modules=["q_proj"])
+    model = get_lora_model(base, cfg)
+    layer = base.q_proj
+    ids = torch.randint(0, 20, (2, 3))
+    ref = model(ids)
+    with torch.no_grad():
+        layer.lora_B.weight.normal_()
+    assert not torch.allclose(model(ids), ref)
+    layer.init_lora_parameters("gaussian")                   # B back to zero -> output back to the base model
+    torch.testing.assert_close(model(ids), ref)
+    assert float(layer.lora_A.weight.std()) < 0.5            # N(0, 1/r)
+    layer.merge()
+    layer.update_layer(LoraConfig(enable_lora=True, lora_rank=2, lora_alpha=2, target_modules=["q_proj"]))
+    assert layer.lora_A.weight.shape == (2, 16) and not layer.merged and layer.scaling == 1.0
+    torch.testing.assert_close(model(ids), ref)              # unmerged before the rebuild: base weight intact
+    assert torch.equal(layer.transpose(layer.lora_A.weight), layer.lora_A.weight)
+    assert model.dtype == torch.float32 and model.config is None
+    model.print_model_info()
