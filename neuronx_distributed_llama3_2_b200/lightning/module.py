@@ -44,6 +44,35 @@ class NeuronLTModule(ModuleBase):
     def forward(self, *a, **kw):
         return self.model(*a, **kw)
 
+    # -- Lightning hooks the reference overrides (``module.py:88-140``) ----------------------------------------------------
+    def configure_gradient_clipping(self, *args, **kwargs) -> None:
+        """Clipping happens inside ``NxDOptimizer`` / the ZeRO-1 step (it needs the norm over TP, PP and the shards):
+        Lightning's own clipping is switched off."""
+
+    def clip_gradients(self, *args, **kwargs) -> None:
+        """See ``configure_gradient_clipping``."""
+
+    def on_train_batch_end(self, *args, **kwargs) -> None:
+        """User hook."""
+
+    def named_parameters(self, *args, **kwargs):
+        if self.model is None:
+            return iter(())
+        return self.model.named_parameters(*args, **kwargs)
+
+    def get_param_groups_by_weight_decay(self, weight_decay: float = 0.01):
+        """Two optimizer groups: decayed weights, and biases / norm weights without decay.  Under pipeline parallelism
+        only the parameters of the local stages are listed (ZeRO-1 takes its device from the first one)."""
+        m = self.model
+        inner = getattr(m, "module", m)
+        if hasattr(inner, "local_named_parameters") and getattr(inner, "partitioned", True) and getattr(m, "pp_enabled", False):
+            named = list(inner.local_named_parameters())
+        else:
+            named = list(m.named_parameters())
+        no_decay = ("bias", "LayerNorm", "layernorm", "norm.weight")
+        return [{"params": [p for n, p in named if not any(k in n for k in no_decay)], "weight_decay": weight_decay},
+                {"params": [p for n, p in named if any(k in n for k in no_decay)], "weight_decay": 0.0}]
+
     def training_step(self, batch, batch_idx: int = 0):
         """Manual optimisation: backward every micro-step (inside ``run_train``), optimizer step every
         ``grad_accum_steps`` micro-steps."""

@@ -59,6 +59,19 @@ class NeuronXLAStrategy(StrategyBase):
             return type(batch)(v.to(dev, non_blocking=True) if isinstance(v, torch.Tensor) else v for v in batch)
         return batch.to(dev, non_blocking=True) if isinstance(batch, torch.Tensor) else batch
 
+    def broadcast(self, obj, src: int = 0):
+        """Every rank builds identical python objects from identical configuration (reference ``strategy.py:79-80``)."""
+        return obj
+
+    def model_to_device(self) -> None:
+        """``initialize_parallel_model`` already placed the shards on this rank's GPU (reference ``:124-126``)."""
+
+    def process_dataloader(self, dataloader):
+        """The reference wraps loaders in an XLA device loader unless PP keeps batches on the host (``:178-196``); here
+        ``batch_to_device`` issues the non-blocking H2D copy (and leaves batches on the host under PP, where the
+        pipeline engine moves each micro-batch itself), so loaders pass through unchanged."""
+        return getattr(dataloader, "_loader", dataloader) if self.pipeline_parallel_size > 1 else dataloader
+
     def reduce(self, tensor, group=None, reduce_op="mean"):
         if not dist.is_initialized():
             return tensor

@@ -213,6 +213,149 @@ class CheckpointConverterBase:
             merged_stages.update(self.merge_tp(shards))
         return self.nxd_full_to_hf(merged_stages)
 
+    # -- reference method surface (``scripts/checkpoint_converter.py:22-637``): small overridable steps -----------------
+    def get_partition_dim(self, name: str) -> Optional[int]:
+        """Dimension a parameter is sharded on over TP, ``None`` for replicated ones (override to add layer types)."""
+        return self._partition_dim(name)
+
+    def get_hf_to_nxd_model_keys(self, qkv_linear: bool = True, is_gqa: bool = True) -> Dict[str, str]:
+        """HF sub-key -> framework sub-key (reference ``:49-69``)."""
+        keys = {"mlp.gate_proj.weight": "mlp.gate_up_proj.weight", "mlp.up_proj.weight": "mlp.gate_up_proj.weight"}
+        if qkv_linear:
+            tgt = "qkv_proj.weight_qkv" if self.fuse_qkv else None
+            for n in "qkv":
+                keys[f"self_attn.{n}_proj.weight"] = f"self_attn.{tgt or 'qkv_proj.weight_' + n}"
+        return keys
+
+    def get_fused_qkv_key(self, prefix: str = "") -> str:
+        return prefix + "self_attn.qkv_proj.weight_qkv"
+
+    @staticmethod
+    def is_qkv_weight(name: str) -> bool:
+        return bool(re.search(r"self_attn\.(q_proj|k_proj|v_proj|qkv_proj)\.", name))
+
+    @staticmethod
+    def get_weight_key(prefix: str, name: str) -> str:
+        return f"{prefix}{name}.weight"
+
+    def coalesce_qkv(self, state_dict: Dict[str, torch.Tensor], config: Optional[dict] = None, tp_degree: Optional[int] = None
+                     ) -> Dict[str, torch.Tensor]:
+        """Fuse every layer's ``q/k/v_proj.weight`` into ``qkv_proj.weight_qkv`` in place (reference ``:78-93``)."""
+        for i in range(self.L):
+            p = f"model.layers.{i}.self_attn."
+            if p + "q_proj.weight" in state_dict:
+                parts = [state_dict.pop(p + f"{n}_proj.weight") for n in "qkv"]
+                state_dict[p + "qkv_proj.weight_qkv"] = torch.cat(parts, dim=0)
+        return state_dict
+
+    def convert_partial_state_to_fused_qkv(self, partial: Dict[str, torch.Tensor]) -> Dict[str, torch.Tensor]:
+        """One TP shard with separate ``weight_q / weight_k / weight_v`` -> fused ``weight_qkv``."""
+        for k in [k for k in partial if k.endswith("qkv_proj.weight_q")]:
+            base = k[: -len("weight_q")]
+            partial[base + "weight_qkv"] = torch.cat([partial.pop(base + "weight_q"), partial.pop(base + "weight_k"),
+                                                      partial.pop(base + "weight_v")], dim=0)
+        return partial
+
+    def convert_partial_state_to_non_fused_qkv(self, partial: Dict[str, torch.Tensor]) -> Dict[str, torch.Tensor]:
+        q_sz = self.nq * self.D // self.tp
+        kv_sz = self.nkv * self.D * self.m // self.tp
+        for k in [k for k in partial if k.endswith("qkv_proj.weight_qkv")]:
+            base = k[: -len("weight_qkv")]
+            q, k_, v_ = torch.split(partial.pop(k), [q_sz, kv_sz, kv_sz], dim=0)
+            partial[base + "weight_q"], partial[base + "weight_k"], partial[base + "weight_v"] = q, k_, v_
+        return partial
+
+    def pre_process_full_state_before_tp_conversion(self, state_dict: Dict[str, torch.Tensor], args=None):
+        """Hook: edit the full (HF-named) state before it is renamed and sharded.  Default: nothing."""
+        return state_dict
+
+    def post_process_full_state_after_tp_conversion(self, state_dict: Dict[str, torch.Tensor], args=None):
+        """Hook: edit the merged full (HF-named) state before it is written.  Default: nothing."""
+        return state_dict
+
+    @staticmethod
+    def find_size(obj) -> int:
+        """Bytes held by the tensors inside a (nested) state."""
+        if isinstance(obj, torch.Tensor):
+            return obj.numel() * obj.element_size()
+        if isinstance(obj, dict):
+            return sum(CheckpointConverterBase.find_size(v) for v in obj.values())
+        if isinstance(obj, (list, tuple)):
+            return sum(CheckpointConverterBase.find_size(v) for v in obj)
+        return 0
+
+    @staticmethod
+    def prune_state(state: Dict[str, Any]) -> Dict[str, Any]:
+        """Drop everything that is not part of the model state: trainer checkpoints keep it under ``"model"``."""
+        return state["model"] if isinstance(state, dict) and "model" in state and isinstance(state["model"], dict) else state
+
+    def get_input_filename(self, args, tp: int, pp: int, ep: Optional[int] = None, xser: Optional[bool] = None) -> str:
+        return self.shard_file(args.input_dir, tp, pp, ep)
+
+    def get_output_filename(self, args, tp: int, pp: int, ep: Optional[int] = None, xser: Optional[bool] = None) -> str:
+        return self.shard_file(args.output_dir, tp, pp, ep)
+
+    def load_partial_xser(self, args, tp: int, pp: int, ep: Optional[int] = None) -> Dict[str, Any]:
+        return self.prune_state(xser.load(self.get_input_filename(args, tp, pp, ep, True)))
+
+    def load_partial_no_xser(self, args, tp: int, pp: int, ep: Optional[int] = None) -> Dict[str, Any]:
+        return self.prune_state(torch.load(self.get_input_filename(args, tp, pp, ep, False), map_location="cpu",
+                                           weights_only=False))
+
+    def save_partial_xser(self, args, state: Dict[str, Any], tp: int, pp: int, ep: Optional[int] = None) -> None:
+        path = self.get_output_filename(args, tp, pp, ep, True)
+        os.makedirs(os.path.dirname(path), exist_ok=True)
+        xser.save(state, path)
+
+    def save_partial_no_xser(self, args, state: Dict[str, Any], tp: int, pp: int, ep: Optional[int] = None) -> None:
+        path = self.get_output_filename(args, tp, pp, ep, False)
+        os.makedirs(os.path.dirname(path), exist_ok=True)
+        torch.save(state, path)
+
+    def load_full_state(self, args) -> Dict[str, torch.Tensor]:
+        """A full HF-style checkpoint: a directory (safetensors / bin, sharded or not) or a single ``torch.save`` file."""
+        path = args.input_dir
+        if os.path.isdir(path):
+            from ..inference.checkpoint import load_state_dict
+
+            try:
+                return load_state_dict(path)
+            except FileNotFoundError:
+                state: Dict[str, Any] = {}
+                for f in sorted(os.listdir(path)):
+                    if f.endswith(".safetensors"):
+                        from safetensors.torch import load_file
+
+                        state.update(load_file(os.path.join(path, f)))
+                    elif f.endswith((".bin", ".pt")):
+                        state.update(torch.load(os.path.join(path, f), map_location="cpu", weights_only=False))
+                return state
+        return self.prune_state(torch.load(path, map_location="cpu", weights_only=False))
+
+    def save_full(self, args, full_state: Dict[str, torch.Tensor]) -> None:
+        os.makedirs(args.output_dir, exist_ok=True)
+        torch.save(full_state, os.path.join(args.output_dir, "checkpoint.pt"))
+
+    def convert_full_state_to_tp(self, args) -> None:
+        state = self.pre_process_full_state_before_tp_conversion(self.load_full_state(args), args)
+        self.convert_from_full_state(state, args.output_dir, use_xser=getattr(args, "save_xser", False))
+
+    def merge_tp_checkpoints(self, args) -> Dict[str, torch.Tensor]:
+        full = self.convert_to_full_state(args.input_dir, load_xser=getattr(args, "load_xser", False) or None)
+        return self.post_process_full_state_after_tp_conversion(full, args)
+
+    def _all_ranks(self):
+        return [(t, s) for t in range(self.tp) for s in range(self.pp)]
+
+    def convert_from_xser(self, args) -> None:
+        """Every ``(tp, pp)`` shard: tensor-per-file (xser) layout -> one ``torch.save`` file (reference ``:627-631``)."""
+        for t, s in self._all_ranks():
+            self.save_partial_no_xser(args, self.load_partial_xser(args, t, s), t, s)
+
+    def convert_to_xser(self, args) -> None:
+        for t, s in self._all_ranks():
+            self.save_partial_xser(args, self.load_partial_no_xser(args, t, s), t, s)
+
     # -- CLI -------------------------------------------------------------------------------------------------------
     @staticmethod
     def get_arg_parser() -> argparse.ArgumentParser:
@@ -228,6 +371,8 @@ class CheckpointConverterBase:
         ap.add_argument("--convert_to_full_state", action="store_true")
         ap.add_argument("--load_xser", action="store_true")
         ap.add_argument("--save_xser", action="store_true")
+        ap.add_argument("--convert_from_xser", action="store_true", help="sharded xser -> sharded torch.save")
+        ap.add_argument("--convert_to_xser", action="store_true", help="sharded torch.save -> sharded xser")
         return ap
 
     @classmethod
@@ -239,25 +384,15 @@ class CheckpointConverterBase:
                    cfg.get("head_dim", cfg["hidden_size"] // heads), a.tp_size, a.pp_size, a.kv_size_multiplier,
                    tie_word_embeddings=cfg.get("tie_word_embeddings", False))
         if a.convert_from_full_state:
-            path = a.input_dir
-            if os.path.isdir(path):
-                from safetensors.torch import load_file
-
-                state: Dict[str, Any] = {}
-                for f in sorted(os.listdir(path)):
-                    if f.endswith(".safetensors"):
-                        state.update(load_file(os.path.join(path, f)))
-                    elif f.endswith(".bin") or f.endswith(".pt"):
-                        state.update(torch.load(os.path.join(path, f), map_location="cpu", weights_only=False))
-            else:
-                state = torch.load(path, map_location="cpu", weights_only=False)
-            conv.convert_from_full_state(state, a.output_dir, use_xser=a.save_xser)
+            conv.convert_full_state_to_tp(a)
         elif a.convert_to_full_state:
-            full = conv.convert_to_full_state(a.input_dir, load_xser=a.load_xser or None)
-            os.makedirs(a.output_dir, exist_ok=True)
-            torch.save(full, os.path.join(a.output_dir, "checkpoint.pt"))
+            conv.save_full(a, conv.merge_tp_checkpoints(a))
+        elif a.convert_from_xser:
+            conv.convert_from_xser(a)
+        elif a.convert_to_xser:
+            conv.convert_to_xser(a)
         else:
-            raise SystemExit("pass --convert_from_full_state or --convert_to_full_state")
+            raise SystemExit("pass --convert_from_full_state, --convert_to_full_state, --convert_from_xser or --convert_to_xser")
 
 
 if __name__ == "__main__":

@@ -113,3 +113,50 @@ def test_converted_shards_load_into_parallel_model():
             @ hf[p + "mlp.down_proj.weight"].t()
     ref = rms(h, hf["model.norm.weight"]) @ hf["model.embed_tokens.weight"].t()
     torch.testing.assert_close(logits, ref, atol=2e-4, rtol=1e-3)
+
+
+def test_cli_paths_hooks_and_xser_conversion(tmp_path):
+    """The reference-named steps: full -> sharded through the CLI entry point with a subclass hook, sharded torch.save ->
+    xser -> torch.save, and merge back to the original full state."""
+    import json
+
+    hf = _hf_state(tied=False)
+    src = tmp_path / "hf"
+    os.makedirs(src)
+    torch.save(hf, src / "pytorch_model.bin")
+    cfg = tmp_path / "config.json"
+    cfg.write_text(json.dumps({"num_hidden_layers": 4, "num_attention_heads": 8, "num_key_value_heads": 2,
+                               "hidden_size": 64, "head_dim": 8, "tie_word_embeddings": False}))
+    seen = {}
+
+    class Conv(CheckpointConverterBase):
+        def pre_process_full_state_before_tp_conversion(self, state_dict, args=None):
+            seen["pre"] = len(state_dict)
+            return state_dict
+
+        def post_process_full_state_after_tp_conversion(self, state_dict, args=None):
+            seen["post"] = len(state_dict)
+            return state_dict
+
+    common = ["--config", str(cfg), "--tp_size", "2", "--pp_size", "1"]
+    Conv.run(["--input_dir", str(src), "--output_dir", str(tmp_path / "sharded"), "--convert_from_full_state"] + common)
+    assert seen["pre"] == len(hf)
+    Conv.run(["--input_dir", str(tmp_path / "sharded"), "--output_dir", str(tmp_path / "xser"), "--convert_to_xser"] + common)
+    assert os.path.isdir(tmp_path / "xser" / "model" / "dp_rank_00_tp_rank_01_pp_rank_00.pt.tensors")
+    Conv.run(["--input_dir", str(tmp_path / "xser"), "--output_dir", str(tmp_path / "plain"), "--convert_from_xser"] + common)
+    Conv.run(["--input_dir", str(tmp_path / "plain"), "--output_dir", str(tmp_path / "full"), "--convert_to_full_state"]
+             + common)
+    assert seen["post"] == len(hf)
+    back = torch.load(tmp_path / "full" / "checkpoint.pt", weights_only=False)
+    assert set(back) == set(hf) and all(torch.equal(back[k], hf[k]) for k in hf)
+    conv = Conv(4, 8, 2, 8, tp_size=2)
+    assert conv.get_partition_dim("model.layers.0.mlp.down_proj.weight") == 1 and conv.get_partition_dim("model.norm.weight") is None
+    assert conv.is_qkv_weight("model.layers.1.self_attn.k_proj.weight") and not conv.is_qkv_weight("model.norm.weight")
+    fused = conv.coalesce_qkv(dict(hf))
+    assert fused[conv.get_fused_qkv_key("model.layers.0.")].shape == (8 * 8 + 2 * 2 * 8, 64)
+    shard = torch.load(tmp_path / "plain" / "model" / "dp_rank_00_tp_rank_00_pp_rank_00.pt", weights_only=False)
+    split = conv.convert_partial_state_to_non_fused_qkv(dict(shard))
+    assert split["model.layers.0.self_attn.qkv_proj.weight_q"].shape[0] == 32
+    again = conv.convert_partial_state_to_fused_qkv(split)
+    assert torch.equal(again["model.layers.0.self_attn.qkv_proj.weight_qkv"], shard["model.layers.0.self_attn.qkv_proj.weight_qkv"])
+    assert conv.find_size({"a": torch.zeros(4, 4), "b": [torch.zeros(2, dtype=torch.bfloat16)]}) == 68
