@@ -575,6 +575,112 @@ class NxDPPModel(nn.Module):
     def get_model_layer(self, chunk: int = 0) -> nn.Module:
         return self.stage_modules[self._stage_id(chunk)]
 
+    # -- reference method names (``pipeline/model.py``) ----------------------------------------------------------------------
+    def get_model_layers(self, module: Optional[nn.Module] = None, layer_cls: Optional[type] = None) -> List[nn.Module]:
+        """Transformer layers (instances of ``transformer_layer_cls``) inside ``module`` -- by default the local pipeline
+        stages, in execution order."""
+        cls = layer_cls or self.transformer_layer_cls
+        roots = [module] if module is not None else (list(self.local_stage_modules) if self.partitioned
+                                                     else [self.original_torch_module])
+        return [m for r in roots for m in r.modules() if cls is not None and isinstance(m, cls)]
+
+    def register_shared_weights(self) -> None:
+        """Tag tied weights that several stages use and build the group that keeps them in sync."""
+        self._mark_shared_weights()
+
+    def create_schedule(self) -> None:
+        self._create_schedules()
+
+    def get_current_stage(self, model_chunk_id: int = 0) -> int:
+        """Global stage index executed by this rank for ``model_chunk_id`` (interleaved schedule: several)."""
+        return self._stage_id(model_chunk_id)
+
+    def is_last_pp_rank_last_model_chunk(self, model_chunk_id: int = 0) -> bool:
+        return self._stage_id(model_chunk_id) == self.num_stages - 1
+
+    def get_batch_iterator(self, batch_kwargs: Dict[str, Any]):
+        """Micro-batches of a batch (dim 0 split in ``num_microbatches`` equal parts)."""
+        return iter(self._split_microbatches(batch_kwargs))
+
+    def clear_minibatch_state(self) -> None:
+        """Drop everything that belongs to the mini-batch that just ran (received activations, stage outputs kept for
+        the backward, gradients in flight, losses)."""
+        for name in ("microbatches", "losses", "eval_outputs"):
+            setattr(self, name, [])
+        for name in ("recv_values", "recv_tensors", "stage_outputs", "sent_tensors", "recv_grads"):
+            setattr(self, name, {})
+
+    def maybe_deallocate_output_tensor(self, tensor: torch.Tensor) -> None:
+        """After an activation has been sent to the next stage only its autograd node is needed: release the storage
+        (reference ``deallocate_pipeline_outputs``).  Views of other tensors are left alone."""
+        if self.deallocate_pipeline_outputs and isinstance(tensor, torch.Tensor) and tensor._base is None:
+            tensor.data = torch.empty((1,), device=tensor.device, dtype=tensor.dtype)
+
+    @staticmethod
+    def custom_backward(outputs: List[torch.Tensor], grad_outputs: List[Optional[torch.Tensor]]) -> None:
+        """Backward through stage outputs whose storage may have been released (the shapes of output and gradient no
+        longer match, which ``torch.autograd.backward`` checks): call the engine directly."""
+        pairs = [(o, g) for o, g in zip(outputs, grad_outputs) if isinstance(o, torch.Tensor) and o.requires_grad]
+        if not pairs:
+            return
+        outs, gs = zip(*pairs)
+        try:
+            torch.autograd.backward(outs, gs)
+        except RuntimeError:
+            from torch.autograd import Variable
+
+            Variable._execution_engine.run_backward(tuple(outs), tuple(gs), False, False, tuple(), True, True)
+
+    def translate_origin_state_dict_to_local_state_dict(self, state_dict: Dict[str, Any]) -> Dict[str, Any]:
+        """Original (un-partitioned) key names -> ``submod_k.*`` names of the local stages; keys of other stages are
+        dropped."""
+        local_prefixes = tuple(f"submod_{k}." for k in self.local_stage_ids)
+        out = OrderedDict()
+        for k, v in state_dict.items():
+            loc = self.original_name_to_local_name.get(k)
+            if loc is not None and loc.startswith(local_prefixes):
+                out[loc] = v
+        return out
+
+    def translate_local_state_dict_to_origin_state_dict(self, state_dict: Dict[str, Any]) -> Dict[str, Any]:
+        return OrderedDict((self.local_name_to_original_name.get(k, k), v) for k, v in state_dict.items())
+
+    def construct_state_dict_per_model_chunk(self, state_dict: Dict[str, Any], strict: bool = True) -> List[Dict[str, Any]]:
+        """One state dict per local model chunk (keys relative to the stage module), from original-name keys."""
+        chunks = []
+        for k in self.local_stage_ids:
+            part = {}
+            for n in self.stage_modules[k].state_dict().keys():
+                orig = self.local_name_to_original_name.get(f"submod_{k}.{n}", f"submod_{k}.{n}")
+                if orig in state_dict:
+                    part[n] = state_dict[orig]
+                elif strict:
+                    raise RuntimeError(f"missing key {orig} for pipeline stage {k}")
+            chunks.append(part)
+        return chunks
+
+    def move_model_to_device(self, device=None) -> None:
+        """Move the LOCAL stages to this rank's device (parameters of other stages were dropped at partition time)."""
+        device = device or (torch.device("cuda", torch.cuda.current_device()) if torch.cuda.is_available() else torch.device("cpu"))
+        if any(p.device.type == "meta" for p in self.local_stage_modules.parameters()):
+            self.maybe_materialize_local_module(device)
+        self.local_stage_modules.to(device)
+
+    def maybe_materialize_local_module(self, device=None) -> None:
+        """Materialise local stages that were built on the meta device (delayed initialisation)."""
+        from ..utils.model_utils import maybe_materalize_model
+
+        for m in self.local_stage_modules:
+            maybe_materalize_model(m, device)
+
+    def perform_delayed_tracing_and_partition(self, args=None, kwargs=None) -> None:
+        """Trace + partition on first use when construction was asked to wait for real inputs (``trace_file_path`` /
+        delayed tracing of the reference; hard-disabled there, kept for API parity)."""
+        if self.traced_model is None:
+            self.trace(args=args, kwargs=kwargs, input_names=self.input_names)
+        if not self.partitioned:
+            self.partition()
+
     @property
     def config(self):
         return getattr(self.original_torch_module, "config", None)

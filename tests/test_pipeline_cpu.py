@@ -145,3 +145,23 @@ def test_debug_mode_partition_and_names():
     assert m.model.layers[0].mlp.down_proj.weight.numel() == 0
     with pytest.raises(RuntimeError):
         pp(torch.zeros(1))
+    # reference-named helpers
+    layers = pp.get_model_layers()
+    assert len(layers) == 2 and all(isinstance(l, LlamaDecoderLayer) for l in layers)
+    assert pp.get_current_stage(0) == 1 and not pp.is_last_pp_rank_last_model_chunk(0)
+    sd = pp.local_state_dict()
+    loc = pp.translate_origin_state_dict_to_local_state_dict(dict(sd, **{"model.layers.7.mlp.down_proj.weight": torch.zeros(1)}))
+    assert loc and all(k.startswith("submod_1.") for k in loc) and len(loc) == len(sd)
+    back = pp.translate_local_state_dict_to_origin_state_dict(loc)
+    assert set(back) == set(sd)
+    chunks = pp.construct_state_dict_per_model_chunk(sd)
+    assert len(chunks) == 1 and len(chunks[0]) == len(sd)
+    mbs = list(pp.get_batch_iterator({"input_ids": torch.zeros(4, 8, dtype=torch.long), "flag": True}))
+    assert len(mbs) == 2 and mbs[0]["input_ids"].shape == (2, 8) and mbs[1]["flag"] is True
+    pp.clear_minibatch_state()
+    assert pp.stage_outputs == {} and pp.losses == []
+    a = torch.randn(3, requires_grad=True)
+    out = a * 2
+    NxDPPModel.custom_backward([out], [torch.ones(3)])
+    assert torch.equal(a.grad, torch.full((3,), 2.0))
+    pp.move_model_to_device(torch.device("cpu"))
