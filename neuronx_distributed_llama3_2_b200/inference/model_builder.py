@@ -174,6 +174,23 @@ class NxDModel(torch.nn.Module):
         _, bucket = self.router(args)
         return bucket(*args)
 
+    def initialize_spmd_models(self, states=None, weights: Optional[Dict[str, torch.Tensor]] = None) -> None:
+        """Hand (already sharded) weights to every sub-model; ``states`` (KV caches) are owned by the modules here."""
+        if weights is not None:
+            self.initialize(weights)
+
+    def initialize_with_saved_weights(self, serialize_path: Optional[str] = None, rank: Optional[int] = None) -> None:
+        """Load this rank's ``tp{rank}_sharded_checkpoint.safetensors`` written by ``ModelBuilder.shard_checkpoint``
+        (the reference re-uses weights kept inside the saved TorchScript artefact)."""
+        path = serialize_path or getattr(self, "serialize_path", None)
+        if path is None:
+            raise ValueError("initialize_with_saved_weights needs the directory of the sharded checkpoint")
+        self.load_sharded_checkpoint(path, rank=rank)
+
+    def mock_initialization(self, mock: bool = True) -> None:
+        """Mark the weights as initialised without loading anything (random weights: shape / latency runs)."""
+        self.weights_initialized = bool(mock)
+
     def release_graphs(self) -> None:
         """Destroy the captured CUDA graphs (buckets fall back to eager execution).  Call this -- or drop the model --
         BEFORE ``torch.distributed.destroy_process_group()``: NCCL keeps a communicator alive while a CUDA graph that
@@ -215,24 +232,63 @@ class ModelBuilder:
         if have != tp:
             raise RuntimeError(f"ModelBuilder(tp_degree={tp}) but the process group has tp={have}: launch one process per "
                                "GPU (torchrun) and call initialize_model_parallel first")
-        buckets: Dict[str, Dict[str, _Bucket]] = {}
+        weights = self.checkpoint_loader() if (initialize_model_weights and self.checkpoint_loader is not None) else None
+        rank = ps.get_tensor_model_parallel_rank()
         modules: Dict[str, torch.nn.Module] = {}
-        weights = None
-        if initialize_model_weights and self.checkpoint_loader is not None:
-            full = self.checkpoint_loader()
-            weights = full
         # priority model first (kept for parity with the reference's compile order)
         order = sorted(self.model_collection, key=lambda k: self.model_collection[k]["priority_model_idx"] is None)
         for key in order:
-            entry = self.model_collection[key]
-            inst: BaseModelInstance = entry["instance"]
+            inst: BaseModelInstance = self.model_collection[key]["instance"]
             if inst.module is None:
                 inst.load_module()
-            module = inst.module
             if weights is not None:
-                shard = get_sharded_checkpoint(weights, module, ps.get_tensor_model_parallel_rank(), tp)
-                module.load_state_dict(shard, strict=False)
-            modules[key] = module
+                inst.module.load_state_dict(self.shard_weights(rank, self.model_collection[key], weights), strict=False)
+            modules[key] = inst.module
+        return self.build_nxd_model(modules, order)
+
+    # -- the build steps under the reference's names (``model_builder.py:263-451``) ---------------------------------------
+    def shard_weights(self, rank: int, model_container, checkpoint: Optional[Dict[str, Any]] = None) -> Dict[str, Any]:
+        """This rank's slice of the un-sharded checkpoint for one registered sub-model (preshard hooks, partition dim /
+        stride, fused-QKV aware)."""
+        inst = model_container["instance"] if isinstance(model_container, dict) else model_container.model_instance
+        checkpoint = checkpoint if checkpoint is not None else self.checkpoint_loader()
+        module = inst.module
+        if module is None:
+            with torch.device("meta"):
+                module = inst.module_cls()
+        return get_sharded_checkpoint(checkpoint, module, rank, self.tp_degree)
+
+    def build_state_initializer(self, modules: Optional[Dict[str, torch.nn.Module]] = None) -> "StateInitializer":
+        """Shapes / dtypes of the per-rank state (the KV cache) of the registered models, as a ``StateInitializer``."""
+        shapes, dtypes = {}, {}
+        for key, entry in self.model_collection.items():
+            m = (modules or {}).get(key) or entry["instance"].module
+            cache = getattr(m, "kv_cache", None)
+            if cache is not None and getattr(cache, "k", None):
+                for i, (k, v) in enumerate(zip(cache.k, cache.v)):          # one (K, V) pair per layer
+                    shapes[f"{key}.layers.{i}.kv_cache.k"], dtypes[f"{key}.layers.{i}.kv_cache.k"] = tuple(k.shape), k.dtype
+                    shapes[f"{key}.layers.{i}.kv_cache.v"], dtypes[f"{key}.layers.{i}.kv_cache.v"] = tuple(v.shape), v.dtype
+        return StateInitializer(shapes, dtypes)
+
+    def build_flattener_map(self) -> Dict[str, Callable]:
+        """Per sub-model: nested inputs -> flat tensor list (the reference builds torch_neuronx Flatteners)."""
+        def flatten(inputs):
+            out = []
+            for x in (inputs if isinstance(inputs, (list, tuple)) else [inputs]):
+                out.extend(flatten(x) if isinstance(x, (list, tuple)) else [x])
+            return out
+        return {key: flatten for key in self.model_collection}
+
+    def build_packer(self) -> Callable:
+        """Flat result list -> user structure; the sub-models here return one tensor (or a flat tuple) already."""
+        return lambda result: result[0] if isinstance(result, (list, tuple)) and len(result) == 1 else result
+
+    def build_nxd_model(self, modules: Dict[str, torch.nn.Module], order: Optional[List[str]] = None) -> NxDModel:
+        """Capture one executable per (key, bucket) over the loaded modules and assemble the shape-routed ``NxDModel``."""
+        buckets: Dict[str, Dict[str, _Bucket]] = {}
+        for key in (order or list(self.model_collection)):
+            entry = self.model_collection[key]
+            inst: BaseModelInstance = entry["instance"]
             buckets[key] = {}
             for rank_idx, ex in enumerate(entry["example_inputs"]):
                 mod, _aliases = inst.get(rank_idx)

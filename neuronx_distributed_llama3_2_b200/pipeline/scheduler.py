@@ -153,8 +153,13 @@ class Train1F1BSchedule(PipeSchedule):
 
     def __init__(self, num_microbatches: int, stages: int, stage_id: int):
         super().__init__(num_microbatches, stages, stage_id)
-        self.num_warmup_steps = min(stages - stage_id - 1, num_microbatches)
-        self.num_steady_state_microbatches = num_microbatches - self.num_warmup_steps
+        self.get_microbatche_schedule()
+
+    def get_microbatche_schedule(self) -> None:
+        """Phase sizes of this stage: warm-up forwards, steady 1F1B pairs, cool-down backwards (method name, typo
+        included, from the reference ``scheduler.py:179-184``)."""
+        self.num_warmup_steps = min(self.stages - self.stage_id - 1, self.num_microbatches)
+        self.num_steady_state_microbatches = self.num_microbatches - self.num_warmup_steps
         self.num_remaining_microbatches = self.num_warmup_steps
 
     def _op_sequence(self) -> List[Tuple[str, int]]:
@@ -214,13 +219,23 @@ class TrainInterleavedSchedule(PipeSchedule):
         self.fused_send_recv = fused_send_recv
         self.fused_fwd_bwd = fused_fwd_bwd
         self.use_odd_even_scheduler = use_odd_even_scheduler
-        total = num_microbatches * num_model_chunks
-        self.total_num_microbatches = total
-        if num_microbatches == stages:
+        self.get_step_schedule()
+
+    def get_step_schedule(self) -> None:
+        """Warm-up / steady / cool-down sizes in virtual micro-batches (reference ``scheduler.py:296-317``): all forwards
+        first when there are exactly as many micro-batches as stages, otherwise ``2 (stages - stage - 1)`` plus one round
+        per extra model chunk."""
+        total = self.num_microbatches * self.num_model_chunks
+        self.total_num_microbatches = self.num_microbatches_steps = total
+        if self.num_microbatches == self.stages:
             self.num_warmup_microbatches = total
         else:
-            self.num_warmup_microbatches = min((stages - stage_id - 1) * 2 + (num_model_chunks - 1) * stages, total)
+            self.num_warmup_microbatches = min((self.stages - self.stage_id - 1) * 2
+                                               + (self.num_model_chunks - 1) * self.stages, total)
         self.num_microbatches_remaining = total - self.num_warmup_microbatches
+        self.num_warmup_steps = self.num_warmup_microbatches
+        self.num_steady_state_steps = self.num_microbatches_remaining
+        self.num_remaining_steps = self.num_warmup_microbatches
 
     # -- index helpers (virtual micro-batch k -> (chunk, micro-batch)) ------------------------------------------
     def get_model_chunk_id(self, k: int, forward: bool) -> int:

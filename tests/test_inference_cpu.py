@@ -304,3 +304,40 @@ def test_model_wrapper_pads_splits_and_reorders():
         raise AssertionError("longer than the largest bucket must fail")
     except ValueError:
         pass
+
+
+def test_model_builder_named_steps():
+    cfg, train, _ = _models()
+    full_sd = {k: v.clone() for k, v in train.state_dict().items()}
+
+    def make():
+        m = LlamaInferenceModel(tiny_llama(sequence_parallel_enabled=False),
+                                InferenceConfig(batch_size=2, max_context_length=32, seq_len=64))
+        m.init_kv_cache(device=torch.device("cpu"))
+        return m
+
+    builder = ModelBuilder(tp_degree=1, checkpoint_loader=lambda: full_sd, use_cuda_graphs=False)
+    inst = BaseModelInstance(make)
+    ex = (torch.zeros(2, 16, dtype=torch.long), torch.zeros(2, 16, dtype=torch.long))
+    builder.add("context_encoding_model", inst, [ex], priority_model_idx=0)
+    shard = builder.shard_weights(0, builder.model_collection["context_encoding_model"])
+    assert set(shard) >= {"model.norm.weight", "lm_head.weight"}
+    inst.load_module()
+    inst.module.load_state_dict(shard, strict=False)
+    model = builder.build_nxd_model({"context_encoding_model": inst.module})
+    init = builder.build_state_initializer({"context_encoding_model": inst.module})
+    state = init()
+    assert any(k.endswith("kv_cache.k") for k in state) and all(v.abs().sum() == 0 for v in state.values())
+    assert builder.build_flattener_map()["context_encoding_model"]([ex[0], (ex[1],)]) == [ex[0], ex[1]]
+    assert builder.build_packer()([ex[0]]) is ex[0]
+    ids = torch.randint(1, cfg.vocab_size, (2, 16))
+    pos = torch.arange(16).unsqueeze(0).expand(2, 16)
+    assert torch.equal(model(ids, pos), _full_logits(train, ids)[:, -1].argmax(-1))
+    model.mock_initialization(True)
+    assert model.weights_initialized
+    with tempfile.TemporaryDirectory() as d:
+        builder.shard_checkpoint(d)
+        with torch.no_grad():
+            inst.module.model.norm.weight.zero_()
+        model.initialize_with_saved_weights(d, rank=0)
+    assert torch.equal(model(ids, pos), _full_logits(train, ids)[:, -1].argmax(-1))
