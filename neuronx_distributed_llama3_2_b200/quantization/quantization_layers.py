@@ -74,6 +74,13 @@ class QuantizedParallelLinearLayerStateDictAdaptor:
 
 
 class BaseQuantizeParallelLinear(torch.nn.Module):
+    # state-dict accessors every quantized layer offers (reference ``quantization_layers.py:60-250``)
+    get_weight_from_state_dict = staticmethod(QuantizedParallelLinearLayerStateDictAdaptor.get_weight_from_state_dict)
+    set_weight_to_state_dict = staticmethod(QuantizedParallelLinearLayerStateDictAdaptor.set_weight_to_state_dict)
+    get_bias_from_state_dict = staticmethod(QuantizedParallelLinearLayerStateDictAdaptor.get_bias_from_state_dict)
+    set_bias_to_state_dict = staticmethod(QuantizedParallelLinearLayerStateDictAdaptor.set_bias_to_state_dict)
+    get_scale_from_state_dict = staticmethod(QuantizedParallelLinearLayerStateDictAdaptor.get_scale_from_state_dict)
+
     def _setup_scale(self, weight_shape, partition_dim: int, quantization_type: QuantizationType,
                      per_channel_axis: Optional[int], device, expert_dims: int = 0) -> None:
         self.quantization_type = quantization_type

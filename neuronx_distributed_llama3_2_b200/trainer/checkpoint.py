@@ -153,6 +153,39 @@ class CheckpointIOState:
                 storage.remove_dir(t)
         _rendezvous("ckpt-prune")
 
+    # -- reference method names (``trainer/checkpoint.py:99-285``) ---------------------------------------------------
+    def add_dcp_save_task(self, state_dict: Any, dirname: str, aux_infos: Any = None) -> None:
+        """Queue a torch.distributed.checkpoint style save of a ZeRO-1 optimizer state: one file per rank below
+        ``dirname`` (written by ``optimizer/zero_dcp_utils.py`` when the queue is flushed)."""
+        from ..optimizer.zero_dcp_utils import _suffix
+
+        self._tasks.append((_to_cpu(state_dict), os.path.join(dirname, f"__{_suffix()}.distcp"), False))
+
+    def wait_save(self, async_remove: bool = False) -> None:
+        """Block until the queued writes of the current tag are on disk and its ``done`` marker is published."""
+        self.wait_all()
+
+    def submit_remove(self, tags: List[str]) -> None:
+        """Delete old checkpoint tags (``done`` marker first, then the directory), on the writer thread when async."""
+        storage = self._storage
+        if storage is None or _rank() != 0:
+            return
+
+        def _rm():
+            for t in tags:
+                storage.remove_file(os.path.join(t, "done"))
+                storage.remove_dir(t)
+
+        if self._async:
+            self._pending.append(self._executor.submit(_rm))
+        else:
+            _rm()
+
+    def wait_remove(self) -> None:
+        for f in self._pending:
+            f.result()
+        self._pending = []
+
     def wait_all(self) -> None:
         """Block until queued async writes are on disk, then publish ``done`` (collective)."""
         for f in self._pending:

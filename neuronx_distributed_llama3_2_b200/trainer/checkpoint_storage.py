@@ -12,7 +12,7 @@ import random
 import re
 import shutil
 import time
-from typing import Any, List, Optional
+from typing import Tuple, Any, List, Optional
 
 import torch
 
@@ -153,6 +153,41 @@ class S3CheckpointStorage(BaseCheckpointStorage):
 
             self._client = boto3.session.Session().client("s3")
         return self._client
+
+    # -- reference method names (``checkpoint_storage.py:219-555``) ---------------------------------------------------
+    @staticmethod
+    def parse_path(path: str) -> Tuple[str, str]:
+        """``s3://bucket/key/...`` -> ``(bucket, key)``."""
+        m = re.match(r"s3://([^/]+)/?(.*)", path)
+        if not m:
+            raise ValueError(f"not an s3 url: {path}")
+        return m.group(1), m.group(2)
+
+    def convert_path_to_key(self, path: str) -> str:
+        return self._k(path)
+
+    def get_client(self):
+        return self.client
+
+    def get_resource(self):
+        import boto3  # noqa: WPS433
+
+        return boto3.session.Session().resource("s3")
+
+    @staticmethod
+    def is_slow_down_error(exc: Exception) -> bool:
+        return S3CheckpointStorage._is_slow_down(exc)
+
+    def s3_action_with_retry(self, fn, *a, **kw):
+        return self._retry(fn, *a, **kw)
+
+    def upload_stream_to_file(self, stream, filename: str) -> None:
+        self._upload(stream.getvalue() if hasattr(stream, "getvalue") else stream.read(), self._k(filename))
+
+    def download_file_to_stream(self, filename: str, stream) -> None:
+        resp = self._retry(self.client.get_object, Bucket=self._bucket, Key=self._k(filename))
+        stream.write(resp["Body"].read())
+        stream.seek(0)
 
     def _k(self, name: str) -> str:
         return f"{self._base_key}/{name}".strip("/") if name else self._base_key

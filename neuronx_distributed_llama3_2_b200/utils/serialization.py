@@ -66,6 +66,39 @@ class SerializationManager:
 
         return walk(obj), tensors, metas
 
+    MAX_OBJECT_BYTES = 64 * 1024 * 1024
+
+    def catch_and_raise_for_large_object(self, obj: Any) -> None:
+        """The python structure around the tensors travels pickled through an object channel: refuse anything that is
+        large once the tensors are taken out (it is almost always a tensor hidden in an unsupported container)."""
+        import pickle
+
+        stub, _, _ = self.serialize(obj)
+        n = len(pickle.dumps(stub))
+        if n > self.MAX_OBJECT_BYTES:
+            raise ValueError(f"pipeline stage output serialises to {n} bytes of python objects (limit "
+                             f"{self.MAX_OBJECT_BYTES}): pass tensors in lists / tuples / dicts / namedtuples")
+
+    def extract_stubs(self, stub_obj: Any) -> List[Any]:
+        """The tensor placeholders of a serialised structure, in tensor-index order."""
+        found: List[_Stub] = []
+
+        def walk(x):
+            if isinstance(x, _Stub):
+                found.append(x)
+            elif isinstance(x, dict):
+                for v in x.values():
+                    walk(v)
+            elif isinstance(x, (list, tuple)):
+                for v in x:
+                    walk(v)
+            elif isinstance(x, slice):
+                for v in (x.start, x.stop, x.step):
+                    walk(v)
+
+        walk(stub_obj)
+        return sorted(found, key=lambda t: t.idx)
+
     def deserialize(self, stub_obj: Any, tensors: List[torch.Tensor]) -> Any:
         def walk(x):
             if isinstance(x, _Stub):
