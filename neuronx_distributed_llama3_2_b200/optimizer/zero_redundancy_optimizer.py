@@ -516,6 +516,18 @@ class NeuronEPZero1Optimizer(torch.optim.Optimizer):
         self._grad_norm = None
 
     @property
+    def sharding_groups(self):
+        """Rank meshes the two inner optimizers shard over: ``(data-parallel, expert-data-parallel)`` (reference
+        ``:204-214``)."""
+        if not (dist.is_initialized() and ps.model_parallel_is_initialized()):
+            return None
+        return ps.get_data_parallel_group(as_list=True), ps.get_expert_data_parallel_group(as_list=True)
+
+    @sharding_groups.setter
+    def sharding_groups(self, value) -> None:
+        """Accepted for compatibility with the base class, which assigns it; the groups come from ``parallel_state``."""
+
+    @property
     def grad_norm(self):
         return self._grad_norm
 
