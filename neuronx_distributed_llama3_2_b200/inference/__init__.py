@@ -3,7 +3,7 @@
 from .checkpoint_sharding import _mock_parallel_state, get_sharded_checkpoint, shard_children  # noqa: F401
 from .config import InferenceConfig  # noqa: F401
 from .kv_cache import KVCache  # noqa: F401
-from .model import KVCacheInferenceMixin, LlamaInferenceModel, MixtralInferenceModel  # noqa: F401
+from .model import DbrxInferenceModel, KVCacheInferenceMixin, LlamaInferenceModel, MixtralInferenceModel  # noqa: F401
 from .gqa import GQA, determine_sharding_strategy, get_shardable_head_counts  # noqa: F401
 from .autobucketing import generate_buckets  # noqa: F401
 from .checkpoint import load_state_dict, save_state_dict_safetensors  # noqa: F401

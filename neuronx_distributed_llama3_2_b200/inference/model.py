@@ -24,6 +24,7 @@ import torch
 import torch.nn as nn
 
 from ..models.llama import LlamaConfig, LlamaForCausalLM
+from ..models.dbrx import DbrxConfig, DbrxForCausalLM
 from ..models.mixtral import MixtralConfig, MixtralForCausalLM
 from ..ops import activation as act_ops
 from ..ops import attention as attn_ops
@@ -87,7 +88,7 @@ class KVCacheInferenceMixin:
             qkv = attn.qkv_proj(h, return_fused=True)
         else:
             qkv = torch.cat(attn.qkv_proj(h), dim=-1)
-        qkv = qkv.reshape(B * T, nq + 2 * nkv, D)
+        qkv = self._post_qkv(qkv.reshape(B * T, nq + 2 * nkv, D))
         cos, sin = self._rope(h.device)
         qkv = rope_ops.rope_inplace_(qkv.contiguous(), cos, sin, nq + nkv, positions=positions.reshape(-1))
         qkv = qkv.reshape(B, T, nq + 2 * nkv, D)
@@ -115,15 +116,22 @@ class KVCacheInferenceMixin:
             o = o.reshape(B, 1, nq * D)
         return attn.o_proj(o)
 
-    def _layer(self, i: int, layer, hidden, residual, positions, seq_ids, lengths, prefill):
-        eps = layer.input_layernorm.variance_epsilon
+    def _add_norm(self, norm, hidden: torch.Tensor, residual: Optional[torch.Tensor]):
+        """``(norm(hidden + residual), hidden + residual)`` -- RMSNorm through the fused add + norm kernel; model
+        families with another norm override this."""
+        eps = norm.variance_epsilon
         if residual is None:
-            residual = hidden
-            h = norm_ops.rms_norm(hidden, layer.input_layernorm.weight, eps)
-        else:
-            h, residual = norm_ops.fused_add_rms_norm(hidden, residual, layer.input_layernorm.weight, eps)
+            return norm_ops.rms_norm(hidden, norm.weight, eps), hidden
+        return norm_ops.fused_add_rms_norm(hidden, residual, norm.weight, eps)
+
+    def _post_qkv(self, qkv: torch.Tensor) -> torch.Tensor:
+        """Hook on the fused projection output ``[B*T, heads, D]`` before RoPE (DBRX clamps it)."""
+        return qkv
+
+    def _layer(self, i: int, layer, hidden, residual, positions, seq_ids, lengths, prefill):
+        h, residual = self._add_norm(layer.input_layernorm, hidden, residual)
         a = self._attention(i, layer.self_attn, h, positions, seq_ids, lengths, prefill)
-        h, residual = norm_ops.fused_add_rms_norm(a, residual, layer.post_attention_layernorm.weight, eps)
+        h, residual = self._add_norm(layer.post_attention_layernorm, a, residual)
         return self._mlp(layer, h), residual
 
     # -- graphs ----------------------------------------------------------------------------------------------------
@@ -154,9 +162,7 @@ class KVCacheInferenceMixin:
             hidden, residual = hidden[rows, idx.long()], residual[rows, idx.long()]
         else:
             hidden, residual = hidden[:, 0], residual[:, 0]
-        norm = self._final_norm()
-        hidden, _ = norm_ops.fused_add_rms_norm(hidden.contiguous(), residual.contiguous(), norm.weight,
-                                                norm.variance_epsilon)
+        hidden, _ = self._add_norm(self._final_norm(), hidden.contiguous(), residual.contiguous())
         logits = self.lm_head(hidden)                                   # [B, V/tp]
         logits = mappings.gather_from_tensor_model_parallel_region(logits)[:, : self.config.vocab_size]
         tokens = self.sampler.sample(logits.float() if logits.dtype not in (torch.float32, torch.bfloat16) else logits,
@@ -221,16 +227,8 @@ class LlamaInferenceModel(KVCacheInferenceMixin, LlamaForCausalLM):
         self._init_inference(inference_config)
 
 
-class MixtralInferenceModel(KVCacheInferenceMixin, MixtralForCausalLM):
-    """Mixtral-style MoE decoder with a KV cache (reference ``examples/inference/mixtral`` + ``modules/moe`` inference
-    paths): context encoding runs the capacity-free all-experts path, token generation loads only the selected experts
-    (``ExpertMLPs.forward_selective_loading``)."""
-
-    def __init__(self, config: MixtralConfig, inference_config: Optional[InferenceConfig] = None, device=None):
-        config.sequence_parallel_enabled = False
-        config.activation_checkpointing = False
-        MixtralForCausalLM.__init__(self, config, device=device)
-        self._init_inference(inference_config)
+class _MoEDecoderLayout:
+    """Where ``MixtralForCausalLM``-shaped models keep their pieces, and how their feed-forward runs at inference."""
 
     def _decoder_layers(self):
         return self.layers
@@ -246,3 +244,30 @@ class MixtralInferenceModel(KVCacheInferenceMixin, MixtralForCausalLM):
             return layer.mlp.down_proj(act_ops.swiglu(layer.mlp.gate_up_proj(h)))
         out = layer.mlp(h.transpose(0, 1))[0]          # the MoE block is sequence-first: [T, B, H]
         return out.transpose(0, 1)
+
+
+class MixtralInferenceModel(_MoEDecoderLayout, KVCacheInferenceMixin, MixtralForCausalLM):
+    """Mixtral-style MoE decoder with a KV cache (reference ``examples/inference/mixtral`` + ``modules/moe`` inference
+    paths): context encoding runs the capacity-free all-experts path, token generation loads only the selected experts
+    (``ExpertMLPs.forward_selective_loading``)."""
+
+    def __init__(self, config: MixtralConfig, inference_config: Optional[InferenceConfig] = None, device=None):
+        config.sequence_parallel_enabled = False
+        config.activation_checkpointing = False
+        MixtralForCausalLM.__init__(self, config, device=device)
+        self._init_inference(inference_config)
+
+
+class DbrxInferenceModel(_MoEDecoderLayout, KVCacheInferenceMixin, DbrxForCausalLM):
+    """DBRX with a KV cache (reference ``examples/inference/dbrx``): the Mixtral inference model with weight-only
+    LayerNorm in place of RMSNorm; the QKV clamp is a forward hook of the projection and applies here unchanged."""
+
+    def __init__(self, config: DbrxConfig, inference_config: Optional[InferenceConfig] = None, device=None):
+        config.sequence_parallel_enabled = False
+        config.activation_checkpointing = False
+        DbrxForCausalLM.__init__(self, config, device=device)
+        self._init_inference(inference_config)
+
+    def _add_norm(self, norm, hidden: torch.Tensor, residual: Optional[torch.Tensor]):
+        summed = hidden if residual is None else hidden + residual
+        return norm(summed), summed

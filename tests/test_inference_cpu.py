@@ -341,3 +341,45 @@ def test_model_builder_named_steps():
             inst.module.model.norm.weight.zero_()
         model.initialize_with_saved_weights(d, rank=0)
     assert torch.equal(model(ids, pos), _full_logits(train, ids)[:, -1].argmax(-1))
+
+
+def test_dbrx_generation_matches_recompute_and_hf_key_conversion():
+    from neuronx_distributed_llama3_2_b200.inference import DbrxInferenceModel
+    from neuronx_distributed_llama3_2_b200.models import DbrxForCausalLM, convert_dbrx_hf_state_dict, tiny_dbrx
+
+    torch.manual_seed(0)
+    cfg = tiny_dbrx(sequence_parallel_enabled=False)
+    train = DbrxForCausalLM(cfg).eval()
+    with torch.no_grad():                                  # make the clamp bite: some projections exceed clip_qkv = 0.5
+        for layer in train.layers:
+            layer.self_attn.qkv_proj.weight_qkv.mul_(8.0)
+    inf = DbrxInferenceModel(tiny_dbrx(sequence_parallel_enabled=False),
+                             InferenceConfig(batch_size=2, max_context_length=32, seq_len=64))
+    inf.load_state_dict(train.state_dict())
+    prompts = torch.randint(1, cfg.vocab_size, (2, 9))
+    out = inf.generate(prompts, max_new_tokens=4)
+    for b in range(2):
+        seq = prompts[b].clone()
+        for _ in range(4):
+            with torch.no_grad():
+                nxt = train(seq.unsqueeze(0)).transpose(0, 1)[0, -1].argmax()
+            seq = torch.cat([seq, nxt.reshape(1)])
+        assert torch.equal(out[b], seq), (b, out[b], seq)
+    # HF DBRX key layout -> ours (experts stacked [E * I, H] there, [E, H, 2I] / [E, I, H] here)
+    E, I, H = cfg.num_local_experts, cfg.intermediate_size, cfg.hidden_size
+    sd = train.state_dict()
+    hf = {"transformer.wte.weight": sd["embed_tokens.weight"], "transformer.norm_f.weight": sd["norm.weight"],
+          "lm_head.weight": sd["lm_head.weight"]}
+    for i in range(cfg.num_hidden_layers):
+        p, q = f"layers.{i}.", f"transformer.blocks.{i}."
+        gu = sd[p + "mlp.expert_mlps.mlp_op.gate_up_proj.weight"]                       # [E, H, 2I]
+        hf[q + "ffn.experts.mlp.w1"] = gu[:, :, :I].transpose(1, 2).reshape(E * I, H)
+        hf[q + "ffn.experts.mlp.v1"] = gu[:, :, I:].transpose(1, 2).reshape(E * I, H)
+        hf[q + "ffn.experts.mlp.w2"] = sd[p + "mlp.expert_mlps.mlp_op.down_proj.weight"].reshape(E * I, H)
+        hf[q + "ffn.router.layer.weight"] = sd[p + "mlp.router.linear_router.weight"]
+        hf[q + "norm_attn_norm.attn.Wqkv.weight"] = sd[p + "self_attn.qkv_proj.weight_qkv"]
+        hf[q + "norm_attn_norm.attn.out_proj.weight"] = sd[p + "self_attn.o_proj.weight"]
+        hf[q + "norm_attn_norm.norm_1.weight"] = sd[p + "input_layernorm.weight"]
+        hf[q + "norm_attn_norm.norm_2.weight"] = sd[p + "post_attention_layernorm.weight"]
+    back = convert_dbrx_hf_state_dict(hf, cfg)
+    assert set(back) == set(sd) and all(torch.equal(back[k], sd[k]) for k in sd)
