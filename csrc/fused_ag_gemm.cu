@@ -46,6 +46,9 @@ struct AgArgs {
     // only), a slab holds R / expert_rows experts and expert e multiplies weight rows [e * w_expert_stride, ...)
     int expert_rows;              // 0 = all-gather mode
     int w_expert_stride;
+    // NVLS (EXPERIMENTAL, not yet run on hardware): multicast address of X_total for this call.  One multimem.st reaches
+    // every rank's copy through the switch, so 1/tp of the bytes leave the GPU compared with the per-peer pushes.
+    bf16* mc_total;               // nullptr = per-peer TMA pushes
 };
 
 __device__ __forceinline__ unsigned long long gtime() {
@@ -79,6 +82,11 @@ __device__ __forceinline__ uint32_t atom_add_release_gpu(uint32_t* p, uint32_t v
     return old;
 }
 __device__ __forceinline__ void fence_proxy_async_all() { asm volatile("fence.proxy.async;" ::: "memory"); }
+__device__ __forceinline__ void multimem_st_16(void* mc_addr, const uint4& v) {
+    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc_addr), "f"(__uint_as_float(v.x)),
+                 "f"(__uint_as_float(v.y)), "f"(__uint_as_float(v.z)), "f"(__uint_as_float(v.w))
+                 : "memory");
+}
 __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
                      ptx::smem_u32(dst)),
@@ -155,6 +163,31 @@ ag_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a_local, const __grid_co
     const int chunks_per_slab = ag.R / kChunkRows;
     const size_t slab_bytes = (size_t)ag.R * K * 2;
 
+    if (cluster_id < 0 && ag.mc_total != nullptr && ag.expert_rows == 0) {
+        // ============== communication CTAs, NVLS variant: all threads, 16-byte loads -> multicast stores ==============
+        const int cid = (int)blockIdx.x;
+        const size_t chunk_bytes = (size_t)kChunkRows * K * 2;
+        const size_t piece = ((chunk_bytes / ag.comm_ctas) + 15) & ~size_t(15);
+        const size_t p0 = min((size_t)cid * piece, chunk_bytes);
+        const size_t p1 = min(p0 + piece, chunk_bytes);
+        const int n16 = (int)((p1 - p0) >> 4);
+        for (int c = 0; c < chunks_per_slab; ++c) {
+            const uint4* src = reinterpret_cast<const uint4*>(reinterpret_cast<const uint8_t*>(ag.x_local) +
+                                                              (size_t)c * chunk_bytes + p0);
+            uint4* dst = reinterpret_cast<uint4*>(reinterpret_cast<uint8_t*>(ag.mc_total) + (size_t)ag.rank * slab_bytes +
+                                                  (size_t)c * chunk_bytes + p0);
+            for (int i = threadIdx.x; i < n16; i += blockDim.x) multimem_st_16(dst + i, __ldg(src + i));
+            __syncthreads();
+            if (threadIdx.x == 0) {
+                __threadfence_system();
+                for (int d = 1; d < ag.tp; ++d) {
+                    const int peer = (ag.rank + d) % ag.tp;
+                    red_relaxed_sys_add_u32(ag.sig_peer[peer] + ag.slot_chunks + ag.rank * chunks_per_slab + c, 1u);
+                }
+            }
+        }
+        return;
+    }
     if (cluster_id < 0) {
         // =========================== communication CTAs (copy engine, no MMA) ===========================
         if (threadIdx.x != 0) return;
@@ -413,7 +446,8 @@ ag_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a_local, const __grid_co
 // [tp*R, K] for this call, and signal pad.  R % 256 == 0, K % 64 == 0, N % 8 == 0.  trace: optional 16 x u64 (device).
 static int ag_gemm_impl(int layout, const void* x_local, const void* w, void* y, int R, int N, int K, long long ldw,
                         long long ldy, void* const* xt_ptrs, void* const* sig_ptrs, int tp, int rank, int slot_chunks,
-                        unsigned epoch, int comm_ctas, int block_n, void* trace, int expert_rows, void* stream) {
+                        unsigned epoch, int comm_ctas, int block_n, void* trace, int expert_rows, void* stream,
+                        void* mc_total = nullptr) {
     using namespace nxd_gemm;
     NXD_REQUIRE(expert_rows == 0 || (expert_rows % kChunkRows == 0 && R % expert_rows == 0),
                 "a2a_gemm: rows per expert (%d) must be a multiple of %d and divide the slab (%d)", expert_rows, kChunkRows, R);
@@ -437,6 +471,7 @@ static int ag_gemm_impl(int layout, const void* x_local, const void* w, void* y,
     ag.tp = tp; ag.rank = rank; ag.R = R; ag.comm_ctas = comm_ctas; ag.epoch = epoch;
     ag.trace = (unsigned long long*)trace;
     ag.expert_rows = expert_rows;
+    ag.mc_total = (bf16*)mc_total;
     ag.w_expert_stride = layout == 0 ? N : K;     // stacked expert weights: [E * N, K] (nt) or [E * K, N] (nn)
     CUtensorMap ta_l, ta_t, tb, td;
     int rc;
@@ -490,4 +525,16 @@ NXD_API int nxd_a2a_gemm_bf16(int layout, const void* x_local, const void* w, vo
     NXD_REQUIRE(C > 0, "a2a_gemm: capacity must be positive");
     return ag_gemm_impl(layout, x_local, w, y, R, N, K, ldw, ldy, xt_ptrs, sig_ptrs, ep, rank, slot_chunks, epoch,
                         comm_ctas, block_n, trace, C, stream);
+}
+
+// EXPERIMENTAL (compiled, not yet run on hardware): nxd_ag_gemm_bf16 whose copy CTAs write the local shard ONCE to the
+// NVLS multicast address `mc_total` of the gathered buffer (the same buffer xt_ptrs point to, mapped through
+// cuMulticast* / torch.distributed._symmetric_memory) instead of pushing it to every peer.
+NXD_API int nxd_ag_gemm_bf16_nvls(int layout, const void* x_local, const void* w, void* y, int R, int N, int K,
+                                  long long ldw, long long ldy, void* const* xt_ptrs, void* const* sig_ptrs, int tp,
+                                  int rank, int slot_chunks, unsigned epoch, int comm_ctas, int block_n, void* mc_total,
+                                  void* stream) {
+    NXD_REQUIRE(mc_total != nullptr, "ag_gemm_nvls: multicast pointer required");
+    return ag_gemm_impl(layout, x_local, w, y, R, N, K, ldw, ldy, xt_ptrs, sig_ptrs, tp, rank, slot_chunks, epoch,
+                        comm_ctas, block_n, nullptr, 0, stream, mc_total);
 }

@@ -144,6 +144,11 @@ int nxd_symm_barrier(void* const* sig_peers, void* sig_local, int world, int ran
 int nxd_ag_gemm_bf16(int layout, const void* x_local, const void* w, void* y, int R, int N, int K, long long ldw,
                      long long ldy, void* const* xt_ptrs, void* const* sig_ptrs, int tp, int rank, int slot_chunks,
                      unsigned epoch, int comm_ctas, int block_n, void* trace, void* stream);
+/* EXPERIMENTAL (compiled, not yet run on hardware): same, but the copy CTAs store the local shard ONCE to the NVLS
+ * multicast address of the gathered buffer (multimem.st) instead of once per peer. */
+int nxd_ag_gemm_bf16_nvls(int layout, const void* x_local, const void* w, void* y, int R, int N, int K, long long ldw,
+                          long long ldy, void* const* xt_ptrs, void* const* sig_ptrs, int tp, int rank, int slot_chunks,
+                          unsigned epoch, int comm_ctas, int block_n, void* mc_total, void* stream);
 /* out[R, N] = reduce_scatter_r(X[tp*R, K] * op(W))  (reference: layers.py:452-461 matmul then reduce_scatter).
  * stage_ptrs: tp pointers to every rank's staging region [tp][R][N] bf16 (double-buffered by the caller through
  * epoch parity), slot_cnt: first of tp * R/256 flags. */

@@ -69,7 +69,13 @@ def fused_ag_gemm(ctx, x_shard: torch.Tensor, weight: torch.Tensor, layout: str 
     comm_ctas = _comm_ctas(tp)
     # counters / buffers are per configuration: the counters accumulate a fixed amount per call
     cfg = f"ag:{R}:{K}:{comm_ctas}"
-    local_ptr, table = ctx.region(cfg, 2 * total_bytes)   # X_total, double buffered
+    mc_base = 0
+    if os.environ.get("NXD_NVLS", "0") == "1":            # EXPERIMENTAL: multicast stores through the switch
+        got = ctx.region_mc(cfg, 2 * total_bytes)
+        if got is not None:
+            local_ptr, table, mc_base = got
+    if not mc_base:
+        local_ptr, table = ctx.region(cfg, 2 * total_bytes)   # X_total, double buffered
     st = ctx.__dict__.setdefault("_fused_state", {})
     if cfg not in st:
         st[cfg] = {"chunks": ctx.signal_slots(cfg + ":chunks", 8 * (R // 256)),
@@ -83,6 +89,14 @@ def fused_ag_gemm(ctx, x_shard: torch.Tensor, weight: torch.Tensor, layout: str 
                           ctx.tensor_view(local_ptr + parity * total_bytes, (tp * R, K), torch.bfloat16))
     xt_ptrs, x_total = s["bufs"][key]
     y = torch.empty((tp * R, N), dtype=torch.bfloat16, device=x_shard.device)
+    if mc_base:
+        rc = _lib.lib().nxd_ag_gemm_bf16_nvls(
+            _c.c_int(_LAYOUT[layout]), _lib.ptr(x_shard), _lib.ptr(weight), _lib.ptr(y), _c.c_int(R), _c.c_int(N),
+            _c.c_int(K), _c.c_longlong(weight.stride(0)), _c.c_longlong(y.stride(0)), xt_ptrs, s["sigs"], _c.c_int(tp),
+            _c.c_int(ctx.rank), _c.c_int(s["chunks"]), _c.c_uint(epoch), _c.c_int(comm_ctas), _c.c_int(0),
+            _c.c_void_p(mc_base + parity * total_bytes), _lib.stream_ptr())
+        _lib.check(rc, "nxd_ag_gemm_bf16_nvls")
+        return y, (x_total.clone() if persistent_total else x_total)
     trace = _trace_buf(x_shard.device, f"ag {R}x{K}x{N}")
     rc = _lib.lib().nxd_ag_gemm_bf16(
         _c.c_int(_LAYOUT[layout]), _lib.ptr(x_shard), _lib.ptr(weight), _lib.ptr(y), _c.c_int(R), _c.c_int(N),

@@ -72,6 +72,37 @@ class SymmMemContext:
         local, peers, size, table = self._regions[name]
         return local, table
 
+    def region_mc(self, name: str, nbytes: int):
+        """EXPERIMENTAL (not yet run on hardware): a symmetric region that also has an NVLS MULTICAST address, allocated
+        and exchanged by ``torch.distributed._symmetric_memory`` (cuMem + cuMulticast under the hood; CUDA IPC memory from
+        ``region`` cannot be bound to a multicast object).  Returns ``(local_ptr, peer_ptr_table, multicast_ptr)`` or
+        ``None`` when the platform / group has no multicast support."""
+        key = "mc:" + name
+        cur = self._regions.get(key)
+        if cur is not None and cur[2] >= nbytes:
+            return cur[0], cur[3], cur[4]
+        try:
+            import torch.distributed._symmetric_memory as tsm
+
+            size = (max(int(nbytes), 1 << 21) + (1 << 21) - 1) >> 21 << 21
+            buf = tsm.empty(size, dtype=torch.uint8, device=self.device)
+            hdl = tsm.rendezvous(buf, self.group)
+            mc = int(getattr(hdl, "multicast_ptr", 0) or 0)
+            if not mc:
+                return None
+            peers = [int(p) for p in hdl.buffer_ptrs]
+            table = torch.tensor(peers, dtype=torch.int64, device=self.device)
+            buf.zero_()
+            # (local, peers, size, table, multicast, keep-alive references)
+            self._regions[key] = (peers[self.rank], peers, size, table, mc, (buf, hdl))
+            self.barrier()
+            return peers[self.rank], table, mc
+        except Exception as e:  # noqa: BLE001 - old driver, no NVSwitch, group not enabled for symmetric memory, ...
+            from ..utils.logger import get_logger
+
+            get_logger().warning("NVLS multicast region unavailable (%s): using per-peer pushes", e)
+            return None
+
     def tensor_view(self, ptr: int, shape, dtype: torch.dtype) -> torch.Tensor:
         """Zero-copy torch tensor over symmetric memory at ``ptr`` (through ``__cuda_array_interface__``)."""
         nbytes = torch.empty(0, dtype=dtype).element_size()
@@ -113,6 +144,8 @@ class SymmMemContext:
         self.closed = True
         torch.cuda.synchronize()
         for key, val in list(self._regions.items()):
+            if key.startswith("mc:"):
+                continue          # owned by torch.distributed._symmetric_memory (freed with the tensors we hold)
             local, peers = val[0], val[1]
             for r, p in enumerate(peers):
                 if r != self.rank:
