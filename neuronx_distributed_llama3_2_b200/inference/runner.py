@@ -151,6 +151,28 @@ class InferenceRunner:
         ref = reference_model(input_ids).transpose(0, 1)[:, -1]
         return bool((logits.float() - ref.float()).abs().max() <= atol)
 
+    def torch_profile(self, chrome_trace_path: str = "torch-trace.json", prompt_len: Optional[int] = None,
+                      new_tokens: int = 8, warmup: int = 1, with_stack: bool = False) -> str:
+        """One ``generate`` under ``torch.profiler`` (CPU + CUDA activities when a GPU is present), exported as a Chrome
+        trace (reference ``runner.py:434-458``).  Graph replays show up as one ``cudaGraphLaunch`` each; trace with
+        ``use_cuda_graphs=False`` to see the individual kernels.  Numbers taken under the profiler are not benchmarks."""
+        from torch.profiler import ProfilerActivity, profile
+
+        ic = self.config
+        T = prompt_len or min(ic.max_context_length, 128)
+        ids = torch.randint(1, self.model_config.vocab_size, (ic.ctx_batch_size, T), device=self.device)
+        for _ in range(warmup):
+            self.generate(ids, max_new_tokens=new_tokens)
+        acts = [ProfilerActivity.CPU] + ([ProfilerActivity.CUDA] if self.device.type == "cuda" else [])
+        with profile(activities=acts, with_stack=with_stack, record_shapes=True) as prof:
+            self.generate(ids, max_new_tokens=new_tokens)
+            if self.device.type == "cuda":
+                torch.cuda.synchronize()
+        d = os.path.dirname(os.path.abspath(chrome_trace_path))
+        os.makedirs(d, exist_ok=True)
+        prof.export_chrome_trace(chrome_trace_path)
+        return chrome_trace_path
+
     def benchmark_sampling(self, prompt_len: Optional[int] = None, new_tokens: Optional[int] = None, n_runs: int = 20,
                            warmup: int = 1) -> Dict:
         """1 warm-up + ``n_runs`` timed ``generate`` calls; e2e, context-encoding (TTFT) and token-generation reports

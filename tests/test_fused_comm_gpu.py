@@ -276,6 +276,63 @@ def case_moe_fused(rank, world):
     os.environ["NXD_FUSED_MOE"] = "1"
 
 
+def case_flag_protocol_stress(rank, world):
+    """Back-to-back calls of the four symmetric-memory kernels with changing payloads and skewed rank arrival (a
+    busy-wait kernel delays a different rank every iteration), each checked against NCCL.  A flag that is consumed one
+    call early / late, a staging buffer reused before its readers are done, or a missing system fence shows up as a
+    stale payload (the generator seed changes every call) or as a hang (bounded by the spawn deadline)."""
+    import torch.distributed as dist
+
+    from neuronx_distributed_llama3_2_b200.ops.fused_comm import (fused_ag_gemm, fused_gemm_ar, fused_gemm_rs,
+                                                                    oneshot_all_reduce)
+    from neuronx_distributed_llama3_2_b200.parallel import parallel_state as ps
+
+    ctx = ps.get_symm_mem_context("tp")
+    iters = int(os.environ.get("NXD_STRESS_ITERS", "200"))
+    R, K, N = 256, 512, 768
+    w_nt = (torch.randn(N, K, device="cuda", generator=torch.Generator(device="cuda").manual_seed(3)) * 0.1).bfloat16()
+    for it in range(iters):
+        g = torch.Generator(device="cuda").manual_seed(7919 * it + rank)
+        if it % world == rank:                                   # this rank arrives late (~0.2 ms at 2 GHz)
+            torch.cuda._sleep(400_000 * (1 + it % 3))
+        op = it % 4
+        if op == 0:
+            x = torch.randn(R, K, device="cuda", generator=g).bfloat16()
+            y, x_total = fused_ag_gemm(ctx, x, w_nt, "nt")
+            ref_total = torch.empty(world * R, K, device="cuda", dtype=torch.bfloat16)
+            dist.all_gather_into_tensor(ref_total, x)
+            assert torch.equal(x_total, ref_total), f"ag iteration {it}: stale or torn gather"
+            assert _rel(y, ref_total.float() @ w_nt.float().t()) < 6e-3, it
+        elif op == 1:
+            x = torch.randn(world * R, K, device="cuda", generator=g).bfloat16()
+            out = fused_gemm_rs(ctx, x, w_nt, "nt")
+            ref = x.float() @ w_nt.float().t()
+            dist.all_reduce(ref)
+            assert _rel(out, ref[rank * R:(rank + 1) * R]) < 8e-3, f"rs iteration {it}"
+        elif op == 2:
+            x = torch.randn(1 + it % 8, K, device="cuda", generator=g).bfloat16()
+            out = fused_gemm_ar(ctx, x, w_nt, "nt")
+            ref = x.float() @ w_nt.float().t()
+            dist.all_reduce(ref)
+            assert _rel(out, ref) < 4e-3, f"gemm_ar iteration {it}"
+        else:
+            t = torch.randn(8 * (1 + (37 * it) % 4096), device="cuda", generator=g).bfloat16()
+            got = oneshot_all_reduce(ctx, t)
+            ref = t.float()
+            dist.all_reduce(ref)
+            assert _rel(got, ref) < 4e-3, f"oneshot iteration {it}"
+
+
+@pytest.mark.skipif(os.environ.get("NXD_STRESS", "0") != "1", reason="opt-in: NXD_STRESS=1 (see tools/run_sanitizers.sh)")
+def test_flag_protocol_stress():
+    world = int(os.environ.get("NXD_STRESS_WORLD", "2"))
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs")
+    from conftest import spawn_gpu_workers
+
+    spawn_gpu_workers(_worker, (world, _free_port(), "case_flag_protocol_stress"), world, deadline_s=300.0)
+
+
 def test_fused_ag_gemm_tp2():
     _spawn("case_ag_gemm", 2)
 

@@ -154,6 +154,11 @@ def test_runner_generate_buckets_and_benchmark_report():
     rep = runner.benchmark_sampling(prompt_len=16, new_tokens=4, n_runs=2)
     assert rep["ttft_ms_p50"] > 0 and rep["decode_tokens_per_s"] > 0
     assert set(rep["e2e_model"]) >= {"latency_ms_p50", "latency_ms_p99", "throughput"}
+    with tempfile.TemporaryDirectory() as d:
+        import json
+        path = runner.torch_profile(os.path.join(d, "prof", "trace.json"), prompt_len=16, new_tokens=2)
+        with open(path) as f:
+            assert len(json.load(f)["traceEvents"]) > 0
 
 
 def _attention(x, q, k, v, o, hq, hkv, d):
