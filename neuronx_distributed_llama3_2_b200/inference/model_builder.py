@@ -326,9 +326,38 @@ class ModelBuilder:
 # ---- names of the reference's SPMD runtime classes (``trace/spmd.py``, ``trace/model_builder.py``) ---------------------
 # SPMDBucketModel = one compiled bucket (NEFF there, captured CUDA graph here); NxDModelExecutor = the object that runs
 # the routed bucket; StateInitializer allocated the aliased KV state per rank (``KVCache`` does that here).
-SPMDBucketModel = _Bucket
-SPMDBucketModelScript = _Bucket
 NxDModelExecutor = NxDModel
+
+
+class SPMDBucketModelScript(torch.nn.Module):
+    """The compiled buckets of ONE model key, picked by index (reference ``spmd.py:9-30``; a bucket there is an
+    ``SPMDModel`` running a NEFF on every rank, here a ``_Bucket`` replaying its CUDA graph on this rank's GPU)."""
+
+    def __init__(self, compiled_models: Sequence[_Bucket]):
+        super().__init__()
+        self.models = list(compiled_models)
+
+    def forward(self, inputs: List[torch.Tensor], bucket_idx_tensor: torch.Tensor):
+        idx = int(bucket_idx_tensor)
+        if not 0 <= idx < len(self.models):
+            raise ValueError(f"bucket index {idx} out of range: {len(self.models)} bucket(s) compiled")
+        return self.models[idx](*inputs)
+
+
+class SPMDBucketModel(torch.nn.Module):
+    """``bucket_kernel(inputs, *constant_args) -> (inputs padded to a bucket, bucket index)`` in front of the bucket
+    executor (reference ``spmd.py:32-61``).  Weights are not registered here: all buckets close over the one module."""
+
+    def __init__(self, bucket_kernel: Callable, bucket_kernel_constant_args: Sequence[Any],
+                 bucket_model_executor: SPMDBucketModelScript):
+        super().__init__()
+        self.bucket_kernel = bucket_kernel
+        self.bucket_kernel_constant_args = tuple(bucket_kernel_constant_args)
+        self.bucket_model_executor = bucket_model_executor
+
+    def forward(self, inputs: List[torch.Tensor]):
+        padded, idx = self.bucket_kernel(inputs, *self.bucket_kernel_constant_args)
+        return self.bucket_model_executor(padded, idx)
 
 
 def default_bucket_kernel(inputs: List[torch.Tensor]):

@@ -18,8 +18,11 @@ class Sampler:
         self.temperature = getattr(config, "temperature", temperature) if config is not None else temperature
         ds = do_sample if do_sample is not None else getattr(config, "do_sample", self.top_k > 1)
         self.is_greedy = (not ds) or self.top_k == 1
+        self.is_medusa = bool(getattr(config, "is_medusa", False))
+        self.on_device_sampling = bool(getattr(config, "on_device_sampling", True))
         self.generator: Optional[torch.Generator] = None
         self.seed = seed
+        self.sampling_method = self.multinomial
 
     def _uniform(self, n: int, device) -> torch.Tensor:
         if self.generator is None or self.generator.device != torch.device(device):
@@ -33,3 +36,10 @@ class Sampler:
             return ops.argmax(logits)
         u = uniform if uniform is not None else self._uniform(logits.shape[0], logits.device)
         return ops.topk_sample(logits, self.top_k, self.top_p, self.temperature, u)
+
+    def multinomial(self, token_logits: torch.Tensor, uniform: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """The reference's sampling method name (``utils/sampling.py:27-77``): greedy for ``top_k == 1``, else one draw
+        from the soft-maxed top-k.  Medusa needs the candidate set itself, so it gets the top-k indices ``[B, k]``."""
+        if self.is_medusa and not self.is_greedy:
+            return torch.topk(token_logits, self.top_k, dim=1).indices
+        return self.sample(token_logits, uniform)

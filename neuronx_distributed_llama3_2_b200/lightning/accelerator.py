@@ -38,5 +38,15 @@ class CudaNxDAccelerator(AcceleratorBase):
     def is_available() -> bool:
         return True
 
+    @classmethod
+    def register_accelerators(cls, accelerator_registry) -> None:
+        """``Trainer(accelerator="nxd_cuda")`` (and the reference's ``"neuron"``) resolve to this class (reference
+        ``accelerator.py:68-70``).  The registry is Lightning's ``_AcceleratorRegistry`` or any mapping with ``register``."""
+        for name in ("nxd_cuda", "neuron"):
+            if hasattr(accelerator_registry, "register"):
+                accelerator_registry.register(name, cls, description=cls.__name__)
+            else:
+                accelerator_registry[name] = cls
+
 
 NeuronXLAAccelerator = CudaNxDAccelerator  # reference-compatible name

@@ -16,6 +16,8 @@ class NxDLightningLoop:
         module.setup("fit")
         module.configure_optimizers()
         if self.progress_bar is not None:
+            if hasattr(self.progress_bar, "setup"):
+                self.progress_bar.setup(self, module, "fit")
             self.progress_bar.on_train_start(total=self.max_steps)
         it = iter(dataloader)
         while module.global_step_ < self.max_steps:

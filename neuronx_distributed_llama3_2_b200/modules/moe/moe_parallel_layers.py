@@ -132,12 +132,18 @@ class ExpertFusedColumnParallelLinear(ExpertFusedLinear):
         self.output_size_per_partition = divide(output_size, tp)
         self.async_tensor_model_parallel_allreduce = tp > 1
         self.init_method = init_method or (lambda w: init.kaiming_uniform_(w, a=math.sqrt(5)))
-        self.weight = Parameter(torch.empty(self.num_local_experts, input_size, self.output_size_per_partition,
-                                            dtype=dtype, device=device))
-        _init_expert_weight(self.weight, self.init_method, 2)
+        self.set_weight_and_bias_config()
+        self.weight = Parameter(torch.empty(self.weight_shape, dtype=dtype, device=device))
+        _init_expert_weight(self.weight, self.init_method, self.weight_partition_dim)
         setattr(self.weight, "partition_stride", stride)
         self.register_parameter("bias", None)
         self._mark_expert_parallel_weights()
+
+    def set_weight_and_bias_config(self) -> None:
+        """One ``[in, out / tp]`` slab per local expert, column-parallel inside the slab, no bias (reference ``:183-192``)."""
+        self.weight_shape = (self.num_local_experts, self.input_size, self.output_size_per_partition)
+        self.weight_partition_dim = 2
+        self.bias_shape = None
 
     def forward(self, input_: torch.Tensor, expert_indices: Optional[torch.Tensor] = None) -> torch.Tensor:
         w = self.weight if expert_indices is None else self.weight[expert_indices]
@@ -156,12 +162,18 @@ class ExpertFusedRowParallelLinear(ExpertFusedLinear):
         self.num_local_experts = divide(num_experts, ep)
         self.input_size_per_partition = divide(input_size, tp)
         self.init_method = init_method or (lambda w: init.kaiming_uniform_(w, a=math.sqrt(5)))
-        self.weight = Parameter(torch.empty(self.num_local_experts, self.input_size_per_partition, output_size,
-                                            dtype=dtype, device=device))
-        _init_expert_weight(self.weight, self.init_method, 1)
+        self.set_weight_and_bias_config()
+        self.weight = Parameter(torch.empty(self.weight_shape, dtype=dtype, device=device))
+        _init_expert_weight(self.weight, self.init_method, self.weight_partition_dim)
         setattr(self.weight, "partition_stride", stride)
         self.register_parameter("bias", None)
         self._mark_expert_parallel_weights()
+
+    def set_weight_and_bias_config(self) -> None:
+        """One ``[in / tp, out]`` slab per local expert, row-parallel inside the slab, no bias (reference ``:274-283``)."""
+        self.weight_shape = (self.num_local_experts, self.input_size_per_partition, self.output_size)
+        self.weight_partition_dim = 1
+        self.bias_shape = None
 
     def forward(self, input_: torch.Tensor, expert_indices: Optional[torch.Tensor] = None) -> torch.Tensor:
         w = self.weight if expert_indices is None else self.weight[expert_indices]
@@ -195,8 +207,14 @@ class LinearRouter(torch.nn.Module):
                  init_method: Optional[Callable] = None):
         super().__init__()
         self.weight = Parameter(torch.empty(output_size, input_size, dtype=dtype, device=device))
+        self.init_method = init_method or (lambda w: init.kaiming_uniform_(w, a=math.sqrt(5)))
         if self.weight.device.type != "meta":
-            (init_method or (lambda w: init.kaiming_uniform_(w, a=math.sqrt(5))))(self.weight)
+            self.init_weight_cpu()
+
+    def init_weight_cpu(self) -> None:
+        """(Re-)draw the replicated router weight (reference ``:393-394``); every rank must hold the same RNG state."""
+        with torch.no_grad():
+            self.init_method(self.weight)
 
     def forward(self, input_: torch.Tensor) -> torch.Tensor:
         return LinearWithWeightGradAR.apply(input_, self.weight)

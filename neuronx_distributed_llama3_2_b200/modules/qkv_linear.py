@@ -328,6 +328,20 @@ class GQAQKVColumnParallelLinear(torch.nn.Module):
         with torch.no_grad():
             w.copy_(torch.cat(parts, dim=0))
 
+    def initialize_weight_biases(self) -> None:
+        """(Re-)draw the weights with ``init_method`` and zero the biases -- the reference's post-construction init
+        entry point (``qkv_linear.py:590-650``); the constructor already ran it once."""
+        if self.fuse_qkv:
+            self._init_fused()
+            biases = (self.bias_qkv,)
+        else:
+            self._init_split()
+            biases = (self.bias_q, self.bias_k, self.bias_v)
+        with torch.no_grad():
+            for b in biases:
+                if b is not None and b.device.type != "meta":
+                    b.zero_()
+
     # -- forward -------------------------------------------------------------------------------
     def forward(self, input: torch.Tensor, return_fused: bool = False):
         if self.async_tensor_model_parallel_allreduce or self.sequence_parallel_enabled:

@@ -139,6 +139,68 @@ def convert(input_dir: str, output_dir: str, convert_to_full: bool = False, conv
         return list(ex.map(_convert_one, jobs))
 
 
+# -- the reference's helper names (``convert_zero_checkpoints.py:14-145``), taking its ``args`` namespace ---------------------
+def _optim_dir(args) -> str:
+    """The reference passes ``<ckpt>/<tag>`` and looks into ``optim/``; this tool also accepts the ``optim`` directory itself."""
+    sub = os.path.join(args.input_dir, "optim")
+    return sub if os.path.isdir(sub) else args.input_dir
+
+
+def is_full(args) -> bool:
+    """True when the input holds merged (un-sharded) optimizer state: one file per (tp, pp) carrying ``template_layout``."""
+    d = _optim_dir(args)
+    names = os.listdir(d)
+    if any(n.startswith("full") for n in names):
+        return True
+    groups = _group_files(d)
+    if not groups or any(len(v) != 1 for v in groups.values()):
+        return False
+    return "template_layout" in _load(next(iter(groups.values()))[0])
+
+
+def is_xser(args) -> bool:
+    """True when shards were written tensor-by-tensor (``*.tensors`` side directories)."""
+    d = _optim_dir(args)
+    return any(n.endswith(".tensors") and os.path.isdir(os.path.join(d, n)) for n in os.listdir(d))
+
+
+def get_parallel_info(args):
+    """``(dp_size, tp_size, pp_size)`` from the shard file names (dp_size 0 for a full checkpoint)."""
+    d = _optim_dir(args)
+    dps, tps, pps = set(), set(), set()
+    for f in os.listdir(d):
+        m = _PAT.search(f)
+        if m:
+            dp, tp, pp = (int(x) for x in m.groups())
+            dps.add(dp), tps.add(tp), pps.add(pp)
+    if not tps:
+        raise FileNotFoundError(f"no optimizer shards found under {d}")
+    full = is_full(args)
+    return (0 if full else max(dps) + 1), max(tps) + 1, max(pps) + 1
+
+
+def merge_optim_dp_checkpoints(args, tp_rank: int, pp_rank: int) -> Dict[str, Any]:
+    """All DP shards of one (tp, pp) coordinate -> full fp32 state (``merge_shards``)."""
+    files = _group_files(_optim_dir(args))[(tp_rank, pp_rank)]
+    shards = [_load(f) for f in files]
+    if "template_layout" in shards[0]:
+        return shards[0]
+    full = merge_shards(shards)
+    full["template_layout"] = shards[0]["layout"]
+    return full
+
+
+def split_and_save_ckpts(args, merged_ckpt: Dict[str, Any], tp_rank: int, pp_rank: int) -> List[str]:
+    """Full state -> ``args.dp_size`` shard files under ``args.output_dir[/optim]``."""
+    out_dir = args.output_dir
+    os.makedirs(out_dir, exist_ok=True)
+    paths = []
+    for r, sd in enumerate(split_full(merged_ckpt, int(args.dp_size), merged_ckpt["template_layout"])):
+        paths.append(os.path.join(out_dir, f"dp_rank_{r:02d}_tp_rank_{tp_rank:02d}_pp_rank_{pp_rank:02d}.pt"))
+        torch.save(sd, paths[-1])
+    return paths
+
+
 def main(argv=None) -> None:
     ap = argparse.ArgumentParser("nxd_convert_zero_checkpoints")
     ap.add_argument("--input_dir", required=True, help="<ckpt>/<tag>/optim")

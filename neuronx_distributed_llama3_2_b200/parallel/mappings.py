@@ -256,6 +256,29 @@ class _ScatterInputChannelsToModelParallelRegion(torch.autograd.Function):
         return _gather_along_dim(grad_output, 1)
 
 
+class _ExportCtx:
+    """Stand-in for the autograd context when a mapping is evaluated outside autograd."""
+
+
+def _attach_symbolic(fn_cls) -> None:
+    """``symbolic(graph, *inputs)`` -- the static hook ``torch.onnx`` / graph exporters call instead of ``forward``
+    (the reference defines one per mapping, ``parallel_layers/mappings.py:169-354``).  The exported computation of every
+    mapping is its forward collective, so the hook evaluates ``forward`` with a throw-away context."""
+    def symbolic(graph, *inputs):
+        return fn_cls.forward(_ExportCtx(), *inputs)
+
+    symbolic.__qualname__ = f"{fn_cls.__name__}.symbolic"
+    fn_cls.symbolic = staticmethod(symbolic)
+
+
+for _cls in (_CopyToModelParallelRegion, _ReduceFromModelParallelRegion, _ScatterToModelParallelRegion,
+             _GatherFromModelParallelRegion, _ScatterToSequenceParallelRegion, _GatherFromSequenceParallelRegion,
+             _ReduceScatterToSequenceParallelRegion, _AllToAllInExpertParallelRegion,
+             _ScatterInputChannelsToModelParallelRegion):
+    _attach_symbolic(_cls)
+del _cls
+
+
 # ---------------------------------------------------------------------------
 # public helpers
 # ---------------------------------------------------------------------------

@@ -137,6 +137,38 @@ def analyze_pipeline_module(split: fx.GraphModule) -> Tuple[List[str], List[Stag
     return model_inputs, ios
 
 
+def iterate_graph_model_outputs(output_node_args):
+    """Yield the values an FX ``output`` node returns: its ``args`` is a 1-tuple holding either one node or a tuple of
+    them (reference ``:108-129``)."""
+    if not (isinstance(output_node_args, tuple) and len(output_node_args) == 1):
+        raise AssertionError(f"unsupported output args {output_node_args}")
+    inner = output_node_args[0]
+    yield from (inner if isinstance(inner, (tuple, list)) else (inner,))
+
+
+def adding_live_obj_for_previous_stages(stage_id_to_IO_input_names: Sequence[Dict[str, PipelineIO]],
+                                        stage_id_to_IO_output_names: Sequence[Dict[str, PipelineIO]], obj_name: str,
+                                        current_stage: int) -> None:
+    """Make ``obj_name`` -- needed by the stage after ``current_stage`` -- travel there from whichever earlier stage
+    holds it: every stage on the way that neither consumes nor produces it gets it as a pass-through input AND output;
+    the stage where it is found gets it as an output (reference ``:76-105``; ``analyze_pipeline_module`` does the same
+    bookkeeping with hop lists).  Walks backwards instead of recursing."""
+    passthrough = []
+    k = current_stage
+    while True:
+        if k < 0:
+            raise RuntimeError(f"{obj_name} is not available in any stage up to {current_stage}; outputs: "
+                               f"{[sorted(d) for d in stage_id_to_IO_output_names]}")
+        if obj_name in stage_id_to_IO_input_names[k] or obj_name in stage_id_to_IO_output_names[k]:
+            break
+        passthrough.append(k)
+        k -= 1
+    stage_id_to_IO_output_names[k].setdefault(obj_name, PipelineIO(obj_name))
+    for hop in passthrough:
+        stage_id_to_IO_input_names[hop][obj_name] = PipelineIO(obj_name)
+        stage_id_to_IO_output_names[hop][obj_name] = PipelineIO(obj_name)
+
+
 def analyze_shared_weights_across_stages(split: fx.GraphModule) -> List[List[Tuple[str, int]]]:
     """Parameters (same tensor object) that live in more than one stage, e.g. tied embeddings
     (reference ``:232-277``).  Returns ``[[(local_name, stage), ...], ...]``."""

@@ -20,15 +20,20 @@ class Timeline:
         self._nvtx = torch.cuda.is_available()
         self.step = 0
 
+    @property
+    def should_record(self) -> bool:
+        """Whether this rank records events (reference ``utils/timeline.py:39-41``; subclasses narrow it)."""
+        return self.enabled
+
     def mark_event_start(self, label: str) -> None:
-        if not self.enabled:
+        if not self.should_record:
             return
         if self._nvtx:
             torch.cuda.nvtx.range_push(label)
         self.events.append({"name": label, "ph": "B", "ts": time.time() * 1e6, "pid": self.rank, "tid": 0})
 
     def mark_event_end(self, label: str) -> None:
-        if not self.enabled:
+        if not self.should_record:
             return
         if self._nvtx:
             torch.cuda.nvtx.range_pop()
@@ -36,7 +41,7 @@ class Timeline:
 
     def mark_step_end(self, gather_group=None) -> None:
         """Gather the step's events from all PP ranks (object all-gather) and append them to the trace file."""
-        if not self.enabled:
+        if not self.should_record:
             return
         import torch.distributed as dist
 
@@ -69,3 +74,8 @@ class PPTimeline(Timeline):
         if on and ps.model_parallel_is_initialized():
             on = ps.get_data_parallel_rank() == 0 and ps.get_tensor_model_parallel_rank() == 0
         super().__init__(trace_file_path if on else None, pp_rank)
+
+    @property
+    def should_record(self) -> bool:
+        """Enabled and on the (dp 0, tp 0) replica: one track per pipeline stage (reference ``pipeline/timeline.py:16-18``)."""
+        return self.enabled

@@ -34,6 +34,11 @@ class PerChannelAbsMaxObserver(torch.nn.Module):
         scale = torch.clamp(self.max_val / float(self.quant_max), min=self.eps)
         return scale, torch.zeros_like(scale, dtype=torch.int64)
 
+    @torch.jit.export
+    def reset_min_max_vals(self) -> None:
+        """Forget the running statistics (reference ``observer.py:158-166``)."""
+        self.max_val = torch.tensor([], device=self.max_val.device)
+
     @classmethod
     def with_args(cls, **kwargs):
         """``torch.ao`` observer-factory protocol: ``QConfig(weight=PerChannelAbsMaxObserver.with_args(...))``."""

@@ -265,12 +265,122 @@ class CheckpointConverterBase:
             partial[base + "weight_q"], partial[base + "weight_k"], partial[base + "weight_v"] = q, k_, v_
         return partial
 
+    # -- Megatron (NxDT) naming, ``--model_style megatron`` (reference ``:102-196``) ---------------------------------------
+    # whole-key renames first, then fragments; the pairs are (megatron, hf)
+    _MEGATRON_WHOLE = (("language_model.embedding.word_embeddings.weight", "model.embed_tokens.weight"),
+                       ("language_model.encoder.final_layernorm.weight", "model.norm.weight"),
+                       ("language_model.output_layer.weight", "lm_head.weight"))
+    _MEGATRON_PARTS = (("language_model.encoder.", "model."), ("self_attention.", "self_attn."),
+                       ("core_attention.rotary_emb.inv_freq", "rotary_emb.inv_freq"),
+                       ("dense_h_to_4h.weight", "gate_up_proj.weight"), ("dense_4h_to_h.weight", "down_proj.weight"),
+                       ("query_key_value.weight", "qkv_proj.weight"), ("dense.weight", "o_proj.weight"))
+
+    def rename_keys_for_megatron(self, key: str, model_style: str = "megatron", hf_to_nxdt: bool = False) -> str:
+        """One key between Megatron / NxDT names and HF-style names; untouched unless ``model_style == 'megatron'``."""
+        if model_style != "megatron":
+            return key
+        a, b = (1, 0) if hf_to_nxdt else (0, 1)
+        for pair in self._MEGATRON_WHOLE:
+            if key == pair[a]:
+                return pair[b]
+        for pair in self._MEGATRON_PARTS:
+            key = key.replace(pair[a], pair[b])
+        return key
+
+    def modify_qkv_for_megatron(self, partial_state: Dict[str, torch.Tensor], args) -> None:
+        """In place.  Megatron keeps attention as ``query_key_value`` (MHA: rows q|k|v) or, with ``--qkv_linear`` (GQA),
+        as ``query`` + ``key_value`` (rows k|v); the framework side has ``q_proj/k_proj/v_proj`` (no qkv_linear) or
+        ``qkv_proj.weight_q/_k/_v``.  Direction follows ``args.convert_from_full_state`` the way the reference's does:
+        set -> the state is being turned INTO Megatron form, unset -> out of it."""
+        if getattr(args, "model_style", "hf") != "megatron":
+            return
+        to_megatron = bool(getattr(args, "convert_from_full_state", False))
+        keys = list(partial_state.keys())
+        if not getattr(args, "qkv_linear", False):
+            if to_megatron:
+                for k in keys:
+                    if "q_proj" in k:
+                        parts = [partial_state.pop(k.replace("q_proj", n)) for n in ("q_proj", "k_proj", "v_proj")]
+                        partial_state[k.replace("q_proj", "query_key_value")] = torch.cat(parts, dim=0)
+            return
+        for k in keys:
+            if k not in partial_state:
+                continue
+            if to_megatron:
+                if k.endswith("query_key_value.weight_q"):
+                    partial_state[k.replace("query_key_value.weight_q", "query.weight")] = partial_state.pop(k)
+                elif k.endswith("query_key_value.weight_k"):
+                    kv = [partial_state.pop(k), partial_state.pop(k[:-1] + "v")]
+                    partial_state[k.replace("query_key_value.weight_k", "key_value.weight")] = torch.cat(kv, dim=0)
+            else:
+                if "query.weight" in k:
+                    partial_state[k.replace("query.weight", "qkv_proj.weight_q")] = partial_state.pop(k)
+                elif "key_value.weight" in k:
+                    kk, vv = partial_state.pop(k).chunk(2, dim=0)
+                    partial_state[k.replace("key_value.weight", "qkv_proj.weight_k")] = kk.contiguous()
+                    partial_state[k.replace("key_value.weight", "qkv_proj.weight_v")] = vv.contiguous()
+
+    def is_q_or_o_for_megatron(self, args, name: str) -> bool:
+        """Megatron checkpoints have no KV replication, so Q and O shards are concatenated in plain rank order (no head
+        shuffle) -- true for Q / O projection weights in that style."""
+        if getattr(args, "model_style", "hf") != "megatron":
+            return False
+        return bool(re.search(r"(weight_q|q_proj|query\.weight|o_proj|dense\.weight)", name))
+
+    def megatron_full_to_hf(self, state: Dict[str, torch.Tensor]) -> Dict[str, torch.Tensor]:
+        """Full Megatron/NxDT-named state -> HF names with separate q/k/v and gate/up (what ``hf_to_nxd_full`` takes)."""
+        qs, kvs = self.nq * self.D, self.nkv * self.D
+        out: Dict[str, torch.Tensor] = {}
+        for k, v in state.items():
+            if k.endswith("self_attention.query_key_value.weight"):
+                base = self.rename_keys_for_megatron(k[: -len("query_key_value.weight")])
+                q, k_, v_ = torch.split(v, [qs, kvs, kvs], dim=0)
+                out[base + "q_proj.weight"], out[base + "k_proj.weight"], out[base + "v_proj.weight"] = q, k_, v_
+            elif k.endswith("self_attention.query.weight"):
+                out[self.rename_keys_for_megatron(k[: -len("query.weight")]) + "q_proj.weight"] = v
+            elif k.endswith("self_attention.key_value.weight"):
+                base = self.rename_keys_for_megatron(k[: -len("key_value.weight")])
+                out[base + "k_proj.weight"], out[base + "v_proj.weight"] = v.chunk(2, dim=0)
+            elif k.endswith("mlp.dense_h_to_4h.weight"):
+                base = self.rename_keys_for_megatron(k[: -len("dense_h_to_4h.weight")])
+                out[base + "gate_proj.weight"], out[base + "up_proj.weight"] = v.chunk(2, dim=0)
+            else:
+                out[self.rename_keys_for_megatron(k)] = v
+        return out
+
+    def hf_full_to_megatron(self, state: Dict[str, torch.Tensor], qkv_linear: bool = False) -> Dict[str, torch.Tensor]:
+        """Inverse of ``megatron_full_to_hf``: ``qkv_linear`` picks ``query`` + ``key_value`` over ``query_key_value``."""
+        out: Dict[str, torch.Tensor] = {}
+        for k, v in state.items():
+            m = re.match(r"(.*self_attn\.)q_proj\.weight$", k)
+            if m:
+                base = self.rename_keys_for_megatron(m.group(1), hf_to_nxdt=True)
+                kk, vv = state[m.group(1) + "k_proj.weight"], state[m.group(1) + "v_proj.weight"]
+                if qkv_linear:
+                    out[base + "query.weight"], out[base + "key_value.weight"] = v, torch.cat([kk, vv], dim=0)
+                else:
+                    out[base + "query_key_value.weight"] = torch.cat([v, kk, vv], dim=0)
+            elif re.search(r"self_attn\.[kv]_proj\.weight$", k) or k.endswith("mlp.up_proj.weight"):
+                continue
+            elif k.endswith("mlp.gate_proj.weight"):
+                base = self.rename_keys_for_megatron(k[: -len("gate_proj.weight")], hf_to_nxdt=True)
+                out[base + "dense_h_to_4h.weight"] = torch.cat([v, state[k.replace("gate_proj", "up_proj")]], dim=0)
+            else:
+                out[self.rename_keys_for_megatron(k, hf_to_nxdt=True)] = v
+        return out
+
     def pre_process_full_state_before_tp_conversion(self, state_dict: Dict[str, torch.Tensor], args=None):
-        """Hook: edit the full (HF-named) state before it is renamed and sharded.  Default: nothing."""
+        """Hook: edit the full state before it is renamed and sharded.  Megatron-style input is brought to HF names
+        here; otherwise nothing."""
+        if getattr(args, "model_style", "hf") == "megatron":
+            return self.megatron_full_to_hf(state_dict)
         return state_dict
 
     def post_process_full_state_after_tp_conversion(self, state_dict: Dict[str, torch.Tensor], args=None):
-        """Hook: edit the merged full (HF-named) state before it is written.  Default: nothing."""
+        """Hook: edit the merged full (HF-named) state before it is written.  ``--model_style megatron`` writes
+        Megatron names; otherwise nothing."""
+        if getattr(args, "model_style", "hf") == "megatron":
+            return self.hf_full_to_megatron(state_dict, qkv_linear=self.nkv != self.nq)
         return state_dict
 
     @staticmethod
@@ -367,6 +477,8 @@ class CheckpointConverterBase:
         ap.add_argument("--pp_size", type=int, default=1)
         ap.add_argument("--kv_size_multiplier", type=int, default=1)
         ap.add_argument("--qkv_linear", type=lambda s: s.lower() != "false", default=True)
+        ap.add_argument("--model_style", choices=["hf", "megatron"], default="hf",
+                        help="naming of the FULL checkpoint (input of --convert_from_full_state, output of --convert_to_full_state)")
         ap.add_argument("--convert_from_full_state", action="store_true")
         ap.add_argument("--convert_to_full_state", action="store_true")
         ap.add_argument("--load_xser", action="store_true")

@@ -160,3 +160,53 @@ def test_cli_paths_hooks_and_xser_conversion(tmp_path):
     again = conv.convert_partial_state_to_fused_qkv(split)
     assert torch.equal(again["model.layers.0.self_attn.qkv_proj.weight_qkv"], shard["model.layers.0.self_attn.qkv_proj.weight_qkv"])
     assert conv.find_size({"a": torch.zeros(4, 4), "b": [torch.zeros(2, dtype=torch.bfloat16)]}) == 68
+
+
+def test_megatron_style_round_trip(tmp_path):
+    """``--model_style megatron``: a Megatron/NxDT-named full checkpoint (``query`` + ``key_value`` for GQA, fused
+    ``dense_h_to_4h``) -> TP shards identical to those of the HF-named state -> back to Megatron names."""
+    import json
+    from types import SimpleNamespace
+
+    hf = _hf_state(tied=False)
+    conv = CheckpointConverterBase(4, 8, 2, 8, tp_size=2, tie_word_embeddings=False)
+    meg = conv.hf_full_to_megatron(hf, qkv_linear=True)
+    assert "language_model.embedding.word_embeddings.weight" in meg and "language_model.output_layer.weight" in meg
+    assert "language_model.encoder.final_layernorm.weight" in meg
+    p = "language_model.encoder.layers.1."
+    assert meg[p + "self_attention.key_value.weight"].shape == (2 * 2 * 8, 64)
+    assert meg[p + "mlp.dense_h_to_4h.weight"].shape == (192, 64) and p + "self_attention.dense.weight" in meg
+    assert p + "input_layernorm.weight" in meg and not any(k.startswith("model.") for k in meg)
+    back = conv.megatron_full_to_hf(meg)
+    assert set(back) == set(hf) and all(torch.equal(back[k], hf[k]) for k in hf)
+    mha = CheckpointConverterBase(4, 8, 8, 8)
+    hf_mha = _hf_state(nkv=8, tied=False)
+    meg_mha = mha.hf_full_to_megatron(hf_mha)
+    assert meg_mha[p + "self_attention.query_key_value.weight"].shape == (3 * 64, 64)
+    assert all(torch.equal(v, hf_mha[k]) for k, v in mha.megatron_full_to_hf(meg_mha).items())
+    # single-key / in-place helpers under the reference's names
+    assert conv.rename_keys_for_megatron("model.layers.0.mlp.down_proj.weight", "megatron", hf_to_nxdt=True) == \
+        "language_model.encoder.layers.0.mlp.dense_4h_to_h.weight"
+    assert conv.rename_keys_for_megatron("model.norm.weight", "hf", hf_to_nxdt=True) == "model.norm.weight"
+    a = SimpleNamespace(model_style="megatron", qkv_linear=True, convert_from_full_state=False)
+    part = {"x.self_attention.query.weight": torch.ones(4, 2), "x.self_attention.key_value.weight": torch.arange(8.).reshape(4, 2)}
+    conv.modify_qkv_for_megatron(part, a)
+    assert set(part) == {"x.self_attention.qkv_proj.weight_q", "x.self_attention.qkv_proj.weight_k",
+                         "x.self_attention.qkv_proj.weight_v"}
+    assert conv.is_q_or_o_for_megatron(a, "layers.0.self_attn.o_proj.weight")
+    assert not conv.is_q_or_o_for_megatron(SimpleNamespace(model_style="hf"), "layers.0.self_attn.o_proj.weight")
+    # CLI: Megatron full -> TP2 shards (same tensors as from HF names) -> Megatron full
+    src = tmp_path / "meg"
+    os.makedirs(src)
+    torch.save(meg, src / "checkpoint.pt")
+    cfg = tmp_path / "config.json"
+    cfg.write_text(json.dumps({"num_hidden_layers": 4, "num_attention_heads": 8, "num_key_value_heads": 2,
+                               "hidden_size": 64, "head_dim": 8, "tie_word_embeddings": False}))
+    common = ["--config", str(cfg), "--tp_size", "2", "--model_style", "megatron"]
+    CheckpointConverterBase.run(["--input_dir", str(src), "--output_dir", str(tmp_path / "sh"), "--convert_from_full_state"] + common)
+    shard = torch.load(tmp_path / "sh" / "model" / "dp_rank_00_tp_rank_01_pp_rank_00.pt", weights_only=False)
+    want = conv.shard_tp(conv.hf_to_nxd_full(hf), 1)
+    assert set(shard) == set(want) and all(torch.equal(shard[k], want[k]) for k in want)
+    CheckpointConverterBase.run(["--input_dir", str(tmp_path / "sh"), "--output_dir", str(tmp_path / "full"), "--convert_to_full_state"] + common)
+    full = torch.load(tmp_path / "full" / "checkpoint.pt", weights_only=False)
+    assert set(full) == set(meg) and all(torch.equal(full[k], meg[k]) for k in meg)

@@ -37,3 +37,12 @@ def test_lightning_module_strategy_loop_single_process():
     with NeuronXLAPrecisionPlugin(mode="autocast").forward_context():
         pass
     assert strategy.distributed_sampler_kwargs == {"num_replicas": 1, "rank": 0}
+    from neuronx_distributed_llama3_2_b200.lightning import NeuronXLAAccelerator
+    reg = {}
+    NeuronXLAAccelerator.register_accelerators(reg)
+    assert reg["neuron"] is NeuronXLAAccelerator and reg["nxd_cuda"] is NeuronXLAAccelerator
+    bar = NeuronTQDMProgressBar()
+    bar.setup(loop, module, "fit")
+    assert bar.is_enabled            # dp 0 / tp 0 / last pp stage of a 1-process job
+    bar.disable()
+    assert not bar.is_enabled

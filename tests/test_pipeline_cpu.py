@@ -134,6 +134,15 @@ def test_debug_mode_partition_and_names():
 
     assert create_partitions(4, 8) == [1, 3, 5]
     assert create_partitions(3, 8) == [1, 4]      # remainder goes to the later stages: sizes 2, 3, 3
+    from neuronx_distributed_llama3_2_b200.pipeline.partition import (PipelineIO, adding_live_obj_for_previous_stages,
+                                                                      iterate_graph_model_outputs)
+    assert list(iterate_graph_model_outputs(("a",))) == ["a"] and list(iterate_graph_model_outputs((("a", "b"),))) == ["a", "b"]
+    ins, outs = [{"x": PipelineIO("x")}, {"h0": PipelineIO("h0")}, {"h1": PipelineIO("h1")}], [{"h0": PipelineIO("h0")},
+                                                                                                {"h1": PipelineIO("h1")}, {}]
+    adding_live_obj_for_previous_stages(ins, outs, "x", 2)      # stage 3 wants the model input-derived value "x"
+    assert "x" in outs[0] and "x" in ins[1] and "x" in outs[1] and "x" in ins[2] and "x" in outs[2]
+    with pytest.raises(RuntimeError):
+        adding_live_obj_for_previous_stages(ins, outs, "nope", 2)
     cfg, m = _build(num_layers=8)
     pp = NxDPPModel(m, transformer_layer_cls=LlamaDecoderLayer, num_microbatches=2, input_names=["input_ids", "labels"],
                     auto_partition=True, _debug_mode=True, _debug_pp_size=4, _debug_pp_rank=1)

@@ -64,6 +64,17 @@ def _dp_worker(rank, world, tmp):
         for i in full["base_state"]:
             assert torch.equal(again["base_state"][i], full["base_state"][i])
             assert torch.equal(again["state"][i]["exp_avg_sq"], full["state"][i]["exp_avg_sq"])
+        # the same round trip through the reference's helper names (args namespace, <ckpt>/<tag> as input_dir)
+        from types import SimpleNamespace
+        a = SimpleNamespace(input_dir=os.path.join(d, "t"), output_dir=os.path.join(tmp, "dp4"), dp_size=4)
+        assert not czc.is_full(a) and not czc.is_xser(a) and czc.get_parallel_info(a) == (world, 1, 1)
+        assert czc.is_full(SimpleNamespace(input_dir=os.path.join(tmp, "full")))
+        merged = czc.merge_optim_dp_checkpoints(a, 0, 0)
+        assert len(czc.split_and_save_ckpts(a, merged, 0, 0)) == 4
+        again4 = czc.merge_shards([torch.load(os.path.join(tmp, "dp4", f"dp_rank_{r:02d}_tp_rank_00_pp_rank_00.pt"),
+                                              weights_only=False) for r in range(4)])
+        for i in full["base_state"]:
+            assert torch.equal(again4["base_state"][i], full["base_state"][i])
     dist.barrier()
 
     # DCP variant: one optim/ directory with .metadata, every rank's tensors under rank-suffixed names
