@@ -11,5 +11,5 @@ from .model_builder import BaseModelInstance, ModelBuilder, NxDModel  # noqa: F4
 from .sampling import Sampler  # noqa: F401
 from .trace import parallel_model_load, parallel_model_save, parallel_model_trace  # noqa: F401
 from .benchmark import Benchmark, LatencyCollector, generate_report  # noqa: F401
-from .runner import InferenceRunner  # noqa: F401
+from .runner import DbrxRunner, InferenceRunner, LlamaRunner, MixtralRunner  # noqa: F401
 from .model_wrapper import ModelWrapper  # noqa: F401

@@ -80,8 +80,8 @@ class KVCacheInferenceMixin:
         return self._rope_tables
 
     # -- one decoder layer ---------------------------------------------------------------------------------------
-    def _attention(self, layer_idx: int, attn, h: torch.Tensor, positions: torch.Tensor, seq_ids: torch.Tensor,
-                   lengths: torch.Tensor, prefill: bool) -> torch.Tensor:
+    def _qkv_to_cache(self, layer_idx: int, attn, h: torch.Tensor, positions: torch.Tensor, seq_ids):
+        """Projection, RoPE at ``positions`` and the write of the new K/V rows into the cache; ``(q, k, v, ck, cv)``."""
         B, T, _ = h.shape
         nq, nkv, D = attn.q_heads_local, attn.kv_heads_local, attn.head_dim
         if self.config.fuse_qkv:
@@ -99,6 +99,30 @@ class KVCacheInferenceMixin:
         kw = dict(block_table=self.kv_cache.block_table, page_size=self.kv_cache.page_size) if self.kv_cache.paged else {}
         attn_ops.kv_cache_update(ck, cv, k.permute(0, 2, 1, 3), v.permute(0, 2, 1, 3), positions[:, 0], seq_ids=seq_ids,
                                  **kw)
+        return q, k, v, ck, cv
+
+    def _attention_with_past(self, layer_idx: int, attn, h: torch.Tensor, positions: torch.Tensor,
+                             seq_ids: torch.Tensor) -> torch.Tensor:
+        """A few NEW tokens per sequence attending to the cache AND causally to each other (speculation verify):
+        every (sequence, token) pair is one row of the decode-attention kernel with its own length."""
+        B, T, _ = h.shape
+        nq, D = attn.q_heads_local, attn.head_dim
+        q, _, _, ck, cv = self._qkv_to_cache(layer_idx, attn, h, positions, seq_ids)
+        rows = seq_ids.long().repeat_interleave(T)
+        lengths = (positions + 1).reshape(-1).to(torch.int32)
+        q2 = q.reshape(B * T, nq, D).contiguous()
+        if self.kv_cache.paged:
+            o = attn_ops.decode_attention(q2, ck, cv, lengths, block_table=self.kv_cache.block_table[rows],
+                                          page_size=self.kv_cache.page_size)
+        else:
+            o = attn_ops.decode_attention(q2, ck.index_select(0, rows), cv.index_select(0, rows), lengths)
+        return attn.o_proj(o.reshape(B, T, nq * D))
+
+    def _attention(self, layer_idx: int, attn, h: torch.Tensor, positions: torch.Tensor, seq_ids: torch.Tensor,
+                   lengths: torch.Tensor, prefill: bool) -> torch.Tensor:
+        B, T, _ = h.shape
+        nq, D = attn.q_heads_local, attn.head_dim
+        q, k, v, ck, cv = self._qkv_to_cache(layer_idx, attn, h, positions, seq_ids)
         if prefill:
             o = attn_ops.flash_attn_func(q.permute(0, 2, 1, 3), k.permute(0, 2, 1, 3), v.permute(0, 2, 1, 3), causal=True)
             o = o.permute(0, 2, 1, 3).reshape(B, T, nq * D)
@@ -168,6 +192,29 @@ class KVCacheInferenceMixin:
         tokens = self.sampler.sample(logits.float() if logits.dtype not in (torch.float32, torch.bfloat16) else logits,
                                      uniform)
         return (tokens, logits) if return_logits else tokens
+
+    @torch.no_grad()
+    def forward_speculation(self, input_ids: torch.Tensor, position_ids: torch.Tensor,
+                            seq_ids: Optional[torch.Tensor] = None, return_logits: bool = False):
+        """The ``speculation_model`` graph of the reference (``model_base.py:853-860``): the TARGET model on ``k + 1``
+        tokens per sequence at consecutive positions, on top of the KV cache.  Writes their K/V into the cache (rows
+        past the accepted prefix are simply overwritten by the next round) and returns the greedy token after EVERY
+        position, ``[B, k + 1]`` -- what ``NeuronSpeculation.target_verify`` needs."""
+        assert self.kv_cache is not None, "call init_kv_cache() first"
+        B, T = input_ids.shape
+        lines = seq_ids if seq_ids is not None else torch.arange(B, device=input_ids.device, dtype=torch.int32)
+        hidden, residual = self._embed(input_ids), None
+        for i, layer in enumerate(self._decoder_layers()):
+            h, residual = self._add_norm(layer.input_layernorm, hidden, residual)
+            a = self._attention_with_past(i, layer.self_attn, h, position_ids, lines)
+            h, residual = self._add_norm(layer.post_attention_layernorm, a, residual)
+            hidden = self._mlp(layer, h)
+        H = hidden.shape[-1]
+        hidden, _ = self._add_norm(self._final_norm(), hidden.reshape(B * T, H).contiguous(),
+                                   residual.reshape(B * T, H).contiguous())
+        logits = mappings.gather_from_tensor_model_parallel_region(self.lm_head(hidden))[:, : self.config.vocab_size]
+        tokens = logits.argmax(dim=-1).reshape(B, T)
+        return (tokens, logits.reshape(B, T, -1)) if return_logits else tokens
 
     def forward(self, input_ids: torch.Tensor, position_ids: torch.Tensor, seq_ids: Optional[torch.Tensor] = None,
                 last_token_index: Optional[torch.Tensor] = None):

@@ -32,10 +32,17 @@ logger = get_logger()
 class BaseModelInstance:
     """How to build the module for one sub-model (reference ``model_builder.py:37-47``)."""
 
-    def __init__(self, module_cls: Callable[[], torch.nn.Module], input_output_aliases: Optional[Dict] = None):
+    def __init__(self, module_cls: Callable[[], torch.nn.Module], input_output_aliases: Optional[Dict] = None,
+                 forward_method: Optional[str] = None):
         self.module_cls = module_cls
         self.module: Optional[torch.nn.Module] = None
         self.input_output_aliases = input_output_aliases or {}
+        # entry point of this sub-model when it is not the module's ``forward`` (e.g. ``forward_speculation``): several
+        # sub-models of one module then differ by what they run, not only by their input shapes
+        self.forward_method = forward_method
+
+    def entry_point(self) -> Callable:
+        return getattr(self.module, self.forward_method) if self.forward_method else self.module
 
     def load_module(self) -> None:
         self.module = self.module_cls()
@@ -292,7 +299,8 @@ class ModelBuilder:
             buckets[key] = {}
             for rank_idx, ex in enumerate(entry["example_inputs"]):
                 mod, _aliases = inst.get(rank_idx)
-                b = _Bucket(mod, tuple(ex), self.use_cuda_graphs)
+                fn = getattr(mod, inst.forward_method) if getattr(inst, "forward_method", None) else mod
+                b = _Bucket(fn, tuple(ex), self.use_cuda_graphs)
                 b.capture()
                 buckets[key][_shape_key(ex)] = b
         return NxDModel(buckets, modules)

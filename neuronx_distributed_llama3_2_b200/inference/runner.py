@@ -22,26 +22,84 @@ from .model_builder import BaseModelInstance, ModelBuilder, NxDModel
 
 CONTEXT_ENCODING_MODEL = "context_encoding_model"
 TOKEN_GENERATION_MODEL = "token_generation_model"
+SPECULATION_MODEL = "speculation_model"
 
 
 class InferenceRunner:
-    def __init__(self, model_config: LlamaConfig, inference_config: InferenceConfig, checkpoint_loader=None, device=None):
+    """``model_cls`` picks the family (``LlamaInferenceModel`` by default, ``MixtralInferenceModel``,
+    ``DbrxInferenceModel`` -- the reference has one runner subclass per family, ``examples/inference/{llama3,mixtral,
+    dbrx}/*_runner.py``).  With ``inference_config.quantized`` the decoder layers' parallel linears are swapped for the
+    int8 weight-only layers and a float checkpoint is quantized on load (reference ``run_llama_quantized.py``)."""
+
+    model_cls = LlamaInferenceModel
+
+    def __init__(self, model_config: LlamaConfig, inference_config: InferenceConfig, checkpoint_loader=None, device=None,
+                 model_cls=None):
         self.model_config = model_config
         self.config = inference_config
-        self.checkpoint_loader = checkpoint_loader
+        if model_cls is not None:
+            self.model_cls = model_cls
+        self._float_loader = checkpoint_loader
+        self.checkpoint_loader = (self._quantized_loader if (inference_config.quantized and checkpoint_loader is not None)
+                                  else checkpoint_loader)
         self.device = device or (torch.device("cuda", torch.cuda.current_device()) if torch.cuda.is_available()
                                  else torch.device("cpu"))
         self.model: Optional[LlamaInferenceModel] = None
         self.nxd_model: Optional[NxDModel] = None
 
     # -- build --------------------------------------------------------------------------------------------------------
+    def _q_config(self) -> dict:
+        from ..quantization.quantization_config import (QuantizationType, get_default_custom_qconfig_dict,
+                                                        get_default_per_channel_custom_qconfig_dict)
+
+        if QuantizationType(self.config.quantization_type) == QuantizationType.PER_CHANNEL_SYMMETRIC:
+            return get_default_per_channel_custom_qconfig_dict()
+        return get_default_custom_qconfig_dict()
+
+    def _quantize_layers(self, m) -> None:
+        """int8 weight-only layers inside the decoder blocks; embedding, (tied) LM head, QKV and routers stay float."""
+        from ..quantization.quantize import convert
+
+        for layer in m._decoder_layers():
+            convert(layer, self._q_config(), inplace=True)
+
     def _make_module(self) -> LlamaInferenceModel:
         if torch.empty(0).device.type == "meta":   # shard_checkpoint builds shape-only replicas under torch.device("meta")
-            return LlamaInferenceModel(self.model_config, self.config, device="meta")
-        m = LlamaInferenceModel(self.model_config, self.config, device=self.device)
+            m = self.model_cls(self.model_config, self.config, device="meta")
+            if self.config.quantized:
+                self._quantize_layers(m)
+            return m
+        m = self.model_cls(self.model_config, self.config, device=self.device)
+        if self.config.quantized:
+            self._quantize_layers(m)
         m.init_kv_cache(device=self.device)
         self.model = m
         return m
+
+    def generate_quantized_state_dict(self, state_dict: Dict[str, torch.Tensor]) -> Dict[str, torch.Tensor]:
+        """Float full state -> the state the quantized model loads: ``<layer>.weight`` int8 + ``<layer>.scale`` for
+        exactly the layers ``_quantize_layers`` converts (reference ``model_base.py`` ``generate_quantized_state_dict``)."""
+        from ..quantization.quantization_layers import BaseQuantizeParallelLinear
+        from ..quantization.quantization_utils import quantize_per_channel_symmetric, quantize_per_tensor_symmetric
+
+        with torch.device("meta"):
+            meta = self.model_cls(self.model_config, self.config, device="meta")
+            self._quantize_layers(meta)
+        out = dict(state_dict)
+        for name, mod in meta.named_modules():
+            key = name + ".weight"
+            if not isinstance(mod, BaseQuantizeParallelLinear) or key not in out or not out[key].is_floating_point():
+                continue
+            if mod.scale.numel() > 1:       # per channel: scale already shaped to broadcast against the weight
+                q, sc = quantize_per_channel_symmetric(out[key].float(), (mod.per_channel_axis or 0) % out[key].dim())
+            else:
+                q, sc = quantize_per_tensor_symmetric(out[key].float())
+            out[key], out[name + ".scale"] = q, sc.to(torch.float32)
+        return out
+
+    def _quantized_loader(self) -> Dict[str, torch.Tensor]:
+        sd = self._float_loader()
+        return sd if any(k.endswith(".scale") for k in sd) else self.generate_quantized_state_dict(sd)
 
     def trace(self, traced_model_path: Optional[str] = None) -> NxDModel:
         """Compile both sub-models (reference ``runner.trace`` -> ``model.compile`` -> ``ModelBuilder.trace``) and,
@@ -59,12 +117,21 @@ class InferenceRunner:
         builder.add(CONTEXT_ENCODING_MODEL, inst, [ex(ic.ctx_batch_size, t) for t in ic.context_buckets()],
                     priority_model_idx=0)
         builder.add(TOKEN_GENERATION_MODEL, inst, [ex(ic.tkg_batch_size, 1)])
+        if ic.speculation_length > 0:
+            # the target's verify graph: k + 1 tokens per sequence on top of the KV cache (same module, other entry point)
+            def shared():
+                return self.model if (self.model is not None and torch.empty(0).device.type != "meta") else self._make_module()
+
+            k1 = ic.speculation_length + 1
+            builder.add(SPECULATION_MODEL, BaseModelInstance(shared, forward_method="forward_speculation"),
+                        [ex(ic.tkg_batch_size, k1)[:3]])
         self.nxd_model = builder.trace(initialize_model_weights=self.checkpoint_loader is not None)
         if traced_model_path:
             os.makedirs(traced_model_path, exist_ok=True)
             with open(os.path.join(traced_model_path, "config.json"), "w") as f:
-                json.dump({"model": self.model_config.to_dict(), "inference": self.config.__dict__}, f, indent=1,
-                          default=str)
+                mc = self.model_config
+                json.dump({"model": mc.to_dict() if hasattr(mc, "to_dict") else dict(vars(mc)),
+                           "inference": self.config.__dict__}, f, indent=1, default=str)
             if self.checkpoint_loader is not None and ps.is_global_rank_zero():
                 builder.shard_checkpoint(os.path.join(traced_model_path, "weights"))
         return self.nxd_model
@@ -140,6 +207,42 @@ class InferenceRunner:
             res[b, L:L + gen.shape[1]] = gen[b]
         return res
 
+    @torch.no_grad()
+    def generate_speculative(self, draft: "InferenceRunner", input_ids: torch.Tensor,
+                             max_new_tokens: Optional[int] = None) -> torch.Tensor:
+        """Assisted decoding (reference ``run_llama_speculative.py`` / ``utils/speculative_decoding.py``): ``draft`` proposes
+        ``speculation_length`` tokens with its token-generation graph, this (target) runner verifies them with ONE call of
+        its ``speculation_model`` graph.  Batch 1 as in the reference; the result equals ``generate`` of the target."""
+        from .speculative import NeuronSpeculation
+
+        ic, dev = self.config, self.device
+        assert ic.speculation_length > 0, "trace the target with InferenceConfig(speculation_length=k)"
+        assert input_ids.shape[0] == 1 and ic.tkg_batch_size == 1 and draft.config.tkg_batch_size == 1
+        max_new = max_new_tokens or ic.max_new_tokens
+        T = input_ids.shape[1]
+        first = None
+        for r in (draft, self):                                  # context encoding fills both KV caches
+            Tb = r._bucket_len(T)
+            ids = torch.full((r.config.ctx_batch_size, Tb), r.config.pad_token_id, dtype=torch.long, device=dev)
+            ids[:1, :T] = input_ids.to(dev)
+            pos = torch.arange(Tb, device=dev).unsqueeze(0).expand(r.config.ctx_batch_size, Tb).contiguous()
+            last = torch.zeros(r.config.ctx_batch_size, dtype=torch.long, device=dev)
+            last[0] = T - 1
+            first = r.nxd_model(ids, pos, torch.arange(r.config.ctx_batch_size, dtype=torch.int32, device=dev), last).clone()
+        seq1 = torch.arange(1, dtype=torch.int32, device=dev)
+        zero = torch.zeros(1, dtype=torch.long, device=dev)
+
+        def draft_step(tok, pos):
+            return draft.nxd_model(tok.reshape(1, 1), pos.reshape(1, 1), seq1, zero).clone()
+
+        def target_verify(toks, pos):
+            return self.nxd_model(toks.contiguous(), pos.contiguous(), seq1).clone()
+
+        spec = NeuronSpeculation(draft_step, target_verify, ic.speculation_length)
+        new = spec.generate(first[:1], torch.tensor([T], device=dev), max_new - 1, eos_token_id=ic.eos_token_id)
+        self.last_acceptance = list(spec.accepted_hist)
+        return torch.cat([input_ids.to(dev)[0], first[:1], new]).unsqueeze(0)
+
     # -- checks / benchmark ------------------------------------------------------------------------------------------------
     @torch.no_grad()
     def check_accuracy_logits(self, reference_model, input_ids: torch.Tensor, atol: float = 5e-2) -> bool:
@@ -201,3 +304,28 @@ class InferenceRunner:
         report["ttft_ms_p50"] = report[CONTEXT_ENCODING_MODEL]["latency_ms_p50"]
         report["decode_tokens_per_s"] = report[TOKEN_GENERATION_MODEL]["throughput"]
         return report
+
+
+class LlamaRunner(InferenceRunner):
+    """Reference ``examples/inference/llama3/llama3_runner.py``."""
+    model_cls = LlamaInferenceModel
+
+
+class MixtralRunner(InferenceRunner):
+    """Reference ``examples/inference/mixtral/mixtral_runner.py``."""
+
+    def __init__(self, *a, **kw):
+        from .model import MixtralInferenceModel
+
+        kw.setdefault("model_cls", MixtralInferenceModel)
+        super().__init__(*a, **kw)
+
+
+class DbrxRunner(InferenceRunner):
+    """Reference ``examples/inference/dbrx/dbrx_runner.py``."""
+
+    def __init__(self, *a, **kw):
+        from .model import DbrxInferenceModel
+
+        kw.setdefault("model_cls", DbrxInferenceModel)
+        super().__init__(*a, **kw)

@@ -48,6 +48,10 @@ class NeuronSpeculation:
                 out.append(x)
                 if eos_token_id is not None and x == eos_token_id:
                     return torch.tensor(out[:max_new_tokens], device=last_token.device)
+            if n_ok == self.k:
+                # every draft accepted: the draft model never consumed its own last proposal, so its KV cache has a hole
+                # at that position -- fill it (the prediction is discarded) or the next round drafts from a stale context
+                self.draft_step(drafts[-1], pos + self.k)
             tok = torch.tensor([[new[-1]]], device=last_token.device)
             pos = pos + len(new)
         return torch.tensor(out[:max_new_tokens], device=last_token.device)

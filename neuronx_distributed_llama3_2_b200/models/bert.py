@@ -208,4 +208,44 @@ class BertForPreTraining(nn.Module):
         return loss
 
 
-__all__ = ["BertConfig", "BertForPreTraining", "BertLayer", "bert_large", "tiny_bert"]
+def convert_bert_hf_state_dict(hf, config: BertConfig):
+    """HF ``BertForPreTraining`` names -> this model's names, un-sharded.  The separate query / key / value projections
+    are interleaved per head into the fused ``[heads, (q, k, v), D]`` rows, so that a contiguous TP split is a split
+    over heads; the vocabulary is zero-padded up to ``config.vocab_size`` (padding rows never win: bias ``-inf``-like)."""
+    nh, D, H = config.num_attention_heads, config.head_dim, config.hidden_size
+
+    def pad_vocab(t, fill=0.0):
+        extra = config.vocab_size - t.shape[0]
+        if extra <= 0:
+            return t
+        return torch.cat([t, torch.full((extra,) + tuple(t.shape[1:]), fill, dtype=t.dtype)], dim=0)
+
+    out = {"embeddings.word_embeddings.weight": pad_vocab(hf["bert.embeddings.word_embeddings.weight"]),
+           "embeddings.position_embeddings.weight": hf["bert.embeddings.position_embeddings.weight"],
+           "embeddings.token_type_embeddings.weight": hf["bert.embeddings.token_type_embeddings.weight"],
+           "embeddings.LayerNorm.weight": hf["bert.embeddings.LayerNorm.weight"],
+           "embeddings.LayerNorm.bias": hf["bert.embeddings.LayerNorm.bias"],
+           "transform.weight": hf["cls.predictions.transform.dense.weight"],
+           "transform.bias": hf["cls.predictions.transform.dense.bias"],
+           "transform_layernorm.weight": hf["cls.predictions.transform.LayerNorm.weight"],
+           "transform_layernorm.bias": hf["cls.predictions.transform.LayerNorm.bias"],
+           "decoder_bias": pad_vocab(hf["cls.predictions.bias"], fill=-1e4),
+           "pooler.weight": hf["bert.pooler.dense.weight"], "pooler.bias": hf["bert.pooler.dense.bias"],
+           "seq_relationship.weight": hf["cls.seq_relationship.weight"],
+           "seq_relationship.bias": hf["cls.seq_relationship.bias"]}
+    out["decoder.weight"] = out["embeddings.word_embeddings.weight"]
+    for i in range(config.num_hidden_layers):
+        src, dst = f"bert.encoder.layer.{i}.", f"layers.{i}."
+        ws = [hf[src + f"attention.self.{n}.weight"].reshape(nh, D, H) for n in ("query", "key", "value")]
+        bs = [hf[src + f"attention.self.{n}.bias"].reshape(nh, D) for n in ("query", "key", "value")]
+        out[dst + "attention.query_key_value.weight"] = torch.stack(ws, dim=1).reshape(3 * H, H)
+        out[dst + "attention.query_key_value.bias"] = torch.stack(bs, dim=1).reshape(3 * H)
+        for a, b in (("attention.output.dense", "attention.dense"), ("attention.output.LayerNorm", "attention_layernorm"),
+                     ("intermediate.dense", "intermediate"), ("output.dense", "output"),
+                     ("output.LayerNorm", "output_layernorm")):
+            out[dst + b + ".weight"] = hf[src + a + ".weight"]
+            out[dst + b + ".bias"] = hf[src + a + ".bias"]
+    return out
+
+
+__all__ = ["BertConfig", "BertForPreTraining", "BertLayer", "bert_large", "convert_bert_hf_state_dict", "tiny_bert"]

@@ -117,7 +117,67 @@ def tiny_llama(**kw) -> LlamaConfig:
     return LlamaConfig(**base)
 
 
-PRESETS = {"llama3.2-1b": llama3_2_1b, "llama3.2-3b": llama3_2_3b, "llama3.1-8b": llama3_1_8b, "tiny": tiny_llama}
+_LLAMA31_ROPE = {"rope_type": "llama3", "factor": 8.0, "low_freq_factor": 1.0, "high_freq_factor": 4.0,
+                 "original_max_position_embeddings": 8192}
+
+
+def _preset(doc: str, **base):
+    def make(**kw) -> LlamaConfig:
+        cfg = dict(base)
+        cfg.update(kw)
+        return LlamaConfig(**cfg)
+
+    make.__doc__ = doc
+    return make
+
+
+# the other sizes the reference ships configs for (``examples/training/llama/tp_zero1_llama_hf_pretrain/*_config_*`` and
+# ``tp_pp_llama_hf_pretrain/*_config_*``)
+llama2_7b = _preset("Llama-2 7B (reference 7B_config_llama2)", vocab_size=32000, hidden_size=4096, intermediate_size=11008,
+                    num_hidden_layers=32, num_attention_heads=32, num_key_value_heads=32, head_dim=128, rope_theta=10000.0,
+                    rope_scaling=None, max_position_embeddings=4096, tie_word_embeddings=False)
+llama2_13b = _preset("Llama-2 13B (reference 13B_config_llama2)", vocab_size=32000, hidden_size=5120,
+                     intermediate_size=13824, num_hidden_layers=40, num_attention_heads=40, num_key_value_heads=40,
+                     head_dim=128, rope_theta=10000.0, rope_scaling=None, max_position_embeddings=4096,
+                     tie_word_embeddings=False)
+llama2_70b = _preset("Llama-2 70B (reference 70B_config_llama2)", vocab_size=32000, hidden_size=8192,
+                     intermediate_size=28672, num_hidden_layers=80, num_attention_heads=64, num_key_value_heads=8,
+                     head_dim=128, rope_theta=10000.0, rope_scaling=None, max_position_embeddings=4096,
+                     tie_word_embeddings=False)
+llama3_8b = _preset("Llama-3 8B (reference 8B_config_llama3)", hidden_size=4096, intermediate_size=14336,
+                    num_hidden_layers=32, num_attention_heads=32, num_key_value_heads=8, head_dim=128, rope_scaling=None,
+                    max_position_embeddings=8192, tie_word_embeddings=False)
+llama3_70b = _preset("Llama-3 70B (reference 70B_config_llama3)", hidden_size=8192, intermediate_size=28672,
+                     num_hidden_layers=80, num_attention_heads=64, num_key_value_heads=8, head_dim=128, rope_scaling=None,
+                     max_position_embeddings=8192, tie_word_embeddings=False)
+llama3_1_70b = _preset("Llama-3.1 70B (reference 70B_config_llama3.1)", hidden_size=8192, intermediate_size=28672,
+                       num_hidden_layers=80, num_attention_heads=64, num_key_value_heads=8, head_dim=128,
+                       rope_scaling=dict(_LLAMA31_ROPE), tie_word_embeddings=False)
+
+PRESETS = {"llama3.2-1b": llama3_2_1b, "llama3.2-3b": llama3_2_3b, "llama3.1-8b": llama3_1_8b, "tiny": tiny_llama,
+           "llama2-7b": llama2_7b, "llama2-13b": llama2_13b, "llama2-70b": llama2_70b, "llama3-8b": llama3_8b,
+           "llama3-70b": llama3_70b, "llama3.1-70b": llama3_1_70b}
+
+
+def config_from_hf_json(path_or_dict, **overrides) -> LlamaConfig:
+    """An HF ``config.json`` (path or dict) -> ``LlamaConfig``; unknown keys are dropped, ``overrides`` win.  The
+    reference's scripts pass ``--model_path <dir with config.json>``."""
+    import json
+    from dataclasses import fields
+
+    d = path_or_dict
+    if not isinstance(d, dict):
+        import os
+
+        p = os.path.join(d, "config.json") if os.path.isdir(d) else d
+        with open(p) as f:
+            d = json.load(f)
+    known = {f.name for f in fields(LlamaConfig)}
+    kw = {k: v for k, v in d.items() if k in known and k != "torch_dtype"}
+    if isinstance(d.get("torch_dtype"), str):
+        kw["torch_dtype"] = getattr(torch, d["torch_dtype"])
+    kw.update(overrides)
+    return LlamaConfig(**kw)
 
 
 def _init_fn(std: float):

@@ -133,3 +133,53 @@ class MixtralForCausalLM(nn.Module):
                                            cfg.num_experts_per_tok)
             loss = loss + cfg.router_aux_loss_coef * aux
         return loss
+
+
+def convert_mixtral_hf_state_dict(hf, config: MixtralConfig):
+    """HF ``MixtralForCausalLM`` names -> this model's names, un-sharded (reference
+    ``examples/training/mixtral/convert_checkpoints.py``): q/k/v fused into ``qkv_proj.weight_qkv``; the per-expert
+    ``w1`` (gate) / ``w3`` (up) ``[I, H]`` become one ``[E, H, 2I]`` slab, ``w2`` ``[H, I]`` becomes ``[E, I, H]``."""
+    E = config.num_local_experts
+    out = {"embed_tokens.weight": hf["model.embed_tokens.weight"], "norm.weight": hf["model.norm.weight"]}
+    if "lm_head.weight" in hf:
+        out["lm_head.weight"] = hf["lm_head.weight"]
+    for i in range(config.num_hidden_layers):
+        src, dst = f"model.layers.{i}.", f"layers.{i}."
+        out[dst + "self_attn.qkv_proj.weight_qkv"] = torch.cat([hf[src + f"self_attn.{n}_proj.weight"] for n in "qkv"], 0)
+        out[dst + "self_attn.o_proj.weight"] = hf[src + "self_attn.o_proj.weight"]
+        out[dst + "input_layernorm.weight"] = hf[src + "input_layernorm.weight"]
+        out[dst + "post_attention_layernorm.weight"] = hf[src + "post_attention_layernorm.weight"]
+        moe = src + "block_sparse_moe."
+        out[dst + "mlp.router.linear_router.weight"] = hf[moe + "gate.weight"]
+        gate = torch.stack([hf[moe + f"experts.{e}.w1.weight"] for e in range(E)])       # [E, I, H]
+        up = torch.stack([hf[moe + f"experts.{e}.w3.weight"] for e in range(E)])
+        down = torch.stack([hf[moe + f"experts.{e}.w2.weight"] for e in range(E)])       # [E, H, I]
+        out[dst + "mlp.expert_mlps.mlp_op.gate_up_proj.weight"] = torch.cat([gate, up], dim=1).transpose(1, 2).contiguous()
+        out[dst + "mlp.expert_mlps.mlp_op.down_proj.weight"] = down.transpose(1, 2).contiguous()
+    return out
+
+
+def convert_mixtral_state_dict_to_hf(sd, config: MixtralConfig):
+    """Inverse of ``convert_mixtral_hf_state_dict``."""
+    E, I = config.num_local_experts, config.intermediate_size
+    qs, kvs = config.num_attention_heads * config.head_dim, config.num_key_value_heads * config.head_dim
+    out = {"model.embed_tokens.weight": sd["embed_tokens.weight"], "model.norm.weight": sd["norm.weight"]}
+    if "lm_head.weight" in sd:
+        out["lm_head.weight"] = sd["lm_head.weight"]
+    for i in range(config.num_hidden_layers):
+        src, dst = f"layers.{i}.", f"model.layers.{i}."
+        q, k, v = torch.split(sd[src + "self_attn.qkv_proj.weight_qkv"], [qs, kvs, kvs], dim=0)
+        out[dst + "self_attn.q_proj.weight"], out[dst + "self_attn.k_proj.weight"] = q, k
+        out[dst + "self_attn.v_proj.weight"] = v
+        out[dst + "self_attn.o_proj.weight"] = sd[src + "self_attn.o_proj.weight"]
+        out[dst + "input_layernorm.weight"] = sd[src + "input_layernorm.weight"]
+        out[dst + "post_attention_layernorm.weight"] = sd[src + "post_attention_layernorm.weight"]
+        moe = dst + "block_sparse_moe."
+        out[moe + "gate.weight"] = sd[src + "mlp.router.linear_router.weight"]
+        gu = sd[src + "mlp.expert_mlps.mlp_op.gate_up_proj.weight"].transpose(1, 2)          # [E, 2I, H]
+        down = sd[src + "mlp.expert_mlps.mlp_op.down_proj.weight"].transpose(1, 2)           # [E, H, I]
+        for e in range(E):
+            out[moe + f"experts.{e}.w1.weight"] = gu[e, :I].contiguous()
+            out[moe + f"experts.{e}.w3.weight"] = gu[e, I:].contiguous()
+            out[moe + f"experts.{e}.w2.weight"] = down[e].contiguous()
+    return out

@@ -157,6 +157,10 @@ class QuantizedColumnParallel(BaseQuantizeParallelLinear):
                   quantization_per_channel_axis=q_config.get("quantization_per_channel_axis"))
         if mod.bias is not None and mod.bias.device.type != "meta":
             new.bias.data.copy_(mod.bias.data)
+        # a strided shard layout (fused gate|up) must survive the swap: checkpoint sharding reads it from the weight
+        setattr(new.weight, "partition_stride", getattr(mod.weight, "partition_stride", 1))
+        if new.scale_partitioned:
+            setattr(new.scale, "partition_stride", getattr(mod.weight, "partition_stride", 1))
         return new
 
 

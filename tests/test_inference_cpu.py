@@ -447,3 +447,51 @@ def test_weight_layout_transform_between_graphs(tmp_path):
     out = hu.run_weight_layout_transform(wlt, sd)
     assert torch.equal(out["experts"], sd["experts"].transpose(1, 2)) and out["experts"].is_contiguous()
     assert out["dense"] is sd["dense"] and out["norm"] is sd["norm"]
+
+
+def test_family_runners_and_quantized_runner():
+    """``MixtralRunner`` drives the MoE KV-cache model through the same trace / generate path; a quantized Llama runner
+    swaps the decoder linears for int8 weight-only layers, quantizes the float checkpoint on load and stays close to
+    the float model."""
+    from neuronx_distributed_llama3_2_b200.inference import InferenceRunner, MixtralRunner
+    from neuronx_distributed_llama3_2_b200.models import MixtralForCausalLM, tiny_mixtral
+    from neuronx_distributed_llama3_2_b200.quantization.quantization_layers import BaseQuantizeParallelLinear
+
+    torch.manual_seed(0)
+    mcfg = tiny_mixtral(sequence_parallel_enabled=False)
+    mtrain = MixtralForCausalLM(mcfg).eval()
+    msd = {k: v.clone() for k, v in mtrain.state_dict().items()}
+    ic = InferenceConfig(batch_size=2, max_context_length=32, seq_len=64, buckets=[16, 32], use_cuda_graphs=False)
+    r = MixtralRunner(tiny_mixtral(sequence_parallel_enabled=False), ic, checkpoint_loader=lambda: msd,
+                      device=torch.device("cpu"))
+    r.trace()
+    prompts = torch.randint(1, mcfg.vocab_size, (2, 9))
+    out = r.generate(prompts, max_new_tokens=4)
+    seq = prompts[0].clone()
+    for _ in range(4):
+        with torch.no_grad():
+            seq = torch.cat([seq, mtrain(seq.unsqueeze(0)).transpose(0, 1)[0, -1].argmax().reshape(1)])
+    assert torch.equal(out[0], seq)
+
+    cfg, train, _ = _models()
+    sd = {k: v.clone() for k, v in train.state_dict().items()}
+    for qtype in ("per_tensor_symmetric", "per_channel_symmetric"):
+        icq = InferenceConfig(batch_size=2, max_context_length=32, seq_len=64, buckets=[16, 32], use_cuda_graphs=False,
+                              quantized=True, quantization_type=qtype)
+        rq = InferenceRunner(tiny_llama(sequence_parallel_enabled=False), icq, checkpoint_loader=lambda: sd,
+                             device=torch.device("cpu"))
+        qsd = rq.generate_quantized_state_dict(sd)
+        k = "model.layers.0.mlp.down_proj"
+        assert qsd[k + ".weight"].dtype == torch.int8 and k + ".scale" in qsd
+        assert qsd["model.layers.0.self_attn.qkv_proj.weight_qkv"].is_floating_point() and "lm_head.scale" not in qsd
+        with tempfile.TemporaryDirectory() as d:
+            rq.trace(d)
+            assert os.path.exists(os.path.join(d, "weights", "tp0_sharded_checkpoint.safetensors"))
+        n_q = sum(isinstance(m, BaseQuantizeParallelLinear) for m in rq.model.modules())
+        assert n_q == 3 * cfg.num_hidden_layers, n_q                    # o_proj, gate_up_proj, down_proj per layer
+        ids = torch.randint(1, cfg.vocab_size, (2, 16))
+        pos = torch.arange(16).unsqueeze(0).expand(2, 16)
+        _, logits = rq.model.forward_infer(ids, pos, return_logits=True)
+        ref = _full_logits(train, ids)[:, -1]
+        rel = ((logits - ref).norm() / ref.norm()).item()
+        assert rel < 0.05, (qtype, rel)

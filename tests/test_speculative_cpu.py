@@ -53,3 +53,57 @@ def test_medusa_helpers():
     target[0] = torch.tensor([11, 21, 9, 0])                        # target agrees with the first two speculated tokens
     best, n_acc = evaluate_posterior(target, cands, valid=buf["retrieve_indices"] >= 0)
     assert (best, n_acc) == (0, 2)
+
+
+def test_speculation_with_kv_cache_models_equals_target_greedy():
+    """Real graphs: a 1-layer draft and the 2-layer target, each with its own KV cache; the target's
+    ``forward_speculation`` verifies k+1 tokens on top of the cache.  Output == the target's own greedy decoding, for the
+    contiguous and the paged cache."""
+    from neuronx_distributed_llama3_2_b200.inference import InferenceConfig, LlamaInferenceModel
+    from neuronx_distributed_llama3_2_b200.models import LlamaForCausalLM, tiny_llama
+
+    for paged in (False, True):
+        torch.manual_seed(0)
+        ic = dict(batch_size=1, max_context_length=32, seq_len=96, paged_kv=paged, page_size=16)
+        target = LlamaInferenceModel(tiny_llama(sequence_parallel_enabled=False), InferenceConfig(**ic))
+        draft = LlamaInferenceModel(tiny_llama(sequence_parallel_enabled=False, num_hidden_layers=1), InferenceConfig(**ic))
+        sd = LlamaForCausalLM(tiny_llama(sequence_parallel_enabled=False)).state_dict()
+        target.load_state_dict(sd)
+        draft.load_state_dict({k: v for k, v in sd.items() if "layers.1." not in k})      # shares layer 0, embedding, head
+        prompt = torch.randint(1, 512, (1, 12))
+        ref = target.generate(prompt, max_new_tokens=24)[0, 12:]
+        target.init_kv_cache()
+        draft.init_kv_cache()
+        pos = torch.arange(12).unsqueeze(0)
+        first = target.forward_infer(prompt, pos)
+        draft.forward_infer(prompt, pos)
+        # the verify graph agrees with token-by-token decoding on logits, not only on the argmax
+        spec = NeuronSpeculation(lambda t, p: draft.forward_infer(t, p), lambda t, p: target.forward_speculation(t, p),
+                                 speculation_length=3)
+        new = spec.generate(first, torch.tensor([12]), max_new_tokens=23)
+        assert torch.equal(torch.cat([first, new]), ref), (paged, torch.cat([first, new]), ref)
+        assert len(spec.accepted_hist) < 23                       # fewer target calls than tokens
+
+
+def test_runner_speculative_generation():
+    """Target runner traced with ``speculation_length`` gets a third sub-model (the verify graph); assisted generation
+    through the two runners equals the target runner's own ``generate``."""
+    from neuronx_distributed_llama3_2_b200.inference import InferenceConfig, InferenceRunner
+    from neuronx_distributed_llama3_2_b200.models import LlamaForCausalLM, tiny_llama
+
+    torch.manual_seed(0)
+    sd = {k: v.clone() for k, v in LlamaForCausalLM(tiny_llama(sequence_parallel_enabled=False)).state_dict().items()}
+    dsd = {k: v for k, v in sd.items() if "layers.1." not in k}
+    kw = dict(batch_size=1, max_context_length=32, seq_len=96, buckets=[16, 32], use_cuda_graphs=False)
+    target = InferenceRunner(tiny_llama(sequence_parallel_enabled=False), InferenceConfig(speculation_length=3, **kw),
+                             checkpoint_loader=lambda: sd, device=torch.device("cpu"))
+    draft = InferenceRunner(tiny_llama(sequence_parallel_enabled=False, num_hidden_layers=1), InferenceConfig(**kw),
+                            checkpoint_loader=lambda: dsd, device=torch.device("cpu"))
+    target.trace()
+    draft.trace()
+    assert set(target.nxd_model.keys()) == {"context_encoding_model", "token_generation_model", "speculation_model"}
+    prompt = torch.randint(1, 512, (1, 11))
+    ref = target.generate(prompt, max_new_tokens=20)
+    out = target.generate_speculative(draft, prompt, max_new_tokens=20)
+    assert torch.equal(out, ref), (out, ref)
+    assert len(target.last_acceptance) < 19
