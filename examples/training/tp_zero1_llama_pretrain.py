@@ -21,12 +21,14 @@ import torch.distributed as dist
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 
 import neuronx_distributed_llama3_2_b200 as nxd  # noqa: E402
-from neuronx_distributed_llama3_2_b200.models import PRESETS, LlamaForCausalLM  # noqa: E402
+from neuronx_distributed_llama3_2_b200.models import PRESETS, LlamaForCausalLM, config_from_hf_json  # noqa: E402
 from neuronx_distributed_llama3_2_b200.parallel import parallel_state as ps  # noqa: E402
 from neuronx_distributed_llama3_2_b200.parallel.random import model_parallel_manual_seed  # noqa: E402
 from neuronx_distributed_llama3_2_b200.utils.logger import get_logger  # noqa: E402
+from neuronx_distributed_llama3_2_b200.utils.data import DevicePrefetcher, create_llama_pretraining_dataset  # noqa: E402
 from neuronx_distributed_llama3_2_b200.utils.training_utils import (CosineAnnealing, SyntheticTokens, Throughput,  # noqa: E402
-                                                                  TrainingMetrics)
+                                                                  TrainingLogger, TrainingMetrics, get_dtype,
+                                                                  get_param_groups_by_weight_decay)
 
 logger = get_logger()
 
@@ -34,6 +36,12 @@ logger = get_logger()
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--model", default="llama3.2-1b", choices=sorted(PRESETS))
+    ap.add_argument("--model_path", default=None, help="directory with an HF config.json (overrides --model)")
+    ap.add_argument("--data_dir", default=None, help="tokenised dataset: HF datasets directory or flat .npy/.bin token "
+                    "file (examples/training/get_dataset.py); synthetic tokens when omitted")
+    ap.add_argument("--pretrained_weight", default=None, help="sharded checkpoint directory (checkpoint converter output) "
+                    "to start from")
+    ap.add_argument("--tensorboard", type=int, default=0)
     ap.add_argument("--tensor_parallel_size", type=int, default=1)
     ap.add_argument("--seq_len", type=int, default=4096)
     ap.add_argument("--batch_size", type=int, default=1, help="micro batch per DP rank")
@@ -73,13 +81,18 @@ def main():
                                 "use_master_weights_in_ckpt": False},
         activation_checkpoint_config="full" if args.full_activation_checkpoint else None)
     model_parallel_manual_seed(args.seed)
-    cfg = PRESETS[args.model](sequence_parallel_enabled=sp, selective_checkpoint_enabled=bool(args.selective_checkpoint))
+    kw = dict(sequence_parallel_enabled=sp, selective_checkpoint_enabled=bool(args.selective_checkpoint))
+    cfg = config_from_hf_json(args.model_path, **kw) if args.model_path else PRESETS[args.model](**kw)
     if not cuda:
         cfg.torch_dtype = torch.float32
     model = nxd.initialize_parallel_model(nxd_config, lambda: LlamaForCausalLM(cfg, device=device), device=device)
     model.train()
-    optimizer = nxd.initialize_parallel_optimizer(nxd_config, torch.optim.AdamW, model.parameters(), lr=args.lr,
-                                                  betas=(0.9, 0.95), weight_decay=args.weight_decay)
+    if args.pretrained_weight:
+        w = os.path.abspath(args.pretrained_weight)      # <dir>/<tag> as written by the checkpoint converter
+        nxd.load_checkpoint(os.path.dirname(w), tag=os.path.basename(w), model=model, strict=False)
+    optimizer = nxd.initialize_parallel_optimizer(nxd_config, torch.optim.AdamW,
+                                                  get_param_groups_by_weight_decay(model, args.weight_decay), lr=args.lr,
+                                                  betas=(0.9, 0.95))
     scheduler = CosineAnnealing(optimizer, max_steps=args.max_steps, warmup_steps=args.warmup_steps, min_lr=args.lr * 0.1)
 
     step0 = 0
@@ -92,7 +105,13 @@ def main():
 
     dp = ps.get_data_parallel_size() if ps.model_parallel_is_initialized() else 1
     dp_rank = ps.get_data_parallel_rank() if ps.model_parallel_is_initialized() else 0
-    data = SyntheticTokens(cfg.vocab_size, args.batch_size, args.seq_len, device, seed=args.seed + dp_rank)
+    if args.data_dir:
+        loader, _ = create_llama_pretraining_dataset(args.data_dir, args.batch_size, dp, dp_rank, args.seed,
+                                                     seq_len=args.seq_len)
+        data = iter(DevicePrefetcher(loader, device))
+    else:
+        data = SyntheticTokens(cfg.vocab_size, args.batch_size, args.seq_len, device, seed=args.seed + dp_rank)
+    tb = TrainingLogger(args, world, get_dtype(model)) if (args.tensorboard and ps.is_global_rank_zero()) else None
     throughput = Throughput(args.batch_size, dp, args.grad_accum_usteps, logging_interval=args.logging_interval)
     metrics = TrainingMetrics(os.path.join(args.output_dir, "metrics.json"))
     os.makedirs(args.output_dir, exist_ok=True)
@@ -102,8 +121,9 @@ def main():
         optimizer.zero_grad()
         running = 0.0
         for _ in range(args.grad_accum_usteps):
-            ids = next(data)
-            loss = model(ids, labels=ids) / args.grad_accum_usteps
+            batch = next(data)
+            ids, labels = (batch["input_ids"], batch["labels"]) if isinstance(batch, dict) else (batch, batch)
+            loss = model(ids, labels=labels) / args.grad_accum_usteps
             loss.backward()
             running += float(loss.detach())
         optimizer.step()
@@ -114,12 +134,16 @@ def main():
             if ps.is_global_rank_zero():
                 logger.info("step %d loss %.4f grad-norm %.3f lr %.3e throughput %.2f seq/s (%.0f tokens/s)", step + 1,
                             running, float(optimizer.grad_norm), scheduler.get_last_lr()[0], seqs, seqs * args.seq_len)
+                if tb is not None:
+                    tb.log(0, step + 1, running, scheduler.get_last_lr()[0], seqs, float(optimizer.grad_norm))
         if args.checkpoint_dir and args.checkpoint_freq and (step + 1) % args.checkpoint_freq == 0:
             nxd.save_checkpoint(args.checkpoint_dir, f"step_{step + 1}", model=model, optimizer=optimizer,
                                 scheduler=scheduler, user_content={"total_steps": step + 1},
                                 use_xser=bool(args.use_xser), num_kept_ckpts=args.num_kept_checkpoint,
                                 async_save=bool(args.async_checkpoint))
     nxd.finalize_checkpoint()
+    if tb is not None:
+        tb.close()
     if ps.is_global_rank_zero():
         skip = max(1, 10 // args.logging_interval)
         steady = tps_hist[skip:] or tps_hist

@@ -1,4 +1,4 @@
-from .llama import (LlamaConfig, LlamaForCausalLM, LlamaModel, PRESETS, config_from_hf_json, flops_per_token,  # noqa: F401
+from .llama import (LlamaConfig, LlamaForCausalLM, LlamaModel, PRESETS, config_from_hf_json, config_from_json, flops_per_token,  # noqa: F401
                     llama2_7b, llama2_13b, llama2_70b, llama3_1_8b, llama3_1_70b, llama3_2_1b, llama3_2_3b, llama3_8b,
                     llama3_70b, tiny_llama)
 from .mixtral import (MixtralConfig, MixtralForCausalLM, convert_mixtral_hf_state_dict,  # noqa: F401

@@ -159,25 +159,29 @@ PRESETS = {"llama3.2-1b": llama3_2_1b, "llama3.2-3b": llama3_2_3b, "llama3.1-8b"
            "llama3-70b": llama3_70b, "llama3.1-70b": llama3_1_70b}
 
 
-def config_from_hf_json(path_or_dict, **overrides) -> LlamaConfig:
-    """An HF ``config.json`` (path or dict) -> ``LlamaConfig``; unknown keys are dropped, ``overrides`` win.  The
-    reference's scripts pass ``--model_path <dir with config.json>``."""
+def config_from_json(config_cls, path_or_dict, **overrides):
+    """An HF-style ``config.json`` (path, directory or dict) -> ``config_cls`` (any config dataclass of this package);
+    unknown keys are dropped, ``overrides`` win."""
     import json
+    import os
     from dataclasses import fields
 
     d = path_or_dict
     if not isinstance(d, dict):
-        import os
-
         p = os.path.join(d, "config.json") if os.path.isdir(d) else d
         with open(p) as f:
             d = json.load(f)
-    known = {f.name for f in fields(LlamaConfig)}
+    known = {f.name for f in fields(config_cls)}
     kw = {k: v for k, v in d.items() if k in known and k != "torch_dtype"}
     if isinstance(d.get("torch_dtype"), str):
         kw["torch_dtype"] = getattr(torch, d["torch_dtype"])
     kw.update(overrides)
-    return LlamaConfig(**kw)
+    return config_cls(**kw)
+
+
+def config_from_hf_json(path_or_dict, **overrides) -> LlamaConfig:
+    """``config_from_json`` for the Llama family.  The reference's scripts pass ``--model_path <dir with config.json>``."""
+    return config_from_json(LlamaConfig, path_or_dict, **overrides)
 
 
 def _init_fn(std: float):

@@ -73,7 +73,10 @@ class ExpertMLPs(torch.nn.Module):
     # -- full capacity, dropless -----------------------------------------------------------------------------
     def forward_all_experts(self, hidden_states, expert_affinities, expert_index):
         if ps.get_expert_model_parallel_size() > 1:
-            raise NotImplementedError("expert parallelism needs the capacity-factor path (reference :145-146)")
+            # the reference refuses this combination (:145-146).  With experts spread over ranks the dispatch needs a
+            # fixed per-expert buffer, so run the capacity path with room for EVERY token (capacity = T): nothing is
+            # dropped, the result equals the dropless one.
+            return self.forward_capacity_factor(hidden_states, expert_affinities, expert_index, full_capacity=True)
         T, H = hidden_states.shape
         mask = self.get_expert_mask(expert_index)
         aff = self.get_expert_affinities_masked(expert_affinities, mask)                 # (T, E)
@@ -97,10 +100,10 @@ class ExpertMLPs(torch.nn.Module):
         return output
 
     # -- fixed capacity with token dropping ------------------------------------------------------------------
-    def forward_capacity_factor(self, hidden_states, expert_affinities, expert_index):
+    def forward_capacity_factor(self, hidden_states, expert_affinities, expert_index, full_capacity: bool = False):
         T, H = hidden_states.shape
         E, k = self.num_experts, self.top_k
-        capacity = min(math.ceil(T * k * self.capacity_factor / E), T)
+        capacity = T if full_capacity else min(math.ceil(T * k * self.capacity_factor / E), T)
         mask = self.get_expert_mask(expert_index)                                         # (T, E)
         position = torch.cumsum(mask, dim=0)                                              # 1-based slot in expert
         mask = mask.masked_fill(position > capacity, 0)                                   # drop the overflow

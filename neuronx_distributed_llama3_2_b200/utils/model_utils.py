@@ -104,22 +104,47 @@ def reinit_model(model: nn.Module, device, param_init_fn: Optional[Callable[[nn.
                 mod._buffers[name] = torch.empty_like(b, device=device)
     retie_shared_weights(shared)
     for mod in model.modules():
-        if param_init_fn is not None:
-            param_init_fn(mod, device)
-        elif hasattr(mod, "init_weight_cpu_or_device"):
-            mod.init_weight_cpu_or_device()
-        elif hasattr(mod, "_init_weight") and hasattr(mod, "weight_partition_dim"):
-            # re-run the TP-aware init on the now-real tensor; tags are already set
-            w = mod.weight
-            for tag in ("tensor_model_parallel", "partition_dim", "partition_stride"):
-                if hasattr(w, tag):
-                    delattr(w, tag)
-            mod._init_weight(w, mod.weight_partition_dim)
+        (param_init_fn or default_param_init_fn)(mod, device)
+
+
+def default_param_init_fn(mod: nn.Module, device=None) -> None:
+    """Initialise ONE module's own (already materialised) parameters: the ``param_init_fn`` to put into
+    ``model_init_config`` with ``meta_device_init`` when the model has no special needs (the reference's examples carry
+    their own ``init_weights(module, device)``, e.g. ``run_llama_nxd.py``).  TP-aware inits draw the full-size master
+    weight and keep this rank's slice, norms get ones / zeros, anything else falls back to ``reset_parameters``."""
+    own = [p for p in mod.parameters(recurse=False)]
+    if not own or any(p.device.type == "meta" for p in own) or all(p.numel() == 0 for p in own):
+        return          # nothing here, not materialised yet, or released (another pipeline stage owns this module)
+    name = type(mod).__name__
+
+    def strip(w):      # the TP-aware initialisers tag the tensor themselves and refuse one that is tagged already
+        for tag in ("tensor_model_parallel", "partition_dim", "partition_stride", "num_partitions"):
+            if hasattr(w, tag):
+                delattr(w, tag)
+
+    if hasattr(mod, "init_weight_cpu_or_device"):
+        strip(mod.weight)
+        mod.init_weight_cpu_or_device()
+    elif hasattr(mod, "initialize_weight_biases"):            # GQAQKVColumnParallelLinear
+        mod.initialize_weight_biases()
+    elif hasattr(mod, "_init_weight") and hasattr(mod, "weight_partition_dim"):
+        # re-run the TP-aware init on the now-real tensor; tags are already set
+        w = mod.weight
+        strip(w)
+        mod._init_weight(w, mod.weight_partition_dim)
+        if getattr(mod, "bias", None) is not None:
+            with torch.no_grad():
+                mod.bias.zero_()
+    elif name.endswith("Norm") and not hasattr(mod, "reset_parameters"):
+        with torch.no_grad():
+            if getattr(mod, "weight", None) is not None:
+                mod.weight.fill_(1.0)
             if getattr(mod, "bias", None) is not None:
-                with torch.no_grad():
-                    mod.bias.zero_()
-        elif hasattr(mod, "reset_parameters") and any(True for _ in mod.parameters(recurse=False)):
-            mod.reset_parameters()
+                mod.bias.zero_()
+    elif hasattr(mod, "init_weight_cpu") and name.endswith("Router"):
+        mod.init_weight_cpu()
+    elif hasattr(mod, "reset_parameters"):
+        mod.reset_parameters()
 
 
 def move_model_to_device(model: nn.Module, device) -> nn.Module:

@@ -129,3 +129,155 @@ class SyntheticTokens:
         out = self._next
         self._prefetch()
         return out
+
+
+# -- the remaining helpers of the reference's example utilities (``examples/training/llama/training_utils.py``, ``lr.py``) ----
+class WarmupAnnealHoldPolicy(torch.optim.lr_scheduler.LRScheduler):
+    """Base schedule: linear warm-up for ``warmup_steps`` (or ``warmup_ratio * max_steps``), a decay phase implemented by
+    ``_get_lr(step)`` in subclasses, then ``min_lr`` held for ``constant_steps`` (reference ``lr.py:25-112``)."""
+
+    def __init__(self, optimizer, *, max_steps: int, warmup_steps: Optional[int] = None, warmup_ratio: Optional[float] = None,
+                 constant_steps: Optional[int] = None, constant_ratio: Optional[float] = None, min_lr: float = 0.0,
+                 last_epoch: int = -1):
+        assert not (warmup_steps is not None and warmup_ratio is not None), "give warmup_steps OR warmup_ratio"
+        assert not (constant_steps is not None and constant_ratio is not None), "give constant_steps OR constant_ratio"
+        self.max_steps, self.min_lr = max_steps, min_lr
+        self.warmup_steps = warmup_steps if warmup_steps is not None else int((warmup_ratio or 0.0) * max_steps)
+        self.constant_steps = constant_steps if constant_steps is not None else int((constant_ratio or 0.0) * max_steps)
+        self.decay_steps = max_steps - (self.constant_steps + self.warmup_steps)
+        super().__init__(optimizer, last_epoch)
+
+    def get_lr(self):
+        step = self.last_epoch
+        if self.warmup_steps > 0 and step <= self.warmup_steps:
+            return [base * (step + 1) / (self.warmup_steps + 1) for base in self.base_lrs]
+        if self.constant_steps > 0 and self.warmup_steps + self.decay_steps < step <= self.max_steps:
+            return [self.min_lr for _ in self.base_lrs]
+        if step > self.max_steps:
+            return [self.min_lr for _ in self.base_lrs]
+        return self._get_lr(step)
+
+    def _get_lr(self, step: int):
+        return list(self.base_lrs)
+
+
+def get_learning_rate_scheduler(optimizer, args, last_epoch: int = -1) -> CosineAnnealing:
+    """``CosineAnnealing`` from ``args.max_steps / min_lr / warmup_steps / constant_steps`` (reference ``:65-74``)."""
+    return CosineAnnealing(optimizer, max_steps=args.max_steps, min_lr=getattr(args, "min_lr", 0.0),
+                           warmup_steps=getattr(args, "warmup_steps", 0),
+                           constant_steps=getattr(args, "constant_steps", 0), last_epoch=last_epoch)
+
+
+def get_param_groups_by_weight_decay(model, weight_decay: float = 0.01) -> List[Dict[str, Any]]:
+    """Two groups: weights with decay; biases and norm scales without (reference ``:77-96``).  A partitioned pipeline
+    model contributes its LOCAL parameters only."""
+    if getattr(model, "partitioned", False) and hasattr(model, "local_named_parameters"):
+        named = list(model.local_named_parameters())
+    else:
+        named = list(model.named_parameters())
+    no_decay = ("bias", "LayerNorm", "layernorm", "layer_norm", "norm.weight")
+
+    def is_plain(n, p):          # by name as the reference, and every 1-D tensor (norm scales, biases) whatever its name
+        return p.dim() <= 1 or any(k in n for k in no_decay)
+
+    decay = [p for n, p in named if p.requires_grad and not is_plain(n, p)]
+    plain = [p for n, p in named if p.requires_grad and is_plain(n, p)]
+    return [{"params": decay, "weight_decay": weight_decay}, {"params": plain, "weight_decay": 0.0}]
+
+
+def create_partition(num_hidden_layers: int, pipeline_parallel_size: int, prefix: str = "model.layers.") -> List[str]:
+    """Names of the layers AFTER which the pipeline is cut: even split, remainder to the later stages (reference
+    ``:210-221``)."""
+    from ..pipeline.partition import create_partitions
+
+    return [f"{prefix}{i}" for i in create_partitions(pipeline_parallel_size, num_hidden_layers)]
+
+
+def get_sin_cos_matrix(config):
+    """``(sin, cos)`` rotary tables ``[max_position_embeddings, head_dim / 2]`` in fp32 (reference ``:224-232``)."""
+    head_dim = getattr(config, "head_dim", None) or config.hidden_size // config.num_attention_heads
+    base = getattr(config, "rope_theta", 10000.0)
+    inv_freq = 1.0 / (base ** (torch.arange(0, head_dim, 2).float() / head_dim))
+    t = torch.arange(config.max_position_embeddings, dtype=torch.float32)
+    freqs = torch.outer(t, inv_freq)
+    return freqs.sin(), freqs.cos()
+
+
+def get_dtype(model) -> str:
+    """``torch.float32`` / ``torch.bfloat16`` ... of the model's parameters; with master weights kept by the optimizer
+    the model dtype is what the forward runs in (reference ``:235-246``)."""
+    cfg = getattr(model, "nxd_config", None) or {}
+    if cfg.get("mixed_precision_config", {}).get("use_master_weights") and torch.cuda.is_available():
+        return "torch.bfloat16"
+    p = next(iter(model.parameters()), None)
+    return str(p.dtype) if p is not None else "torch.float32"
+
+
+def print_logs(loss, global_norm, args, throughput, logger, total_steps: int, current_lr: float,
+               input_ids: torch.Tensor, start: float) -> None:
+    """One training log line + TensorBoard scalars (reference ``:249-252``).  ``throughput`` is the seq/s number or a
+    ``Throughput`` meter, ``logger`` a ``TrainingLogger``."""
+    tps = throughput.get_throughput() if hasattr(throughput, "get_throughput") else float(throughput)
+    gn = float(global_norm) if global_norm is not None else None
+    logger.log(0, total_steps, float(loss), current_lr, tps, gn)
+
+
+def load_events(event_file: str) -> Dict[str, Any]:
+    """Scalars of a TensorBoard event file, ``{tag: [ScalarEvent, ...]}`` (reference ``tp_zero1_llama_hf_pretrain/logger.py:11-19``)."""
+    from tensorboard.backend.event_processing.event_accumulator import EventAccumulator
+
+    acc = EventAccumulator(event_file)
+    acc.Reload()
+    return {tag: acc.Scalars(tag) for tag in acc.Tags()["scalars"]}
+
+
+class TrainingLogger:
+    """Console line + TensorBoard scalars ``step loss / learning rate / throughput / grad-norm`` under a run directory
+    named after the hyper-parameters (reference ``tp_zero1_llama_hf_pretrain/logger.py:22-75``).  Create it on the rank
+    that should log (global rank 0, or the last PP stage's dp0/tp0 rank)."""
+
+    def __init__(self, args, world_size: int, model_dtype: str):
+        self.throughputs: List[float] = []
+        run = (f"nxd_tblogs_{time.strftime('%m%d%y_%H%M')}_{str(model_dtype).replace('torch.', '')}_w{world_size}"
+               f"_lr{getattr(args, 'lr', 0)}_bs{getattr(args, 'batch_size', 0)}_acc{getattr(args, 'grad_accum_usteps', 1)}"
+               f"_warmup{getattr(args, 'warmup_steps', 0)}_max{getattr(args, 'max_steps', 0)}_{self.get_instance_type()}")
+        self.log_dir = os.path.join(getattr(args, "output_dir", "."), run)
+        try:
+            from torch.utils.tensorboard import SummaryWriter
+
+            self.tb = SummaryWriter(self.log_dir)
+        except Exception:  # noqa: BLE001 - tensorboard is optional
+            self.tb = None
+
+    @staticmethod
+    def get_instance_type() -> str:
+        if torch.cuda.is_available():
+            return torch.cuda.get_device_name(0).replace(" ", "_")
+        return os.environ.get("HOSTNAME", "cpu")
+
+    def log(self, epoch: int, step: int, step_loss: float, learning_rate: float, throughput: float,
+            grad_norm: Optional[float] = None) -> None:
+        gn = f"grad-norm : {grad_norm:.4f}" if grad_norm is not None else ""
+        print(f"LOG {time.asctime()} - ({epoch}, {step}) step_loss : {step_loss:.4f} learning_rate : {learning_rate:.2e} "
+              f"throughput : {throughput:.2f} seq/s {gn}", flush=True)
+        if self.tb is not None:
+            self.tb.add_scalar("step loss", step_loss, step)
+            self.tb.add_scalar("learning rate", learning_rate, step)
+            self.tb.add_scalar("throughput", throughput, step)
+            if grad_norm is not None:
+                self.tb.add_scalar("grad-norm", grad_norm, step)
+        self.throughputs.append(throughput)
+
+    def close(self) -> None:
+        if self.tb is not None:
+            self.tb.flush()
+            self.tb.close()
+
+
+Logger = TrainingLogger  # the reference's example class name
+
+
+def get_mixed_precision_config(use_gpu_compatible_precision) -> Dict[str, bool]:
+    """fp32 master weights + fp32 gradient accumulation when GPU-compatible precision is requested (reference ``:354-359``)."""
+    on = bool(use_gpu_compatible_precision)
+    return {"use_master_weights": on, "use_fp32_grad_acc": on, "use_master_weights_in_ckpt": False}

@@ -210,3 +210,58 @@ def test_megatron_style_round_trip(tmp_path):
     CheckpointConverterBase.run(["--input_dir", str(tmp_path / "sh"), "--output_dir", str(tmp_path / "full"), "--convert_to_full_state"] + common)
     full = torch.load(tmp_path / "full" / "checkpoint.pt", weights_only=False)
     assert set(full) == set(meg) and all(torch.equal(full[k], meg[k]) for k in meg)
+
+
+def test_mixtral_converter_tp_pp_ep_round_trip(tmp_path):
+    """HF Mixtral names -> (tp 2, pp 2, ep 2) shards cut by the model's own parameter tags -> back, bit-exact; every
+    shard has exactly the local shapes the parallel model allocates at that coordinate."""
+    from neuronx_distributed_llama3_2_b200.models import (MixtralForCausalLM, convert_mixtral_state_dict_to_hf,
+                                                          tiny_mixtral)
+    from neuronx_distributed_llama3_2_b200.scripts.checkpoint_converter_moe import (CheckpointConverterMixtral,
+                                                                                      mock_parallel_state)
+
+    torch.manual_seed(0)
+    cfg = tiny_mixtral(sequence_parallel_enabled=False, num_hidden_layers=4)
+    full_model = MixtralForCausalLM(cfg)
+    hf = convert_mixtral_state_dict_to_hf(full_model.state_dict(), cfg)
+    conv = CheckpointConverterMixtral(cfg, tp_size=2, pp_size=2, ep_size=2)
+    out = str(tmp_path / "sharded")
+    conv.convert_from_full_state(hf, out)
+    seen = {}
+    for e in range(2):
+        for t in range(2):
+            with mock_parallel_state(2, t, 2, e), torch.device("meta"):
+                local = MixtralForCausalLM(cfg, device="meta").state_dict()
+            merged = {}
+            for s in range(2):
+                part = torch.load(conv.shard_file(out, t, s, e), weights_only=False)
+                assert all(("layers.0." in k or "layers.1." in k or "embed" in k) == (s == 0) for k in part
+                           if "layers." in k or "embed" in k), (s, list(part))
+                merged.update(part)
+            assert set(merged) == set(local)
+            for k, v in merged.items():
+                assert tuple(v.shape) == tuple(local[k].shape), (k, v.shape, local[k].shape)
+            seen[(e, t)] = merged
+    w = full_model.state_dict()["layers.2.mlp.expert_mlps.mlp_op.down_proj.weight"]          # [E, I, H]: EP dim 0, TP dim 1
+    I = w.shape[1]
+    torch.testing.assert_close(seen[(1, 0)]["layers.2.mlp.expert_mlps.mlp_op.down_proj.weight"], w[2:, : I // 2])
+    gu = full_model.state_dict()["layers.2.mlp.expert_mlps.mlp_op.gate_up_proj.weight"]      # [E, H, 2I], stride 2 on dim 2
+    g, u = gu.chunk(2, dim=2)
+    torch.testing.assert_close(seen[(0, 1)]["layers.2.mlp.expert_mlps.mlp_op.gate_up_proj.weight"],
+                               torch.cat([g[:2, :, I // 2:], u[:2, :, I // 2:]], dim=2))
+    back = conv.convert_to_full_state(out)
+    assert set(back) == set(hf) and all(torch.equal(back[k], hf[k]) for k in hf)
+    # CLI
+    import json
+    cfgp = tmp_path / "config.json"
+    cfgp.write_text(json.dumps({"vocab_size": 512, "hidden_size": 128, "intermediate_size": 256, "num_hidden_layers": 4,
+                                "num_attention_heads": 4, "num_key_value_heads": 2, "head_dim": 32, "num_local_experts": 4,
+                                "num_experts_per_tok": 2, "tie_word_embeddings": False, "max_position_embeddings": 512}))
+    torch.save(hf, tmp_path / "hf.pt")
+    common = ["--config", str(cfgp), "--tp_size", "2", "--ep_size", "2"]
+    CheckpointConverterMixtral.run(["--input_dir", str(tmp_path / "hf.pt"), "--output_dir", str(tmp_path / "s2"),
+                                    "--convert_from_full_state", "--save_xser"] + common)
+    CheckpointConverterMixtral.run(["--input_dir", str(tmp_path / "s2"), "--output_dir", str(tmp_path / "f2"),
+                                    "--convert_to_full_state"] + common)
+    again = torch.load(tmp_path / "f2" / "checkpoint.pt", weights_only=False)
+    assert all(torch.equal(again[k], hf[k]) for k in hf)

@@ -138,6 +138,12 @@ def _ep_worker(rank, world):
     torch.testing.assert_close(out.reshape(T, 32), ref, atol=1e-4, rtol=1e-4)
     out.sum().backward()
     assert moe.expert_mlps.mlp_op.down_proj.weight.grad is not None
+    # dropless (capacity_factor None) with experts spread over EP ranks: runs as capacity = T, nothing is dropped
+    dropless = _build(E=4, k=2, cf=None)
+    dropless.train()
+    dropless.load_state_dict(moe.state_dict())
+    ref2, _, _ = _golden(x.reshape(T, 32), full["router"], full["gate_up"], full["down"], 2, True, capacity=None)
+    torch.testing.assert_close(dropless(x)[0].reshape(T, 32), ref2, atol=1e-4, rtol=1e-4)
 
 
 def _build_full_weights():
