@@ -82,7 +82,7 @@ def token_batches(args, vocab_size: int, device) -> Iterator:
     return ({"input_ids": ids, "labels": ids} for ids in synth)
 
 
-def fit(args, nxd_config, model, batches: Iterator, step_fn: Optional[Callable] = None) -> float:
+def fit(args, nxd_config, model, batches: Iterator, step_fn: Optional[Callable] = None, teardown: bool = True) -> float:
     """Optimizer + schedule + (resume) + step loop.  ``step_fn(model, batch) -> loss`` runs forward AND backward of one
     micro batch, scaling the loss by ``1 / grad_accum_usteps`` before ``backward`` (default: ``model(**batch)``; pipeline
     models go through ``run_train``)."""
@@ -150,6 +150,6 @@ def fit(args, nxd_config, model, batches: Iterator, step_fn: Optional[Callable] 
         m.store_metrics([m.metric("Final loss", running, ""), m.metric("Time to train", (time.time() - t0) / 60.0, "minutes"),
                          m.metric("Average throughput", sum(steady) / len(steady), "seq/s"),
                          m.metric("Peak throughput", max(hist), "seq/s")])
-    if dist.is_initialized():
+    if teardown and dist.is_initialized():      # teardown=False: the caller still needs the groups (e.g. evaluation)
         dist.destroy_process_group()
     return running
