@@ -171,20 +171,22 @@ def is_pjrt_device() -> bool:
     return False
 
 
-def verify_casted_dtype(value) -> None:
-    """Under autocast, check that every tensor inside ``value`` already has the autocast dtype (reference
-    ``utils.py:249-266``; used after ``cast_if_autocast_enabled``)."""
+def verify_casted_dtype(value, _device_type=None) -> None:
+    """Under autocast, check that every floating tensor inside ``value`` already has the autocast dtype (reference
+    ``utils.py:249-266``; used after ``cast_if_autocast_enabled``).  Autocast is looked up for the device type of the
+    tensor itself (CUDA and CPU autocast are separate switches in torch)."""
     import collections.abc
 
-    if not torch.is_autocast_enabled():
-        return
-    want = torch.get_autocast_gpu_dtype()
     if isinstance(value, torch.Tensor):
-        assert not value.is_floating_point() or value.dtype == want, f"expected {want}, got {value.dtype}"
+        dev = _device_type or value.device.type
+        if not torch.is_autocast_enabled(dev) or not value.is_floating_point():
+            return
+        want = torch.get_autocast_dtype(dev)
+        assert value.dtype == want, f"Datatype of tensor is expected to be {want}, got {value.dtype} instead"
     elif isinstance(value, collections.abc.Mapping):
         for k, v in value.items():
-            verify_casted_dtype(k)
-            verify_casted_dtype(v)
-    elif isinstance(value, (list, tuple)):
+            verify_casted_dtype(k, _device_type)
+            verify_casted_dtype(v, _device_type)
+    elif isinstance(value, (list, tuple, set)):
         for v in value:
-            verify_casted_dtype(v)
+            verify_casted_dtype(v, _device_type)

@@ -15,10 +15,10 @@ class PostPartitionHooks:
             raise TypeError("hook must be callable")
         self.hooks.append((callable_function, tuple(func_args), dict(func_kwargs or {})))
 
-    def execute_all_hooks(self, model: Any = None) -> None:
-        for fn, args, kwargs in self.hooks:
-            fn(*args, **kwargs)
-        self.hooks.clear()
+    def execute_all_hooks(self, model: Any = None) -> List[Any]:
+        """Run the hooks in registration order, forget them, return their results."""
+        pending, self.hooks = self.hooks, []
+        return [fn(*args, **kwargs) for fn, args, kwargs in pending]
 
 
 hooks = PostPartitionHooks()

@@ -8,17 +8,19 @@ from __future__ import annotations
 import logging
 import os
 import sys
+from functools import lru_cache, wraps
+from typing import Callable, Optional
 
+# "trace" opens the DEBUG level as in the reference; ``logger.trace(...)`` lines are emitted (at DEBUG) only then
 _LEVELS = {
-    "trace": logging.DEBUG - 5,
+    "trace": logging.DEBUG,
     "debug": logging.DEBUG,
     "info": logging.INFO,
     "warning": logging.WARNING,
     "error": logging.ERROR,
     "fatal": logging.FATAL,
-    "off": logging.FATAL + 10,
+    "off": logging.FATAL + 1,
 }
-logging.addLevelName(_LEVELS["trace"], "TRACE")
 
 
 class PackagePathFilter(logging.Filter):
@@ -37,20 +39,40 @@ class PackagePathFilter(logging.Filter):
 _LOGGERS = {}
 
 
+@lru_cache
 def get_log_level() -> int:
+    """``NXD_LOG_LEVEL`` -> ``logging`` level; cached (``get_log_level.cache_clear()`` after changing the variable)."""
     name = os.environ.get("NXD_LOG_LEVEL", "info").lower()
     if name not in _LEVELS:
-        raise ValueError(f"NXD_LOG_LEVEL={name!r} is not one of {sorted(_LEVELS)}")
+        raise ValueError(f"Allowed NXD_LOG_LEVELS are: info, trace, debug, warning, error, fatal, off. Got: {name}")
     return _LEVELS[name]
 
 
+def _trace_enabled() -> bool:
+    return os.environ.get("NXD_LOG_LEVEL", "info").lower() == "trace"
+
+
 def _is_rank0() -> bool:
+    """Global rank 0: the process group's rank once it exists, the launcher's ``RANK`` variable before that."""
     try:
         import torch.distributed as dist
 
-        return (not dist.is_available()) or (not dist.is_initialized()) or dist.get_rank() == 0
-    except Exception:
-        return True
+        if dist.is_available() and dist.is_initialized():
+            return dist.get_rank() == 0
+    except Exception:  # noqa: BLE001
+        pass
+    return int(os.environ.get("RANK", "0")) == 0
+
+
+def _rank0_only(fn: Callable, default=None, **extra_kwargs) -> Callable:
+    """``fn`` that runs on global rank 0 only and returns ``default`` elsewhere (reference ``logger.py:91-112``)."""
+    @wraps(fn)
+    def wrapped_fn(*args, **kwargs):
+        if _is_rank0():
+            return fn(*args, **{**kwargs, **extra_kwargs})
+        return default
+
+    return wrapped_fn
 
 
 class _Rank0Logger:
@@ -64,8 +86,8 @@ class _Rank0Logger:
         return (not self._rank0_only) or _is_rank0()
 
     def trace(self, msg, *a, **k):
-        if self._ok():
-            self._inner.log(_LEVELS["trace"], msg, *a, **k)
+        if self._ok() and _trace_enabled():
+            self._inner.debug(msg, *a, **k)
 
     def __getattr__(self, name):
         attr = getattr(self._inner, name)
@@ -90,7 +112,11 @@ def get_logger(name: str = "nxd_b200", rank0_only: bool = True) -> _Rank0Logger:
         handler.setFormatter(logging.Formatter(fmt))
         inner.addHandler(handler)
         inner.propagate = False
-    inner.setLevel(get_log_level())
+    level = get_log_level()
+    if level > logging.FATAL:
+        inner.disabled = True           # NXD_LOG_LEVEL=off
+    else:
+        inner.setLevel(level)
     out = _Rank0Logger(inner, rank0_only)
     _LOGGERS[key] = out
     return out

@@ -9,7 +9,7 @@ from __future__ import annotations
 import base64
 import pickle
 from dataclasses import dataclass
-from typing import Any, List, Optional, Tuple
+from typing import Any, List, NamedTuple, Optional, Tuple
 
 import torch
 
@@ -22,16 +22,15 @@ def unpickle_from_str(s: str) -> Any:
     return pickle.loads(base64.b64decode(s.encode("ascii")))
 
 
-@dataclass
-class TensorMeta:
+class TensorMeta(NamedTuple):
+    """What the receiving side needs to allocate the buffer of one tensor that travels separately from the pickled
+    structure (reference ``utils/serialization.py:73-83``)."""
+
     tensor_index: int
     dtype: torch.dtype
-    shape: Tuple[int, ...]
+    shape: torch.Size
     requires_grad: bool
-    device: Optional[str] = None
-
-    def __repr__(self):
-        return f"TensorMeta(idx={self.tensor_index}, {self.dtype}, {tuple(self.shape)}, grad={self.requires_grad})"
+    device: Optional[torch.device] = None
 
 
 class _Stub:
@@ -52,7 +51,7 @@ class SerializationManager:
             if isinstance(x, torch.Tensor):
                 idx = len(tensors)
                 tensors.append(x)
-                metas.append(TensorMeta(idx, x.dtype, tuple(x.shape), x.requires_grad, str(x.device)))
+                metas.append(TensorMeta(idx, x.dtype, x.shape, x.requires_grad, x.device))
                 return _Stub(idx)
             if isinstance(x, dict):
                 return type(x)((k, walk(v)) for k, v in x.items())
