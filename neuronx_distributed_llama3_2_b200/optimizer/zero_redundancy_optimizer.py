@@ -237,6 +237,35 @@ class NeuronZero1Optimizer(torch.optim.Optimizer):
 
     # ------------------------------------------------------------------------------------------
     @property
+    def base_optimizer(self) -> torch.optim.Optimizer:
+        """The optimizer over this rank's fp32 master shards, as ``optimizer_class`` (the reference's ZeRO-1 wraps such
+        an instance and exposes it under this name).  Non-fused classes really step through it; for the fused AdamW
+        path it is a VIEW: its parameters are the master shards and its ``exp_avg / exp_avg_sq`` state tensors alias the
+        flat moment buffers, so ``base_optimizer.state_dict()`` and hyper-parameter reads show the live values."""
+        self.init_zero()
+        if self.inner is not None:
+            return self.inner
+        view = getattr(self, "_base_view", None)
+        if view is None:
+            groups = []
+            for gi, group in enumerate(self.param_groups):
+                g = {k: v for k, v in group.items() if k != "params"}
+                g["params"] = []
+                for b in self.buckets:
+                    if b.group_idx == gi:
+                        if getattr(b, "master_param", None) is None:
+                            b.master_param = torch.nn.Parameter(b.master, requires_grad=True)
+                        g["params"].append(b.master_param)
+                groups.append(g)
+            view = self.optimizer_class([g for g in groups if g["params"]] or [{"params": []}])
+            self._base_view = view
+        for b in self.buckets:
+            if b.exp_avg is not None and getattr(b, "master_param", None) is not None:
+                view.state[b.master_param] = {"step": torch.tensor(float(self._step_count)), "exp_avg": b.exp_avg,
+                                              "exp_avg_sq": b.exp_avg_sq}
+        return view
+
+    @property
     def grad_norm(self):
         return self._grad_norm
 

@@ -35,10 +35,14 @@ class NxDTracer(fx.Tracer):
         import math
 
         super().__init__(autowrap_modules=(math, *autowrap_modules), autowrap_functions=tuple(autowrap_functions))
-        self.leaf_classes = tuple(leaf_classes)
+        # leaves are given as classes or, as in the reference (``leaf_modules=["MyModule"]``), as class names
+        self.leaf_classes = tuple(c for c in leaf_classes if isinstance(c, type))
+        self.leaf_names = frozenset(c for c in leaf_classes if isinstance(c, str))
 
     def is_leaf_module(self, m: torch.nn.Module, module_qualified_name: str) -> bool:
         if isinstance(m, self.leaf_classes) or getattr(m, "_nxd_fx_leaf", False):
+            return True
+        if self.leaf_names and any(c.__name__ in self.leaf_names for c in type(m).__mro__):
             return True
         return super().is_leaf_module(m, module_qualified_name)
 
@@ -96,12 +100,32 @@ class TorchTracerWrapper(NxDTracer):
                          autowrap_modules=tuple(config.get("autowrap_modules", ())))
 
 
+class HFTracerWrapper(TorchTracerWrapper):
+    """Tracer selected for Hugging Face ``PreTrainedModel``s (reference ``pipeline/trace.py:24-55`` wraps transformers'
+    ``HFTracer``).  ``transformers.utils.fx`` was removed in transformers 5 and its models' decorated ``forward`` is not
+    symbolically traceable by plain torch.fx either, so this class exists for the selection logic (``tracer_cls="hf"``)
+    and traces models written in torch.fx-friendly style -- the model families of this package, which load HF
+    checkpoints through the converters -- with the same leaf rules as ``TorchTracerWrapper``."""
+
+
+def _is_hf_model(model) -> bool:
+    try:
+        from transformers import PreTrainedModel
+
+        return isinstance(model, PreTrainedModel)
+    except Exception:  # noqa: BLE001
+        return False
+
+
 def get_tracer_class(model: torch.nn.Module = None, tracer_cls=None):
-    """``None`` / ``"torch"`` -> the torch.fx based tracer; a class is returned unchanged.  The reference also offers
-    ``"hf"`` (transformers' HFTracer); HF models trace through the same torch.fx path here because the transformer
-    layer class is a leaf."""
-    if tracer_cls is None or tracer_cls == "torch" or tracer_cls == "hf":
+    """``"torch"`` / ``"hf"`` pick the wrapper, ``None`` picks by model type, a class is returned unchanged, any other
+    string is an error (reference ``:107-122``)."""
+    if tracer_cls is None:
+        return HFTracerWrapper if _is_hf_model(model) else TorchTracerWrapper
+    if tracer_cls == "torch":
         return TorchTracerWrapper
+    if tracer_cls == "hf":
+        return HFTracerWrapper
     if isinstance(tracer_cls, str):
         raise ValueError(f"Unsupported tracer_cls {tracer_cls}")
     return tracer_cls

@@ -174,3 +174,125 @@ def test_debug_mode_partition_and_names():
     NxDPPModel.custom_backward([out], [torch.ones(3)])
     assert torch.equal(a.grad, torch.full((3,), 2.0))
     pp.move_model_to_device(torch.device("cpu"))
+
+
+class _Inner(torch.nn.Module):
+    def __init__(self):
+        super().__init__()
+        self.linear1, self.linear2, self.linear3 = (torch.nn.Linear(2, 2) for _ in range(3))
+
+    def forward(self, x):
+        return (self.linear3(self.linear2(self.linear1(x))) + x).transpose(0, 1)
+
+
+class _Nested(torch.nn.Module):
+    def __init__(self):
+        super().__init__()
+        self.my_mod = _Inner()
+        self.linear4 = torch.nn.Linear(2, 2)
+
+    def forward(self, x):
+        return self.linear4(self.my_mod(x))
+
+
+from neuronx_distributed_llama3_2_b200.parallel.loss_functions import parallel_cross_entropy  # noqa: E402  (module level:
+# torch.fx auto-wraps a function by patching it in the globals of the module that calls it)
+
+
+class _WithParallel(torch.nn.Module):
+    def __init__(self):
+        super().__init__()
+        from neuronx_distributed_llama3_2_b200.parallel.layers import ColumnParallelLinear
+
+        self.my_mod = _Inner()
+        self.cpl = ColumnParallelLinear(2, 6, gather_output=False)
+
+    def forward(self, x, labels):
+        return parallel_cross_entropy(self.cpl(self.my_mod(x)), labels)
+
+
+def test_trace_helpers_leaf_names_and_tracer_selection():
+    """The reference's ``test/unit_test/pipeline/test_trace.py`` cases: concrete args, tracer selection by keyword,
+    node sequence of a traced module, leaves given by class NAME, auto-wrapped parallel functions."""
+    from neuronx_distributed_llama3_2_b200.pipeline import trace as T
+
+    class Optional_(torch.nn.Module):
+        def forward(self, x, unused=None, flag=True):
+            return x
+
+    assert T.get_concrete_args(Optional_(), ["x"]) == {"unused": None, "flag": True}
+    assert T.get_concrete_args(_Nested(), ["x"]) == {}
+    assert T.get_tracer_class(_Inner()) is T.TorchTracerWrapper
+    assert T.get_tracer_class(_Inner(), "hf") is T.HFTracerWrapper
+    assert T.get_tracer_class(_Inner(), "torch") is T.TorchTracerWrapper
+    with pytest.raises(ValueError):
+        T.get_tracer_class(_Inner(), "test")
+    ops = [(n.op, n.name) for n in T.trace_model(_Inner(), input_names=["x"]).graph.nodes]
+    assert ops == [("placeholder", "x"), ("call_module", "linear1"), ("call_module", "linear2"), ("call_module", "linear3"),
+                   ("call_function", "add"), ("call_method", "transpose"), ("output", "output")]
+    ops = [(n.op, n.name) for n in T.trace_model(_Nested(), input_names=["x"], leaf_modules=["_Inner"]).graph.nodes]
+    assert ops == [("placeholder", "x"), ("call_module", "my_mod"), ("call_module", "linear4"), ("output", "output")]
+
+    gm = T.trace_model(_WithParallel(), input_names=["x", "labels"], leaf_modules=[_Inner])
+    ops = [(n.op, n.name) for n in gm.graph.nodes]
+    assert ops == [("placeholder", "x"), ("placeholder", "labels"), ("call_module", "my_mod"), ("call_module", "cpl"),
+                   ("call_function", "parallel_cross_entropy"), ("output", "output")]
+    x, y = torch.randn(2, 2), torch.randint(0, 6, (2,))
+    torch.testing.assert_close(gm(x, y), parallel_cross_entropy(gm.cpl(gm.my_mod(x)), y))
+
+
+def test_partition_io_maps_and_shared_weights_of_eight_stage_model():
+    """The reference's fixture (``test/unit_test/pipeline/test_base.py``): an 8-block decoder with tied embeddings cut after
+    every block but the last -> 8 stages; hidden states hop stage to stage, ``labels`` is consumed where the loss lives,
+    the tied weight is reported as shared between stage 0 and stage 7."""
+    from neuronx_distributed_llama3_2_b200.pipeline import partition as P
+    from neuronx_distributed_llama3_2_b200.pipeline.trace import trace_model
+
+    class Block(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.ln, self.fc = torch.nn.LayerNorm(16), torch.nn.Linear(16, 16)
+
+        def forward(self, h, mask):
+            return h + self.fc(self.ln(h)) * mask
+
+    class GPT(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.wte = torch.nn.Embedding(50, 16)
+            self.h = torch.nn.ModuleList(Block() for _ in range(8))
+            self.ln_f = torch.nn.LayerNorm(16)
+            self.lm_head = torch.nn.Linear(16, 50, bias=False)
+            self.lm_head.weight = self.wte.weight
+
+        def forward(self, input_ids, attention_mask, labels):
+            h = self.wte(input_ids)
+            m = attention_mask.unsqueeze(-1).to(h.dtype)
+            for blk in self.h:
+                h = blk(h, m)
+            logits = self.lm_head(self.ln_f(h))
+            return torch.nn.functional.cross_entropy(logits.flatten(0, 1), labels.flatten())
+
+    torch.manual_seed(0)
+    model = GPT()
+    traced = trace_model(model, input_names=["input_ids", "attention_mask", "labels"], leaf_modules=["Block"])
+    cuts = [f"h.{i}" for i in range(7)]
+    split = P.partition_traced_model(traced, cuts)
+    stages = [n for n, _ in split.named_children()]
+    assert stages == [f"submod_{i}" for i in range(8)]
+    inputs, ios = P.analyze_pipeline_module(split)
+    assert inputs == ["input_ids", "attention_mask", "labels"]
+    assert [n for n, _ in ios[0].model_inputs] == ["input_ids", "attention_mask"] and ios[0].recv == []
+    assert [n for n, _ in ios[7].model_inputs] == ["labels"] and ios[7].send == [] and ios[7].returns_model_output
+    for k in range(1, 8):
+        # two values cross every boundary: the hidden state and the broadcast mask computed on stage 0
+        assert len(ios[k].recv) == 2 and {io.name for io in ios[k].recv} == {io.name for io in ios[k - 1].send}
+        assert all(io.input_idx is not None for io in ios[k].recv)
+    shared = P.analyze_shared_weights_across_stages(split)
+    assert len(shared) == 1 and sorted(s for _, s in shared[0]) == [0, 7]
+    assert {n for n, _ in shared[0]} == {"wte.weight", "lm_head.weight"}
+    ids = torch.randint(0, 50, (2, 6))
+    mask, labels = torch.ones(2, 6), torch.randint(0, 50, (2, 6))
+    torch.testing.assert_close(split(ids, mask, labels), model(ids, mask, labels))
+    with pytest.raises(ValueError):
+        P.partition_traced_model(traced, ["h.42"])

@@ -156,3 +156,38 @@ def test_delayed_tracing_is_off():
 
     assert get_delay_tracing({"pipeline_config": {"_delay_tracing": True}}) is False
     assert check_delay_tracing({"pipeline_config": {"use_model_wrapper": True}}) is False
+
+
+# -- wrapper/test_model_wrapper.py, wrapper/test_optimizer_wrapper.py ------------------------------------------------------------
+def test_model_and_optimizer_wrappers():
+    from neuronx_distributed_llama3_2_b200.models import LlamaForCausalLM, tiny_llama
+    from neuronx_distributed_llama3_2_b200.optimizer import NeuronZero1Optimizer
+    from neuronx_distributed_llama3_2_b200.trainer.optimizer import NxDOptimizer
+
+    for zero1 in (True, False):
+        cfg = nxd.neuronx_distributed_config(optimizer_config={"zero_one_enabled": zero1, "grad_clipping": True,
+                                                               "max_grad_norm": 1.0}, activation_checkpoint_config="full")
+        model = nxd.initialize_parallel_model(cfg, lambda: LlamaForCausalLM(tiny_llama(sequence_parallel_enabled=False)),
+                                              device=torch.device("cpu"))
+        assert model.nxd_config == cfg and "NxDPPModel" not in str(model)
+        result = model.load_state_dict(model.state_dict())
+        assert result is not None and not result.missing_keys and not result.unexpected_keys
+        assert all(k.startswith("model_prefix.") for k in model.state_dict(prefix="model_prefix."))
+        opt = nxd.initialize_parallel_optimizer(cfg, torch.optim.AdamW, model.parameters(), lr=1e-3)
+        assert opt.nxd_config == cfg and isinstance(opt, NxDOptimizer)
+        assert len(list(model.parameters())) == len(opt.params) and opt.grad_norm is None
+        if zero1:
+            assert isinstance(opt.optimizer, NeuronZero1Optimizer)
+            assert isinstance(opt.optimizer.base_optimizer, torch.optim.AdamW)
+        else:
+            assert isinstance(opt.optimizer, torch.optim.AdamW)
+        ids = torch.randint(0, 512, (2, 16))
+        model(ids, labels=ids).backward()
+        opt.step()
+        assert opt.grad_norm is not None and float(opt.grad_norm) > 0
+        opt.zero_grad()
+        sd = opt.state_dict()
+        assert sd
+        if zero1:       # the view reflects the live fused state: one step taken, moments non-zero
+            inner = opt.optimizer.base_optimizer.state_dict()["state"]
+            assert inner and all(float(st["exp_avg_sq"].abs().sum()) > 0 for st in inner.values())
