@@ -16,7 +16,9 @@
 #include <cstdint>
 #include <cstdio>
 #include <cstring>
+#include <deque>
 #include <map>
+#include <mutex>
 #include <string>
 #include <thread>
 #include <vector>
@@ -322,3 +324,272 @@ NXD_RT_API int nxd_router_route_padded(void* r, const char* key, int batch, int 
     if (out_seq) *out_seq = best->seq;
     return best->graph;
 }
+
+// ---------------------------------------------------------------------------------------------------------------------
+// paged KV-cache block manager
+//
+// The device cache of a layer is a pool of pages [num_pages, kv_heads, page_size, head_dim]; a sequence (cache line) owns an
+// ordered list of pages, the block table row the attention kernels index with.  The pool may be smaller than
+// lines * max_pages: pages are handed out as sequences grow and return to the free list when a line is released.  Pages
+// are reference counted so that a line can be forked (speculation branches, shared prompt prefixes): full pages are
+// shared, the partially filled last page is copied by the caller (the manager reports which page to copy where).
+// ---------------------------------------------------------------------------------------------------------------------
+struct KvPool {
+    int num_pages, page_size, max_lines, max_pages;
+    std::vector<int> free_list;                  // LIFO: recently freed pages are reused first (L2-warm)
+    std::vector<int> refcnt;                     // per page
+    std::vector<std::vector<int>> pages;         // per line
+    std::vector<int64_t> tokens;                 // per line: tokens reserved so far
+    std::mutex mu;
+};
+
+NXD_RT_API void* nxd_kv_create(int num_pages, int page_size, int max_lines, int max_pages_per_line) {
+    if (num_pages <= 0 || page_size <= 0 || max_lines <= 0 || max_pages_per_line <= 0) {
+        fail("kv_create: bad arguments");
+        return nullptr;
+    }
+    KvPool* p = new KvPool();
+    p->num_pages = num_pages; p->page_size = page_size; p->max_lines = max_lines; p->max_pages = max_pages_per_line;
+    p->refcnt.assign(num_pages, 0);
+    p->pages.resize(max_lines);
+    p->tokens.assign(max_lines, 0);
+    p->free_list.reserve(num_pages);
+    for (int i = num_pages - 1; i >= 0; --i) p->free_list.push_back(i);     // page 0 is handed out first
+    return p;
+}
+
+NXD_RT_API void nxd_kv_destroy(void* h) { delete (KvPool*)h; }
+
+NXD_RT_API int nxd_kv_num_free(void* h) { return h ? (int)((KvPool*)h)->free_list.size() : -1; }
+
+NXD_RT_API int64_t nxd_kv_line_tokens(void* h, int line) {
+    KvPool* p = (KvPool*)h;
+    return (p && line >= 0 && line < p->max_lines) ? p->tokens[line] : -1;
+}
+
+// Pages line `line` needs IN ADDITION to what it holds to store `n_tokens` tokens in total.
+NXD_RT_API int nxd_kv_pages_needed(void* h, int line, int64_t n_tokens) {
+    KvPool* p = (KvPool*)h;
+    if (!p || line < 0 || line >= p->max_lines) return -1;
+    int64_t want = (n_tokens + p->page_size - 1) / p->page_size;
+    int64_t have = (int64_t)p->pages[line].size();
+    return (int)(want > have ? want - have : 0);
+}
+
+// Make room for `n_tokens` tokens in total on `line`.  Returns the number of pages newly allocated, -1 when the pool (or
+// the per-line limit) cannot hold them -- in that case nothing is allocated.
+NXD_RT_API int nxd_kv_reserve(void* h, int line, int64_t n_tokens) {
+    KvPool* p = (KvPool*)h;
+    if (!p || line < 0 || line >= p->max_lines || n_tokens < 0) return fail("kv_reserve: bad arguments");
+    std::lock_guard<std::mutex> g(p->mu);
+    int64_t want = (n_tokens + p->page_size - 1) / p->page_size;
+    if (want > p->max_pages) return fail("kv_reserve: %lld tokens exceed the per-line limit of %d pages", (long long)n_tokens, p->max_pages);
+    int64_t have = (int64_t)p->pages[line].size();
+    int need = (int)(want > have ? want - have : 0);
+    if (need > (int)p->free_list.size()) return fail("kv_reserve: out of pages (%d needed, %d free)", need, (int)p->free_list.size());
+    for (int i = 0; i < need; ++i) {
+        int pg = p->free_list.back();
+        p->free_list.pop_back();
+        p->refcnt[pg] = 1;
+        p->pages[line].push_back(pg);
+    }
+    if (n_tokens > p->tokens[line]) p->tokens[line] = n_tokens;
+    return need;
+}
+
+// Release every page of `line` (pages shared with a fork stay alive until their last owner lets go).  Returns pages freed.
+NXD_RT_API int nxd_kv_free_line(void* h, int line) {
+    KvPool* p = (KvPool*)h;
+    if (!p || line < 0 || line >= p->max_lines) return fail("kv_free_line: bad line");
+    std::lock_guard<std::mutex> g(p->mu);
+    int freed = 0;
+    for (auto it = p->pages[line].rbegin(); it != p->pages[line].rend(); ++it)
+        if (--p->refcnt[*it] == 0) { p->free_list.push_back(*it); ++freed; }
+    p->pages[line].clear();
+    p->tokens[line] = 0;
+    return freed;
+}
+
+// Drop the pages of `line` beyond `n_tokens` (speculation rollback).  Returns pages freed.
+NXD_RT_API int nxd_kv_truncate(void* h, int line, int64_t n_tokens) {
+    KvPool* p = (KvPool*)h;
+    if (!p || line < 0 || line >= p->max_lines || n_tokens < 0) return fail("kv_truncate: bad arguments");
+    std::lock_guard<std::mutex> g(p->mu);
+    size_t keep = (size_t)((n_tokens + p->page_size - 1) / p->page_size);
+    int freed = 0;
+    while (p->pages[line].size() > keep) {
+        int pg = p->pages[line].back();
+        p->pages[line].pop_back();
+        if (--p->refcnt[pg] == 0) { p->free_list.push_back(pg); ++freed; }
+    }
+    if (n_tokens < p->tokens[line]) p->tokens[line] = n_tokens;
+    return freed;
+}
+
+// dst becomes a copy-on-write fork of src: full pages are shared (reference counted); when the last page of src is only
+// partially filled, dst gets a fresh page for it and (*copy_src, *copy_dst) tell the caller which page to copy on the device
+// (both -1 when no copy is needed).  Returns 0, or -1 when the pool is exhausted.
+NXD_RT_API int nxd_kv_fork(void* h, int src, int dst, int* copy_src, int* copy_dst) {
+    KvPool* p = (KvPool*)h;
+    if (!p || src < 0 || dst < 0 || src >= p->max_lines || dst >= p->max_lines || src == dst) return fail("kv_fork: bad lines");
+    std::lock_guard<std::mutex> g(p->mu);
+    if (!p->pages[dst].empty()) return fail("kv_fork: destination line %d is in use", dst);
+    if (copy_src) *copy_src = -1;
+    if (copy_dst) *copy_dst = -1;
+    const std::vector<int>& sp = p->pages[src];
+    bool partial = !sp.empty() && (p->tokens[src] % p->page_size) != 0;
+    if (partial && p->free_list.empty()) return fail("kv_fork: out of pages");
+    size_t shared = partial ? sp.size() - 1 : sp.size();
+    for (size_t i = 0; i < shared; ++i) { ++p->refcnt[sp[i]]; p->pages[dst].push_back(sp[i]); }
+    if (partial) {
+        int pg = p->free_list.back();
+        p->free_list.pop_back();
+        p->refcnt[pg] = 1;
+        p->pages[dst].push_back(pg);
+        if (copy_src) *copy_src = sp.back();
+        if (copy_dst) *copy_dst = pg;
+    }
+    p->tokens[dst] = p->tokens[src];
+    return 0;
+}
+
+// Is the page that position `pos` of `line` falls on shared with another line?  (A writer must un-share it first.)
+NXD_RT_API int nxd_kv_page_shared(void* h, int line, int64_t pos) {
+    KvPool* p = (KvPool*)h;
+    if (!p || line < 0 || line >= p->max_lines || pos < 0) return -1;
+    size_t i = (size_t)(pos / p->page_size);
+    if (i >= p->pages[line].size()) return 0;
+    return p->refcnt[p->pages[line][i]] > 1 ? 1 : 0;
+}
+
+// Replace the shared page under position `pos` of `line` by a private one; (*copy_src, *copy_dst) as in nxd_kv_fork.
+NXD_RT_API int nxd_kv_unshare(void* h, int line, int64_t pos, int* copy_src, int* copy_dst) {
+    KvPool* p = (KvPool*)h;
+    if (!p || line < 0 || line >= p->max_lines || pos < 0) return fail("kv_unshare: bad arguments");
+    std::lock_guard<std::mutex> g(p->mu);
+    if (copy_src) *copy_src = -1;
+    if (copy_dst) *copy_dst = -1;
+    size_t i = (size_t)(pos / p->page_size);
+    if (i >= p->pages[line].size()) return 0;
+    int old = p->pages[line][i];
+    if (p->refcnt[old] <= 1) return 0;
+    if (p->free_list.empty()) return fail("kv_unshare: out of pages");
+    int pg = p->free_list.back();
+    p->free_list.pop_back();
+    p->refcnt[pg] = 1;
+    --p->refcnt[old];
+    p->pages[line][i] = pg;
+    if (copy_src) *copy_src = old;
+    if (copy_dst) *copy_dst = pg;
+    return 1;
+}
+
+// Block-table row of `line` into out[max_pages]; unused slots get `fill` (a valid page id keeps kernels in bounds).
+NXD_RT_API int nxd_kv_block_row(void* h, int line, int32_t* out, int fill) {
+    KvPool* p = (KvPool*)h;
+    if (!p || !out || line < 0 || line >= p->max_lines) return fail("kv_block_row: bad arguments");
+    const std::vector<int>& pg = p->pages[line];
+    for (int i = 0; i < p->max_pages; ++i) out[i] = i < (int)pg.size() ? pg[i] : fill;
+    return (int)pg.size();
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// continuous-batching scheduler (host side): which waiting request is admitted to which cache line, given the pages free
+// ---------------------------------------------------------------------------------------------------------------------
+struct SchedReq { int64_t id; int prompt_len; int max_new; int line; int generated; };
+struct Scheduler {
+    KvPool* pool;
+    int max_running;
+    std::deque<SchedReq> waiting;
+    std::vector<SchedReq> running;
+    std::vector<int> free_lines;
+};
+
+NXD_RT_API void* nxd_sched_create(void* kv_pool, int max_running) {
+    KvPool* p = (KvPool*)kv_pool;
+    if (!p || max_running <= 0 || max_running > p->max_lines) { fail("sched_create: bad arguments"); return nullptr; }
+    Scheduler* s = new Scheduler();
+    s->pool = p; s->max_running = max_running;
+    for (int i = max_running - 1; i >= 0; --i) s->free_lines.push_back(i);
+    return s;
+}
+NXD_RT_API void nxd_sched_destroy(void* h) { delete (Scheduler*)h; }
+
+NXD_RT_API int nxd_sched_submit(void* h, int64_t id, int prompt_len, int max_new_tokens) {
+    Scheduler* s = (Scheduler*)h;
+    if (!s || prompt_len <= 0 || max_new_tokens <= 0) return fail("sched_submit: bad arguments");
+    if ((int64_t)prompt_len + max_new_tokens > (int64_t)s->pool->max_pages * s->pool->page_size)
+        return fail("sched_submit: request %lld does not fit a cache line", (long long)id);
+    s->waiting.push_back({id, prompt_len, max_new_tokens, -1, 0});
+    return 0;
+}
+
+// Admit waiting requests in arrival order while a line is free and the pool holds their prompt plus one page of head room
+// per running sequence (so that admitted work can always take its next decode step).  Writes (id, line) pairs; returns count.
+NXD_RT_API int nxd_sched_admit(void* h, int64_t* ids, int* lines, int cap) {
+    Scheduler* s = (Scheduler*)h;
+    if (!s) return -1;
+    int n = 0;
+    while (n < cap && !s->waiting.empty() && !s->free_lines.empty()) {
+        SchedReq r = s->waiting.front();
+        int prompt_pages = (r.prompt_len + 1 + s->pool->page_size - 1) / s->pool->page_size;     // + the first new token
+        int headroom = (int)s->running.size();
+        if (prompt_pages + headroom > (int)s->pool->free_list.size()) break;
+        int line = s->free_lines.back();
+        if (nxd_kv_reserve(s->pool, line, r.prompt_len + 1) < 0) break;
+        s->free_lines.pop_back();
+        s->waiting.pop_front();
+        r.line = line;
+        s->running.push_back(r);
+        if (ids) ids[n] = r.id;
+        if (lines) lines[n] = line;
+        ++n;
+    }
+    return n;
+}
+
+// One decode step was taken by every running request: grow their reservations by one token.  Requests that reached
+// max_new_tokens (or whose id is in done_ids) are retired and their pages freed.  A request that cannot get its next page is
+// preempted: pages freed, request put back at the FRONT of the waiting queue (it will re-run its prompt).  Writes the ids of
+// retired requests to out_done and of preempted ones to out_preempted; returns the number still running.
+NXD_RT_API int nxd_sched_step(void* h, const int64_t* done_ids, int n_done, int64_t* out_done, int* n_out_done,
+                              int64_t* out_preempted, int* n_out_preempted, int cap) {
+    Scheduler* s = (Scheduler*)h;
+    if (!s) return -1;
+    int nd = 0, np = 0;
+    std::vector<SchedReq> keep;
+    for (SchedReq& r : s->running) {
+        ++r.generated;
+        bool done = r.generated >= r.max_new;
+        for (int i = 0; i < n_done && !done; ++i) done = done_ids[i] == r.id;
+        if (done) {
+            nxd_kv_free_line(s->pool, r.line);
+            s->free_lines.push_back(r.line);
+            if (out_done && nd < cap) out_done[nd] = r.id;
+            ++nd;
+            continue;
+        }
+        keep.push_back(r);
+    }
+    s->running.clear();
+    // grow oldest first; the youngest sequences are the ones preempted when the pool runs dry
+    for (SchedReq& r : keep) {
+        if (nxd_kv_reserve(s->pool, r.line, (int64_t)r.prompt_len + r.generated + 1) < 0) {
+            nxd_kv_free_line(s->pool, r.line);
+            s->free_lines.push_back(r.line);
+            if (out_preempted && np < cap) out_preempted[np] = r.id;
+            ++np;
+            SchedReq w = r;
+            w.line = -1; w.generated = 0;
+            s->waiting.push_front(w);
+            continue;
+        }
+        s->running.push_back(r);
+    }
+    if (n_out_done) *n_out_done = nd;
+    if (n_out_preempted) *n_out_preempted = np;
+    return (int)s->running.size();
+}
+
+NXD_RT_API int nxd_sched_num_waiting(void* h) { return h ? (int)((Scheduler*)h)->waiting.size() : -1; }
+NXD_RT_API int nxd_sched_num_running(void* h) { return h ? (int)((Scheduler*)h)->running.size() : -1; }

@@ -54,11 +54,12 @@ def init_distributed(tp_degree: int) -> int:
 
 
 def inference_config(args, **extra) -> InferenceConfig:
-    return InferenceConfig(tp_degree=args.tp_degree, batch_size=args.batch_size,
-                           max_context_length=args.max_context_length, seq_len=args.seq_len,
-                           max_new_tokens=args.max_new_tokens, top_k=args.top_k, top_p=args.top_p,
-                           temperature=args.temperature, do_sample=args.top_k > 1,
-                           use_cuda_graphs=not args.no_cuda_graphs, paged_kv=args.paged_kv, **extra)
+    kw = dict(tp_degree=args.tp_degree, batch_size=args.batch_size, max_context_length=args.max_context_length,
+              seq_len=args.seq_len, max_new_tokens=args.max_new_tokens, top_k=args.top_k, top_p=args.top_p,
+              temperature=args.temperature, do_sample=args.top_k > 1, use_cuda_graphs=not args.no_cuda_graphs,
+              paged_kv=args.paged_kv)
+    kw.update(extra)
+    return InferenceConfig(**kw)
 
 
 def model_config(args, presets):

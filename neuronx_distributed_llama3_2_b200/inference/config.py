@@ -32,6 +32,7 @@ class InferenceConfig:
     use_cuda_graphs: bool = True
     paged_kv: bool = False
     page_size: int = 128
+    num_kv_pages: Optional[int] = None      # paged cache: size of the page pool (default: lines * pages per line)
     pad_token_id: int = 0
     eos_token_id: Optional[int] = None
 

@@ -69,7 +69,8 @@ class KVCacheInferenceMixin:
         attn0 = self._decoder_layers()[0].self_attn
         device = device or next(self.parameters()).device
         self.kv_cache = KVCache(cfg.num_hidden_layers, ic.max_batch_size, attn0.kv_heads_local, ic.seq_len, cfg.head_dim,
-                                dtype=dtype or cfg.torch_dtype, device=device, paged=ic.paged_kv, page_size=ic.page_size)
+                                dtype=dtype or cfg.torch_dtype, device=device, paged=ic.paged_kv, page_size=ic.page_size,
+                                num_pages=ic.num_kv_pages if ic.paged_kv else None)
         return self.kv_cache
 
     def _rope(self, device) -> Tuple[torch.Tensor, torch.Tensor]:
@@ -245,11 +246,19 @@ class KVCacheInferenceMixin:
             attention_mask = torch.ones_like(input_ids)
         lens = attention_mask.sum(dim=1).to(torch.long)
         pos = torch.arange(T, device=dev).unsqueeze(0).expand(B, T)
+        dynamic = self.kv_cache.pool is not None
+        if dynamic:                                         # the prompt (incl. its padding) and the first new token
+            for b in range(B):
+                self.kv_cache.free(b)
+                self.kv_cache.reserve(b, T + 1)
         tok = self.forward_infer(input_ids, pos, last_token_index=lens - 1)
         out = [tok]
         cur = lens.clone()
         finished = torch.zeros(B, dtype=torch.bool, device=dev)
-        for _ in range(max_new_tokens - 1):
+        for step in range(max_new_tokens - 1):
+            if dynamic:
+                for b in range(B):
+                    self.kv_cache.reserve(b, max(T + 1, int(lens[b]) + step + 2))
             if eos_token_id is not None:
                 finished |= tok == eos_token_id
                 if bool(finished.all()):

@@ -63,6 +63,29 @@ def lib() -> C.CDLL:
             L.nxd_router_route_exact.argtypes = [C.c_void_p, C.c_int, C.c_int]
             L.nxd_router_route_padded.argtypes = [C.c_void_p, C.c_char_p, C.c_int, C.c_int, C.POINTER(C.c_int),
                                                   C.POINTER(C.c_int)]
+            L.nxd_kv_create.restype = C.c_void_p
+            L.nxd_kv_create.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int]
+            L.nxd_kv_destroy.argtypes = [C.c_void_p]
+            L.nxd_kv_num_free.argtypes = [C.c_void_p]
+            L.nxd_kv_line_tokens.restype = C.c_int64
+            L.nxd_kv_line_tokens.argtypes = [C.c_void_p, C.c_int]
+            L.nxd_kv_pages_needed.argtypes = [C.c_void_p, C.c_int, C.c_int64]
+            L.nxd_kv_reserve.argtypes = [C.c_void_p, C.c_int, C.c_int64]
+            L.nxd_kv_free_line.argtypes = [C.c_void_p, C.c_int]
+            L.nxd_kv_truncate.argtypes = [C.c_void_p, C.c_int, C.c_int64]
+            L.nxd_kv_fork.argtypes = [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int)]
+            L.nxd_kv_page_shared.argtypes = [C.c_void_p, C.c_int, C.c_int64]
+            L.nxd_kv_unshare.argtypes = [C.c_void_p, C.c_int, C.c_int64, C.POINTER(C.c_int), C.POINTER(C.c_int)]
+            L.nxd_kv_block_row.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_int32), C.c_int]
+            L.nxd_sched_create.restype = C.c_void_p
+            L.nxd_sched_create.argtypes = [C.c_void_p, C.c_int]
+            L.nxd_sched_destroy.argtypes = [C.c_void_p]
+            L.nxd_sched_submit.argtypes = [C.c_void_p, C.c_int64, C.c_int, C.c_int]
+            L.nxd_sched_admit.argtypes = [C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int), C.c_int]
+            L.nxd_sched_step.argtypes = [C.c_void_p, C.POINTER(C.c_int64), C.c_int, C.POINTER(C.c_int64),
+                                         C.POINTER(C.c_int), C.POINTER(C.c_int64), C.POINTER(C.c_int), C.c_int]
+            L.nxd_sched_num_waiting.argtypes = [C.c_void_p]
+            L.nxd_sched_num_running.argtypes = [C.c_void_p]
             _lib = L
     return _lib
 
@@ -184,3 +207,114 @@ class NativeRouter:
                 self._h = None
         except Exception:  # noqa: BLE001
             pass
+
+
+class PagedKVPool:
+    """Host-side page allocator of a paged KV cache (``nxd_kv_*``): cache lines own ordered page lists, pages are
+    reference counted (``fork`` shares full pages copy-on-write), the pool may be smaller than ``lines * max_pages``."""
+
+    def __init__(self, num_pages: int, page_size: int, max_lines: int, max_pages_per_line: int):
+        self.num_pages, self.page_size, self.max_lines, self.max_pages = num_pages, page_size, max_lines, max_pages_per_line
+        self._h = lib().nxd_kv_create(num_pages, page_size, max_lines, max_pages_per_line)
+        if not self._h:
+            raise ValueError(_err())
+
+    @property
+    def num_free(self) -> int:
+        return lib().nxd_kv_num_free(self._h)
+
+    def line_tokens(self, line: int) -> int:
+        return int(lib().nxd_kv_line_tokens(self._h, line))
+
+    def pages_needed(self, line: int, n_tokens: int) -> int:
+        return lib().nxd_kv_pages_needed(self._h, line, n_tokens)
+
+    def reserve(self, line: int, n_tokens: int) -> int:
+        """Room for ``n_tokens`` tokens in total on ``line``; pages newly allocated.  ``MemoryError`` when the pool is dry."""
+        rc = lib().nxd_kv_reserve(self._h, line, n_tokens)
+        if rc < 0:
+            raise MemoryError(_err())
+        return rc
+
+    def free_line(self, line: int) -> int:
+        return lib().nxd_kv_free_line(self._h, line)
+
+    def truncate(self, line: int, n_tokens: int) -> int:
+        return lib().nxd_kv_truncate(self._h, line, n_tokens)
+
+    def fork(self, src: int, dst: int) -> Optional[Tuple[int, int]]:
+        """``dst`` shares ``src``'s full pages; returns ``(src_page, dst_page)`` to copy on the device when the last page
+        was partially filled, else ``None``."""
+        a, b = C.c_int(-1), C.c_int(-1)
+        if lib().nxd_kv_fork(self._h, src, dst, C.byref(a), C.byref(b)) != 0:
+            raise MemoryError(_err())
+        return (a.value, b.value) if a.value >= 0 else None
+
+    def page_shared(self, line: int, pos: int) -> bool:
+        return lib().nxd_kv_page_shared(self._h, line, pos) == 1
+
+    def unshare(self, line: int, pos: int) -> Optional[Tuple[int, int]]:
+        a, b = C.c_int(-1), C.c_int(-1)
+        if lib().nxd_kv_unshare(self._h, line, pos, C.byref(a), C.byref(b)) < 0:
+            raise MemoryError(_err())
+        return (a.value, b.value) if a.value >= 0 else None
+
+    def block_row(self, line: int, fill: int = 0) -> Tuple[List[int], int]:
+        buf = (C.c_int32 * self.max_pages)()
+        n = lib().nxd_kv_block_row(self._h, line, buf, fill)
+        return list(buf), n
+
+    def close(self) -> None:
+        if self._h:
+            lib().nxd_kv_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:  # noqa: BLE001
+            pass
+
+
+class NativeScheduler:
+    """Continuous-batching admission / retirement / preemption over a ``PagedKVPool`` (``nxd_sched_*``).  FIFO admission
+    while a cache line is free and the pool holds the prompt plus one page of head room per running sequence; when a
+    running sequence cannot get its next page the youngest are preempted back to the front of the queue."""
+
+    def __init__(self, pool: PagedKVPool, max_running: int):
+        self.pool = pool
+        self._h = lib().nxd_sched_create(pool._h, max_running)
+        if not self._h:
+            raise ValueError(_err())
+        self._cap = max(max_running, 1)
+
+    def submit(self, req_id: int, prompt_len: int, max_new_tokens: int) -> None:
+        if lib().nxd_sched_submit(self._h, req_id, prompt_len, max_new_tokens) != 0:
+            raise ValueError(_err())
+
+    def admit(self) -> List[Tuple[int, int]]:
+        ids, lines = (C.c_int64 * self._cap)(), (C.c_int * self._cap)()
+        n = lib().nxd_sched_admit(self._h, ids, lines, self._cap)
+        return [(int(ids[i]), int(lines[i])) for i in range(n)]
+
+    def step(self, finished: Iterable[int] = ()) -> Tuple[List[int], List[int], int]:
+        """After one model call for every running request.  Returns ``(retired ids, preempted ids, still running)``."""
+        fin = list(finished)
+        arr = (C.c_int64 * max(len(fin), 1))(*fin)
+        done, pre = (C.c_int64 * self._cap)(), (C.c_int64 * self._cap)()
+        nd, np_ = C.c_int(0), C.c_int(0)
+        running = lib().nxd_sched_step(self._h, arr, len(fin), done, C.byref(nd), pre, C.byref(np_), self._cap)
+        return [int(done[i]) for i in range(nd.value)], [int(pre[i]) for i in range(np_.value)], running
+
+    @property
+    def num_waiting(self) -> int:
+        return lib().nxd_sched_num_waiting(self._h)
+
+    @property
+    def num_running(self) -> int:
+        return lib().nxd_sched_num_running(self._h)
+
+    def close(self) -> None:
+        if self._h:
+            lib().nxd_sched_destroy(self._h)
+            self._h = None

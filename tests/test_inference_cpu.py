@@ -495,3 +495,52 @@ def test_family_runners_and_quantized_runner():
         ref = _full_logits(train, ids)[:, -1]
         rel = ((logits - ref).norm() / ref.norm()).item()
         assert rel < 0.05, (qtype, rel)
+
+
+def test_continuous_batching_over_paged_pool_matches_isolated_generation():
+    """Six requests of different lengths through three cache lines and a page pool that cannot hold them all at once:
+    admission waits for pages, finished requests hand theirs back, a starved request is preempted and re-run -- and every
+    request still gets exactly the tokens it gets when generated alone on a contiguous cache."""
+    from neuronx_distributed_llama3_2_b200.inference.continuous_batching import ContinuousBatcher
+    from neuronx_distributed_llama3_2_b200.runtime.native import NativeScheduler, PagedKVPool
+
+    # the allocator itself: growth, fork (copy-on-write of the partial page), un-share, truncate, exhaustion
+    pool = PagedKVPool(6, 4, 3, 4)
+    assert pool.reserve(0, 5) == 2 and pool.num_free == 4 and pool.block_row(0)[0][:2] == [0, 1]
+    assert pool.fork(0, 1) == (1, 2) and pool.block_row(1)[0][:2] == [0, 2] and pool.page_shared(0, 0)
+    assert not pool.page_shared(0, 4) and pool.unshare(1, 0) == (0, 3) and pool.unshare(1, 0) is None
+    assert pool.truncate(0, 4) == 1 and pool.free_line(1) == 2 and pool.free_line(0) == 1 and pool.num_free == 6
+    with pytest.raises(MemoryError):
+        pool.reserve(2, 17)
+    sched = NativeScheduler(pool, 2)
+    for i, (pl, mn) in enumerate([(5, 3), (3, 2), (2, 2)]):
+        sched.submit(100 + i, pl, mn)
+    assert sched.admit() == [(100, 0), (101, 1)] and sched.num_waiting == 1
+    assert sched.step() == ([], [], 2) and sched.step() == ([101], [], 1)
+    assert sched.admit() == [(102, 1)] and sched.step() == ([100], [], 1) and sched.step() == ([102], [], 0)
+    assert pool.num_free == 6
+
+    cfg, train, _ = _models()
+    sd = train.state_dict()
+    ref_model = LlamaInferenceModel(tiny_llama(sequence_parallel_enabled=False),
+                                    InferenceConfig(batch_size=1, max_context_length=32, seq_len=64))
+    ref_model.load_state_dict(sd)
+    g = torch.Generator().manual_seed(7)
+    specs = [(11, 9), (5, 14), (17, 6), (8, 12), (3, 10), (13, 7)]
+    prompts = [torch.randint(1, cfg.vocab_size, (T,), generator=g) for T, _ in specs]
+    want = [ref_model.generate(p.unsqueeze(0), max_new_tokens=n)[0, p.numel():].tolist() for p, (_, n) in zip(prompts, specs)]
+    for n_pages, expect_preempt in ((12, False), (4, True)):
+        ic = InferenceConfig(batch_size=3, max_context_length=32, seq_len=64, paged_kv=True, page_size=8,
+                             num_kv_pages=n_pages, is_continuous_batching=True)
+        model = LlamaInferenceModel(tiny_llama(sequence_parallel_enabled=False), ic)
+        model.load_state_dict(sd)
+        engine = ContinuousBatcher(model, max_running=3, pad_decode_to=3 if n_pages == 12 else None)
+        rids = [engine.submit(p, n) for p, (_, n) in zip(prompts, specs)]
+        got = engine.run()
+        for rid, w in zip(rids, want):
+            assert got[rid] == w, (n_pages, rid, got[rid], w)
+        st = engine.stats
+        assert st["prefills"] == 6 + st["preemptions"] and st["max_running"] <= 3
+        assert model.kv_cache.pool.num_free == n_pages
+        assert st["decode_rows"] > st["decode_calls"]                       # requests really shared decode calls
+        assert (st["preemptions"] > 0) == expect_preempt, st
