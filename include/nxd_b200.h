@@ -190,6 +190,11 @@ int nxd_skinny_gemm_ar_bf16(const void* x, const void* w, const void* residual, 
                             long long ldx, long long ldw, long long ldo, void* const* stage_ptrs,
                             void* const* sig_ptrs, size_t slot_elems, int tp, int rank, int slot, void* state,
                             void* stream);
+/* Weight-only int8 skinny GEMM (reference: quantization_layers.py:444-478 dequantise + matmul): out[B, N] (+ residual) =
+ * (x[B, K] bf16 * w[N, K]^T int8) * scale, fp32 accumulation; scale_n == 1 (per tensor) or N (per output channel).
+ * B <= 8, K % 16 == 0, ldw (bytes) % 16 == 0.  Streams half the bytes of the bf16 skinny GEMM. */
+int nxd_skinny_gemm_i8(const void* x, const void* w, const void* scale, int scale_n, const void* residual, void* out,
+                       int B, int N, int K, long long ldx, long long ldw, long long ldo, void* stream);
 /* out[n] = sum over ranks of in[n] (bf16, n % 8 == 0, n <= slot_elems): one-shot all-reduce for small messages */
 int nxd_allreduce_oneshot(const void* in, void* out, long long n, void* const* stage_ptrs, void* const* sig_ptrs,
                           size_t slot_elems, int tp, int rank, int slot, void* state, void* stream);

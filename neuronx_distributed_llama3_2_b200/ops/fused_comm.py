@@ -219,6 +219,34 @@ def skinny_gemm(x2d: torch.Tensor, weight: torch.Tensor, residual: Optional[torc
     return out
 
 
+def skinny_gemm_i8(x2d: torch.Tensor, weight_i8: torch.Tensor, scale: torch.Tensor,
+                   residual: Optional[torch.Tensor] = None) -> Optional[torch.Tensor]:
+    """``(x2d[B, K] @ weight_i8[N, K]^T) * scale (+ residual)`` for B <= 8 bf16 rows and int8 weights: the weight-only
+    quantized token-generation GEMM (``csrc/skinny_int8.cu``).  ``scale`` has 1 element (per tensor) or N (per output
+    channel).  ``None`` when the shape does not qualify."""
+    B, K = x2d.shape
+    N = weight_i8.shape[0]
+    sn = scale.numel()
+    if (B == 0 or B > 8 or x2d.dtype != torch.bfloat16 or weight_i8.dtype != torch.int8 or K % 16 or x2d.stride(1) != 1
+            or weight_i8.stride(1) != 1 or x2d.stride(0) % 8 or weight_i8.stride(0) % 16 or sn not in (1, N)):
+        return None
+    kb = 1 if B <= 1 else 2 if B <= 2 else 4 if B <= 4 else 8
+    if kb * K * 2 + kb * 16 * 4 > 200 * 1024:
+        return None
+    sc = scale.reshape(-1).to(torch.float32).contiguous()
+    out = torch.empty((B, N), dtype=torch.bfloat16, device=x2d.device)
+    if residual is not None:
+        residual = residual.reshape(B, N)
+        if residual.stride(1) != 1 or residual.stride(0) != out.stride(0):
+            residual = residual.contiguous()
+    rc = _lib.lib().nxd_skinny_gemm_i8(
+        _lib.ptr(x2d), _lib.ptr(weight_i8), _lib.ptr(sc), _c.c_int(sn), _lib.ptr(residual), _lib.ptr(out), _c.c_int(B),
+        _c.c_int(N), _c.c_int(K), _c.c_longlong(x2d.stride(0)), _c.c_longlong(weight_i8.stride(0)),
+        _c.c_longlong(out.stride(0)), _lib.stream_ptr())
+    _lib.check(rc, "nxd_skinny_gemm_i8")
+    return out
+
+
 def fused_gemm_ar(ctx, x2d: torch.Tensor, weight: torch.Tensor, layout: str = "nt") -> Optional[torch.Tensor]:
     """``all_reduce(x2d @ W_op)``: one kernel for token generation (<= 16 rows), tcgen05 GEMM + one-shot all-reduce
     for messages up to 2 MB (short prefill), ``None`` beyond (NCCL's ring / NVLS wins on bandwidth there)."""

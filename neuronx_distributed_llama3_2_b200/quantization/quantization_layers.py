@@ -6,6 +6,8 @@ the scale.  Per-channel scales follow the weight's sharding; per-tensor scales a
 """
 from __future__ import annotations
 
+import os
+
 from typing import Optional
 
 import torch
@@ -104,8 +106,19 @@ class BaseQuantizeParallelLinear(torch.nn.Module):
 
 def _int8_linear(x: torch.Tensor, weight_i8: torch.Tensor, scale: torch.Tensor, out_axis_scale: bool) -> torch.Tensor:
     """``x @ W^T`` with int8 ``W [out, in]``: exact cast, GEMM on the tensor cores, then scale the output."""
-    w = direct_cast_dequantize(weight_i8, x.dtype)
     x2 = x.reshape(-1, x.shape[-1])
+    if (x2.shape[0] <= 8 and x2.is_cuda and x2.dtype == torch.bfloat16 and weight_i8.dim() == 2
+            and os.environ.get("NXD_INT8_SKINNY", "0") == "1"):
+        # token generation: stream the int8 weight once (half the bytes of bf16) instead of dequantising all of it.
+        # Opt-in until the kernel has been run on hardware (csrc/skinny_int8.cu was written after the GPU budget ended).
+        from ..ops.fused_comm import skinny_gemm_i8
+
+        per_out = out_axis_scale and scale.numel() > 1
+        if per_out or scale.numel() == 1:
+            y = skinny_gemm_i8(x2.contiguous(), weight_i8, scale if per_out else scale.reshape(-1)[:1])
+            if y is not None:
+                return y.reshape(x.shape[:-1] + (weight_i8.shape[0],))
+    w = direct_cast_dequantize(weight_i8, x.dtype)
     y = gemm_ops.gemm_nt(x2, w)
     s = scale.reshape(1, -1) if (out_axis_scale and scale.numel() > 1) else scale.reshape(-1)[:1]
     y = (y.float() * s.float()).to(x.dtype)
