@@ -48,6 +48,12 @@ class KVCacheInferenceMixin:
         self.kv_cache: Optional[KVCache] = None
         self.sampler = Sampler(self.inference_config)
         self._rope_tables = None
+        self.num_medusa_heads = 0
+        if self.inference_config.num_medusa_heads > 0:
+            from .medusa import add_medusa_heads
+
+            first = next(self.parameters())
+            add_medusa_heads(self, self.inference_config.num_medusa_heads, device=first.device)
         self.eval()
 
     # -- where the host model keeps its modules (Llama layout by default) ------------------------------------------
@@ -163,7 +169,7 @@ class KVCacheInferenceMixin:
     @torch.no_grad()
     def forward_infer(self, input_ids: torch.Tensor, position_ids: torch.Tensor, seq_ids: Optional[torch.Tensor] = None,
                       last_token_index: Optional[torch.Tensor] = None, return_logits: bool = False,
-                      uniform: Optional[torch.Tensor] = None):
+                      uniform: Optional[torch.Tensor] = None, return_hidden: bool = False):
         """``input_ids [B, T]``; ``position_ids [B, T]`` absolute positions; ``seq_ids [B]`` cache lines (default
         ``arange(B)``); ``last_token_index [B]`` index (within T) of the last real prompt token (context encoding with
         right padding).  Returns sampled tokens ``[B]`` (and the ``[B, V]`` logits with ``return_logits``)."""
@@ -192,11 +198,14 @@ class KVCacheInferenceMixin:
         logits = mappings.gather_from_tensor_model_parallel_region(logits)[:, : self.config.vocab_size]
         tokens = self.sampler.sample(logits.float() if logits.dtype not in (torch.float32, torch.bfloat16) else logits,
                                      uniform)
+        if return_hidden:                  # final-norm output of the selected position: what extra heads (Medusa) read
+            return tokens, logits, hidden
         return (tokens, logits) if return_logits else tokens
 
     @torch.no_grad()
     def forward_speculation(self, input_ids: torch.Tensor, position_ids: torch.Tensor,
-                            seq_ids: Optional[torch.Tensor] = None, return_logits: bool = False):
+                            seq_ids: Optional[torch.Tensor] = None, return_logits: bool = False,
+                            return_hidden: bool = False):
         """The ``speculation_model`` graph of the reference (``model_base.py:853-860``): the TARGET model on ``k + 1``
         tokens per sequence at consecutive positions, on top of the KV cache.  Writes their K/V into the cache (rows
         past the accepted prefix are simply overwritten by the next round) and returns the greedy token after EVERY
@@ -215,6 +224,8 @@ class KVCacheInferenceMixin:
                                    residual.reshape(B * T, H).contiguous())
         logits = mappings.gather_from_tensor_model_parallel_region(self.lm_head(hidden))[:, : self.config.vocab_size]
         tokens = logits.argmax(dim=-1).reshape(B, T)
+        if return_hidden:
+            return tokens, logits.reshape(B, T, -1), hidden.reshape(B, T, H)
         return (tokens, logits.reshape(B, T, -1)) if return_logits else tokens
 
     def forward(self, input_ids: torch.Tensor, position_ids: torch.Tensor, seq_ids: Optional[torch.Tensor] = None,

@@ -107,3 +107,40 @@ def test_runner_speculative_generation():
     out = target.generate_speculative(draft, prompt, max_new_tokens=20)
     assert torch.equal(out, ref), (out, ref)
     assert len(target.last_acceptance) < 19
+
+
+def test_medusa_generation_equals_base_greedy():
+    """Medusa heads + candidate tree + path verification on forked cache lines: whatever the heads guess, the output
+    is the base model's greedy continuation; heads that guess well make it take fewer model calls."""
+    from neuronx_distributed_llama3_2_b200.inference import InferenceConfig, LlamaInferenceModel
+    from neuronx_distributed_llama3_2_b200.inference.medusa import DEFAULT_MEDUSA_CHOICES, medusa_generate
+    from neuronx_distributed_llama3_2_b200.models import LlamaForCausalLM, tiny_llama
+
+    torch.manual_seed(0)
+    sd = LlamaForCausalLM(tiny_llama(sequence_parallel_enabled=False)).state_dict()
+    ref = LlamaInferenceModel(tiny_llama(sequence_parallel_enabled=False),
+                              InferenceConfig(batch_size=1, max_context_length=32, seq_len=96))
+    ref.load_state_dict(sd)
+    prompt = torch.randint(1, 512, (13,), generator=torch.Generator().manual_seed(3))
+    want = ref.generate(prompt.unsqueeze(0), max_new_tokens=30)[0, 13:]
+    n_paths = 4                                                   # leaves of the default tree
+    ic = InferenceConfig(batch_size=n_paths + 1, max_context_length=32, seq_len=96, paged_kv=True, page_size=8,
+                         num_kv_pages=40, num_medusa_heads=3)
+    model = LlamaInferenceModel(tiny_llama(sequence_parallel_enabled=False), ic)
+    missing = model.load_state_dict(sd, strict=False)
+    assert sorted(missing.missing_keys) == sorted(
+        f"medusa_head_{i}.{k}" for i in range(3) for k in ("0.linear.weight", "0.linear.bias", "1.weight"))
+    # untrained heads (random projection): guesses are mostly wrong, the result must still be the greedy one
+    got, acc = medusa_generate(model, prompt, 30, DEFAULT_MEDUSA_CHOICES)
+    assert torch.equal(got, want), (got, want)
+    assert len(acc) >= 30 // 4 and model.kv_cache.pool.num_free >= 40 - 2 * ((13 + 30 + 8) // 8 + 1)
+    # heads that copy the LM head guess "the same token again": right whenever the model repeats itself, which this
+    # random model soon does -- accepted guesses then cut the number of model calls
+    with torch.no_grad():
+        for i in range(3):
+            getattr(model, f"medusa_head_{i}")[1].weight.copy_(model.lm_head.weight)
+    got2, acc2 = medusa_generate(model, prompt, 30)
+    assert torch.equal(got2, want)
+    assert sum(a + 1 for a in acc2) >= 30 and all(0 <= a <= 3 for a in acc2)
+    assert max(acc2) == 3 and len(acc2) < len(acc) // 2, (acc2, len(acc))
+    assert model.kv_cache.pool.num_free >= 40 - ((13 + 34) // 8 + 1)          # losing forks gave their pages back
