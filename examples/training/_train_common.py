@@ -31,6 +31,9 @@ def add_common_args(ap: argparse.ArgumentParser) -> argparse.ArgumentParser:
     ap.add_argument("--data_dir", default=None, help="tokenised dataset (get_dataset.py); synthetic tokens when omitted")
     ap.add_argument("--pretrained_weight", default=None, help="<dir>/<tag> written by convert_checkpoints.py")
     ap.add_argument("--tensor_parallel_size", type=int, default=1)
+    ap.add_argument("--pipeline_parallel_size", type=int, default=1)
+    ap.add_argument("--num_microbatches", type=int, default=4, help="pipeline parallelism: micro-batches per step "
+                    "(--batch_size is then the batch of one step on a data-parallel rank)")
     ap.add_argument("--use_sequence_parallel", type=int, default=1)
     ap.add_argument("--layers", type=int, default=0, help="override the layer count (smoke runs)")
     ap.add_argument("--seq_len", type=int, default=2048)
@@ -54,6 +57,16 @@ def add_common_args(ap: argparse.ArgumentParser) -> argparse.ArgumentParser:
     ap.add_argument("--logging_interval", type=int, default=1)
     ap.add_argument("--seed", type=int, default=1234)
     return ap
+
+
+def pipeline_kwargs(args, layer_cls, input_names) -> dict:
+    """``pipeline_parallel_size`` / ``pipeline_config`` for ``neuronx_distributed_config`` (empty without PP)."""
+    if args.pipeline_parallel_size <= 1:
+        return {}
+    return {"pipeline_parallel_size": args.pipeline_parallel_size,
+            "pipeline_config": {"transformer_layer_cls": layer_cls, "num_microbatches": args.num_microbatches,
+                                "auto_partition": True, "input_names": list(input_names),
+                                "broadcast_and_average_loss": True, "use_zero1_optimizer": bool(args.use_zero_1)}}
 
 
 def init_process_group() -> torch.device:

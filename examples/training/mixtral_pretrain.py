@@ -22,6 +22,7 @@ import _train_common as C  # noqa: E402  (puts the repo root on sys.path)
 import neuronx_distributed_llama3_2_b200 as nxd  # noqa: E402
 from neuronx_distributed_llama3_2_b200.models import (MixtralConfig, MixtralForCausalLM, config_from_json,  # noqa: E402
                                                       mixtral_8x7b, tiny_mixtral)
+from neuronx_distributed_llama3_2_b200.models.mixtral import MixtralDecoderLayer  # noqa: E402
 
 
 def main():
@@ -37,7 +38,8 @@ def main():
         tensor_parallel_size=args.tensor_parallel_size, expert_parallel_size=args.expert_parallel_size,
         sequence_parallel=sp,
         optimizer_config={"zero_one_enabled": bool(args.use_zero_1), "grad_clipping": True, "max_grad_norm": 1.0},
-        activation_checkpoint_config="full" if args.full_activation_checkpoint else None)
+        activation_checkpoint_config="full" if args.full_activation_checkpoint else None,
+        **C.pipeline_kwargs(args, MixtralDecoderLayer, ["input_ids", "labels"]))
     kw = dict(sequence_parallel_enabled=sp, capacity_factor=args.capacity_factor,
               router_aux_loss_coef=args.router_aux_loss_coef)
     if args.model_path:

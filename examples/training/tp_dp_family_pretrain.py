@@ -26,6 +26,8 @@ import neuronx_distributed_llama3_2_b200 as nxd  # noqa: E402
 from neuronx_distributed_llama3_2_b200.models import (BertConfig, BertForPreTraining, GPTNeoXConfig,  # noqa: E402
                                                       GPTNeoXForCausalLM, bert_large, codegen25_7b, config_from_json,
                                                       gpt_neox_20b, tiny_bert, tiny_gpt_neox)
+from neuronx_distributed_llama3_2_b200.models.bert import BertLayer  # noqa: E402
+from neuronx_distributed_llama3_2_b200.models.gpt_neox import GPTNeoXLayer  # noqa: E402
 from neuronx_distributed_llama3_2_b200.utils.data import BertPretrainingDataset  # noqa: E402
 
 
@@ -56,8 +58,7 @@ def bert_batches(args, cfg, device):
         pick = torch.rand(ids.shape, generator=gen) < 0.15
         labels[pick] = ids[pick]
         nsp = torch.randint(0, 2, (args.batch_size,), generator=gen)
-        yield {"input_ids": ids.to(device), "token_type_ids": None, "attention_mask": None, "labels": labels.to(device),
-               "next_sentence_label": nsp.to(device)}
+        yield {"input_ids": ids.to(device), "labels": labels.to(device), "next_sentence_label": nsp.to(device)}
 
 
 def main():
@@ -68,10 +69,18 @@ def main():
     args = ap.parse_args()
     device = C.init_process_group()
     sp = bool(args.use_sequence_parallel) and args.tensor_parallel_size > 1
+    if args.family == "bert":
+        # pipeline tracing fixes the inputs that are None (synthetic batches carry no segment ids / padding mask)
+        layer_cls = BertLayer
+        input_names = (["input_ids", "token_type_ids", "attention_mask", "labels", "next_sentence_label"] if args.data_dir
+                       else ["input_ids", "labels", "next_sentence_label"])
+    else:
+        layer_cls, input_names = GPTNeoXLayer, ["input_ids", "labels"]
     nxd_config = nxd.neuronx_distributed_config(
         tensor_parallel_size=args.tensor_parallel_size, sequence_parallel=sp,
         optimizer_config={"zero_one_enabled": bool(args.use_zero_1), "grad_clipping": True, "max_grad_norm": 1.0},
-        activation_checkpoint_config="full" if args.full_activation_checkpoint else None)
+        activation_checkpoint_config="full" if args.full_activation_checkpoint else None,
+        **C.pipeline_kwargs(args, layer_cls, input_names))
     kw = dict(sequence_parallel_enabled=sp)
     if device.type != "cuda":
         kw["torch_dtype"] = torch.float32

@@ -187,7 +187,8 @@ class BertForPreTraining(nn.Module):
         from torch.utils.checkpoint import checkpoint
 
         cfg = self.config
-        if attention_mask is not None and bool(attention_mask.all()):
+        if (attention_mask is not None and not isinstance(attention_mask, torch.fx.Proxy)
+                and bool(attention_mask.all())):       # nothing is padded: take the flash-attention path
             attention_mask = None
         hidden = self.embeddings(input_ids, token_type_ids)
         for layer in self.layers:

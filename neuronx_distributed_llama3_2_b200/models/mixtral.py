@@ -87,6 +87,8 @@ class MixtralDecoderLayer(nn.Module):
 class MixtralForCausalLM(nn.Module):
     """``forward(input_ids, labels)`` -> ``lm_loss + router_aux_loss_coef * load_balancing_loss``."""
 
+    _fx_wrap_functions = [load_balancing_loss_func]       # kept opaque by the pipeline tracer (pipeline/trace.py)
+
     def __init__(self, config: MixtralConfig, device=None):
         super().__init__()
         self.config = config
@@ -129,8 +131,9 @@ class MixtralForCausalLM(nn.Module):
             return logits
         loss = self.loss_fn(logits, labels)
         if cfg.output_router_logits and all_router_logits:
-            aux = load_balancing_loss_func(torch.cat(all_router_logits, dim=0), cfg.num_local_experts,
-                                           cfg.num_experts_per_tok)
+            # the list goes in as is: under pipeline tracing the call is one opaque node (``_fx_wrap_functions``) whose
+            # inputs are the per-layer router logits carried from their stages to the last one
+            aux = load_balancing_loss_func(all_router_logits, cfg.num_local_experts, cfg.num_experts_per_tok)
             loss = loss + cfg.router_aux_loss_coef * aux
         return loss
 

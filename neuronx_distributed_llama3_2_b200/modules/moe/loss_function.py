@@ -15,7 +15,8 @@ import torch
 def load_balancing_loss_func(concatenated_gate_logits: Union[torch.Tensor, Sequence[torch.Tensor]], num_experts: int,
                              top_k: int) -> torch.Tensor:
     if not isinstance(concatenated_gate_logits, torch.Tensor):
-        concatenated_gate_logits = torch.cat([g.reshape(-1, g.shape[-1]) for g in concatenated_gate_logits], dim=0)
+        concatenated_gate_logits = torch.cat([g.reshape(-1, g.shape[-1]) for g in concatenated_gate_logits
+                                              if g is not None], dim=0)
     logits = concatenated_gate_logits.reshape(-1, num_experts).float()
     probs = torch.softmax(logits, dim=-1)
     _, selected = torch.topk(probs, top_k, dim=-1)

@@ -7,6 +7,7 @@ from __future__ import annotations
 from dataclasses import dataclass, field
 from typing import Dict, List, Optional, Sequence, Tuple
 
+import torch
 import torch.fx as fx
 from torch.fx.passes.split_module import split_module
 
@@ -73,7 +74,51 @@ def partition_traced_model(traced: fx.GraphModule, cut_names: Sequence[str]) -> 
                          f"{[n.target for n in traced.graph.nodes if n.op == 'call_module'][:50]}")
     # getitem nodes that unpack a cut node's tuple output belong to the NEXT stage (they were assigned there already
     # because they come after the cut node in topological order)
-    return split_module(traced, None, lambda n: stage_of[n])
+    split = split_module(traced, None, lambda n: stage_of[n])
+    _sink_root_attributes(split)
+    return split
+
+
+def _sink_root_attributes(split: fx.GraphModule) -> None:
+    """Parameters / buffers that the model's own ``forward`` reads directly (``self.bias``, a norm that is traced through)
+    are ``get_attr`` nodes of the ROOT graph after ``split_module`` and reach the stages as call arguments.  A stage must
+    own what it uses -- local parameter lists, optimizer, checkpoint names all go by stage -- so each such tensor is
+    registered on the consuming stage module (the same object on every stage that uses it: a shared weight) and read there."""
+    changed = False
+    for node in list(split.graph.nodes):
+        if node.op != "get_attr":
+            continue
+        obj = split
+        for part in node.target.split("."):
+            obj = getattr(obj, part)
+        if not isinstance(obj, torch.Tensor):
+            continue
+        for user in list(node.users):
+            if user.op != "call_module" or not str(user.target).startswith("submod_"):
+                continue
+            sub = getattr(split, user.target)
+            local = "_root_" + node.target.replace(".", "_")
+            if not hasattr(sub, local):
+                if isinstance(obj, torch.nn.Parameter):
+                    sub.register_parameter(local, obj)
+                else:
+                    sub.register_buffer(local, obj)
+            while node in user.args:
+                pos = list(user.args).index(node)
+                ph = [n for n in sub.graph.nodes if n.op == "placeholder"][pos]
+                with sub.graph.inserting_after(ph):
+                    inner = sub.graph.get_attr(local)
+                ph.replace_all_uses_with(inner)
+                sub.graph.erase_node(ph)
+                user.args = tuple(a for i, a in enumerate(user.args) if i != pos)
+            sub.graph.lint()
+            sub.recompile()
+            changed = True
+        if not node.users:
+            split.graph.erase_node(node)
+    if changed:
+        split.graph.lint()
+        split.recompile()
 
 
 def analyze_pipeline_module(split: fx.GraphModule) -> Tuple[List[str], List[StageIO]]:

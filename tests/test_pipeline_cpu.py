@@ -296,3 +296,110 @@ def test_partition_io_maps_and_shared_weights_of_eight_stage_model():
     torch.testing.assert_close(split(ids, mask, labels), model(ids, mask, labels))
     with pytest.raises(ValueError):
         P.partition_traced_model(traced, ["h.42"])
+
+
+def _pp_mixtral_worker(rank, world):
+    """Mixtral under pipeline parallelism: the decoder layer returns (hidden, residual, router logits); the router logits
+    of the first stage travel to the last one, where the load-balancing loss is one opaque node of the traced graph."""
+    from neuronx_distributed_llama3_2_b200 import trainer as nxd
+    from neuronx_distributed_llama3_2_b200.models import MixtralForCausalLM, tiny_mixtral
+    from neuronx_distributed_llama3_2_b200.models.mixtral import MixtralDecoderLayer
+
+    nxd_cfg = nxd.neuronx_distributed_config(
+        tensor_parallel_size=1, pipeline_parallel_size=2,
+        pipeline_config={"transformer_layer_cls": MixtralDecoderLayer, "num_microbatches": 2, "auto_partition": True,
+                         "input_names": ["input_ids", "labels"]},
+        optimizer_config={"zero_one_enabled": True, "grad_clipping": True, "max_grad_norm": 1.0})
+
+    def build():
+        torch.manual_seed(0)
+        return MixtralForCausalLM(tiny_mixtral(sequence_parallel_enabled=False, num_hidden_layers=4, capacity_factor=1.0))
+
+    ref = build()
+    ids = torch.randint(0, 512, (4, 32), generator=torch.Generator().manual_seed(1))
+    ref_loss = torch.stack([ref(c, labels=c) for c in torch.chunk(ids, 2, dim=0)]).mean()
+    ref_loss.backward()
+    ref_grads = {n: p.grad.clone() for n, p in ref.named_parameters() if p.grad is not None}
+    model = nxd.initialize_parallel_model(nxd_cfg, build, device=torch.device("cpu"))
+    loss = model.run_train(input_ids=ids, labels=ids)
+    if rank == world - 1:
+        assert abs(float(loss) - float(ref_loss)) < 1e-5, (float(loss), float(ref_loss))
+    checked = 0
+    for n, p in model.named_parameters():
+        if p.grad is not None and n in ref_grads:
+            torch.testing.assert_close(p.grad, ref_grads[n], atol=2e-5, rtol=1e-3, msg=lambda m: f"{n}: {m}")
+            checked += 1
+    assert checked > 5
+    # the aux loss reaches the routers of the FIRST stage too (their logits are inputs of the loss on the last stage)
+    if rank == 0:
+        g = dict(model.named_parameters())["layers.0.mlp.router.linear_router.weight"].grad
+        assert g is not None and float(g.abs().sum()) > 0
+    opt = nxd.initialize_parallel_optimizer(nxd_cfg, torch.optim.AdamW, model.parameters(), lr=1e-2)
+    losses = []
+    for _ in range(3):
+        opt.zero_grad()
+        out = model.run_train(input_ids=ids, labels=ids)
+        opt.step()
+        if out is not None:
+            losses.append(float(out))
+    if rank == world - 1:
+        assert losses[-1] < losses[0]
+
+
+def test_pp2_mixtral_matches_single_process():
+    run_distributed(_pp_mixtral_worker, 2)
+
+
+def _pp_family_worker(rank, world, fam):
+    """GPT-NeoX, DBRX and BERT under PP = 2.  DBRX's final norm is traced through and BERT adds ``self.decoder_bias`` in
+    its own forward: such root-level parameters are handed to the stage that reads them and keep their original names."""
+    from neuronx_distributed_llama3_2_b200 import models as M
+    from neuronx_distributed_llama3_2_b200 import trainer as nxd
+    from neuronx_distributed_llama3_2_b200.models.bert import BertLayer
+    from neuronx_distributed_llama3_2_b200.models.dbrx import DbrxDecoderLayer
+    from neuronx_distributed_llama3_2_b200.models.gpt_neox import GPTNeoXLayer
+
+    layer_cls = {"neox": GPTNeoXLayer, "dbrx": DbrxDecoderLayer, "bert": BertLayer}[fam]
+    names = ["input_ids", "labels"] + (["next_sentence_label"] if fam == "bert" else [])
+    nxd_cfg = nxd.neuronx_distributed_config(
+        tensor_parallel_size=1, pipeline_parallel_size=2,
+        pipeline_config={"transformer_layer_cls": layer_cls, "num_microbatches": 2, "auto_partition": True,
+                         "input_names": names},
+        optimizer_config={"zero_one_enabled": True, "grad_clipping": True, "max_grad_norm": 1.0})
+
+    def build():
+        torch.manual_seed(0)
+        if fam == "neox":
+            return M.GPTNeoXForCausalLM(M.tiny_gpt_neox(num_hidden_layers=4))
+        if fam == "dbrx":
+            return M.DbrxForCausalLM(M.tiny_dbrx(sequence_parallel_enabled=False, num_hidden_layers=4, capacity_factor=1.0))
+        return M.BertForPreTraining(M.tiny_bert(num_hidden_layers=4))
+
+    ref = build()
+    ids = torch.randint(0, 512, (4, 32), generator=torch.Generator().manual_seed(1))
+    kw = dict(input_ids=ids, labels=ids)
+    if fam == "bert":
+        kw["next_sentence_label"] = torch.tensor([0, 1, 1, 0])
+    ref_loss = torch.stack([ref(**{k: torch.chunk(v, 2, 0)[i] for k, v in kw.items()}) for i in range(2)]).mean()
+    ref_loss.backward()
+    # tied weights (BERT's MLM decoder = word embedding) have one tensor and two original names
+    ref_grads = {n: p.grad for n, p in ref.named_parameters(remove_duplicate=False) if p.grad is not None}
+    model = nxd.initialize_parallel_model(nxd_cfg, build, device=torch.device("cpu"))
+    loss = model.run_train(**kw)
+    if rank == world - 1:
+        assert abs(float(loss.detach()) - float(ref_loss.detach())) < 1e-5, (fam, float(loss), float(ref_loss))
+    local = dict(model.named_parameters())
+    assert set(local) <= set(ref_grads), set(local) - set(ref_grads)
+    for n, p in local.items():
+        if n in ref_grads:
+            assert p.grad is not None, n
+            torch.testing.assert_close(p.grad, ref_grads[n], atol=2e-5, rtol=1e-3, msg=lambda m: f"{fam} {n}: {m}")
+    root_level = {"dbrx": "norm.weight", "bert": "decoder_bias"}.get(fam)
+    if root_level and rank == world - 1:
+        assert root_level in local and local[root_level].grad is not None
+    assert root_level is None or root_level in model.state_dict() or rank != world - 1
+
+
+@pytest.mark.parametrize("fam", ["neox", "dbrx", "bert"])
+def test_pp2_other_families_match_single_process(fam):
+    run_distributed(_pp_family_worker, 2, fam)
