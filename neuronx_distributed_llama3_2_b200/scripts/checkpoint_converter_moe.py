@@ -8,7 +8,9 @@ coordinate; its ``tensor_model_parallel / partition_dim / partition_stride / fus
 how each tensor is cut (``inference.checkpoint_sharding.shard_children`` does the TP part, expert slabs are chunked on
 dim 0 over EP, layers are dealt to PP stages as ``NxDPPModel`` auto-partitioning would).  Merging reads the same tags.
 
-File layout is the trainer's: ``<out>/model/dp_rank_00[_ep_rank_EE]_tp_rank_TT_pp_rank_PP.pt`` + ``checkpoint`` / ``done``.
+File layout is the trainer's (``trainer/checkpoint.py``): ``<out>/model/dp_rank_00_tp_rank_TT_pp_rank_PP.pt`` and, with
+expert parallelism, the expert-parallel tensors apart in ``dp_rank_00_ep_rank_EE_tp_rank_TT_pp_rank_PP.pt`` (the dense
+remainder is written once per (tp, pp)); ``checkpoint`` / ``done`` markers.
 """
 from __future__ import annotations
 
@@ -85,6 +87,10 @@ class ModelDrivenCheckpointConverter:
     def _ep_arg(self, e: int) -> Optional[int]:
         return e if self.ep > 1 else None
 
+    def _expert_keys(self, tp_rank: int, ep_rank: int) -> set:
+        return {n for n, p in self._meta_model(tp_rank, ep_rank).state_dict(keep_vars=True).items()
+                if getattr(p, "expert_model_parallel", False)}
+
     # -- full -> sharded ---------------------------------------------------------------------------------------------
     def shard(self, full: Dict[str, torch.Tensor], tp_rank: int, ep_rank: int = 0) -> Dict[str, torch.Tensor]:
         """One (tp, ep) coordinate of the model-named full state (all PP stages)."""
@@ -102,13 +108,19 @@ class ModelDrivenCheckpointConverter:
         if self.tied_output and self.tied_output not in full and self.tied_input in full:
             full[self.tied_output] = full[self.tied_input]
         os.makedirs(os.path.join(out_dir, "model"), exist_ok=True)
+        save = xser.save if use_xser else torch.save
         for e in range(self.ep):
             for t in range(self.tp):
                 shard = self.shard(full, t, e)
+                expert_keys = self._expert_keys(t, e) if self.ep > 1 else set()
                 for s in range(self.pp):
                     part = {k: v.contiguous().clone() for k, v in shard.items() if s in self.stage_of_key(k)}
-                    path = self.shard_file(out_dir, t, s, self._ep_arg(e))
-                    (xser.save if use_xser else torch.save)(part, path)
+                    if self.ep > 1:
+                        save({k: v for k, v in part.items() if k in expert_keys}, self.shard_file(out_dir, t, s, e))
+                        if e == 0:
+                            save({k: v for k, v in part.items() if k not in expert_keys}, self.shard_file(out_dir, t, s))
+                    else:
+                        save(part, self.shard_file(out_dir, t, s))
         for marker in ("checkpoint", "done"):
             open(os.path.join(out_dir, marker), "w").write("1")
 
@@ -146,13 +158,22 @@ class ModelDrivenCheckpointConverter:
             is_x = os.path.isdir(path + ".tensors") if load_xser is None else load_xser
             return xser.load(path) if is_x else torch.load(path, map_location="cpu", weights_only=False)
 
+        def load_coord(t, s, e):
+            """Everything rank (tp t, pp s, ep e) holds: its expert file plus the dense file shared by the EP ranks."""
+            if self.ep == 1:
+                return load(self.shard_file(in_dir, t, s))
+            state = dict(load(self.shard_file(in_dir, t, s, e)))
+            dense = self.shard_file(in_dir, t, s)
+            if os.path.exists(dense) or os.path.isdir(dense + ".tensors"):
+                state.update(load(dense))
+            return state
+
         per_ep: List[Dict[str, torch.Tensor]] = []
         for e in range(self.ep):
             model = self._meta_model(0, e)
             merged: Dict[str, torch.Tensor] = {}
             for s in range(self.pp):
-                merged.update(self._merge_tp(model, [load(self.shard_file(in_dir, t, s, self._ep_arg(e)))
-                                                     for t in range(self.tp)]))
+                merged.update(self._merge_tp(model, [load_coord(t, s, e) for t in range(self.tp)]))
             per_ep.append(merged)
         full = dict(per_ep[0])
         if self.ep > 1:

@@ -234,7 +234,9 @@ def test_mixtral_converter_tp_pp_ep_round_trip(tmp_path):
                 local = MixtralForCausalLM(cfg, device="meta").state_dict()
             merged = {}
             for s in range(2):
-                part = torch.load(conv.shard_file(out, t, s, e), weights_only=False)
+                part = dict(torch.load(conv.shard_file(out, t, s, e), weights_only=False))      # expert tensors
+                assert part and all("expert_mlps" in k for k in part)
+                part.update(torch.load(conv.shard_file(out, t, s), weights_only=False))          # dense remainder
                 assert all(("layers.0." in k or "layers.1." in k or "embed" in k) == (s == 0) for k in part
                            if "layers." in k or "embed" in k), (s, list(part))
                 merged.update(part)

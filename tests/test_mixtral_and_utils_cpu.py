@@ -29,7 +29,7 @@ def test_tiny_mixtral_trains_single_process():
     assert losses[-1] < losses[0] - 0.3, losses
 
 
-def _moe_ep_worker(rank, world):
+def _moe_ep_worker(rank, world, tmp):
     from neuronx_distributed_llama3_2_b200 import trainer as nxd
     from neuronx_distributed_llama3_2_b200.models import MixtralForCausalLM, tiny_mixtral
     from neuronx_distributed_llama3_2_b200.optimizer import NeuronEPZero1Optimizer
@@ -54,9 +54,50 @@ def _moe_ep_worker(rank, world):
     assert losses[-1] < losses[0] - 0.2, losses
     assert float(opt.grad_norm) > 0
 
+    # checkpoint with expert parallelism: one model file per (ep, tp) coordinate, EP-aware ZeRO-1 state; round trip
+    import os
 
-def test_mixtral_tp2_ep2_sp_zero1_trains():
-    run_distributed(_moe_ep_worker, 4)
+    from neuronx_distributed_llama3_2_b200.scripts.checkpoint_converter_moe import CheckpointConverterMixtral
+
+    ep_rank, tp_rank = ps.get_expert_model_parallel_rank(), ps.get_tensor_model_parallel_rank()
+    nxd.save_checkpoint(tmp, "s", model=model, optimizer=opt, use_xser=False)
+    files = sorted(os.listdir(os.path.join(tmp, "s", "model")))
+    assert files == sorted([f"dp_rank_00_ep_rank_{e:02d}_tp_rank_{t:02d}_pp_rank_00.pt" for e in range(2) for t in range(2)]
+                           + [f"dp_rank_00_tp_rank_{t:02d}_pp_rank_00.pt" for t in range(2)]), files   # experts | dense
+    before = {k: v.clone() for k, v in model.state_dict().items()}
+    import copy
+
+    opt_before = copy.deepcopy(opt.state_dict())
+    opt.zero_grad()
+    model.run_train(ids, labels=ids)
+    opt.step()                                   # weights, master copies and moments all move away from the checkpoint
+    nxd.load_checkpoint(tmp, "s", model=model, optimizer=opt)
+    for k, v in model.state_dict().items():
+        assert torch.equal(v, before[k]), k
+    def tensors(obj, prefix=""):
+        if isinstance(obj, torch.Tensor):
+            yield prefix, obj
+        elif isinstance(obj, dict):
+            for k, v in obj.items():
+                yield from tensors(v, f"{prefix}/{k}")
+        elif isinstance(obj, (list, tuple)):
+            for i, v in enumerate(obj):
+                yield from tensors(v, f"{prefix}/{i}")
+
+    a, b = dict(tensors(opt_before)), dict(tensors(opt.state_dict()))
+    assert a and set(a) == set(b) and all(torch.equal(a[k], b[k]) for k in a)
+    # the offline converter merges those (tp, ep) shards into HF names and cuts them again: this rank's shard comes back
+    mcfg = tiny_mixtral(capacity_factor=1.5)
+    conv = CheckpointConverterMixtral(mcfg, tp_size=2, ep_size=2)
+    hf = conv.convert_to_full_state(os.path.join(tmp, "s"))
+    assert hf["model.layers.0.block_sparse_moe.experts.3.w1.weight"].shape == (mcfg.intermediate_size, mcfg.hidden_size)
+    mine = conv.shard(conv.to_model_names(dict(hf)), tp_rank, ep_rank)
+    for k, v in before.items():
+        torch.testing.assert_close(mine[k], v, msg=lambda m: f"{k}: {m}")
+
+
+def test_mixtral_tp2_ep2_sp_zero1_trains(tmp_path):
+    run_distributed(_moe_ep_worker, 4, str(tmp_path))
 
 
 def test_training_utils():
