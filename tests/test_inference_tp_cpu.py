@@ -103,3 +103,40 @@ def _oracle(rank, world):
 
 def test_tp2_inference_stack_matches_single_process():
     run_distributed(_tp_worker, 2)
+
+
+def _tp_moe_worker(rank, world):
+    from neuronx_distributed_llama3_2_b200.inference import (DbrxInferenceModel, DbrxRunner, InferenceConfig,
+                                                             MixtralInferenceModel, MixtralRunner)
+    from neuronx_distributed_llama3_2_b200.models import DbrxForCausalLM, MixtralForCausalLM, tiny_dbrx, tiny_mixtral
+    from neuronx_distributed_llama3_2_b200.parallel import parallel_state as ps
+    from neuronx_distributed_llama3_2_b200.scripts.checkpoint_converter_moe import mock_parallel_state
+
+    families = (("mixtral", MixtralForCausalLM, MixtralInferenceModel, MixtralRunner, tiny_mixtral),
+                ("dbrx", DbrxForCausalLM, DbrxInferenceModel, DbrxRunner, tiny_dbrx))
+    oracle = {}
+    with mock_parallel_state(1, 0):                      # single-rank oracle before the real groups exist
+        for name, train_cls, inf_cls, _, cfg_fn in families:
+            torch.manual_seed(0)
+            mk = lambda: cfg_fn(sequence_parallel_enabled=False, capacity_factor=None)   # noqa: E731
+            sd = {k: v.clone() for k, v in train_cls(mk()).state_dict().items()}
+            ref = inf_cls(mk(), InferenceConfig(batch_size=2, max_context_length=32, seq_len=64))
+            ref.load_state_dict(sd)
+            prompts = torch.randint(1, 512, (2, 11), generator=torch.Generator().manual_seed(2))
+            oracle[name] = (sd, prompts, ref.generate(prompts, max_new_tokens=6))
+    ps.initialize_model_parallel(tensor_model_parallel_size=2)
+    for name, _, _, runner_cls, cfg_fn in families:
+        sd, prompts, want = oracle[name]
+        ic = InferenceConfig(tp_degree=2, batch_size=2, max_context_length=32, seq_len=64, buckets=[16, 32],
+                             use_cuda_graphs=False)
+        r = runner_cls(cfg_fn(sequence_parallel_enabled=False, capacity_factor=None), ic, checkpoint_loader=lambda: sd,
+                       device=torch.device("cpu"))
+        r.trace()
+        experts = r.model.layers[0].mlp.expert_mlps.mlp_op.down_proj.weight
+        assert experts.shape[1] * 2 == sd["layers.0.mlp.expert_mlps.mlp_op.down_proj.weight"].shape[1]     # TP-sharded slabs
+        got = r.generate(prompts, max_new_tokens=6)
+        assert torch.equal(got, want), (rank, name, got, want)
+
+
+def test_tp2_moe_inference_matches_single_process():
+    run_distributed(_tp_moe_worker, 2)
