@@ -27,8 +27,11 @@ from neuronx_distributed_llama3_2_b200.utils.training_utils import CosineAnneali
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--model", default="llama3.2-1b", choices=sorted(PRESETS))
+    ap.add_argument("--model", default="llama3.2-1b", choices=sorted(PRESETS) + ["mixtral-8x7b", "tiny-mixtral"],
+                    help="a Llama preset, or a Mixtral one (the reference's mixtral_pretrain example is its Lightning driver)")
+    ap.add_argument("--layers", type=int, default=0)
     ap.add_argument("--tensor_parallel_size", type=int, default=1)
+    ap.add_argument("--expert_parallel_size", type=int, default=1)
     ap.add_argument("--seq_len", type=int, default=4096)
     ap.add_argument("--batch_size", type=int, default=1)
     ap.add_argument("--grad_accum_steps", type=int, default=1)
@@ -46,13 +49,21 @@ def main():
     device = torch.device("cuda", torch.cuda.current_device()) if cuda else torch.device("cpu")
     sp = args.tensor_parallel_size > 1
     nxd_config = nxd.neuronx_distributed_config(
-        tensor_parallel_size=args.tensor_parallel_size, sequence_parallel=sp,
-        optimizer_config={"zero_one_enabled": True, "grad_clipping": True, "max_grad_norm": 1.0})
-    cfg = PRESETS[args.model](sequence_parallel_enabled=sp)
+        tensor_parallel_size=args.tensor_parallel_size, expert_parallel_size=args.expert_parallel_size,
+        sequence_parallel=sp, optimizer_config={"zero_one_enabled": True, "grad_clipping": True, "max_grad_norm": 1.0})
+    if "mixtral" in args.model:
+        from neuronx_distributed_llama3_2_b200.models import MixtralForCausalLM, mixtral_8x7b, tiny_mixtral
+
+        cfg = (tiny_mixtral if args.model.startswith("tiny") else mixtral_8x7b)(sequence_parallel_enabled=sp)
+        model_cls = MixtralForCausalLM
+    else:
+        cfg, model_cls = PRESETS[args.model](sequence_parallel_enabled=sp), LlamaForCausalLM
+    if args.layers:
+        cfg.num_hidden_layers = args.layers
     if not cuda:
         cfg.torch_dtype = torch.float32
     module = NeuronLTModule(nxd_config, torch.optim.AdamW, CosineAnnealing,
-                            model_fn=lambda **kw: LlamaForCausalLM(cfg, device=device),
+                            model_fn=lambda **kw: model_cls(cfg, device=device),
                             opt_kwargs={"lr": args.lr, "betas": (0.9, 0.95), "weight_decay": 0.1},
                             scheduler_kwargs={"max_steps": args.max_steps, "warmup_steps": max(1, args.max_steps // 10)},
                             grad_accum_steps=args.grad_accum_steps, device=device)
