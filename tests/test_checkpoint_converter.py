@@ -267,3 +267,75 @@ def test_mixtral_converter_tp_pp_ep_round_trip(tmp_path):
                                     "--convert_to_full_state"] + common)
     again = torch.load(tmp_path / "f2" / "checkpoint.pt", weights_only=False)
     assert all(torch.equal(again[k], hf[k]) for k in hf)
+
+
+def _load_converted_worker(rank, world, tmp):
+    """HF-named weights -> offline converter (tp 2 x pp 2) -> ``nxd.load_checkpoint`` into a TP2 x PP2 (+SP) model: the
+    training loss equals the one of a single-process model holding the same weights."""
+    from neuronx_distributed_llama3_2_b200 import trainer as nxd
+    from neuronx_distributed_llama3_2_b200.inference import _mock_parallel_state
+    from neuronx_distributed_llama3_2_b200.models import LlamaForCausalLM, tiny_llama
+    from neuronx_distributed_llama3_2_b200.models.llama import LlamaDecoderLayer
+
+    ids = torch.randint(0, 512, (4, 32), generator=torch.Generator().manual_seed(9))
+    with _mock_parallel_state(1, 0):
+        torch.manual_seed(123)
+        full = LlamaForCausalLM(tiny_llama(num_hidden_layers=4, sequence_parallel_enabled=False))
+        conv = CheckpointConverterBase(4, 8, 2, 32, tp_size=2, pp_size=2, tie_word_embeddings=True)
+        hf = CheckpointConverterBase(4, 8, 2, 32, tie_word_embeddings=True).nxd_full_to_hf(full.state_dict())
+        with torch.no_grad():
+            want = float(torch.stack([full(c, labels=c) for c in torch.chunk(ids, 2, 0)]).mean())
+    ckpt = os.path.join(tmp, "pretrained")
+    if rank == 0:
+        conv.convert_from_full_state(hf, ckpt)
+    torch.distributed.barrier()
+    nxd_cfg = nxd.neuronx_distributed_config(
+        tensor_parallel_size=2, pipeline_parallel_size=2, sequence_parallel=True,
+        pipeline_config={"transformer_layer_cls": LlamaDecoderLayer, "num_microbatches": 2, "auto_partition": True,
+                         "input_names": ["input_ids", "labels"], "broadcast_and_average_loss": True})
+    torch.manual_seed(7)                                  # different random init: the checkpoint must overwrite it
+    model = nxd.initialize_parallel_model(nxd_cfg, lambda: LlamaForCausalLM(tiny_llama(num_hidden_layers=4)),
+                                          device=torch.device("cpu"))
+    nxd.load_checkpoint(tmp, tag="pretrained", model=model, strict=False)
+    got = float(model.run_train(input_ids=ids, labels=ids))
+    assert abs(got - want) < 2e-5, (rank, got, want)
+
+
+def test_converted_tp2_pp2_checkpoint_loads_into_parallel_model(tmp_path):
+    from conftest import run_distributed
+
+    run_distributed(_load_converted_worker, 4, str(tmp_path))
+
+
+def _load_kv_replicated_worker(rank, world, tmp):
+    """tp = 4 with 2 KV heads: the converter tiles the KV heads twice and re-orders the query heads so that every rank's
+    queries sit next to the KV head it holds; the model (``kv_shared_group_size=2``) must compute the same loss."""
+    from neuronx_distributed_llama3_2_b200 import trainer as nxd
+    from neuronx_distributed_llama3_2_b200.inference import _mock_parallel_state
+    from neuronx_distributed_llama3_2_b200.models import LlamaForCausalLM, tiny_llama
+
+    ids = torch.randint(0, 512, (2, 32), generator=torch.Generator().manual_seed(9))
+    with _mock_parallel_state(1, 0):
+        torch.manual_seed(321)
+        full = LlamaForCausalLM(tiny_llama(sequence_parallel_enabled=False))
+        hf = CheckpointConverterBase(2, 8, 2, 32, tie_word_embeddings=True).nxd_full_to_hf(full.state_dict())
+        with torch.no_grad():
+            want = float(full(ids, labels=ids))
+    ckpt = os.path.join(tmp, "pretrained")
+    if rank == 0:
+        CheckpointConverterBase(2, 8, 2, 32, tp_size=4, kv_size_multiplier=2, tie_word_embeddings=True
+                                ).convert_from_full_state(hf, ckpt)
+    torch.distributed.barrier()
+    nxd_cfg = nxd.neuronx_distributed_config(tensor_parallel_size=4, sequence_parallel=True)
+    torch.manual_seed(7)
+    model = nxd.initialize_parallel_model(nxd_cfg, lambda: LlamaForCausalLM(tiny_llama(kv_shared_group_size=2)),
+                                          device=torch.device("cpu"))
+    nxd.load_checkpoint(tmp, tag="pretrained", model=model, strict=False)
+    got = float(model(ids, labels=ids))
+    assert abs(got - want) < 2e-5, (rank, got, want)
+
+
+def test_converted_kv_replicated_checkpoint_loads_at_tp4(tmp_path):
+    from conftest import run_distributed
+
+    run_distributed(_load_kv_replicated_worker, 4, str(tmp_path))
