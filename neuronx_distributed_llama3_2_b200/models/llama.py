@@ -244,6 +244,32 @@ class LlamaAttention(nn.Module):
                                         input_is_parallel=True, init_method=init, sequence_parallel_enabled=sp,
                                         dtype=dt, device=device)
 
+    def preshard_hook(self, model_state_dict: dict, prefix: str) -> None:
+        """Called on an UN-SHARDED state dict right before it is cut for a TP rank (``get_sharded_checkpoint`` /
+        ``parallel.checkpointing``; reference ``GQAQKVColumnParallelLinear.preshard_hook``, ``modules/qkv_linear.py``).
+        With replicated KV heads rank ``r`` holds KV head ``r % n_kv``, so the query heads -- and the matching columns of
+        the output projection -- are re-ordered for a contiguous split to hand every rank the queries of ITS KV head.
+        (Checkpoints written by the offline converter are permuted and sharded already and never pass through here.)"""
+        m = self.kv_size_multiplier
+        if m <= 1:
+            return
+        from ..parallel import parallel_state as ps
+        from ..scripts.checkpoint_converter import q_head_permutation
+
+        base = prefix[: -len("weight")]
+        D = self.head_dim
+        perm = q_head_permutation(self.num_heads, self.num_kv_heads, ps.get_tensor_model_parallel_size(), m)
+        rows = torch.tensor([h * D + d for h in perm for d in range(D)])
+        qs = self.num_heads * D
+        for key in (base + "qkv_proj.weight_qkv", base + "qkv_proj.weight_q", base + "qkv_proj.bias_qkv",
+                    base + "qkv_proj.bias_q"):
+            t = model_state_dict.get(key)
+            if t is not None:
+                model_state_dict[key] = torch.cat([t[:qs][rows.to(t.device)], t[qs:]], dim=0)
+        o = model_state_dict.get(base + "o_proj.weight")
+        if o is not None:
+            model_state_dict[base + "o_proj.weight"] = o[:, rows.to(o.device)]
+
     def forward(self, x: torch.Tensor, cos: torch.Tensor, sin: torch.Tensor) -> torch.Tensor:
         nq, nkv, D = self.q_heads_local, self.kv_heads_local, self.head_dim
         if self.config.fuse_qkv:

@@ -140,3 +140,28 @@ def _tp_moe_worker(rank, world):
 
 def test_tp2_moe_inference_matches_single_process():
     run_distributed(_tp_moe_worker, 2)
+
+
+def _tp4_kv_replication_worker(rank, world):
+    """tp = 4 with 2 KV heads: the un-sharded checkpoint goes through ``LlamaAttention.preshard_hook`` (query heads and
+    o_proj columns re-ordered next to the replicated KV head of each rank) before it is cut."""
+    from neuronx_distributed_llama3_2_b200.inference import InferenceConfig, InferenceRunner, _mock_parallel_state
+    from neuronx_distributed_llama3_2_b200.models import tiny_llama
+    from neuronx_distributed_llama3_2_b200.parallel import parallel_state as ps
+
+    with _mock_parallel_state(1, 0):
+        sd, ref = _reference()
+        prompts = torch.randint(1, 512, (2, 11), generator=torch.Generator().manual_seed(2))
+        want = ref.generate(prompts, max_new_tokens=6)
+    ps.initialize_model_parallel(tensor_model_parallel_size=4)
+    ic = InferenceConfig(tp_degree=4, batch_size=2, max_context_length=32, seq_len=96, buckets=[16, 32], use_cuda_graphs=False)
+    r = InferenceRunner(tiny_llama(sequence_parallel_enabled=False), ic, checkpoint_loader=lambda: sd, device=torch.device("cpu"))
+    r.trace()
+    attn = r.model.model.layers[0].self_attn
+    assert attn.kv_size_multiplier == 2 and attn.kv_heads_local == 1 and attn.q_heads_local == 2
+    got = r.generate(prompts, max_new_tokens=6)
+    assert torch.equal(got, want), (rank, got, want)
+
+
+def test_tp4_inference_with_replicated_kv_heads():
+    run_distributed(_tp4_kv_replication_worker, 4)
