@@ -142,6 +142,17 @@ class InferenceRunner:
             self.nxd_model.release_graphs()
 
     # -- generate -------------------------------------------------------------------------------------------------------
+    def _reserve_lines(self, n_lines: int, n_tokens: int) -> None:
+        """With a dynamic page pool (``num_kv_pages``) the cache lines of a ``generate`` call get their pages up front:
+        the loop itself runs captured graphs and never talks to the allocator."""
+        cache = self.model.kv_cache if self.model is not None else None
+        if cache is None or cache.pool is None:
+            return
+        for line in range(n_lines):
+            cache.free(line)
+        for line in range(n_lines):
+            cache.reserve(line, min(n_tokens, self.config.seq_len))
+
     def _bucket_len(self, n: int) -> int:
         if self.nxd_model is not None:
             hit = self.nxd_model.route_padded(CONTEXT_ENCODING_MODEL, self.config.ctx_batch_size, n)
@@ -166,6 +177,7 @@ class InferenceRunner:
         lens = attention_mask.sum(dim=1).to(torch.long)
         Tb = self._bucket_len(T)
         Bc = ic.ctx_batch_size
+        self._reserve_lines(max(Bc, ic.tkg_batch_size), Tb + max_new)
         ids = torch.full((Bc, Tb), ic.pad_token_id, dtype=torch.long, device=dev)
         ids[:B, :T] = input_ids.to(dev)
         pos = torch.arange(Tb, device=dev).unsqueeze(0).expand(Bc, Tb).contiguous()
@@ -223,6 +235,7 @@ class InferenceRunner:
         first = None
         for r in (draft, self):                                  # context encoding fills both KV caches
             Tb = r._bucket_len(T)
+            r._reserve_lines(r.config.ctx_batch_size, Tb + max_new + ic.speculation_length + 1)
             ids = torch.full((r.config.ctx_batch_size, Tb), r.config.pad_token_id, dtype=torch.long, device=dev)
             ids[:1, :T] = input_ids.to(dev)
             pos = torch.arange(Tb, device=dev).unsqueeze(0).expand(r.config.ctx_batch_size, Tb).contiguous()

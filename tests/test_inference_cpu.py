@@ -544,3 +544,21 @@ def test_continuous_batching_over_paged_pool_matches_isolated_generation():
         assert model.kv_cache.pool.num_free == n_pages
         assert st["decode_rows"] > st["decode_calls"]                       # requests really shared decode calls
         assert (st["preemptions"] > 0) == expect_preempt, st
+
+
+def test_runner_with_dynamic_page_pool_reserves_lines():
+    """``num_kv_pages`` with the runner: ``generate`` gives every cache line its pages up front (the loop itself never talks
+    to the allocator) and successive calls recycle them."""
+    from neuronx_distributed_llama3_2_b200.inference import InferenceRunner
+
+    cfg, train, _ = _models()
+    sd = {k: v.clone() for k, v in train.state_dict().items()}
+    outs = []
+    for kw in (dict(), dict(paged_kv=True, page_size=8, num_kv_pages=12)):
+        ic = InferenceConfig(batch_size=2, max_context_length=32, seq_len=64, buckets=[16, 32], use_cuda_graphs=False, **kw)
+        r = InferenceRunner(tiny_llama(sequence_parallel_enabled=False), ic, checkpoint_loader=lambda: sd, device=torch.device("cpu"))
+        r.trace()
+        p = torch.randint(1, cfg.vocab_size, (2, 11), generator=torch.Generator().manual_seed(2))
+        outs.append([r.generate(p, max_new_tokens=9), r.generate(p[:, :7], max_new_tokens=20)])
+    assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1])
+    assert r.model.kv_cache.pool.num_free == 12 - 2 * ((16 + 20 + 7) // 8)
