@@ -250,13 +250,16 @@ class LlamaAttention(nn.Module):
         With replicated KV heads rank ``r`` holds KV head ``r % n_kv``, so the query heads -- and the matching columns of
         the output projection -- are re-ordered for a contiguous split to hand every rank the queries of ITS KV head.
         (Checkpoints written by the offline converter are permuted and sharded already and never pass through here.)"""
+        base = prefix[: -len("weight")]
+        for name, child in self.named_children():      # the walk stops at a module with a hook: pass it on ourselves
+            if hasattr(child, "preshard_hook"):
+                child.preshard_hook(model_state_dict, base + name + ".weight")
         m = self.kv_size_multiplier
         if m <= 1:
             return
         from ..parallel import parallel_state as ps
         from ..scripts.checkpoint_converter import q_head_permutation
 
-        base = prefix[: -len("weight")]
         D = self.head_dim
         perm = q_head_permutation(self.num_heads, self.num_kv_heads, ps.get_tensor_model_parallel_size(), m)
         rows = torch.tensor([h * D + d for h in perm for d in range(D)])
