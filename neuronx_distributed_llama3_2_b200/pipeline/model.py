@@ -47,7 +47,10 @@ class NxDPPModel(nn.Module):
                  _turn_off_odd_even_scheduler: bool = False, _all_reduce_send_recv: bool = False,
                  _fused_send_recv: bool = False, _fused_fwd_bwd: bool = False, _deallocate_send_tensors: bool = True,
                  _use_gloo_for_metadata_comm: bool = False, _debug_mode: bool = False, _debug_pp_size: int = 8,
-                 _debug_pp_rank: int = 0, _delay_tracing: bool = False):
+                 _debug_pp_rank: int = 0, _delay_tracing: bool = False, _mark_step_before_pp_runtime: bool = True,
+                 _mark_step_after_pp_runtime: bool = True):
+        # the two ``_mark_step_*`` switches cut the XLA graph around the pipeline runtime in the reference; eager CUDA
+        # execution has no graph to cut, they are accepted so that reference configs load unchanged
         super().__init__()
         self.original_torch_module = module
         self.transformer_layer_cls = transformer_layer_cls

@@ -70,7 +70,9 @@ def trace_model(model: torch.nn.Module, input_names: Optional[List[str]] = None,
     leaves = tuple(leaf_modules or ()) + _default_leaf_classes()
     wrap_fns = list(PARALLEL_FUNCTIONS) + list(autowrap_functions or [])
     wrap_fns += list(getattr(model, "_fx_wrap_functions", []))
-    tracer = (tracer_cls or NxDTracer)(leaf_classes=leaves, autowrap_functions=wrap_fns,
+    if tracer_cls is None or isinstance(tracer_cls, str):        # None / "torch" / "hf" as in the reference's pipeline_config
+        tracer_cls = get_tracer_class(model, tracer_cls)
+    tracer = tracer_cls(leaf_classes=leaves, autowrap_functions=wrap_fns,
                                        autowrap_modules=tuple(autowrap_modules or ()))
     patched = []
     if autowrap_obj_methods:  # reference ``:125-148``: make bound methods opaque call_function nodes
