@@ -212,7 +212,12 @@ class NxDModel(torch.nn.Module):
 
 class ModelBuilder:
     def __init__(self, router=None, tp_degree: int = 1, checkpoint_loader: Optional[Callable[[], Dict[str, Any]]] = None,
-                 compiler_workdir: Optional[str] = None, debug: bool = False, use_cuda_graphs: bool = True):
+                 compiler_workdir: Optional[str] = None, debug: bool = False, use_cuda_graphs: bool = True,
+                 master_proc_env_vars: Optional[Dict[str, str]] = None):
+        # ``master_proc_env_vars``: environment of the reference's compile sub-processes; every rank is its own
+        # process here, so the variables are simply exported
+        for k, v in (master_proc_env_vars or {}).items():
+            os.environ[str(k)] = str(v)
         self.router = router
         self.tp_degree = tp_degree
         self.checkpoint_loader = checkpoint_loader
@@ -377,8 +382,10 @@ class StateInitializer(torch.nn.Module):
     """Allocates the per-rank state tensors of a traced model from ``{name: (shape, dtype)}`` (reference
     ``spmd.py:63-80`` builds them from the metaneff); used for KV caches that live outside ``KVCache``."""
 
-    def __init__(self, shapes: Dict[str, Any], dtypes: Dict[str, torch.dtype], local_ranks_size: int = 1):
+    def __init__(self, shapes: Dict[str, Any], dtypes: Dict[str, torch.dtype], local_ranks_size: int = 1,
+                 tp_degree: Optional[int] = None):
         super().__init__()
+        local_ranks_size = tp_degree if tp_degree is not None else local_ranks_size     # reference argument name
         self.shapes, self.dtypes, self.local_ranks_size = shapes, dtypes, local_ranks_size
 
     def forward(self, device=None) -> Dict[str, torch.Tensor]:

@@ -16,8 +16,9 @@ class NeuronLTModule(ModuleBase):
                  model_fn: Optional[Callable] = None, model_args: Tuple = (), model_kwargs: Optional[Dict] = None,
                  opt_args: Tuple = (), opt_kwargs: Optional[Dict] = None, scheduler_args: Tuple = (),
                  scheduler_kwargs: Optional[Dict] = None, grad_accum_steps: int = 1, log_rank0: bool = False,
-                 manual_opt: bool = True, device=None):
+                 manual_opt: bool = True, device=None, train_batch_size: int = 16, logging_interval: int = 1):
         super().__init__()
+        self.train_batch_size, self.logging_interval = train_batch_size, logging_interval
         self.nxd_config, self.opt_cls, self.scheduler_cls = nxd_config, opt_cls, scheduler_cls
         self.model_fn, self.model_args, self.model_kwargs = model_fn, model_args, dict(model_kwargs or {})
         self.opt_args, self.opt_kwargs = opt_args, dict(opt_kwargs or {})

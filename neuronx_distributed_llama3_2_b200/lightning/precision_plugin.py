@@ -10,9 +10,12 @@ from ._compat import PrecisionBase
 
 
 class NeuronXLAPrecisionPlugin(PrecisionBase):
-    def __init__(self, mode: str = "bf16-params", dtype: torch.dtype = torch.bfloat16):
+    def __init__(self, mode: str = "bf16-params", dtype: torch.dtype = torch.bfloat16,
+                 mixed_precision_enabled: bool = False):
+        """``mixed_precision_enabled`` is the reference's only argument (``precision_plugin.py:12-16``): fp32 master
+        weights live in the optimizer, the forward runs in ``dtype`` parameters -- the default ``bf16-params`` mode."""
         super().__init__()
-        self.mode, self.dtype = mode, dtype
+        self.mode, self.dtype, self.mixed_precision_enabled = mode, dtype, mixed_precision_enabled
 
     def forward_context(self):
         if self.mode == "autocast":

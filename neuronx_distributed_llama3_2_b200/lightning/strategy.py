@@ -18,7 +18,8 @@ from .launcher import _NxDLauncher
 class NeuronXLAStrategy(StrategyBase):
     def __init__(self, nxd_config: Optional[Dict[str, Any]] = None, tensor_parallel_size: int = 1,
                  pipeline_parallel_size: int = 1, save_load_xser: bool = True, accelerator=None, checkpoint_io=None,
-                 precision_plugin=None, **kw):
+                 precision_plugin=None, expert_parallel_size: int = 1, debug: bool = False,
+                 sync_module_states: bool = False, **kw):
         try:
             super().__init__(**kw)
         except TypeError:
@@ -26,7 +27,8 @@ class NeuronXLAStrategy(StrategyBase):
         self.nxd_config = nxd_config
         self.tensor_parallel_size = nxd_config["tensor_parallel_size"] if nxd_config else tensor_parallel_size
         self.pipeline_parallel_size = nxd_config["pipeline_parallel_size"] if nxd_config else pipeline_parallel_size
-        self.expert_parallel_size = (nxd_config or {}).get("expert_parallel_size", 1)
+        self.expert_parallel_size = nxd_config.get("expert_parallel_size", 1) if nxd_config else expert_parallel_size
+        self.debug, self._sync_module_states = debug, sync_module_states
         self._accelerator = accelerator or CudaNxDAccelerator()
         self._checkpoint_io = checkpoint_io or NeuronCheckpointIO(save_xser=save_load_xser, load_xser=save_load_xser)
         self._precision = precision_plugin

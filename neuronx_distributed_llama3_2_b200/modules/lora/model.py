@@ -175,7 +175,9 @@ class LoraModel(nn.Module):
         return res
 
     # -- single-file save / load (reference ``:467-492,559-603``) ----------------------------------------------
-    def save_lora(self, save_dir: Optional[str] = None, tag: str = "lora_adapter") -> str:
+    def save_lora(self, save_dir: Optional[str] = None, adapter_tag: Optional[str] = None, tag: Optional[str] = None) -> str:
+        """``adapter_tag`` is the reference's argument name, ``tag`` the older alias; default file ``lora_adapter.pt``."""
+        tag = adapter_tag or tag or "lora_adapter"
         save_dir = save_dir or self.lora_config.lora_save_dir
         assert save_dir, "lora_save_dir is not set"
         os.makedirs(save_dir, exist_ok=True)
@@ -190,9 +192,17 @@ class LoraModel(nn.Module):
             self.unmerge_lora()
         return path
 
-    def load_lora(self, config: Optional[LoraConfig] = None) -> None:
+    def load_lora(self, save_dir=None, adapter_tag: Optional[str] = None, ckpt_path: Optional[str] = None,
+                  adapter_only: bool = True, config: Optional[LoraConfig] = None) -> None:
+        """Single-file load (reference ``:559-591``): ``ckpt_path`` names the file directly, else
+        ``<save_dir>/<adapter_tag>.pt`` with both defaulting to the LoRA config.  A ``LoraConfig`` as first argument is
+        still accepted.  Whatever the file holds is loaded: the adapter (and ``modules_to_save``) always, base weights
+        when it was saved with ``save_lora_base`` -- ``adapter_only`` is accepted for signature parity."""
+        if isinstance(save_dir, LoraConfig):
+            config, save_dir = save_dir, None
         config = config or self.lora_config
-        path = os.path.join(config.lora_save_dir, f"{config.lora_load_tag or 'lora_adapter'}.pt")
+        path = ckpt_path or os.path.join(save_dir or config.lora_save_dir,
+                                         f"{adapter_tag or config.lora_load_tag or 'lora_adapter'}.pt")
         sd = torch.load(path, map_location="cpu", weights_only=False)
         self.load_state_dict(sd, strict=False)
 

@@ -8,14 +8,15 @@ from .layers import ColumnParallelLinear, RowParallelLinear
 from .parallel_state import get_tensor_model_parallel_size
 
 
-def get_number_of_extra_heads(num_head: int, tp_degree: int) -> int:
-    return 0 if num_head % tp_degree == 0 else tp_degree - num_head % tp_degree
+def get_number_of_extra_heads(n_head: int, tp_degree: int) -> int:
+    return 0 if n_head % tp_degree == 0 else tp_degree - n_head % tp_degree
 
 
-def pad_model(model: torch.nn.Module, tp_degree: int, num_heads: int, wrapped_classes=(), pad_hook_fn=None):
+def pad_model(model: torch.nn.Module, tp_degree: int, n_heads: int, wrapped_classes=(), pad_hook_fn=None):
     """Zero-pad every Column-parallel output dim / Row-parallel input dim inside modules of
     ``wrapped_classes`` by the ratio ``tgt_heads / num_heads`` and patch ``num_heads`` attributes.
     Padded heads produce zeros and receive zero gradients, so results are unchanged."""
+    num_heads = n_heads
     tgt = num_heads + get_number_of_extra_heads(num_heads, tp_degree)
     if tgt == num_heads:
         return model

@@ -34,9 +34,14 @@ class StageIO:
     returns_model_output: bool = False
 
 
-def create_partitions(num_stages: int, num_layers: int) -> List[int]:
+def create_partitions(num_stages: int, num_layers) -> List:
     """Even split of ``num_layers`` over ``num_stages``, remainder to the LATER stages; returns the 0-based index of
-    the last layer of every stage but the final one (reference ``:280-303``)."""
+    the last layer of every stage but the final one (reference ``:280-303``).  The reference's call form
+    ``create_partitions(pipeline_parallel_size, model_layer_names)`` -- a LIST of layer names -- returns the names of
+    those layers (the pipeline cuts) instead."""
+    if not isinstance(num_layers, int):
+        names = list(num_layers)
+        return [names[i] for i in create_partitions(num_stages, len(names))]
     if num_stages > num_layers:
         raise ValueError(f"cannot cut {num_layers} layers into {num_stages} stages")
     base, rem = divmod(num_layers, num_stages)

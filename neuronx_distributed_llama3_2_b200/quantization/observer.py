@@ -9,8 +9,12 @@ import torch
 
 class PerChannelAbsMaxObserver(torch.nn.Module):
     def __init__(self, ch_axis: int = 0, dtype: torch.dtype = torch.qint8, qscheme=torch.per_channel_symmetric,
-                 quant_min: int = -128, quant_max: int = 127, eps: float = torch.finfo(torch.float32).eps):
+                 quant_min: int = -128, quant_max: int = 127, eps: float = torch.finfo(torch.float32).eps,
+                 reduce_range: bool = False, factory_kwargs=None, **_):
+        # ``reduce_range`` / ``factory_kwargs`` belong to the torch.ao observer protocol the reference derives from
         super().__init__()
+        if reduce_range:
+            raise NotImplementedError("reduce_range is not supported for symmetric int8 weights")
         if qscheme != torch.per_channel_symmetric:
             raise NotImplementedError("PerChannelAbsMaxObserver only supports per_channel_symmetric")
         self.ch_axis, self.dtype, self.qscheme = ch_axis, dtype, qscheme

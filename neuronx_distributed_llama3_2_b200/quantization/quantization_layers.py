@@ -132,18 +132,19 @@ class QuantizedColumnParallel(BaseQuantizeParallelLinear):
                  dtype: torch.dtype = torch.float32, device=None,
                  quantization_type: QuantizationType = QuantizationType.PER_TENSOR_SYMMETRIC,
                  quantized_dtype: QuantizedDtype = QuantizedDtype.INT8, quantization_per_channel_axis: Optional[int] = None,
-                 sequence_parallel_enabled: bool = False):
+                 sequence_parallel_enabled: bool = False, stride: int = 1, keep_master_weight: bool = False):
         super().__init__()
         if sequence_parallel_enabled:
             raise NotImplementedError("quantized layers are inference-only: sequence parallelism is not supported")
         tp = ps.get_tensor_model_parallel_size()
         self.input_size, self.output_size = input_size, output_size
+        self.stride, self.keep_master_weight = stride, keep_master_weight
         self.gather_output = gather_output
         self.dtype = dtype
         self.output_size_per_partition = divide(output_size, tp)
         self.weight = Parameter(torch.zeros(self.output_size_per_partition, input_size, dtype=quantized_dtype.value,
                                             device=device), requires_grad=False)
-        set_tensor_model_parallel_attributes(self.weight, True, 0, 1)
+        set_tensor_model_parallel_attributes(self.weight, True, 0, stride)
         self._setup_scale(self.weight.shape, 0, quantization_type, quantization_per_channel_axis, device)
         if bias:
             self.bias = Parameter(torch.zeros(self.output_size_per_partition, dtype=dtype, device=device),
@@ -184,12 +185,13 @@ class QuantizedRowParallel(BaseQuantizeParallelLinear):
                  dtype: torch.dtype = torch.float32, device=None,
                  quantization_type: QuantizationType = QuantizationType.PER_TENSOR_SYMMETRIC,
                  quantized_dtype: QuantizedDtype = QuantizedDtype.INT8, quantization_per_channel_axis: Optional[int] = None,
-                 sequence_parallel_enabled: bool = False):
+                 sequence_parallel_enabled: bool = False, stride: int = 1, keep_master_weight: bool = False):
         super().__init__()
         if sequence_parallel_enabled:
             raise NotImplementedError("quantized layers are inference-only: sequence parallelism is not supported")
         tp = ps.get_tensor_model_parallel_size()
         self.input_size, self.output_size = input_size, output_size
+        self.stride, self.keep_master_weight = stride, keep_master_weight
         self.input_is_parallel = input_is_parallel
         self.dtype = dtype
         self.input_size_per_partition = divide(input_size, tp)
@@ -243,8 +245,9 @@ class _QuantizedExpertFused(BaseQuantizeParallelLinear):
 class QuantizedExpertFusedColumnParallel(_QuantizedExpertFused):
     def __init__(self, num_experts: int, input_size: int, output_size: int, dtype=torch.float32, device=None,
                  quantization_type=QuantizationType.PER_TENSOR_SYMMETRIC, quantized_dtype=QuantizedDtype.INT8,
-                 quantization_per_channel_axis: Optional[int] = None):
+                 quantization_per_channel_axis: Optional[int] = None, stride: int = 1, keep_master_weight: bool = False):
         super().__init__()
+        self.stride, self.keep_master_weight = stride, keep_master_weight
         tp, ep = ps.get_tensor_model_parallel_size(), ps.get_expert_model_parallel_size()
         self.num_experts, self.input_size, self.output_size = num_experts, input_size, output_size
         self.weight = Parameter(torch.zeros(divide(num_experts, ep), input_size, divide(output_size, tp),
@@ -268,8 +271,10 @@ class QuantizedExpertFusedColumnParallel(_QuantizedExpertFused):
 class QuantizedExpertFusedRowParallel(_QuantizedExpertFused):
     def __init__(self, num_experts: int, input_size: int, output_size: int, reduce_output: bool = True,
                  dtype=torch.float32, device=None, quantization_type=QuantizationType.PER_TENSOR_SYMMETRIC,
-                 quantized_dtype=QuantizedDtype.INT8, quantization_per_channel_axis: Optional[int] = None):
+                 quantized_dtype=QuantizedDtype.INT8, quantization_per_channel_axis: Optional[int] = None,
+                 stride: int = 1, keep_master_weight: bool = False):
         super().__init__()
+        self.stride, self.keep_master_weight = stride, keep_master_weight
         tp, ep = ps.get_tensor_model_parallel_size(), ps.get_expert_model_parallel_size()
         self.num_experts, self.input_size, self.output_size = num_experts, input_size, output_size
         self.reduce_output = reduce_output

@@ -8,13 +8,15 @@ import torch
 from .observer import PerChannelAbsMaxObserver
 
 
-def quantize_per_tensor_symmetric(w: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor]:
+def quantize_per_tensor_symmetric(tensor: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor]:
+    w = tensor
     scale = torch.clamp(w.detach().abs().max().float() / 127.0, min=torch.finfo(torch.float32).eps)
     q = torch.clamp(torch.round(w.detach().float() / scale), -128, 127).to(torch.int8)
     return q, scale.reshape(1)
 
 
-def quantize_per_channel_symmetric(w: torch.Tensor, ch_axis: int = 0) -> Tuple[torch.Tensor, torch.Tensor]:
+def quantize_per_channel_symmetric(tensor: torch.Tensor, channel_axis: int = 0) -> Tuple[torch.Tensor, torch.Tensor]:
+    w, ch_axis = tensor, channel_axis
     obs = PerChannelAbsMaxObserver(ch_axis=ch_axis)
     obs(w)
     scale, _ = obs.calculate_qparams()

@@ -32,9 +32,12 @@ def checkpoint_wrapper(module: torch.nn.Module) -> torch.nn.Module:
     return module
 
 
-def apply_activation_checkpointing(model: torch.nn.Module, check_fn: Callable[[torch.nn.Module], bool] = lambda _: True
-                                   ) -> None:
-    """Checkpoint every sub-module for which ``check_fn`` is true (outermost match wins)."""
+def apply_activation_checkpointing(model: torch.nn.Module, checkpoint_wrapper_fn: Callable = None,
+                                   check_fn: Callable[[torch.nn.Module], bool] = lambda _: True) -> None:
+    """Checkpoint every sub-module for which ``check_fn`` is true (outermost match wins).  Argument order as the
+    reference (``activation_checkpoint.py:55-59``); ``checkpoint_wrapper_fn(module)`` defaults to ``checkpoint_wrapper``,
+    which patches ``forward`` in place -- a custom wrapper that RETURNS a new module is put in the parent's place."""
+    wrap = checkpoint_wrapper_fn or checkpoint_wrapper
     root = model.module if hasattr(model, "module") and isinstance(model.module, torch.nn.Module) else model
     if hasattr(root, "local_modules"):
         candidates = list(root.local_modules())
@@ -46,7 +49,11 @@ def apply_activation_checkpointing(model: torch.nn.Module, check_fn: Callable[[t
             continue
         if any(m is not w and any(m is c for c in w.modules()) for w in wrapped):
             continue
-        checkpoint_wrapper(m)
+        holders = [(parent, name) for parent in root.modules() for name, child in parent.named_children() if child is m]
+        new = wrap(m)
+        if new is not None and new is not m:
+            for parent, name in holders:
+                setattr(parent, name, new)
         wrapped.append(m)
 
 
@@ -76,9 +83,18 @@ class NxDCheckpointWrapper(torch.nn.Module):
         for n, p in super().named_parameters(prefix=prefix, recurse=recurse, remove_duplicate=remove_duplicate):
             yield n.replace("_checkpoint_wrapped_module.", ""), p
 
-    def state_dict(self, *args, **kwargs):
-        sd = super().state_dict(*args, **kwargs)
-        return type(sd)((k.replace("_checkpoint_wrapped_module.", ""), v) for k, v in sd.items())
+    def state_dict(self, *args, destination=None, prefix: str = "", keep_vars: bool = False):
+        """Keys without the wrapper's attribute name -- also when this wrapper sits inside a larger model whose
+        ``state_dict`` recursion lands here with a ``destination`` and a ``prefix``."""
+        if args:                                   # deprecated positional form (destination, prefix, keep_vars)
+            destination = args[0] if len(args) > 0 else destination
+            prefix = args[1] if len(args) > 1 else prefix
+            keep_vars = args[2] if len(args) > 2 else keep_vars
+        local = super().state_dict(prefix=prefix, keep_vars=keep_vars)
+        out = destination if destination is not None else type(local)()
+        for k, v in local.items():
+            out[k.replace("_checkpoint_wrapped_module.", "")] = v
+        return out
 
     def _load_from_state_dict(self, state_dict, prefix, *args, **kwargs):
         inner_prefix = prefix + "_checkpoint_wrapped_module."

@@ -16,7 +16,9 @@ from ..ops import optim as optim_ops
 
 
 class AdamW_FP32OptimParams(torch.optim.Optimizer):
-    def __init__(self, params, lr=1e-3, betas=(0.9, 0.999), eps=1e-6, weight_decay=0.0, correct_bias=True):
+    def __init__(self, params, lr=1e-3, betas=(0.9, 0.999), eps=1e-6, weight_decay=0.0, correct_bias=True,
+                 no_deprecation_warning: bool = True, capturable: bool = False, differentiable: bool = False):
+        # the last three exist for signature parity with the HF-derived reference optimizer; nothing here depends on them
         if lr < 0.0:
             raise ValueError(f"Invalid learning rate: {lr}")
         if not 0.0 <= betas[0] < 1.0 or not 0.0 <= betas[1] < 1.0:
