@@ -12,12 +12,12 @@ from typing import Sequence, Union
 import torch
 
 
-def load_balancing_loss_func(concatenated_gate_logits: Union[torch.Tensor, Sequence[torch.Tensor]], num_experts: int,
+def load_balancing_loss_func(router_logits: Union[torch.Tensor, Sequence[torch.Tensor]], num_experts: int,
                              top_k: int) -> torch.Tensor:
-    if not isinstance(concatenated_gate_logits, torch.Tensor):
-        concatenated_gate_logits = torch.cat([g.reshape(-1, g.shape[-1]) for g in concatenated_gate_logits
+    if not isinstance(router_logits, torch.Tensor):
+        router_logits = torch.cat([g.reshape(-1, g.shape[-1]) for g in router_logits
                                               if g is not None], dim=0)
-    logits = concatenated_gate_logits.reshape(-1, num_experts).float()
+    logits = router_logits.reshape(-1, num_experts).float()
     probs = torch.softmax(logits, dim=-1)
     _, selected = torch.topk(probs, top_k, dim=-1)
     counts = torch.zeros(num_experts, dtype=torch.float32, device=logits.device)

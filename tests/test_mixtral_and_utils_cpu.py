@@ -154,7 +154,18 @@ def test_utils_namespace_matches_reference_modules():
     cands = torch.tensor([[1, 2, 3], [1, 4, 0], [1, 5, 6]])
     logits = torch.randn(3, 3, V)
     mlog = torch.randn(heads, 3, 3, V)
-    ids2, l2, m2, n_new, sel = medusa_utils.update_inference_inputs(ids, cands, 0, 2, ri, logits, mlog, 0)
+    ids2, l2, m2, n_new, sel = medusa_utils.update_inference_inputs(ids, cands, 0, 2, ri, None, logits, mlog, 0)
     assert ids2.tolist() == [[5, 6, 7, 1, 2, 3]] and n_new == 3
     assert l2.shape == (1, 1, V) and torch.equal(l2[0, 0], logits[0, 2]) and m2.shape == (heads, 1, 1, V)
     assert torch.equal(sel, ri[0, :3] + 3)
+    # the reference's token-id convention: base top-k ids [1, 1, k], head top-k ids [heads, 1, 1, topk]
+    base_ids = torch.tensor([[[9, 8]]])
+    head_ids = torch.tensor([[[[11, 12]]], [[[21, 22]]]])
+    cart, tree = medusa_utils.generate_candidates(head_ids, base_ids, bufs["tree_indices"], ri)
+    assert tree.shape == (1, 6) and tree[0, 0] == 9 and cart[0].tolist() == [9, 11, 21]
+    verifier = torch.zeros(cart.shape[0], 3, 2, dtype=torch.long)
+    verifier[:, 0, 0], verifier[:, 1, 0] = 11, 22                  # agrees with head 0's best guess, then with 22
+    best, acc = medusa_utils.evaluate_posterior(verifier, cart)
+    assert int(acc) == 2 and cart[int(best)].tolist() == [9, 11, 22]
+    best0, acc0 = medusa_utils.evaluate_posterior(torch.full_like(verifier, 3), cart)
+    assert int(acc0) == 0 and int(best0) == 0
