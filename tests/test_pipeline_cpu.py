@@ -403,3 +403,50 @@ def _pp_family_worker(rank, world, fam):
 @pytest.mark.parametrize("fam", ["neox", "dbrx", "bert"])
 def test_pp2_other_families_match_single_process(fam):
     run_distributed(_pp_family_worker, 2, fam)
+
+
+class _Payload:
+    def __init__(self, x):
+        self.x = x
+
+    def __eq__(self, other):
+        return isinstance(other, _Payload) and self.x == other.x
+
+
+def _comm_relay_worker(rank, world):
+    """The reference's ``test/integration/parallel_layers/pipeline/test_comm.py``: a tensor and a python object are relayed
+    stage by stage down the pipeline, then a gradient-channel tensor travels back up while activations still flow."""
+    from neuronx_distributed_llama3_2_b200.parallel import parallel_state as ps
+    from neuronx_distributed_llama3_2_b200.pipeline import comm
+    from neuronx_distributed_llama3_2_b200.utils.serialization import TensorMeta
+
+    ps.initialize_model_parallel(tensor_model_parallel_size=1, pipeline_model_parallel_size=world)
+    comm.init_p2p_groups()
+    pp, last = ps.get_pipeline_model_parallel_rank(), world - 1
+    meta = TensorMeta(tensor_index=-1, dtype=torch.float32, shape=torch.Size([2, 3]), requires_grad=False, device=None)
+    want = torch.arange(6, dtype=torch.float32).reshape(2, 3) * 1.5
+    if pp == 0:
+        comm.send(want.clone())
+        comm.send_python_object({"step": 3, "obj": _Payload([1, 2])})
+    else:
+        got = comm.recv_from(meta)
+        obj = comm.recv_python_object()
+        assert torch.equal(got, want) and obj == {"step": 3, "obj": _Payload([1, 2])}
+        if pp < last:
+            comm.send(got)
+            comm.send_python_object(obj)
+    # both directions at once between neighbours: activation down (tag / communicator A), gradient up (B)
+    if pp < last:
+        comm.send(want + pp)
+    if pp > 0:
+        comm.send(want - pp, send_next=False)
+    if pp > 0:
+        assert torch.equal(comm.recv_from(meta), want + (pp - 1))
+    if pp < last:
+        assert torch.equal(comm.recv_from(meta, recv_prev=False), want - (pp + 1))
+    comm.flush_sends()
+    comm.reset_p2p_groups()
+
+
+def test_pipeline_comm_relay_and_bidirectional_channels():
+    run_distributed(_comm_relay_worker, 4)
