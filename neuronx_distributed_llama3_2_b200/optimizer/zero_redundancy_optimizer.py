@@ -280,6 +280,7 @@ class NeuronZero1Optimizer(torch.optim.Optimizer):
             # GEMM stores straight into it, other grads are copied in by _sync_grad_views), later ones accumulate.
             for p in b.params:
                 p.grad = None
+                p._nxd_flat_written = False
 
     def _norm_groups(self):
         groups = []
@@ -313,6 +314,7 @@ class NeuronZero1Optimizer(torch.optim.Optimizer):
             for p, o in zip(b.params, b.offsets):
                 view = b.flat_grad[o:o + p.numel()].view(p.shape)
                 g = p.grad
+                p._nxd_flat_written = False      # the backward pass that set it is over (see layers._accumulate_wgrad)
                 if g is None:
                     zero.append(view)
                 elif g.data_ptr() != view.data_ptr():
@@ -363,6 +365,21 @@ class NeuronZero1Optimizer(torch.optim.Optimizer):
                 optim_ops.sumsq_(b.grad_shard[a0:a1], s, accumulate=True)
             if d1 > d0:
                 optim_ops.sumsq_(b.grad_shard[d0:d1], sd, accumulate=True)
+        # weights tied across pipeline stages hold the same (summed) gradient on every owning stage: only the first
+        # owner counts them (``p.shared`` is set on the others, pipeline/model.py) -- take their part out again
+        skip, skip_dup = None, None
+        for b in self.buckets:
+            for p, o in zip(b.params, b.offsets):
+                if not getattr(p, "shared", False):
+                    continue
+                r0, r1 = b.local_range(o, o + p.numel())
+                if r1 <= r0:
+                    continue
+                if skip is None:
+                    skip, skip_dup = torch.zeros_like(s), torch.zeros_like(sd)
+                optim_ops.sumsq_(b.grad_shard[r0:r1], skip if o < b.sp_begin else skip_dup, accumulate=True)
+        if skip is not None:
+            s, sd = s - skip, sd - skip_dup
         tp = ps.get_tensor_model_parallel_size() if ps.model_parallel_is_initialized() else 1
         total = s + sd / float(tp)
         # grads in grad_shard are SUMs over dp (not yet averaged): norm of the averaged grads

@@ -232,10 +232,15 @@ def _accumulate_wgrad(weight: torch.Tensor, dy2d: torch.Tensor, x2d: torch.Tenso
         gemm_ops.gemm_tn(dy2d, x2d, out=main_grad, accumulate=True)
         return None
     flat = getattr(weight, "_nxd_flat_grad", None)
-    if flat is not None and weight.grad is None and flat.dtype == weight.dtype and flat.shape == weight.shape:
+    if (flat is not None and weight.grad is None and not getattr(weight, "_nxd_flat_written", False)
+            and flat.dtype == weight.dtype and flat.shape == weight.shape):
         # first gradient after zero_grad(): the GEMM stores straight into the ZeRO-1 flat gradient buffer (no zero
         # fill before, no add after).  A fresh view object is returned so that autograd adopts it as ``.grad``.
+        # ``.grad`` stays None until the END of a backward pass, so a weight that is used several times in one graph
+        # (several forward passes before one backward, a module called twice) needs the flag: only the first of its
+        # contributions may overwrite the buffer, the others are ordinary tensors that autograd adds.
         gemm_ops.gemm_tn(dy2d, x2d, out=flat)
+        weight._nxd_flat_written = True
         return flat.view(flat.shape)
     return gemm_ops.gemm_tn(dy2d, x2d, out_dtype=weight.dtype)
 

@@ -211,7 +211,9 @@ class NxDPPModel(nn.Module):
                 param = dict(self.stage_modules[local[0][1]].named_parameters(remove_duplicate=False))[local[0][0]]
             entry = {"group": group, "pp_ranks": pp_ranks, "param": param, "pg": None}
             if param is not None and len(pp_ranks) > 1:
-                setattr(param, "shared", True)
+                # the tag says "skip me in the global grad norm": after the grad all-reduce every owner holds the same
+                # summed gradient, so it is counted on the FIRST owning pp rank only (reference partition.py:240-268)
+                setattr(param, "shared", self.pipeline_parallel_rank != pp_ranks[0])
             self.shared_weights.append(entry)
         if self._debug_mode or self.pipeline_parallel_size == 1 or not dist.is_initialized():
             return

@@ -72,8 +72,12 @@ def trace_model(model: torch.nn.Module, input_names: Optional[List[str]] = None,
     wrap_fns += list(getattr(model, "_fx_wrap_functions", []))
     if tracer_cls is None or isinstance(tracer_cls, str):        # None / "torch" / "hf" as in the reference's pipeline_config
         tracer_cls = get_tracer_class(model, tracer_cls)
+    # model code reaches the collectives as ``mappings.gather_from_...(x)``: a module attribute, which only
+    # ``autowrap_modules`` keeps opaque (``autowrap_functions`` patches bare global names)
+    from ..parallel import mappings as _mappings
+
     tracer = tracer_cls(leaf_classes=leaves, autowrap_functions=wrap_fns,
-                                       autowrap_modules=tuple(autowrap_modules or ()))
+                        autowrap_modules=(_mappings,) + tuple(autowrap_modules or ()))
     patched = []
     if autowrap_obj_methods:  # reference ``:125-148``: make bound methods opaque call_function nodes
         for obj, names in autowrap_obj_methods.items():
