@@ -28,8 +28,15 @@ void nxd_set_error(const char* fmt, ...);
         }                                        \
     } while (0)
 
-#define NXD_LAUNCH_CHECK()                                                      \
+// Every kernel launch of the library goes through NXD_LAUNCH_CHECK (or NXD_LAUNCH_CHECK_N when one check covers
+// several launches), which also feeds the process-wide launch counter read by nxd_kernel_launches().
+void nxd_count_launches(int n);
+
+#define NXD_LAUNCH_CHECK() NXD_LAUNCH_CHECK_N(1)
+
+#define NXD_LAUNCH_CHECK_N(n_launches)                                          \
     do {                                                                        \
+        nxd_count_launches(n_launches);                                         \
         cudaError_t _e = cudaGetLastError();                                    \
         if (_e != cudaSuccess) {                                                \
             nxd_set_error("%s:%d: launch -> %s", __FILE__, __LINE__, cudaGetErrorString(_e)); \

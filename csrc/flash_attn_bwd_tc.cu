@@ -579,7 +579,7 @@ NXD_API int nxd_flash_attn_bwd_tc(const void* q, const void* k, const void* v, c
                                                                                 strides[20], B, Hkv, Sk, D);
         fa_bwd_tc_dq_convert_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(dv_acc, (bf16*)dv, strides[21], strides[22],
                                                                                 strides[23], B, Hkv, Sk, D);
-        NXD_LAUNCH_CHECK();
+        NXD_LAUNCH_CHECK_N(2);
     }
     {
         const long long n = (long long)B * Hq * Sq * (D / 8);

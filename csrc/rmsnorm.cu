@@ -236,13 +236,22 @@ static int rmsnorm_bwd_impl(const void* dy, const void* x, const void* w, const 
     return 0;
 }
 
+// rows == 0: nothing to differentiate, but a caller that asked for a fresh dW (accumulate == 0) still gets zeros
+// (the column-sum kernel with no partial rows reads nothing and stores 0).
+static int rmsnorm_bwd_empty(void* dw_bf16, float* dw_f32, int accumulate, int H, cudaStream_t s) {
+    if (accumulate || (dw_bf16 == nullptr && dw_f32 == nullptr)) return 0;
+    colsum_partials_kernel<<<(H + 255) / 256, 256, 0, s>>>(nullptr, 0, H, (bf16*)dw_bf16, dw_f32, 0);
+    NXD_LAUNCH_CHECK();
+    return 0;
+}
+
 // scratch: caller-provided device buffer of nxd_rmsnorm_bwd_num_partials(rows) * H floats.
 NXD_API int nxd_rmsnorm_bwd(const void* dy, const void* x, const void* w, const float* rstd,
                             const void* dresidual, void* dx, void* dw_bf16, float* dw_f32, int accumulate,
                             float* scratch, int rows, int H, void* stream) {
     NXD_REQUIRE(H % 8 == 0 && H <= 65536, "rmsnorm_bwd: H=%d must be a multiple of 8 and <= 65536", H);
     NXD_REQUIRE(scratch != nullptr, "rmsnorm_bwd: scratch buffer is required");
-    if (rows == 0) return 0;
+    if (rows == 0) return rmsnorm_bwd_empty(dw_bf16, dw_f32, accumulate, H, (cudaStream_t)stream);
     return rmsnorm_bwd_impl(dy, x, w, rstd, dresidual, dx, dw_bf16, dw_f32, accumulate, scratch, rows, H,
                             (cudaStream_t)stream);
 }
@@ -327,7 +336,7 @@ NXD_API int nxd_rmsnorm_bwd_static(const void* dy, const void* x, const void* w,
                 "caller-provided scratch buffer instead",
                 H, kStaticMaxH);
     NXD_REQUIRE(rows >= 0, "rmsnorm_bwd_static: negative row count");
-    if (rows == 0) return 0;
+    if (rows == 0) return rmsnorm_bwd_empty(dw_bf16, dw_f32, accumulate, H, (cudaStream_t)stream);
     float* scratch = nullptr;
     if (int rc = static_scratch_for_current_device(&scratch)) return rc;
     int P = nxd_rmsnorm_bwd_num_partials(rows);

@@ -15,6 +15,10 @@ void nxd_set_error(const char* fmt, ...) {
 
 NXD_API const char* nxd_last_error() { return g_err; }
 
+static unsigned long long g_launches = 0;   // relaxed counter: exactness across threads is not needed
+void nxd_count_launches(int n) { __atomic_fetch_add(&g_launches, (unsigned long long)n, __ATOMIC_RELAXED); }
+NXD_API unsigned long long nxd_kernel_launches() { return __atomic_load_n(&g_launches, __ATOMIC_RELAXED); }
+
 NXD_API int nxd_version() { return 100; }
 
 NXD_API int nxd_device_sm_count() { return nxd_num_sms(); }

@@ -21,6 +21,8 @@ extern "C" {
 const char* nxd_last_error(void);
 int nxd_version(void);
 int nxd_device_sm_count(void);
+/* Kernel launches made by this library in the calling process so far (bench.py's "gpu_launches"). */
+unsigned long long nxd_kernel_launches(void);
 /* Overwrite `bytes` of `buf` (> L2 size) so the next timed iteration starts with a cold L2. */
 int nxd_l2_flush(void* buf, size_t bytes, void* stream);
 

@@ -122,10 +122,9 @@ class Experts(torch.nn.Module):
     def _fused_context(self, hidden_states: torch.Tensor):
         """Symmetric-memory context of the EP group when the fused kernels apply: bf16 on the GPU, capacity a multiple
         of the 256-row tile, TMA-compatible feature sizes, at most 8 EP ranks (``NXD_FUSED_MOE=0`` disables)."""
-        import os
+        from ...ops import backend
 
-        if (not hidden_states.is_cuda or hidden_states.dtype != torch.bfloat16
-                or os.environ.get("NXD_FUSED_MOE", "1") != "1" or os.environ.get("NXD_FUSED_COMM", "1") != "1"):
+        if (not hidden_states.is_cuda or hidden_states.dtype != torch.bfloat16 or not backend.fused_moe_enabled()):
             return None
         e, c, h = hidden_states.shape
         w1 = (self.gate_up_proj if self.glu else self.up_proj).weight
@@ -134,6 +133,8 @@ class Experts(torch.nn.Module):
         el = e // ep
         if (c % 256 or h % 64 or w1.shape[2] % 64 or w2.shape[1] % 64 or ep > 8 or el * c // 256 > 64
                 or w1.dtype != torch.bfloat16):
+            backend.note_fallback("moe_a2a_gemm", f"E={e} C={c} H={h} ep={ep}: shape outside the fused dispatch/combine "
+                                  "kernels -> NCCL all-to-all + grouped GEMM")
             return None
         try:
             return ps.get_symm_mem_context("ep")

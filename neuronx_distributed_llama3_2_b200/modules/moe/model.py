@@ -28,14 +28,30 @@ class MoE(torch.nn.Module):
         self.return_expert_index = return_expert_index
         self.sequence_parallel_enabled = sequence_parallel_enabled
         self.ep_enabled = ps.get_expert_model_parallel_size() > 1
+        # TP without EP: the expert down projections deliver PARTIAL sums and this module reduces once at its exit
+        # (reference :141-150).  Everything between entry and exit then back-propagates per-rank partial gradients --
+        # the expert input grads and, through the affinities, the router's -- so the entry op sums them over TP in ONE
+        # collective (reduce-scatter under SP, all-reduce otherwise) and the expert column projections skip theirs.
+        # The reference all-reduces only the expert part (moe_parallel_layers.py:96-101) and drops the router part of
+        # the input gradient; summing at the entry is exact and saves a collective.
+        self.deferred_reduction = ps.get_tensor_model_parallel_size() > 1 and not self.ep_enabled
+        if self.deferred_reduction:
+            from .moe_parallel_layers import ExpertFusedColumnParallelLinear
+
+            for m in self.expert_mlps.modules():
+                if isinstance(m, ExpertFusedColumnParallelLinear):
+                    m.async_tensor_model_parallel_allreduce = False
 
     def forward(self, hidden_states: torch.Tensor):
         tp = ps.get_tensor_model_parallel_size()
         sp = self.sequence_parallel_enabled and tp > 1
         if sp and not self.training:
             raise NotImplementedError("sequence parallelism is not supported for MoE inference (reference :108-110)")
-        if sp:  # gather the sequence; the matching reduce-scatter happens at the exit, not in this op's backward
-            full = mappings.gather_from_sequence_parallel_region(hidden_states, to_model_parallel=False)
+        if sp:  # deferred reduction: backward = reduce-scatter of the partial input grads; with EP they are complete: split
+            full = mappings.gather_from_sequence_parallel_region(hidden_states,
+                                                                 to_model_parallel=self.deferred_reduction)
+        elif self.deferred_reduction:
+            full = mappings.copy_to_tensor_model_parallel_region(hidden_states)
         else:
             full = hidden_states
         shape = full.shape

@@ -185,10 +185,14 @@ class ExpertFusedRowParallelLinear(ExpertFusedLinear):
 
 class LinearWithWeightGradAR(torch.autograd.Function):
     """Replicated router projection whose WEIGHT grad is all-reduced over TP: the MoE layer defers its output
-    reduction, so each TP rank back-propagates only a partial grad into the router (reference ``:319-394``)."""
+    reduction, so each TP rank back-propagates only a partial grad into the router (reference ``:319-394``).
+    ``reduce_weight_grad`` is False with expert parallelism: there the down projection has already reduced, the
+    affinity gradient is complete on every TP rank and summing it again would scale it by tp (reference ``:383-385``).
+    The INPUT grad stays partial here; ``MoE`` sums it together with the experts' input grad at its entry."""
 
     @staticmethod
-    def forward(ctx, input, weight):
+    def forward(ctx, input, weight, reduce_weight_grad=True):
+        ctx.reduce_weight_grad = reduce_weight_grad
         ctx.save_for_backward(input, weight)
         return torch.matmul(input, weight.t())
 
@@ -197,9 +201,9 @@ class LinearWithWeightGradAR(torch.autograd.Function):
         input, weight = ctx.saved_tensors
         grad_input = torch.matmul(grad_output, weight)
         gw = torch.matmul(grad_output.reshape(-1, grad_output.shape[-1]).t(), input.reshape(-1, input.shape[-1]))
-        if ps.get_tensor_model_parallel_size() > 1:
+        if ctx.reduce_weight_grad and ps.get_tensor_model_parallel_size() > 1:
             dist.all_reduce(gw, group=ps.get_tensor_model_parallel_group())
-        return grad_input, gw
+        return grad_input, gw, None
 
 
 class LinearRouter(torch.nn.Module):
@@ -217,4 +221,4 @@ class LinearRouter(torch.nn.Module):
             self.init_method(self.weight)
 
     def forward(self, input_: torch.Tensor) -> torch.Tensor:
-        return LinearWithWeightGradAR.apply(input_, self.weight)
+        return LinearWithWeightGradAR.apply(input_, self.weight, ps.get_expert_model_parallel_size() == 1)

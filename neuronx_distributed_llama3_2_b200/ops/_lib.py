@@ -136,6 +136,13 @@ def available() -> bool:
         ) from e
 
 
+def kernel_launches() -> int:
+    """Kernel launches made by the library in this process so far (counted at every ``<<<>>>`` in csrc/)."""
+    fn = lib().nxd_kernel_launches
+    fn.restype = ctypes.c_ulonglong
+    return int(fn())
+
+
 def stream_ptr() -> ctypes.c_void_p:
     return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
 

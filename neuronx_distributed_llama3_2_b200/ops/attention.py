@@ -7,7 +7,7 @@
   ``examples/training/llama/modeling_llama_nxd.py:409-410``).
 * ``decode_attention`` / ``kv_cache_update`` -- token generation over a contiguous or paged cache.
 
-Backends for ``flash_attn_func`` (``NXD_ATTN_BACKEND``):
+Backends for ``flash_attn_func`` (``ops.backend.set_backends(attn=...)``, default from ``NXD_ATTN_BACKEND``):
   ``nxd``   hand-written sm_100a tcgen05 kernel (``csrc/flash_attn_tcgen05.cu``)  [default on GPU]
   ``sdpa``  ``torch.nn.functional.scaled_dot_product_attention`` -- library call, used only as the
             baseline arm and as the numerics oracle
@@ -23,7 +23,7 @@ from typing import Optional
 import torch
 import torch.nn.functional as F
 
-from . import _lib
+from . import _lib, backend
 
 
 def attention_ref(q, k, v, causal=True, softmax_scale=None):
@@ -46,10 +46,13 @@ def attention_ref(q, k, v, causal=True, softmax_scale=None):
 def _backend(q: torch.Tensor) -> str:
     if not q.is_cuda:
         return "ref"
-    be = os.environ.get("NXD_ATTN_BACKEND", "nxd")
-    if be == "nxd" and not (_lib.available() and hasattr(_lib.lib(), "nxd_flash_attn_fwd")
-                            and q.dtype == torch.bfloat16 and q.shape[-1] in (64, 128)):
-        return "sdpa"
+    be = backend.attn_backend()
+    if be == "nxd":
+        if not _lib.available():
+            return "sdpa"
+        if q.dtype != torch.bfloat16 or q.shape[-1] not in (64, 128):
+            backend.note_fallback("flash_attn", f"dtype {q.dtype}, head dim {q.shape[-1]} (kernel: bf16, D in 64/128)")
+            return "sdpa"
     return be
 
 

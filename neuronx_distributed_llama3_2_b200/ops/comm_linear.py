@@ -22,6 +22,7 @@ import torch
 import torch.distributed as dist
 
 from ..parallel import parallel_state as ps
+from . import backend
 from . import linear as gemm_ops
 
 
@@ -42,7 +43,7 @@ def _fused_ctx(x: torch.Tensor, group):
     """Symmetric-memory context for the fused kernels, or None."""
     if not x.is_cuda or group is not None:
         return None
-    if os.environ.get("NXD_FUSED_COMM", "1") != "1":
+    if not backend.fused_comm_enabled():
         return None
     if x.dtype != torch.bfloat16:
         return None
@@ -90,6 +91,7 @@ def ag_gemm(x_shard2d: torch.Tensor, weight: torch.Tensor, layout: str = "nt", g
         res = fused_ag_gemm(ctx, x_shard2d, weight, layout, persistent_total=persistent_total)
         if res is not None:
             return res
+        backend.note_fallback("ag_gemm", f"shard {tuple(x_shard2d.shape)} x weight {tuple(weight.shape)} {layout} -> NCCL + GEMM")
     total = all_gather_rows(x_shard2d, group=g)
     return _gemm(total, weight, layout), total
 
@@ -106,6 +108,7 @@ def gemm_rs(x2d: torch.Tensor, weight: torch.Tensor, layout: str = "nt", group=N
         res = fused_gemm_rs(ctx, x2d, weight, layout)
         if res is not None:
             return res
+        backend.note_fallback("gemm_rs", f"x {tuple(x2d.shape)} x weight {tuple(weight.shape)} {layout} -> GEMM + NCCL")
     return reduce_scatter_rows(_gemm(x2d, weight, layout), group=g)
 
 
@@ -121,6 +124,9 @@ def gemm_ar(x2d: torch.Tensor, weight: torch.Tensor, layout: str = "nt", group=N
         res = fused_gemm_ar(ctx, x2d, weight, layout)
         if res is not None:
             return res
+        if x2d.shape[0] * (weight.shape[0] if layout == "nt" else weight.shape[1]) <= (1 << 20):
+            # beyond 2 MB NCCL is the intended path (ring / NVLS wins on bandwidth), below it is a fallback
+            backend.note_fallback("gemm_ar", f"x {tuple(x2d.shape)} x weight {tuple(weight.shape)} {layout} -> GEMM + NCCL")
     y = _gemm(x2d, weight, layout)
     dist.all_reduce(y, group=g)
     return y

@@ -11,34 +11,38 @@ tcgen05/TMA kernel in ``csrc/gemm_tcgen05.cu`` (all three layouts are handled by
 operand-major bits in the UMMA descriptors, no transposed copies).  Everything
 else (CPU tests, fp32, odd shapes) takes the plain ``torch.matmul`` path.
 
-``NXD_GEMM_BACKEND`` = ``tcgen05`` (default on GPU) | ``cublas`` selects the
-library GEMM instead; the latter is the NCCL+cuBLAS *baseline* arm.
+``ops.backend.set_backends(gemm=...)`` (default from ``NXD_GEMM_BACKEND``) = ``tcgen05`` | ``cublas`` selects the
+library GEMM instead; the latter is the NCCL+cuBLAS *baseline* arm.  A CUDA call that wanted the kernel but did not
+qualify is counted by ``ops.backend.note_fallback``.
 """
 from __future__ import annotations
 
-import os
 from typing import Optional
 
 import torch
 
-from . import _lib
+from . import _lib, backend
 
 
 def _backend() -> str:
-    return os.environ.get("NXD_GEMM_BACKEND", "tcgen05")
+    return backend.gemm_backend()
 
 
-def _use_kernel(a: torch.Tensor, b: torch.Tensor, m: int, n: int, k: int) -> bool:
+def _use_kernel(a: torch.Tensor, b: torch.Tensor, m: int, n: int, k: int, layout: str = "nt") -> bool:
     if not (a.is_cuda and b.is_cuda):
-        return False
-    if a.dtype != torch.bfloat16 or b.dtype != torch.bfloat16:
         return False
     if _backend() != "tcgen05":
         return False
-    # TMA needs 16-byte aligned row pitches; tiles are masked by TMA OOB handling.
-    if (k % 8) or (n % 8) or (m % 8):
+    if not _lib.available():
         return False
-    return _lib.available()
+    if a.dtype != torch.bfloat16 or b.dtype != torch.bfloat16:
+        backend.note_fallback("gemm", f"dtype {a.dtype}/{b.dtype} (kernel is bf16)")
+        return False
+    # TMA needs 16-byte aligned row pitches (K and N multiples of 8 elements); M is free (OOB rows are clipped).
+    if (k % 8) or (n % 8) or (layout == "tn" and m % 8):
+        backend.note_fallback("gemm", f"{layout} M={m} N={n} K={k}: a leading dimension is not a multiple of 8")
+        return False
+    return True
 
 
 def gemm_nt(a: torch.Tensor, b: torch.Tensor, out: Optional[torch.Tensor] = None,
@@ -67,7 +71,7 @@ def gemm_nn(a: torch.Tensor, b: torch.Tensor, out: Optional[torch.Tensor] = None
     """``a[M,K] @ b[K,N]``."""
     m, k = a.shape
     n = b.shape[1]
-    if _use_kernel(a, b, m, n, k):
+    if _use_kernel(a, b, m, n, k, "nn"):
         from .gemm import gemm
 
         return gemm(a, b, "nn", out=out, out_dtype=out_dtype, accumulate=accumulate)
@@ -80,7 +84,7 @@ def gemm_tn(a: torch.Tensor, b: torch.Tensor, out: Optional[torch.Tensor] = None
     """``a[K,M]^T @ b[K,N]``."""
     k, m = a.shape
     n = b.shape[1]
-    if _use_kernel(a, b, m, n, k):
+    if _use_kernel(a, b, m, n, k, "tn"):
         from .gemm import gemm
 
         return gemm(a, b, "tn", out=out, out_dtype=out_dtype, accumulate=accumulate)

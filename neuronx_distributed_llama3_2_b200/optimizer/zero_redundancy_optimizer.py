@@ -132,6 +132,9 @@ class _Bucket:
         return (a - self.lo, b - self.lo) if b > a else (0, 0)
 
 
+NO_SHARD_GROUP = "no-shard-group"
+
+
 class NeuronZero1Optimizer(torch.optim.Optimizer):
     """ZeRO-1 over the DP group.  Constructor keywords follow the reference wiring
     (``trainer/trainer.py:244-269``)."""
@@ -150,8 +153,10 @@ class NeuronZero1Optimizer(torch.optim.Optimizer):
         self.save_master_weights = save_master_weights
         self.coalesce_cc = coalesce_cc
         self.pin_layout = pin_layout
-        self._shard_group = shard_process_group
-        if self._shard_group is None and dist.is_initialized() and ps.model_parallel_is_initialized() \
+        # ``NO_SHARD_GROUP`` = "this optimizer's parameters are not replicated anywhere" (expert shards when the
+        # expert-data-parallel size is 1): no reduce-scatter / all-gather at all.  ``None`` = default to the DP group.
+        self._shard_group = None if shard_process_group is NO_SHARD_GROUP else shard_process_group
+        if shard_process_group is None and dist.is_initialized() and ps.model_parallel_is_initialized() \
                 and ps.get_data_parallel_size() > 1:
             self._shard_group = ps.get_data_parallel_group()
         self.sharding_groups = sharding_groups
@@ -545,9 +550,11 @@ class NeuronEPZero1Optimizer(torch.optim.Optimizer):
         self.grad_clipping = kw.get("grad_clipping", True)
         self.max_norm = kw.get("max_norm", 1.0) or 1.0
         inner_kw = dict(kw, grad_clipping=False)
+        # expert shards differ between EP ranks: they may only ever be reduced / gathered inside the expert-DP group,
+        # and not at all when that group has one member (falling back to the DP group would mix different experts)
         exp_dp = ps.get_expert_data_parallel_group() if (
             dist.is_initialized() and ps.model_parallel_is_initialized()
-            and ps.get_expert_data_parallel_size() > 1) else None
+            and ps.get_expert_data_parallel_size() > 1) else NO_SHARD_GROUP
         self.non_ep_zero_optimizer = NeuronZero1Optimizer(nonep_groups, optimizer_class, **inner_kw) \
             if nonep_groups else None
         self.ep_zero_optimizer = NeuronZero1Optimizer(ep_groups, optimizer_class, shard_process_group=exp_dp,

@@ -116,13 +116,18 @@ def clip_grad_norm(parameters, max_norm: float, norm_type: float = 2.0, zero1_op
 def bucket_allreduce_gradients(grads: List[torch.Tensor], reduce_over_ep_group: bool = False) -> None:
     """Average grads over the (expert-)data-parallel group in flat per-dtype buckets of at most
     ``ALLREDUCE_BUCKET_CAP_MB`` (default 512), last-produced grads first (reference :243-310)."""
+    # Scaling as the reference (grads.py:243-310): the FIRST pass sums every gradient -- dense and expert -- over the
+    # expert-data-parallel group and divides by the FULL data-parallel size; the second pass (dense gradients only)
+    # sums over the EP group with divisor 1.  Dense: sum over exp_dp x ep = dp ranks, / dp.  Expert: the token
+    # all-to-all already brought every EP rank's tokens to the expert's owner, so its gradient is summed over exp_dp
+    # only and still divided by dp.
     if reduce_over_ep_group:
-        size = ps.get_expert_model_parallel_size()
-        group = ps.get_expert_model_parallel_group() if size > 1 else None
+        size = 1
+        group = ps.get_expert_model_parallel_group() if ps.get_expert_model_parallel_size() > 1 else None
     else:
-        size = ps.get_expert_data_parallel_size()
-        group = ps.get_expert_data_parallel_group() if size > 1 else None
-    if size == 1 or group is None:
+        size = ps.get_data_parallel_size()
+        group = ps.get_expert_data_parallel_group() if ps.get_expert_data_parallel_size() > 1 else None
+    if size == 1 and group is None:
         return
     cap = int(os.environ.get("ALLREDUCE_BUCKET_CAP_MB", 512)) * 1024 * 1024
     by_dtype = {}
@@ -134,8 +139,10 @@ def bucket_allreduce_gradients(grads: List[torch.Tensor], reduce_over_ep_group: 
             if not bucket:
                 return
             flat = torch.cat([g.reshape(-1) for g in bucket])
-            flat.div_(size)
-            dist.all_reduce(flat, group=group)
+            if size != 1:
+                flat.div_(size)
+            if group is not None:
+                dist.all_reduce(flat, group=group)
             off = 0
             for g in bucket:
                 g.copy_(flat[off: off + g.numel()].view_as(g))

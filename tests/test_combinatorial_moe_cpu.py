@@ -99,8 +99,41 @@ def test_moe_first_step_loss_is_independent_of_the_parallel_layout(world, tp, sp
     run_distributed(_worker, world, tp, sp, ep, zero1, 1)
 
 
-@pytest.mark.xfail(strict=False, reason="MoE gradients deviate from the single-process run under TP and under EP (router "
-                   "weight gradient is a per-TP-rank partial sum; EP gradient scaling): docs/NEXT.md, 'MoE sweep'")
 @pytest.mark.parametrize("world,tp,sp,ep,zero1", CONFIGS)
 def test_moe_loss_trajectory_is_independent_of_the_parallel_layout(world, tp, sp, ep, zero1):
     run_distributed(_worker, world, tp, sp, ep, zero1, STEPS)
+
+
+def _ep_distinct_worker(rank, world):
+    """ep = world = 2, expert-DP size 1: the expert shards of the two ranks are DIFFERENT tensors.  With lr = 0 a step must
+    leave each rank's expert weights exactly where they were (no reduce-scatter / all-gather across EP ranks)."""
+    from neuronx_distributed_llama3_2_b200 import trainer as nxd
+    from neuronx_distributed_llama3_2_b200.models import MixtralForCausalLM
+    from neuronx_distributed_llama3_2_b200.parallel import parallel_state as ps
+
+    cfg = nxd.neuronx_distributed_config(
+        tensor_parallel_size=1, expert_parallel_size=2,
+        optimizer_config={"zero_one_enabled": True, "grad_clipping": True, "max_grad_norm": 1.0})
+    assert ps.get_expert_data_parallel_size() == 1
+
+    def build():
+        torch.manual_seed(0)
+        return MixtralForCausalLM(_config(0))
+
+    model = nxd.initialize_parallel_model(cfg, build, device=torch.device("cpu"))
+    experts = {n: p for n, p in model.named_parameters() if getattr(p, "expert_model_parallel", False)}
+    assert experts
+    with torch.no_grad():
+        for p in experts.values():
+            p.fill_(float(rank + 1))
+    opt = nxd.initialize_parallel_optimizer(cfg, torch.optim.AdamW, model.parameters(), lr=0.0, weight_decay=0.0)
+    ids = _batch().chunk(2, 0)[rank]
+    opt.zero_grad()
+    model(ids, labels=ids).backward()
+    opt.step()
+    for n, p in experts.items():
+        assert torch.all(p == float(rank + 1)), (rank, n, p.flatten()[:4])
+
+
+def test_expert_shards_stay_local_to_their_ep_rank_under_zero1():
+    run_distributed(_ep_distinct_worker, 2)

@@ -11,6 +11,12 @@ import torch
 pytestmark = pytest.mark.gpu
 
 
+
+def _backend():
+    from neuronx_distributed_llama3_2_b200.ops import backend
+
+    return backend
+
 def _free_port():
     with socket.socket() as s:
         s.bind(("127.0.0.1", 0))
@@ -150,7 +156,7 @@ def case_sp_embedding(rank, world):
     for it in range(4):
         g = torch.Generator(device="cpu").manual_seed(50 + it)
         ids = torch.randint(0, V, (B, S), generator=g).cuda()
-        os.environ["NXD_FUSED_COMM"] = "1"
+        _backend().set_backends(fused_comm=True)
         out = emb(ids)                                   # [S/tp, B, H] through the push kernel
         ref = full[ids].transpose(0, 1)[rank * (S // world):(rank + 1) * (S // world)]
         assert out.shape == ref.shape and torch.equal(out, ref), it
@@ -158,13 +164,13 @@ def case_sp_embedding(rank, world):
         emb.weight.grad = None
         out.backward(dy)
         g_push = emb.weight.grad.clone()
-        os.environ["NXD_FUSED_COMM"] = "0"
+        _backend().set_backends(fused_comm=False)
         emb.weight.grad = None
         out2 = emb(ids)                                  # NCCL reduce-scatter path
         assert torch.equal(out2, ref)
         out2.backward(dy)
         assert _rel(g_push, emb.weight.grad) < 1e-3
-    os.environ["NXD_FUSED_COMM"] = "1"
+    _backend().set_backends(fused_comm=True)
 
 
 def _worker_dp(rank, world, port, case):
@@ -260,7 +266,7 @@ def case_moe_fused(rank, world):
         x = torch.randn(E, C, H, device="cuda", generator=g).bfloat16()
         dy = torch.randn(E, C, H, device="cuda", generator=g).bfloat16()
         for fused in ("0", "1"):
-            os.environ["NXD_FUSED_MOE"] = fused
+            _backend().set_backends(fused_moe=(fused == "1"))
             xr = x.clone().requires_grad_()
             for p in experts.parameters():
                 p.grad = None
@@ -273,7 +279,7 @@ def case_moe_fused(rank, world):
         assert _rel(gx1, gx0) < 1e-2, (it, _rel(gx1, gx0))
         for a, b in zip(gw1, gw0):
             assert _rel(a, b) < 1e-2, (it, _rel(a, b))
-    os.environ["NXD_FUSED_MOE"] = "1"
+    _backend().set_backends(fused_moe=True)
 
 
 def case_flag_protocol_stress(rank, world):

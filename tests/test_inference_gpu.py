@@ -128,7 +128,9 @@ def _tp_worker(rank, world, port, modes):
         table = {"nccl_eager": ("0", False), "fused_eager": ("1", False), "fused_graphs": ("1", True)}
         for name in modes:
             fused, graphs = table[name]
-            os.environ["NXD_FUSED_COMM"] = fused
+            from neuronx_distributed_llama3_2_b200.ops import backend as _be
+
+            _be.set_backends(fused_comm=(fused == "1"))
             ic = InferenceConfig(tp_degree=world, batch_size=2, max_context_length=128, seq_len=256, buckets=[64, 128],
                                  max_new_tokens=8, use_cuda_graphs=graphs)
             runner = InferenceRunner(_cfg(), ic, checkpoint_loader=lambda: sd, device=dev)

@@ -20,6 +20,7 @@ sys.path.insert(0, ROOT)
 
 from neuronx_distributed_llama3_2_b200.ops import _lib  # noqa: E402
 from neuronx_distributed_llama3_2_b200.ops import attention as A  # noqa: E402
+from neuronx_distributed_llama3_2_b200.ops import backend  # noqa: E402
 from neuronx_distributed_llama3_2_b200.ops.gemm import gemm  # noqa: E402
 
 PEAKS = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))) if os.path.exists(
@@ -113,7 +114,7 @@ def bench_attention(rows):
         fl_f = 4.0 * B * Hq * S * S * D * 0.5
         res = {"op": "flash_attn", "case": name, "B": B, "Hq": Hq, "Hkv": Hkv, "S": S, "D": D}
         for be in ("nxd", "sdpa"):
-            os.environ["NXD_ATTN_BACKEND"] = be
+            backend.set_backends(attn=be)
             o = A.flash_attn_func(q, k, v, causal=True)
             tf = time_ms(lambda: A.flash_attn_func(q, k, v, causal=True))
 
@@ -128,7 +129,7 @@ def bench_attention(rows):
             res[f"{be}_bwd_ms"] = tfb - tf
             res[f"{be}_bwd_tflops"] = 2.5 * fl_f / max(tfb - tf, 1e-6) / 1e9
             del o
-        os.environ["NXD_ATTN_BACKEND"] = "nxd"
+        backend.set_backends(attn="nxd")
         res["fwd_frac_of_measured_peak"] = res["nxd_fwd_tflops"] / PEAKS["bf16_tflops"]
         rows.append(res)
         print(json.dumps(res), flush=True)
