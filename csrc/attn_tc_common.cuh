@@ -24,10 +24,41 @@ __device__ __forceinline__ void tma_store_4d(const CUtensorMap* map, const void*
                  "r"(ptx::smem_u32(src)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
                  : "memory");
 }
+// Coordinates 1..3 of a 4-D map whose (row, head, batch) dims sit in slots pos[0..2].  Written as selects on purpose:
+// indexing a local array with pos[] would put the array in local memory (STL / LDL per TMA issue).
 __device__ __forceinline__ void coords(const int* pos, int row, int h, int b, int* c) {
-    c[pos[0]] = row;
-    c[pos[1]] = h;
-    c[pos[2]] = b;
+    const int pr = pos[0], ph = pos[1];
+    c[1] = pr == 1 ? row : (ph == 1 ? h : b);
+    c[2] = pr == 2 ? row : (ph == 2 ? h : b);
+    c[3] = pr == 3 ? row : (ph == 3 ? h : b);
+}
+
+// 1024-byte aligned start of the dynamic shared memory window.  The result is derived from the __shared__ array by
+// pointer arithmetic (not through an integer cast), so the compiler keeps the shared state space and emits LDS / STS
+// instead of generic LD / ST.
+__device__ __forceinline__ uint8_t* align_smem_1024(uint8_t* smem_raw) {
+    return smem_raw + ((1024u - (ptx::smem_u32(smem_raw) & 1023u)) & 1023u);
+}
+
+__device__ __forceinline__ void st_shared_v4(void* dst, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(ptx::smem_u32(dst)), "r"(a), "r"(b), "r"(c), "r"(d)
+                 : "memory");
+}
+__device__ __forceinline__ float4 ld_shared_f4(const void* src) {
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+                 : "r"(ptx::smem_u32(src)));
+    return v;
+}
+__device__ __forceinline__ float ex2_approx(float x) {
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+__device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
+    uint32_t r;
+    asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+    return r;
 }
 
 __device__ __forceinline__ void tmem_st_32x32b_x32(uint32_t taddr, const uint32_t* r) {

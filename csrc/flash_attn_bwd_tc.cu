@@ -31,6 +31,8 @@
 #include "gemm_tcgen05.cuh"
 #include "ptx.cuh"
 
+#include <type_traits>
+
 namespace {
 using namespace nxd_attn;
 
@@ -78,7 +80,7 @@ fa_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
     using L = BwdSmem<kD>;
     constexpr uint32_t kColDK = 0, kColDV = kD, kColST = 2 * kD, kColDPT = 2 * kD + 64, kColDQT = 2 * kD + 128;
     extern __shared__ __align__(1024) uint8_t smem_raw[];
-    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* smem = align_smem_1024(smem_raw);
     uint8_t* sK = smem + L::kKOff;
     uint8_t* sV = smem + L::kVOff;
     uint8_t* sQ = smem + L::kQOff;
@@ -152,11 +154,11 @@ fa_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
                 coords(p.pos_v, n0, hkv, b, c);
                 tma_load_4d(&tmap_v, kv_full, sV + g * (kBN * 128), c[0], c[1], c[2], c[3]);
             }
+            int th = it0 % tiles_per_head, hq = hkv * group + it0 / tiles_per_head;   // (q tile, q head) walk
             for (int it = 0; it < total; ++it) {
                 const int st = it & 1;
                 const uint32_t ph = (uint32_t)(it >> 1) & 1u;
-                const int hq = hkv * group + (it0 + it) / tiles_per_head;
-                const int m0 = (mb_start + (it0 + it) % tiles_per_head) * kBM;
+                const int m0 = (mb_start + th) * kBM;
                 ptx::mbar_wait(&qdo_empty[st], ph ^ 1u);
                 ptx::mbar_arrive_expect_tx(&qdo_full[st], L::kTxPerStage);
 #pragma unroll
@@ -171,6 +173,7 @@ fa_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
                 const long long row = ((long long)b * p.Hq + hq) * p.Sq_pad + m0;
                 bulk_load_1d(sLD + st * 2 * kBM, p.lse_pad + row, kBM * 4, &qdo_full[st]);
                 bulk_load_1d(sLD + st * 2 * kBM + kBM, p.delta_pad + row, kBM * 4, &qdo_full[st]);
+                if (++th == tiles_per_head) { th = 0; ++hq; }
             }
         }
     } else if (warp == 1) {
@@ -244,17 +247,18 @@ fa_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
         const int row = q4 * 32 + lane;         // K/V row inside the tile == TMEM lane (and d index for dQ^T)
         const int krow = n0 + row;
         const uint32_t lane_off = (uint32_t)(q4 * 32) << 16;
-        const int tidm = threadIdx.x - 64;       // 0 .. 255 inside the math group
         const int half = (warp - 2) >> 2;        // which 32 of the 64 query columns this warp handles
         const int c0h = half * 32;
+        const bool has_rows = q4 * 32 < kD;      // head dim 64: TMEM lanes 64..127 of dQ^T are padding
+        // dQ^T staging of THIS warp: 32 d rows x 32 q columns fp32 = 32 swizzled 128-byte rows (one TMA box)
+        uint8_t* dq_stage = sDQ + (half * (kD / 32) + q4) * 4096;
 
-        auto drain_dq = [&](int it) {
-            // dQ^T(it) [d = row][64 q] -> sDQ [d group of 32][q][32 floats] (128-byte swizzled rows) -> TMA reduce-add
-            const int hq = hkv * group + (it0 + it) / tiles_per_head;
-            const int m0 = (mb_start + (it0 + it) % tiles_per_head) * kBM;
+        // dQ^T(it) [d = TMEM lane][64 q]: this warp's 32 x 32 block -> its staging rows (no transpose: the fp32 dQ
+        // accumulator in global memory is d-major) -> TMA reduce-add.  No CTA-wide barrier: the staging buffer, the
+        // bulk group and the wait on it are all private to the warp.
+        auto drain_dq = [&](int it, int hq, int m0) {
             ptx::mbar_wait(dq_full, (uint32_t)it & 1u);
             ptx::tcgen05_fence_after();
-            const bool has_rows = q4 * 32 < kD;          // head dim 64: TMEM lanes 64..127 of dQ^T are padding
             uint32_t v[32];
             if (has_rows) {
                 ptx::tmem_ld_32x32b_x32(tmem_base + kColDQT + lane_off + c0h, v);
@@ -262,35 +266,63 @@ fa_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
             }
             ptx::tcgen05_fence_before();
             ptx::mbar_arrive(dq_empty);
-            if (tidm == 0) ptx::bulk_wait_read<0>();     // the previous reduce-add has finished reading sDQ
-            named_bar_sync(1, kMathThreads);
             if (has_rows) {
-                uint8_t* base = sDQ + q4 * (kBM * 128);      // d group of 32 == this TMEM lane quadrant
+                if (lane == 0) ptx::bulk_wait_read<0>();     // this warp's previous reduce-add has read the staging rows
+                __syncwarp();
+                uint8_t* dst = dq_stage + lane * 128;
 #pragma unroll
-                for (int j = 0; j < 32; ++j) {
-                    const int qq = c0h + j;
-                    float* dst =
-                        reinterpret_cast<float*>(base + qq * 128 + (((lane >> 2) ^ (qq & 7)) << 4) + (lane & 3) * 4);
-                    *dst = __uint_as_float(v[j]) * p.scale;
+                for (int c = 0; c < 8; ++c)
+                    st_shared_v4(dst + ((c ^ (lane & 7)) << 4), __float_as_uint(__uint_as_float(v[4 * c]) * p.scale),
+                                 __float_as_uint(__uint_as_float(v[4 * c + 1]) * p.scale),
+                                 __float_as_uint(__uint_as_float(v[4 * c + 2]) * p.scale),
+                                 __float_as_uint(__uint_as_float(v[4 * c + 3]) * p.scale));
+                ptx::fence_proxy_async();
+                __syncwarp();
+                if (lane == 0) {
+                    int c[4];
+                    c[0] = m0 + c0h;
+                    coords(p.pos_dq, q4 * 32, hq, b, c);
+                    tma_reduce_add_4d(&tmap_dq, dq_stage, c[0], c[1], c[2], c[3]);
+                    ptx::bulk_commit();
                 }
-            }
-            ptx::fence_proxy_async();
-            named_bar_sync(1, kMathThreads);
-            if (tidm == 0) {
-                int c[4];
-#pragma unroll
-                for (int g = 0; g < kD / 32; ++g) {
-                    c[0] = g * 32;
-                    coords(p.pos_dq, m0, hq, b, c);
-                    tma_reduce_add_4d(&tmap_dq, sDQ + g * (kBM * 128), c[0], c[1], c[2], c[3]);
-                }
-                ptx::bulk_commit();
             }
         };
 
+        // P^T = exp2(S^T c - L_q), dS^T = P^T (dP^T - Delta_q) for this thread's K/V row and 32 query columns.
+        // MASK is instantiated only for the tiles that touch the causal diagonal or the end of the K/V sequence.
+        auto softmax_bwd = [&](auto mask_tag, const uint32_t* s, const uint32_t* dp, const float* Ls, const float* Ds,
+                               int m0, uint32_t* pk, uint32_t* dk_) {
+            constexpr bool MASK = decltype(mask_tag)::value;
+            // masked <=> krow >= Sk, or (causal) krow > m0 + c0h + c + offset  <=>  c < first_ok
+            int first_ok = 0;
+            if (MASK) {
+                first_ok = CAUSAL ? krow - offset - m0 - c0h : 0;
+                if (krow >= p.Sk) first_ok = 64;
+            }
+#pragma unroll
+            for (int c = 0; c < 32; c += 4) {
+                const float4 l4 = ld_shared_f4(Ls + c0h + c);
+                const float4 d4 = ld_shared_f4(Ds + c0h + c);
+                const float lv[4] = {l4.x, l4.y, l4.z, l4.w}, dv[4] = {d4.x, d4.y, d4.z, d4.w};
+                float pv[4], dsv[4];
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    pv[e] = ex2_approx(fmaf(__uint_as_float(s[c + e]), p.scale_log2, -lv[e]));
+                    if (MASK && c + e < first_ok) pv[e] = 0.f;
+                    dsv[e] = pv[e] * (__uint_as_float(dp[c + e]) - dv[e]);
+                }
+                pk[c >> 1] = pack_bf16x2(pv[0], pv[1]);
+                pk[(c >> 1) + 1] = pack_bf16x2(pv[2], pv[3]);
+                dk_[c >> 1] = pack_bf16x2(dsv[0], dsv[1]);
+                dk_[(c >> 1) + 1] = pack_bf16x2(dsv[2], dsv[3]);
+            }
+        };
+
+        int th = it0 % tiles_per_head, hq = hkv * group + it0 / tiles_per_head;
+        int prev_hq = hq, prev_m0 = 0;
         for (int it = 0; it < total; ++it) {
             const int st = it & 1;
-            const int m0 = (mb_start + (it0 + it) % tiles_per_head) * kBM;
+            const int m0 = (mb_start + th) * kBM;
             ptx::mbar_wait(st_full, (uint32_t)it & 1u);
             ptx::tcgen05_fence_after();
             uint32_t s[32], dp[32];
@@ -304,46 +336,35 @@ fa_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
             ptx::mbar_wait(&qdo_full[st], (uint32_t)(it >> 1) & 1u);
             const float* Ls = sLD + st * 2 * kBM;
             const float* Ds = Ls + kBM;
-            const bool need_mask = (n0 + kBN > p.Sk) || (CAUSAL && (n0 + q4 * 32 + 31 > m0 + offset));
+            // warp-uniform: does any (K/V row of this warp, query column of this warp) need masking?
+            const bool need_mask = (n0 + kBN > p.Sk) || (CAUSAL && (n0 + q4 * 32 + 31 > m0 + c0h + offset));
             uint32_t pk[16], dk_[16];
-#pragma unroll
-            for (int c = 0; c < 32; c += 2) {
-                const int cg = c0h + c;                  // query column inside the 64-row tile
-                float p0 = exp2f(__uint_as_float(s[c]) * p.scale_log2 - Ls[cg]);
-                float p1 = exp2f(__uint_as_float(s[c + 1]) * p.scale_log2 - Ls[cg + 1]);
-                if (need_mask) {
-                    const int mq = m0 + cg;
-                    if (krow >= p.Sk || (CAUSAL && krow > mq + offset)) p0 = 0.f;
-                    if (krow >= p.Sk || (CAUSAL && krow > mq + 1 + offset)) p1 = 0.f;
-                }
-                const float d0 = p0 * (__uint_as_float(dp[c]) - Ds[cg]);
-                const float d1 = p1 * (__uint_as_float(dp[c + 1]) - Ds[cg + 1]);
-                bf162 tp = __floats2bfloat162_rn(p0, p1);
-                bf162 td = __floats2bfloat162_rn(d0, d1);
-                pk[c >> 1] = *reinterpret_cast<uint32_t*>(&tp);
-                dk_[c >> 1] = *reinterpret_cast<uint32_t*>(&td);
-            }
+            if (need_mask) softmax_bwd(std::true_type{}, s, dp, Ls, Ds, m0, pk, dk_);
+            else softmax_bwd(std::false_type{}, s, dp, Ls, Ds, m0, pk, dk_);
             if (it > 0) ptx::mbar_wait(pds_empty, ((uint32_t)(it - 1)) & 1u);  // MMAs of tile it-1 finished with sPt/sDSt
             uint8_t* prow = sPt + row * 128;
             uint8_t* drow = sDSt + row * 128;
 #pragma unroll
             for (int c = 0; c < 4; ++c) {                // this warp's 4 of the row's 8 sixteen-byte chunks
                 const int sw = ((half * 4 + c) ^ (row & 7)) << 4;
-                *reinterpret_cast<uint4*>(prow + sw) = make_uint4(pk[4 * c], pk[4 * c + 1], pk[4 * c + 2], pk[4 * c + 3]);
-                *reinterpret_cast<uint4*>(drow + sw) = make_uint4(dk_[4 * c], dk_[4 * c + 1], dk_[4 * c + 2], dk_[4 * c + 3]);
+                st_shared_v4(prow + sw, pk[4 * c], pk[4 * c + 1], pk[4 * c + 2], pk[4 * c + 3]);
+                st_shared_v4(drow + sw, dk_[4 * c], dk_[4 * c + 1], dk_[4 * c + 2], dk_[4 * c + 3]);
             }
             ptx::fence_proxy_async();
             ptx::tcgen05_fence_before();
             ptx::mbar_arrive(pds_full);
-            if (it > 0) drain_dq(it - 1);
+            if (it > 0) drain_dq(it - 1, prev_hq, prev_m0);
+            prev_hq = hq;
+            prev_m0 = m0;
+            if (++th == tiles_per_head) { th = 0; ++hq; }
         }
         if (total > 0) {
-            drain_dq(total - 1);
+            drain_dq(total - 1, prev_hq, prev_m0);
             // the commit behind dq_full(total-1) covered every earlier MMA: dK / dV are final
         }
         if (total == 0) ptx::mbar_wait(kv_full, 0);  // nothing consumed K/V: let their TMA land before the tiles are reused
-        if (tidm == 0) ptx::bulk_wait_read<0>();
-        named_bar_sync(1, kMathThreads);
+        if (lane == 0) ptx::bulk_wait_read<0>();      // this warp's last dQ reduce-add has read its staging rows
+        named_bar_sync(1, kMathThreads);              // ... and everybody's: the epilogue below reuses all of smem
         if (p.nsplit > 1) {
             // ---- split epilogue: this CTA holds PARTIAL dV / dK -> fp32 -> smem -> TMA reduce-add into the accumulators
             // (32 rows x 32 columns per warp and step, two 4 KB staging buffers per warp in the dead K / V / Q / dO
@@ -485,6 +506,28 @@ __global__ void fa_bwd_tc_dq_convert_kernel(const float* __restrict__ acc, bf16*
     reinterpret_cast<bf16x8*>(dq + b * sb + h * sh + (long long)i * ss)[c] = pack8(f);
 }
 
+// d-major fp32 accumulator [B, Hq, D, Sq_pad] -> strided bf16 dq [.., Sq, D]: 32 query rows per block through a padded
+// shared tile (coalesced 128-byte reads along q, 16-byte writes along d)
+__global__ void __launch_bounds__(256)
+fa_bwd_tc_dq_transpose_kernel(const float* __restrict__ acc, bf16* __restrict__ dq, long long sb, long long sh,
+                              long long ss, int Hq, int Sq, int Sq_pad, int D) {
+    __shared__ float tile[128][33];
+    const int q0 = blockIdx.x * 32, h = blockIdx.y, b = blockIdx.z;
+    const float* src = acc + ((long long)b * Hq + h) * D * Sq_pad;
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    for (int d = w; d < D; d += 8) tile[d][lane] = (q0 + lane < Sq_pad) ? src[(long long)d * Sq_pad + q0 + lane] : 0.f;
+    __syncthreads();
+    const int chunks = D / 8;                    // 16-byte chunks per output row
+    for (int t = threadIdx.x; t < 32 * chunks; t += 256) {
+        const int r = t / chunks, c = t % chunks;
+        if (q0 + r >= Sq) continue;
+        float f[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) f[e] = tile[c * 8 + e][r];
+        reinterpret_cast<bf16x8*>(dq + b * sb + h * sh + (long long)(q0 + r) * ss)[c] = pack8(f);
+    }
+}
+
 template <int kD, bool CAUSAL>
 int launch_bwd_tc(dim3 grid, cudaStream_t st, const CUtensorMap& tq, const CUtensorMap& tdo, const CUtensorMap& tk,
                   const CUtensorMap& tv, const CUtensorMap& tdk, const CUtensorMap& tdv, const CUtensorMap& tdq,
@@ -515,7 +558,7 @@ NXD_API int nxd_flash_attn_bwd_tc_num_splits(int B, int Hq, int Hkv, int Sq, int
 }
 
 // Head dim 128 or 64.  scratch: lse_pad and delta_pad are [B*Hq*Sq_pad] floats (Sq_pad = Sq rounded up to 64);
-// dq_accum is a ZERO-FILLED [B, Hq, Sq, D] fp32 buffer.  dkv_accum: NULL, or a ZERO-FILLED [2, B, Hkv, Sk, D] fp32
+// dq_accum is a ZERO-FILLED [B, Hq, D, Sq_pad] fp32 buffer (d-major).  dkv_accum: NULL, or a ZERO-FILLED [2, B, Hkv, Sk, D] fp32
 // buffer -- then nxd_flash_attn_bwd_tc_num_splits() CTAs share every K/V block (small batch x heads: tensor
 // parallel shards, long sequences) and add their partial dK / dV with TMA reduce-add.  strides as nxd_flash_attn_bwd
 // (24 values).
@@ -550,8 +593,10 @@ NXD_API int nxd_flash_attn_bwd_tc(const void* q, const void* k, const void* v, c
     if ((rc = make_tmap_bhsd(&tdo, dout, D, Sq, Hq, B, strides[14], strides[13], strides[12], kBM, p.pos_do))) return rc;
     if ((rc = make_tmap_bhsd(&tdk, dk, D, Sk, Hkv, B, strides[20], strides[19], strides[18], 32, p.pos_dk))) return rc;
     if ((rc = make_tmap_bhsd(&tdv, dv, D, Sk, Hkv, B, strides[23], strides[22], strides[21], 32, p.pos_dv))) return rc;
-    if ((rc = make_tmap_bhsd(&tdq, dq_accum, D, Sq, Hq, B, D, (long long)Sq * D, (long long)Hq * Sq * D, kBM, p.pos_dq,
-                             4)))
+    // dQ accumulator: d-major [B, Hq, D, Sq_pad] fp32, so that a warp's 32 (d) x 32 (q) block of dQ^T leaves TMEM
+    // and shared memory without a transpose; box = 32 d rows x 32 q columns (128 bytes)
+    if ((rc = make_tmap_bhsd(&tdq, dq_accum, p.Sq_pad, D, Hq, B, p.Sq_pad, (long long)D * p.Sq_pad,
+                             (long long)Hq * D * p.Sq_pad, 32, p.pos_dq, 4)))
         return rc;
     const long long kv_elems = (long long)B * Hkv * Sk * D;
     float* dk_acc = p.nsplit > 1 ? dkv_accum : dq_accum;   // unused maps still have to be valid
@@ -582,9 +627,9 @@ NXD_API int nxd_flash_attn_bwd_tc(const void* q, const void* k, const void* v, c
         NXD_LAUNCH_CHECK_N(2);
     }
     {
-        const long long n = (long long)B * Hq * Sq * (D / 8);
-        fa_bwd_tc_dq_convert_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(
-            dq_accum, (bf16*)dq, strides[15], strides[16], strides[17], B, Hq, Sq, D);
+        dim3 g((unsigned)((Sq + 31) / 32), (unsigned)Hq, (unsigned)B);
+        fa_bwd_tc_dq_transpose_kernel<<<g, 256, 0, st>>>(dq_accum, (bf16*)dq, strides[15], strides[16], strides[17], Hq,
+                                                         Sq, p.Sq_pad, D);
         NXD_LAUNCH_CHECK();
     }
     return 0;

@@ -22,6 +22,8 @@
 #include "attn_tc_common.cuh"
 #include "ptx.cuh"
 
+#include <type_traits>
+
 namespace {
 using namespace nxd_attn;
 
@@ -59,7 +61,7 @@ fa_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
                  const TcParams p) {
     using L = TcSmem<D>;
     extern __shared__ __align__(1024) uint8_t smem_raw[];
-    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* smem = align_smem_1024(smem_raw);
     uint8_t* sQ = smem + L::kQOff;
     uint8_t* sRing = smem + L::kRingOff;
     uint8_t* sP = smem + L::kPOff;
@@ -189,10 +191,12 @@ fa_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
         const int row = q * 32 + lane;          // row inside the q tile == TMEM lane
         const int grow = m0 + row;
         const uint32_t lane_off = (uint32_t)(q * 32) << 16;
+        // Running max in RAW score units (the scale is positive, so max commutes with it); the exponent argument is one
+        // FFMA per element: s * scale_log2 - m * scale_log2.
         float m_run = -INFINITY, l_run = 0.f;
-        for (int j = 0; j < n_tiles; ++j) {
-            ptx::mbar_wait(s_full, (uint32_t)j & 1u);
-            ptx::tcgen05_fence_after();
+        // one tile of the online softmax; MASK is instantiated only for tiles on the causal diagonal / past Sk
+        auto tile_softmax = [&](auto mask_tag, int j) {
+            constexpr bool MASK = decltype(mask_tag)::value;
             uint32_t sr[kBN];
             ptx::tmem_ld_32x32b_x32(tmem_s + lane_off, sr);
             ptx::tmem_ld_32x32b_x32(tmem_s + lane_off + 32, sr + 32);
@@ -200,41 +204,47 @@ fa_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
             ptx::tcgen05_fence_before();
             ptx::mbar_arrive(s_empty);
             const int n0 = j * kBN;
-            const bool need_mask = (n0 + kBN > p.Sk) || (CAUSAL && (n0 + kBN - 1 > m0 + q * 32 + offset));
-            float mx = -INFINITY;
+            if (MASK) {
+                // columns c >= first_bad are masked: beyond the causal diagonal of this row, or beyond the sequence end
+                int first_bad = p.Sk - n0;
+                if (CAUSAL) first_bad = min(first_bad, grow + offset + 1 - n0);
 #pragma unroll
-            for (int c = 0; c < kBN; ++c) {
-                float v = __uint_as_float(sr[c]) * p.scale_log2;
-                if (need_mask) {
-                    const int col = n0 + c;
-                    if (col >= p.Sk || (CAUSAL && col > grow + offset)) v = -INFINITY;
-                }
-                sr[c] = __float_as_uint(v);
-                mx = fmaxf(mx, v);
+                for (int c = 0; c < kBN; ++c)
+                    if (c >= first_bad) sr[c] = 0xff800000u;   // -inf
             }
-            // lazy rescale: keep the stale max unless it moved by more than 2^8
+            float mx0 = __uint_as_float(sr[0]), mx1 = __uint_as_float(sr[1]), mx2 = __uint_as_float(sr[2]),
+                  mx3 = __uint_as_float(sr[3]);
+#pragma unroll
+            for (int c = 4; c < kBN; c += 4) {
+                mx0 = fmaxf(mx0, __uint_as_float(sr[c]));
+                mx1 = fmaxf(mx1, __uint_as_float(sr[c + 1]));
+                mx2 = fmaxf(mx2, __uint_as_float(sr[c + 2]));
+                mx3 = fmaxf(mx3, __uint_as_float(sr[c + 3]));
+            }
+            const float mx = fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3));
+            // lazy rescale: keep the stale max unless it moved by more than 2^8 (in scaled log2 units)
             float alpha = 1.f;
             bool rescale = false;
-            if (mx > m_run + kRescaleThreshold || m_run == -INFINITY) {
+            if ((mx - m_run) * p.scale_log2 > kRescaleThreshold || m_run == -INFINITY) {
                 const float m_new = fmaxf(m_run, mx);
                 if (m_new != -INFINITY) {
-                    alpha = exp2f(m_run - m_new);   // 0 when m_run was -inf
+                    alpha = ex2_approx((m_run - m_new) * p.scale_log2);   // 0 when m_run was -inf
                     rescale = (j > 0) && (m_run != -INFINITY);
                     m_run = m_new;
                 }
             }
-            const float m_use = (m_run == -INFINITY) ? 0.f : m_run;
-            float rs = 0.f;
+            const float neg_m = (m_run == -INFINITY) ? 0.f : -m_run * p.scale_log2;
+            float rs0 = 0.f, rs1 = 0.f;
             uint32_t pk[kBN / 2];
 #pragma unroll
             for (int c = 0; c < kBN; c += 2) {
-                const float p0 = exp2f(__uint_as_float(sr[c]) - m_use);
-                const float p1 = exp2f(__uint_as_float(sr[c + 1]) - m_use);
-                rs += p0 + p1;
-                bf162 t = __floats2bfloat162_rn(p0, p1);
-                pk[c >> 1] = *reinterpret_cast<uint32_t*>(&t);
+                const float p0 = ex2_approx(fmaf(__uint_as_float(sr[c]), p.scale_log2, neg_m));
+                const float p1 = ex2_approx(fmaf(__uint_as_float(sr[c + 1]), p.scale_log2, neg_m));
+                rs0 += p0;
+                rs1 += p1;
+                pk[c >> 1] = pack_bf16x2(p0, p1);
             }
-            l_run = l_run * alpha + rs;
+            l_run = l_run * alpha + (rs0 + rs1);
             if (j > 0) {
                 ptx::mbar_wait(pv_done, ((uint32_t)(j - 1)) & 1u);  // P buffer free, O up to date
                 ptx::tcgen05_fence_after();
@@ -255,11 +265,19 @@ fa_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
             uint8_t* prow = sP + row * 128;
 #pragma unroll
             for (int c = 0; c < 8; ++c)
-                *reinterpret_cast<uint4*>(prow + ((c ^ (row & 7)) << 4)) =
-                    make_uint4(pk[4 * c], pk[4 * c + 1], pk[4 * c + 2], pk[4 * c + 3]);
+                st_shared_v4(prow + ((c ^ (row & 7)) << 4), pk[4 * c], pk[4 * c + 1], pk[4 * c + 2], pk[4 * c + 3]);
             ptx::fence_proxy_async();
             ptx::tcgen05_fence_before();
             ptx::mbar_arrive(p_full);
+        };
+        for (int j = 0; j < n_tiles; ++j) {
+            ptx::mbar_wait(s_full, (uint32_t)j & 1u);
+            ptx::tcgen05_fence_after();
+            const int n0 = j * kBN;
+            // warp-uniform: the tile crosses the sequence end, or the causal diagonal of one of this warp's 32 rows
+            const bool need_mask = (n0 + kBN > p.Sk) || (CAUSAL && (n0 + kBN - 1 > m0 + q * 32 + offset));
+            if (need_mask) tile_softmax(std::true_type{}, j);
+            else tile_softmax(std::false_type{}, j);
         }
         // ---- epilogue ----
         if (n_tiles > 0) {
@@ -268,7 +286,7 @@ fa_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
         }
         const float inv = l_run > 0.f ? 1.f / l_run : 0.f;
         if (p.lse && grow < p.Sq)
-            p.lse[((long long)b * p.Hq + hq) * p.Sq + grow] = l_run > 0.f ? m_run + log2f(l_run) : INFINITY;
+            p.lse[((long long)b * p.Hq + hq) * p.Sq + grow] = l_run > 0.f ? m_run * p.scale_log2 + log2f(l_run) : INFINITY;
         // every MMA that read Q has completed: reuse the Q tile as staging (warp q owns rows [32q, 32q+32) of
         // each 64-column group: 32 rows x 128 bytes = one TMA store box)
 #pragma unroll 1
@@ -292,7 +310,7 @@ fa_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
                                                     __uint_as_float(o[8 * c + 2 * e + 1]) * inv);
                     w[e] = *reinterpret_cast<uint32_t*>(&t);
                 }
-                *reinterpret_cast<uint4*>(dst + ((c ^ (row & 7)) << 4)) = make_uint4(w[0], w[1], w[2], w[3]);
+                st_shared_v4(dst + ((c ^ (row & 7)) << 4), w[0], w[1], w[2], w[3]);
             }
             ptx::fence_proxy_async();
             __syncwarp();

@@ -116,7 +116,7 @@ int nxd_flash_attn_bwd(const void* q, const void* k, const void* v, const void* 
 int nxd_flash_attn_fwd_tc(const void* q, const void* k, const void* v, void* o, float* lse,
                           const long long* strides, int B, int Hq, int Hkv, int Sq, int Sk, int D, float scale,
                           int causal, void* stream);
-/* scratch: lse_pad, delta_pad = B * Hq * roundup(Sq, 64) floats each; dq_accum = B * Hq * Sq * D floats, ZEROED
+/* scratch: lse_pad, delta_pad = B * Hq * roundup(Sq, 64) floats each; dq_accum = B * Hq * D * roundup(Sq, 64) floats (d-major), ZEROED
  * by the caller before the call (dQ is accumulated with TMA reduce-add).  dkv_accum: NULL, or 2 * B * Hkv * Sk * D
  * ZEROED floats: then nxd_flash_attn_bwd_tc_num_splits() CTAs share each K/V block and reduce-add their partial
  * dK / dV (few heads per GPU under tensor parallelism would otherwise leave most SMs idle). */

@@ -65,7 +65,7 @@ class _FlashAttnFn(torch.autograd.Function):
             sq_pad = (Sq + 63) // 64 * 64
             lse_pad = torch.empty(B * Hq * sq_pad, dtype=torch.float32, device=q.device)
             delta_pad = torch.empty_like(lse_pad)
-            dq_acc = torch.zeros((B, Hq, Sq, D), dtype=torch.float32, device=q.device)
+            dq_acc = torch.zeros((B, Hq, D, sq_pad), dtype=torch.float32, device=q.device)   # d-major accumulator
             # few (kv block, kv head) pairs per GPU (tensor-parallel shards): several CTAs share a K/V block and
             # reduce-add partial dK / dV into fp32 accumulators
             nsplit = int(_lib.lib().nxd_flash_attn_bwd_tc_num_splits(_c.c_int(B), _c.c_int(Hq), _c.c_int(Hkv),
