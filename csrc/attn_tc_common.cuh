@@ -33,12 +33,7 @@ __device__ __forceinline__ void coords(const int* pos, int row, int h, int b, in
     c[3] = pr == 3 ? row : (ph == 3 ? h : b);
 }
 
-// 1024-byte aligned start of the dynamic shared memory window.  The result is derived from the __shared__ array by
-// pointer arithmetic (not through an integer cast), so the compiler keeps the shared state space and emits LDS / STS
-// instead of generic LD / ST.
-__device__ __forceinline__ uint8_t* align_smem_1024(uint8_t* smem_raw) {
-    return smem_raw + ((1024u - (ptx::smem_u32(smem_raw) & 1023u)) & 1023u);
-}
+using ptx::align_smem_1024;
 
 __device__ __forceinline__ void st_shared_v4(void* dst, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
     asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(ptx::smem_u32(dst)), "r"(a), "r"(b), "r"(c), "r"(d)

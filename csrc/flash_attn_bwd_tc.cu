@@ -22,7 +22,7 @@
 // the MN-major A descriptor then walks 64 rows past the K tile into the V tile, which fills TMEM lanes 64..127 with
 // finite garbage that nobody reads -- cheaper than a second code path for the M = 64 TMEM layout.
 //
-// warp 0: TMA producer (K, V once; Q_i, dO_i, L_i, Delta_i through a 2-stage ring)   warp 1: TMEM alloc + MMA issue
+// warp 0: TMA producer (K, V once; Q_i, dO_i, L_i, Delta_i through a 3-stage ring)   warp 1: TMEM alloc + MMA issue
 // warps 2-9: softmax-backward math, dQ drain, epilogue.  Two math warps share every TMEM lane quadrant (warp % 4) and
 // split the 64 query columns of a tile between them: half the serial work per warp and twice the warps to hide the
 // TMEM-load / exp2 / shared-store latencies behind (the 4-warp version ran one warp per SM sub-partition and was
@@ -40,6 +40,7 @@ constexpr int kBN = 128;  // K/V rows per CTA
 constexpr int kBM = 64;   // query rows per tile
 constexpr int kThreadsBwd = 320;      // TMA warp + MMA warp + 8 math warps
 constexpr int kMathThreads = 256;
+constexpr int kQStages = 3;          // Q_i / dO_i / L_i / Delta_i ring: a tile is requested one full iteration before its MMAs
 
 struct BwdParams {
     const float* lse_pad;    // [B*Hq, Sq_pad] log2-domain LSE, +inf in the padding
@@ -54,14 +55,14 @@ template <int kD>
 struct BwdSmem {
     static constexpr int kKOff = 0;                       // [kD / 64 groups][128 rows][64]   32 KB at D = 128
     static constexpr int kVOff = kKOff + kBN * kD * 2;    // 32 KB
-    static constexpr int kQOff = kVOff + kBN * kD * 2;    // 2 stages x [2 groups][64 rows][64]   32 KB
-    static constexpr int kDOOff = kQOff + 2 * kBM * kD * 2;   // 32 KB
-    static constexpr int kPtOff = kDOOff + 2 * kBM * kD * 2;  // [128 rows][64] bf16   16 KB
+    static constexpr int kQOff = kVOff + kBN * kD * 2;    // kQStages x [2 groups][64 rows][64]   48 KB
+    static constexpr int kDOOff = kQOff + kQStages * kBM * kD * 2;   // 48 KB
+    static constexpr int kPtOff = kDOOff + kQStages * kBM * kD * 2;  // [128 rows][64] bf16   16 KB
     static constexpr int kDStOff = kPtOff + kBN * kBM * 2;    // 16 KB
     static constexpr int kDQOff = kDStOff + kBN * kBM * 2;    // [4 groups][64 q rows][32 fp32]   32 KB
-    static constexpr int kLOff = kDQOff + kBM * kD * 4;       // 2 stages x (64 L + 64 Delta) floats   1 KB
-    static constexpr int kBarOff = kLOff + 2 * 2 * kBM * 4;
-    static constexpr int kNumBars = 1 + 2 + 2 + 6;
+    static constexpr int kLOff = kDQOff + kBM * kD * 4;       // kQStages x (64 L + 64 Delta) floats   1.5 KB
+    static constexpr int kBarOff = kLOff + kQStages * 2 * kBM * 4;
+    static constexpr int kNumBars = 1 + 2 * kQStages + 6;
     // at least 120 KB so that only ONE CTA fits an SM: each CTA allocates all 512 TMEM columns
     static constexpr int kUsed = kBarOff + kNumBars * 8 + 16 + 1024;
     static constexpr int kBytes = kUsed < 120 * 1024 ? 120 * 1024 : kUsed;
@@ -91,14 +92,14 @@ fa_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
     float* sLD = reinterpret_cast<float*>(smem + L::kLOff);  // [stage][0: L, 1: Delta][64]
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L::kBarOff);
     uint64_t* kv_full = bars;
-    uint64_t* qdo_full = bars + 1;    // [2]
-    uint64_t* qdo_empty = bars + 3;   // [2]
-    uint64_t* st_full = bars + 5;
-    uint64_t* st_empty = bars + 6;
-    uint64_t* pds_full = bars + 7;
-    uint64_t* pds_empty = bars + 8;
-    uint64_t* dq_full = bars + 9;
-    uint64_t* dq_empty = bars + 10;
+    uint64_t* qdo_full = bars + 1;                  // [kQStages]
+    uint64_t* qdo_empty = qdo_full + kQStages;      // [kQStages]
+    uint64_t* st_full = qdo_empty + kQStages;
+    uint64_t* st_empty = st_full + 1;
+    uint64_t* pds_full = st_full + 2;
+    uint64_t* pds_empty = st_full + 3;
+    uint64_t* dq_full = st_full + 4;
+    uint64_t* dq_empty = st_full + 5;
     uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bars + L::kNumBars);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -123,7 +124,7 @@ fa_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
         ptx::prefetch_tensormap(&tmap_v);
         ptx::prefetch_tensormap(&tmap_dq);
         ptx::mbar_init(kv_full, 1);
-        for (int i = 0; i < 2; ++i) {
+        for (int i = 0; i < kQStages; ++i) {
             ptx::mbar_init(&qdo_full[i], 1);
             ptx::mbar_init(&qdo_empty[i], 1);
         }
@@ -156,8 +157,8 @@ fa_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
             }
             int th = it0 % tiles_per_head, hq = hkv * group + it0 / tiles_per_head;   // (q tile, q head) walk
             for (int it = 0; it < total; ++it) {
-                const int st = it & 1;
-                const uint32_t ph = (uint32_t)(it >> 1) & 1u;
+                const int st = it % kQStages;
+                const uint32_t ph = (uint32_t)(it / kQStages) & 1u;
                 const int m0 = (mb_start + th) * kBM;
                 ptx::mbar_wait(&qdo_empty[st], ph ^ 1u);
                 ptx::mbar_arrive_expect_tx(&qdo_full[st], L::kTxPerStage);
@@ -185,8 +186,8 @@ fa_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
             const uint32_t k_addr = ptx::smem_u32(sK), v_addr = ptx::smem_u32(sV), q_addr = ptx::smem_u32(sQ),
                            do_addr = ptx::smem_u32(sDO), pt_addr = ptx::smem_u32(sPt), dst_addr = ptx::smem_u32(sDSt);
             auto issue_scores = [&](int it) {
-                const int st = it & 1;
-                ptx::mbar_wait(&qdo_full[st], (uint32_t)(it >> 1) & 1u);
+                const int st = it % kQStages;
+                ptx::mbar_wait(&qdo_full[st], (uint32_t)(it / kQStages) & 1u);
                 ptx::mbar_wait(st_empty, ((uint32_t)it & 1u) ^ 1u);  // S^T/dP^T of tile it-1 are in registers
                 ptx::tcgen05_fence_after();
                 const uint32_t qb = q_addr + st * L::kStageBytes, dob = do_addr + st * L::kStageBytes;
@@ -210,7 +211,7 @@ fa_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
             issue_scores(0);
             for (int it = 0; it < total; ++it) {
                 if (it + 1 < total) issue_scores(it + 1);
-                const int st = it & 1;
+                const int st = it % kQStages;
                 const uint32_t qb = q_addr + st * L::kStageBytes, dob = do_addr + st * L::kStageBytes;
                 ptx::mbar_wait(pds_full, (uint32_t)it & 1u);
                 ptx::tcgen05_fence_after();
@@ -321,7 +322,7 @@ fa_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
         int th = it0 % tiles_per_head, hq = hkv * group + it0 / tiles_per_head;
         int prev_hq = hq, prev_m0 = 0;
         for (int it = 0; it < total; ++it) {
-            const int st = it & 1;
+            const int st = it % kQStages;
             const int m0 = (mb_start + th) * kBM;
             ptx::mbar_wait(st_full, (uint32_t)it & 1u);
             ptx::tcgen05_fence_after();
@@ -333,7 +334,7 @@ fa_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
             ptx::mbar_arrive(st_empty);
             // L / Delta of this tile were delivered with Q_i / dO_i (the MMA warp already saw qdo_full complete;
             // wait on it here too so that the bulk-copied bytes are visible to this thread)
-            ptx::mbar_wait(&qdo_full[st], (uint32_t)(it >> 1) & 1u);
+            ptx::mbar_wait(&qdo_full[st], (uint32_t)(it / kQStages) & 1u);
             const float* Ls = sLD + st * 2 * kBM;
             const float* Ds = Ls + kBM;
             // warp-uniform: does any (K/V row of this warp, query column of this warp) need masking?

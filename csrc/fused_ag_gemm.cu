@@ -151,7 +151,7 @@ ag_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a_local, const __grid_co
                const AgArgs ag, int M, int N, int K) {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     using L = SmemLayout<BN>;
-    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* smem = ptx::align_smem_1024(smem_raw);
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
     const uint32_t cta_rank = ptx::cluster_ctarank();

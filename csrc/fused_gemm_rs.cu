@@ -67,7 +67,7 @@ gemm_rs_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                const __grid_constant__ RsTmaps tmaps_d, const RsArgs rs, int M, int N, int K) {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     using L = SmemLayout<BN>;
-    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* smem = ptx::align_smem_1024(smem_raw);
     uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + L::kBarrierOffset);
     constexpr int kStages = L::kStages;
     uint64_t* empty_bar = full_bar + kStages;

@@ -30,6 +30,13 @@ __device__ __forceinline__ bool elect_one() {
     return pred != 0;
 }
 
+// 1024-byte aligned start of the dynamic shared memory window.  The result is derived from the __shared__ array by
+// pointer arithmetic (not through an integer cast), so the compiler keeps the shared state space and emits LDS / STS
+// instead of generic LD / ST.
+__device__ __forceinline__ uint8_t* align_smem_1024(uint8_t* smem_raw) {
+    return smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+}
+
 // ---- mbarrier ---------------------------------------------------------------
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));

@@ -272,16 +272,15 @@ def save_checkpoint(checkpoint_dir_str: str, tag: str, model=None, optimizer=Non
         has_ep = ep_size > 1 and any(getattr(v, "expert_model_parallel", False) for v in state.values()
                                      if isinstance(v, torch.Tensor))
         if has_ep:
-            # expert weights differ per EP rank: one file per ep rank holding the expert tensors, the dense
-            # remainder in the ep_rank-less file written by expert-DP rank 0 of EP rank 0
-            ep_state = {k: v for k, v in state.items() if getattr(v, "expert_model_parallel", False)}
-            dense = {k: v for k, v in state.items() if not getattr(v, "expert_model_parallel", False)}
-            exp_dp_rank = ps.get_expert_data_parallel_rank()
-            if exp_dp_rank == 0:
-                _queue(io, ep_state, os.path.join(tag, "model", _shard_name(0, tp_rank, pp_rank, ep_rank)), use_xser,
-                       0, 1)
-            if dp_rank == 0:
-                _queue(io, dense, os.path.join(tag, "model", _shard_name(0, tp_rank, pp_rank)), use_xser, 0, 1)
+            # expert weights differ per EP rank: like the reference (``_get_path("model", ep=True)``, checkpoint.py:655)
+            # every EP rank writes ONE file with its whole state -- dense tensors included -- from expert-DP rank 0;
+            # with xser the tensors of a file are spread over the expert-DP replicas of that EP rank
+            exp_dp_rank, exp_dp_size = ps.get_expert_data_parallel_rank(), ps.get_expert_data_parallel_size()
+            fname = os.path.join(tag, "model", _shard_name(0, tp_rank, pp_rank, ep_rank))
+            if use_xser:
+                _queue(io, state, fname, True, exp_dp_rank, exp_dp_size)
+            elif exp_dp_rank == 0:
+                _queue(io, state, fname, False, 0, 1)
         else:
             fname = os.path.join(tag, "model", _shard_name(0, tp_rank, pp_rank))
             if use_xser:
@@ -300,6 +299,11 @@ def save_checkpoint(checkpoint_dir_str: str, tag: str, model=None, optimizer=Non
             save_optim_state_dict(os.path.join(checkpoint_dir_str, tag, "optim"), state)
         elif zero1:
             _queue(io, state, os.path.join(tag, "optim", _shard_name(dp_rank, tp_rank, pp_rank)), use_xser, 0, 1)
+        elif ep_size > 1:
+            # plain optimizer under EP: the expert moments differ per EP rank -> one file per EP rank, written by its
+            # expert-DP rank 0 (reference ``_get_path("optim", ep=True)``, checkpoint.py:693-697)
+            if ps.get_expert_data_parallel_rank() == 0:
+                _queue(io, state, os.path.join(tag, "optim", _shard_name(0, tp_rank, pp_rank, ep_rank)), use_xser, 0, 1)
         elif dp_rank == 0:
             _queue(io, state, os.path.join(tag, "optim", _shard_name(0, tp_rank, pp_rank)), use_xser, 0, 1)
 
@@ -373,11 +377,16 @@ def load_checkpoint(path: str, tag: Optional[str] = None, model=None, optimizer=
     dp_group = ps.get_data_parallel_group() if (_mp() and ps.get_data_parallel_size() > 1) else None
 
     if model is not None:
-        fname = os.path.join(tag, "model", _shard_name(0, tp_rank, pp_rank))
-        state = _load_obj(storage, fname, use_xser, dp_group)
         ep_file = os.path.join(tag, "model", _shard_name(0, tp_rank, pp_rank, ep_rank))
+        plain = os.path.join(tag, "model", _shard_name(0, tp_rank, pp_rank))
         if ep_size > 1 and storage.file_exists(ep_file):
-            state.update(_load_obj(storage, ep_file, use_xser, None))
+            # reference layout: the EP rank's file is complete.  Checkpoints of the first release of this framework kept
+            # the dense tensors in the ep-less file and only the experts per EP rank: merge when both exist.
+            exp_dp_group = ps.get_expert_data_parallel_group() if ps.get_expert_data_parallel_size() > 1 else None
+            state = _load_obj(storage, plain, use_xser, dp_group) if storage.file_exists(plain) else {}
+            state.update(_load_obj(storage, ep_file, use_xser, exp_dp_group))
+        else:
+            state = _load_obj(storage, plain, use_xser, dp_group)
         if hasattr(model, "load_local_state_dict"):
             model.load_local_state_dict(state, strict=strict)
         else:
@@ -391,7 +400,12 @@ def load_checkpoint(path: str, tag: Optional[str] = None, model=None, optimizer=
             state = load_optim_state_dict(os.path.join(path, tag, "optim"), optimizer.state_dict())
         else:
             fname = os.path.join(tag, "optim", _shard_name(dp_rank if zero1 else 0, tp_rank, pp_rank))
-            state = _load_obj(storage, fname, use_xser, None if zero1 else dp_group)
+            group = None if zero1 else dp_group
+            ep_opt = os.path.join(tag, "optim", _shard_name(0, tp_rank, pp_rank, ep_rank))
+            if not zero1 and ep_size > 1 and storage.file_exists(ep_opt):
+                fname = ep_opt
+                group = ps.get_expert_data_parallel_group() if ps.get_expert_data_parallel_size() > 1 else None
+            state = _load_obj(storage, fname, use_xser, group)
         optimizer.load_state_dict(state)
 
     if scheduler is not None and storage.file_exists(os.path.join(tag, "scheduler.pt")):

@@ -137,3 +137,58 @@ def _ep_distinct_worker(rank, world):
 
 def test_expert_shards_stay_local_to_their_ep_rank_under_zero1():
     run_distributed(_ep_distinct_worker, 2)
+
+
+def _ep_resume_worker(rank, world, tmp, zero1):
+    """Save after step 1, run step 2; rebuild everything, load, run step 2 again: parameters must agree exactly.  Under
+    EP the expert Adam moments are different tensors on every EP rank, so each EP rank needs its own optimizer file."""
+    import os
+
+    from neuronx_distributed_llama3_2_b200 import trainer as nxd
+    from neuronx_distributed_llama3_2_b200.models import MixtralForCausalLM
+
+    cfg = nxd.neuronx_distributed_config(
+        tensor_parallel_size=1, expert_parallel_size=2,
+        optimizer_config={"zero_one_enabled": bool(zero1), "grad_clipping": True, "max_grad_norm": 1.0})
+
+    def build():
+        torch.manual_seed(0)
+        model = nxd.initialize_parallel_model(cfg, lambda: MixtralForCausalLM(_config(0)), device=torch.device("cpu"))
+        opt = nxd.initialize_parallel_optimizer(cfg, torch.optim.AdamW, model.parameters(), lr=LR, betas=(0.9, 0.95),
+                                                weight_decay=0.01)
+        return model, opt
+
+    ids = _batch().chunk(2, 0)[rank]
+
+    def step(model, opt):
+        opt.zero_grad()
+        model(ids, labels=ids).backward()
+        opt.step()
+
+    model, opt = build()
+    step(model, opt)
+    nxd.save_checkpoint(tmp, "s1", model=model, optimizer=opt)
+    step(model, opt)
+    want = {k: v.detach().clone() for k, v in model.state_dict().items()}
+    if rank == 0:
+        names = sorted(os.listdir(os.path.join(tmp, "s1", "model")))
+        assert names == ["dp_rank_00_ep_rank_00_tp_rank_00_pp_rank_00.pt", "dp_rank_00_ep_rank_01_tp_rank_00_pp_rank_00.pt"], names
+        onames = sorted(os.listdir(os.path.join(tmp, "s1", "optim")))
+        if zero1:
+            assert onames == ["dp_rank_00_tp_rank_00_pp_rank_00.pt", "dp_rank_01_tp_rank_00_pp_rank_00.pt"], onames
+        else:
+            assert onames == ["dp_rank_00_ep_rank_00_tp_rank_00_pp_rank_00.pt",
+                              "dp_rank_00_ep_rank_01_tp_rank_00_pp_rank_00.pt"], onames
+    model2, opt2 = build()
+    with torch.no_grad():
+        for p in model2.parameters():
+            p.add_(1.0)                       # make sure the load does the work
+    nxd.load_checkpoint(tmp, "s1", model=model2, optimizer=opt2)
+    step(model2, opt2)
+    for k, v in model2.state_dict().items():
+        assert torch.equal(v, want[k]), (rank, k, float((v - want[k]).abs().max()))
+
+
+@pytest.mark.parametrize("zero1", [0, 1])
+def test_ep_checkpoint_resume_keeps_every_ep_ranks_optimizer_state(tmp_path, zero1):
+    run_distributed(_ep_resume_worker, 2, str(tmp_path), zero1)

@@ -3,7 +3,7 @@
 set -u
 OUT=${GRAFT_REPO_ROOT:-.}/gpurun_out
 mkdir -p "$OUT"
-timeout 600 python -m pytest tests/test_kernels_gpu.py -m gpu -x -q -p no:cacheprovider -k "flash_attention" > "$OUT/attn_tests.log" 2>&1; echo "attn tests rc=$?"
+timeout 600 python -m pytest tests/test_kernels_gpu.py -m gpu -x -q -p no:cacheprovider -k "${NXD_TEST_FILTER:-flash_attention}" > "$OUT/attn_tests.log" 2>&1; echo "attn tests rc=$?"
 tail -n 15 "$OUT/attn_tests.log"
 timeout 600 python tools/bench_kernels.py --only attn > "$OUT/attn_micro.jsonl" 2> "$OUT/attn_micro.err"; echo "attn micro rc=$?"
 python - <<'PY'
