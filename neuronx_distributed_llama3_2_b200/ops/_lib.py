@@ -27,8 +27,8 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 _REPO = os.path.dirname(os.path.dirname(_HERE))
 CSRC_DIR = os.path.join(_REPO, "csrc")
 INCLUDE_DIR = os.path.join(_REPO, "include")
-LIB_PATH = os.path.join(_HERE, "libnxd_b200.so")
-BUILD_DIR = os.path.join(_REPO, "build", "obj")
+LIB_PATH = os.environ.get("NXD_B200_LIB") or os.path.join(_HERE, "libnxd_b200.so")   # override: kernel experiments
+BUILD_DIR = os.environ.get("NXD_BUILD_DIR") or os.path.join(_REPO, "build", "obj")
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
@@ -36,7 +36,7 @@ NVCC_FLAGS = [
     "--expt-relaxed-constexpr", "--use_fast_math",
     "-Xcompiler", "-fPIC",
     "-Xptxas", "-v",
-]
+] + [f for f in os.environ.get("NXD_NVCC_EXTRA", "").split() if f]
 
 _lib: Optional[ctypes.CDLL] = None
 _lock = threading.Lock()
