@@ -109,7 +109,12 @@ class CheckpointIOState:
 
     def _write_all(self, storage: BaseCheckpointStorage, tasks) -> None:
         for obj, filename, use_x in tasks:
-            if use_x:
+            if use_x == "dcp":
+                # collective-free torch.distributed.checkpoint save (safe on this thread, see zero_dcp_utils)
+                from ..optimizer.zero_dcp_utils import save_optim_state_dict
+
+                save_optim_state_dict(filename, obj)
+            elif use_x:
                 ref, tensors = obj
                 for tid, t in tensors:
                     storage.save_object(t, f"{filename}.tensors/tensor_{tid}.pt")
@@ -155,11 +160,10 @@ class CheckpointIOState:
 
     # -- reference method names (``trainer/checkpoint.py:99-285``) ---------------------------------------------------
     def add_dcp_save_task(self, state_dict: Any, dirname: str, aux_infos: Any = None) -> None:
-        """Queue a torch.distributed.checkpoint style save of a ZeRO-1 optimizer state: one file per rank below
-        ``dirname`` (written by ``optimizer/zero_dcp_utils.py`` when the queue is flushed)."""
-        from ..optimizer.zero_dcp_utils import _suffix
-
-        self._tasks.append((_to_cpu(state_dict), os.path.join(dirname, f"__{_suffix()}.distcp"), False))
+        """Queue a ``torch.distributed.checkpoint`` save of a ZeRO-1 optimizer state into the directory ``dirname``
+        (a file-system path).  The state is snapshotted to host memory now; the writer thread later runs
+        ``optimizer/zero_dcp_utils.save_optim_state_dict``, which issues no collective (reference ``:701-703``)."""
+        self._tasks.append((_to_cpu(state_dict), dirname, "dcp"))
 
     def wait_save(self, async_remove: bool = False) -> None:
         """Block until the queued writes of the current tag are on disk and its ``done`` marker is published."""
@@ -293,10 +297,7 @@ def save_checkpoint(checkpoint_dir_str: str, tag: str, model=None, optimizer=Non
             optimizer.__class__.__name__.endswith("Zero1Optimizer")
         state = optimizer.state_dict()
         if use_zero1_dcp and zero1:
-            from ..optimizer.zero_dcp_utils import save_optim_state_dict
-
-            io.wait_all()
-            save_optim_state_dict(os.path.join(checkpoint_dir_str, tag, "optim"), state)
+            io.add_dcp_save_task(state, os.path.join(checkpoint_dir_str, tag, "optim"))
         elif zero1:
             _queue(io, state, os.path.join(tag, "optim", _shard_name(dp_rank, tp_rank, pp_rank)), use_xser, 0, 1)
         elif ep_size > 1:

@@ -93,6 +93,68 @@ def _dp_worker(rank, world, tmp):
             assert torch.equal(before["state"][i]["exp_avg"], after["state"][i]["exp_avg"])
 
 
+def _dcp_async_worker(rank, world, tmp):
+    """Asynchronous save with the DCP optimizer path (reference unit test ``test_checkpoint.py:197-332``): the writer
+    thread must produce ``optim/.metadata`` + one ``__<rank>_0.distcp`` per rank without issuing a collective, and the
+    state must round-trip."""
+    import torch.distributed as dist
+
+    from neuronx_distributed_llama3_2_b200 import trainer as nxd
+
+    cfg = nxd.neuronx_distributed_config(optimizer_config={"zero_one_enabled": True, "grad_clipping": True,
+                                                           "max_grad_norm": 1.0})
+    model = nxd.initialize_parallel_model(cfg, _net, device=torch.device("cpu"))
+    opt = nxd.initialize_parallel_optimizer(cfg, torch.optim.AdamW, model.parameters(), lr=1e-2)
+    g = torch.Generator().manual_seed(11 + rank)
+    for _ in range(2):
+        opt.zero_grad()
+        (model(torch.randn(6, 24, generator=g)) ** 2).mean().backward()
+        opt.step()
+    before = opt.state_dict()
+    calls = []
+    real = {n: getattr(dist, n) for n in ("all_reduce", "all_gather", "all_gather_object", "gather_object", "broadcast",
+                                          "broadcast_object_list", "scatter_object_list", "reduce_scatter_tensor")}
+
+    def spy(name):
+        def f(*a, **k):
+            import threading
+
+            if threading.current_thread() is not threading.main_thread():
+                calls.append(name)
+            return real[name](*a, **k)
+        return f
+
+    for n in real:
+        setattr(dist, n, spy(n))
+    try:
+        d = os.path.join(tmp, "ck_async")
+        nxd.save_checkpoint(d, "t", model=model, optimizer=opt, use_zero1_dcp=True, async_save=True)
+        nxd.finalize_checkpoint()
+    finally:
+        for n, f in real.items():
+            setattr(dist, n, f)
+    assert not calls, f"collectives issued from the checkpoint writer thread: {calls}"
+    names = set(os.listdir(os.path.join(d, "t", "optim")))
+    assert ".metadata" in names and f"__{rank}_0.distcp" in names, names
+    assert not [n for n in names if n.startswith("write_results")], names
+    assert os.path.exists(os.path.join(d, "t", "done"))
+    for b in opt.optimizer.buckets:
+        b.master.zero_()
+        b.exp_avg.zero_()
+        b.exp_avg_sq.zero_()
+    nxd.load_checkpoint(d, "t", model=model, optimizer=opt, use_zero1_dcp=True)
+    after = opt.state_dict()
+    for i in before["base_state"]:
+        assert torch.equal(before["base_state"][i], after["base_state"][i])
+        if i in before["state"]:
+            assert torch.equal(before["state"][i]["exp_avg_sq"], after["state"][i]["exp_avg_sq"])
+
+
+def test_zero1_dcp_async_save_is_collective_free():
+    with tempfile.TemporaryDirectory() as tmp:
+        run_distributed(_dcp_async_worker, 2, tmp)
+
+
 def test_zero1_dp2_parity_convert_and_dcp():
     with tempfile.TemporaryDirectory() as tmp:
         run_distributed(_dp_worker, 2, tmp)
