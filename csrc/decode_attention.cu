@@ -6,17 +6,16 @@
 // examples/inference/modules/model_base.py:388-422 re-emits the whole cache through
 // torch.scatter.  Here the new K/V row is first written in place (nxd_kv_cache_update) and one
 // split-K kernel attends over positions [0, len) of the cache:
-//   grid = (B * n_kv_heads, n_splits); a CTA serves the `group = n_q/n_kv` query heads that share
-//   its KV head (native GQA, no repeat_kv), scoring keys thread-per-key and accumulating PV
-//   thread-per-channel; partial (m, l, o) per split go to scratch and a second kernel merges.
+//   grid = (B * n_kv_heads * head chunks, n_splits); a CTA serves up to 4 of the `group = n_q/n_kv` query heads that
+//   share its KV head (native GQA, no repeat_kv); every 8-lane group of a warp owns a strided subset of the keys with
+//   its own online-softmax state (see the kernel); partial (m, l, o) per split go to scratch and a second kernel merges.
 // The cache is either contiguous [B, n_kv, S_max, D] or paged [n_pages, n_kv, page, D] with a
 // block table [B, max_pages_per_seq].
 #include "common.cuh"
 
 namespace {
 
-constexpr int kMaxGroup = 8;     // q heads per kv head handled by one CTA
-constexpr int kChunk = 256;      // keys per inner chunk == threads per CTA
+constexpr int kMaxGroup = 64;    // q heads per kv head (processed in chunks of up to 4 heads per CTA)
 
 struct CacheView {
     const bf16* k;
@@ -37,172 +36,169 @@ __device__ __forceinline__ const bf16* row_ptr(const bf16* base, const CacheView
     return base + (size_t)b * c.stride_b + (size_t)h * c.stride_h + (size_t)pos * D;
 }
 
-// Block-wide max / sum of kMaxGroup values at once: one shared-memory exchange (two barriers) for the whole group
-// instead of one per query head.  red: kMaxGroup * 8 floats (8 warps).
-template <bool kMax>
-__device__ __forceinline__ void block_reduce_group(float (&v)[kMaxGroup], int group, float (*red)[kChunk / 32]) {
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-#pragma unroll
-    for (int g = 0; g < kMaxGroup; ++g) {
-        if (g < group) {
-#pragma unroll
-            for (int o = 16; o > 0; o >>= 1) {
-                const float t = __shfl_xor_sync(0xffffffffu, v[g], o);
-                v[g] = kMax ? fmaxf(v[g], t) : v[g] + t;
-            }
-        }
-    }
-    __syncthreads();   // protect `red` from its previous use
-    if (lane == 0) {
-#pragma unroll
-        for (int g = 0; g < kMaxGroup; ++g)
-            if (g < group) red[g][warp] = v[g];
-    }
-    __syncthreads();
-#pragma unroll
-    for (int g = 0; g < kMaxGroup; ++g) {
-        if (g < group) {
-            float r = red[g][0];
-#pragma unroll
-            for (int w = 1; w < kChunk / 32; ++w) r = kMax ? fmaxf(r, red[g][w]) : r + red[g][w];
-            v[g] = r;
-        }
-    }
-}
-
-template <int D>
-__global__ void __launch_bounds__(kChunk) decode_attn_split_kernel(
+// Split-K decode attention, one pass over the cache rows [start, end) of one (sequence, kv head, head chunk).
+//
+// Work decomposition (no shared memory and no block barrier inside the key loop):
+//   * a row of K or V (D bf16) is read by kLanes = 8 adjacent lanes, 16 bytes each (D = 128: two 16-byte pieces per
+//     lane), so a warp streams 4 consecutive rows = 512 (1024) contiguous bytes per load instruction;
+//   * lane group `sub` (0..3) of warp `w` owns the keys  start + (w * 4 + sub) + 16 * i  and keeps its OWN online-softmax
+//     state (m, l, o) for the G query heads of the chunk: the partial dot products are summed over the 8 lanes with
+//     3 shuffles, after which all 8 lanes hold the same score and update the same state, each for its D / 8 channels;
+//   * kUnroll keys per lane group are loaded before the first is used (memory-level parallelism: 8 KB per warp);
+//   * at the end the 16 lane groups of the CTA merge through shared memory and write one (m, l, o) partial.
+template <int D, int G>
+__global__ void __launch_bounds__(128) decode_attn_split_kernel(
     const bf16* __restrict__ q,  // [B, n_q, D]
     CacheView cache, const int* __restrict__ lengths, float* __restrict__ part_o,  // [B, n_q, splits, D]
     float* __restrict__ part_ml,                                                   // [B, n_q, splits, 2]
-    int n_q, int n_kv, int n_splits, float scale) {
-    const int b = blockIdx.x / n_kv;
-    const int hk = blockIdx.x % n_kv;
-    const int split = blockIdx.y;
+    int n_q, int n_kv, int n_splits, float scale_log2) {
+    constexpr int kLanes = 8;            // lanes per cache row
+    constexpr int kE = D / kLanes;       // channels per lane: 8 (D = 64) or 16 (D = 128)
+    constexpr int kV = kE / 8;           // 16-byte pieces per lane and row
+    constexpr int kUnroll = 4;
+    constexpr int kGroups = 16;          // lane groups per CTA (4 warps x 4)
     const int group = n_q / n_kv;
+    const int chunks = group / G;
+    const int b = blockIdx.x / (n_kv * chunks);
+    const int hk = (blockIdx.x / chunks) % n_kv;
+    const int h0 = hk * group + (blockIdx.x % chunks) * G;     // first query head of this CTA
+    const int split = blockIdx.y;
     const int len = lengths[b];
     const int per = (len + n_splits - 1) / n_splits;
     const int start = split * per;
     const int end = min(len, start + per);
-    const int tid = threadIdx.x;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int sub = lane >> 3, l8 = lane & 7;
+    const int gid = warp * 4 + sub;
 
-    constexpr int kLanesPerRow = D / 2;                  // PV phase: a thread owns two channels (one bf162 load per key)
-    constexpr int kParts = kChunk / kLanesPerRow;        // key partitions: 8 for D = 64, 4 for D = 128
-    __shared__ float sq[kMaxGroup][D];
-    __shared__ float sp[kMaxGroup][kChunk];
-    __shared__ float red[kMaxGroup][kChunk / 32];
-    __shared__ float2 so[kParts][kMaxGroup][kLanesPerRow];
+    float qf[G][kE];
+#pragma unroll
+    for (int g = 0; g < G; ++g) {
+        const bf16x8* qp = reinterpret_cast<const bf16x8*>(q + ((size_t)b * n_q + h0 + g) * D);
+#pragma unroll
+        for (int v = 0; v < kV; ++v) {
+            float t[8];
+            unpack8(qp[l8 + v * kLanes], t);
+#pragma unroll
+            for (int e = 0; e < 8; ++e) qf[g][v * 8 + e] = t[e] * scale_log2;
+        }
+    }
+    float m_run[G], l_run[G], o[G][kE];
+#pragma unroll
+    for (int g = 0; g < G; ++g) {
+        m_run[g] = -INFINITY;
+        l_run[g] = 0.f;
+#pragma unroll
+        for (int e = 0; e < kE; ++e) o[g][e] = 0.f;
+    }
 
-    for (int i = tid; i < group * D; i += kChunk) {
+    // the trip count is CTA-uniform (the shuffles below need every lane of the warp); a lane group whose keys fall
+    // behind `end` carries -inf scores through the iteration
+    for (int kb = start; kb < end; kb += kGroups * kUnroll) {
+        const int k0 = kb + gid;
+        bf16x8 kr[kUnroll][kV], vr[kUnroll][kV];
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u) {
+            const int pos = k0 + u * kGroups;
+            if (pos < end) {
+                const bf16x8* kp = reinterpret_cast<const bf16x8*>(row_ptr(cache.k, cache, b, hk, pos, D));
+                const bf16x8* vp = reinterpret_cast<const bf16x8*>(row_ptr(cache.v, cache, b, hk, pos, D));
+#pragma unroll
+                for (int v = 0; v < kV; ++v) {
+                    kr[u][v] = kp[l8 + v * kLanes];
+                    vr[u][v] = vp[l8 + v * kLanes];
+                }
+            }
+        }
+        float sc[kUnroll][G];
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u) {
+            float kf[kE];
+#pragma unroll
+            for (int v = 0; v < kV; ++v) unpack8(kr[u][v], kf + v * 8);
+#pragma unroll
+            for (int g = 0; g < G; ++g) {
+                float acc = 0.f;
+#pragma unroll
+                for (int e = 0; e < kE; ++e) acc = fmaf(kf[e], qf[g][e], acc);
+                sc[u][g] = acc;
+            }
+        }
+        // sum the partial dot products over the 8 lanes of the group (all lanes of the warp take part)
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u)
+#pragma unroll
+            for (int g = 0; g < G; ++g) {
+                float t = sc[u][g];
+                t += __shfl_xor_sync(0xffffffffu, t, 1);
+                t += __shfl_xor_sync(0xffffffffu, t, 2);
+                t += __shfl_xor_sync(0xffffffffu, t, 4);
+                sc[u][g] = (k0 + u * kGroups < end) ? t : -INFINITY;
+            }
+#pragma unroll
+        for (int g = 0; g < G; ++g) {
+            float mx = sc[0][g];
+#pragma unroll
+            for (int u = 1; u < kUnroll; ++u) mx = fmaxf(mx, sc[u][g]);
+            const float m_new = fmaxf(m_run[g], mx);
+            const float m_use = (m_new == -INFINITY) ? 0.f : m_new;     // no key of this lane group yet: all weights 0
+            const float alpha = exp2f(m_run[g] - m_use);                // exp2(-inf) = 0 while the state is empty
+            m_run[g] = m_new;
+            float pw[kUnroll], ps = 0.f;
+#pragma unroll
+            for (int u = 0; u < kUnroll; ++u) {
+                pw[u] = exp2f(sc[u][g] - m_use);
+                ps += pw[u];
+            }
+            l_run[g] = l_run[g] * alpha + ps;
+#pragma unroll
+            for (int e = 0; e < kE; ++e) o[g][e] *= alpha;
+#pragma unroll
+            for (int u = 0; u < kUnroll; ++u) {
+                if (k0 + u * kGroups < end) {
+#pragma unroll
+                    for (int v = 0; v < kV; ++v) {
+                        float vf[8];
+                        unpack8(vr[u][v], vf);
+#pragma unroll
+                        for (int e = 0; e < 8; ++e) o[g][v * 8 + e] = fmaf(pw[u], vf[e], o[g][v * 8 + e]);
+                    }
+                }
+            }
+        }
+    }
+
+    // merge the 16 lane groups: (m, l) per (group, head) and o per (group, head, channel) through shared memory
+    __shared__ float s_m[kGroups][G], s_l[kGroups][G];
+    __shared__ float s_o[kGroups][G][D + 4];
+    if (l8 == 0) {
+#pragma unroll
+        for (int g = 0; g < G; ++g) { s_m[gid][g] = m_run[g]; s_l[gid][g] = l_run[g]; }
+    }
+#pragma unroll
+    for (int g = 0; g < G; ++g)
+#pragma unroll
+        for (int v = 0; v < kV; ++v)
+#pragma unroll
+            for (int e = 0; e < 8; ++e) s_o[gid][g][(l8 + v * kLanes) * 8 + e] = o[g][v * 8 + e];
+    __syncthreads();
+    for (int i = threadIdx.x; i < G * D; i += blockDim.x) {
         const int g = i / D, d = i % D;
-        sq[g][d] = __bfloat162float(q[((size_t)b * n_q + hk * group + g) * D + d]) * scale;
-    }
-    __syncthreads();
-
-    float m_run[kMaxGroup], l_run[kMaxGroup];
-    float2 o_acc[kMaxGroup];
+        float m = -INFINITY;
 #pragma unroll
-    for (int g = 0; g < kMaxGroup; ++g) { m_run[g] = -INFINITY; l_run[g] = 0.f; o_acc[g] = make_float2(0.f, 0.f); }
-    const int d2 = tid % kLanesPerRow;
-    const int part = tid / kLanesPerRow;
-
-    for (int c0 = start; c0 < end; c0 += kChunk) {
-        const int pos = c0 + tid;
-        const bool valid = pos < end;
-        float s[kMaxGroup];
+        for (int t = 0; t < kGroups; ++t) m = fmaxf(m, s_m[t][g]);
+        float l = 0.f, acc = 0.f;
 #pragma unroll
-        for (int g = 0; g < kMaxGroup; ++g) s[g] = 0.f;
-        if (valid) {
-            const bf16x8* kr = reinterpret_cast<const bf16x8*>(row_ptr(cache.k, cache, b, hk, pos, D));
-#pragma unroll
-            for (int c = 0; c < D / 8; ++c) {
-                float kv[8];
-                bf16x8 p = kr[c];
-                unpack8(p, kv);
-#pragma unroll
-                for (int g = 0; g < kMaxGroup; ++g) {
-                    if (g < group) {
-#pragma unroll
-                        for (int e = 0; e < 8; ++e) s[g] += kv[e] * sq[g][c * 8 + e];
-                    }
-                }
-            }
+        for (int t = 0; t < kGroups; ++t) {
+            const float w = (s_m[t][g] == -INFINITY) ? 0.f : exp2f(s_m[t][g] - m);
+            l += s_l[t][g] * w;
+            acc += s_o[t][g][d] * w;
         }
-        // chunk softmax for all heads of the group (online across chunks)
-        float cm[kMaxGroup], pv[kMaxGroup], alpha[kMaxGroup];
-#pragma unroll
-        for (int g = 0; g < kMaxGroup; ++g) cm[g] = valid ? s[g] : -INFINITY;
-        block_reduce_group<true>(cm, group, red);
-#pragma unroll
-        for (int g = 0; g < kMaxGroup; ++g) {
-            if (g < group) {
-                const float nm = fmaxf(m_run[g], cm[g]);
-                pv[g] = valid ? __expf(s[g] - nm) : 0.f;
-                alpha[g] = __expf(m_run[g] - nm);
-                m_run[g] = nm;
-                sp[g][tid] = pv[g];
-            }
-        }
-        block_reduce_group<false>(pv, group, red);        // its barriers also publish sp[][] to the block
-#pragma unroll
-        for (int g = 0; g < kMaxGroup; ++g) {
-            if (g < group) {
-                l_run[g] = l_run[g] * alpha[g] + pv[g];
-                o_acc[g].x *= alpha[g];
-                o_acc[g].y *= alpha[g];
-            }
-        }
-        // PV: thread (part, d2) accumulates keys j = part, part + kParts, ... for channels 2 d2, 2 d2 + 1
-        const int nk = min(kChunk, end - c0);
-        // 8 V rows are requested before the first one is used: the loop is bound by load latency (a profile at
-        // batch 16 showed ~0.6 us per serial iteration), not by bandwidth or math
-        constexpr int kPf = 8;
-        for (int j0 = part; j0 < nk; j0 += kParts * kPf) {
-            bf162 raw[kPf];
-#pragma unroll
-            for (int u = 0; u < kPf; ++u) {
-                const int j = j0 + u * kParts;
-                raw[u] = j < nk ? reinterpret_cast<const bf162*>(row_ptr(cache.v, cache, b, hk, c0 + j, D))[d2]
-                                : __floats2bfloat162_rn(0.f, 0.f);
-            }
-#pragma unroll
-            for (int u = 0; u < kPf; ++u) {
-                const int j = j0 + u * kParts;
-                if (j < nk) {
-                    const float2 vv = __bfloat1622float2(raw[u]);
-#pragma unroll
-                    for (int g = 0; g < kMaxGroup; ++g) {
-                        if (g < group) {
-                            const float w = sp[g][j];
-                            o_acc[g].x += w * vv.x;
-                            o_acc[g].y += w * vv.y;
-                        }
-                    }
-                }
-            }
-        }
-        __syncthreads();     // sp[][] is rewritten by the next chunk
-    }
-    // merge the kParts partial accumulators
-    __shared__ float sml[kMaxGroup][2];
-#pragma unroll
-    for (int g = 0; g < kMaxGroup; ++g) {
-        if (g < group) {
-            so[part][g][d2] = o_acc[g];
-            if (tid == 0) { sml[g][0] = m_run[g]; sml[g][1] = l_run[g]; }
-        }
-    }
-    __syncthreads();
-    for (int i = tid; i < group * kLanesPerRow; i += kChunk) {
-        const int g = i / kLanesPerRow, dd = i % kLanesPerRow;
-        float2 acc = make_float2(0.f, 0.f);
-#pragma unroll
-        for (int p = 0; p < kParts; ++p) { acc.x += so[p][g][dd].x; acc.y += so[p][g][dd].y; }
-        const size_t base = (((size_t)b * n_q + hk * group + g) * n_splits + split);
-        reinterpret_cast<float2*>(part_o + base * D)[dd] = acc;
-        if (dd == 0) {
-            part_ml[base * 2 + 0] = sml[g][0];
-            part_ml[base * 2 + 1] = sml[g][1];
+        const size_t base = (((size_t)b * n_q + h0 + g) * n_splits + split);
+        part_o[base * D + d] = acc;
+        if (d == 0) {
+            part_ml[base * 2 + 0] = m;       // log2 domain, like the weights of the merge kernel
+            part_ml[base * 2 + 1] = l;
         }
     }
 }
@@ -217,7 +213,7 @@ __global__ void decode_attn_merge_kernel(const float* __restrict__ part_o, const
     float l = 0.f, o = 0.f;
     for (int s = 0; s < n_splits; ++s) {
         const float ms = part_ml[(bh * n_splits + s) * 2];
-        const float w = (ms == -INFINITY) ? 0.f : __expf(ms - m);
+        const float w = (ms == -INFINITY) ? 0.f : exp2f(ms - m);
         l += part_ml[(bh * n_splits + s) * 2 + 1] * w;
         o += part_o[(bh * n_splits + s) * D + d] * w;
     }
@@ -258,9 +254,9 @@ __global__ void kv_cache_update_kernel(const bf16* __restrict__ new_k, const bf1
 }  // namespace
 
 NXD_API int nxd_decode_attn_num_splits(int B, int n_kv, int max_len) {
-    // enough CTAs to cover the machine, at least 256 keys per split
+    // enough CTAs to cover the machine, at least 128 keys per split (two iterations of the 64-key CTA step)
     int want = (2 * nxd_num_sms() + B * n_kv - 1) / (B * n_kv);
-    int by_len = (max_len + 255) / 256;
+    int by_len = (max_len + 127) / 128;
     int s = want < by_len ? want : by_len;
     if (s < 1) s = 1;
     if (s > 64) s = 64;
@@ -281,18 +277,31 @@ NXD_API int nxd_decode_attn(const void* q, const void* cache_k, const void* cach
                  page_size > 0 ? page_size : 1, max_pages};
     float* part_o = scratch;
     float* part_ml = scratch + (size_t)B * n_q * n_splits * D;
-    dim3 grid(B * n_kv, n_splits);
+    const int group = n_q / n_kv;
+    const int G = group <= 4 ? group : (group % 4 == 0 ? 4 : (group % 3 == 0 ? 3 : (group % 2 == 0 ? 2 : 1)));
+    dim3 grid(B * n_kv * (group / G), n_splits);
+    const float scale_log2 = scale * 1.4426950408889634f;
+#define NXD_DECODE_LAUNCH(DD, GG)                                                                                  \
+    decode_attn_split_kernel<DD, GG><<<grid, 128, 0, s>>>((const bf16*)q, cv, lengths, part_o, part_ml, n_q, n_kv, \
+                                                          n_splits, scale_log2)
+#define NXD_DECODE_DISPATCH(DD)                 \
+    switch (G) {                                \
+        case 1: NXD_DECODE_LAUNCH(DD, 1); break; \
+        case 2: NXD_DECODE_LAUNCH(DD, 2); break; \
+        case 3: NXD_DECODE_LAUNCH(DD, 3); break; \
+        default: NXD_DECODE_LAUNCH(DD, 4); break; \
+    }
     if (D == 64) {
-        decode_attn_split_kernel<64><<<grid, kChunk, 0, s>>>((const bf16*)q, cv, lengths, part_o, part_ml, n_q,
-                                                             n_kv, n_splits, scale);
+        NXD_DECODE_DISPATCH(64)
         NXD_LAUNCH_CHECK();
         decode_attn_merge_kernel<64><<<B * n_q, 64, 0, s>>>(part_o, part_ml, (bf16*)out, n_splits);
     } else {
-        decode_attn_split_kernel<128><<<grid, kChunk, 0, s>>>((const bf16*)q, cv, lengths, part_o, part_ml, n_q,
-                                                              n_kv, n_splits, scale);
+        NXD_DECODE_DISPATCH(128)
         NXD_LAUNCH_CHECK();
         decode_attn_merge_kernel<128><<<B * n_q, 128, 0, s>>>(part_o, part_ml, (bf16*)out, n_splits);
     }
+#undef NXD_DECODE_DISPATCH
+#undef NXD_DECODE_LAUNCH
     NXD_LAUNCH_CHECK();
     return 0;
 }
