@@ -85,6 +85,26 @@ __device__ __forceinline__ void tma_reduce_add_4d(const CUtensorMap* map, const 
         "r"(ptx::smem_u32(src)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
         : "memory");
 }
+// Attention dropout (reference: nki_flash_attn_func(..., dropout_p, ..., seed), kernels/flash_attn.py:122-127,151-160).
+// The keep decision of element (batch b, q head h, query i, key j) is a pure function of (seed, b, h, i, j), so the
+// forward pass (thread = query row) and the backward pass (thread = key row) regenerate the same mask without storing
+// it: a 32-bit integer hash (two multiply-xorshift rounds) compared with dropout_p * 2^32.
+struct DropParams {
+    uint32_t threshold;   // drop iff hash < threshold; 0 = no dropout
+    float inv_keep;       // 1 / (1 - dropout_p)
+    uint32_t seed;
+};
+__host__ __device__ __forceinline__ uint32_t drop_head_seed(uint32_t seed, uint32_t bh) { return seed ^ (bh * 0x9E3779B1u); }
+__host__ __device__ __forceinline__ bool drop_keep(uint32_t head_seed, uint32_t i, uint32_t j, uint32_t threshold) {
+    uint32_t x = (i * 0x85EBCA77u) ^ (j * 0xC2B2AE3Du) ^ head_seed;
+    x ^= x >> 16;
+    x *= 0x7FEB352Du;
+    x ^= x >> 15;
+    x *= 0x846CA68Bu;
+    x ^= x >> 16;
+    return x >= threshold;
+}
+
 __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
     asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
 }

@@ -49,6 +49,7 @@ struct BwdParams {
     int nsplit;              // CTAs that share one (kv block, kv head): each walks 1/nsplit of the (q head, q tile) list
     int pos_q[3], pos_do[3], pos_k[3], pos_v[3], pos_dk[3], pos_dv[3], pos_dq[3], pos_acc[3];
     float scale, scale_log2;
+    DropParams drop;
 };
 
 template <int kD>
@@ -71,7 +72,7 @@ struct BwdSmem {
 };
 static_assert(BwdSmem<128>::kBytes <= 232448, "shared memory budget exceeded");
 
-template <int kD, bool CAUSAL>
+template <int kD, bool CAUSAL, bool DROP>
 __global__ void __launch_bounds__(kThreadsBwd, 1)
 fa_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_do,
                  const __grid_constant__ CUtensorMap tmap_k, const __grid_constant__ CUtensorMap tmap_v,
@@ -292,7 +293,7 @@ fa_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
         // P^T = exp2(S^T c - L_q), dS^T = P^T (dP^T - Delta_q) for this thread's K/V row and 32 query columns.
         // MASK is instantiated only for the tiles that touch the causal diagonal or the end of the K/V sequence.
         auto softmax_bwd = [&](auto mask_tag, const uint32_t* s, const uint32_t* dp, const float* Ls, const float* Ds,
-                               int m0, uint32_t* pk, uint32_t* dk_) {
+                               int m0, int hq, uint32_t* pk, uint32_t* dk_) {
             constexpr bool MASK = decltype(mask_tag)::value;
             // masked <=> krow >= Sk, or (causal) krow > m0 + c0h + c + offset  <=>  c < first_ok
             int first_ok = 0;
@@ -310,7 +311,19 @@ fa_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
                 for (int e = 0; e < 4; ++e) {
                     pv[e] = ex2_approx(fmaf(__uint_as_float(s[c + e]), p.scale_log2, -lv[e]));
                     if (MASK && c + e < first_ok) pv[e] = 0.f;
-                    dsv[e] = pv[e] * (__uint_as_float(dp[c + e]) - dv[e]);
+                    float dpe = __uint_as_float(dp[c + e]);
+                    if (DROP) {
+                        // forward multiplied P by keep / (1 - p) before P V: dV takes the dropped P, and dP (= dO V^T
+                        // w.r.t. the dropped P) is masked the same way before it meets Delta
+                        const uint32_t hs = drop_head_seed(p.drop.seed, (uint32_t)(b * p.Hq + hq));
+                        const float km = drop_keep(hs, (uint32_t)(m0 + c0h + c + e), (uint32_t)krow, p.drop.threshold)
+                                             ? p.drop.inv_keep : 0.f;
+                        dpe *= km;
+                        dsv[e] = pv[e] * (dpe - dv[e]);
+                        pv[e] *= km;
+                    } else {
+                        dsv[e] = pv[e] * (dpe - dv[e]);
+                    }
                 }
                 pk[c >> 1] = pack_bf16x2(pv[0], pv[1]);
                 pk[(c >> 1) + 1] = pack_bf16x2(pv[2], pv[3]);
@@ -340,8 +353,8 @@ fa_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
             // warp-uniform: does any (K/V row of this warp, query column of this warp) need masking?
             const bool need_mask = (n0 + kBN > p.Sk) || (CAUSAL && (n0 + q4 * 32 + 31 > m0 + c0h + offset));
             uint32_t pk[16], dk_[16];
-            if (need_mask) softmax_bwd(std::true_type{}, s, dp, Ls, Ds, m0, pk, dk_);
-            else softmax_bwd(std::false_type{}, s, dp, Ls, Ds, m0, pk, dk_);
+            if (need_mask) softmax_bwd(std::true_type{}, s, dp, Ls, Ds, m0, hq, pk, dk_);
+            else softmax_bwd(std::false_type{}, s, dp, Ls, Ds, m0, hq, pk, dk_);
             if (it > 0) ptx::mbar_wait(pds_empty, ((uint32_t)(it - 1)) & 1u);  // MMAs of tile it-1 finished with sPt/sDSt
             uint8_t* prow = sPt + row * 128;
             uint8_t* drow = sDSt + row * 128;
@@ -529,14 +542,14 @@ fa_bwd_tc_dq_transpose_kernel(const float* __restrict__ acc, bf16* __restrict__ 
     }
 }
 
-template <int kD, bool CAUSAL>
+template <int kD, bool CAUSAL, bool DROP>
 int launch_bwd_tc(dim3 grid, cudaStream_t st, const CUtensorMap& tq, const CUtensorMap& tdo, const CUtensorMap& tk,
                   const CUtensorMap& tv, const CUtensorMap& tdk, const CUtensorMap& tdv, const CUtensorMap& tdq,
                   const CUtensorMap& tdka, const CUtensorMap& tdva, const BwdParams& p) {
-    static cudaError_t once = cudaFuncSetAttribute(fa_bwd_tc_kernel<kD, CAUSAL>,
+    static cudaError_t once = cudaFuncSetAttribute(fa_bwd_tc_kernel<kD, CAUSAL, DROP>,
                                                    cudaFuncAttributeMaxDynamicSharedMemorySize, BwdSmem<kD>::kBytes);
     NXD_CHECK_CUDA(once);
-    fa_bwd_tc_kernel<kD, CAUSAL><<<grid, kThreadsBwd, BwdSmem<kD>::kBytes, st>>>(tq, tdo, tk, tv, tdk, tdv, tdq, tdka, tdva, p);
+    fa_bwd_tc_kernel<kD, CAUSAL, DROP><<<grid, kThreadsBwd, BwdSmem<kD>::kBytes, st>>>(tq, tdo, tk, tv, tdk, tdv, tdq, tdka, tdva, p);
     NXD_LAUNCH_CHECK();
     return 0;
 }
@@ -563,10 +576,10 @@ NXD_API int nxd_flash_attn_bwd_tc_num_splits(int B, int Hq, int Hkv, int Sq, int
 // buffer -- then nxd_flash_attn_bwd_tc_num_splits() CTAs share every K/V block (small batch x heads: tensor
 // parallel shards, long sequences) and add their partial dK / dV with TMA reduce-add.  strides as nxd_flash_attn_bwd
 // (24 values).
-NXD_API int nxd_flash_attn_bwd_tc(const void* q, const void* k, const void* v, const void* o, const void* dout,
-                                  const float* lse, float* lse_pad, float* delta_pad, float* dq_accum, float* dkv_accum,
-                                  void* dq, void* dk, void* dv, const long long* strides, int B, int Hq, int Hkv, int Sq,
-                                  int Sk, int D, float scale, int causal, void* stream) {
+static int bwd_tc_impl(const void* q, const void* k, const void* v, const void* o, const void* dout, const float* lse,
+                       float* lse_pad, float* delta_pad, float* dq_accum, float* dkv_accum, void* dq, void* dk, void* dv,
+                       const long long* strides, int B, int Hq, int Hkv, int Sq, int Sk, int D, float scale, int causal,
+                       float dropout_p, unsigned long long seed, void* stream) {
     NXD_REQUIRE(D == 128 || D == 64, "flash_attn_bwd_tc: head dim %d not supported (64 or 128)", D);
     NXD_REQUIRE(B > 0 && Hq > 0 && Hkv > 0 && Sq > 0 && Sk > 0 && Hq % Hkv == 0, "flash_attn_bwd_tc: bad problem");
     for (int i = 0; i < 24; ++i)
@@ -578,6 +591,10 @@ NXD_API int nxd_flash_attn_bwd_tc(const void* q, const void* k, const void* v, c
     p.Sq_pad = (Sq + kBM - 1) / kBM * kBM;
     p.lse_pad = lse_pad; p.delta_pad = delta_pad;
     p.scale = scale; p.scale_log2 = scale * 1.4426950408889634f;
+    NXD_REQUIRE(dropout_p >= 0.f && dropout_p < 1.f, "flash_attn_bwd_tc: dropout_p %f not in [0, 1)", dropout_p);
+    p.drop.threshold = dropout_p > 0.f ? (uint32_t)fmin(4294967295.0, (double)dropout_p * 4294967296.0) : 0u;
+    p.drop.inv_keep = 1.f / (1.f - dropout_p);
+    p.drop.seed = (uint32_t)(seed ^ (seed >> 32));
     p.nsplit = dkv_accum ? nxd_flash_attn_bwd_tc_num_splits(B, Hq, Hkv, Sq, Sk) : 1;
     {
         const long long rows = (long long)B * Hq * p.Sq_pad;
@@ -612,12 +629,16 @@ NXD_API int nxd_flash_attn_bwd_tc(const void* q, const void* k, const void* v, c
         tdva = tdq;
     }
     dim3 grid((Sk + kBN - 1) / kBN, Hkv * p.nsplit, B);
-    if (D == 128)
-        rc = causal ? launch_bwd_tc<128, true>(grid, st, tq, tdo, tk, tv, tdk, tdv, tdq, tdka, tdva, p)
-                    : launch_bwd_tc<128, false>(grid, st, tq, tdo, tk, tv, tdk, tdv, tdq, tdka, tdva, p);
-    else
-        rc = causal ? launch_bwd_tc<64, true>(grid, st, tq, tdo, tk, tv, tdk, tdv, tdq, tdka, tdva, p)
-                    : launch_bwd_tc<64, false>(grid, st, tq, tdo, tk, tv, tdk, tdv, tdq, tdka, tdva, p);
+#define NXD_BWD_ARGS grid, st, tq, tdo, tk, tv, tdk, tdv, tdq, tdka, tdva, p
+    const bool drop = p.drop.threshold != 0;
+    if (D == 128) {
+        if (drop) rc = causal ? launch_bwd_tc<128, true, true>(NXD_BWD_ARGS) : launch_bwd_tc<128, false, true>(NXD_BWD_ARGS);
+        else rc = causal ? launch_bwd_tc<128, true, false>(NXD_BWD_ARGS) : launch_bwd_tc<128, false, false>(NXD_BWD_ARGS);
+    } else {
+        if (drop) rc = causal ? launch_bwd_tc<64, true, true>(NXD_BWD_ARGS) : launch_bwd_tc<64, false, true>(NXD_BWD_ARGS);
+        else rc = causal ? launch_bwd_tc<64, true, false>(NXD_BWD_ARGS) : launch_bwd_tc<64, false, false>(NXD_BWD_ARGS);
+    }
+#undef NXD_BWD_ARGS
     if (rc) return rc;
     if (p.nsplit > 1) {
         const long long n = kv_elems / 8;
@@ -634,4 +655,22 @@ NXD_API int nxd_flash_attn_bwd_tc(const void* q, const void* k, const void* v, c
         NXD_LAUNCH_CHECK();
     }
     return 0;
+}
+
+NXD_API int nxd_flash_attn_bwd_tc(const void* q, const void* k, const void* v, const void* o, const void* dout,
+                                  const float* lse, float* lse_pad, float* delta_pad, float* dq_accum, float* dkv_accum,
+                                  void* dq, void* dk, void* dv, const long long* strides, int B, int Hq, int Hkv, int Sq,
+                                  int Sk, int D, float scale, int causal, void* stream) {
+    return bwd_tc_impl(q, k, v, o, dout, lse, lse_pad, delta_pad, dq_accum, dkv_accum, dq, dk, dv, strides, B, Hq, Hkv, Sq,
+                       Sk, D, scale, causal, 0.f, 0ull, stream);
+}
+
+// Backward of nxd_flash_attn_fwd_tc_dropout: same dropout_p and seed as the forward call.
+NXD_API int nxd_flash_attn_bwd_tc_dropout(const void* q, const void* k, const void* v, const void* o, const void* dout,
+                                          const float* lse, float* lse_pad, float* delta_pad, float* dq_accum,
+                                          float* dkv_accum, void* dq, void* dk, void* dv, const long long* strides, int B,
+                                          int Hq, int Hkv, int Sq, int Sk, int D, float scale, int causal,
+                                          float dropout_p, unsigned long long seed, void* stream) {
+    return bwd_tc_impl(q, k, v, o, dout, lse, lse_pad, delta_pad, dq_accum, dkv_accum, dq, dk, dv, strides, B, Hq, Hkv, Sq,
+                       Sk, D, scale, causal, dropout_p, seed, stream);
 }

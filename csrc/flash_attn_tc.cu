@@ -38,6 +38,7 @@ struct TcParams {
     int B, Hq, Hkv, Sq, Sk;
     int pos_q[3], pos_k[3], pos_v[3], pos_o[3];  // coordinate slot (1..3) of (row, head, batch) in each tensor map
     float scale_log2;
+    DropParams drop;
 };
 
 template <int D>
@@ -54,7 +55,7 @@ struct TcSmem {
     static constexpr int kTmemCols = (D + kBN <= 128) ? 128 : 256;
 };
 
-template <int D, bool CAUSAL>
+template <int D, bool CAUSAL, bool DROP>
 __global__ void __launch_bounds__(kThreadsTc, 2)
 fa_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_k,
                  const __grid_constant__ CUtensorMap tmap_v, const __grid_constant__ CUtensorMap tmap_o,
@@ -242,7 +243,14 @@ fa_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
                 const float p1 = ex2_approx(fmaf(__uint_as_float(sr[c + 1]), p.scale_log2, neg_m));
                 rs0 += p0;
                 rs1 += p1;
-                pk[c >> 1] = pack_bf16x2(p0, p1);
+                if (DROP) {   // the row sum (softmax denominator) is taken before dropout, the PV operand after it
+                    const uint32_t hs = drop_head_seed(p.drop.seed, (uint32_t)(b * p.Hq + hq));
+                    const bool k0 = drop_keep(hs, (uint32_t)grow, (uint32_t)(n0 + c), p.drop.threshold);
+                    const bool k1 = drop_keep(hs, (uint32_t)grow, (uint32_t)(n0 + c + 1), p.drop.threshold);
+                    pk[c >> 1] = pack_bf16x2(k0 ? p0 * p.drop.inv_keep : 0.f, k1 ? p1 * p.drop.inv_keep : 0.f);
+                } else {
+                    pk[c >> 1] = pack_bf16x2(p0, p1);
+                }
             }
             l_run = l_run * alpha + (rs0 + rs1);
             if (j > 0) {
@@ -329,32 +337,35 @@ fa_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
     if (warp == 1) ptx::tmem_dealloc<1>(tmem_base, L::kTmemCols);
 }
 
+template <int D, bool CAUSAL, bool DROP>
+int launch_fwd_tc_one(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const CUtensorMap& to,
+                      const TcParams& p, cudaStream_t st) {
+    using L = TcSmem<D>;
+    dim3 grid((p.Sq + kBM - 1) / kBM, p.Hq, p.B);
+    static cudaError_t once = cudaFuncSetAttribute(fa_fwd_tc_kernel<D, CAUSAL, DROP>,
+                                                   cudaFuncAttributeMaxDynamicSharedMemorySize, L::kBytes);
+    NXD_CHECK_CUDA(once);
+    fa_fwd_tc_kernel<D, CAUSAL, DROP><<<grid, kThreadsTc, L::kBytes, st>>>(tq, tk, tv, to, p);
+    NXD_LAUNCH_CHECK();
+    return 0;
+}
+
 template <int D>
 int launch_fwd_tc(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const CUtensorMap& to,
                   const TcParams& p, int causal, cudaStream_t st) {
-    using L = TcSmem<D>;
-    dim3 grid((p.Sq + kBM - 1) / kBM, p.Hq, p.B);
-    if (causal) {
-        static cudaError_t once = cudaFuncSetAttribute(fa_fwd_tc_kernel<D, true>,
-                                                       cudaFuncAttributeMaxDynamicSharedMemorySize, L::kBytes);
-        NXD_CHECK_CUDA(once);
-        fa_fwd_tc_kernel<D, true><<<grid, kThreadsTc, L::kBytes, st>>>(tq, tk, tv, to, p);
-    } else {
-        static cudaError_t once = cudaFuncSetAttribute(fa_fwd_tc_kernel<D, false>,
-                                                       cudaFuncAttributeMaxDynamicSharedMemorySize, L::kBytes);
-        NXD_CHECK_CUDA(once);
-        fa_fwd_tc_kernel<D, false><<<grid, kThreadsTc, L::kBytes, st>>>(tq, tk, tv, to, p);
-    }
-    NXD_LAUNCH_CHECK();
-    return 0;
+    const bool drop = p.drop.threshold != 0;
+    if (causal) return drop ? launch_fwd_tc_one<D, true, true>(tq, tk, tv, to, p, st)
+                            : launch_fwd_tc_one<D, true, false>(tq, tk, tv, to, p, st);
+    return drop ? launch_fwd_tc_one<D, false, true>(tq, tk, tv, to, p, st)
+                : launch_fwd_tc_one<D, false, false>(tq, tk, tv, to, p, st);
 }
 
 }  // namespace
 
 // Same arguments as nxd_flash_attn_fwd.  Extra requirement: 16-byte aligned base pointers.
-NXD_API int nxd_flash_attn_fwd_tc(const void* q, const void* k, const void* v, void* o, float* lse,
-                                  const long long* strides, int B, int Hq, int Hkv, int Sq, int Sk, int D, float scale,
-                                  int causal, void* stream) {
+static int fwd_tc_impl(const void* q, const void* k, const void* v, void* o, float* lse, const long long* strides, int B,
+                       int Hq, int Hkv, int Sq, int Sk, int D, float scale, int causal, float dropout_p,
+                       unsigned long long seed, void* stream) {
     NXD_REQUIRE(D == 64 || D == 128, "flash_attn_tc: head dim %d not supported (64 or 128)", D);
     NXD_REQUIRE(B > 0 && Hq > 0 && Hkv > 0 && Sq > 0 && Sk > 0 && Hq % Hkv == 0, "flash_attn_tc: bad problem");
     for (int i = 0; i < 12; ++i)
@@ -366,6 +377,10 @@ NXD_API int nxd_flash_attn_fwd_tc(const void* q, const void* k, const void* v, v
     p.lse = lse;
     p.B = B; p.Hq = Hq; p.Hkv = Hkv; p.Sq = Sq; p.Sk = Sk;
     p.scale_log2 = scale * 1.4426950408889634f;
+    NXD_REQUIRE(dropout_p >= 0.f && dropout_p < 1.f, "flash_attn_tc: dropout_p %f not in [0, 1)", dropout_p);
+    p.drop.threshold = dropout_p > 0.f ? (uint32_t)fmin(4294967295.0, (double)dropout_p * 4294967296.0) : 0u;
+    p.drop.inv_keep = 1.f / (1.f - dropout_p);
+    p.drop.seed = (uint32_t)(seed ^ (seed >> 32));
     CUtensorMap tq, tk, tv, to;
     int rc;
     if ((rc = make_tmap_bhsd(&tq, q, D, Sq, Hq, B, strides[2], strides[1], strides[0], kBM, p.pos_q))) return rc;
@@ -374,4 +389,19 @@ NXD_API int nxd_flash_attn_fwd_tc(const void* q, const void* k, const void* v, v
     if ((rc = make_tmap_bhsd(&to, o, D, Sq, Hq, B, strides[11], strides[10], strides[9], 32, p.pos_o))) return rc;
     return D == 64 ? launch_fwd_tc<64>(tq, tk, tv, to, p, causal, (cudaStream_t)stream)
                    : launch_fwd_tc<128>(tq, tk, tv, to, p, causal, (cudaStream_t)stream);
+}
+
+NXD_API int nxd_flash_attn_fwd_tc(const void* q, const void* k, const void* v, void* o, float* lse,
+                                  const long long* strides, int B, int Hq, int Hkv, int Sq, int Sk, int D, float scale,
+                                  int causal, void* stream) {
+    return fwd_tc_impl(q, k, v, o, lse, strides, B, Hq, Hkv, Sq, Sk, D, scale, causal, 0.f, 0ull, stream);
+}
+
+// Same, with attention dropout: P is multiplied by a keep mask / (1 - dropout_p) before the PV product; the mask is a
+// function of (seed, batch, head, query, key) that nxd_flash_attn_bwd_tc_dropout regenerates.
+NXD_API int nxd_flash_attn_fwd_tc_dropout(const void* q, const void* k, const void* v, void* o, float* lse,
+                                          const long long* strides, int B, int Hq, int Hkv, int Sq, int Sk, int D,
+                                          float scale, int causal, float dropout_p, unsigned long long seed,
+                                          void* stream) {
+    return fwd_tc_impl(q, k, v, o, lse, strides, B, Hq, Hkv, Sq, Sk, D, scale, causal, dropout_p, seed, stream);
 }

@@ -191,6 +191,77 @@ __global__ void __launch_bounds__(kArThreads) skinny_gemm_ar_kernel(const bf16* 
     if (ar.tp > 1) ar_end(ar, epoch);
 }
 
+// ---- single GPU, long K (down projection, K = intermediate size): with one column pair per warp a warp walks K in
+// several dependent batches of loads and the kernel is latency bound (33 MB in ~22 us).  Here a CTA owns only two
+// column pairs and its 8 warps split K four ways, so every warp has ONE batch of loads in flight and four times as
+// many warps share the stream; the four partial sums per output meet in shared memory.
+template <int kB>
+__global__ void __launch_bounds__(kArThreads) skinny_splitk_kernel(const bf16* __restrict__ x, const bf16* __restrict__ w,
+                                                                   const bf16* __restrict__ residual, bf16* __restrict__ out,
+                                                                   int B, int N, int K, long long ldx, long long ldw,
+                                                                   long long ldo) {
+    constexpr int kSplit = 4, kPairs = kArWarps / kSplit, kCols = 2 * kPairs;
+    extern __shared__ __align__(16) uint8_t ar_smem[];
+    bf16* xs = reinterpret_cast<bf16*>(ar_smem);
+    float* part = reinterpret_cast<float*>(ar_smem + (size_t)kB * K * sizeof(bf16));   // [kSplit][kB][kCols]
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int k8 = K / 8;
+    for (int i = threadIdx.x; i < kB * k8; i += kArThreads) {
+        const int row = i / k8, c = i % k8;
+        uint4 v = make_uint4(0u, 0u, 0u, 0u);
+        if (row < B) v = *reinterpret_cast<const uint4*>(x + (size_t)row * ldx + (size_t)c * 8);
+        reinterpret_cast<uint4*>(xs)[i] = v;
+    }
+    __syncthreads();
+    const int pair = warp % kPairs, ks = warp / kPairs;
+    const int c0 = (int)blockIdx.x * kCols + pair * 2;
+    const bool v0 = c0 < N, v1 = c0 + 1 < N;
+    const bf16* w0 = w + (size_t)(v0 ? c0 : 0) * ldw;
+    const bf16* w1 = w + (size_t)(v1 ? c0 + 1 : 0) * ldw;
+    const int per = (k8 + kSplit - 1) / kSplit;
+    const int kbeg = ks * per, kend = min(k8, kbeg + per);
+    float acc0[kB], acc1[kB];
+#pragma unroll
+    for (int b = 0; b < kB; ++b) acc0[b] = acc1[b] = 0.f;
+#pragma unroll (kB <= 2 ? 8 : 4)
+    for (int k = kbeg + lane; k < kend; k += 32) {
+        const uint4 a0 = __ldg(reinterpret_cast<const uint4*>(w0) + k);
+        const uint4 a1 = __ldg(reinterpret_cast<const uint4*>(w1) + k);
+#pragma unroll
+        for (int b = 0; b < kB; ++b) {
+            const uint4 xv = reinterpret_cast<const uint4*>(xs)[b * k8 + k];
+            acc0[b] = dot8(a0, xv, acc0[b]);
+            acc1[b] = dot8(a1, xv, acc1[b]);
+        }
+    }
+#pragma unroll
+    for (int b = 0; b < kB; ++b) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            acc0[b] += __shfl_xor_sync(0xffffffffu, acc0[b], o);
+            acc1[b] += __shfl_xor_sync(0xffffffffu, acc1[b], o);
+        }
+    }
+    if (lane == 0) {
+#pragma unroll
+        for (int b = 0; b < kB; ++b) {
+            part[(ks * kB + b) * kCols + pair * 2] = acc0[b];
+            part[(ks * kB + b) * kCols + pair * 2 + 1] = acc1[b];
+        }
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < B * kCols; i += kArThreads) {
+        const int b = i / kCols, c = i % kCols;
+        const int col = (int)blockIdx.x * kCols + c;
+        if (col >= N) continue;
+        float v = 0.f;
+#pragma unroll
+        for (int s2 = 0; s2 < kSplit; ++s2) v += part[(s2 * kB + b) * kCols + c];
+        if (residual) v += __bfloat162float(residual[(size_t)b * ldo + col]);
+        out[(size_t)b * ldo + col] = __float2bfloat16(v);
+    }
+}
+
 // ---- 9 .. 16 rows: the FMA loop above re-reads every X row from shared memory per weight vector and becomes FMA /
 // LDS bound; here the 16 x K activation tile feeds mma.sync m16n8k16 (M = 16 is exactly one fragment).  A CTA owns
 // `cols` output columns and walks them 8 at a time; its 8 warps split K, every lane fetches 16 contiguous bytes of a
@@ -333,6 +404,14 @@ int fill_args(ArArgs& ar, void* const* stage_ptrs, void* const* sig_ptrs, int tp
 template <int kB>
 int launch_skinny(const bf16* x, const bf16* w, const bf16* residual, bf16* out, int B, int N, int K, long long ldx,
                   long long ldw, long long ldo, const ArArgs& ar, cudaStream_t st) {
+    if (ar.tp == 1 && K >= 4096 && kB <= 4) {     // long contraction on one GPU: split K inside the CTA
+        const size_t smem_k = (size_t)kB * K * sizeof(bf16) + (size_t)4 * kB * 4 * sizeof(float);
+        NXD_REQUIRE(smem_k <= 200 * 1024, "skinny_gemm_ar: B %d x K %d does not fit shared memory", B, K);
+        NXD_CHECK_CUDA(cudaFuncSetAttribute(skinny_splitk_kernel<kB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_k));
+        skinny_splitk_kernel<kB><<<(N + 3) / 4, kArThreads, smem_k, st>>>(x, w, residual, out, B, N, K, ldx, ldw, ldo);
+        NXD_LAUNCH_CHECK();
+        return 0;
+    }
     // columns per CTA: multiple of 16 (8 warps x 2 columns), as few as co-residency allows
     int dev = 0, sms = 0;
     NXD_CHECK_CUDA(cudaGetDevice(&dev));

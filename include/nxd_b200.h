@@ -211,6 +211,32 @@ int nxd_embedding_fwd_sp_push(const long long* ids, const void* weight, void* co
 int nxd_p2p_push_probe(int mode, const void* src, const void* const* dst_ptrs, int n_dst, size_t bytes, int ctas,
                        int chunk, int bufs, int read_lag, int sig_mode, int sig_every, size_t flag_off, void* stream);
 
+/* Attention dropout (reference: nki_flash_attn_func(q, k, v, dropout_p, ..., seed), kernels/flash_attn.py:122-127,151-160).
+ * Same arguments as the calls above plus dropout_p in [0, 1) and a seed; the keep mask is a hash of
+ * (seed, batch, head, query, key), so the backward call regenerates it from the same two values. */
+int nxd_flash_attn_fwd_tc_dropout(const void* q, const void* k, const void* v, void* o, float* lse,
+                                  const long long* strides, int B, int Hq, int Hkv, int Sq, int Sk, int D, float scale,
+                                  int causal, float dropout_p, unsigned long long seed, void* stream);
+int nxd_flash_attn_bwd_tc_dropout(const void* q, const void* k, const void* v, const void* o, const void* dout,
+                                  const float* lse, float* lse_pad, float* delta_pad, float* dq_accum, float* dkv_accum,
+                                  void* dq, void* dk, void* dv, const long long* strides, int B, int Hq, int Hkv, int Sq,
+                                  int Sk, int D, float scale, int causal, float dropout_p, unsigned long long seed,
+                                  void* stream);
+
+/* ---- token-generation projections with fused neighbours (reference: the token-generation graph,
+ *      examples/inference/modules/model_base.py:459-518, attention_base.py:172-200) ----------------------------------
+ * q, k, v = W_qkv rmsnorm(x); RoPE(q, k) at positions[b]; q -> q_out [B, n_q, D]; k, v -> the KV cache row
+ * (contiguous [lines, n_kv, S, D] with strides in elements, or paged with block_table [lines, max_pages]).
+ * norm_w NULL = no norm.  B <= 8, D in {64, 128}. */
+int nxd_decode_qkv_rope_cache(const void* x, long long ldx, const void* norm_w, float eps, const void* w, long long ldw,
+                              const float* cos_t, const float* sin_t, const int* positions, void* q_out, void* cache_k,
+                              void* cache_v, const int* seq_ids, const int* block_table, long long stride_b,
+                              long long stride_h, int page_size, int max_pages, int B, int K, int n_q, int n_kv, int D,
+                              void* stream);
+/* out[B, I] = silu(W_gate rmsnorm(x)) * (W_up rmsnorm(x)); w = [2 I, K] with the gate rows first.  B <= 8. */
+int nxd_decode_gate_up_swiglu(const void* x, long long ldx, const void* norm_w, float eps, const void* w, long long ldw,
+                              void* out, long long ldo, int B, int K, int I, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

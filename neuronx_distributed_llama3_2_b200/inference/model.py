@@ -159,7 +159,87 @@ class KVCacheInferenceMixin:
         """Hook on the fused projection output ``[B*T, heads, D]`` before RoPE (DBRX clamps it)."""
         return qkv
 
+    # -- fused token-generation layer (6 launches) -------------------------------------------------------------------
+    def _fused_decode_ok(self, layer, hidden: torch.Tensor) -> bool:
+        """The fused decode kernels apply to the plain Llama layer shape: RMSNorm, bias-free fused QKV, SwiGLU MLP,
+        bf16 weights, at most 8 sequences, native backends selected, and (tensor parallel) the one-shot all-reduce
+        context for the row-parallel projections.  Model families that override the hooks take the generic path."""
+        from ..ops import backend, decode_fused
+        from ..parallel.layers import RowParallelLinear
+
+        cached = getattr(layer, "_nxd_fused_decode", None)
+        if cached is None:
+            cls = type(self)
+            attn, mlp = getattr(layer, "self_attn", None), getattr(layer, "mlp", None)
+            qkv = getattr(attn, "qkv_proj", None)
+            w = getattr(qkv, "weight_qkv", None)
+            cached = bool(
+                cls._post_qkv is KVCacheInferenceMixin._post_qkv and cls._add_norm is KVCacheInferenceMixin._add_norm
+                and cls._mlp is KVCacheInferenceMixin._mlp and getattr(self.config, "fuse_qkv", False)
+                and isinstance(w, torch.Tensor) and w.dtype == torch.bfloat16 and getattr(qkv, "bias_qkv", None) is None
+                and type(getattr(attn, "o_proj", None)) is RowParallelLinear and attn.o_proj.bias is None
+                and type(getattr(mlp, "down_proj", None)) is RowParallelLinear and mlp.down_proj.bias is None
+                and hasattr(mlp, "gate_up_proj") and type(mlp.gate_up_proj).__name__ == "ColumnParallelLinear"
+                and mlp.gate_up_proj.bias is None and mlp.gate_up_proj.weight.dtype == torch.bfloat16
+                and hasattr(layer.input_layernorm, "variance_epsilon") and attn.head_dim in (64, 128)
+                and qkv.kv_size_multiplier == 1)
+            layer._nxd_fused_decode = cached
+        if not cached or backend.gemm_backend() != "tcgen05":
+            return False
+        x = hidden.reshape(hidden.shape[0], -1)
+        if not decode_fused.qualifies(x):
+            return False
+        if ps.get_tensor_model_parallel_size() > 1:
+            return backend.fused_comm_enabled() and ps.get_symm_mem_context("tp") is not None
+        return True
+
+    def _layer_fused_decode(self, i: int, layer, hidden, residual, positions, seq_ids, lengths):
+        """One token per sequence: RMSNorm+QKV+RoPE+cache write | attention (split, merge) | o_proj+residual |
+        RMSNorm+gate/up+SwiGLU | down_proj+residual.  The residual stream leaves every row-parallel GEMV already
+        summed, so the returned residual is ``None`` (the next layer's norm reads the stream directly)."""
+        from ..ops import decode_fused
+        from ..ops.fused_comm import skinny_gemm
+
+        B = hidden.shape[0]
+        x = hidden.reshape(B, -1)
+        if residual is not None:
+            x = x + residual.reshape(B, -1)
+        attn, mlp = layer.self_attn, layer.mlp
+        nq, nkv, D = attn.q_heads_local, attn.kv_heads_local, attn.head_dim
+        cos, sin = self._rope(x.device)
+        ck, cv = self.kv_cache.layer(i)
+        kc = self.kv_cache
+        memo = getattr(self, "_decode_i32", None)          # int32 copies once per forward, not once per layer
+        if memo is None or memo[0] is not positions or memo[1] is not seq_ids:
+            memo = (positions, seq_ids, positions[:, 0].to(torch.int32).contiguous(),
+                    seq_ids.to(torch.int32).contiguous() if seq_ids is not None else None)
+            self._decode_i32 = memo
+        pos, sid = memo[2], memo[3]
+        table = kc.block_table if kc.paged else None
+        q = decode_fused.qkv_rope_cache(x, layer.input_layernorm.weight, layer.input_layernorm.variance_epsilon,
+                                        attn.qkv_proj.weight_qkv, cos, sin, pos, ck, cv, nq, nkv, D, seq_ids=sid,
+                                        block_table=table, page_size=kc.page_size if kc.paged else 0)
+        if kc.paged:
+            t = table if seq_ids is None else table[seq_ids.long()]
+            o = attn_ops.decode_attention(q, ck, cv, lengths, block_table=t, page_size=kc.page_size)
+        elif seq_ids is not None:
+            o = attn_ops.decode_attention(q, ck.index_select(0, seq_ids.long()), cv.index_select(0, seq_ids.long()), lengths)
+        else:
+            o = attn_ops.decode_attention(q, ck, cv, lengths)
+        ctx = ps.get_symm_mem_context("tp") if ps.get_tensor_model_parallel_size() > 1 else None
+        x2 = skinny_gemm(o.reshape(B, nq * D), attn.o_proj.weight, residual=x, ctx=ctx)
+        if x2 is None:      # shape outside the skinny kernel: generic projection, then the residual
+            x2 = attn.o_proj(o.reshape(B, 1, nq * D)).reshape(B, -1) + x
+        act = decode_fused.gate_up_swiglu(x2, layer.post_attention_layernorm.weight,
+                                          layer.post_attention_layernorm.variance_epsilon, mlp.gate_up_proj.weight)
+        x3 = skinny_gemm(act, mlp.down_proj.weight, residual=x2, ctx=ctx)
+        if x3 is None:
+            x3 = mlp.down_proj(act.reshape(B, 1, -1)).reshape(B, -1) + x2
+        return x3.reshape(B, 1, -1), None
+
     def _layer(self, i: int, layer, hidden, residual, positions, seq_ids, lengths, prefill):
+        if not prefill and hidden.shape[1] == 1 and self._fused_decode_ok(layer, hidden):
+            return self._layer_fused_decode(i, layer, hidden, residual, positions, seq_ids, lengths)
         h, residual = self._add_norm(layer.input_layernorm, hidden, residual)
         a = self._attention(i, layer.self_attn, h, positions, seq_ids, lengths, prefill)
         h, residual = self._add_norm(layer.post_attention_layernorm, a, residual)
@@ -192,8 +272,9 @@ class KVCacheInferenceMixin:
             rows = torch.arange(B, device=hidden.device)
             hidden, residual = hidden[rows, idx.long()], residual[rows, idx.long()]
         else:
-            hidden, residual = hidden[:, 0], residual[:, 0]
-        hidden, _ = self._add_norm(self._final_norm(), hidden.contiguous(), residual.contiguous())
+            hidden, residual = hidden[:, 0], (residual[:, 0] if residual is not None else None)
+        hidden, _ = self._add_norm(self._final_norm(), hidden.contiguous(),
+                                   residual.contiguous() if residual is not None else None)
         logits = self.lm_head(hidden)                                   # [B, V/tp]
         logits = mappings.gather_from_tensor_model_parallel_region(logits)[:, : self.config.vocab_size]
         tokens = self.sampler.sample(logits.float() if logits.dtype not in (torch.float32, torch.bfloat16) else logits,

@@ -26,8 +26,8 @@ import torch.nn.functional as F
 from . import _lib, backend
 
 
-def attention_ref(q, k, v, causal=True, softmax_scale=None):
-    """fp32 reference.  q [B,Hq,S,D], k/v [B,Hkv,Sk,D]."""
+def attention_ref(q, k, v, causal=True, softmax_scale=None, dropout_p=0.0, seed=0):
+    """fp32 reference.  q [B,Hq,S,D], k/v [B,Hkv,Sk,D].  Dropout uses the kernels' keep mask (same seed -> same mask)."""
     B, Hq, S, D = q.shape
     Hkv = k.shape[1]
     scale = softmax_scale if softmax_scale is not None else 1.0 / math.sqrt(D)
@@ -40,6 +40,11 @@ def attention_ref(q, k, v, causal=True, softmax_scale=None):
         mask = torch.ones(S, Sk, dtype=torch.bool, device=q.device).tril(diagonal=Sk - S)
         s = s.masked_fill(~mask, float("-inf"))
     p = torch.softmax(s, dim=-1)
+    if dropout_p > 0.0:
+        from .flash_attn import dropout_keep_mask
+
+        keep = dropout_keep_mask(seed, B, Hq, S, k.shape[2], dropout_p, device=q.device)
+        p = p * keep / (1.0 - dropout_p)
     return torch.matmul(p, vf).to(q.dtype)
 
 
@@ -59,17 +64,22 @@ def _backend(q: torch.Tensor) -> str:
 def flash_attn_func(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, dropout_p: float = 0.0,
                     softmax_scale: Optional[float] = None, causal: bool = True, mixed_precision: bool = True,
                     seed: Optional[int] = None) -> torch.Tensor:
-    """q ``[B, Hq, S, D]``, k/v ``[B, Hkv, S, D]`` (any strides with unit stride on D) -> ``[B, Hq, S, D]``."""
-    assert dropout_p == 0.0, "attention dropout is not implemented (Llama-3.x trains with 0.0)"
+    """q ``[B, Hq, S, D]``, k/v ``[B, Hkv, S, D]`` (any strides with unit stride on D) -> ``[B, Hq, S, D]``.
+
+    ``dropout_p`` / ``seed`` as in the reference (``kernels/flash_attn.py:122-127,151-160``): the softmax probabilities
+    are dropped with probability ``dropout_p`` and rescaled by ``1 / (1 - dropout_p)`` before the PV product; the mask is
+    a deterministic function of ``seed`` (drawn from the torch generator when ``None``), so backward regenerates it."""
     be = _backend(q)
+    if dropout_p > 0.0 and seed is None:
+        seed = int(torch.randint(0, 2 ** 62, (1,)).item())
     if be == "nxd":
         from .flash_attn import flash_attn_nxd
 
-        return flash_attn_nxd(q, k, v, softmax_scale, causal)
+        return flash_attn_nxd(q, k, v, softmax_scale, causal, dropout_p, seed or 0)
     if be == "sdpa":
-        return F.scaled_dot_product_attention(q, k, v, is_causal=causal, scale=softmax_scale,
+        return F.scaled_dot_product_attention(q, k, v, dropout_p=dropout_p, is_causal=causal, scale=softmax_scale,
                                               enable_gqa=(q.shape[1] != k.shape[1]))
-    return attention_ref(q, k, v, causal, softmax_scale)
+    return attention_ref(q, k, v, causal, softmax_scale, dropout_p, seed or 0)
 
 
 nki_flash_attn_func = flash_attn_func  # reference-compatible alias

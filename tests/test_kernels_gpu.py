@@ -501,3 +501,99 @@ def test_skinny_gemm_i8(B, K, N, per_channel):
     out = skinny_gemm_i8(x, w, scale, residual=res)
     ref = ref + res.float()
     assert ((out.float() - ref).norm() / ref.norm()).item() < 4e-3
+
+
+@pytest.mark.parametrize("B,D,paged", [(1, 64, False), (3, 128, False), (8, 64, True)])
+def test_decode_fused_qkv_rope_cache(B, D, paged):
+    """RMSNorm + fused QKV GEMV + RoPE + KV-cache write in one launch against the unfused fp32 math."""
+    from neuronx_distributed_llama3_2_b200.ops import decode_fused, rope as rope_ops
+
+    torch.manual_seed(B * 7 + D)
+    H, nq, nkv, S = 1024, 8, 2, 256
+    x = torch.randn(B, H, device="cuda").bfloat16()
+    nw = (1 + 0.1 * torch.randn(H, device="cuda")).bfloat16()
+    w = (torch.randn((nq + 2 * nkv) * D, H, device="cuda") * 0.03).bfloat16()
+    cos, sin = rope_ops.build_rope_cache(S, D, 500000.0, None, device="cuda")
+    pos = torch.randint(0, S, (B,), device="cuda", dtype=torch.int32)
+    page = 16
+    if paged:
+        n_pages = B * S // page
+        ck = torch.zeros(n_pages, nkv, page, D, device="cuda", dtype=torch.bfloat16)
+        cv = torch.zeros_like(ck)
+        table = torch.randperm(n_pages, device="cuda").reshape(B, S // page).to(torch.int32)
+    else:
+        ck = torch.zeros(B, nkv, S, D, device="cuda", dtype=torch.bfloat16)
+        cv = torch.zeros_like(ck)
+        table = None
+    q = decode_fused.qkv_rope_cache(x, nw, 1e-5, w, cos, sin, pos, ck, cv, nq, nkv, D, block_table=table,
+                                    page_size=page if paged else 0)
+    xf = x.float()
+    xn = (xf * torch.rsqrt(xf.pow(2).mean(-1, keepdim=True) + 1e-5) * nw.float()).bfloat16().float()
+    qkv = (xn @ w.float().t()).reshape(B, nq + 2 * nkv, D)
+    c, s_ = cos[pos.long()], sin[pos.long()]                       # [B, D/2]
+    a, b_ = qkv[:, : nq + nkv, : D // 2], qkv[:, : nq + nkv, D // 2:]
+    rot = torch.cat([a * c[:, None] - b_ * s_[:, None], b_ * c[:, None] + a * s_[:, None]], dim=-1)
+    assert (q.float() - rot[:, :nq]).abs().max() < 3e-2
+    for b in range(B):
+        p = int(pos[b])
+        if paged:
+            krow = ck[int(table[b, p // page]), :, p % page]
+            vrow = cv[int(table[b, p // page]), :, p % page]
+        else:
+            krow, vrow = ck[b, :, p], cv[b, :, p]
+        assert (krow.float() - rot[b, nq:]).abs().max() < 3e-2
+        assert (vrow.float() - qkv[b, nq + nkv:]).abs().max() < 3e-2
+    assert int((ck != 0).any(-1).sum()) == B * nkv        # exactly one row per (sequence, kv head) was written
+
+
+@pytest.mark.parametrize("B", [1, 5, 8])
+def test_decode_fused_gate_up_swiglu(B):
+    from neuronx_distributed_llama3_2_b200.ops import decode_fused
+
+    torch.manual_seed(B)
+    H, I = 2048, 1536
+    x = torch.randn(B, H, device="cuda").bfloat16()
+    nw = (1 + 0.1 * torch.randn(H, device="cuda")).bfloat16()
+    w = (torch.randn(2 * I, H, device="cuda") * 0.03).bfloat16()
+    out = decode_fused.gate_up_swiglu(x, nw, 1e-5, w)
+    xf = x.float()
+    xn = (xf * torch.rsqrt(xf.pow(2).mean(-1, keepdim=True) + 1e-5) * nw.float()).bfloat16().float()
+    gu = xn @ w.float().t()
+    ref = torch.nn.functional.silu(gu[:, :I]) * gu[:, I:]
+    assert (out.float() - ref).abs().max() < 3e-2 * max(1.0, float(ref.abs().max()))
+    plain = decode_fused.gate_up_swiglu(x, None, 0.0, w)           # no norm: x is used as is
+    gu2 = xf @ w.float().t()
+    ref2 = torch.nn.functional.silu(gu2[:, :I]) * gu2[:, I:]
+    assert (plain.float() - ref2).abs().max() < 3e-2 * max(1.0, float(ref2.abs().max()))
+
+
+@pytest.mark.parametrize("D,causal", [(128, True), (64, True), (128, False)])
+def test_flash_attention_dropout_matches_oracle_mask(D, causal):
+    """Attention dropout in the tcgen05 kernels (reference ``kernels/flash_attn.py:122-127,151-160``): forward and all three
+    gradients against fp32 math that applies the SAME keep mask (restated from the kernel's hash), plus the keep rate and
+    seed dependence."""
+    from neuronx_distributed_llama3_2_b200.ops import attention as A
+    from neuronx_distributed_llama3_2_b200.ops.flash_attn import dropout_keep_mask
+
+    torch.manual_seed(D)
+    B, Hq, Hkv, S, p_drop, seed = 2, 4, 2, 320, 0.2, 987654321
+    q = (torch.randn(B, Hq, S, D, device="cuda") * 0.5).bfloat16().requires_grad_()
+    k = (torch.randn(B, Hkv, S, D, device="cuda") * 0.5).bfloat16().requires_grad_()
+    v = torch.randn(B, Hkv, S, D, device="cuda").bfloat16().requires_grad_()
+    do = torch.randn(B, Hq, S, D, device="cuda").bfloat16()
+    o = A.flash_attn_func(q, k, v, dropout_p=p_drop, causal=causal, seed=seed)
+    o.backward(do)
+    got = (o.detach().float(), q.grad.float(), k.grad.float(), v.grad.float())
+    qf, kf, vf = (t.detach().float().requires_grad_() for t in (q, k, v))
+    ref = A.attention_ref(qf, kf, vf, causal, None, p_drop, seed).float()
+    ref.backward(do.float())
+    want = (ref.detach(), qf.grad, kf.grad, vf.grad)
+    for name, a, b in zip(("o", "dq", "dk", "dv"), got, want):
+        rel = float((a - b).norm() / (b.norm() + 1e-12))
+        assert rel < 2e-2, (name, rel)
+    keep = dropout_keep_mask(seed, B, Hq, S, S, p_drop, device="cuda")
+    assert abs(float(keep.float().mean()) - (1 - p_drop)) < 5e-3
+    o2 = A.flash_attn_func(q.detach(), k.detach(), v.detach(), dropout_p=p_drop, causal=causal, seed=seed + 1)
+    assert float((o2.float() - o.detach().float()).abs().max()) > 1e-2      # another seed, another mask
+    o3 = A.flash_attn_func(q.detach(), k.detach(), v.detach(), dropout_p=p_drop, causal=causal, seed=seed)
+    assert torch.equal(o3, o.detach())
