@@ -31,10 +31,13 @@
 
 namespace nxd_gemm {
 
-template <int BN, bool A_MN, bool B_MN, int OUT_MODE>
+// GROUPED: `batches` independent problems of the same shape (the experts of an MoE layer) in ONE launch.  The tensor
+// maps are 3-D, the outermost coordinate is the problem index; a tile never mixes two problems because rows past M
+// are out of bounds of dimension 1 (zero-filled on load, clipped on store), so M needs no alignment.
+template <int BN, bool A_MN, bool B_MN, int OUT_MODE, bool GROUPED = false>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
 gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
-                 const __grid_constant__ CUtensorMap tmap_d, int M, int N, int K) {
+                 const __grid_constant__ CUtensorMap tmap_d, int M, int N, int K, int batches) {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     using L = SmemLayout<BN>;
     uint8_t* smem = ptx::align_smem_1024(smem_raw);
@@ -52,7 +55,8 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
 
     const int num_m_tiles = (M + kTileM - 1) / kTileM;
     const int num_n_tiles = (N + BN - 1) / BN;
-    const int num_tiles = num_m_tiles * num_n_tiles;
+    const int tiles_per_batch = num_m_tiles * num_n_tiles;
+    const int num_tiles = tiles_per_batch * (GROUPED ? batches : 1);
     const int num_k_blocks = (K + kBlockK - 1) / kBlockK;
     const int cluster_id = blockIdx.x >> 1;
     const int num_clusters = gridDim.x >> 1;
@@ -86,7 +90,8 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
             uint32_t phase = 0;
             for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
                 int tm, tn;
-                tile_coords(tile, num_m_tiles, num_n_tiles, tm, tn);
+                const int e = GROUPED ? tile / tiles_per_batch : 0;
+                tile_coords(GROUPED ? tile - e * tiles_per_batch : tile, num_m_tiles, num_n_tiles, tm, tn);
                 const int m0 = tm * kTileM + (int)cta_rank * kBlockM;
                 const int n0 = tn * BN + (int)cta_rank * (BN / 2);
                 for (int kb = 0; kb < num_k_blocks; ++kb) {
@@ -95,21 +100,21 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                     uint8_t* sb = sa + L::kABytes;
                     const int k0 = kb * kBlockK;
                     if (is_leader) ptx::mbar_arrive_expect_tx(&full_bar[stage], 2 * L::kStageBytes);
+                    auto load = [&](const CUtensorMap* map, void* dst, int c0, int c1) {
+                        if constexpr (GROUPED) ptx::tma_load_3d_pair(map, &full_bar[stage], dst, c0, c1, e);
+                        else ptx::tma_load_2d_pair(map, &full_bar[stage], dst, c0, c1);
+                    };
                     if constexpr (!A_MN) {
-                        ptx::tma_load_2d_pair(&tmap_a, &full_bar[stage], sa, k0, m0);
+                        load(&tmap_a, sa, k0, m0);
                     } else {
 #pragma unroll
-                        for (int g = 0; g < kBlockM / 64; ++g)
-                            ptx::tma_load_2d_pair(&tmap_a, &full_bar[stage], sa + g * (kBlockK * 128), m0 + g * 64,
-                                                  k0);
+                        for (int g = 0; g < kBlockM / 64; ++g) load(&tmap_a, sa + g * (kBlockK * 128), m0 + g * 64, k0);
                     }
                     if constexpr (!B_MN) {
-                        ptx::tma_load_2d_pair(&tmap_b, &full_bar[stage], sb, k0, n0);
+                        load(&tmap_b, sb, k0, n0);
                     } else {
 #pragma unroll
-                        for (int g = 0; g < (BN / 2) / 64; ++g)
-                            ptx::tma_load_2d_pair(&tmap_b, &full_bar[stage], sb + g * (kBlockK * 128), n0 + g * 64,
-                                                  k0);
+                        for (int g = 0; g < (BN / 2) / 64; ++g) load(&tmap_b, sb + g * (kBlockK * 128), n0 + g * 64, k0);
                     }
                     if (++stage == kStages) { stage = 0; phase ^= 1; }
                 }
@@ -162,7 +167,8 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         uint32_t acc_phase = 0;
         for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
             int tm, tn;
-            tile_coords(tile, num_m_tiles, num_n_tiles, tm, tn);
+            const int e = GROUPED ? tile / tiles_per_batch : 0;
+            tile_coords(GROUPED ? tile - e * tiles_per_batch : tile, num_m_tiles, num_n_tiles, tm, tn);
             const int row0 = tm * kTileM + (int)cta_rank * kBlockM + q * 32;
             const int n0 = tn * BN;
             ptx::mbar_wait(&tmem_full_bar[acc], acc_phase);
@@ -202,10 +208,16 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                 if (lane == 0) {
                     const int col0 = n0 + c * kCols;
                     if (col0 < N && row0 < M) {
-                        if constexpr (OUT_MODE == kOutF32Acc)
+                        if constexpr (GROUPED) {
+                            if constexpr (OUT_MODE == kOutF32Acc)
+                                ptx::tma_reduce_add_3d(&tmap_d, stg + buf * (32 * 128), col0, row0, e);
+                            else
+                                ptx::tma_store_3d(&tmap_d, stg + buf * (32 * 128), col0, row0, e);
+                        } else if constexpr (OUT_MODE == kOutF32Acc) {
                             ptx::tma_reduce_add_2d(&tmap_d, stg + buf * (32 * 128), col0, row0);
-                        else
+                        } else {
                             ptx::tma_store_2d(&tmap_d, stg + buf * (32 * 128), col0, row0);
+                        }
                     }
                     ptx::bulk_commit();
                 }
@@ -239,7 +251,7 @@ static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMa
     const int num_tiles = ((M + kTileM - 1) / kTileM) * ((N + BN - 1) / BN);
     int clusters = nxd_num_sms() / 2;
     if (clusters > num_tiles) clusters = num_tiles;
-    kern<<<dim3(clusters * 2), dim3(kThreads), L::kSmemBytes, stream>>>(ta, tb, td, M, N, K);
+    kern<<<dim3(clusters * 2), dim3(kThreads), L::kSmemBytes, stream>>>(ta, tb, td, M, N, K, 1);
     NXD_LAUNCH_CHECK();
     return 0;
 }
@@ -303,7 +315,84 @@ int run(int layout, const void* a, const void* b, long long lda, long long ldb, 
 #undef NXD_GEMM_DISPATCH
 }
 
+template <int BN, bool A_MN, bool B_MN, int OUT_MODE>
+static int launch_grouped(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& td, int E, int M, int N,
+                          int K, cudaStream_t stream) {
+    using L = SmemLayout<BN>;
+    auto kern = gemm_pair_kernel<BN, A_MN, B_MN, OUT_MODE, true>;
+    static bool configured = false;
+    if (!configured) {
+        NXD_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kSmemBytes));
+        configured = true;
+    }
+    const long num_tiles = (long)E * ((M + kTileM - 1) / kTileM) * ((N + BN - 1) / BN);
+    long clusters = nxd_num_sms() / 2;
+    if (clusters > num_tiles) clusters = num_tiles;
+    kern<<<dim3((unsigned)clusters * 2), dim3(kThreads), L::kSmemBytes, stream>>>(ta, tb, td, M, N, K, E);
+    NXD_LAUNCH_CHECK();
+    return 0;
+}
+
+// E problems D_e[M, N] (+)= A_e op B_e of one shape, operands stacked with strides sa / sb / sd (elements) between
+// problems.  The tile shape comes from the total tile count (E * tiles per problem), M needs no alignment.
+int run_grouped(int layout, const void* a, const void* b, long long lda, long long ldb, long long sa, long long sb,
+                const EpilogueArgs& ep, long long sd, int E, int M, int N, int K, cudaStream_t stream) {
+    NXD_REQUIRE(layout >= 0 && layout <= 2, "gemm_grouped: bad layout %d", layout);
+    NXD_REQUIRE(E > 0 && M > 0 && N > 0 && K > 0, "gemm_grouped: empty problem %d x %dx%dx%d", E, M, N, K);
+    NXD_REQUIRE(lda % 8 == 0 && ldb % 8 == 0 && ep.ldd % 8 == 0 && sa % 8 == 0 && sb % 8 == 0 && sd % 8 == 0,
+                "gemm_grouped: leading dims and problem strides must be multiples of 8 elements");
+    NXD_REQUIRE(N % 8 == 0, "gemm_grouped: N must be a multiple of 8");
+    NXD_REQUIRE(((uintptr_t)a & 15) == 0 && ((uintptr_t)b & 15) == 0 && ((uintptr_t)ep.d & 15) == 0,
+                "gemm_grouped: operands must be 16-byte aligned");
+    const bool a_mn = layout == kLayoutTN;
+    const bool b_mn = layout != kLayoutNT;
+    const int bn = pick_block_n(M * E, N);
+    CUtensorMap ta, tb, td;
+    int rc;
+    if (!a_mn) rc = make_tmap_3d(&ta, a, (uint64_t)K, (uint64_t)M, (uint64_t)E, (uint64_t)lda, (uint64_t)sa, 64, kBlockM);
+    else rc = make_tmap_3d(&ta, a, (uint64_t)M, (uint64_t)K, (uint64_t)E, (uint64_t)lda, (uint64_t)sa, 64, kBlockK);
+    if (rc) return rc;
+    if (!b_mn) rc = make_tmap_3d(&tb, b, (uint64_t)K, (uint64_t)N, (uint64_t)E, (uint64_t)ldb, (uint64_t)sb, 64, bn / 2);
+    else rc = make_tmap_3d(&tb, b, (uint64_t)N, (uint64_t)K, (uint64_t)E, (uint64_t)ldb, (uint64_t)sb, 64, kBlockK);
+    if (rc) return rc;
+    if (ep.mode == kOutBF16)
+        rc = make_tmap_3d(&td, ep.d, (uint64_t)N, (uint64_t)M, (uint64_t)E, (uint64_t)ep.ldd, (uint64_t)sd, 64, 32, 2);
+    else
+        rc = make_tmap_3d(&td, ep.d, (uint64_t)N, (uint64_t)M, (uint64_t)E, (uint64_t)ep.ldd, (uint64_t)sd, 32, 32, 4);
+    if (rc) return rc;
+#define NXD_GG_LAYOUT(BN_, MODE_)                                                                              \
+    switch (layout) {                                                                                          \
+        case kLayoutNT: return launch_grouped<BN_, false, false, MODE_>(ta, tb, td, E, M, N, K, stream);       \
+        case kLayoutNN: return launch_grouped<BN_, false, true, MODE_>(ta, tb, td, E, M, N, K, stream);        \
+        default: return launch_grouped<BN_, true, true, MODE_>(ta, tb, td, E, M, N, K, stream);                \
+    }
+#define NXD_GG_MODE(BN_)                                                          \
+    switch (ep.mode) {                                                            \
+        case kOutBF16: NXD_GG_LAYOUT(BN_, kOutBF16)                               \
+        case kOutF32: NXD_GG_LAYOUT(BN_, kOutF32)                                 \
+        case kOutF32Acc: NXD_GG_LAYOUT(BN_, kOutF32Acc)                           \
+        default: nxd_set_error("gemm_grouped: bad output mode %d", ep.mode); return -1; \
+    }
+    if (bn == 256) { NXD_GG_MODE(256) }
+    NXD_GG_MODE(128)
+#undef NXD_GG_MODE
+#undef NXD_GG_LAYOUT
+}
+
 }  // namespace nxd_gemm
+
+// Grouped (batched over experts) GEMM: E problems of one shape in ONE launch.  a / b / d point at problem 0, stride_*
+// are the element distances between consecutive problems; layouts, pitches and out_mode as nxd_gemm_bf16.
+NXD_API int nxd_gemm_grouped_bf16(int layout, const void* a, const void* b, void* d, int E, int M, int N, int K,
+                                  long long lda, long long ldb, long long ldd, long long stride_a, long long stride_b,
+                                  long long stride_d, int out_mode, void* stream) {
+    nxd_gemm::EpilogueArgs ep{};
+    ep.d = d;
+    ep.ldd = ldd;
+    ep.mode = out_mode;
+    return nxd_gemm::run_grouped(layout, a, b, lda, ldb, stride_a, stride_b, ep, stride_d, E, M, N, K,
+                                 (cudaStream_t)stream);
+}
 
 // C-ABI: layout 0 = nt, 1 = nn, 2 = tn (see header).  out_mode 0 = bf16, 1 = fp32, 2 = fp32 accumulate.
 // lda / ldb / ldd are row pitches in elements of the row-major operands as they sit in memory.

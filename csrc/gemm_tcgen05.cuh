@@ -55,6 +55,10 @@ __device__ __forceinline__ void tile_coords(int tile, int num_m_tiles, int num_n
 int make_tmap_2d(CUtensorMap* out, const void* base, uint64_t inner, uint64_t outer, uint64_t pitch_elems,
                  uint32_t box_inner, uint32_t box_outer, int elem_bytes = 2);
 
+// 3-D variant: `batch` stacked 2-D problems `batch_stride_elems` apart (coordinate 2 = problem index).
+int make_tmap_3d(CUtensorMap* out, const void* base, uint64_t inner, uint64_t outer, uint64_t batch, uint64_t pitch_elems,
+                 uint64_t batch_stride_elems, uint32_t box_inner, uint32_t box_outer, int elem_bytes = 2);
+
 int pick_block_n(int M, int N);
 
 int run(int layout, const void* a, const void* b, long long lda, long long ldb, const EpilogueArgs& ep, int M, int N,

@@ -43,4 +43,23 @@ int make_tmap_2d(CUtensorMap* out, const void* base, uint64_t inner, uint64_t ou
     return 0;
 }
 
+int make_tmap_3d(CUtensorMap* out, const void* base, uint64_t inner, uint64_t outer, uint64_t batch, uint64_t pitch_elems,
+                 uint64_t batch_stride_elems, uint32_t box_inner, uint32_t box_outer, int elem_bytes) {
+    auto encode = get_encode();
+    NXD_REQUIRE(encode != nullptr, "cuTensorMapEncodeTiled could not be resolved from the driver");
+    cuuint64_t dims[3] = {inner, outer, batch};
+    cuuint64_t strides[2] = {pitch_elems * (cuuint64_t)elem_bytes, batch_stride_elems * (cuuint64_t)elem_bytes};
+    if (batch == 1 && strides[1] < strides[0] * outer) strides[1] = strides[0] * outer;   // any legal value
+    cuuint32_t box[3] = {box_inner, box_outer, 1};
+    cuuint32_t estr[3] = {1, 1, 1};
+    CUresult r = encode(out, elem_bytes == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3,
+                        const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                        CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    NXD_REQUIRE(r == CUDA_SUCCESS,
+                "cuTensorMapEncodeTiled(3d) failed (%d): inner=%llu outer=%llu batch=%llu pitch=%llu stride=%llu box=%ux%u",
+                (int)r, (unsigned long long)inner, (unsigned long long)outer, (unsigned long long)batch,
+                (unsigned long long)pitch_elems, (unsigned long long)batch_stride_elems, box_inner, box_outer);
+    return 0;
+}
+
 }  // namespace nxd_gemm

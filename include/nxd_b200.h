@@ -211,6 +211,21 @@ int nxd_embedding_fwd_sp_push(const long long* ids, const void* weight, void* co
 int nxd_p2p_push_probe(int mode, const void* src, const void* const* dst_ptrs, int n_dst, size_t bytes, int ctas,
                        int chunk, int bufs, int read_lag, int sig_mode, int sig_every, size_t flag_off, void* stream);
 
+/* ---- MoE: grouped expert GEMM and token permutation (reference: modules/moe/moe_parallel_layers.py:78,94,108 einsum
+ *      over e; modules/moe/expert_mlps.py:183-265 gather by token_assignments / weighted scatter-combine) -------------
+ * E problems of one shape in one launch; stride_* = elements between consecutive problems; M needs no alignment. */
+int nxd_gemm_grouped_bf16(int layout, const void* a, const void* b, void* d, int E, int M, int N, int K, long long lda,
+                          long long ldb, long long ldd, long long stride_a, long long stride_b, long long stride_d,
+                          int out_mode, void* stream);
+/* out[r] = slot_token[r] >= 0 ? scale[r] * x[slot_token[r]] : 0   (scale NULL = 1) */
+int nxd_moe_gather(const void* x, const int* slot_token, const float* scale, void* out, long long slots, int H,
+                   void* stream);
+/* out[t] = sum_j w[t, j] * y[slot_of[t, j]]   (pairs with w == 0 are skipped) */
+int nxd_moe_combine(const void* y, const int* slot_of, const float* w, void* out, long long T, int k, int H, void* stream);
+/* dw[t, j] = kept[t, j] ? <dout[t], y[slot_of[t, j]]> : 0 */
+int nxd_moe_combine_dw(const void* y, const void* dout, const int* slot_of, const unsigned char* kept, float* dw,
+                       long long T, int k, int H, void* stream);
+
 /* Attention dropout (reference: nki_flash_attn_func(q, k, v, dropout_p, ..., seed), kernels/flash_attn.py:122-127,151-160).
  * Same arguments as the calls above plus dropout_p in [0, 1) and a seed; the keep mask is a hash of
  * (seed, batch, head, query, key), so the backward call regenerates it from the same two values. */

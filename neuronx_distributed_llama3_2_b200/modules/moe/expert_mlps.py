@@ -112,6 +112,18 @@ class ExpertMLPs(torch.nn.Module):
         kept = mask.gather(1, expert_index) > 0                                           # (T, k)
         slot = (position.gather(1, expert_index).long() - 1).clamp(min=0)                 # (T, k)
         flat_pos = expert_index * capacity + slot                                         # index into (E*C)
+        from ...ops import moe_permute
+
+        if moe_permute.usable(hidden_states):
+            # two kernels (+ the grouped expert GEMMs) instead of indexing chains: gather by token_assignments, weighted
+            # scatter-combine (csrc/moe_permute.cu); empty slots are zero rows, dropped pairs carry weight 0
+            slot_token = torch.full((E * capacity,), -1, dtype=torch.int32, device=hidden_states.device)
+            slot_token[flat_pos[kept]] = tok[kept].to(torch.int32)
+            slot_of = flat_pos.clamp(max=E * capacity - 1).to(torch.int32).contiguous()
+            aligned = moe_permute.dispatch(hidden_states, slot_token, slot_of, kept).reshape(E, capacity, H)
+            aligned_out = self.mlp_op(aligned).reshape(E * capacity, H)
+            w = aff.gather(1, expert_index) * kept
+            return moe_permute.combine(aligned_out, w, slot_of, slot_token, kept)
         # expert-aligned gather table; empty slots point at token 0 and are zeroed through the affinity
         assign = torch.zeros(E * capacity, dtype=torch.long, device=hidden_states.device)
         assign[flat_pos[kept]] = tok[kept]

@@ -28,33 +28,36 @@ def _use_tc(*ts: torch.Tensor) -> bool:
 
     if not all(t.is_cuda and t.dtype == torch.bfloat16 for t in ts) or gemm_ops._backend() != "tcgen05":
         return False
-    return all(d % 8 == 0 for t in ts for d in t.shape[-2:])
+    # only the contiguous (last) dims must be 16-byte multiples; row counts (the expert capacity) are free
+    return all(t.shape[-1] % 8 == 0 for t in ts) and _lib_ok()
+
+
+def _lib_ok() -> bool:
+    from ...ops import _lib
+
+    return _lib.available()
 
 
 def _grouped_mm(x: torch.Tensor, w: torch.Tensor, layout: str = "nn") -> torch.Tensor:
     """Per-expert GEMM.  ``nn``: ``(e, c, a) @ (e, a, b) -> (e, c, b)``; ``nt``: ``(e, c, b) @ (e, a, b)^T -> (e, c, a)``;
-    ``tn``: ``(e, c, a)^T @ (e, c, b) -> (e, a, b)``.  Extra leading dims of ``x`` are folded into ``c``."""
+    ``tn``: ``(e, c, a)^T @ (e, c, b) -> (e, a, b)``.  Extra leading dims of ``x`` are folded into ``c``.  On the GPU all
+    experts run in ONE grouped tcgen05 launch (``ops.gemm.gemm_grouped``; the reference contracts over ``e`` in one
+    einsum, ``moe_parallel_layers.py:78,94,108``); the capacity ``c`` needs no alignment."""
     e = x.shape[0]
     lead = x.shape[1:-1]
     x3 = x.reshape(e, -1, x.shape[-1])
     if layout == "tn":
         w3 = w.reshape(e, -1, w.shape[-1])
         if _use_tc(x3, w3):
-            from ...ops.gemm import gemm
+            from ...ops.gemm import gemm_grouped
 
-            y = torch.empty((e, x3.shape[2], w3.shape[2]), dtype=x.dtype, device=x.device)
-            for i in range(e):
-                gemm(x3[i], w3[i], "tn", out=y[i])
-            return y
+            return gemm_grouped(x3, w3, "tn")
         return torch.bmm(x3.transpose(1, 2), w3)
     n_out = w.shape[-1] if layout == "nn" else w.shape[-2]
-    if _use_tc(x3, w):
-        from ...ops.gemm import gemm
+    if _use_tc(x3, w) and n_out % 8 == 0:
+        from ...ops.gemm import gemm_grouped
 
-        x3 = x3.contiguous()
-        y = torch.empty((e, x3.shape[1], n_out), dtype=x.dtype, device=x.device)
-        for i in range(e):
-            gemm(x3[i], w[i], layout, out=y[i])
+        y = gemm_grouped(x3, w, layout)
     else:
         y = torch.bmm(x3, w if layout == "nn" else w.transpose(1, 2))
     return y.reshape((e,) + tuple(lead) + (n_out,))

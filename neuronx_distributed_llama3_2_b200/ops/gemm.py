@@ -51,3 +51,32 @@ def gemm(a: torch.Tensor, b: torch.Tensor, layout: str, out: Optional[torch.Tens
         _c.c_int(block_n), _lib.stream_ptr())
     _lib.check(rc, "nxd_gemm_bf16")
     return out
+
+
+def gemm_grouped(a: torch.Tensor, b: torch.Tensor, layout: str, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """``E`` GEMMs of one shape in ONE launch (``nxd_gemm_grouped_bf16``: 3-D tensor maps, the persistent tile loop runs
+    over every expert's tiles; rows past an expert's extent are out of bounds of the map, so the row count needs no
+    alignment).  ``a``/``b`` are 3-D bf16 with a unit inner stride:
+    ``nn``  ``a [E, M, K] @ b [E, K, N]``     ``nt``  ``a [E, M, K] @ b [E, N, K]^T``     ``tn``  ``a [E, K, M]^T @ b [E, K, N]``."""
+    assert a.dim() == 3 and b.dim() == 3 and a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16
+    if a.stride(2) != 1:
+        a = a.contiguous()
+    if b.stride(2) != 1:
+        b = b.contiguous()
+    E = a.shape[0]
+    if layout == "nt":
+        m, k, n = a.shape[1], a.shape[2], b.shape[1]
+    elif layout == "nn":
+        m, k, n = a.shape[1], a.shape[2], b.shape[2]
+    else:
+        k, m, n = a.shape[1], a.shape[2], b.shape[2]
+    if out is None:
+        out = torch.empty((E, m, n), dtype=torch.bfloat16, device=a.device)
+    assert out.shape == (E, m, n) and out.stride(2) == 1 and out.dtype == torch.bfloat16
+    rc = _lib.lib().nxd_gemm_grouped_bf16(
+        _c.c_int(_LAYOUT[layout]), _lib.ptr(a), _lib.ptr(b), _lib.ptr(out), _c.c_int(E), _c.c_int(m), _c.c_int(n),
+        _c.c_int(k), _c.c_longlong(a.stride(1)), _c.c_longlong(b.stride(1)), _c.c_longlong(out.stride(1)),
+        _c.c_longlong(a.stride(0)), _c.c_longlong(b.stride(0)), _c.c_longlong(out.stride(0)), _c.c_int(0),
+        _lib.stream_ptr())
+    _lib.check(rc, "nxd_gemm_grouped_bf16")
+    return out
