@@ -45,6 +45,10 @@ def parse_args():
     ap.add_argument("--seq-len", type=int, default=int(os.environ.get("NXD_BENCH_SEQ", 8192)))
     ap.add_argument("--micro-batch", type=int, default=int(os.environ.get("NXD_BENCH_MB", 1)))
     ap.add_argument("--layers", type=int, default=0, help="debug only: override the layer count (marks the run invalid)")
+    ap.add_argument("--tp", type=int, default=0, help="tensor-parallel degree (default: all GPUs, the headline layout)")
+    ap.add_argument("--pp", type=int, default=1, help="pipeline stages (BASELINE config #3 is --tp 4 --pp 2 --act-ckpt)")
+    ap.add_argument("--microbatches", type=int, default=4, help="micro-batches per step when --pp > 1")
+    ap.add_argument("--act-ckpt", action="store_true", help="full activation checkpointing per decoder layer")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-baseline", action="store_true",
                     help="skip the library arm (cuBLAS + SDPA + NCCL) that normally runs after ours in the same job")
@@ -230,41 +234,59 @@ def train_arm(args, arm, arm_name, dev, world, rank, local_rank):
     from neuronx_distributed_llama3_2_b200.ops import _lib, backend
     from neuronx_distributed_llama3_2_b200.parallel.random import model_parallel_manual_seed
 
-    tp = world
+    tp, pp = (args.tp or world // args.pp), args.pp
+    assert world % (tp * pp) == 0, f"world {world} is not a multiple of tp {tp} x pp {pp}"
+    dp = world // (tp * pp)
     cfg = PRESETS[args.model](sequence_parallel_enabled=tp > 1)
     if args.layers:
         cfg.num_hidden_layers = args.layers
     prev = backend.set_backends(**arm)
     backend.reset_fallback_counts()
+    extra = {}
+    if pp > 1:
+        from neuronx_distributed_llama3_2_b200.models.llama import LlamaDecoderLayer
+
+        extra["pipeline_parallel_size"] = pp
+        extra["pipeline_config"] = {"transformer_layer_cls": LlamaDecoderLayer, "num_microbatches": args.microbatches,
+                                    "auto_partition": True, "input_names": ["input_ids", "labels"],
+                                    "broadcast_and_average_loss": True}
+    if args.act_ckpt:
+        extra["activation_checkpoint_config"] = "full"
     nxd_cfg = nxd.neuronx_distributed_config(
         tensor_parallel_size=tp, sequence_parallel=tp > 1,
         optimizer_config={"zero_one_enabled": True, "grad_clipping": True, "max_grad_norm": 1.0},
         mixed_precision_config={"use_master_weights": True, "use_fp32_grad_acc": False,
-                                "use_master_weights_in_ckpt": False})
+                                "use_master_weights_in_ckpt": False}, **extra)
     model_parallel_manual_seed(1234)
     model = nxd.initialize_parallel_model(nxd_cfg, lambda: LlamaForCausalLM(cfg, device=dev), device=dev)
     model.train()
     opt = nxd.initialize_parallel_optimizer(nxd_cfg, torch.optim.AdamW, model.parameters(), lr=3e-4,
                                             betas=(0.9, 0.95), weight_decay=0.1)
 
-    B, S = args.micro_batch, args.seq_len
+    from neuronx_distributed_llama3_2_b200.parallel import parallel_state as ps
+
+    # per-rank batch: micro_batch sequences (x micro-batches under PP); every DP replica draws its own data
+    B, S = args.micro_batch * (args.microbatches if pp > 1 else 1), args.seq_len
     n_batches = 4
-    g = torch.Generator().manual_seed(99)
+    g = torch.Generator().manual_seed(99 + (ps.get_data_parallel_rank() if dp > 1 else 0))
     host = [torch.randint(0, cfg.vocab_size, (B, S), generator=g).pin_memory() for _ in range(n_batches)]
     dev_batches = [h.to(dev) for h in host]
     loss_host = torch.zeros(1, dtype=torch.float32).pin_memory()
 
+    def run(ids):
+        return model.run_train(input_ids=ids, labels=ids) if pp > 1 else model.run_train(ids, labels=ids)
+
     def step_dev(i):
         ids = dev_batches[i % n_batches]
         opt.zero_grad()
-        loss = model.run_train(ids, labels=ids)
+        loss = run(ids)
         opt.step()
         return loss
 
     def step_e2e(i):
         ids = host[i % n_batches].to(dev, non_blocking=True)     # H2D of this step's batch from pinned memory
         opt.zero_grad()
-        loss = model.run_train(ids, labels=ids)
+        loss = run(ids)
         opt.step()
         loss_host.copy_(loss.detach().float().reshape(1), non_blocking=True)  # D2H read of the step result
         torch.cuda.current_stream().synchronize()
@@ -307,8 +329,8 @@ def train_arm(args, arm, arm_name, dev, world, rank, local_rank):
         return None
     torch.cuda.reset_peak_memory_stats(dev)
     ms, launches, clocks, last_loss = timed(step_dev, args.steps)
-    tokens = B * S * args.steps
-    res = {"arm": arm_name, "backends": backend.describe(), "value": tokens / (ms / 1e3), "ms_per_step": ms / args.steps,
+    tokens = B * S * dp * args.steps
+    res = {"arm": arm_name, "layout": {"tp": tp, "pp": pp, "dp": dp, "global_batch": B * dp}, "backends": backend.describe(), "value": tokens / (ms / 1e3), "ms_per_step": ms / args.steps,
            "first_step_loss": first_loss, "first_step_grad_norm": first_norm,
            "loss": float(last_loss.detach()) if isinstance(last_loss, torch.Tensor) else last_loss,
            "clocks": clocks, "gpu_launches": int(launches), "cfg": cfg,
@@ -320,13 +342,22 @@ def train_arm(args, arm, arm_name, dev, world, rank, local_rank):
                       "h2d_bytes_per_step": B * S * 8, "d2h_bytes_per_step": 4}
     res["fallbacks"] = backend.fallback_counts()
     fused_check = None
-    if world > 1 and arm.get("fused_comm"):
-        fused_check = fused_numerics_probe(cfg, dev, world, S * B)
+    if tp == world and world > 1 and arm.get("fused_comm"):
+        fused_check = fused_numerics_probe(cfg, dev, world, S * args.micro_batch)
     res["fused_check"] = fused_check
     del model, opt, dev_batches
     torch.cuda.empty_cache()
     backend.set_backends(**prev)
     return res
+
+
+def _layout_name(l):
+    name = f"tp{l['tp']}" + ("+sp" if l["tp"] > 1 else "")
+    if l["pp"] > 1:
+        name += f" x pp{l['pp']}"
+    if l["dp"] > 1:
+        name += f" x dp{l['dp']} (zero1)"
+    return name
 
 
 def fused_numerics_probe(cfg, dev, world, tokens):
@@ -388,7 +419,7 @@ def main():
 
     assert _lib.available(), "kernel library must be loadable on the GPU box"
     t_start = time.time()
-    B, S, tp = args.micro_batch, args.seq_len, world
+    S = args.seq_len
     # --impl baseline: the library arm alone (cuBLAS + SDPA + NCCL with the same layers)
     main_arm = backend.LIBRARY_ARM if args.impl == "baseline" else backend.NATIVE_ARM
     ours = train_arm(args, main_arm, "library" if args.impl == "baseline" else "native", dev, world, rank, local_rank)
@@ -420,7 +451,8 @@ def main():
             # the comparison arm: cuBLAS + SDPA + NCCL with the same layers, measured in THIS job right after ours.
             "vs_baseline": (value / lib_arm["value"]) if lib_arm else None,
             "dtype": "bf16", "data": "synthetic token ids, random-init weights",
-            "config": {"model": args.model, "global_batch": B, "seq_len": S, "parallelism": f"tp{tp}+sp" if tp > 1 else "tp1",
+            "config": {"model": args.model, "global_batch": ours["layout"]["global_batch"], "seq_len": S,
+                       "parallelism": _layout_name(ours["layout"]), "activation_checkpointing": bool(args.act_ckpt),
                        "layers": cfg.num_hidden_layers, "zero1": True, "optimizer": "AdamW fp32 master",
                        "grad_clip": 1.0, "l2": "working set (6.4 GB weights + activations) >> 126 MB L2; no flush needed",
                        "gemm_backend": ours["backends"]["gemm"], "attn_backend": ours["backends"]["attn"],

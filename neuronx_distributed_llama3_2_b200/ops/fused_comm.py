@@ -48,6 +48,25 @@ def dump_traces(limit: int = 6):  # noqa: D401
     return out
 
 
+def _ag_block_n(tp: int, R: int, N: int, comm_ctas: int) -> int:
+    """Tile width of the AG->GEMM kernel: 256-wide tiles re-use operands best, but with few output columns per rank
+    (qkv at TP8: N = 640) they leave a ragged last wave on the clusters that are not copy engines.  Same cost model as
+    ``pick_block_n`` in csrc/gemm_tcgen05.cu; ``NXD_AG_BLOCK_N`` overrides."""
+    env = os.environ.get("NXD_AG_BLOCK_N")
+    if env:
+        return int(env)
+    sms = 148
+    try:
+        sms = int(_lib.lib().nxd_device_sm_count())
+    except Exception:  # noqa: BLE001
+        pass
+    clusters = max(1, (sms - comm_ctas) // 2)
+    mt = (tp * R + 255) // 256
+    t256, t128 = mt * ((N + 255) // 256), mt * ((N + 127) // 128)
+    w256, w128 = -(-t256 // clusters), -(-t128 // clusters)
+    return 256 if w256 * 100 <= w128 * 55 else 128
+
+
 def _host_ptrs(ctx, table: torch.Tensor, offset: int):
     return (_c.c_void_p * ctx.world)(*[p + offset for p in table.tolist()])
 
@@ -101,8 +120,8 @@ def fused_ag_gemm(ctx, x_shard: torch.Tensor, weight: torch.Tensor, layout: str 
     rc = _lib.lib().nxd_ag_gemm_bf16(
         _c.c_int(_LAYOUT[layout]), _lib.ptr(x_shard), _lib.ptr(weight), _lib.ptr(y), _c.c_int(R), _c.c_int(N),
         _c.c_int(K), _c.c_longlong(weight.stride(0)), _c.c_longlong(y.stride(0)), xt_ptrs, s["sigs"], _c.c_int(tp),
-        _c.c_int(ctx.rank), _c.c_int(s["chunks"]), _c.c_uint(epoch), _c.c_int(comm_ctas), _c.c_int(0), _lib.ptr(trace),
-        _lib.stream_ptr())
+        _c.c_int(ctx.rank), _c.c_int(s["chunks"]), _c.c_uint(epoch), _c.c_int(comm_ctas),
+        _c.c_int(_ag_block_n(tp, R, N, comm_ctas)), _lib.ptr(trace), _lib.stream_ptr())
     _lib.check(rc, "nxd_ag_gemm_bf16")
     return y, (x_total.clone() if persistent_total else x_total)
 

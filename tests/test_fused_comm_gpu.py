@@ -69,7 +69,9 @@ def case_ag_gemm(rank, world):
         x = torch.randn(R, K, device="cuda", generator=g).bfloat16()
         gw = torch.Generator(device="cuda").manual_seed(7 + it)
         w = torch.randn((N, K) if layout == "nt" else (K, N), device="cuda", generator=gw).bfloat16()
+        os.environ["NXD_AG_BLOCK_N"] = ("128", "256")[it % 2]      # both tile widths (the default is a wave heuristic)
         res = fused_ag_gemm(ctx, x, w, layout)
+        os.environ.pop("NXD_AG_BLOCK_N")
         assert res is not None
         y, x_total = res
         ref_total = torch.empty(world * R, K, device="cuda", dtype=torch.bfloat16)
@@ -339,20 +341,28 @@ def test_flag_protocol_stress():
     spawn_gpu_workers(_worker, (world, _free_port(), "case_flag_protocol_stress"), world, deadline_s=300.0)
 
 
-def test_fused_ag_gemm_tp2():
-    _spawn("case_ag_gemm", 2)
+# every protocol at world 2, 4 and 8 (7 peers, all copy CTAs): skipped where the box has fewer GPUs
+_WORLDS = [2, 4, 8]
 
 
-def test_fused_gemm_rs_tp2():
-    _spawn("case_gemm_rs", 2)
+@pytest.mark.parametrize("world", _WORLDS)
+def test_fused_ag_gemm(world):
+    _spawn("case_ag_gemm", world)
 
 
-def test_fused_gemm_ar_tp2():
-    _spawn("case_gemm_ar", 2)
+@pytest.mark.parametrize("world", _WORLDS)
+def test_fused_gemm_rs(world):
+    _spawn("case_gemm_rs", world)
 
 
-def test_sp_embedding_push_tp2():
-    _spawn("case_sp_embedding", 2)
+@pytest.mark.parametrize("world", _WORLDS)
+def test_fused_gemm_ar(world):
+    _spawn("case_gemm_ar", world)
+
+
+@pytest.mark.parametrize("world", _WORLDS)
+def test_sp_embedding_push(world):
+    _spawn("case_sp_embedding", world)
 
 
 def test_zero1_fused_step_dp2():
