@@ -46,7 +46,7 @@ struct AgArgs {
     // only), a slab holds R / expert_rows experts and expert e multiplies weight rows [e * w_expert_stride, ...)
     int expert_rows;              // 0 = all-gather mode
     int w_expert_stride;
-    // NVLS (EXPERIMENTAL, not yet run on hardware): multicast address of X_total for this call.  One multimem.st reaches
+    // NVLS (run at 2 and 8 GPUs): multicast address of X_total for this call.  One multimem.st reaches
     // every rank's copy through the switch, so 1/tp of the bytes leave the GPU compared with the per-peer pushes.
     bf16* mc_total;               // nullptr = per-peer TMA pushes
 };

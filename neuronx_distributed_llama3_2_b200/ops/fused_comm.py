@@ -49,22 +49,12 @@ def dump_traces(limit: int = 6):  # noqa: D401
 
 
 def _ag_block_n(tp: int, R: int, N: int, comm_ctas: int) -> int:
-    """Tile width of the AG->GEMM kernel: 256-wide tiles re-use operands best, but with few output columns per rank
-    (qkv at TP8: N = 640) they leave a ragged last wave on the clusters that are not copy engines.  Same cost model as
-    ``pick_block_n`` in csrc/gemm_tcgen05.cu; ``NXD_AG_BLOCK_N`` overrides."""
+    """Tile width of the AG->GEMM kernel.  256 everywhere: at TP8 the 128-wide tiles were tried for the narrow
+    projections (a wave-count model picked them for qkv N = 640 and gate_up N = 2048) and lost -- 123 vs 115 us and
+    171 vs 131 us (``profiles/r2/fused_comm_tp8_bn*.jsonl``): the kernel is bound by the gather, and narrower tiles only
+    add B-operand traffic.  ``NXD_AG_BLOCK_N=128`` keeps the variant reachable (the tests run both)."""
     env = os.environ.get("NXD_AG_BLOCK_N")
-    if env:
-        return int(env)
-    sms = 148
-    try:
-        sms = int(_lib.lib().nxd_device_sm_count())
-    except Exception:  # noqa: BLE001
-        pass
-    clusters = max(1, (sms - comm_ctas) // 2)
-    mt = (tp * R + 255) // 256
-    t256, t128 = mt * ((N + 255) // 256), mt * ((N + 127) // 128)
-    w256, w128 = -(-t256 // clusters), -(-t128 // clusters)
-    return 256 if w256 * 100 <= w128 * 55 else 128
+    return int(env) if env else 256
 
 
 def _host_ptrs(ctx, table: torch.Tensor, offset: int):
@@ -89,7 +79,11 @@ def fused_ag_gemm(ctx, x_shard: torch.Tensor, weight: torch.Tensor, layout: str 
     # counters / buffers are per configuration: the counters accumulate a fixed amount per call
     cfg = f"ag:{R}:{K}:{comm_ctas}"
     mc_base = 0
-    if os.environ.get("NXD_NVLS", "0") == "1":            # EXPERIMENTAL: multicast stores through the switch
+    # NVLS: the copy CTAs store the local shard ONCE to the multicast address of the gathered buffer (multimem.st, the
+    # switch replicates it) instead of once per peer.  Verified at 2 and 8 GPUs; TP8 step 55.8 -> 53.2 ms
+    # (profiles/r2/bench_tp8_nvls.json).  Falls back to per-peer pushes where no multicast object can be bound.
+    nvls = os.environ.get("NXD_NVLS")          # unset: on for tp > 2 (one peer gains nothing); "1": always; "0": never
+    if nvls == "1" or (nvls is None and tp > 2):
         got = ctx.region_mc(cfg, 2 * total_bytes)
         if got is not None:
             local_ptr, table, mc_base = got

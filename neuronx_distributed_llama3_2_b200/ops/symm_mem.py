@@ -73,14 +73,15 @@ class SymmMemContext:
         return local, table
 
     def region_mc(self, name: str, nbytes: int):
-        """EXPERIMENTAL (not yet run on hardware): a symmetric region that also has an NVLS MULTICAST address, allocated
-        and exchanged by ``torch.distributed._symmetric_memory`` (cuMem + cuMulticast under the hood; CUDA IPC memory from
+        """A symmetric region that also has an NVLS MULTICAST address (run at 2 and 8 GPUs), allocated and exchanged by ``torch.distributed._symmetric_memory`` (cuMem + cuMulticast under the hood; CUDA IPC memory from
         ``region`` cannot be bound to a multicast object).  Returns ``(local_ptr, peer_ptr_table, multicast_ptr)`` or
         ``None`` when the platform / group has no multicast support."""
         key = "mc:" + name
         cur = self._regions.get(key)
         if cur is not None and cur[2] >= nbytes:
             return cur[0], cur[3], cur[4]
+        if getattr(self, "_mc_unavailable", False):     # asked once, answered once: do not retry on every call
+            return None
         try:
             import torch.distributed._symmetric_memory as tsm
 
@@ -89,6 +90,7 @@ class SymmMemContext:
             hdl = tsm.rendezvous(buf, self.group)
             mc = int(getattr(hdl, "multicast_ptr", 0) or 0)
             if not mc:
+                self._mc_unavailable = True
                 return None
             peers = [int(p) for p in hdl.buffer_ptrs]
             table = torch.tensor(peers, dtype=torch.int64, device=self.device)
@@ -101,6 +103,7 @@ class SymmMemContext:
             from ..utils.logger import get_logger
 
             get_logger().warning("NVLS multicast region unavailable (%s): using per-peer pushes", e)
+            self._mc_unavailable = True
             return None
 
     def tensor_view(self, ptr: int, shape, dtype: torch.dtype) -> torch.Tensor:
