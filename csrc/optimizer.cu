@@ -19,12 +19,46 @@ __device__ __forceinline__ float to_f<float>(float v) { return v; }
 template <>
 __device__ __forceinline__ float to_f<bf16>(bf16 v) { return __bfloat162float(v); }
 
+// 16-byte loads over the aligned middle of the range (two in flight per thread), scalars for the unaligned head and the
+// tail: the scalar-only version read the 6.4 GB bf16 gradient buffer of the 3B model at 1.2 TB/s (5.2 ms per step).
 template <typename T>
 __global__ void sumsq_partial_kernel(const T* __restrict__ x, size_t n, float* __restrict__ partial) {
     __shared__ float red[32];
-    float acc = 0.f;
-    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
-        const float v = to_f<T>(x[i]);
+    constexpr size_t kPer = 16 / sizeof(T);                       // elements per 16-byte vector
+    const size_t tid = (size_t)blockIdx.x * blockDim.x + threadIdx.x, nthr = (size_t)gridDim.x * blockDim.x;
+    size_t head = ((16 - (reinterpret_cast<uintptr_t>(x) & 15)) & 15) / sizeof(T);
+    if (head > n) head = n;
+    const size_t nvec = (n - head) / kPer;
+    const uint4* xv = reinterpret_cast<const uint4*>(x + head);
+    float acc = 0.f, acc2 = 0.f;
+    auto add_vec = [](const uint4& v, float a) {
+        if constexpr (sizeof(T) == 4) {
+            const float* f = reinterpret_cast<const float*>(&v);
+            return a + f[0] * f[0] + f[1] * f[1] + f[2] * f[2] + f[3] * f[3];
+        } else {
+            const bf162* h = reinterpret_cast<const bf162*>(&v);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const float2 f = __bfloat1622float2(h[i]);
+                a = fmaf(f.x, f.x, fmaf(f.y, f.y, a));
+            }
+            return a;
+        }
+    };
+    size_t i = tid;
+    for (; i + nthr < nvec; i += 2 * nthr) {
+        const uint4 a = xv[i], b = xv[i + nthr];
+        acc = add_vec(a, acc);
+        acc2 = add_vec(b, acc2);
+    }
+    if (i < nvec) acc = add_vec(xv[i], acc);
+    acc += acc2;
+    for (size_t j = tid; j < head; j += nthr) {
+        const float v = to_f<T>(x[j]);
+        acc += v * v;
+    }
+    for (size_t j = head + nvec * kPer + tid; j < n; j += nthr) {
+        const float v = to_f<T>(x[j]);
         acc += v * v;
     }
     acc = block_sum(acc, red);
@@ -56,7 +90,54 @@ __global__ void adamw_kernel(float* __restrict__ master, float* __restrict__ m, 
                              float beta1, float beta2, float eps, float wd, float bc1, float bc2,
                              float grad_scale, const float* __restrict__ clip_coef) {
     const float scale = grad_scale * (clip_coef ? clip_coef[0] : 1.f);
-    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    const size_t tid = (size_t)blockIdx.x * blockDim.x + threadIdx.x, nthr = (size_t)gridDim.x * blockDim.x;
+    size_t done = 0;
+    // four elements per thread and step through 16-byte (fp32 state) / 8-byte (bf16 grad, param) accesses when every
+    // array is aligned for it; the scalar loop below takes what is left
+    const bool aligned = ((reinterpret_cast<uintptr_t>(master) | reinterpret_cast<uintptr_t>(m) |
+                           reinterpret_cast<uintptr_t>(v)) & 15) == 0 &&
+                         (reinterpret_cast<uintptr_t>(grad) & (4 * sizeof(G) - 1)) == 0 &&
+                         (param_out == nullptr || (reinterpret_cast<uintptr_t>(param_out) & 7) == 0);
+    if (aligned) {
+        const size_t n4 = n / 4;
+        const float omw = 1.f - lr * wd, ib1 = 1.f / bc1, ib2 = 1.f / bc2;
+        for (size_t i = tid; i < n4; i += nthr) {
+            float4 mi = reinterpret_cast<float4*>(m)[i], vi = reinterpret_cast<float4*>(v)[i];
+            float4 p = reinterpret_cast<float4*>(master)[i];
+            float g[4];
+            if constexpr (sizeof(G) == 4) {
+                const float4 gv = reinterpret_cast<const float4*>(grad)[i];
+                g[0] = gv.x; g[1] = gv.y; g[2] = gv.z; g[3] = gv.w;
+            } else {
+                const uint2 gv = reinterpret_cast<const uint2*>(grad)[i];
+                const float2 a = __bfloat1622float2(*reinterpret_cast<const bf162*>(&gv.x));
+                const float2 b = __bfloat1622float2(*reinterpret_cast<const bf162*>(&gv.y));
+                g[0] = a.x; g[1] = a.y; g[2] = b.x; g[3] = b.y;
+            }
+            float* mp = reinterpret_cast<float*>(&mi);
+            float* vp = reinterpret_cast<float*>(&vi);
+            float* pp = reinterpret_cast<float*>(&p);
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                const float ge = g[e] * scale;
+                mp[e] = beta1 * mp[e] + (1.f - beta1) * ge;
+                vp[e] = beta2 * vp[e] + (1.f - beta2) * ge * ge;
+                pp[e] = pp[e] * omw - lr * (mp[e] * ib1) / (sqrtf(vp[e] * ib2) + eps);
+            }
+            reinterpret_cast<float4*>(m)[i] = mi;
+            reinterpret_cast<float4*>(v)[i] = vi;
+            reinterpret_cast<float4*>(master)[i] = p;
+            if (param_out) {
+                bf162 lo = __floats2bfloat162_rn(pp[0], pp[1]), hi = __floats2bfloat162_rn(pp[2], pp[3]);
+                uint2 o;
+                o.x = *reinterpret_cast<uint32_t*>(&lo);
+                o.y = *reinterpret_cast<uint32_t*>(&hi);
+                reinterpret_cast<uint2*>(param_out)[i] = o;
+            }
+        }
+        done = n4 * 4;
+    }
+    for (size_t i = done + tid; i < n; i += nthr) {
         const float g = to_f<G>(grad[i]) * scale;
         float mi = m[i], vi = v[i], p = master[i];
         mi = beta1 * mi + (1.f - beta1) * g;
