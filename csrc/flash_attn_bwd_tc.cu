@@ -23,7 +23,7 @@
 // finite garbage that nobody reads -- cheaper than a second code path for the M = 64 TMEM layout.
 //
 // warp 0: TMA producer (K, V once; Q_i, dO_i, L_i, Delta_i through a 3-stage ring)   warp 1: TMEM alloc + MMA issue
-// warps 2-9: softmax-backward math, dQ drain, epilogue.  Two math warps share every TMEM lane quadrant (warp % 4) and
+// warps 2-9: softmax-backward math, epilogue.  warps 10-13: dQ^T drain (TMEM -> smem -> TMA reduce-add).  Two math warps share every TMEM lane quadrant (warp % 4) and
 // split the 64 query columns of a tile between them: half the serial work per warp and twice the warps to hide the
 // TMEM-load / exp2 / shared-store latencies behind (the 4-warp version ran one warp per SM sub-partition and was
 // latency bound); in the epilogue one half stores dV while the other stores dK.
@@ -38,8 +38,10 @@ using namespace nxd_attn;
 
 constexpr int kBN = 128;  // K/V rows per CTA
 constexpr int kBM = 64;   // query rows per tile
-constexpr int kThreadsBwd = 320;      // TMA warp + MMA warp + 8 math warps
+constexpr int kThreadsBwd = 448;      // TMA warp + MMA warp + 8 math warps + 4 dQ drain warps
 constexpr int kMathThreads = 256;
+constexpr int kDrainThreads = 128;
+constexpr int kFirstDrainWarp = 10;
 constexpr int kQStages = 3;          // Q_i / dO_i / L_i / Delta_i ring: a tile is requested one full iteration before its MMAs
 
 struct BwdParams {
@@ -81,6 +83,9 @@ fa_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
                  const __grid_constant__ CUtensorMap tmap_dv_acc, const BwdParams p) {
     using L = BwdSmem<kD>;
     constexpr uint32_t kColDK = 0, kColDV = kD, kColST = 2 * kD, kColDPT = 2 * kD + 64, kColDQT = 2 * kD + 128;
+    // bf16 P^T and dS^T as TENSOR-MEMORY A operands of the dV / dK MMAs: 128 lanes x 64 q = 32 packed columns each
+    constexpr uint32_t kColPT = 2 * kD + 192, kColDST = kColPT + 32;
+    static_assert(kColDST + 32 <= 512, "tensor memory budget");
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     uint8_t* smem = align_smem_1024(smem_raw);
     uint8_t* sK = smem + L::kKOff;
@@ -104,7 +109,9 @@ fa_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
     uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bars + L::kNumBars);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int nbk = blockIdx.x, hkv = blockIdx.y / p.nsplit, split = blockIdx.y % p.nsplit, b = blockIdx.z;
+    // grid = (kv heads x splits, batch, K/V blocks): the block index is the SLOWEST launch dimension, so with a causal mask
+    // the CTAs are handed to the SMs longest first (K/V block 0 meets every query tile, the last one only two)
+    const int nbk = blockIdx.z, hkv = blockIdx.x / p.nsplit, split = blockIdx.x % p.nsplit, b = blockIdx.y;
     const int group = p.Hq / p.Hkv;
     const int n0 = nbk * kBN;
     const int offset = p.Sk - p.Sq;
@@ -134,7 +141,7 @@ fa_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
         ptx::mbar_init(pds_full, kMathThreads);
         ptx::mbar_init(pds_empty, 1);
         ptx::mbar_init(dq_full, 1);
-        ptx::mbar_init(dq_empty, kMathThreads);
+        ptx::mbar_init(dq_empty, kDrainThreads);
         ptx::fence_barrier_init();
     }
     if (warp == 1) ptx::tmem_alloc<1>(tmem_ptr_smem, 512);
@@ -219,13 +226,13 @@ fa_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
                 // dV += P^T dO ; dK += dS^T Q      (contraction over the 64 q rows: 4 MMAs of K = 16 each)
 #pragma unroll
                 for (int kk = 0; kk < kBM / 16; ++kk) {
-                    ptx::umma_bf16<1>(tmem_base + kColDV, ptx::make_smem_desc(pt_addr + kk * 32, 16, 1024),
+                    ptx::umma_bf16_ts(tmem_base + kColDV, tmem_base + kColPT + kk * 8,
                                       ptx::make_smem_desc(dob + kk * 2048, kBM * 128, 1024), idesc_kv,
                                       (it | kk) != 0 ? 1u : 0u);
                 }
 #pragma unroll
                 for (int kk = 0; kk < kBM / 16; ++kk) {
-                    ptx::umma_bf16<1>(tmem_base + kColDK, ptx::make_smem_desc(dst_addr + kk * 32, 16, 1024),
+                    ptx::umma_bf16_ts(tmem_base + kColDK, tmem_base + kColDST + kk * 8,
                                       ptx::make_smem_desc(qb + kk * 2048, kBM * 128, 1024), idesc_kv,
                                       (it | kk) != 0 ? 1u : 0u);
                 }
@@ -243,53 +250,64 @@ fa_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
                 ptx::umma_commit(dq_full);
             }
         }
+    } else if (warp >= kFirstDrainWarp) {
+        // ============================ dQ drain ============================
+        // dQ^T(it) [d = TMEM lane][64 q] -> this warp's staging rows (no transpose: the fp32 dQ accumulator in global
+        // memory is d-major) -> TMA reduce-add, 32 q columns per box.  Its own warps: the softmax warps never wait for
+        // the staging fence, and the tensor core gets its dQ^T columns back as soon as they are in registers.  No
+        // CTA-wide barrier: staging buffers, bulk groups and the waits on them are private to the warp.
+        const int q4 = warp & 3;                 // TMEM lane quadrant this warp may access
+        const uint32_t lane_off = (uint32_t)(q4 * 32) << 16;
+        const bool has_rows = q4 * 32 < kD;      // head dim 64: TMEM lanes 64..127 of dQ^T are padding
+        uint8_t* stage = sDQ + q4 * 8192;        // two 32 x 32 fp32 boxes (4 KB each) of this warp
+        int th = it0 % tiles_per_head, hq = hkv * group + it0 / tiles_per_head;
+        for (int it = 0; it < total; ++it) {
+            const int m0 = (mb_start + th) * kBM;
+            ptx::mbar_wait(dq_full, (uint32_t)it & 1u);
+            ptx::tcgen05_fence_after();
+            uint32_t v[64];
+            if (has_rows) {
+                ptx::tmem_ld_32x32b_x32(tmem_base + kColDQT + lane_off, v);
+                ptx::tmem_ld_32x32b_x32(tmem_base + kColDQT + lane_off + 32, v + 32);
+                ptx::tmem_ld_wait();
+            }
+            ptx::tcgen05_fence_before();
+            ptx::mbar_arrive(dq_empty);
+            if (has_rows) {
+                if (lane == 0) ptx::bulk_wait_read<0>();     // the previous reduce-adds have read the staging rows
+                __syncwarp();
+#pragma unroll
+                for (int h2 = 0; h2 < 2; ++h2) {
+                    uint8_t* dst = stage + h2 * 4096 + lane * 128;
+#pragma unroll
+                    for (int c = 0; c < 8; ++c)
+                        st_shared_v4(dst + ((c ^ (lane & 7)) << 4),
+                                     __float_as_uint(__uint_as_float(v[h2 * 32 + 4 * c]) * p.scale),
+                                     __float_as_uint(__uint_as_float(v[h2 * 32 + 4 * c + 1]) * p.scale),
+                                     __float_as_uint(__uint_as_float(v[h2 * 32 + 4 * c + 2]) * p.scale),
+                                     __float_as_uint(__uint_as_float(v[h2 * 32 + 4 * c + 3]) * p.scale));
+                }
+                ptx::fence_proxy_async();
+                __syncwarp();
+                if (lane == 0) {
+                    int c[4];
+                    coords(p.pos_dq, q4 * 32, hq, b, c);
+                    tma_reduce_add_4d(&tmap_dq, stage, m0, c[1], c[2], c[3]);
+                    tma_reduce_add_4d(&tmap_dq, stage + 4096, m0 + 32, c[1], c[2], c[3]);
+                    ptx::bulk_commit();
+                }
+            }
+            if (++th == tiles_per_head) { th = 0; ++hq; }
+        }
+        if (lane == 0) ptx::bulk_wait<0>();
     } else {
-        // ============================ softmax backward / dQ drain / epilogue ============================
+        // ============================ softmax backward / epilogue ============================
         const int q4 = warp & 3;
         const int row = q4 * 32 + lane;         // K/V row inside the tile == TMEM lane (and d index for dQ^T)
         const int krow = n0 + row;
         const uint32_t lane_off = (uint32_t)(q4 * 32) << 16;
         const int half = (warp - 2) >> 2;        // which 32 of the 64 query columns this warp handles
         const int c0h = half * 32;
-        const bool has_rows = q4 * 32 < kD;      // head dim 64: TMEM lanes 64..127 of dQ^T are padding
-        // dQ^T staging of THIS warp: 32 d rows x 32 q columns fp32 = 32 swizzled 128-byte rows (one TMA box)
-        uint8_t* dq_stage = sDQ + (half * (kD / 32) + q4) * 4096;
-
-        // dQ^T(it) [d = TMEM lane][64 q]: this warp's 32 x 32 block -> its staging rows (no transpose: the fp32 dQ
-        // accumulator in global memory is d-major) -> TMA reduce-add.  No CTA-wide barrier: the staging buffer, the
-        // bulk group and the wait on it are all private to the warp.
-        auto drain_dq = [&](int it, int hq, int m0) {
-            ptx::mbar_wait(dq_full, (uint32_t)it & 1u);
-            ptx::tcgen05_fence_after();
-            uint32_t v[32];
-            if (has_rows) {
-                ptx::tmem_ld_32x32b_x32(tmem_base + kColDQT + lane_off + c0h, v);
-                ptx::tmem_ld_wait();
-            }
-            ptx::tcgen05_fence_before();
-            ptx::mbar_arrive(dq_empty);
-            if (has_rows) {
-                if (lane == 0) ptx::bulk_wait_read<0>();     // this warp's previous reduce-add has read the staging rows
-                __syncwarp();
-                uint8_t* dst = dq_stage + lane * 128;
-#pragma unroll
-                for (int c = 0; c < 8; ++c)
-                    st_shared_v4(dst + ((c ^ (lane & 7)) << 4), __float_as_uint(__uint_as_float(v[4 * c]) * p.scale),
-                                 __float_as_uint(__uint_as_float(v[4 * c + 1]) * p.scale),
-                                 __float_as_uint(__uint_as_float(v[4 * c + 2]) * p.scale),
-                                 __float_as_uint(__uint_as_float(v[4 * c + 3]) * p.scale));
-                ptx::fence_proxy_async();
-                __syncwarp();
-                if (lane == 0) {
-                    int c[4];
-                    c[0] = m0 + c0h;
-                    coords(p.pos_dq, q4 * 32, hq, b, c);
-                    tma_reduce_add_4d(&tmap_dq, dq_stage, c[0], c[1], c[2], c[3]);
-                    ptx::bulk_commit();
-                }
-            }
-        };
-
         // P^T = exp2(S^T c - L_q), dS^T = P^T (dP^T - Delta_q) for this thread's K/V row and 32 query columns.
         // MASK is instantiated only for the tiles that touch the causal diagonal or the end of the K/V sequence.
         auto softmax_bwd = [&](auto mask_tag, const uint32_t* s, const uint32_t* dp, const float* Ls, const float* Ds,
@@ -333,7 +351,6 @@ fa_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
         };
 
         int th = it0 % tiles_per_head, hq = hkv * group + it0 / tiles_per_head;
-        int prev_hq = hq, prev_m0 = 0;
         for (int it = 0; it < total; ++it) {
             const int st = it % kQStages;
             const int m0 = (mb_start + th) * kBM;
@@ -356,29 +373,29 @@ fa_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
             if (need_mask) softmax_bwd(std::true_type{}, s, dp, Ls, Ds, m0, hq, pk, dk_);
             else softmax_bwd(std::false_type{}, s, dp, Ls, Ds, m0, hq, pk, dk_);
             if (it > 0) ptx::mbar_wait(pds_empty, ((uint32_t)(it - 1)) & 1u);  // MMAs of tile it-1 finished with sPt/sDSt
-            uint8_t* prow = sPt + row * 128;
+            // P^T and dS^T go to tensor memory (A operands of dV / dK: this thread's row, its 32 q columns = 16 packed
+            // words each); only dS^T is also needed in shared memory, as the MN-major B operand of dQ^T
+            tmem_st_32x32b_x16(tmem_base + kColPT + lane_off + half * 16, pk);
+            tmem_st_32x32b_x16(tmem_base + kColDST + lane_off + half * 16, dk_);
             uint8_t* drow = sDSt + row * 128;
 #pragma unroll
             for (int c = 0; c < 4; ++c) {                // this warp's 4 of the row's 8 sixteen-byte chunks
                 const int sw = ((half * 4 + c) ^ (row & 7)) << 4;
-                st_shared_v4(prow + sw, pk[4 * c], pk[4 * c + 1], pk[4 * c + 2], pk[4 * c + 3]);
                 st_shared_v4(drow + sw, dk_[4 * c], dk_[4 * c + 1], dk_[4 * c + 2], dk_[4 * c + 3]);
             }
+            tmem_st_wait();
             ptx::fence_proxy_async();
             ptx::tcgen05_fence_before();
             ptx::mbar_arrive(pds_full);
-            if (it > 0) drain_dq(it - 1, prev_hq, prev_m0);
-            prev_hq = hq;
-            prev_m0 = m0;
             if (++th == tiles_per_head) { th = 0; ++hq; }
         }
         if (total > 0) {
-            drain_dq(total - 1, prev_hq, prev_m0);
-            // the commit behind dq_full(total-1) covered every earlier MMA: dK / dV are final
+            // the commit behind pds_empty(total-1) follows the last dQ^T MMA and covers every earlier MMA: dK / dV are final
+            ptx::mbar_wait(pds_empty, ((uint32_t)(total - 1)) & 1u);
+            ptx::tcgen05_fence_after();
         }
         if (total == 0) ptx::mbar_wait(kv_full, 0);  // nothing consumed K/V: let their TMA land before the tiles are reused
-        if (lane == 0) ptx::bulk_wait_read<0>();      // this warp's last dQ reduce-add has read its staging rows
-        named_bar_sync(1, kMathThreads);              // ... and everybody's: the epilogue below reuses all of smem
+        named_bar_sync(1, kMathThreads);              // every math warp is past its last use of the K / V / Q / dO tiles
         if (p.nsplit > 1) {
             // ---- split epilogue: this CTA holds PARTIAL dV / dK -> fp32 -> smem -> TMA reduce-add into the accumulators
             // (32 rows x 32 columns per warp and step, two 4 KB staging buffers per warp in the dead K / V / Q / dO
@@ -628,7 +645,7 @@ static int bwd_tc_impl(const void* q, const void* k, const void* v, const void* 
         tdka = tdq;
         tdva = tdq;
     }
-    dim3 grid((Sk + kBN - 1) / kBN, Hkv * p.nsplit, B);
+    dim3 grid(Hkv * p.nsplit, B, (Sk + kBN - 1) / kBN);
 #define NXD_BWD_ARGS grid, st, tq, tdo, tk, tv, tdk, tdv, tdq, tdka, tdva, p
     const bool drop = p.drop.threshold != 0;
     if (D == 128) {

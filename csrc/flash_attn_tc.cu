@@ -77,8 +77,10 @@ fa_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
     uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(pv_done + 1);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int mb = gridDim.x - 1 - blockIdx.x;  // late (long) causal blocks first
-    const int hq = blockIdx.y, b = blockIdx.z;
+    // grid = (q heads, batch, q blocks): the q block is the slowest launch dimension and counted from the end, so the
+    // long causal rows of EVERY head are scheduled before any short one (longest-first list scheduling)
+    const int mb = gridDim.z - 1 - blockIdx.z;
+    const int hq = blockIdx.x, b = blockIdx.y;
     const int hkv = hq / (p.Hq / p.Hkv);
     const int m0 = mb * kBM;
     const int offset = p.Sk - p.Sq;
@@ -341,7 +343,7 @@ template <int D, bool CAUSAL, bool DROP>
 int launch_fwd_tc_one(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const CUtensorMap& to,
                       const TcParams& p, cudaStream_t st) {
     using L = TcSmem<D>;
-    dim3 grid((p.Sq + kBM - 1) / kBM, p.Hq, p.B);
+    dim3 grid(p.Hq, p.B, (p.Sq + kBM - 1) / kBM);
     static cudaError_t once = cudaFuncSetAttribute(fa_fwd_tc_kernel<D, CAUSAL, DROP>,
                                                    cudaFuncAttributeMaxDynamicSharedMemorySize, L::kBytes);
     NXD_CHECK_CUDA(once);
