@@ -345,6 +345,13 @@ def train_arm(args, arm, arm_name, dev, world, rank, local_rank):
     if tp == world and world > 1 and arm.get("fused_comm"):
         fused_check = fused_numerics_probe(cfg, dev, world, S * args.micro_batch)
     res["fused_check"] = fused_check
+    res["symm_mem"] = None
+    if world > 1 and arm.get("fused_comm"):
+        try:
+            ctx = ps.get_symm_mem_context("tp")
+            res["symm_mem"] = ctx.memory_report() if ctx is not None else None
+        except Exception:  # noqa: BLE001 - accounting only
+            pass
     del model, opt, dev_batches
     torch.cuda.empty_cache()
     backend.set_backends(**prev)
@@ -465,7 +472,7 @@ def main():
             "clocks": ours["clocks"], "e2e": ours.get("e2e"), "gpu_launches": ours["gpu_launches"],
             "gpu_launches_note": "kernel launches of libnxd_b200.so inside the timed region (counted in the library at "
                                  "every <<<>>>), this rank",
-            "fallbacks": ours["fallbacks"], "fused_check": ours["fused_check"],
+            "fallbacks": ours["fallbacks"], "fused_check": ours["fused_check"], "symm_mem": ours["symm_mem"],
         }
         if lib_arm:
             out["baseline_arm"] = {

@@ -22,6 +22,15 @@ from . import _lib
 SIGNAL_BYTES = 1 << 20
 
 
+def _budget_bytes() -> int:
+    """Upper bound on the symmetric memory of ONE context (``NXD_SYMM_BUDGET_MB``, default 16 GiB): regions are keyed
+    by (kernel, shape) and live until the group is destroyed, so a program that keeps presenting new shapes would
+    otherwise grow them without limit."""
+    import os
+
+    return int(os.environ.get("NXD_SYMM_BUDGET_MB", 16384)) << 20
+
+
 class SymmMemContext:
     def __init__(self, group, ranks: List[int], data_bytes: int = 0):
         assert torch.cuda.is_available()
@@ -33,6 +42,7 @@ class SymmMemContext:
         self.lib = _lib.lib()
         self._regions: Dict[str, Tuple[int, List[int], int]] = {}
         self._epochs: Dict[str, int] = {}
+        self._bytes: Dict[str, int] = {}          # region name -> bytes held on this rank (accounting, see memory_report)
         self.closed = False
         self.sig_local, self.sig_peers = self._alloc_exchange(SIGNAL_BYTES)
         self.sig_ptrs = torch.tensor(self.sig_peers, dtype=torch.int64, device=self.device)
@@ -65,6 +75,7 @@ class SymmMemContext:
         if cur is None or cur[2] < nbytes:
             size = max(int(nbytes), 1 << 20)
             size = (size + (1 << 21) - 1) >> 21 << 21
+            self._charge(name, size)
             local, peers = self._alloc_exchange(size)
             table = torch.tensor(peers, dtype=torch.int64, device=self.device)
             self._regions[name] = (local, peers, size, table)
@@ -86,6 +97,7 @@ class SymmMemContext:
             import torch.distributed._symmetric_memory as tsm
 
             size = (max(int(nbytes), 1 << 21) + (1 << 21) - 1) >> 21 << 21
+            self._charge(key, size)
             buf = tsm.empty(size, dtype=torch.uint8, device=self.device)
             hdl = tsm.rendezvous(buf, self.group)
             mc = int(getattr(hdl, "multicast_ptr", 0) or 0)
@@ -105,6 +117,22 @@ class SymmMemContext:
             get_logger().warning("NVLS multicast region unavailable (%s): using per-peer pushes", e)
             self._mc_unavailable = True
             return None
+
+    def _charge(self, name: str, size: int) -> None:
+        """Account ``size`` bytes to region ``name`` (a grown region keeps its old allocation mapped by the peers until
+        teardown, so growth adds up) and refuse to pass the budget with a message that names the consumers."""
+        total = sum(self._bytes.values()) + size
+        if total > _budget_bytes():
+            raise RuntimeError(
+                f"symmetric memory budget exceeded: {total >> 20} MiB > {_budget_bytes() >> 20} MiB "
+                f"(NXD_SYMM_BUDGET_MB) while allocating {size >> 20} MiB for '{name}'.  " + self.memory_report())
+        self._bytes[name] = self._bytes.get(name, 0) + size
+
+    def memory_report(self) -> str:
+        """One line per region, largest first: what holds the peer-mapped memory of this group on this rank."""
+        rows = sorted(self._bytes.items(), key=lambda kv: -kv[1])
+        return f"{sum(self._bytes.values()) >> 20} MiB in {len(rows)} regions: " + ", ".join(
+            f"{n}={b >> 20}MiB" for n, b in rows[:12])
 
     def tensor_view(self, ptr: int, shape, dtype: torch.dtype) -> torch.Tensor:
         """Zero-copy torch tensor over symmetric memory at ``ptr`` (through ``__cuda_array_interface__``)."""
