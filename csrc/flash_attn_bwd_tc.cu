@@ -65,7 +65,7 @@ struct BwdSmem {
     static constexpr int kDQOff = kDStOff + kBN * kBM * 2;    // [4 groups][64 q rows][32 fp32]   32 KB
     static constexpr int kLOff = kDQOff + kBM * kD * 4;       // kQStages x (64 L + 64 Delta) floats   1.5 KB
     static constexpr int kBarOff = kLOff + kQStages * 2 * kBM * 4;
-    static constexpr int kNumBars = 1 + 2 * kQStages + 8;
+    static constexpr int kNumBars = 1 + 2 * kQStages + 6;
     // at least 120 KB so that only ONE CTA fits an SM: each CTA allocates all 512 TMEM columns
     static constexpr int kUsed = kBarOff + kNumBars * 8 + 16 + 1024;
     static constexpr int kBytes = kUsed < 120 * 1024 ? 120 * 1024 : kUsed;
@@ -84,9 +84,8 @@ fa_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
     using L = BwdSmem<kD>;
     constexpr uint32_t kColDK = 0, kColDV = kD, kColST = 2 * kD, kColDPT = 2 * kD + 64, kColDQT = 2 * kD + 128;
     // bf16 P^T and dS^T as TENSOR-MEMORY A operands of the dV / dK MMAs: 128 lanes x 64 q = 32 packed columns each
-    // DOUBLE-BUFFERED (tile parity): the softmax warps may finish tile it + 1 while the tensor core still reads tile it
-    constexpr uint32_t kColPT = 2 * kD + 192;
-    static_assert(kColPT + 64 <= 512, "tensor memory budget");
+    constexpr uint32_t kColPT = 2 * kD + 192, kColDST = kColPT + 32;
+    static_assert(kColDST + 32 <= 512, "tensor memory budget");
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     uint8_t* smem = align_smem_1024(smem_raw);
     uint8_t* sK = smem + L::kKOff;
@@ -103,10 +102,10 @@ fa_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
     uint64_t* qdo_empty = qdo_full + kQStages;      // [kQStages]
     uint64_t* st_full = qdo_empty + kQStages;
     uint64_t* st_empty = st_full + 1;
-    uint64_t* pds_full = st_full + 2;     // [2]
-    uint64_t* pds_empty = st_full + 4;    // [2]
-    uint64_t* dq_full = st_full + 6;
-    uint64_t* dq_empty = st_full + 7;
+    uint64_t* pds_full = st_full + 2;
+    uint64_t* pds_empty = st_full + 3;
+    uint64_t* dq_full = st_full + 4;
+    uint64_t* dq_empty = st_full + 5;
     uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bars + L::kNumBars);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -139,10 +138,8 @@ fa_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
         }
         ptx::mbar_init(st_full, 1);
         ptx::mbar_init(st_empty, kMathThreads);
-        for (int i = 0; i < 2; ++i) {
-            ptx::mbar_init(&pds_full[i], kMathThreads);
-            ptx::mbar_init(&pds_empty[i], 1);
-        }
+        ptx::mbar_init(pds_full, kMathThreads);
+        ptx::mbar_init(pds_empty, 1);
         ptx::mbar_init(dq_full, 1);
         ptx::mbar_init(dq_empty, kDrainThreads);
         ptx::fence_barrier_init();
@@ -195,7 +192,7 @@ fa_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
             constexpr uint32_t idesc_kv = ptx::make_idesc_bf16(kBN, kD, 0, 1);    // dV, dK: 128 x 128, B MN-major
             constexpr uint32_t idesc_dq = ptx::make_idesc_bf16(128, kBM, 1, 1);   // dQ^T: 128 x 64, A and B MN-major
             const uint32_t k_addr = ptx::smem_u32(sK), v_addr = ptx::smem_u32(sV), q_addr = ptx::smem_u32(sQ),
-                           do_addr = ptx::smem_u32(sDO), ds_addr0 = ptx::smem_u32(sPt);   // dS^T buffers: sPt, sDSt
+                           do_addr = ptx::smem_u32(sDO), pt_addr = ptx::smem_u32(sPt), dst_addr = ptx::smem_u32(sDSt);
             auto issue_scores = [&](int it) {
                 const int st = it % kQStages;
                 ptx::mbar_wait(&qdo_full[st], (uint32_t)(it / kQStages) & 1u);
@@ -224,20 +221,18 @@ fa_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
                 if (it + 1 < total) issue_scores(it + 1);
                 const int st = it % kQStages;
                 const uint32_t qb = q_addr + st * L::kStageBytes, dob = do_addr + st * L::kStageBytes;
-                const int pb = it & 1;                                  // P^T / dS^T buffer of this tile
-                const uint32_t dst_addr = ds_addr0 + pb * (kBN * kBM * 2);
-                ptx::mbar_wait(&pds_full[pb], (uint32_t)(it >> 1) & 1u);
+                ptx::mbar_wait(pds_full, (uint32_t)it & 1u);
                 ptx::tcgen05_fence_after();
                 // dV += P^T dO ; dK += dS^T Q      (contraction over the 64 q rows: 4 MMAs of K = 16 each)
 #pragma unroll
                 for (int kk = 0; kk < kBM / 16; ++kk) {
-                    ptx::umma_bf16_ts(tmem_base + kColDV, tmem_base + kColPT + pb * 32 + kk * 8,
+                    ptx::umma_bf16_ts(tmem_base + kColDV, tmem_base + kColPT + kk * 8,
                                       ptx::make_smem_desc(dob + kk * 2048, kBM * 128, 1024), idesc_kv,
                                       (it | kk) != 0 ? 1u : 0u);
                 }
 #pragma unroll
                 for (int kk = 0; kk < kBM / 16; ++kk) {
-                    ptx::umma_bf16<1>(tmem_base + kColDK, ptx::make_smem_desc(dst_addr + kk * 32, 16, 1024),
+                    ptx::umma_bf16_ts(tmem_base + kColDK, tmem_base + kColDST + kk * 8,
                                       ptx::make_smem_desc(qb + kk * 2048, kBM * 128, 1024), idesc_kv,
                                       (it | kk) != 0 ? 1u : 0u);
                 }
@@ -251,7 +246,7 @@ fa_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
                                       ptx::make_smem_desc(dst_addr + kk * 2048, kBN * 128, 1024), idesc_dq,
                                       kk != 0 ? 1u : 0u);
                 }
-                ptx::umma_commit(&pds_empty[pb]);
+                ptx::umma_commit(pds_empty);
                 ptx::umma_commit(dq_full);
             }
         }
@@ -377,13 +372,12 @@ fa_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
             uint32_t pk[16], dk_[16];
             if (need_mask) softmax_bwd(std::true_type{}, s, dp, Ls, Ds, m0, hq, pk, dk_);
             else softmax_bwd(std::false_type{}, s, dp, Ls, Ds, m0, hq, pk, dk_);
-            const int pb = it & 1;
-            // the MMAs of tile it - 2 (same buffer) have finished with P^T / dS^T; tile it - 1 may still be in flight
-            if (it > 1) ptx::mbar_wait(&pds_empty[pb], ((uint32_t)((it >> 1) - 1)) & 1u);
-            // P^T goes to tensor memory (A operand of dV: this thread's row, its 32 q columns = 16 packed words), dS^T to
-            // shared memory (K-major A operand of dK and, read MN-major, B operand of dQ^T)
-            tmem_st_32x32b_x16(tmem_base + kColPT + pb * 32 + lane_off + half * 16, pk);
-            uint8_t* drow = sPt + pb * (kBN * kBM * 2) + row * 128;
+            if (it > 0) ptx::mbar_wait(pds_empty, ((uint32_t)(it - 1)) & 1u);  // MMAs of tile it-1 finished with sPt/sDSt
+            // P^T and dS^T go to tensor memory (A operands of dV / dK: this thread's row, its 32 q columns = 16 packed
+            // words each); only dS^T is also needed in shared memory, as the MN-major B operand of dQ^T
+            tmem_st_32x32b_x16(tmem_base + kColPT + lane_off + half * 16, pk);
+            tmem_st_32x32b_x16(tmem_base + kColDST + lane_off + half * 16, dk_);
+            uint8_t* drow = sDSt + row * 128;
 #pragma unroll
             for (int c = 0; c < 4; ++c) {                // this warp's 4 of the row's 8 sixteen-byte chunks
                 const int sw = ((half * 4 + c) ^ (row & 7)) << 4;
@@ -392,12 +386,12 @@ fa_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
             tmem_st_wait();
             ptx::fence_proxy_async();
             ptx::tcgen05_fence_before();
-            ptx::mbar_arrive(&pds_full[pb]);
+            ptx::mbar_arrive(pds_full);
             if (++th == tiles_per_head) { th = 0; ++hq; }
         }
         if (total > 0) {
             // the commit behind pds_empty(total-1) follows the last dQ^T MMA and covers every earlier MMA: dK / dV are final
-            ptx::mbar_wait(&pds_empty[(total - 1) & 1], ((uint32_t)((total - 1) >> 1)) & 1u);
+            ptx::mbar_wait(pds_empty, ((uint32_t)(total - 1)) & 1u);
             ptx::tcgen05_fence_after();
         }
         if (total == 0) ptx::mbar_wait(kv_full, 0);  // nothing consumed K/V: let their TMA land before the tiles are reused

@@ -14,7 +14,7 @@
 //   warp 1    TMEM allocation (O: D columns, S: 64 columns) and MMA issue.  S(j+1) is issued BEFORE waiting for
 //             P(j), so it runs while the softmax warps work on tile j.
 //   warps 2-5 softmax: one thread per query row (TMEM lane).  tcgen05.ld S -> scale, mask, running max, exp2 ->
-//             bf16 P written to swizzled smem (the K-major A operand of the PV MMA).  O stays in TMEM across the
+//             bf16 P written to tensor memory (tcgen05.st), the A operand of the PV MMA.  O stays in TMEM across the
 //             whole loop; it is rescaled (tcgen05.ld / st) only when the running max moved by more than 2^8
 //             ("lazy rescale"), which is rare after the first tiles.  Epilogue: O / l -> bf16 -> smem -> TMA store.
 #include "common.cuh"
@@ -52,7 +52,7 @@ struct TcSmem {
     static constexpr int kBarOff = kPOff + kPBytes;
     static constexpr int kNumBars = 1 + 2 * kSlots + 4;
     static constexpr int kBytes = kBarOff + kNumBars * 8 + 16 + 1024;  // + manual 1024-byte alignment slack
-    static constexpr int kTmemCols = (D + kBN <= 128) ? 128 : 256;
+    static constexpr int kTmemCols = 256;   // O (D) + S (64) + bf16 P as the tensor-memory A operand of P V (32)
 };
 
 template <int D, bool CAUSAL, bool DROP>
@@ -110,6 +110,7 @@ fa_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
     const uint32_t tmem_base = *tmem_ptr_smem;
     const uint32_t tmem_o = tmem_base;
     const uint32_t tmem_s = tmem_base + D;
+    const uint32_t tmem_p = tmem_base + D + kBN;   // 128 lanes x 64 keys bf16 = 32 packed columns
 
     if (warp == 0) {
         // ============================ TMA producer ============================
@@ -148,7 +149,7 @@ fa_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
         if (lane == 0 && n_tiles > 0) {
             constexpr uint32_t idesc_s = ptx::make_idesc_bf16(kBM, kBN, 0, 0);
             constexpr uint32_t idesc_o = ptx::make_idesc_bf16(kBM, D, 0, 1);
-            const uint32_t q_addr = ptx::smem_u32(sQ), ring_addr = ptx::smem_u32(sRing), p_addr = ptx::smem_u32(sP);
+            const uint32_t q_addr = ptx::smem_u32(sQ), ring_addr = ptx::smem_u32(sRing);
             int it = 0;
             auto issue_s = [&](int j) {
                 const int slot = it % kSlots;
@@ -180,9 +181,8 @@ fa_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
                 const uint32_t vb = ring_addr + slot * L::kSlotBytes;
 #pragma unroll
                 for (int kk = 0; kk < kBN / 16; ++kk) {
-                    const uint64_t da = ptx::make_smem_desc(p_addr + kk * 32, 16, 1024);
                     const uint64_t db = ptx::make_smem_desc(vb + kk * 2048, kBN * 128, 1024);
-                    ptx::umma_bf16<1>(tmem_o, da, db, idesc_o, (j | kk) != 0 ? 1u : 0u);
+                    ptx::umma_bf16_ts(tmem_o, tmem_p + kk * 8, db, idesc_o, (j | kk) != 0 ? 1u : 0u);
                 }
                 ptx::umma_commit(&slot_empty[slot]);
                 ptx::umma_commit(pv_done);
@@ -272,11 +272,11 @@ fa_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
                     tmem_st_wait();
                 }
             }
-            uint8_t* prow = sP + row * 128;
-#pragma unroll
-            for (int c = 0; c < 8; ++c)
-                st_shared_v4(prow + ((c ^ (row & 7)) << 4), pk[4 * c], pk[4 * c + 1], pk[4 * c + 2], pk[4 * c + 3]);
-            ptx::fence_proxy_async();
+            // P goes to TENSOR MEMORY (this thread's row, 64 keys = 32 packed words): the A operand of the P V MMA never
+            // touches shared memory (no 16 KB store + re-read per tile, no async-proxy fence)
+            tmem_st_32x32b_x16(tmem_p + lane_off, pk);
+            tmem_st_32x32b_x16(tmem_p + lane_off + 16, pk + 16);
+            tmem_st_wait();
             ptx::tcgen05_fence_before();
             ptx::mbar_arrive(p_full);
         };
