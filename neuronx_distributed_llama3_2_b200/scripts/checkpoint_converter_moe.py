@@ -9,8 +9,9 @@ how each tensor is cut (``inference.checkpoint_sharding.shard_children`` does th
 dim 0 over EP, layers are dealt to PP stages as ``NxDPPModel`` auto-partitioning would).  Merging reads the same tags.
 
 File layout is the trainer's (``trainer/checkpoint.py``): ``<out>/model/dp_rank_00_tp_rank_TT_pp_rank_PP.pt`` and, with
-expert parallelism, the expert-parallel tensors apart in ``dp_rank_00_ep_rank_EE_tp_rank_TT_pp_rank_PP.pt`` (the dense
-remainder is written once per (tp, pp)); ``checkpoint`` / ``done`` markers.
+expert parallelism, ``dp_rank_00_ep_rank_EE_tp_rank_TT_pp_rank_PP.pt``.  The trainer writes one COMPLETE file per EP rank
+(dense tensors included, the reference layout); the converter's own output keeps the dense remainder once per (tp, pp) in
+the ep-less file, and both layouts are read back (``load_coord``); ``checkpoint`` / ``done`` markers.
 """
 from __future__ import annotations
 

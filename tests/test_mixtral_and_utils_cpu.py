@@ -62,8 +62,9 @@ def _moe_ep_worker(rank, world, tmp):
     ep_rank, tp_rank = ps.get_expert_model_parallel_rank(), ps.get_tensor_model_parallel_rank()
     nxd.save_checkpoint(tmp, "s", model=model, optimizer=opt, use_xser=False)
     files = sorted(os.listdir(os.path.join(tmp, "s", "model")))
-    assert files == sorted([f"dp_rank_00_ep_rank_{e:02d}_tp_rank_{t:02d}_pp_rank_00.pt" for e in range(2) for t in range(2)]
-                           + [f"dp_rank_00_tp_rank_{t:02d}_pp_rank_00.pt" for t in range(2)]), files   # experts | dense
+    # the reference layout: ONE complete model file per (EP rank, TP rank), dense tensors included (checkpoint.py:655)
+    assert files == sorted([f"dp_rank_00_ep_rank_{e:02d}_tp_rank_{t:02d}_pp_rank_00.pt" for e in range(2)
+                            for t in range(2)]), files
     before = {k: v.clone() for k, v in model.state_dict().items()}
     import copy
 
