@@ -14,7 +14,7 @@
 // rows with 16-byte loads (all k steps of a lane in flight), the activations sit normalised in shared memory.  A pair is
 // exactly what the epilogue combines: (d, d + D/2) of one head for RoPE, (gate_j, up_j) for SwiGLU.  Lane 0 of the warp
 // applies the epilogue to the reduced sums and stores.
-#include "common.cuh"
+#include "decode_common.cuh"
 
 namespace {
 
@@ -115,23 +115,8 @@ __device__ __forceinline__ void pair_dot(const bf16* __restrict__ w0, const bf16
     }
 }
 
-struct CacheDst {
-    bf16* k;
-    bf16* v;
-    const int* block_table;  // null -> contiguous cache [lines, n_kv, S_max, D]
-    const int* seq_ids;      // null -> cache line = batch row
-    long long stride_b, stride_h;
-    int page_size, max_pages;
-};
-
-__device__ __forceinline__ size_t cache_row(const CacheDst& c, int b, int h, int pos, int D) {
-    const int line = c.seq_ids ? c.seq_ids[b] : b;
-    if (c.block_table) {
-        const int page = c.block_table[(size_t)line * c.max_pages + pos / c.page_size];
-        return (size_t)page * c.stride_b + (size_t)h * c.stride_h + (size_t)(pos % c.page_size) * D;
-    }
-    return (size_t)line * c.stride_b + (size_t)h * c.stride_h + (size_t)pos * D;
-}
+using nxd_decode::CacheDst;
+using nxd_decode::cache_row;
 
 // grid = (n_q + 2 n_kv) heads x (D / 16) pair groups.  w: [(n_q + 2 n_kv) * D, K], head-major rows (q | k | v).
 template <int kB>

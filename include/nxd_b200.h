@@ -192,6 +192,22 @@ int nxd_skinny_gemm_ar_bf16(const void* x, const void* w, const void* residual, 
                             long long ldx, long long ldw, long long ldo, void* const* stage_ptrs,
                             void* const* sig_ptrs, size_t slot_elems, int tp, int rank, int slot, void* state,
                             void* stream);
+/* Weight-streaming tcgen05 GEMM for 1..128 activation rows (batched token generation): out[B, N] = x[B, K] @ w[N, K]^T
+ * (+ residual[B, N]); the weight rows are the UMMA M dimension, the padded row count (16/32/64/128) the UMMA N dimension;
+ * split-K over a thread-block cluster with a distributed-shared-memory reduction.  K, ldx, ldw % 8 == 0;
+ * splits: 0 = choose, else 1 / 2 / 4 / 8. */
+int nxd_gemm_smallm_bf16(const void* x, const void* w, const void* residual, void* out, int B, int N, int K,
+                         long long ldx, long long ldw, long long ldo, long long ldr, int splits, void* stream);
+/* The same kernel with the decoder layer's element-wise neighbours in its epilogue (batched counterparts of
+ * nxd_decode_qkv_rope_cache / nxd_decode_gate_up_swiglu, without the norm: x is the normalised activation).
+ * qkv: B <= 128, D in {64, 128}; gate_up: B <= 64, I % 8 == 0 (a CTA streams gate slab t and up slab t). */
+int nxd_smallm_qkv_rope_cache(const void* x, long long ldx, const void* w, long long ldw, const float* cos_t,
+                              const float* sin_t, const int* positions, void* q_out, void* cache_k, void* cache_v,
+                              const int* seq_ids, const int* block_table, long long stride_b, long long stride_h,
+                              int page_size, int max_pages, int B, int K, int n_q, int n_kv, int D, int splits,
+                              void* stream);
+int nxd_smallm_gate_up_swiglu(const void* x, long long ldx, const void* w, long long ldw, void* out, long long ldo, int B,
+                              int K, int I, int splits, void* stream);
 /* Weight-only int8 skinny GEMM (reference: quantization_layers.py:444-478 dequantise + matmul): out[B, N] (+ residual) =
  * (x[B, K] bf16 * w[N, K]^T int8) * scale, fp32 accumulation; scale_n == 1 (per tensor) or N (per output channel).
  * B <= 8, K % 16 == 0, ldw (bytes) % 16 == 0.  Streams half the bytes of the bf16 skinny GEMM. */

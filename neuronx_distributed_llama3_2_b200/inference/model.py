@@ -160,7 +160,7 @@ class KVCacheInferenceMixin:
         return qkv
 
     # -- fused token-generation layer (6 launches) -------------------------------------------------------------------
-    def _fused_decode_ok(self, layer, hidden: torch.Tensor) -> bool:
+    def _fused_decode_ok(self, layer, hidden: torch.Tensor, batched: bool = False) -> bool:
         """The fused decode kernels apply to the plain Llama layer shape: RMSNorm, bias-free fused QKV, SwiGLU MLP,
         bf16 weights, at most 8 sequences, native backends selected, and (tensor parallel) the one-shot all-reduce
         context for the row-parallel projections.  Model families that override the hooks take the generic path."""
@@ -187,11 +187,64 @@ class KVCacheInferenceMixin:
         if not cached or backend.gemm_backend() != "tcgen05":
             return False
         x = hidden.reshape(hidden.shape[0], -1)
-        if not decode_fused.qualifies(x):
+        if not (decode_fused.qualifies_batched(x) if batched else decode_fused.qualifies(x)):
             return False
         if ps.get_tensor_model_parallel_size() > 1:
-            return backend.fused_comm_enabled() and ps.get_symm_mem_context("tp") is not None
+            # the batched kernels have no all-reduce epilogue: tensor-parallel batches above 8 rows take the generic
+            # layer (its GEMMs still run on the small-M tensor-core kernel, ops/linear.py)
+            return (not batched) and backend.fused_comm_enabled() and ps.get_symm_mem_context("tp") is not None
         return True
+
+    def _decode_i32(self, positions, seq_ids):
+        """int32 copies of the positions / cache lines once per forward, not once per layer."""
+        memo = getattr(self, "_decode_i32_memo", None)
+        if memo is None or memo[0] is not positions or memo[1] is not seq_ids:
+            memo = (positions, seq_ids, positions[:, 0].to(torch.int32).contiguous(),
+                    seq_ids.to(torch.int32).contiguous() if seq_ids is not None else None)
+            self._decode_i32_memo = memo
+        return memo[2], memo[3]
+
+    def _decode_attention(self, q, ck, cv, seq_ids, lengths):
+        kc = self.kv_cache
+        if kc.paged:
+            t = kc.block_table if seq_ids is None else kc.block_table[seq_ids.long()]
+            return attn_ops.decode_attention(q, ck, cv, lengths, block_table=t, page_size=kc.page_size)
+        if seq_ids is not None:
+            return attn_ops.decode_attention(q, ck.index_select(0, seq_ids.long()), cv.index_select(0, seq_ids.long()),
+                                             lengths)
+        return attn_ops.decode_attention(q, ck, cv, lengths)
+
+    def _layer_batched_decode(self, i: int, layer, hidden, residual, positions, seq_ids, lengths):
+        """One token per sequence for 9 .. 128 sequences on the small-M tensor-core kernels (``csrc/gemm_smallm.cu``):
+        RMSNorm | QKV GEMM+RoPE+cache write | attention (split, merge) | o_proj+residual | RMSNorm | gate/up+SwiGLU |
+        down_proj+residual -- eight launches, no copies between them."""
+        from ..ops import activation, decode_fused
+        from ..ops.gemm import gemm_smallm
+
+        B = hidden.shape[0]
+        x = hidden.reshape(B, -1)
+        if residual is not None:
+            x = x + residual.reshape(B, -1)
+        attn, mlp = layer.self_attn, layer.mlp
+        nq, nkv, D = attn.q_heads_local, attn.kv_heads_local, attn.head_dim
+        cos, sin = self._rope(x.device)
+        ck, cv = self.kv_cache.layer(i)
+        kc = self.kv_cache
+        pos, sid = self._decode_i32(positions, seq_ids)
+        xn = norm_ops.rms_norm(x, layer.input_layernorm.weight, layer.input_layernorm.variance_epsilon)
+        q = decode_fused.qkv_rope_cache_batched(xn, attn.qkv_proj.weight_qkv, cos, sin, pos, ck, cv, nq, nkv, D,
+                                                seq_ids=sid, block_table=kc.block_table if kc.paged else None,
+                                                page_size=kc.page_size if kc.paged else 0)
+        o = self._decode_attention(q, ck, cv, seq_ids, lengths)
+        x2 = gemm_smallm(o.reshape(B, nq * D), attn.o_proj.weight, residual=x)
+        xn2 = norm_ops.rms_norm(x2, layer.post_attention_layernorm.weight,
+                                layer.post_attention_layernorm.variance_epsilon)
+        if B <= decode_fused.BATCHED_SWIGLU_MAX_ROWS:
+            act = decode_fused.gate_up_swiglu_batched(xn2, mlp.gate_up_proj.weight)
+        else:
+            act = activation.swiglu(gemm_smallm(xn2, mlp.gate_up_proj.weight))
+        x3 = gemm_smallm(act, mlp.down_proj.weight, residual=x2)
+        return x3.reshape(B, 1, -1), None
 
     def _layer_fused_decode(self, i: int, layer, hidden, residual, positions, seq_ids, lengths):
         """One token per sequence: RMSNorm+QKV+RoPE+cache write | attention (split, merge) | o_proj+residual |
@@ -209,23 +262,12 @@ class KVCacheInferenceMixin:
         cos, sin = self._rope(x.device)
         ck, cv = self.kv_cache.layer(i)
         kc = self.kv_cache
-        memo = getattr(self, "_decode_i32", None)          # int32 copies once per forward, not once per layer
-        if memo is None or memo[0] is not positions or memo[1] is not seq_ids:
-            memo = (positions, seq_ids, positions[:, 0].to(torch.int32).contiguous(),
-                    seq_ids.to(torch.int32).contiguous() if seq_ids is not None else None)
-            self._decode_i32 = memo
-        pos, sid = memo[2], memo[3]
+        pos, sid = self._decode_i32(positions, seq_ids)
         table = kc.block_table if kc.paged else None
         q = decode_fused.qkv_rope_cache(x, layer.input_layernorm.weight, layer.input_layernorm.variance_epsilon,
                                         attn.qkv_proj.weight_qkv, cos, sin, pos, ck, cv, nq, nkv, D, seq_ids=sid,
                                         block_table=table, page_size=kc.page_size if kc.paged else 0)
-        if kc.paged:
-            t = table if seq_ids is None else table[seq_ids.long()]
-            o = attn_ops.decode_attention(q, ck, cv, lengths, block_table=t, page_size=kc.page_size)
-        elif seq_ids is not None:
-            o = attn_ops.decode_attention(q, ck.index_select(0, seq_ids.long()), cv.index_select(0, seq_ids.long()), lengths)
-        else:
-            o = attn_ops.decode_attention(q, ck, cv, lengths)
+        o = self._decode_attention(q, ck, cv, seq_ids, lengths)
         ctx = ps.get_symm_mem_context("tp") if ps.get_tensor_model_parallel_size() > 1 else None
         x2 = skinny_gemm(o.reshape(B, nq * D), attn.o_proj.weight, residual=x, ctx=ctx)
         if x2 is None:      # shape outside the skinny kernel: generic projection, then the residual
@@ -238,8 +280,11 @@ class KVCacheInferenceMixin:
         return x3.reshape(B, 1, -1), None
 
     def _layer(self, i: int, layer, hidden, residual, positions, seq_ids, lengths, prefill):
-        if not prefill and hidden.shape[1] == 1 and self._fused_decode_ok(layer, hidden):
-            return self._layer_fused_decode(i, layer, hidden, residual, positions, seq_ids, lengths)
+        if not prefill and hidden.shape[1] == 1:
+            if self._fused_decode_ok(layer, hidden):
+                return self._layer_fused_decode(i, layer, hidden, residual, positions, seq_ids, lengths)
+            if hidden.shape[0] > 8 and self._fused_decode_ok(layer, hidden, batched=True):
+                return self._layer_batched_decode(i, layer, hidden, residual, positions, seq_ids, lengths)
         h, residual = self._add_norm(layer.input_layernorm, hidden, residual)
         a = self._attention(i, layer.self_attn, h, positions, seq_ids, lengths, prefill)
         h, residual = self._add_norm(layer.post_attention_layernorm, a, residual)

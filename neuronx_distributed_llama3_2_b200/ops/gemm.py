@@ -80,3 +80,33 @@ def gemm_grouped(a: torch.Tensor, b: torch.Tensor, layout: str, out: Optional[to
         _lib.stream_ptr())
     _lib.check(rc, "nxd_gemm_grouped_bf16")
     return out
+
+
+SMALLM_MAX_ROWS = 128
+
+
+def gemm_smallm(x: torch.Tensor, w: torch.Tensor, residual: Optional[torch.Tensor] = None, splits: int = 0
+                ) -> Optional[torch.Tensor]:
+    """``x[B, K] @ w[N, K]^T (+ residual)`` for ``B <= 128`` rows on the tensor cores with the WEIGHT rows as the UMMA M
+    dimension (``csrc/gemm_smallm.cu``): a pure stream of the weight matrix, split-K over a thread-block cluster for
+    narrow layers.  The batched token-generation GEMM (reference: the parallel linear layers of
+    ``parallel_layers/layers.py`` at ``[batch, 1, hidden]``).  ``None`` when the shape does not qualify."""
+    B, K = x.shape
+    N = w.shape[0]
+    if (B == 0 or B > SMALLM_MAX_ROWS or x.dtype != torch.bfloat16 or w.dtype != torch.bfloat16 or K % 8
+            or x.stride(1) != 1 or w.stride(1) != 1 or x.stride(0) % 8 or w.stride(0) % 8
+            or x.data_ptr() % 16 or w.data_ptr() % 16):
+        return None
+    out = torch.empty((B, N), dtype=torch.bfloat16, device=x.device)
+    ldr = 0
+    if residual is not None:
+        residual = residual.reshape(B, N)
+        if residual.stride(1) != 1:
+            residual = residual.contiguous()
+        ldr = residual.stride(0)
+    rc = _lib.lib().nxd_gemm_smallm_bf16(
+        _lib.ptr(x), _lib.ptr(w), _lib.ptr(residual), _lib.ptr(out), _c.c_int(B), _c.c_int(N), _c.c_int(K),
+        _c.c_longlong(x.stride(0)), _c.c_longlong(w.stride(0)), _c.c_longlong(out.stride(0)), _c.c_longlong(ldr),
+        _c.c_int(splits), _lib.stream_ptr())
+    _lib.check(rc, "nxd_gemm_smallm_bf16")
+    return out

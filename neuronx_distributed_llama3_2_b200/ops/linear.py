@@ -50,12 +50,18 @@ def gemm_nt(a: torch.Tensor, b: torch.Tensor, out: Optional[torch.Tensor] = None
     """``a[M,K] @ b[N,K]^T``.  ``accumulate`` adds into ``out`` (fp32 grad accumulation)."""
     m, k = a.shape
     n = b.shape[0]
-    if (m <= 16 and out is None and not accumulate and out_dtype in (None, torch.bfloat16) and a.is_cuda
+    if (m <= 128 and out is None and not accumulate and out_dtype in (None, torch.bfloat16) and a.is_cuda
             and a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16 and _backend() == "tcgen05" and _lib.available()):
-        # token generation: weight-streaming kernel instead of a 256-row tensor-core tile that is 94 % padding
-        from .fused_comm import skinny_gemm
+        # token generation: weight-streaming kernels instead of a 256-row tensor-core tile that is mostly padding --
+        # FMA GEMV up to 8 rows, above that the tensor-core kernel with the weight rows as the UMMA M dimension
+        if m <= 8:
+            from .fused_comm import skinny_gemm
 
-        res = skinny_gemm(a, b)
+            res = skinny_gemm(a, b)
+        else:
+            from .gemm import gemm_smallm
+
+            res = gemm_smallm(a, b)
         if res is not None:
             return res
     if _use_kernel(a, b, m, n, k):

@@ -70,6 +70,46 @@ def test_generation_matches_recompute(paged):
         cur = cur + 1
 
 
+@pytest.mark.parametrize("B,paged,head_dim", [(12, False, 64), (40, True, 64), (72, False, 128)])
+def test_batched_decode_layer_matches_library_arm(B, paged, head_dim):
+    """9 .. 128 sequences take the small-M tensor-core layer (QKV GEMM + RoPE + cache write, gate/up + SwiGLU, residual
+    epilogues): its logits and its KV cache must agree with the library arm (cuBLAS + SDPA, unfused) step by step."""
+    from neuronx_distributed_llama3_2_b200.inference import InferenceConfig, LlamaInferenceModel
+    from neuronx_distributed_llama3_2_b200.models import LlamaForCausalLM
+    from neuronx_distributed_llama3_2_b200.ops import backend
+
+    torch.manual_seed(3)
+    dev = torch.device("cuda")
+    cfg = _cfg(head_dim=head_dim, hidden_size=8 * head_dim)
+    train = LlamaForCausalLM(cfg, device=dev)
+    prompts = torch.randint(1, 1024, (B, 32), device=dev)
+    pos = torch.arange(32, device=dev).unsqueeze(0).expand(B, 32)
+    runs = []
+    for arm in (backend.NATIVE_ARM, backend.LIBRARY_ARM):
+        with backend.use_backends(**arm):
+            inf = LlamaInferenceModel(cfg, InferenceConfig(batch_size=B, max_context_length=64, seq_len=128,
+                                                           paged_kv=paged, page_size=32), device=dev)
+            inf.load_state_dict(train.state_dict())
+            inf.init_kv_cache(device=dev)
+            tok, _ = inf.forward_infer(prompts, pos, return_logits=True)
+            if arm is backend.NATIVE_ARM:
+                layer = next(iter(inf._decoder_layers()))
+                assert inf._fused_decode_ok(layer, torch.empty(B, 1, cfg.hidden_size, device=dev,
+                                                               dtype=torch.bfloat16), batched=True)
+            cur = torch.full((B,), 32, device=dev)
+            steps = []
+            feed = prompts[:, -1]
+            for _ in range(3):          # the same fed tokens in both arms: compare logits, not trajectories
+                _, logits = inf.forward_infer(feed.reshape(B, 1), cur.reshape(B, 1), return_logits=True)
+                steps.append(logits.float())
+                feed = (feed * 7 + 1) % 1024
+                cur = cur + 1
+            runs.append(steps)
+    for a, b in zip(*runs):
+        assert (a - b).abs().max().item() < 0.12, (a - b).abs().max().item()
+        assert ((a - b).norm() / b.norm()).item() < 2e-2
+
+
 def test_runner_cuda_graphs_match_eager():
     from neuronx_distributed_llama3_2_b200.inference import InferenceConfig, InferenceRunner
     from neuronx_distributed_llama3_2_b200.models import LlamaForCausalLM

@@ -454,6 +454,30 @@ def test_skinny_gemm(B, K, N):
     assert ((out.float() - ref).norm() / ref.norm()).item() < 4e-3
 
 
+@pytest.mark.parametrize("splits", [0, 1, 2, 4, 8])
+@pytest.mark.parametrize("B,K,N", [(16, 2048, 3072), (9, 2048, 2048), (32, 8192, 2048), (33, 1032, 1000), (64, 2048, 16384),
+                                   (100, 3072, 520), (128, 4096, 264), (1, 512, 128), (17, 576, 2048)])
+def test_gemm_smallm(B, K, N, splits):
+    """Weight-streaming tcgen05 GEMM (weight rows = UMMA M) incl. the cluster split-K reduction, ragged N / K, a K
+    slice count that leaves the last cluster rank without k blocks (K = 576 -> 9 blocks over 4 / 8 ranks), strided x."""
+    from neuronx_distributed_llama3_2_b200.ops.gemm import gemm_smallm
+
+    xw = torch.randn(B, K + 64, device="cuda").bfloat16()
+    x = xw[:, :K]                                    # row pitch K + 64
+    w = (torch.randn(N, K, device="cuda") * 0.05).bfloat16()
+    res = torch.randn(B, N, device="cuda").bfloat16()
+    ref = x.float() @ w.float().t()
+    out = gemm_smallm(x, w, splits=splits)
+    assert out is not None
+    assert ((out.float() - ref).norm() / ref.norm()).item() < 4e-3
+    assert (out.float() - ref).abs().max().item() < 0.05 * ref.abs().max().item() + 0.05
+    out = gemm_smallm(x, w, residual=res, splits=splits)
+    ref = ref + res.float()
+    assert ((out.float() - ref).norm() / ref.norm()).item() < 4e-3
+    # bitwise reproducible (rank-ordered reduction, no atomics)
+    assert torch.equal(out, gemm_smallm(x, w, residual=res, splits=splits))
+
+
 @pytest.mark.parametrize("C", [384, 200, 37])
 @pytest.mark.parametrize("layout", ["nn", "nt", "tn"])
 def test_grouped_expert_gemm(layout, C):
@@ -544,6 +568,66 @@ def test_decode_fused_qkv_rope_cache(B, D, paged):
         assert (krow.float() - rot[b, nq:]).abs().max() < 3e-2
         assert (vrow.float() - qkv[b, nq + nkv:]).abs().max() < 3e-2
     assert int((ck != 0).any(-1).sum()) == B * nkv        # exactly one row per (sequence, kv head) was written
+
+
+@pytest.mark.parametrize("splits", [0, 1, 4])
+@pytest.mark.parametrize("B,D,nq,nkv,paged", [(16, 64, 8, 2, False), (9, 128, 6, 2, False), (33, 64, 7, 1, True),
+                                              (64, 128, 4, 4, False), (100, 64, 8, 2, True)])
+def test_smallm_qkv_rope_cache(B, D, nq, nkv, paged, splits):
+    """Batched (9 .. 128 rows) fused QKV tensor-core GEMM + RoPE + KV-cache write against the unfused fp32 math; D = 64
+    with an odd head count leaves the last 128-row weight slab half empty."""
+    from neuronx_distributed_llama3_2_b200.ops import decode_fused, rope as rope_ops
+
+    torch.manual_seed(B * 7 + D)
+    H, S = 1024, 256
+    xn = torch.randn(B, H, device="cuda").bfloat16()
+    w = (torch.randn((nq + 2 * nkv) * D, H, device="cuda") * 0.03).bfloat16()
+    cos, sin = rope_ops.build_rope_cache(S, D, 500000.0, None, device="cuda")
+    pos = torch.randint(0, S, (B,), device="cuda", dtype=torch.int32)
+    page = 16
+    if paged:
+        n_pages = B * S // page
+        ck = torch.zeros(n_pages, nkv, page, D, device="cuda", dtype=torch.bfloat16)
+        cv = torch.zeros_like(ck)
+        table = torch.randperm(n_pages, device="cuda").reshape(B, S // page).to(torch.int32)
+    else:
+        ck = torch.zeros(B, nkv, S, D, device="cuda", dtype=torch.bfloat16)
+        cv = torch.zeros_like(ck)
+        table = None
+    q = decode_fused.qkv_rope_cache_batched(xn, w, cos, sin, pos, ck, cv, nq, nkv, D, block_table=table,
+                                            page_size=page if paged else 0, splits=splits)
+    qkv = (xn.float() @ w.float().t()).reshape(B, nq + 2 * nkv, D)
+    c, s_ = cos[pos.long()], sin[pos.long()]                       # [B, D/2]
+    a, b_ = qkv[:, : nq + nkv, : D // 2], qkv[:, : nq + nkv, D // 2:]
+    rot = torch.cat([a * c[:, None] - b_ * s_[:, None], b_ * c[:, None] + a * s_[:, None]], dim=-1)
+    assert (q.float() - rot[:, :nq]).abs().max() < 3e-2
+    for b in range(B):
+        p = int(pos[b])
+        if paged:
+            krow = ck[int(table[b, p // page]), :, p % page]
+            vrow = cv[int(table[b, p // page]), :, p % page]
+        else:
+            krow, vrow = ck[b, :, p], cv[b, :, p]
+        assert (krow.float() - rot[b, nq:]).abs().max() < 3e-2
+        assert (vrow.float() - qkv[b, nq + nkv:]).abs().max() < 3e-2
+    assert int((ck != 0).any(-1).sum()) == B * nkv        # exactly one row per (sequence, kv head) was written
+
+
+@pytest.mark.parametrize("splits", [0, 1, 2, 8])
+@pytest.mark.parametrize("B,H,I", [(16, 2048, 8192), (9, 1024, 1000), (40, 3072, 2048), (64, 1024, 520)])
+def test_smallm_gate_up_swiglu(B, H, I, splits):
+    """Batched gate/up tensor-core GEMM (two accumulators per CTA) + SwiGLU against fp32; I = 1000 / 520 end inside a
+    128-row slab (the gate slab then overlaps the first up rows, which must not leak into the output)."""
+    from neuronx_distributed_llama3_2_b200.ops import decode_fused
+
+    torch.manual_seed(B + I)
+    xn = torch.randn(B, H, device="cuda").bfloat16()
+    w = (torch.randn(2 * I, H, device="cuda") * 0.03).bfloat16()
+    out = decode_fused.gate_up_swiglu_batched(xn, w, splits=splits)
+    gu = (xn.float() @ w.float().t()).bfloat16().float()
+    ref = torch.nn.functional.silu(gu[:, :I]) * gu[:, I:]
+    assert ((out.float() - ref).norm() / ref.norm()).item() < 6e-3
+    assert (out.float() - ref).abs().max().item() < 0.05 * ref.abs().max().item() + 0.02
 
 
 @pytest.mark.parametrize("B", [1, 5, 8])

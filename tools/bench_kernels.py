@@ -167,6 +167,74 @@ def bench_elementwise(rows):
         print(json.dumps(res), flush=True)
 
 
+def graph_time_ms(fn, calls=40, replays=5):
+    """Device time per call of ``fn`` with the host out of the picture: ``calls`` invocations captured into one CUDA
+    graph (as the token-generation loop runs them), replayed ``replays`` times between two events."""
+    st = torch.cuda.Stream()
+    st.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(st):
+        for _ in range(3):
+            fn()
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g, stream=st):
+        for _ in range(calls):
+            fn()
+    g.replay()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(replays):
+        g.replay()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / (replays * calls)
+
+
+def bench_smallm(rows):
+    """Token-generation GEMMs (9..128 rows) of Llama-3.2-1B / 3B: the weight-streaming tcgen05 kernel against cuBLAS, the
+    previous path (mma.sync skinny kernel up to 16 rows, 256-row tcgen05 tiles above) and the HBM roofline.  Weights are
+    cycled through a pool > 2 x L2 so that every call streams them from HBM, as consecutive layers do; calls are timed
+    inside a CUDA graph (the generation loop is one), so host launch cost is excluded for every contender."""
+    from neuronx_distributed_llama3_2_b200.ops.fused_comm import skinny_gemm
+    from neuronx_distributed_llama3_2_b200.ops.gemm import gemm_smallm
+
+    shapes = [("1B qkv", 3072, 2048), ("1B o", 2048, 2048), ("1B gate_up", 16384, 2048), ("1B down", 2048, 8192),
+              ("1B lm_head", 128256, 2048), ("3B gate_up", 16384, 3072), ("3B down", 3072, 8192)]
+    only_b = [int(v) for v in os.environ.get("NXD_SMALLM_B", "16,32,64,128").split(",")]
+    for name, N, K in shapes:
+        copies = max(2, min(64, (320 << 20) // (N * K * 2) + 1))
+        ws = [torch.randn(N, K, device="cuda").bfloat16() * 0.02 for _ in range(copies)]
+        for B in only_b:
+            x = torch.randn(B, K, device="cuda").bfloat16()
+            it = [0]
+
+            def nxt():
+                it[0] = (it[0] + 1) % copies
+                return ws[it[0]]
+
+            res = {"op": "smallm", "case": name, "B": B, "N": N, "K": K}
+            ref = x.float() @ ws[0].float().t()
+            got = gemm_smallm(x, ws[0])
+            res["max_err"] = float((got.float() - ref).abs().max())
+            res["ours_ms"] = graph_time_ms(lambda: gemm_smallm(x, nxt()))
+            for sp in (1, 2, 4, 8):
+                if sp * 2 <= (K // 64):
+                    res[f"ours_s{sp}_ms"] = graph_time_ms(lambda: gemm_smallm(x, nxt(), splits=sp))
+            res["cublas_ms"] = graph_time_ms(lambda: torch.matmul(x, nxt().t()))
+            if B <= 16 and skinny_gemm(x, ws[0]) is not None:
+                res["prev_ms"] = graph_time_ms(lambda: skinny_gemm(x, nxt()))
+            else:
+                res["prev_ms"] = graph_time_ms(lambda: gemm(x, nxt(), "nt"))
+            bytes_ = N * K * 2 + B * (N + K) * 2
+            res["roofline_ms"] = bytes_ / PEAKS["hbm_gbs"] / 1e6
+            res["frac_of_measured_hbm"] = res["roofline_ms"] / res["ours_ms"]
+            res["vs_cublas"] = res["cublas_ms"] / res["ours_ms"]
+            rows.append(res)
+            print(json.dumps(res), flush=True)
+        del ws
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--only", default="gemm,attn,bw")
@@ -180,6 +248,8 @@ def main():
         bench_attention(rows)
     if "bw" in args.only:
         bench_elementwise(rows)
+    if "smallm" in args.only:
+        bench_smallm(rows)
     if args.md:
         with open(args.md, "w") as f:
             f.write("| op | case | ours | library | ratio / roofline |\n|---|---|---|---|---|\n")
@@ -188,6 +258,10 @@ def main():
                     f.write(f"| gemm {r['layout']} | {r['case']} ({r['M']}x{r['N']}x{r['K']}) | {r['ours_ms']:.3f} ms, "
                             f"{r['ours_tflops']:.0f} TF | cuBLAS {r['cublas_ms']:.3f} ms, {r['cublas_tflops']:.0f} TF | "
                             f"{r['vs_cublas']:.2f}x cuBLAS, {r['frac_of_measured_peak']:.2f} of measured peak |\n")
+                elif r["op"] == "smallm":
+                    f.write(f"| gemm small-M | {r['case']} B={r['B']} ({r['N']}x{r['K']}) | {r['ours_ms'] * 1e3:.1f} us | cuBLAS "
+                            f"{r['cublas_ms'] * 1e3:.1f} us, previous path {r['prev_ms'] * 1e3:.1f} us | {r['vs_cublas']:.2f}x "
+                            f"cuBLAS, {r['frac_of_measured_hbm']:.2f} of measured HBM |\n")
                 elif r["op"] == "flash_attn":
                     f.write(f"| flash_attn | {r['case']} | fwd {r['nxd_fwd_ms']:.3f} ms ({r['nxd_fwd_tflops']:.0f} TF), "
                             f"bwd {r['nxd_bwd_ms']:.3f} ms ({r['nxd_bwd_tflops']:.0f} TF) | SDPA fwd {r['sdpa_fwd_ms']:.3f}"
