@@ -44,6 +44,32 @@ void nxd_count_launches(int n);
         }                                                                       \
     } while (0)
 
+// ---- programmatic dependent launch (PDL) ---------------------------------------
+// The token-generation graph is a chain of short kernels; launch latency and prologues (barrier init, tensor-memory
+// allocation, tensor-map fetch, the first weight tiles) are a large part of every one of them.  Kernels launched through
+// nxd_launch_pdl may START while their predecessor in the stream is still running (as soon as all its CTAs have executed
+// pdl_trigger() or exited); they must call pdl_wait() before they read anything the predecessor wrote and before ANY
+// global write (the predecessor may still be reading a buffer the allocator has handed to this kernel).  Constant data
+// (weights) may be fetched before pdl_wait().  Both instructions are no-ops in a launch without the attribute.
+// NXD_PDL=0 turns the attribute off.
+int nxd_pdl_enabled();
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t nxd_launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                                  Args&&... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = nxd_pdl_enabled();
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+}
+
 // ---- device helpers ---------------------------------------------------------
 typedef __nv_bfloat16 bf16;
 typedef __nv_bfloat162 bf162;
@@ -51,6 +77,12 @@ typedef __nv_bfloat162 bf162;
 struct alignas(16) bf16x8 {
     bf162 v[4];
 };
+
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void prefetch_l2(const void* p) {
+    asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
+}
 
 __device__ __forceinline__ void unpack8(const bf16x8& p, float* f) {
 #pragma unroll

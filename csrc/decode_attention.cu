@@ -57,6 +57,8 @@ __global__ void __launch_bounds__(128) decode_attn_split_kernel(
     constexpr int kV = kE / 8;           // 16-byte pieces per lane and row
     constexpr int kUnroll = 4;
     constexpr int kGroups = 16;          // lane groups per CTA (4 warps x 4)
+    pdl_trigger();
+    pdl_wait();     // q and the newest cache row come from the projection kernel right before this one
     const int group = n_q / n_kv;
     const int chunks = group / G;
     const int b = blockIdx.x / (n_kv * chunks);
@@ -206,6 +208,8 @@ __global__ void __launch_bounds__(128) decode_attn_split_kernel(
 template <int D>
 __global__ void decode_attn_merge_kernel(const float* __restrict__ part_o, const float* __restrict__ part_ml,
                                          bf16* __restrict__ out, int n_splits) {
+    pdl_trigger();
+    pdl_wait();
     const size_t bh = blockIdx.x;  // b * n_q + h
     const int d = threadIdx.x;
     float m = -INFINITY;
@@ -282,8 +286,8 @@ NXD_API int nxd_decode_attn(const void* q, const void* cache_k, const void* cach
     dim3 grid(B * n_kv * (group / G), n_splits);
     const float scale_log2 = scale * 1.4426950408889634f;
 #define NXD_DECODE_LAUNCH(DD, GG)                                                                                  \
-    decode_attn_split_kernel<DD, GG><<<grid, 128, 0, s>>>((const bf16*)q, cv, lengths, part_o, part_ml, n_q, n_kv, \
-                                                          n_splits, scale_log2)
+    NXD_CHECK_CUDA(nxd_launch_pdl(decode_attn_split_kernel<DD, GG>, grid, dim3(128), 0, s, (const bf16*)q, cv, lengths, \
+                                  part_o, part_ml, n_q, n_kv, n_splits, scale_log2))
 #define NXD_DECODE_DISPATCH(DD)                 \
     switch (G) {                                \
         case 1: NXD_DECODE_LAUNCH(DD, 1); break; \
@@ -294,11 +298,13 @@ NXD_API int nxd_decode_attn(const void* q, const void* cache_k, const void* cach
     if (D == 64) {
         NXD_DECODE_DISPATCH(64)
         NXD_LAUNCH_CHECK();
-        decode_attn_merge_kernel<64><<<B * n_q, 64, 0, s>>>(part_o, part_ml, (bf16*)out, n_splits);
+        NXD_CHECK_CUDA(nxd_launch_pdl(decode_attn_merge_kernel<64>, dim3(B * n_q), dim3(64), 0, s, (const float*)part_o,
+                                      (const float*)part_ml, (bf16*)out, n_splits));
     } else {
         NXD_DECODE_DISPATCH(128)
         NXD_LAUNCH_CHECK();
-        decode_attn_merge_kernel<128><<<B * n_q, 128, 0, s>>>(part_o, part_ml, (bf16*)out, n_splits);
+        NXD_CHECK_CUDA(nxd_launch_pdl(decode_attn_merge_kernel<128>, dim3(B * n_q), dim3(128), 0, s, (const float*)part_o,
+                                      (const float*)part_ml, (bf16*)out, n_splits));
     }
 #undef NXD_DECODE_DISPATCH
 #undef NXD_DECODE_LAUNCH

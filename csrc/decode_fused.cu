@@ -33,6 +33,18 @@ __device__ __forceinline__ float dot8f(const uint4& a, const uint4& b, float acc
     return acc;
 }
 
+// Programmatic dependent launch (common.cuh): let the successor start, pull this warp's two weight rows towards L2 (they do
+// not depend on the predecessor), then wait for the predecessor's activations.
+__device__ __forceinline__ void prefetch_rows_then_wait(const bf16* w0, const bf16* w1, int K) {
+    pdl_trigger();
+    const int lane = threadIdx.x & 31;
+    for (int k = lane * 64; k < K; k += 32 * 64) {      // one 128-byte line per lane and step
+        prefetch_l2(w0 + k);
+        prefetch_l2(w1 + k);
+    }
+    pdl_wait();
+}
+
 // xs[b][k] = bf16(x[b][k] * rsqrt(mean(x[b]^2) + eps) * norm_w[k])  (norm_w == nullptr: plain copy).  All threads.
 template <int kB>
 __device__ __forceinline__ void load_normalised(const bf16* __restrict__ x, long long ldx, const bf16* __restrict__ norm_w,
@@ -128,13 +140,14 @@ decode_qkv_kernel(const bf16* __restrict__ x, long long ldx, const bf16* __restr
     extern __shared__ __align__(16) uint8_t dsm[];
     bf16* xs = reinterpret_cast<bf16*>(dsm);
     float* red = reinterpret_cast<float*>(dsm + (size_t)kB * K * sizeof(bf16));
-    load_normalised<kB>(x, ldx, norm_w, eps, B, K, xs, red);
     const int groups = D / 16;
     const int head = blockIdx.x / groups;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int d = (blockIdx.x % groups) * 8 + warp;          // 0 .. D/2 - 1: rotates with d + D/2
     const bf16* w0 = w + ((size_t)head * D + d) * ldw;
     const bf16* w1 = w0 + (size_t)(D / 2) * ldw;
+    prefetch_rows_then_wait(w0, w1, K);
+    load_normalised<kB>(x, ldx, norm_w, eps, B, K, xs, red);
     float a[kB], bq[kB];
     pair_dot<kB>(w0, w1, xs, K, a, bq);
     if (lane != 0) return;
@@ -173,12 +186,13 @@ decode_gate_up_kernel(const bf16* __restrict__ x, long long ldx, const bf16* __r
     extern __shared__ __align__(16) uint8_t dsm[];
     bf16* xs = reinterpret_cast<bf16*>(dsm);
     float* red = reinterpret_cast<float*>(dsm + (size_t)kB * K * sizeof(bf16));
-    load_normalised<kB>(x, ldx, norm_w, eps, B, K, xs, red);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int j = blockIdx.x * 8 + warp;
+    const bf16* w0 = w + (size_t)min(j, I - 1) * ldw;
+    const bf16* w1 = w + ((size_t)I + min(j, I - 1)) * ldw;
+    prefetch_rows_then_wait(w0, w1, K);
+    load_normalised<kB>(x, ldx, norm_w, eps, B, K, xs, red);
     if (j >= I) return;
-    const bf16* w0 = w + (size_t)j * ldw;
-    const bf16* w1 = w + ((size_t)I + j) * ldw;
     float g[kB], u[kB];
     pair_dot<kB>(w0, w1, xs, K, g, u);
     if (lane != 0) return;
@@ -221,9 +235,9 @@ NXD_API int nxd_decode_qkv_rope_cache(const void* x, long long ldx, const void* 
 #define LAUNCH(KB)                                                                                                   \
     do {                                                                                                             \
         if (int rc = set_smem(decode_qkv_kernel<KB>, smem)) return rc;                                               \
-        decode_qkv_kernel<KB><<<grid, kThreads, smem, st>>>((const bf16*)x, ldx, (const bf16*)norm_w, eps,           \
-                                                            (const bf16*)w, ldw, cos_t, sin_t, positions,            \
-                                                            (bf16*)q_out, c, B, K, n_q, n_kv, D);                    \
+        NXD_CHECK_CUDA(nxd_launch_pdl(decode_qkv_kernel<KB>, dim3(grid), dim3(kThreads), smem, st, (const bf16*)x, ldx, \
+                                      (const bf16*)norm_w, eps, (const bf16*)w, ldw, cos_t, sin_t, positions,        \
+                                      (bf16*)q_out, c, B, K, n_q, n_kv, D));                                         \
     } while (0)
     switch (kb) {
         case 1: LAUNCH(1); break;
@@ -249,8 +263,8 @@ NXD_API int nxd_decode_gate_up_swiglu(const void* x, long long ldx, const void* 
 #define LAUNCH(KB)                                                                                                  \
     do {                                                                                                            \
         if (int rc = set_smem(decode_gate_up_kernel<KB>, smem)) return rc;                                          \
-        decode_gate_up_kernel<KB><<<grid, kThreads, smem, st>>>((const bf16*)x, ldx, (const bf16*)norm_w, eps,      \
-                                                                (const bf16*)w, ldw, (bf16*)out, ldo, B, K, I);     \
+        NXD_CHECK_CUDA(nxd_launch_pdl(decode_gate_up_kernel<KB>, dim3(grid), dim3(kThreads), smem, st, (const bf16*)x, \
+                                      ldx, (const bf16*)norm_w, eps, (const bf16*)w, ldw, (bf16*)out, ldo, B, K, I)); \
     } while (0)
     switch (kb) {
         case 1: LAUNCH(1); break;

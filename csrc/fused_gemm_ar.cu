@@ -131,6 +131,20 @@ __global__ void __launch_bounds__(kArThreads) skinny_gemm_ar_kernel(const bf16* 
     float* part = reinterpret_cast<float*>(ar_smem + (size_t)kB * K * sizeof(bf16));
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int k8 = K / 8;
+    const int c0 = (int)blockIdx.x * cols;
+    const int ncols = min(cols, N - c0);
+    // programmatic dependent launch: this kernel may start while its predecessor still runs.  The weights do not depend
+    // on it: pull the rows of the first column pass towards L2, THEN wait for the activations.
+    pdl_trigger();
+    if (warp * 2 < ncols) {
+        const bf16* p0 = w + (size_t)(c0 + warp * 2) * ldw;
+        const bool two = warp * 2 + 1 < ncols;
+        for (int ln = lane; ln * 64 < K; ln += 32) {
+            prefetch_l2(p0 + ln * 64);
+            if (two) prefetch_l2(p0 + ldw + ln * 64);
+        }
+    }
+    pdl_wait();
     for (int i = threadIdx.x; i < kB * k8; i += kArThreads) {
         const int row = i / k8, c = i % k8;
         uint4 v = make_uint4(0u, 0u, 0u, 0u);
@@ -138,8 +152,6 @@ __global__ void __launch_bounds__(kArThreads) skinny_gemm_ar_kernel(const bf16* 
         reinterpret_cast<uint4*>(xs)[i] = v;
     }
     __syncthreads();
-    const int c0 = (int)blockIdx.x * cols;
-    const int ncols = min(cols, N - c0);
     // two columns per warp pass: 2 x (K / 256) independent 16-byte weight loads in flight per lane
     for (int cc = warp * 2; cc < cols; cc += kArWarps * 2) {
         float acc0[kB], acc1[kB];
@@ -206,13 +218,6 @@ __global__ void __launch_bounds__(kArThreads) skinny_splitk_kernel(const bf16* _
     float* part = reinterpret_cast<float*>(ar_smem + (size_t)kB * K * sizeof(bf16));   // [kSplit][kB][kCols]
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int k8 = K / 8;
-    for (int i = threadIdx.x; i < kB * k8; i += kArThreads) {
-        const int row = i / k8, c = i % k8;
-        uint4 v = make_uint4(0u, 0u, 0u, 0u);
-        if (row < B) v = *reinterpret_cast<const uint4*>(x + (size_t)row * ldx + (size_t)c * 8);
-        reinterpret_cast<uint4*>(xs)[i] = v;
-    }
-    __syncthreads();
     const int pair = warp % kPairs, ks = warp / kPairs;
     const int c0 = (int)blockIdx.x * kCols + pair * 2;
     const bool v0 = c0 < N, v1 = c0 + 1 < N;
@@ -220,6 +225,20 @@ __global__ void __launch_bounds__(kArThreads) skinny_splitk_kernel(const bf16* _
     const bf16* w1 = w + (size_t)(v1 ? c0 + 1 : 0) * ldw;
     const int per = (k8 + kSplit - 1) / kSplit;
     const int kbeg = ks * per, kend = min(k8, kbeg + per);
+    // programmatic dependent launch: weights towards L2 first (they do not depend on the predecessor), then wait
+    pdl_trigger();
+    for (int k = kbeg + lane * 8; k < kend; k += 256) {      // one 128-byte line = 8 vectors of 8 bf16
+        prefetch_l2(w0 + (size_t)k * 8);
+        prefetch_l2(w1 + (size_t)k * 8);
+    }
+    pdl_wait();
+    for (int i = threadIdx.x; i < kB * k8; i += kArThreads) {
+        const int row = i / k8, c = i % k8;
+        uint4 v = make_uint4(0u, 0u, 0u, 0u);
+        if (row < B) v = *reinterpret_cast<const uint4*>(x + (size_t)row * ldx + (size_t)c * 8);
+        reinterpret_cast<uint4*>(xs)[i] = v;
+    }
+    __syncthreads();
     float acc0[kB], acc1[kB];
 #pragma unroll
     for (int b = 0; b < kB; ++b) acc0[b] = acc1[b] = 0.f;
@@ -287,6 +306,8 @@ __global__ void __launch_bounds__(kArThreads) skinny16_gemm_ar_kernel(const bf16
     float* part = wpart + kArWarps * 128;                                                      // [16][cols]
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int k8 = K / 8;
+    pdl_trigger();
+    pdl_wait();
     for (int i = threadIdx.x; i < 16 * k8; i += kArThreads) {
         const int row = i / k8, c = i % k8;
         uint4 v = make_uint4(0u, 0u, 0u, 0u);
@@ -408,7 +429,8 @@ int launch_skinny(const bf16* x, const bf16* w, const bf16* residual, bf16* out,
         const size_t smem_k = (size_t)kB * K * sizeof(bf16) + (size_t)4 * kB * 4 * sizeof(float);
         NXD_REQUIRE(smem_k <= 200 * 1024, "skinny_gemm_ar: B %d x K %d does not fit shared memory", B, K);
         NXD_CHECK_CUDA(cudaFuncSetAttribute(skinny_splitk_kernel<kB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_k));
-        skinny_splitk_kernel<kB><<<(N + 3) / 4, kArThreads, smem_k, st>>>(x, w, residual, out, B, N, K, ldx, ldw, ldo);
+        NXD_CHECK_CUDA(nxd_launch_pdl(skinny_splitk_kernel<kB>, dim3((N + 3) / 4), dim3(kArThreads), smem_k, st, x, w, residual,
+                                      out, B, N, K, ldx, ldw, ldo));
         NXD_LAUNCH_CHECK();
         return 0;
     }
@@ -432,7 +454,8 @@ int launch_skinny(const bf16* x, const bf16* w, const bf16* residual, bf16* out,
     }
     NXD_REQUIRE(ar.tp == 1 || (size_t)grid * kB * cols <= ar.slot_elems,
                 "skinny_gemm_ar: staging slot too small (%zu floats, need %zu)", ar.slot_elems, (size_t)grid * kB * cols);
-    skinny_gemm_ar_kernel<kB><<<grid, kArThreads, smem, st>>>(x, w, residual, out, B, N, K, ldx, ldw, ldo, cols, ar);
+    NXD_CHECK_CUDA(nxd_launch_pdl(skinny_gemm_ar_kernel<kB>, dim3(grid), dim3(kArThreads), smem, st, x, w, residual, out, B, N,
+                                  K, ldx, ldw, ldo, cols, ar));
     NXD_LAUNCH_CHECK();
     return 0;
 }
@@ -457,7 +480,8 @@ int launch_skinny16(const bf16* x, const bf16* w, const bf16* residual, bf16* ou
     }
     NXD_REQUIRE(ar.tp == 1 || (size_t)grid * 16 * cols <= ar.slot_elems,
                 "skinny_gemm_ar: staging slot too small (%zu floats, need %zu)", ar.slot_elems, (size_t)grid * 16 * cols);
-    skinny16_gemm_ar_kernel<<<grid, kArThreads, smem, st>>>(x, w, residual, out, B, N, K, ldx, ldw, ldo, cols, ar);
+    NXD_CHECK_CUDA(nxd_launch_pdl(skinny16_gemm_ar_kernel, dim3(grid), dim3(kArThreads), smem, st, x, w, residual, out, B, N, K,
+                                  ldx, ldw, ldo, cols, ar));
     NXD_LAUNCH_CHECK();
     return 0;
 }

@@ -112,6 +112,7 @@ __global__ void __launch_bounds__(kThreads) gemm_smallm_kernel(const __grid_cons
     const bool has_k = kb_begin < kb_end;
     const int tpr = (B + splits - 1) / splits;          // token columns per owner CTA
 
+    pdl_trigger();
     if (warp == 0 && lane == 0) {
         ptx::prefetch_tensormap(&tmap_w);
         ptx::prefetch_tensormap(&tmap_x);
@@ -130,16 +131,28 @@ __global__ void __launch_bounds__(kThreads) gemm_smallm_kernel(const __grid_cons
 
     if (warp == 0) {
         if (lane == 0) {
-            int stage = 0;
-            uint32_t phase = 0;
-            for (int kb = kb_begin; kb < kb_end; ++kb) {
-                ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
+            auto load_w = [&](int kb, int stage) {
                 uint8_t* sw = smem + stage * C::kStageBytes;
                 ptx::mbar_arrive_expect_tx(&full_bar[stage], C::kStageBytes);
                 ptx::tma_load_2d(&tmap_w, &full_bar[stage], sw, kb * kBK, n0);
                 if constexpr (C::kAcc == 2)
                     ptx::tma_load_2d(&tmap_w, &full_bar[stage], sw + kWRows * kBK * 2, kb * kBK, ep.up_row0 + n0);
-                ptx::tma_load_2d(&tmap_x, &full_bar[stage], sw + C::kWBytes, kb * kBK, 0);
+            };
+            auto load_x = [&](int kb, int stage) {
+                ptx::tma_load_2d(&tmap_x, &full_bar[stage], smem + stage * C::kStageBytes + C::kWBytes, kb * kBK, 0);
+            };
+            // the weights do not depend on the previous kernel: fill the pipeline with weight tiles first, then wait
+            // for the activations (programmatic dependent launch)
+            const int pre = min(C::kStages, kb_end - kb_begin);
+            for (int i = 0; i < pre; ++i) load_w(kb_begin + i, i);
+            pdl_wait();
+            for (int i = 0; i < pre; ++i) load_x(kb_begin + i, i);
+            int stage = pre == C::kStages ? 0 : pre;
+            uint32_t phase = pre == C::kStages ? 1 : 0;
+            for (int kb = kb_begin + pre; kb < kb_end; ++kb) {
+                ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
+                load_w(kb, stage);
+                load_x(kb, stage);
                 if (++stage == C::kStages) { stage = 0; phase ^= 1; }
             }
         }
@@ -174,6 +187,7 @@ __global__ void __launch_bounds__(kThreads) gemm_smallm_kernel(const __grid_cons
         // accumulator column b -> slot [split][b / splits] of the staging buffer of CTA b % splits (own buffer when
         // splits == 1); consecutive lanes = consecutive n: 128-byte rows per warp store
         const int q = warp & 3;
+        pdl_wait();     // the epilogue reads the residual / positions and writes global memory
         ptx::mbar_wait(acc_bar, 0);
         ptx::tcgen05_fence_after();
         const int nl = q * 32 + lane;
@@ -370,13 +384,15 @@ int launch(const CUtensorMap& tw, const CUtensorMap& tx, const EpiArgs& ep, int 
     cfg.blockDim = dim3(kThreads);
     cfg.dynamicSmemBytes = C::kSmemBytes;
     cfg.stream = stream;
-    cudaLaunchAttribute attr[1];
+    cudaLaunchAttribute attr[2];
     attr[0].id = cudaLaunchAttributeClusterDimension;
     attr[0].val.clusterDim.x = (unsigned)splits;
     attr[0].val.clusterDim.y = 1;
     attr[0].val.clusterDim.z = 1;
+    attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[1].val.programmaticStreamSerializationAllowed = nxd_pdl_enabled();
     cfg.attrs = attr;
-    cfg.numAttrs = 1;
+    cfg.numAttrs = 2;
     NXD_CHECK_CUDA(cudaLaunchKernelEx(&cfg, kern, tw, tx, ep, B, N, K, splits));
     NXD_LAUNCH_CHECK();
     return 0;

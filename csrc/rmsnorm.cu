@@ -23,6 +23,8 @@ __global__ void rmsnorm_fwd_kernel(const bf16* __restrict__ x, const bf16* __res
                                    bf16* __restrict__ res_out, float* __restrict__ rstd_out, int H,
                                    float eps) {
     __shared__ float red[32];
+    pdl_trigger();
+    pdl_wait();
     const int row = blockIdx.x;
     const int nvec = H >> 3;
     const bf16x8* xr = reinterpret_cast<const bf16x8*>(x + (size_t)row * H);
@@ -215,8 +217,8 @@ NXD_API int nxd_rmsnorm_fwd(const void* x, const void* residual, const void* w, 
     NormCfg c = pick_cfg(H);
     cudaStream_t s = (cudaStream_t)stream;
 #define LAUNCH(V)                                                                                          \
-    rmsnorm_fwd_kernel<V><<<rows, c.threads, 0, s>>>((const bf16*)x, (const bf16*)residual, (const bf16*)w, \
-                                                     (bf16*)y, (bf16*)residual_out, rstd, H, eps)
+    NXD_CHECK_CUDA(nxd_launch_pdl(rmsnorm_fwd_kernel<V>, dim3(rows), dim3(c.threads), 0, s, (const bf16*)x,   \
+                                  (const bf16*)residual, (const bf16*)w, (bf16*)y, (bf16*)residual_out, rstd, H, eps))
     switch (c.vpt) {
         case 1: LAUNCH(1); break;
         case 2: LAUNCH(2); break;

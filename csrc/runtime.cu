@@ -2,6 +2,8 @@
 #include <stdarg.h>
 #include <string.h>
 
+#include <stdlib.h>
+
 #include "common.cuh"
 
 static thread_local char g_err[1024] = {0};
@@ -16,6 +18,15 @@ void nxd_set_error(const char* fmt, ...) {
 NXD_API const char* nxd_last_error() { return g_err; }
 
 static unsigned long long g_launches = 0;   // relaxed counter: exactness across threads is not needed
+int nxd_pdl_enabled() {
+    static int v = -1;
+    if (v < 0) {
+        const char* e = getenv("NXD_PDL");
+        v = (e != nullptr && e[0] == '0') ? 0 : 1;
+    }
+    return v;
+}
+
 void nxd_count_launches(int n) { __atomic_fetch_add(&g_launches, (unsigned long long)n, __ATOMIC_RELAXED); }
 NXD_API unsigned long long nxd_kernel_launches() { return __atomic_load_n(&g_launches, __ATOMIC_RELAXED); }
 
