@@ -11,7 +11,10 @@
 //   its own online-softmax state (see the kernel); partial (m, l, o) per split go to scratch and a second kernel merges.
 // The cache is either contiguous [B, n_kv, S_max, D] or paged [n_pages, n_kv, page, D] with a
 // block table [B, max_pages_per_seq].
+#include <stdlib.h>
+
 #include "common.cuh"
+#include "mma_sync.cuh"
 
 namespace {
 
@@ -205,6 +208,202 @@ __global__ void __launch_bounds__(128) decode_attn_split_kernel(
     }
 }
 
+// Tensor-core variant for GQA groups of 2 .. 16 query heads per KV head (every Llama / Mixtral configuration): the
+// `group` query heads that share a KV head are the M = 16 rows of mma.sync m16n8k16 tiles (rows >= group are zero), so a
+// key costs two tensor-core instructions per 8 keys instead of ~30 FMA-pipe instructions per key, and K / V stream
+// through a per-warp cp.async ring, so the next two tiles are in flight while the current one is multiplied (the FMA
+// kernel above issues its loads and then waits for them, every iteration).
+//
+//   grid = (B * n_kv, n_splits), 4 warps; warp w owns the 32-key tiles w, w + 4, ... of the split and keeps its own
+//   online-softmax state (m, l, O[16 x D]) in registers; the four states merge through shared memory at the end.
+//   Per tile: S[16 x 32] = Q K^T (D / 16 k-steps x 4 key blocks), P = exp2(scale * (S - m)), O += P V
+//   (2 k-steps x D / 8 channel blocks, V fragments through ldmatrix.trans).
+template <int D>
+struct MmaDecodeCfg {
+    static constexpr int kWarps = 4;
+    static constexpr int kTile = 32;                          // keys per warp step
+    static constexpr int kStages = 3;
+    static constexpr int kTileBytes = kTile * D * 2;          // one of K or V
+    static constexpr int kWarpBytes = kStages * 2 * kTileBytes;
+    static constexpr int kSmemBytes = kWarps * kWarpBytes;    // 96 KB (D = 64) / 192 KB (D = 128)
+    static_assert(kWarps * 16 * (D + 4) * 4 + kWarps * 32 * 4 <= kSmemBytes, "merge buffers alias the ring");
+};
+
+template <int D>
+__global__ void __launch_bounds__(128) decode_attn_mma_kernel(
+    const bf16* __restrict__ q,  // [B, n_q, D]
+    CacheView cache, const int* __restrict__ lengths, float* __restrict__ part_o,  // [B, n_q, splits, D]
+    float* __restrict__ part_ml,                                                   // [B, n_q, splits, 2]
+    int n_q, int n_kv, int n_splits, float scale_log2) {
+    using C = MmaDecodeCfg<D>;
+    extern __shared__ __align__(128) uint8_t dsmem[];
+    pdl_trigger();
+    pdl_wait();     // q and the newest cache row come from the projection kernel right before this one
+    const int group = n_q / n_kv;
+    const int b = blockIdx.x / n_kv, hk = blockIdx.x % n_kv;
+    const int h0 = hk * group;
+    const int split = blockIdx.y;
+    const int len = lengths[b];
+    const int per = ((len + n_splits - 1) / n_splits + C::kTile - 1) / C::kTile * C::kTile;   // whole tiles per split
+    const int start = split * per;
+    const int end = min(len, start + per);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int g4 = lane >> 2, t4 = lane & 3;
+    const uint32_t ring = (uint32_t)__cvta_generic_to_shared(dsmem) + warp * C::kWarpBytes;
+
+    // Q fragments: rows = query heads of this KV head (zero rows beyond the group)
+    uint32_t qa[D / 16][4];
+    {
+        const uint32_t* q0 = reinterpret_cast<const uint32_t*>(q + ((size_t)b * n_q + h0 + g4) * D);
+        const uint32_t* q1 = reinterpret_cast<const uint32_t*>(q + ((size_t)b * n_q + h0 + g4 + 8) * D);
+        const bool r0 = g4 < group, r1 = g4 + 8 < group;
+#pragma unroll
+        for (int kk = 0; kk < D / 16; ++kk) {
+            qa[kk][0] = r0 ? q0[kk * 8 + t4] : 0u;
+            qa[kk][1] = r1 ? q1[kk * 8 + t4] : 0u;
+            qa[kk][2] = r0 ? q0[kk * 8 + 4 + t4] : 0u;
+            qa[kk][3] = r1 ? q1[kk * 8 + 4 + t4] : 0u;
+        }
+    }
+    float m_run[2] = {-INFINITY, -INFINITY}, l_run[2] = {0.f, 0.f};
+    float o[D / 8][4];
+#pragma unroll
+    for (int j = 0; j < D / 8; ++j) o[j][0] = o[j][1] = o[j][2] = o[j][3] = 0.f;
+
+    const int n_tiles = end > start ? (end - start + C::kTile - 1) / C::kTile : 0;
+    const int my_tiles = n_tiles > warp ? (n_tiles - warp + C::kWarps - 1) / C::kWarps : 0;
+    auto issue = [&](int i) {       // tile i of this warp -> ring stage i % kStages (an empty group beyond the last tile)
+        if (i < my_tiles) {
+            const int key0 = start + (warp + i * C::kWarps) * C::kTile;
+            const uint32_t sk = ring + (i % C::kStages) * 2 * C::kTileBytes, sv = sk + C::kTileBytes;
+            constexpr int CH = D / 8;
+#pragma unroll
+            for (int j = 0; j < C::kTile * CH / 32; ++j) {
+                const int idx = lane + j * 32;
+                const int r = idx / CH, c = idx % CH;
+                const int pos = key0 + r;
+                const bool ok = pos < end;
+                const size_t off = row_ptr(cache.k, cache, b, hk, ok ? pos : start, D) - cache.k + c * 8;
+                mma::cp_async16(mma::tile_addr<D>(sk, r, c), cache.k + off, ok);
+                mma::cp_async16(mma::tile_addr<D>(sv, r, c), cache.v + off, ok);   // rows past the end: zeros (0 * NaN)
+            }
+        }
+        mma::cp_async_commit();
+    };
+#pragma unroll
+    for (int i = 0; i < C::kStages - 1; ++i) issue(i);
+
+    for (int i = 0; i < my_tiles; ++i) {
+        issue(i + C::kStages - 1);
+        mma::cp_async_wait<C::kStages - 1>();
+        __syncwarp();
+        const int key0 = start + (warp + i * C::kWarps) * C::kTile;
+        const uint32_t sk = ring + (i % C::kStages) * 2 * C::kTileBytes, sv = sk + C::kTileBytes;
+        float s[4][4];
+#pragma unroll
+        for (int nt = 0; nt < 4; ++nt) s[nt][0] = s[nt][1] = s[nt][2] = s[nt][3] = 0.f;
+#pragma unroll
+        for (int kk = 0; kk < D / 16; ++kk) {
+#pragma unroll
+            for (int nb = 0; nb < 2; ++nb) {
+                uint32_t kb[4];
+                mma::load_b<D>(kb, sk, nb * 16, kk, lane);
+                mma::mma16816(s[2 * nb], qa[kk], kb[0], kb[1]);
+                mma::mma16816(s[2 * nb + 1], qa[kk], kb[2], kb[3]);
+            }
+        }
+        if (key0 + C::kTile > end) {      // the last tile of the split: keys past the end do not take part
+#pragma unroll
+            for (int nt = 0; nt < 4; ++nt)
+#pragma unroll
+                for (int c = 0; c < 4; ++c)
+                    if (key0 + nt * 8 + 2 * t4 + (c & 1) >= end) s[nt][c] = -INFINITY;
+        }
+        float alpha[2], mneg[2];
+#pragma unroll
+        for (int r = 0; r < 2; ++r) {
+            float mx = fmaxf(s[0][2 * r], s[0][2 * r + 1]);
+#pragma unroll
+            for (int nt = 1; nt < 4; ++nt) mx = fmaxf(mx, fmaxf(s[nt][2 * r], s[nt][2 * r + 1]));
+            mx = mma::quad_max(mx);
+            const float m_new = fmaxf(m_run[r], mx);      // finite: the first key of a tile is always inside the split
+            alpha[r] = exp2f((m_run[r] - m_new) * scale_log2);
+            m_run[r] = m_new;
+            mneg[r] = -m_new * scale_log2;
+            l_run[r] *= alpha[r];
+        }
+        uint32_t pa[2][4];
+#pragma unroll
+        for (int nt = 0; nt < 4; ++nt) {
+            const float p0 = exp2f(fmaf(s[nt][0], scale_log2, mneg[0])), p1 = exp2f(fmaf(s[nt][1], scale_log2, mneg[0]));
+            const float p2 = exp2f(fmaf(s[nt][2], scale_log2, mneg[1])), p3 = exp2f(fmaf(s[nt][3], scale_log2, mneg[1]));
+            l_run[0] += p0 + p1;
+            l_run[1] += p2 + p3;
+            pa[nt >> 1][(nt & 1) * 2] = mma::pack2(p0, p1);
+            pa[nt >> 1][(nt & 1) * 2 + 1] = mma::pack2(p2, p3);
+        }
+#pragma unroll
+        for (int j = 0; j < D / 8; ++j) {
+            o[j][0] *= alpha[0];
+            o[j][1] *= alpha[0];
+            o[j][2] *= alpha[1];
+            o[j][3] *= alpha[1];
+        }
+#pragma unroll
+        for (int ks = 0; ks < 2; ++ks) {
+#pragma unroll
+            for (int dj = 0; dj < D / 16; ++dj) {
+                uint32_t vb[4];
+                mma::load_bt<D>(vb, sv, ks * 16, dj, lane);
+                mma::mma16816(o[2 * dj], pa[ks], vb[0], vb[1]);
+                mma::mma16816(o[2 * dj + 1], pa[ks], vb[2], vb[3]);
+            }
+        }
+        __syncwarp();       // every lane is done with this stage before the next issue() overwrites it
+    }
+    mma::cp_async_wait<0>();
+    __syncthreads();        // the ring is dead: reuse it for the merge of the four warp states
+
+    float* s_o = reinterpret_cast<float*>(dsmem);                          // [warps][16][D + 4]
+    float* s_ml = s_o + C::kWarps * 16 * (D + 4);                           // [warps][16][2]
+#pragma unroll
+    for (int r = 0; r < 2; ++r) {
+        const float l = mma::quad_sum(l_run[r]);
+        const int row = g4 + 8 * r;
+        if (t4 == 0) {
+            s_ml[(warp * 16 + row) * 2] = m_run[r] * scale_log2;           // log2 domain, like the merge kernel expects
+            s_ml[(warp * 16 + row) * 2 + 1] = l;
+        }
+#pragma unroll
+        for (int j = 0; j < D / 8; ++j) {
+            float* dst = s_o + (warp * 16 + row) * (D + 4) + j * 8 + 2 * t4;
+            dst[0] = o[j][2 * r];
+            dst[1] = o[j][2 * r + 1];
+        }
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < group * D; i += blockDim.x) {
+        const int g = i / D, d = i % D;
+        float m = -INFINITY;
+#pragma unroll
+        for (int w = 0; w < C::kWarps; ++w) m = fmaxf(m, s_ml[(w * 16 + g) * 2]);
+        float l = 0.f, acc = 0.f;
+#pragma unroll
+        for (int w = 0; w < C::kWarps; ++w) {
+            const float mw = s_ml[(w * 16 + g) * 2];
+            const float wgt = (mw == -INFINITY) ? 0.f : exp2f(mw - m);
+            l += s_ml[(w * 16 + g) * 2 + 1] * wgt;
+            acc += s_o[(w * 16 + g) * (D + 4) + d] * wgt;
+        }
+        const size_t base = (((size_t)b * n_q + h0 + g) * n_splits + split);
+        part_o[base * D + d] = acc;
+        if (d == 0) {
+            part_ml[base * 2 + 0] = m;
+            part_ml[base * 2 + 1] = l;
+        }
+    }
+}
+
 template <int D>
 __global__ void decode_attn_merge_kernel(const float* __restrict__ part_o, const float* __restrict__ part_ml,
                                          bf16* __restrict__ out, int n_splits) {
@@ -294,6 +493,44 @@ NXD_API int nxd_decode_attn(const void* q, const void* cache_k, const void* cach
         case 2: NXD_DECODE_LAUNCH(DD, 2); break; \
         case 3: NXD_DECODE_LAUNCH(DD, 3); break; \
         default: NXD_DECODE_LAUNCH(DD, 4); break; \
+    }
+    // GQA groups of 2 .. 16 heads: tensor-core kernel (NXD_DECODE_ATTN=fma keeps the FMA kernel for comparison)
+    static const bool force_fma = [] {
+        const char* e = getenv("NXD_DECODE_ATTN");
+        return e != nullptr && e[0] == 'f';
+    }();
+    const bool use_mma = group >= 2 && group <= 16 && !force_fma;
+    if (use_mma) {
+        dim3 mgrid(B * n_kv, n_splits);
+        if (D == 64) {
+            static bool configured = false;
+            if (!configured) {
+                NXD_CHECK_CUDA(cudaFuncSetAttribute(decode_attn_mma_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                    MmaDecodeCfg<64>::kSmemBytes));
+                configured = true;
+            }
+            NXD_CHECK_CUDA(nxd_launch_pdl(decode_attn_mma_kernel<64>, mgrid, dim3(128), MmaDecodeCfg<64>::kSmemBytes, s,
+                                          (const bf16*)q, cv, lengths, part_o, part_ml, n_q, n_kv, n_splits, scale_log2));
+        } else {
+            static bool configured = false;
+            if (!configured) {
+                NXD_CHECK_CUDA(cudaFuncSetAttribute(decode_attn_mma_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                    MmaDecodeCfg<128>::kSmemBytes));
+                configured = true;
+            }
+            NXD_CHECK_CUDA(nxd_launch_pdl(decode_attn_mma_kernel<128>, mgrid, dim3(128), MmaDecodeCfg<128>::kSmemBytes, s,
+                                          (const bf16*)q, cv, lengths, part_o, part_ml, n_q, n_kv, n_splits, scale_log2));
+        }
+        NXD_LAUNCH_CHECK();
+        if (D == 64) {
+            NXD_CHECK_CUDA(nxd_launch_pdl(decode_attn_merge_kernel<64>, dim3(B * n_q), dim3(64), 0, s, (const float*)part_o,
+                                          (const float*)part_ml, (bf16*)out, n_splits));
+        } else {
+            NXD_CHECK_CUDA(nxd_launch_pdl(decode_attn_merge_kernel<128>, dim3(B * n_q), dim3(128), 0, s,
+                                          (const float*)part_o, (const float*)part_ml, (bf16*)out, n_splits));
+        }
+        NXD_LAUNCH_CHECK();
+        return 0;
     }
     if (D == 64) {
         NXD_DECODE_DISPATCH(64)

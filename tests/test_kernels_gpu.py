@@ -345,6 +345,33 @@ def test_decode_attention_contiguous_and_paged(D):
             assert torch.equal(pk2[table[b, p // page], :, p % page], nk[b, :, t])
 
 
+@pytest.mark.parametrize("D", [64, 128])
+@pytest.mark.parametrize("group", [1, 2, 3, 4, 8, 16, 32])
+def test_decode_attention_gqa_groups(group, D):
+    """Groups of 2 .. 16 query heads per KV head take the tensor-core kernel (heads = rows of the mma tile, rows past the
+    group are zero), 1 and > 16 the FMA kernel; lengths around the 32-key tile and the split boundaries, and large score
+    magnitudes (the running max must rescale)."""
+    from neuronx_distributed_llama3_2_b200.ops import attention as A
+
+    _lib()
+    torch.manual_seed(group * 10 + D)
+    Hkv, Smax = 2, 1024
+    lens = torch.tensor([1, 31, 32, 33, 127, 129, 500, 1024, 1023], device="cuda")
+    B = lens.numel()
+    ck = torch.randn(B, Hkv, Smax, D, device="cuda").bfloat16()
+    cv = torch.randn(B, Hkv, Smax, D, device="cuda").bfloat16()
+    ck[:, :, 100:110] *= 4.0                       # a few dominant keys in the middle of the sequence
+    cv[:, :, Smax - 8:] = float("nan")            # rows past every length < Smax must never be read into the sum
+    lens_safe = torch.minimum(lens, torch.tensor(Smax - 8, device="cuda"))
+    q = torch.randn(B, Hkv * group, D, device="cuda").bfloat16()
+    out = A.decode_attention(q, ck, cv, lens_safe)
+    ref = A.decode_attention_ref(q, ck, cv, lens_safe, 1.0 / math.sqrt(D))
+    assert torch.isfinite(out.float()).all()
+    assert _rel_err(out, ref) < 1e-2
+    for b in range(B):
+        assert _rel_err(out[b], ref[b]) < 2e-2, (b, int(lens_safe[b]))
+
+
 # ---------------------------------------------------------------------------------------------
 # flash attention fwd / bwd
 # ---------------------------------------------------------------------------------------------
