@@ -22,10 +22,13 @@
 //   warps 2-5  epilogue: tcgen05.ld -> fp32 staging in shared memory (aliases the drained pipeline stages)
 //
 // Split-K over a thread-block CLUSTER: narrow layers (N = 2048 -> 16 weight slabs) are cut into up to 8 K slices, one
-// per CTA of a cluster, and the partial sums are added through distributed shared memory: token column b belongs to CTA
-// b % splits of the cluster; every CTA PUSHES its partial column into slot [own rank] of the owner's staging buffer
-// (st.shared::cluster, fire and forget: no remote-load latency), one cluster barrier, then each owner adds its slots in
-// rank order (deterministic), adds the residual and writes 16-byte bf16 vectors.  No workspace, no atomics, one launch.
+// per CTA of a cluster, and the partial sums are added through distributed shared memory: token columns
+// [r * tpr, (r + 1) * tpr) belong to CTA r of the cluster.  Every CTA lays its accumulator out per owner in its own shared
+// memory (the drained pipeline stages) and sends each owner its block with ONE bulk asynchronous copy
+// (cp.async.bulk.shared::cluster.shared::cta) that completes on the owner's mbarrier -- measured: scalar
+// st.shared::cluster pushes of the same data took 4.8 us for 64 tokens, the copies take 0.5.  Each owner then adds its
+// slots in rank order (deterministic), adds the residual and writes 16-byte bf16 vectors.  No workspace, no atomics, no
+// cluster barrier after start-up, one launch.
 #include "decode_common.cuh"
 #include "gemm_tcgen05.cuh"
 #include "ptx.cuh"
@@ -68,11 +71,13 @@ struct Cfg {
     // two accumulators: one CTA per SM with 128-160 KB of weights in flight
     static constexpr int kStages = kAcc == 2 ? (BT <= 32 ? 5 : 4) : (BT == 16 ? 5 : BT == 32 ? 4 : BT == 64 ? 3 : 4);
     static constexpr int kPipeBytes = kStages * kStageBytes;
-    // fp32 [accumulator][slot = source rank * tokens_per_rank + local token][128]; NOT aliased with the pipeline: peers
-    // push into it while this CTA may still be streaming
+    // receive buffer, fp32 [accumulator][slot = source rank * tokens_per_rank + local token][128]; NOT aliased with the
+    // pipeline: peers copy into it while this CTA may still be streaming.  The send buffer (same size, [accumulator]
+    // [owner][local token][128]) aliases the pipeline stages, which are dead once the last MMA has retired.
     static constexpr int kStagingBytes = kAcc * BT * kWRows * 4;
     static constexpr int kBarOffset = kPipeBytes + kStagingBytes;
-    static constexpr int kSmemBytes = kBarOffset + (2 * kStages + 1) * 8 + 16 + 1024;
+    static constexpr int kSmemBytes = kBarOffset + (2 * kStages + 2) * 8 + 16 + 1024;
+    static_assert(kStagingBytes <= kPipeBytes, "the send buffer aliases the pipeline stages");
     static constexpr int kTmemCols = kAcc * BT < 32 ? 32 : kAcc * BT;
     static_assert(kStageBytes % 1024 == 0, "stages must keep the 1024-byte swizzle alignment");
     static_assert(kSmemBytes <= 232448, "shared memory budget exceeded");
@@ -83,11 +88,28 @@ __device__ __forceinline__ uint32_t map_to_cta(uint32_t local_addr, uint32_t cta
     asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(local_addr), "r"(cta));
     return remote;
 }
-__device__ __forceinline__ void st_cluster_f32(uint32_t remote_addr, float v) {
-    asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(remote_addr), "f"(v) : "memory");
+// bytes of this CTA's shared memory -> shared memory of a CTA of the cluster, completing (complete_tx) on ITS mbarrier
+__device__ __forceinline__ void bulk_copy_to_cta(uint32_t remote_dst, uint32_t local_src, uint32_t bytes,
+                                                 uint32_t remote_bar) {
+    asm volatile("cp.async.bulk.shared::cluster.shared::cta.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     remote_dst),
+                 "r"(local_src), "r"(bytes), "r"(remote_bar)
+                 : "memory");
 }
+__device__ __forceinline__ void cluster_wait() { asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory"); }
 __device__ __forceinline__ void epilogue_bar() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
 __device__ __forceinline__ float round_bf16(float v) { return __bfloat162float(__float2bfloat16(v)); }
+
+// Phase stamps of CTA 0 (SM clock) for kernel tuning: build with -DNXD_SMALLM_TRACE, read with nxd_smallm_trace().
+#ifdef NXD_SMALLM_TRACE
+__device__ long long g_smallm_trace[16];
+#define TRACE_STAMP(i, cond)                                   \
+    do {                                                       \
+        if (blockIdx.x == 0 && (cond)) g_smallm_trace[i] = clock64(); \
+    } while (0)
+#else
+#define TRACE_STAMP(i, cond) do { } while (0)
+#endif
 
 template <int BT, int EPI>
 __global__ void __launch_bounds__(kThreads) gemm_smallm_kernel(const __grid_constant__ CUtensorMap tmap_w,
@@ -99,8 +121,10 @@ __global__ void __launch_bounds__(kThreads) gemm_smallm_kernel(const __grid_cons
     uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + C::kBarOffset);
     uint64_t* empty_bar = full_bar + C::kStages;
     uint64_t* acc_bar = empty_bar + C::kStages;
-    uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(acc_bar + 1);
-    float* staging = reinterpret_cast<float*>(smem + C::kPipeBytes);
+    uint64_t* recv_bar = acc_bar + 1;
+    uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(recv_bar + 1);
+    float* staging = reinterpret_cast<float*>(smem + C::kPipeBytes);      // receive buffer
+    float* sendbuf = reinterpret_cast<float*>(smem);                      // aliases the pipeline
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int split = splits > 1 ? (int)ptx::cluster_ctarank() : 0;
@@ -112,7 +136,21 @@ __global__ void __launch_bounds__(kThreads) gemm_smallm_kernel(const __grid_cons
     const bool has_k = kb_begin < kb_end;
     const int tpr = (B + splits - 1) / splits;          // token columns per owner CTA
 
+    TRACE_STAMP(0, threadIdx.x == 0);
     pdl_trigger();
+    // warp 0 lane 0 owns the barriers and the TMA queue: it starts the weight stream right after initialising them,
+    // before the CTA (or, with split-K, the cluster) has met -- the weights do not depend on the previous kernel either
+    auto load_w = [&](int kb, int stage) {
+        uint8_t* sw = smem + stage * C::kStageBytes;
+        ptx::mbar_arrive_expect_tx(&full_bar[stage], C::kStageBytes);
+        ptx::tma_load_2d(&tmap_w, &full_bar[stage], sw, kb * kBK, n0);
+        if constexpr (C::kAcc == 2)
+            ptx::tma_load_2d(&tmap_w, &full_bar[stage], sw + kWRows * kBK * 2, kb * kBK, ep.up_row0 + n0);
+    };
+    auto load_x = [&](int kb, int stage) {
+        ptx::tma_load_2d(&tmap_x, &full_bar[stage], smem + stage * C::kStageBytes + C::kWBytes, kb * kBK, 0);
+    };
+    const int pre = min(C::kStages, kb_end - kb_begin);
     if (warp == 0 && lane == 0) {
         ptx::prefetch_tensormap(&tmap_w);
         ptx::prefetch_tensormap(&tmap_x);
@@ -121,31 +159,26 @@ __global__ void __launch_bounds__(kThreads) gemm_smallm_kernel(const __grid_cons
             ptx::mbar_init(&empty_bar[i], 1);
         }
         ptx::mbar_init(acc_bar, 1);
+        ptx::mbar_init(recv_bar, 1);
         ptx::fence_barrier_init();
+        // every CTA of the cluster sends this one a [tpr][128] fp32 block per accumulator
+        if (splits > 1 && split * tpr < B) ptx::mbar_arrive_expect_tx(recv_bar, (uint32_t)(splits * C::kAcc * tpr * kWRows * 4));
+        for (int i = 0; i < pre; ++i) load_w(kb_begin + i, i);
     }
     if (warp == 1) ptx::tmem_alloc<1>(tmem_ptr_smem, C::kTmemCols);
     ptx::tcgen05_fence_before();
     __syncthreads();
+    // split-K: a peer may only send once this CTA's receive barrier exists.  Every thread arrives at the cluster barrier
+    // now and waits for it after its main loop (measured: a full cluster barrier here costs ~1 us of start-up)
+    if (splits > 1) asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
     ptx::tcgen05_fence_after();
     const uint32_t tmem_base = *tmem_ptr_smem;
+    TRACE_STAMP(1, threadIdx.x == 0);
 
     if (warp == 0) {
         if (lane == 0) {
-            auto load_w = [&](int kb, int stage) {
-                uint8_t* sw = smem + stage * C::kStageBytes;
-                ptx::mbar_arrive_expect_tx(&full_bar[stage], C::kStageBytes);
-                ptx::tma_load_2d(&tmap_w, &full_bar[stage], sw, kb * kBK, n0);
-                if constexpr (C::kAcc == 2)
-                    ptx::tma_load_2d(&tmap_w, &full_bar[stage], sw + kWRows * kBK * 2, kb * kBK, ep.up_row0 + n0);
-            };
-            auto load_x = [&](int kb, int stage) {
-                ptx::tma_load_2d(&tmap_x, &full_bar[stage], smem + stage * C::kStageBytes + C::kWBytes, kb * kBK, 0);
-            };
-            // the weights do not depend on the previous kernel: fill the pipeline with weight tiles first, then wait
-            // for the activations (programmatic dependent launch)
-            const int pre = min(C::kStages, kb_end - kb_begin);
-            for (int i = 0; i < pre; ++i) load_w(kb_begin + i, i);
-            pdl_wait();
+            pdl_wait();         // the activations come from the previous kernel (programmatic dependent launch)
+            TRACE_STAMP(2, true);
             for (int i = 0; i < pre; ++i) load_x(kb_begin + i, i);
             int stage = pre == C::kStages ? 0 : pre;
             uint32_t phase = pre == C::kStages ? 1 : 0;
@@ -157,6 +190,7 @@ __global__ void __launch_bounds__(kThreads) gemm_smallm_kernel(const __grid_cons
             }
         }
         __syncwarp();
+        if (splits > 1) cluster_wait();
     } else if (warp == 1) {
         if (lane == 0) {
             constexpr uint32_t idesc = ptx::make_idesc_bf16(kWRows, BT, 0, 0);
@@ -164,6 +198,7 @@ __global__ void __launch_bounds__(kThreads) gemm_smallm_kernel(const __grid_cons
             uint32_t phase = 0;
             for (int kb = kb_begin; kb < kb_end; ++kb) {
                 ptx::mbar_wait(&full_bar[stage], phase);
+                TRACE_STAMP(3, kb == kb_begin);
                 ptx::tcgen05_fence_after();
                 const uint32_t sw = ptx::smem_u32(smem + stage * C::kStageBytes);
                 const uint32_t sx = sw + C::kWBytes;
@@ -180,21 +215,24 @@ __global__ void __launch_bounds__(kThreads) gemm_smallm_kernel(const __grid_cons
                 ptx::umma_commit(&empty_bar[stage]);
                 if (++stage == C::kStages) { stage = 0; phase ^= 1; }
             }
+            TRACE_STAMP(4, true);
             ptx::umma_commit(acc_bar);   // arrives when every MMA above has retired (immediately when there were none)
         }
         __syncwarp();
+        if (splits > 1) cluster_wait();
     } else {
-        // accumulator column b -> slot [split][b / splits] of the staging buffer of CTA b % splits (own buffer when
-        // splits == 1); consecutive lanes = consecutive n: 128-byte rows per warp store
+        // accumulator column b -> (owner b / tpr, local token b % tpr): straight into the receive buffer when there is
+        // no split-K, else into the send buffer [owner][local token][128]; consecutive lanes = consecutive n:
+        // conflict-free 128-byte rows per warp store
         const int q = warp & 3;
         pdl_wait();     // the epilogue reads the residual / positions and writes global memory
         ptx::mbar_wait(acc_bar, 0);
+        TRACE_STAMP(5, threadIdx.x == 64);
         ptx::tcgen05_fence_after();
         const int nl = q * 32 + lane;
 #pragma unroll
         for (int a = 0; a < C::kAcc; ++a) {
-            float* region = staging + a * (BT * kWRows);
-            const uint32_t my_slot0 = ptx::smem_u32(region + (split * tpr) * kWRows + nl);
+            float* region = (splits == 1 ? staging : sendbuf) + a * (BT * kWRows);
 #pragma unroll
             for (int c = 0; c < (BT + 31) / 32; ++c) {
                 if (c * 32 >= B) break;
@@ -206,29 +244,37 @@ __global__ void __launch_bounds__(kThreads) gemm_smallm_kernel(const __grid_cons
 #pragma unroll
                     for (int j = 0; j < 32; ++j) r[j] = 0u;
                 }
-                if (splits == 1) {
+                // token b sits at row b of the buffer in both cases: owner * tpr + local = b
 #pragma unroll
-                    for (int j = 0; j < 32; ++j)
-                        if (c * 32 + j < B) region[(c * 32 + j) * kWRows + nl] = __uint_as_float(r[j]);
-                } else {
-                    // splits is a power of two <= 8: the owner of column b is b % splits
-#pragma unroll
-                    for (int j = 0; j < 32; ++j) {
-                        const int b = c * 32 + j;
-                        if (b < B) {
-                            const uint32_t addr = my_slot0 + (uint32_t)(b / splits) * (kWRows * 4);
-                            st_cluster_f32(map_to_cta(addr, (uint32_t)(b & (splits - 1))), __uint_as_float(r[j]));
-                        }
+                for (int j = 0; j < 32; ++j)
+                    if (c * 32 + j < B) region[(c * 32 + j) * kWRows + nl] = __uint_as_float(r[j]);
+            }
+        }
+        TRACE_STAMP(6, threadIdx.x == 64);
+        if (splits > 1) {
+            ptx::fence_proxy_async();       // the stores above are read by the bulk-copy engine
+            cluster_wait();                 // every peer has initialised its receive barrier
+            epilogue_bar();
+            if (threadIdx.x == 64) {
+                const uint32_t bytes = (uint32_t)(tpr * kWRows * 4);
+                for (int a = 0; a < C::kAcc; ++a) {
+                    for (int o = 0; o < splits; ++o) {
+                        if (o * tpr >= B) break;     // owners without tokens expect nothing ... see expect_tx below
+                        const uint32_t src = ptx::smem_u32(sendbuf + a * (BT * kWRows) + o * tpr * kWRows);
+                        const uint32_t dst = ptx::smem_u32(staging + a * (BT * kWRows) + (split * tpr) * kWRows);
+                        bulk_copy_to_cta(map_to_cta(dst, (uint32_t)o), src, bytes, map_to_cta(ptx::smem_u32(recv_bar),
+                                                                                                (uint32_t)o));
                     }
                 }
+                ptx::bulk_commit();
             }
+            // the blocks of all peers have landed in this CTA's receive buffer
+            if (split * tpr < B) ptx::mbar_wait(recv_bar, 0);
         }
     }
 
-    // every CTA of the cluster has pushed its partial sums (release / acquire at cluster scope)
-    ptx::tcgen05_fence_before();
-    if (splits > 1) ptx::cluster_sync();
-    else __syncthreads();
+    TRACE_STAMP(7, threadIdx.x == 64);
+    if (splits == 1) __syncthreads();
 
     if (warp >= 2) {
         // owner pass: 16 threads x 8 columns cover the 128 weight rows of one token, 8 tokens per sweep
@@ -256,7 +302,7 @@ __global__ void __launch_bounds__(kThreads) gemm_smallm_kernel(const __grid_cons
                              (residual == nullptr ||
                               ((ldr & 7) == 0 && (reinterpret_cast<uintptr_t>(residual) & 15) == 0));
             for (int j = jrow; j < tpr; j += 8) {
-                const int b = j * splits + split;
+                const int b = split * tpr + j;
                 if (b >= B) break;
                 float acc[8];
                 reduce8(0, j, acc);
@@ -282,7 +328,7 @@ __global__ void __launch_bounds__(kThreads) gemm_smallm_kernel(const __grid_cons
         } else if constexpr (EPI == kEpiSwiglu) {
             // N = I here (rows of ONE of the two stacked matrices); out [B, I], I % 8 == 0
             for (int j = jrow; j < tpr; j += 8) {
-                const int b = j * splits + split;
+                const int b = split * tpr + j;
                 if (b >= B) break;
                 float g[8], u[8];
                 reduce8(0, j, g);
@@ -300,7 +346,7 @@ __global__ void __launch_bounds__(kThreads) gemm_smallm_kernel(const __grid_cons
             // pass 1: reduced, bf16-rounded head values back into slot 0; pass 2: rotate with the partner half
             if (splits > 1) {
                 for (int j = jrow; j < tpr; j += 8) {
-                    if (j * splits + split >= B) break;
+                    if (split * tpr + j >= B) break;
                     float acc[8];
                     reduce8(0, j, acc);
                     float4* p = reinterpret_cast<float4*>(staging + j * kWRows + n8);
@@ -315,7 +361,7 @@ __global__ void __launch_bounds__(kThreads) gemm_smallm_kernel(const __grid_cons
             const int dd = second ? d - half : d;                       // rotation index 0 .. D/2 - 1
             const int partner = second ? n8 - half : n8 + half;         // tile-local column of the other half
             for (int j = jrow; j < tpr; j += 8) {
-                const int b = j * splits + split;
+                const int b = split * tpr + j;
                 if (b >= B) break;
                 if (n >= N) continue;
                 float v[8];
@@ -355,16 +401,21 @@ __global__ void __launch_bounds__(kThreads) gemm_smallm_kernel(const __grid_cons
         }
     }
 
-    // owners read only their own shared memory after the barrier, so no second cluster barrier is needed before exit
+    // owners read only their own shared memory; a CTA leaves once its outgoing copies have read the send buffer and
+    // (waited above) its incoming blocks have landed
+    TRACE_STAMP(8, threadIdx.x == 64);
+    if (splits > 1 && threadIdx.x == 64) ptx::bulk_wait_read<0>();   // outgoing copies have read the send buffer
     __syncthreads();
+    TRACE_STAMP(9, threadIdx.x == 0);
     if (warp == 1) ptx::tmem_dealloc<1>(tmem_base, C::kTmemCols);
 }
 
-int pick_splits(int n_tiles, int nkb, int bt) {
-    // aim at 128-200 CTAs, keep at least two k blocks per slice; the 128-row configuration is one CTA per SM
-    const int max_splits = bt == 128 ? 4 : kMaxSplits;
+int pick_splits(int n_tiles, int nkb, int ctas_per_sm) {
+    // the largest power of two <= 8 that keeps the grid within one resident wave and leaves two k blocks per slice
+    // (measured at the Llama-3.2 decode shapes: 16-24 slabs -> 8, 64 -> 4, 128 -> 2, the 1002 slabs of the LM head -> 1)
+    const int slots = nxd_num_sms() * ctas_per_sm;
     int s = 1;
-    while (s < max_splits && n_tiles * s * 2 <= 200 && nkb / (s * 2) >= 2) s *= 2;
+    while (s < kMaxSplits && n_tiles * s * 2 <= slots && nkb / (s * 2) >= 2) s *= 2;
     return s;
 }
 
@@ -409,7 +460,7 @@ int run(const void* x, const void* w, const EpiArgs& ep, int B, int n_rows, int 
     NXD_REQUIRE(((uintptr_t)x & 15) == 0 && ((uintptr_t)w & 15) == 0, "gemm_smallm: operands must be 16-byte aligned");
     const int bt = B <= 16 ? 16 : B <= 32 ? 32 : B <= 64 ? 64 : 128;
     const int n_tiles = (n_rows + kWRows - 1) / kWRows, nkb = (K + kBK - 1) / kBK;
-    if (splits <= 0) splits = pick_splits(n_tiles, nkb, bt);
+    if (splits <= 0) splits = pick_splits(n_tiles, nkb, (EPI == kEpiSwiglu || bt == 128) ? 1 : 2);
     NXD_REQUIRE(splits == 1 || splits == 2 || splits == 4 || splits == 8, "gemm_smallm: splits=%d", splits);
     CUtensorMap tw, tx;
     int rc = make_tmap_2d(&tw, w, (uint64_t)K, (uint64_t)w_rows, (uint64_t)ldw, kBK, kWRows);
@@ -476,4 +527,14 @@ NXD_API int nxd_smallm_gate_up_swiglu(const void* x, long long ldx, const void* 
     ep.ldo = ldo;
     ep.up_row0 = I;
     return run<kEpiSwiglu>(x, w, ep, B, I, 2 * I, K, ldx, ldw, splits, (cudaStream_t)stream);
+}
+
+// Tuning aid: the phase stamps of CTA 0 of the last launch (zeros unless built with -DNXD_SMALLM_TRACE).
+NXD_API int nxd_smallm_trace(long long* out16) {
+#ifdef NXD_SMALLM_TRACE
+    NXD_CHECK_CUDA(cudaMemcpyFromSymbol(out16, g_smallm_trace, sizeof(long long) * 16));
+#else
+    for (int i = 0; i < 16; ++i) out16[i] = 0;
+#endif
+    return 0;
 }
