@@ -486,37 +486,53 @@ fa_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
 
 // Delta = rowsum(O * dO) and a padded copy of the LSE ([B*Hq, Sq_pad], +inf / 0 in the padding) so that the main
 // kernel can fetch 64-row slices with 256-byte bulk copies and get masking of out-of-range query rows for free.
-__global__ void fa_bwd_tc_prep_kernel(const bf16* __restrict__ o, const bf16* __restrict__ dout,
-                                      const float* __restrict__ lse, float* __restrict__ lse_pad,
-                                      float* __restrict__ delta_pad, long long o_sb, long long o_sh, long long o_ss,
-                                      long long do_sb, long long do_sh, long long do_ss, int B, int Hq, int Sq,
-                                      int Sq_pad, int D) {
+// kD / 8 lanes own a row (16-byte vectors), a warp has 4 x (32 / lanes-per-row) rows in flight: the kernel streams
+// 2 x [B, Hq, Sq, D] bf16 once and is bound by HBM, not by load latency.
+template <int kD>
+__global__ void __launch_bounds__(256) fa_bwd_tc_prep_kernel(const bf16* __restrict__ o, const bf16* __restrict__ dout,
+                                                             const float* __restrict__ lse, float* __restrict__ lse_pad,
+                                                             float* __restrict__ delta_pad, long long o_sb,
+                                                             long long o_sh, long long o_ss, long long do_sb,
+                                                             long long do_sh, long long do_ss, int B, int Hq, int Sq,
+                                                             int Sq_pad) {
+    constexpr int L = kD / 8, R = 32 / L, U = 4;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const long long r = (long long)blockIdx.x * (blockDim.x >> 5) + warp;
+    const int sub = lane / L, l = lane % L;
     const long long total = (long long)B * Hq * Sq_pad;
-    if (r >= total) return;
-    const int i = (int)(r % Sq_pad);
-    const int h = (int)((r / Sq_pad) % Hq);
-    const int b = (int)(r / ((long long)Sq_pad * Hq));
-    if (i >= Sq) {
-        if (lane == 0) {
-            lse_pad[r] = INFINITY;
-            delta_pad[r] = 0.f;
+    const long long r0 = ((long long)blockIdx.x * 8 + warp) * (R * U) + sub;
+    bf16x8 a[U], g[U];
+    bool valid[U];
+    long long lse_idx[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+        const long long r = r0 + u * R;
+        const int i = (int)(r % Sq_pad);
+        const int h = (int)((r / Sq_pad) % Hq);
+        const long long b = r / ((long long)Sq_pad * Hq);
+        valid[u] = r < total && i < Sq;
+        lse_idx[u] = (b * Hq + h) * Sq + i;
+        if (valid[u]) {
+            a[u] = reinterpret_cast<const bf16x8*>(o + b * o_sb + h * o_sh + (long long)i * o_ss)[l];
+            g[u] = reinterpret_cast<const bf16x8*>(dout + b * do_sb + h * do_sh + (long long)i * do_ss)[l];
         }
-        return;
     }
-    const bf16* op = o + b * o_sb + h * o_sh + (long long)i * o_ss;
-    const bf16* dp = dout + b * do_sb + h * do_sh + (long long)i * do_ss;
-    float acc = 0.f;
-    for (int c = 0; c < D / 64; ++c) {
-        const float2 a = __bfloat1622float2(reinterpret_cast<const bf162*>(op)[lane + c * 32]);
-        const float2 g = __bfloat1622float2(reinterpret_cast<const bf162*>(dp)[lane + c * 32]);
-        acc += a.x * g.x + a.y * g.y;
-    }
-    acc = warp_sum(acc);
-    if (lane == 0) {
-        delta_pad[r] = acc;
-        lse_pad[r] = lse[((long long)b * Hq + h) * Sq + i];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+        float acc = 0.f;
+        if (valid[u]) {
+            float fa[8], fg[8];
+            unpack8(a[u], fa);
+            unpack8(g[u], fg);
+#pragma unroll
+            for (int e = 0; e < 8; ++e) acc = fmaf(fa[e], fg[e], acc);
+        }
+#pragma unroll
+        for (int off = L / 2; off > 0; off >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, off);
+        const long long r = r0 + u * R;
+        if (l == 0 && r < total) {
+            delta_pad[r] = valid[u] ? acc : 0.f;
+            lse_pad[r] = valid[u] ? lse[lse_idx[u]] : INFINITY;
+        }
     }
 }
 
@@ -538,24 +554,32 @@ __global__ void fa_bwd_tc_dq_convert_kernel(const float* __restrict__ acc, bf16*
 }
 
 // d-major fp32 accumulator [B, Hq, D, Sq_pad] -> strided bf16 dq [.., Sq, D]: 32 query rows per block through a padded
-// shared tile (coalesced 128-byte reads along q, 16-byte writes along d)
+// shared tile.  Reads: 128-byte rows along q, all D / 8 of a thread in flight; writes: two adjacent lanes write the two
+// 16-byte halves of a 32-byte sector, 16 query rows per warp (tile reads 2-way conflicted at most).
+template <int kD>
 __global__ void __launch_bounds__(256)
 fa_bwd_tc_dq_transpose_kernel(const float* __restrict__ acc, bf16* __restrict__ dq, long long sb, long long sh,
-                              long long ss, int Hq, int Sq, int Sq_pad, int D) {
-    __shared__ float tile[128][33];
+                              long long ss, int Hq, int Sq, int Sq_pad) {
+    __shared__ float tile[kD][33];
     const int q0 = blockIdx.x * 32, h = blockIdx.y, b = blockIdx.z;
-    const float* src = acc + ((long long)b * Hq + h) * D * Sq_pad;
+    const float* src = acc + ((long long)b * Hq + h) * kD * Sq_pad;
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-    for (int d = w; d < D; d += 8) tile[d][lane] = (q0 + lane < Sq_pad) ? src[(long long)d * Sq_pad + q0 + lane] : 0.f;
+    float v[kD / 8];
+    const bool in = q0 + lane < Sq_pad;
+#pragma unroll
+    for (int j = 0; j < kD / 8; ++j) v[j] = in ? src[(long long)(w + 8 * j) * Sq_pad + q0 + lane] : 0.f;
+#pragma unroll
+    for (int j = 0; j < kD / 8; ++j) tile[w + 8 * j][lane] = v[j];
     __syncthreads();
-    const int chunks = D / 8;                    // 16-byte chunks per output row
-    for (int t = threadIdx.x; t < 32 * chunks; t += 256) {
-        const int r = t / chunks, c = t % chunks;
-        if (q0 + r >= Sq) continue;
+    const int r = (w & 1) * 16 + (lane >> 1);
+    if (q0 + r >= Sq) return;
+    bf16* dst = dq + b * sb + h * sh + (long long)(q0 + r) * ss;
+#pragma unroll
+    for (int c = (w >> 1) * 2 + (lane & 1); c < kD / 8; c += 8) {
         float f[8];
 #pragma unroll
         for (int e = 0; e < 8; ++e) f[e] = tile[c * 8 + e][r];
-        reinterpret_cast<bf16x8*>(dq + b * sb + h * sh + (long long)(q0 + r) * ss)[c] = pack8(f);
+        reinterpret_cast<bf16x8*>(dst)[c] = pack8(f);
     }
 }
 
@@ -615,9 +639,15 @@ static int bwd_tc_impl(const void* q, const void* k, const void* v, const void* 
     p.nsplit = dkv_accum ? nxd_flash_attn_bwd_tc_num_splits(B, Hq, Hkv, Sq, Sk) : 1;
     {
         const long long rows = (long long)B * Hq * p.Sq_pad;
-        fa_bwd_tc_prep_kernel<<<(unsigned)((rows + 7) / 8), 256, 0, st>>>(
-            (const bf16*)o, (const bf16*)dout, lse, lse_pad, delta_pad, strides[9], strides[10], strides[11], strides[12],
-            strides[13], strides[14], B, Hq, Sq, p.Sq_pad, D);
+        if (D == 128) {
+            fa_bwd_tc_prep_kernel<128><<<(unsigned)((rows + 63) / 64), 256, 0, st>>>(
+                (const bf16*)o, (const bf16*)dout, lse, lse_pad, delta_pad, strides[9], strides[10], strides[11],
+                strides[12], strides[13], strides[14], B, Hq, Sq, p.Sq_pad);
+        } else {
+            fa_bwd_tc_prep_kernel<64><<<(unsigned)((rows + 127) / 128), 256, 0, st>>>(
+                (const bf16*)o, (const bf16*)dout, lse, lse_pad, delta_pad, strides[9], strides[10], strides[11],
+                strides[12], strides[13], strides[14], B, Hq, Sq, p.Sq_pad);
+        }
         NXD_LAUNCH_CHECK();
     }
     CUtensorMap tq, tdo, tk, tv, tdk, tdv, tdq, tdka, tdva;
@@ -667,8 +697,12 @@ static int bwd_tc_impl(const void* q, const void* k, const void* v, const void* 
     }
     {
         dim3 g((unsigned)((Sq + 31) / 32), (unsigned)Hq, (unsigned)B);
-        fa_bwd_tc_dq_transpose_kernel<<<g, 256, 0, st>>>(dq_accum, (bf16*)dq, strides[15], strides[16], strides[17], Hq,
-                                                         Sq, p.Sq_pad, D);
+        if (D == 128)
+            fa_bwd_tc_dq_transpose_kernel<128><<<g, 256, 0, st>>>(dq_accum, (bf16*)dq, strides[15], strides[16],
+                                                                  strides[17], Hq, Sq, p.Sq_pad);
+        else
+            fa_bwd_tc_dq_transpose_kernel<64><<<g, 256, 0, st>>>(dq_accum, (bf16*)dq, strides[15], strides[16],
+                                                                 strides[17], Hq, Sq, p.Sq_pad);
         NXD_LAUNCH_CHECK();
     }
     return 0;

@@ -29,6 +29,8 @@
 // st.shared::cluster pushes of the same data took 4.8 us for 64 tokens, the copies take 0.5.  Each owner then adds its
 // slots in rank order (deterministic), adds the residual and writes 16-byte bf16 vectors.  No workspace, no atomics, no
 // cluster barrier after start-up, one launch.
+#include <stdlib.h>
+
 #include "decode_common.cuh"
 #include "gemm_tcgen05.cuh"
 #include "ptx.cuh"
@@ -460,7 +462,14 @@ int run(const void* x, const void* w, const EpiArgs& ep, int B, int n_rows, int 
     NXD_REQUIRE(((uintptr_t)x & 15) == 0 && ((uintptr_t)w & 15) == 0, "gemm_smallm: operands must be 16-byte aligned");
     const int bt = B <= 16 ? 16 : B <= 32 ? 32 : B <= 64 ? 64 : 128;
     const int n_tiles = (n_rows + kWRows - 1) / kWRows, nkb = (K + kBK - 1) / kBK;
-    if (splits <= 0) splits = pick_splits(n_tiles, nkb, (EPI == kEpiSwiglu || bt == 128) ? 1 : 2);
+    if (splits <= 0) {
+        static const int forced = [] {      // NXD_SMALLM_SPLITS=1|2|4|8: debugging / tuning override of the heuristic
+            const char* e = getenv("NXD_SMALLM_SPLITS");
+            return e != nullptr ? atoi(e) : 0;
+        }();
+        splits = forced > 0 ? forced : pick_splits(n_tiles, nkb, (EPI == kEpiSwiglu || bt == 128) ? 1 : 2);
+        while (splits > 1 && nkb / splits < 1) splits >>= 1;
+    }
     NXD_REQUIRE(splits == 1 || splits == 2 || splits == 4 || splits == 8, "gemm_smallm: splits=%d", splits);
     CUtensorMap tw, tx;
     int rc = make_tmap_2d(&tw, w, (uint64_t)K, (uint64_t)w_rows, (uint64_t)ldw, kBK, kWRows);

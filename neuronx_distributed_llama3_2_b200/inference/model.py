@@ -190,9 +190,7 @@ class KVCacheInferenceMixin:
         if not (decode_fused.qualifies_batched(x) if batched else decode_fused.qualifies(x)):
             return False
         if ps.get_tensor_model_parallel_size() > 1:
-            # the batched kernels have no all-reduce epilogue: tensor-parallel batches above 8 rows take the generic
-            # layer (its GEMMs still run on the small-M tensor-core kernel, ops/linear.py)
-            return (not batched) and backend.fused_comm_enabled() and ps.get_symm_mem_context("tp") is not None
+            return backend.fused_comm_enabled() and ps.get_symm_mem_context("tp") is not None
         return True
 
     def _decode_i32(self, positions, seq_ids):
@@ -217,34 +215,45 @@ class KVCacheInferenceMixin:
     def _layer_batched_decode(self, i: int, layer, hidden, residual, positions, seq_ids, lengths):
         """One token per sequence for 9 .. 128 sequences on the small-M tensor-core kernels (``csrc/gemm_smallm.cu``):
         RMSNorm | QKV GEMM+RoPE+cache write | attention (split, merge) | o_proj+residual | RMSNorm | gate/up+SwiGLU |
-        down_proj+residual -- eight launches, no copies between them."""
+        down_proj+residual -- eight launches, no copies between them.  Tensor parallel: the two row-parallel GEMMs are
+        followed by the one-shot all-reduce and the residual moves into the fused add+RMSNorm (ten launches)."""
         from ..ops import activation, decode_fused
+        from ..ops.fused_comm import oneshot_all_reduce
         from ..ops.gemm import gemm_smallm
 
+        tp = ps.get_tensor_model_parallel_size()
+        ctx = ps.get_symm_mem_context("tp") if tp > 1 else None
+
+        def all_reduce(y):
+            r = oneshot_all_reduce(ctx, y)
+            return r if r is not None else mappings.reduce_from_tensor_model_parallel_region(y)
+
         B = hidden.shape[0]
-        x = hidden.reshape(B, -1)
-        if residual is not None:
-            x = x + residual.reshape(B, -1)
         attn, mlp = layer.self_attn, layer.mlp
         nq, nkv, D = attn.q_heads_local, attn.kv_heads_local, attn.head_dim
-        cos, sin = self._rope(x.device)
+        cos, sin = self._rope(hidden.device)
         ck, cv = self.kv_cache.layer(i)
         kc = self.kv_cache
         pos, sid = self._decode_i32(positions, seq_ids)
-        xn = norm_ops.rms_norm(x, layer.input_layernorm.weight, layer.input_layernorm.variance_epsilon)
+        xn, x = self._add_norm(layer.input_layernorm, hidden.reshape(B, -1),
+                               residual.reshape(B, -1) if residual is not None else None)
         q = decode_fused.qkv_rope_cache_batched(xn, attn.qkv_proj.weight_qkv, cos, sin, pos, ck, cv, nq, nkv, D,
                                                 seq_ids=sid, block_table=kc.block_table if kc.paged else None,
                                                 page_size=kc.page_size if kc.paged else 0)
-        o = self._decode_attention(q, ck, cv, seq_ids, lengths)
-        x2 = gemm_smallm(o.reshape(B, nq * D), attn.o_proj.weight, residual=x)
-        xn2 = norm_ops.rms_norm(x2, layer.post_attention_layernorm.weight,
-                                layer.post_attention_layernorm.variance_epsilon)
+        o = self._decode_attention(q, ck, cv, seq_ids, lengths).reshape(B, nq * D)
+        if tp == 1:
+            x2 = gemm_smallm(o, attn.o_proj.weight, residual=x)
+            xn2 = norm_ops.rms_norm(x2, layer.post_attention_layernorm.weight,
+                                    layer.post_attention_layernorm.variance_epsilon)
+        else:
+            xn2, x2 = self._add_norm(layer.post_attention_layernorm, all_reduce(gemm_smallm(o, attn.o_proj.weight)), x)
         if B <= decode_fused.BATCHED_SWIGLU_MAX_ROWS:
             act = decode_fused.gate_up_swiglu_batched(xn2, mlp.gate_up_proj.weight)
         else:
             act = activation.swiglu(gemm_smallm(xn2, mlp.gate_up_proj.weight))
-        x3 = gemm_smallm(act, mlp.down_proj.weight, residual=x2)
-        return x3.reshape(B, 1, -1), None
+        if tp == 1:
+            return gemm_smallm(act, mlp.down_proj.weight, residual=x2).reshape(B, 1, -1), None
+        return all_reduce(gemm_smallm(act, mlp.down_proj.weight)).reshape(B, 1, -1), x2.reshape(B, 1, -1)
 
     def _layer_fused_decode(self, i: int, layer, hidden, residual, positions, seq_ids, lengths):
         """One token per sequence: RMSNorm+QKV+RoPE+cache write | attention (split, merge) | o_proj+residual |
@@ -301,6 +310,10 @@ class KVCacheInferenceMixin:
         assert self.kv_cache is not None, "call init_kv_cache() first"
         B, T = input_ids.shape
         prefill = T > 1
+        # the int32 position / cache-line copies are shared by the layers of ONE forward only: a captured graph is
+        # replayed with the same static tensor objects but new contents, so the conversion has to be part of every
+        # forward (and of every capture)
+        self._decode_i32_memo = None
         default_lines = seq_ids is None
         hidden = self._embed(input_ids)
         lengths = (position_ids[:, -1] + 1).to(torch.int32)

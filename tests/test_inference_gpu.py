@@ -110,7 +110,8 @@ def test_batched_decode_layer_matches_library_arm(B, paged, head_dim):
         assert ((a - b).norm() / b.norm()).item() < 2e-2
 
 
-def test_runner_cuda_graphs_match_eager():
+@pytest.mark.parametrize("batch", [2, 12, 40])     # 2: fused GEMV layer, 12 / 40: batched small-M tensor-core layer
+def test_runner_cuda_graphs_match_eager(batch):
     from neuronx_distributed_llama3_2_b200.inference import InferenceConfig, InferenceRunner
     from neuronx_distributed_llama3_2_b200.models import LlamaForCausalLM
 
@@ -118,18 +119,24 @@ def test_runner_cuda_graphs_match_eager():
     dev = torch.device("cuda")
     train = LlamaForCausalLM(_cfg(), device=dev)
     sd = {k: v.detach().cpu().clone() for k, v in train.state_dict().items()}
-    outs = []
+    outs, caches = [], []
     for graphs in (False, True):
-        ic = InferenceConfig(batch_size=2, max_context_length=128, seq_len=256, buckets=[64, 128], max_new_tokens=8,
+        ic = InferenceConfig(batch_size=batch, max_context_length=128, seq_len=256, buckets=[64, 128], max_new_tokens=8,
                              use_cuda_graphs=graphs)
         runner = InferenceRunner(_cfg(), ic, checkpoint_loader=lambda: sd, device=dev)
         runner.trace()
         g = torch.Generator(device="cpu").manual_seed(5)
-        prompts = torch.randint(1, 1024, (2, 50), generator=g).to(dev)
+        prompts = torch.randint(1, 1024, (batch, 50), generator=g).to(dev)
         outs.append(runner.generate(prompts, max_new_tokens=8))
         outs.append(runner.generate(prompts, max_new_tokens=8))     # replay: same result again
+        torch.cuda.synchronize()
+        caches.append([tuple(t[:, :, :57].float().clone() for t in runner.model.kv_cache.layer(i)) for i in range(2)])
     assert torch.equal(outs[0], outs[1]) and torch.equal(outs[2], outs[3])
     assert torch.equal(outs[0], outs[2]), (outs[0][:, -8:], outs[2][:, -8:])
+    # the tokens of a random model barely react to a misplaced cache row: compare the caches themselves (a graph that
+    # replays the positions of its capture writes every new K / V row to the wrong place)
+    for (ke, ve), (kg, vg) in zip(*caches):
+        assert torch.equal(ke, kg) and torch.equal(ve, vg)
     rep = runner.benchmark_sampling(prompt_len=64, new_tokens=8, n_runs=2)
     assert rep["ttft_ms_p50"] > 0 and rep["decode_tokens_per_s"] > 0
 
@@ -140,7 +147,7 @@ def _free_port():
         return s.getsockname()[1]
 
 
-def _tp_worker(rank, world, port, modes):
+def _tp_worker(rank, world, port, modes, batch=2):
     import torch.distributed as dist
 
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world),
@@ -157,7 +164,7 @@ def _tp_worker(rank, world, port, modes):
     full = LlamaForCausalLM(_cfg(), device=torch.device("cpu"))
     sd = {k: v.detach().clone() for k, v in full.state_dict().items()}
     g = torch.Generator(device="cpu").manual_seed(9)
-    prompts = torch.randint(1, 1024, (2, 60), generator=g).to(dev)
+    prompts = torch.randint(1, 1024, (batch, 60), generator=g).to(dev)
     with torch.no_grad():   # single-process forward of the unsharded model = the oracle for the prefill logits
         ref = full.to(dev)(prompts).transpose(0, 1)[:, -1].float()
     del full
@@ -171,7 +178,7 @@ def _tp_worker(rank, world, port, modes):
             from neuronx_distributed_llama3_2_b200.ops import backend as _be
 
             _be.set_backends(fused_comm=(fused == "1"))
-            ic = InferenceConfig(tp_degree=world, batch_size=2, max_context_length=128, seq_len=256, buckets=[64, 128],
+            ic = InferenceConfig(tp_degree=world, batch_size=batch, max_context_length=128, seq_len=256, buckets=[64, 128],
                                  max_new_tokens=8, use_cuda_graphs=graphs)
             runner = InferenceRunner(_cfg(), ic, checkpoint_loader=lambda: sd, device=dev)
             runner.trace()
@@ -179,7 +186,7 @@ def _tp_worker(rank, world, port, modes):
             again = runner.generate(prompts, max_new_tokens=8)
             assert torch.equal(res[name], again), name
             # prefill logits against the unsharded model
-            pos = torch.arange(60, device=dev).unsqueeze(0).expand(2, 60)
+            pos = torch.arange(60, device=dev).unsqueeze(0).expand(batch, 60)
             _, logits = runner.model.forward_infer(prompts, pos, return_logits=True)
             assert (logits.float() - ref).abs().max().item() < 0.1, name
             gathered = [torch.empty_like(res[name]) for _ in range(world)]
@@ -197,11 +204,12 @@ def _tp_worker(rank, world, port, modes):
         dist.destroy_process_group()
 
 
+@pytest.mark.parametrize("batch", [2, 12], ids=["b2", "b12"])     # 12 rows: the batched small-M layer + one-shot all-reduce
 @pytest.mark.parametrize("modes", [("nccl_eager", "fused_eager"), ("fused_eager", "fused_graphs")],
                          ids=["eager", "graphs"])
-def test_tp2_inference_fused_allreduce(modes):
+def test_tp2_inference_fused_allreduce(modes, batch):
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs")
     from conftest import spawn_gpu_workers
 
-    spawn_gpu_workers(_tp_worker, (2, _free_port(), modes), 2, deadline_s=90.0)
+    spawn_gpu_workers(_tp_worker, (2, _free_port(), modes, batch), 2, deadline_s=90.0)
