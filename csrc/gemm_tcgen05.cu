@@ -267,14 +267,15 @@ static int dispatch_layout(int layout, const CUtensorMap& ta, const CUtensorMap&
 }
 
 int pick_block_n(int M, int N) {
-    // Fewer, fatter tiles amortise operand traffic (256 x 256 per CTA pair is the sweet spot), but a
-    // partial last wave wastes SMs: estimate cost = waves * tile_n for both candidates.
+    // Fewer, fatter tiles amortise operand traffic (256 x 256 per CTA pair is the sweet spot).  Measured on every
+    // Llama-3.2 training / prefill shape (tools/bench_kernels.py, NXD_GEMM_CASES=wgrad,dgrad,prefill): a wave of
+    // 256 x 128 tiles takes ~0.95 of the time of a wave of 256 x 256 tiles (the A operand traffic is the same), so the
+    // narrow tile only pays when it does not add a wave.
     const int clusters = nxd_num_sms() / 2;
     const int mt = (M + kTileM - 1) / kTileM;
     const long t256 = (long)mt * ((N + 255) / 256), t128 = (long)mt * ((N + 127) / 128);
     const long w256 = (t256 + clusters - 1) / clusters, w128 = (t128 + clusters - 1) / clusters;
-    // a 128-wide tile runs at ~0.55x the time of a 256-wide one (less operand reuse)
-    return (w256 * 100 <= w128 * 55) ? 256 : 128;
+    return (w256 * 100 <= w128 * 95) ? 256 : 128;
 }
 
 int run(int layout, const void* a, const void* b, long long lda, long long ldb, const EpilogueArgs& ep, int M, int N,

@@ -60,7 +60,18 @@ def bench_gemm(rows):
         ("3B gate_up fwd tp8", "nt", 8192, 2048, 3072), ("3B down fwd tp8", "nt", 8192, 3072, 1024),
         ("3B qkv fwd tp8", "nt", 8192, 640, 3072), ("1B gate_up fwd tp8", "nt", 8192, 2048, 2048),
         ("square 8192", "nt", 8192, 8192, 8192), ("square 4096", "nt", 4096, 4096, 4096),
+        ("3B qkv wgrad tp1", "tn", 5120, 3072, 8192), ("3B o wgrad tp1", "tn", 3072, 3072, 8192),
+        ("3B qkv dgrad tp1", "nn", 8192, 3072, 5120), ("3B o dgrad tp1", "nn", 8192, 3072, 3072),
+        ("3B down dgrad tp1", "nn", 8192, 8192, 3072),
+        ("3B qkv prefill2048", "nt", 2048, 5120, 3072), ("3B o prefill2048", "nt", 2048, 3072, 3072),
+        ("3B gate_up prefill2048", "nt", 2048, 16384, 3072), ("3B down prefill2048", "nt", 2048, 3072, 8192),
+        ("1B qkv prefill2048", "nt", 2048, 3072, 2048), ("1B o prefill2048", "nt", 2048, 2048, 2048),
+        ("1B gate_up prefill2048", "nt", 2048, 16384, 2048), ("1B down prefill2048", "nt", 2048, 2048, 8192),
+        ("1B qkv prefill b16", "nt", 32768, 3072, 2048), ("1B down prefill b16", "nt", 32768, 2048, 8192),
     ]
+    only = os.environ.get("NXD_GEMM_CASES", "")
+    if only:
+        shapes = [s for s in shapes if any(o in s[0] for o in only.split(","))]
     for name, layout, M, N, K in shapes:
         pool = max(2, int(math.ceil(300e6 / ((M * K + N * K) * 2))))
         pool = min(pool, 8)
