@@ -65,5 +65,27 @@ if which in ("all", "decode"):
         skinny_gemm(act, wd, residual=xd)
     q16 = torch.randn(16, nq, D, device="cuda").bfloat16()
     A.decode_attention(q16, ck, cv, torch.full((16,), 2049, device="cuda", dtype=torch.int32))
+if which in ("all", "decode_batched"):
+    # batched token generation (Llama-3.2-1B, 64 sequences at position 2048): the small-M tensor-core GEMM family and
+    # the tensor-core decode attention.  Weights are cycled so that every launch streams them from HBM.
+    from neuronx_distributed_llama3_2_b200.ops import decode_fused, rope as rope_ops
+    from neuronx_distributed_llama3_2_b200.ops.gemm import gemm_smallm
+
+    B, H, nq, nkv, D, S, I = 64, 2048, 32, 8, 64, 4096, 8192
+    xn = torch.randn(B, H, device="cuda").bfloat16()
+    cos, sin = rope_ops.build_rope_cache(S, D, 500000.0, None, device="cuda")
+    ck = torch.randn(B, nkv, S, D, device="cuda").bfloat16()
+    cv = torch.randn(B, nkv, S, D, device="cuda").bfloat16()
+    pos = torch.full((B,), 2048, device="cuda", dtype=torch.int32)
+    wq = [(torch.randn((nq + 2 * nkv) * D, H, device="cuda") * 0.02).bfloat16() for _ in range(24)]
+    wo = [(torch.randn(H, nq * D, device="cuda") * 0.02).bfloat16() for _ in range(36)]
+    wg = [(torch.randn(2 * I, H, device="cuda") * 0.02).bfloat16() for _ in range(6)]
+    wd = [(torch.randn(H, I, device="cuda") * 0.02).bfloat16() for _ in range(10)]
+    for i in range(max(len(wq), len(wo))):      # last launches of each kernel see cold weights
+        qd = decode_fused.qkv_rope_cache_batched(xn, wq[i % len(wq)], cos, sin, pos, ck, cv, nq, nkv, D)
+        o = A.decode_attention(qd, ck, cv, pos + 1)
+        x2 = gemm_smallm(o.reshape(B, nq * D), wo[i % len(wo)], residual=xn)
+        act = decode_fused.gate_up_swiglu_batched(x2, wg[i % len(wg)])
+        gemm_smallm(act, wd[i % len(wd)], residual=x2)
 torch.cuda.synchronize()
 print("done")
