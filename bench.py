@@ -489,11 +489,27 @@ def main():
     # numbers above are final; if the inference half raises, the error text is reported instead (rc stays 0 only
     # because the training half is complete -- the error is in the line).
     if not args.no_inference and os.environ.get("NXD_BENCH_INFERENCE", "1") == "1":
+        budget = float(os.environ.get("NXD_BENCH_INFERENCE_BUDGET", "420"))
+
+        def give_up():
+            # a rank that hangs inside the inference half (a collective that never completes) must not take the
+            # finished training numbers with it: report them with the error and leave without NCCL teardown
+            if rank == 0:
+                out["inference"] = {"error": f"inference half did not finish within {budget + 300:.0f} s"}
+                out["wall_s"] = time.time() - t_start
+                print(json.dumps(out), flush=True)
+            os._exit(0)
+
+        import threading
+
+        watchdog = threading.Timer(budget + 300.0, give_up)
+        watchdog.daemon = True
+        watchdog.start()
         try:
-            budget = float(os.environ.get("NXD_BENCH_INFERENCE_BUDGET", "420"))
             inf = inference_metric(args, dev, world, rank, time.time() + budget)
         except Exception as e:  # noqa: BLE001 - the training number must survive
             inf = {"error": f"{type(e).__name__}: {e}"[:300]}
+        watchdog.cancel()
         if rank == 0:
             out["inference"] = inf
     if rank == 0:
