@@ -15,7 +15,10 @@
 //                              whose bf16 parameter output is PUSHED into every rank's flat parameter buffer -- the
 //                              all-gather is the store of the update itself.
 //
-// The global gradient norm sits between the two (it needs every rank's shard), so the step stays two-phase.
+// The global gradient norm sits between the two (it needs every rank's shard), so the step stays two-phase; the LOCAL
+// part of the norm is not a pass of its own, though: the reduce kernel squares what it has just summed and leaves two
+// partial sums per block (elements before / after `split_at`: tensor-parallel-sharded and replicated parameters are
+// weighted differently in the norm), which nxd_zero1_sumsq_finish adds up in a fixed order (bitwise reproducible).
 // Rendezvous: the caller brackets the pair with nxd_symm_barrier (all gradients complete before the first pull; all
 // parameter slices landed before the next forward).
 #include "common.cuh"
@@ -36,8 +39,52 @@ __device__ __forceinline__ uint4 ld_nc_16(const void* p) {
 }
 
 // grad dtype bf16: 8 elements per 16-byte load; two loads per peer in flight per thread
-__global__ void __launch_bounds__(256) zero1_reduce_shard_bf16_kernel(const ZPeers g, size_t lo, size_t n, float* __restrict__ out) {
+// block-level finish of the two running sums of squares: partials[2 * block] / [2 * block + 1]
+__device__ __forceinline__ void store_block_sumsq(float ss0, float ss1, float* __restrict__ partials) {
+    __shared__ float red[2][8];
+    ss0 = warp_sum(ss0);
+    ss1 = warp_sum(ss1);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (lane == 0) {
+        red[0][warp] = ss0;
+        red[1][warp] = ss1;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        float a = 0.f, b = 0.f;
+#pragma unroll
+        for (int w = 0; w < 8; ++w) {
+            a += red[0][w];
+            b += red[1][w];
+        }
+        partials[2 * blockIdx.x] = a;
+        partials[2 * blockIdx.x + 1] = b;
+    }
+}
+
+// acc[0 .. cnt) are local elements base .. base + cnt: squares go to ss0 before split_at, to ss1 from split_at on
+template <int kCnt>
+__device__ __forceinline__ void add_squares(const float* acc, size_t base, size_t split_at, float& ss0, float& ss1) {
+    float t = 0.f;
+#pragma unroll
+    for (int e = 0; e < kCnt; ++e) t = fmaf(acc[e], acc[e], t);
+    if (base + kCnt <= split_at) {
+        ss0 += t;
+    } else if (base >= split_at) {
+        ss1 += t;
+    } else {
+#pragma unroll
+        for (int e = 0; e < kCnt; ++e) {
+            if (base + e < split_at) ss0 = fmaf(acc[e], acc[e], ss0);
+            else ss1 = fmaf(acc[e], acc[e], ss1);
+        }
+    }
+}
+
+__global__ void __launch_bounds__(256) zero1_reduce_shard_bf16_kernel(const ZPeers g, size_t lo, size_t n, float* __restrict__ out,
+                                                                      size_t split_at, float* __restrict__ partials) {
     const size_t nvec = n >> 3;
+    float ss0 = 0.f, ss1 = 0.f;
     for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (size_t)gridDim.x * blockDim.x) {
         uint4 v[kZMaxDp];
 #pragma unroll
@@ -61,11 +108,15 @@ __global__ void __launch_bounds__(256) zero1_reduce_shard_bf16_kernel(const ZPee
         float4* o = reinterpret_cast<float4*>(out + (i << 3));
         o[0] = make_float4(acc[0], acc[1], acc[2], acc[3]);
         o[1] = make_float4(acc[4], acc[5], acc[6], acc[7]);
+        if (partials) add_squares<8>(acc, i << 3, split_at, ss0, ss1);
     }
+    if (partials) store_block_sumsq(ss0, ss1, partials);
 }
 
-__global__ void __launch_bounds__(256) zero1_reduce_shard_f32_kernel(const ZPeers g, size_t lo, size_t n, float* __restrict__ out) {
+__global__ void __launch_bounds__(256) zero1_reduce_shard_f32_kernel(const ZPeers g, size_t lo, size_t n, float* __restrict__ out,
+                                                                     size_t split_at, float* __restrict__ partials) {
     const size_t nvec = n >> 2;
+    float ss0 = 0.f, ss1 = 0.f;
     for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (size_t)gridDim.x * blockDim.x) {
         float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
@@ -77,6 +128,41 @@ __global__ void __launch_bounds__(256) zero1_reduce_shard_f32_kernel(const ZPeer
             }
         }
         reinterpret_cast<float4*>(out)[i] = acc;
+        if (partials) {
+            const float a4[4] = {acc.x, acc.y, acc.z, acc.w};
+            add_squares<4>(a4, i << 2, split_at, ss0, ss1);
+        }
+    }
+    if (partials) store_block_sumsq(ss0, ss1, partials);
+}
+
+// sums[0] += sum of partials[2 b], sums[1] += sum of partials[2 b + 1] over the blocks, in a fixed order
+__global__ void __launch_bounds__(256) zero1_sumsq_finish_kernel(const float* __restrict__ partials, int blocks,
+                                                                 float* __restrict__ sum_sharded,
+                                                                 float* __restrict__ sum_replicated) {
+    __shared__ float red[2][8];
+    float a = 0.f, b = 0.f;
+    for (int i = threadIdx.x; i < blocks; i += 256) {
+        a += partials[2 * i];
+        b += partials[2 * i + 1];
+    }
+    a = warp_sum(a);
+    b = warp_sum(b);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (lane == 0) {
+        red[0][warp] = a;
+        red[1][warp] = b;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        float x = 0.f, y = 0.f;
+#pragma unroll
+        for (int w = 0; w < 8; ++w) {
+            x += red[0][w];
+            y += red[1][w];
+        }
+        sum_sharded[0] += x;
+        sum_replicated[0] += y;
     }
 }
 
@@ -147,17 +233,45 @@ inline int zero1_blocks(size_t nvec) {
 
 // out[0 .. n) (fp32, local) = sum over ranks r of grad_r[lo .. lo + n).  grad_ptrs: dp pointers to every rank's flat
 // gradient buffer (symmetric memory; [rank] local), grad_dtype 0 = fp32, 1 = bf16; lo and n in ELEMENTS, multiples of 8.
-NXD_API int nxd_zero1_reduce_shard(void* const* grad_ptrs, int grad_dtype, long long lo, long long n, float* out, int dp,
-                                   int rank, void* stream) {
+static int zero1_reduce_impl(void* const* grad_ptrs, int grad_dtype, long long lo, long long n, float* out, int dp, int rank,
+                             long long split_at, float* partials, cudaStream_t s) {
     NXD_REQUIRE(lo >= 0 && n >= 0 && lo % 8 == 0 && n % 8 == 0, "zero1_reduce_shard: lo / n must be multiples of 8");
     if (n == 0) return 0;
     ZPeers z{};
     if (int rc = fill_peers(z, grad_ptrs, dp, rank)) return rc;
-    cudaStream_t s = (cudaStream_t)stream;
     if (grad_dtype == 1)
-        zero1_reduce_shard_bf16_kernel<<<zero1_blocks((size_t)n >> 3), 256, 0, s>>>(z, (size_t)lo, (size_t)n, out);
+        zero1_reduce_shard_bf16_kernel<<<zero1_blocks((size_t)n >> 3), 256, 0, s>>>(z, (size_t)lo, (size_t)n, out,
+                                                                                    (size_t)split_at, partials);
     else
-        zero1_reduce_shard_f32_kernel<<<zero1_blocks((size_t)n >> 2), 256, 0, s>>>(z, (size_t)lo, (size_t)n, out);
+        zero1_reduce_shard_f32_kernel<<<zero1_blocks((size_t)n >> 2), 256, 0, s>>>(z, (size_t)lo, (size_t)n, out,
+                                                                                   (size_t)split_at, partials);
+    NXD_LAUNCH_CHECK();
+    return 0;
+}
+
+NXD_API int nxd_zero1_reduce_shard(void* const* grad_ptrs, int grad_dtype, long long lo, long long n, float* out, int dp,
+                                   int rank, void* stream) {
+    return zero1_reduce_impl(grad_ptrs, grad_dtype, lo, n, out, dp, rank, 0, nullptr, (cudaStream_t)stream);
+}
+
+// Blocks the reduce kernel launches for a shard of n elements: the caller provides 2 * blocks floats of scratch.
+NXD_API int nxd_zero1_reduce_blocks(long long n, int grad_dtype) {
+    return zero1_blocks((size_t)n >> (grad_dtype == 1 ? 3 : 2));
+}
+
+// The same reduction with the local part of the gradient norm folded in: sum_sharded[0] += sum of out[i]^2 for
+// i < split_at, sum_replicated[0] += the same for i >= split_at (both accumulate; out is the UNAVERAGED sum over the
+// ranks).  partials: 2 * nxd_zero1_reduce_blocks(n, grad_dtype) floats of scratch.  0 <= split_at <= n.
+NXD_API int nxd_zero1_reduce_shard_sumsq(void* const* grad_ptrs, int grad_dtype, long long lo, long long n, float* out,
+                                         int dp, int rank, long long split_at, float* partials, float* sum_sharded,
+                                         float* sum_replicated, void* stream) {
+    NXD_REQUIRE(partials && sum_sharded && sum_replicated && split_at >= 0 && split_at <= n,
+                "zero1_reduce_shard_sumsq: scratch / outputs missing or split_at %lld outside [0, %lld]", split_at, n);
+    if (n == 0) return 0;
+    if (int rc = zero1_reduce_impl(grad_ptrs, grad_dtype, lo, n, out, dp, rank, split_at, partials, (cudaStream_t)stream))
+        return rc;
+    zero1_sumsq_finish_kernel<<<1, 256, 0, (cudaStream_t)stream>>>(partials, nxd_zero1_reduce_blocks(n, grad_dtype),
+                                                                  sum_sharded, sum_replicated);
     NXD_LAUNCH_CHECK();
     return 0;
 }

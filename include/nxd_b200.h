@@ -177,6 +177,12 @@ int nxd_gemm_a2a_bf16(int layout, const void* x, const void* w, int R, int C, in
  * brackets the pair with nxd_symm_barrier. */
 int nxd_zero1_reduce_shard(void* const* grad_ptrs, int grad_dtype, long long lo, long long n, float* out, int dp, int rank,
                            void* stream);
+/* The same reduction with the local part of the gradient norm folded in: sum_sharded[0] += sum of out[i]^2
+ * for i < split_at, sum_replicated[0] += the rest; partials = 2 * nxd_zero1_reduce_blocks(n, dtype) floats of scratch. */
+int nxd_zero1_reduce_blocks(long long n, int grad_dtype);
+int nxd_zero1_reduce_shard_sumsq(void* const* grad_ptrs, int grad_dtype, long long lo, long long n, float* out, int dp,
+                                 int rank, long long split_at, float* partials, float* sum_sharded, float* sum_replicated,
+                                 void* stream);
 int nxd_zero1_adamw_allgather(float* master, float* exp_avg, float* exp_avg_sq, const float* grad,
                               void* const* param_ptrs, long long lo, long long n, float lr, float beta1, float beta2,
                               float eps, float weight_decay, int step, float grad_scale, const float* clip_coef, int dp,

@@ -341,12 +341,23 @@ class NeuronZero1Optimizer(torch.optim.Optimizer):
             import ctypes as _c
 
             fused[0].symm.barrier()      # every rank's gradients are complete before anyone pulls them
+            # the pull-reduce also squares what it has just summed, so the local part of the gradient norm
+            # costs no pass of its own over the fp32 shard (_compute_clip skips these buckets)
+            s, sd = self._scalars["sumsq"], self._scalars["sumsq_dup"]
+            s.zero_()
+            sd.zero_()
             for b in fused:
-                rc = _lib.lib().nxd_zero1_reduce_shard(
-                    b.grad_ptrs, _c.c_int(1 if b.flat_grad.dtype == torch.bfloat16 else 0), _c.c_longlong(b.lo),
-                    _c.c_longlong(b.shard_size), _lib.ptr(b.grad_shard), _c.c_int(b.dp), _c.c_int(b.dp_rank),
-                    _lib.stream_ptr())
-                _lib.check(rc, "nxd_zero1_reduce_shard")
+                dt = 1 if b.flat_grad.dtype == torch.bfloat16 else 0
+                if getattr(b, "sumsq_partials", None) is None:
+                    nblk = int(_lib.lib().nxd_zero1_reduce_blocks(_c.c_longlong(b.shard_size), _c.c_int(dt)))
+                    b.sumsq_partials = torch.zeros(2 * nblk, dtype=torch.float32, device=b.device)
+                split_at = min(max(b.sp_begin - b.lo, 0), b.shard_size)
+                rc = _lib.lib().nxd_zero1_reduce_shard_sumsq(
+                    b.grad_ptrs, _c.c_int(dt), _c.c_longlong(b.lo), _c.c_longlong(b.shard_size), _lib.ptr(b.grad_shard),
+                    _c.c_int(b.dp), _c.c_int(b.dp_rank), _c.c_longlong(split_at), _lib.ptr(b.sumsq_partials), _lib.ptr(s),
+                    _lib.ptr(sd), _lib.stream_ptr())
+                _lib.check(rc, "nxd_zero1_reduce_shard_sumsq")
+            self._fused_sumsq = True
         for b in self.buckets:
             if b.dp == 1 or b.symm is not None:
                 continue
@@ -361,9 +372,14 @@ class NeuronZero1Optimizer(torch.optim.Optimizer):
         """Global grad norm over shard/TP/PP groups; replicated params count 1/tp.  Returns the clip
         coefficient tensor (device) or ``None`` when clipping is off."""
         s, sd = self._scalars["sumsq"], self._scalars["sumsq_dup"]
-        s.zero_()
-        sd.zero_()
+        fused_done = getattr(self, "_fused_sumsq", False)       # set by _reduce_scatter_grads: s / sd already hold the
+        self._fused_sumsq = False                                # sums of the buckets reduced by the fused kernel
+        if not fused_done:
+            s.zero_()
+            sd.zero_()
         for b in self.buckets:
+            if fused_done and b.symm is not None:
+                continue
             a0, a1 = b.local_range(0, b.sp_begin)
             d0, d1 = b.local_range(b.sp_begin, b.used)
             if a1 > a0:

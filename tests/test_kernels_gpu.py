@@ -280,6 +280,40 @@ def test_optimizer_kernels():
 # ---------------------------------------------------------------------------------------------
 
 @pytest.mark.parametrize("dt", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("n,split_at", [(8192, 0), (8192, 8192), (100_000, 12_345), (3_000_000, 1_000_003)])
+def test_zero1_reduce_shard_with_fused_sumsq(dt, n, split_at):
+    """the ZeRO-1 pull-reduce with the sum of squares folded in, run with a one-rank "group" (the peer table
+    holds the local buffer): the shard equals the fp32 cast of the gradient slice, the two sums of squares (before /
+    from ``split_at`` on, any alignment) equal the fp64 sums and ACCUMULATE into their outputs, bitwise reproducible."""
+    import ctypes as c
+
+    lib = _lib()
+    n = n // 8 * 8
+    lo = 1024
+    g = (torch.randn(lo + n + 64, device="cuda") * 3).to(dt)
+    out = torch.empty(n, device="cuda", dtype=torch.float32)
+    dtc = 1 if dt == torch.bfloat16 else 0
+    blocks = int(lib.lib().nxd_zero1_reduce_blocks(c.c_longlong(n), c.c_int(dtc)))
+    partials = torch.zeros(2 * blocks, device="cuda", dtype=torch.float32)
+    sums = []
+    for _ in range(2):
+        s0 = torch.full((1,), 5.0, device="cuda")
+        s1 = torch.full((1,), 7.0, device="cuda")
+        ptrs = (c.c_void_p * 1)(g.data_ptr())
+        rc = lib.lib().nxd_zero1_reduce_shard_sumsq(ptrs, c.c_int(dtc), c.c_longlong(lo), c.c_longlong(n), lib.ptr(out),
+                                                    c.c_int(1), c.c_int(0), c.c_longlong(split_at), lib.ptr(partials),
+                                                    lib.ptr(s0), lib.ptr(s1), lib.stream_ptr())
+        lib.check(rc, "nxd_zero1_reduce_shard_sumsq")
+        sums.append((float(s0), float(s1)))
+    ref = g[lo:lo + n].float()
+    assert torch.equal(out, ref)
+    r0 = float(ref[:split_at].double().pow(2).sum()) + 5.0
+    r1 = float(ref[split_at:].double().pow(2).sum()) + 7.0
+    assert abs(sums[0][0] - r0) <= 1e-4 * max(1.0, r0) and abs(sums[0][1] - r1) <= 1e-4 * max(1.0, r1), (sums, r0, r1)
+    assert sums[0] == sums[1]
+
+
+@pytest.mark.parametrize("dt", [torch.float32, torch.bfloat16])
 def test_sampling(dt):
     from neuronx_distributed_llama3_2_b200.ops import sampling
 
