@@ -24,6 +24,7 @@ struct CacheView {
     const bf16* k;
     const bf16* v;
     const int* block_table;  // null -> contiguous
+    const int* seq_ids;      // null -> cache line (contiguous) / block-table row (paged) = batch row
     long long stride_b;      // elements between batches (contiguous) / between pages (paged)
     long long stride_h;      // elements between kv heads
     int page_size;
@@ -32,11 +33,12 @@ struct CacheView {
 
 __device__ __forceinline__ const bf16* row_ptr(const bf16* base, const CacheView& c, int b, int h, int pos,
                                                int D) {
+    const int line = c.seq_ids ? c.seq_ids[b] : b;     // continuous batching: batch row -> cache line, no gathered copy
     if (c.block_table) {
-        const int page = c.block_table[(size_t)b * c.max_pages + pos / c.page_size];
+        const int page = c.block_table[(size_t)line * c.max_pages + pos / c.page_size];
         return base + (size_t)page * c.stride_b + (size_t)h * c.stride_h + (size_t)(pos % c.page_size) * D;
     }
-    return base + (size_t)b * c.stride_b + (size_t)h * c.stride_h + (size_t)pos * D;
+    return base + (size_t)line * c.stride_b + (size_t)h * c.stride_h + (size_t)pos * D;
 }
 
 // Split-K decode attention, one pass over the cache rows [start, end) of one (sequence, kv head, head chunk).
@@ -466,17 +468,18 @@ NXD_API int nxd_decode_attn_num_splits(int B, int n_kv, int max_len) {
     return s;
 }
 
-// scratch: B * n_q * n_splits * (D + 2) floats.
-NXD_API int nxd_decode_attn(const void* q, const void* cache_k, const void* cache_v, const int* lengths,
-                            const int* block_table, long long stride_b, long long stride_h, int page_size,
-                            int max_pages, void* out, float* scratch, int B, int n_q, int n_kv, int D,
+// scratch: B * n_q * n_splits * (D + 2) floats.  seq_ids: [B] int32 cache line (contiguous cache) or block-table row
+// (paged cache) of every batch row, NULL = the row index (continuous batching reads the lines in place).
+static int decode_attn_impl(const void* q, const void* cache_k, const void* cache_v, const int* lengths,
+                            const int* block_table, const int* seq_ids, long long stride_b, long long stride_h,
+                            int page_size, int max_pages, void* out, float* scratch, int B, int n_q, int n_kv, int D,
                             int n_splits, float scale, void* stream) {
     NXD_REQUIRE(D == 64 || D == 128, "decode_attn: head dim %d not in {64, 128}", D);
     NXD_REQUIRE(n_q % n_kv == 0 && n_q / n_kv <= kMaxGroup, "decode_attn: unsupported GQA group %d/%d", n_q, n_kv);
     NXD_REQUIRE(scratch != nullptr && n_splits >= 1, "decode_attn: scratch required");
     if (B == 0) return 0;
     cudaStream_t s = (cudaStream_t)stream;
-    CacheView cv{(const bf16*)cache_k, (const bf16*)cache_v, block_table, stride_b, stride_h,
+    CacheView cv{(const bf16*)cache_k, (const bf16*)cache_v, block_table, seq_ids, stride_b, stride_h,
                  page_size > 0 ? page_size : 1, max_pages};
     float* part_o = scratch;
     float* part_ml = scratch + (size_t)B * n_q * n_splits * D;
@@ -547,6 +550,22 @@ NXD_API int nxd_decode_attn(const void* q, const void* cache_k, const void* cach
 #undef NXD_DECODE_LAUNCH
     NXD_LAUNCH_CHECK();
     return 0;
+}
+
+NXD_API int nxd_decode_attn(const void* q, const void* cache_k, const void* cache_v, const int* lengths,
+                            const int* block_table, long long stride_b, long long stride_h, int page_size,
+                            int max_pages, void* out, float* scratch, int B, int n_q, int n_kv, int D,
+                            int n_splits, float scale, void* stream) {
+    return decode_attn_impl(q, cache_k, cache_v, lengths, block_table, nullptr, stride_b, stride_h, page_size, max_pages, out,
+                            scratch, B, n_q, n_kv, D, n_splits, scale, stream);
+}
+
+NXD_API int nxd_decode_attn_lines(const void* q, const void* cache_k, const void* cache_v, const int* lengths,
+                                  const int* block_table, const int* seq_ids, long long stride_b, long long stride_h,
+                                  int page_size, int max_pages, void* out, float* scratch, int B, int n_q, int n_kv,
+                                  int D, int n_splits, float scale, void* stream) {
+    return decode_attn_impl(q, cache_k, cache_v, lengths, block_table, seq_ids, stride_b, stride_h, page_size, max_pages, out,
+                            scratch, B, n_q, n_kv, D, n_splits, scale, stream);
 }
 
 NXD_API int nxd_kv_cache_update(const void* new_k, const void* new_v, void* cache_k, void* cache_v,

@@ -91,6 +91,12 @@ int nxd_decode_attn(const void* q, const void* cache_k, const void* cache_v, con
                     const int* block_table, long long stride_b, long long stride_h, int page_size,
                     int max_pages, void* out, float* scratch, int B, int n_q, int n_kv, int D, int n_splits,
                     float scale, void* stream);
+/* Same with a cache-line table: seq_ids[b] = cache line (contiguous cache) or block-table row (paged cache) of batch
+ * row b (continuous batching reads the lines in place instead of gathering them first). */
+int nxd_decode_attn_lines(const void* q, const void* cache_k, const void* cache_v, const int* lengths,
+                          const int* block_table, const int* seq_ids, long long stride_b, long long stride_h,
+                          int page_size, int max_pages, void* out, float* scratch, int B, int n_q, int n_kv, int D,
+                          int n_splits, float scale, void* stream);
 int nxd_kv_cache_update(const void* new_k, const void* new_v, void* cache_k, void* cache_v, const int* positions,
                         const int* seq_ids, const int* block_table, long long stride_b, long long stride_h,
                         int page_size, int max_pages, int B, int n_kv, int T_new, int D, void* stream);

@@ -118,11 +118,8 @@ class KVCacheInferenceMixin:
         rows = seq_ids.long().repeat_interleave(T)
         lengths = (positions + 1).reshape(-1).to(torch.int32)
         q2 = q.reshape(B * T, nq, D).contiguous()
-        if self.kv_cache.paged:
-            o = attn_ops.decode_attention(q2, ck, cv, lengths, block_table=self.kv_cache.block_table[rows],
-                                          page_size=self.kv_cache.page_size)
-        else:
-            o = attn_ops.decode_attention(q2, ck.index_select(0, rows), cv.index_select(0, rows), lengths)
+        # every row reads the cache line of its sequence in place (T rows share a line: no gathered copies)
+        o = self._decode_attention(q2, ck, cv, rows, lengths)
         return attn.o_proj(o.reshape(B, T, nq * D))
 
     def _attention(self, layer_idx: int, attn, h: torch.Tensor, positions: torch.Tensor, seq_ids: torch.Tensor,
@@ -134,17 +131,8 @@ class KVCacheInferenceMixin:
             o = attn_ops.flash_attn_func(q.permute(0, 2, 1, 3), k.permute(0, 2, 1, 3), v.permute(0, 2, 1, 3), causal=True)
             o = o.permute(0, 2, 1, 3).reshape(B, T, nq * D)
         else:
-            if seq_ids is not None and not self.kv_cache.paged:
-                # continuous batching: rows of the step map to arbitrary cache lines
-                ck_b, cv_b = ck.index_select(0, seq_ids.long()), cv.index_select(0, seq_ids.long())
-                o = attn_ops.decode_attention(q[:, 0].contiguous(), ck_b, cv_b, lengths)
-            elif self.kv_cache.paged:
-                table = self.kv_cache.block_table if seq_ids is None else self.kv_cache.block_table[seq_ids.long()]
-                o = attn_ops.decode_attention(q[:, 0].contiguous(), ck, cv, lengths, block_table=table,
-                                              page_size=self.kv_cache.page_size)
-            else:
-                o = attn_ops.decode_attention(q[:, 0].contiguous(), ck, cv, lengths)
-            o = o.reshape(B, 1, nq * D)
+            # continuous batching: rows of the step map to arbitrary cache lines, which the kernel follows itself
+            o = self._decode_attention(q[:, 0].contiguous(), ck, cv, seq_ids, lengths).reshape(B, 1, nq * D)
         return attn.o_proj(o)
 
     def _add_norm(self, norm, hidden: torch.Tensor, residual: Optional[torch.Tensor]):
@@ -203,14 +191,11 @@ class KVCacheInferenceMixin:
         return memo[2], memo[3]
 
     def _decode_attention(self, q, ck, cv, seq_ids, lengths):
+        """Attention of one new token per row over its cache line; with continuous batching the kernel follows
+        ``seq_ids`` itself (reference ``attention_base.py:141-170`` gathers nothing either: its cache is per line)."""
         kc = self.kv_cache
-        if kc.paged:
-            t = kc.block_table if seq_ids is None else kc.block_table[seq_ids.long()]
-            return attn_ops.decode_attention(q, ck, cv, lengths, block_table=t, page_size=kc.page_size)
-        if seq_ids is not None:
-            return attn_ops.decode_attention(q, ck.index_select(0, seq_ids.long()), cv.index_select(0, seq_ids.long()),
-                                             lengths)
-        return attn_ops.decode_attention(q, ck, cv, lengths)
+        return attn_ops.decode_attention(q, ck, cv, lengths, block_table=kc.block_table if kc.paged else None,
+                                         page_size=kc.page_size if kc.paged else 0, seq_ids=seq_ids)
 
     def _layer_batched_decode(self, i: int, layer, hidden, residual, positions, seq_ids, lengths):
         """One token per sequence for 9 .. 128 sequences on the small-M tensor-core kernels (``csrc/gemm_smallm.cu``):

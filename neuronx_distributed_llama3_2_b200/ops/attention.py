@@ -128,8 +128,10 @@ def kv_cache_update(cache_k: torch.Tensor, cache_v: torch.Tensor, new_k: torch.T
 
 def decode_attention(q: torch.Tensor, cache_k: torch.Tensor, cache_v: torch.Tensor, lengths: torch.Tensor,
                      softmax_scale: Optional[float] = None, block_table: Optional[torch.Tensor] = None,
-                     page_size: int = 0) -> torch.Tensor:
-    """One new token per sequence: q ``[B, Hq, D]`` attends to cache rows ``[0, lengths[b])``."""
+                     page_size: int = 0, seq_ids: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """One new token per sequence: q ``[B, Hq, D]`` attends to cache rows ``[0, lengths[b])``.  ``seq_ids [B]``
+    (continuous batching): batch row ``b`` reads cache line ``seq_ids[b]`` (contiguous cache) or block-table row
+    ``seq_ids[b]`` (paged cache) IN PLACE -- no gathered copy of the lines."""
     B, Hq, D = q.shape
     Hkv = cache_k.shape[1]
     scale = softmax_scale if softmax_scale is not None else 1.0 / math.sqrt(D)
@@ -147,13 +149,19 @@ def decode_attention(q: torch.Tensor, cache_k: torch.Tensor, cache_v: torch.Tens
         out = torch.empty_like(q)
         bt = block_table.to(torch.int32).contiguous() if block_table is not None else None
         qc = q.contiguous()
-        rc = _lib.lib().nxd_decode_attn(
-            _lib.ptr(qc), _lib.ptr(cache_k), _lib.ptr(cache_v), _lib.ptr(lens), _lib.ptr(bt),
+        sid = seq_ids.to(torch.int32).contiguous() if seq_ids is not None else None
+        rc = _lib.lib().nxd_decode_attn_lines(
+            _lib.ptr(qc), _lib.ptr(cache_k), _lib.ptr(cache_v), _lib.ptr(lens), _lib.ptr(bt), _lib.ptr(sid),
             _c.c_longlong(cache_k.stride(0)), _c.c_longlong(cache_k.stride(1)), _c.c_int(page_size),
             _c.c_int(bt.shape[1] if bt is not None else 0), _lib.ptr(out), _lib.ptr(scratch), _c.c_int(B),
             _c.c_int(Hq), _c.c_int(Hkv), _c.c_int(D), _c.c_int(n_splits), _c.c_float(scale), _lib.stream_ptr())
-        _lib.check(rc, "nxd_decode_attn")
+        _lib.check(rc, "nxd_decode_attn_lines")
         return out
+    if seq_ids is not None:      # reference path: gather the lines (or the table rows), then the plain oracle
+        if block_table is not None:
+            block_table = block_table[seq_ids.long()]
+        else:
+            cache_k, cache_v = cache_k.index_select(0, seq_ids.long()), cache_v.index_select(0, seq_ids.long())
     return decode_attention_ref(q, cache_k, cache_v, lengths, scale, block_table, page_size)
 
 

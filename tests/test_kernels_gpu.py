@@ -404,6 +404,12 @@ def test_decode_attention_gqa_groups(group, D):
     assert _rel_err(out, ref) < 1e-2
     for b in range(B):
         assert _rel_err(out[b], ref[b]) < 2e-2, (b, int(lens_safe[b]))
+    # continuous batching: row b reads cache line seq_ids[b] in place (lines repeated, as in speculation verify)
+    lines = torch.tensor([3, 3, 0, 8, 1, 1, 1, 5, 2], device="cuda", dtype=torch.int32)
+    out_l = A.decode_attention(q, ck, cv, lens_safe, seq_ids=lines)
+    ref_l = A.decode_attention_ref(q, ck.index_select(0, lines.long()), cv.index_select(0, lines.long()), lens_safe,
+                                   1.0 / math.sqrt(D))
+    assert _rel_err(out_l, ref_l) < 1e-2
 
 
 # ---------------------------------------------------------------------------------------------
@@ -652,10 +658,12 @@ def test_smallm_qkv_rope_cache(B, D, nq, nkv, paged, splits):
         cv = torch.zeros_like(ck)
         table = torch.randperm(n_pages, device="cuda").reshape(B, S // page).to(torch.int32)
     else:
-        ck = torch.zeros(B, nkv, S, D, device="cuda", dtype=torch.bfloat16)
+        ck = torch.zeros(B + 3, nkv, S, D, device="cuda", dtype=torch.bfloat16)     # more cache lines than rows
         cv = torch.zeros_like(ck)
         table = None
-    q = decode_fused.qkv_rope_cache_batched(xn, w, cos, sin, pos, ck, cv, nq, nkv, D, block_table=table,
+    # continuous batching: row b writes cache line seq_ids[b] (a permutation that is not the identity)
+    lines = torch.randperm(B if paged else B + 3, device="cuda")[:B].to(torch.int32)
+    q = decode_fused.qkv_rope_cache_batched(xn, w, cos, sin, pos, ck, cv, nq, nkv, D, seq_ids=lines, block_table=table,
                                             page_size=page if paged else 0, splits=splits)
     qkv = (xn.float() @ w.float().t()).reshape(B, nq + 2 * nkv, D)
     c, s_ = cos[pos.long()], sin[pos.long()]                       # [B, D/2]
@@ -664,11 +672,12 @@ def test_smallm_qkv_rope_cache(B, D, nq, nkv, paged, splits):
     assert (q.float() - rot[:, :nq]).abs().max() < 3e-2
     for b in range(B):
         p = int(pos[b])
+        line = int(lines[b])
         if paged:
-            krow = ck[int(table[b, p // page]), :, p % page]
-            vrow = cv[int(table[b, p // page]), :, p % page]
+            krow = ck[int(table[line, p // page]), :, p % page]
+            vrow = cv[int(table[line, p // page]), :, p % page]
         else:
-            krow, vrow = ck[b, :, p], cv[b, :, p]
+            krow, vrow = ck[line, :, p], cv[line, :, p]
         assert (krow.float() - rot[b, nq:]).abs().max() < 3e-2
         assert (vrow.float() - qkv[b, nq + nkv:]).abs().max() < 3e-2
     assert int((ck != 0).any(-1).sum()) == B * nkv        # exactly one row per (sequence, kv head) was written
