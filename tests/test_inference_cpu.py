@@ -408,47 +408,6 @@ def test_dbrx_generation_matches_recompute_and_hf_key_conversion():
     assert set(back) == set(sd) and all(torch.equal(back[k], sd[k]) for k in sd)
 
 
-def test_weight_layout_transform_between_graphs(tmp_path):
-    """C48: the priority graph's layout choice becomes (a) a map applied to the other graphs and (b) a stand-alone
-    load-time transform over ALL weights, in index order, untouched weights passed through."""
-    from neuronx_distributed_llama3_2_b200.inference import hlo_utils as hu
-
-    class Toy(torch.nn.Module):
-        def __init__(self):
-            super().__init__()
-            self.experts = torch.nn.Parameter(torch.randn(4, 8, 6))      # [E, in, out]
-            self.dense = torch.nn.Parameter(torch.randn(6, 8))
-            self.norm = torch.nn.Parameter(torch.ones(8))
-
-    m = Toy()
-    m.experts.preferred_layout_perm = (0, 2, 1)                           # decode wants [E, out, in]
-    prio = hu.new_graph("token_generation_model", m, graph_id=10)
-    name_to_idx = hu.weight_name_to_idx_of(prio)
-    hu.add_weight_idx_attr_to_hlo(prio, {k: v for k, v in name_to_idx.items() if k != "norm"})
-    assert prio["frontend_attributes"][hu.TRANSPOSABLE_WEIGHT_IDX] == "0,1"
-    hu.suggest_layout_transforms(prio, m)
-    hu.write_hlo(prio, tmp_path / "prio.json")
-    prio = hu.read_hlo(tmp_path / "prio.json")
-    tmap = hu.get_layout_transform_map(prio, name_to_idx)
-    assert set(tmap) == {"experts"} and tmap["experts"]["perm"] == [0, 2, 1]
-    moved = hu.update_computation_id_and_name(tmap["experts"], 100, "wlt_")
-    assert moved["id"] == tmap["experts"]["id"] + 100 and moved["name"].startswith("wlt_")
-    assert moved["instructions"][1]["operand_ids"] == [moved["instructions"][0]["id"]] and tmap["experts"]["name"] == "layout_0"
-    other = hu.append_layout_computation_to_hlo(hu.new_graph("context_encoding_model", m, graph_id=20), tmap)
-    assert other["frontend_attributes"][hu.REQUIRE_TRANSPOSE_WEIGHT_IDX] == "0"
-    assert other["frontend_attributes"][hu.REQUIRE_TRANSPOSE_CUSTOM_CALL] == "wlt_layout_0"
-    ids = [i["id"] for c in other["computations"] for i in c["instructions"]] + [c["id"] for c in other["computations"]]
-    assert len(set(ids)) == len(ids) and min(ids) > 20
-    wlt = hu.extract_weight_layout_transform_hlo(prio, name_to_idx)
-    meta = hu.prepare_metaneff_for_wlt_hlo(wlt, name_to_idx)
-    assert [t["checkpoint_key"] for t in meta["input_tensors"]] == ["experts", "dense", "norm"]
-    assert meta["output_tensors"][0]["shape"] == [4, 6, 8] and meta["output_tensors"][1]["shape"] == [6, 8]
-    sd = {k: v.detach().clone() for k, v in m.state_dict().items()}
-    out = hu.run_weight_layout_transform(wlt, sd)
-    assert torch.equal(out["experts"], sd["experts"].transpose(1, 2)) and out["experts"].is_contiguous()
-    assert out["dense"] is sd["dense"] and out["norm"] is sd["norm"]
-
-
 def test_family_runners_and_quantized_runner():
     """``MixtralRunner`` drives the MoE KV-cache model through the same trace / generate path; a quantized Llama runner
     swaps the decoder linears for int8 weight-only layers, quantizes the float checkpoint on load and stays close to
