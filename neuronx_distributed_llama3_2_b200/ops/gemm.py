@@ -93,7 +93,7 @@ def gemm_smallm(x: torch.Tensor, w: torch.Tensor, residual: Optional[torch.Tenso
     ``parallel_layers/layers.py`` at ``[batch, 1, hidden]``).  ``None`` when the shape does not qualify."""
     B, K = x.shape
     N = w.shape[0]
-    if (B == 0 or B > SMALLM_MAX_ROWS or x.dtype != torch.bfloat16 or w.dtype != torch.bfloat16 or K % 8
+    if (not (x.is_cuda and w.is_cuda) or B == 0 or B > SMALLM_MAX_ROWS or x.dtype != torch.bfloat16 or w.dtype != torch.bfloat16 or K % 8
             or x.stride(1) != 1 or w.stride(1) != 1 or x.stride(0) % 8 or w.stride(0) % 8
             or x.data_ptr() % 16 or w.data_ptr() % 16):
         return None
